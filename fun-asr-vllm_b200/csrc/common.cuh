@@ -1,0 +1,96 @@
+// Shared host/device helpers for libfunasr_b200 (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+
+#include "../../include/funasr_b200.h"
+
+namespace fa {
+
+// ---- host-side error plumbing --------------------------------------------------------------
+void set_error(const char* fmt, ...);
+
+#define FA_CHECK_CUDA(expr)                                                                 \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess) {                                                                \
+      fa::set_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__, cudaGetErrorString(_e)); \
+      return 1;                                                                             \
+    }                                                                                       \
+  } while (0)
+
+#define FA_REQUIRE(cond, ...)          \
+  do {                                 \
+    if (!(cond)) {                     \
+      fa::set_error(__VA_ARGS__);      \
+      return 2;                        \
+    }                                  \
+  } while (0)
+
+#define FA_CHECK_LAUNCH() FA_CHECK_CUDA(cudaGetLastError())
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+int sm_count();
+
+// ---- internal launchers shared between api.cu and the op entry points -----------------------
+struct GemmEpilogue {
+  const float* bias = nullptr;  // [N]
+  const float* res1 = nullptr;  // f32 [M, N] (row stride ldc)
+  const float* res2 = nullptr;  // f32 [M, N]
+  int relu = 0;
+  int out_f32 = 0;
+};
+
+struct TensorMap2D {  // opaque 128-byte CUtensorMap
+  alignas(64) unsigned char bytes[128];
+};
+
+// rows x cols bf16 matrix, row stride ld (elements); box = box_rows x 64 cols, 128B swizzle.
+int make_tensor_map_bf16(TensorMap2D* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                         uint32_t box_rows);
+
+int gemm_block_n(int M, int N);  // tile-N heuristic (64 / 128 / 256)
+int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, int block_n, int M, int N, int K,
+                const GemmEpilogue& epi, void* c, int64_t ldc, cudaStream_t stream);
+
+int launch_layernorm(const float* x, const float* g, const float* b, const float* g2, const float* b2,
+                     __nv_bfloat16* y_bf16, float* y_f32, int M, int D, cudaStream_t stream);
+int launch_embed_layernorm(const float* x, const float* inv_ts, const int32_t* cu, int n_utts, float scale,
+                           const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream);
+int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts,
+                float* mem, int M, int D, int kernel, int left_pad, cudaStream_t stream);
+int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int max_len,
+                     int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, cudaStream_t stream);
+int launch_cast_bf16(const float* x, __nv_bfloat16* y, int64_t n, cudaStream_t stream);
+int launch_copy_f32(const float* x, float* y, int64_t n, cudaStream_t stream);
+
+}  // namespace fa
+
+// ---- device helpers --------------------------------------------------------------------------
+#ifdef __CUDACC__
+namespace fa {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+}  // namespace fa
+#endif

@@ -1,0 +1,319 @@
+// HBM/L2-bound row kernels of the SAN-M encoder: LayerNorm (+ fused input scaling / positional
+// encoding, + fused second LayerNorm), FSMN depthwise memory block, row metadata, casts, splice.
+// All work on PACKED rows; utterance boundaries come from cu_seqlens / row_meta.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace fa {
+namespace ew {
+
+constexpr int LN_MAX_D = 1024;
+constexpr int LN_VEC = LN_MAX_D / 128;  // float4 per lane
+
+// ---------------------------------------------------------------- utterance lookup
+// (first row, one-past-last row) of the utterance owning packed row r; cu_seqlens is tiny and
+// L1-resident, so a binary search per row is cheaper than materialising a per-row table.
+__device__ __forceinline__ int2 utt_bounds(const int32_t* __restrict__ cu, int n_utts, int r) {
+  int lo = 0, hi = n_utts;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(cu + mid) <= r) lo = mid; else hi = mid;
+  }
+  return make_int2(__ldg(cu + lo), __ldg(cu + lo + 1));
+}
+
+// ---------------------------------------------------------------- LayerNorm (eps 1e-12)
+// One warp per row, the row lives in registers.  Optional fused pre-op (x*scale + PE(pos)) and an
+// optional second LayerNorm applied to the first one's output (after_norm -> next norm1).
+struct LnArgs {
+  const float* x;
+  const float* g;
+  const float* b;
+  const float* g2;  // second LN (nullable)
+  const float* b2;
+  __nv_bfloat16* y_bf16;  // output of the LAST LN (nullable)
+  float* y_f32;           // output of the FIRST LN (nullable)
+  const float* inv_ts;    // positional encoding (nullable)
+  const int32_t* cu;
+  int n_utts;
+  float scale;
+  int M, D;
+};
+
+__device__ __forceinline__ void ln_stats(const float4 (&v)[LN_VEC], int nvec, int lane, int D, float& mean, float& rstd) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_VEC; ++i)
+    if (lane + 32 * i < nvec) s += v[i].x + v[i].y + v[i].z + v[i].w;
+  mean = warp_sum(s) / static_cast<float>(D);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_VEC; ++i)
+    if (lane + 32 * i < nvec) {
+      const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+      q += a * a + b * b + c * c + d * d;
+    }
+  const float var = warp_sum(q) / static_cast<float>(D);
+  rstd = rsqrtf(var + 1e-12f);  // VLLM/model_executor/models/funasr.py:85 eps=1e-12
+}
+
+template <bool EMBED>
+__global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= a.M) return;
+  const int D = a.D, nvec = D >> 2;
+  const float4* xr = reinterpret_cast<const float4*>(a.x + static_cast<int64_t>(row) * D);
+  float4 v[LN_VEC];
+#pragma unroll
+  for (int i = 0; i < LN_VEC; ++i) {
+    const int c = lane + 32 * i;
+    v[i] = (c < nvec) ? xr[c] : make_float4(0, 0, 0, 0);
+  }
+  if (EMBED) {
+    // xs * sqrt(d_model) + [sin(p*inv) | cos(p*inv)],  p = 1..T within the utterance
+    // (VLLM/model_executor/models/funasr.py:388-390, 256-290); fp32 like the reference.
+    const float pos = static_cast<float>(row - utt_bounds(a.cu, a.n_utts, row).x + 1);
+    const int half = D >> 1;
+#pragma unroll
+    for (int i = 0; i < LN_VEC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        float* e = reinterpret_cast<float*>(&v[i]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int col = 4 * c + k;
+          const float ang = pos * __ldg(a.inv_ts + (col < half ? col : col - half));
+          const float pe = col < half ? sinf(ang) : cosf(ang);
+          e[k] = e[k] * a.scale + pe;
+        }
+      }
+    }
+  }
+  float mean, rstd;
+  ln_stats(v, nvec, lane, D, mean, rstd);
+#pragma unroll
+  for (int i = 0; i < LN_VEC; ++i) {
+    const int c = lane + 32 * i;
+    if (c < nvec) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(a.g) + c);
+      const float4 b = __ldg(reinterpret_cast<const float4*>(a.b) + c);
+      v[i].x = (v[i].x - mean) * rstd * g.x + b.x;
+      v[i].y = (v[i].y - mean) * rstd * g.y + b.y;
+      v[i].z = (v[i].z - mean) * rstd * g.z + b.z;
+      v[i].w = (v[i].w - mean) * rstd * g.w + b.w;
+      if (a.y_f32) reinterpret_cast<float4*>(a.y_f32 + static_cast<int64_t>(row) * D)[c] = v[i];
+    }
+  }
+  if (a.g2) {
+    ln_stats(v, nvec, lane, D, mean, rstd);
+#pragma unroll
+    for (int i = 0; i < LN_VEC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        const float4 g = __ldg(reinterpret_cast<const float4*>(a.g2) + c);
+        const float4 b = __ldg(reinterpret_cast<const float4*>(a.b2) + c);
+        v[i].x = (v[i].x - mean) * rstd * g.x + b.x;
+        v[i].y = (v[i].y - mean) * rstd * g.y + b.y;
+        v[i].z = (v[i].z - mean) * rstd * g.z + b.z;
+        v[i].w = (v[i].w - mean) * rstd * g.w + b.w;
+      }
+    }
+  }
+  if (a.y_bf16) {
+    uint2* yr = reinterpret_cast<uint2*>(a.y_bf16 + static_cast<int64_t>(row) * D);
+#pragma unroll
+    for (int i = 0; i < LN_VEC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) yr[c] = make_uint2(pack_bf16x2(v[i].x, v[i].y), pack_bf16x2(v[i].z, v[i].w));
+    }
+  }
+}
+
+// ---------------------------------------------------------------- FSMN memory block
+// mem[t, c] = v[t, c] + sum_k w[c, k] * v[t + k - left, c]   (zero outside the utterance)
+// (VLLM/model_executor/models/funasr.py:181-201: mask, ConstantPad1d, depthwise Conv1d, +inputs, mask).
+// One thread owns a channel pair and walks FSMN_ROWS consecutive rows with the 2*K-1 tap window
+// held in registers, so every v element is loaded once per CTA (plus the halo).
+constexpr int FSMN_ROWS = 16;
+constexpr int FSMN_MAXK = 16;
+
+__global__ void __launch_bounds__(256)
+fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
+            const int32_t* __restrict__ cu, int n_utts, float* __restrict__ mem, int M, int D, int K, int left) {
+  const int cp = blockIdx.y * blockDim.x + threadIdx.x;  // channel pair
+  if (2 * cp >= D) return;
+  const int r0 = blockIdx.x * FSMN_ROWS;
+  float w0[FSMN_MAXK], w1[FSMN_MAXK];
+#pragma unroll
+  for (int k = 0; k < FSMN_MAXK; ++k) {
+    w0[k] = k < K ? __ldg(w + static_cast<int64_t>(2 * cp) * K + k) : 0.f;
+    w1[k] = k < K ? __ldg(w + static_cast<int64_t>(2 * cp + 1) * K + k) : 0.f;
+  }
+  const __nv_bfloat16* vbase = qkv + v_col + 2 * cp;
+  const int r1 = min(r0 + FSMN_ROWS, M);
+  for (int r = r0; r < r1; ++r) {
+    const int2 ub = utt_bounds(cu, n_utts, r);
+    float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < FSMN_MAXK; ++k) {
+      if (k < K) {
+        const int rr = r + k - left;
+        if (rr >= ub.x && rr < ub.y) {
+          const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(vbase + static_cast<int64_t>(rr) * ld));
+          a0 = fmaf(w0[k], f.x, a0);
+          a1 = fmaf(w1[k], f.y, a1);
+        }
+      }
+    }
+    const float2 self = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(vbase + static_cast<int64_t>(r) * ld));
+    *reinterpret_cast<float2*>(mem + static_cast<int64_t>(r) * D + 2 * cp) = make_float2(a0 + self.x, a1 + self.y);
+  }
+}
+
+// ---------------------------------------------------------------- casts / copies / splice
+__global__ void cast_bf16_kernel(const float4* __restrict__ x, uint2* __restrict__ y, int64_t n4) {
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const float4 v = x[i];
+    y[i] = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+  }
+}
+__global__ void copy_f32_kernel(const float4* __restrict__ x, float4* __restrict__ y, int64_t n4) {
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x)
+    y[i] = x[i];
+}
+
+template <typename T>
+__device__ __forceinline__ float ld_as_f32(const void* p, int64_t i);
+template <>
+__device__ __forceinline__ float ld_as_f32<float>(const void* p, int64_t i) { return static_cast<const float*>(p)[i]; }
+template <>
+__device__ __forceinline__ float ld_as_f32<__nv_bfloat16>(const void* p, int64_t i) {
+  return __bfloat162float(static_cast<const __nv_bfloat16*>(p)[i]);
+}
+
+// grid: (row within utterance output, utterance).  Row j of utterance b is prefix[j], speech
+// [cu[b] + j - P] or suffix[j - P - take]; torch.cat of infer.py:462-466 as one gather.
+__global__ void __launch_bounds__(256)
+splice_kernel(const void* __restrict__ speech, int speech_bf16, const int32_t* __restrict__ cu,
+              const int32_t* __restrict__ take, const void* __restrict__ prefix, int P, const void* __restrict__ suffix,
+              int S, const int64_t* __restrict__ out_off, int dim, void* __restrict__ out, int out_bf16) {
+  const int b = blockIdx.y, j = blockIdx.x;
+  const int len = cu[b + 1] - cu[b];
+  const int tk = take ? min(max(take[b], 0), len) : len;
+  if (j >= P + tk + S) return;
+  const void* src;
+  int64_t src_row;
+  int src_bf16;
+  if (j < P) { src = prefix; src_row = j; src_bf16 = out_bf16; }
+  else if (j < P + tk) { src = speech; src_row = cu[b] + (j - P); src_bf16 = speech_bf16; }
+  else { src = suffix; src_row = j - P - tk; src_bf16 = out_bf16; }
+  const int64_t orow = out_off[b] + j;
+  for (int c = threadIdx.x; c < dim; c += blockDim.x) {
+    const float v = src_bf16 ? ld_as_f32<__nv_bfloat16>(src, src_row * dim + c) : ld_as_f32<float>(src, src_row * dim + c);
+    if (out_bf16) static_cast<__nv_bfloat16*>(out)[orow * dim + c] = __float2bfloat16_rn(v);
+    else static_cast<float*>(out)[orow * dim + c] = v;
+  }
+}
+
+}  // namespace ew
+
+static int ln_check(int D, const void* x) {
+  FA_REQUIRE(D % 4 == 0 && D <= ew::LN_MAX_D, "layernorm: D=%d must be a multiple of 4 and <= %d", D, ew::LN_MAX_D);
+  FA_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "layernorm: x must be 16-byte aligned");
+  return 0;
+}
+
+int launch_layernorm(const float* x, const float* g, const float* b, const float* g2, const float* b2,
+                     __nv_bfloat16* y_bf16, float* y_f32, int M, int D, cudaStream_t stream) {
+  if (int r = ln_check(D, x)) return r;
+  ew::LnArgs a{x, g, b, g2, b2, y_bf16, y_f32, nullptr, nullptr, 0, 1.f, M, D};
+  ew::layernorm_kernel<false><<<ceil_div(M, 8), 256, 0, stream>>>(a);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+int launch_embed_layernorm(const float* x, const float* inv_ts, const int32_t* cu, int n_utts, float scale,
+                           const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream) {
+  if (int r = ln_check(D, x)) return r;
+  ew::LnArgs a{x, g, b, nullptr, nullptr, y, nullptr, inv_ts, cu, n_utts, scale, M, D};
+  ew::layernorm_kernel<true><<<ceil_div(M, 8), 256, 0, stream>>>(a);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts,
+                float* mem, int M, int D, int kernel, int left_pad, cudaStream_t stream) {
+  FA_REQUIRE(kernel >= 1 && kernel <= ew::FSMN_MAXK, "fsmn: kernel size %d not in [1,%d]", kernel, ew::FSMN_MAXK);
+  FA_REQUIRE(D % 2 == 0 && v_col % 2 == 0 && ld % 2 == 0, "fsmn: D, v_col and ld must be even");
+  const int threads = 256;
+  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 2, threads));
+  ew::fsmn_kernel<<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, mem, M, D, kernel, left_pad);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+int launch_cast_bf16(const float* x, __nv_bfloat16* y, int64_t n, cudaStream_t stream) {
+  FA_REQUIRE(n % 4 == 0, "cast: element count must be a multiple of 4");
+  const int64_t n4 = n / 4;
+  const int blocks = static_cast<int>(n4 / 256 + 1 < 148 * 8 ? n4 / 256 + 1 : 148 * 8);
+  ew::cast_bf16_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<uint2*>(y), n4);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+int launch_copy_f32(const float* x, float* y, int64_t n, cudaStream_t stream) {
+  FA_REQUIRE(n % 4 == 0, "copy: element count must be a multiple of 4");
+  const int64_t n4 = n / 4;
+  const int blocks = static_cast<int>(n4 / 256 + 1 < 148 * 8 ? n4 / 256 + 1 : 148 * 8);
+  ew::copy_f32_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), n4);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace fa
+
+using namespace fa;
+
+extern "C" int fa_op_layernorm(const float* x_dev, const float* g_dev, const float* b_dev, void* y_bf16_dev,
+                               float* y_f32_dev, int32_t M, int32_t D, fa_stream_t stream) {
+  FA_REQUIRE(x_dev && g_dev && b_dev && M > 0, "layernorm: bad arguments");
+  return launch_layernorm(x_dev, g_dev, b_dev, nullptr, nullptr, static_cast<__nv_bfloat16*>(y_bf16_dev), y_f32_dev, M,
+                          D, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int fa_op_embed_layernorm(const float* x_dev, const float* inv_ts_dev, const int32_t* cu_seqlens_dev,
+                                     int32_t n_utts, float scale, const float* g_dev, const float* b_dev,
+                                     void* y_bf16_dev, int32_t M, int32_t D, fa_stream_t stream) {
+  FA_REQUIRE(x_dev && inv_ts_dev && cu_seqlens_dev && g_dev && b_dev && y_bf16_dev && M > 0 && n_utts > 0,
+             "embed_layernorm: bad arguments");
+  return launch_embed_layernorm(x_dev, inv_ts_dev, cu_seqlens_dev, n_utts, scale, g_dev, b_dev,
+                                static_cast<__nv_bfloat16*>(y_bf16_dev), M, D, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int fa_op_fsmn(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, const float* w_dev,
+                          const int32_t* cu_seqlens_dev, int32_t n_utts, float* mem_dev, int32_t M, int32_t D,
+                          int32_t kernel, int32_t left_pad, fa_stream_t stream) {
+  FA_REQUIRE(qkv_dev && w_dev && cu_seqlens_dev && mem_dev && M > 0 && n_utts > 0, "fsmn: bad arguments");
+  return launch_fsmn(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, v_col, w_dev, cu_seqlens_dev, n_utts, mem_dev,
+                     M, D, kernel, left_pad, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int fa_splice_embeds(const void* speech_dev, int32_t speech_bf16, const int32_t* cu_seqlens_dev,
+                                const int32_t* take_dev, const void* prefix_dev, int32_t n_prefix,
+                                const void* suffix_dev, int32_t n_suffix, const int64_t* out_off_dev, int32_t n_utts,
+                                int32_t dim, void* out_dev, int32_t out_bf16, int32_t max_rows_per_utt,
+                                fa_stream_t stream) {
+  FA_REQUIRE(speech_dev && cu_seqlens_dev && out_off_dev && out_dev && n_utts > 0 && dim > 0, "splice: bad arguments");
+  FA_REQUIRE((n_prefix == 0 || prefix_dev) && (n_suffix == 0 || suffix_dev), "splice: NULL prefix/suffix");
+  FA_REQUIRE(max_rows_per_utt > 0, "splice: max_rows_per_utt must be positive");
+  dim3 grid(max_rows_per_utt, n_utts);
+  ew::splice_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(speech_dev, speech_bf16, cu_seqlens_dev,
+                                                                         take_dev, prefix_dev, n_prefix, suffix_dev,
+                                                                         n_suffix, out_off_dev, dim, out_dev, out_bf16);
+  FA_CHECK_LAUNCH();
+  return 0;
+}

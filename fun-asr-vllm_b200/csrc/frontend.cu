@@ -1,0 +1,377 @@
+// Fused Kaldi fbank -> LFR -> CMVN frontend for sm_100a.
+//
+// One CTA produces FA_FE_TILE_ROWS low-frame-rate rows of one utterance:
+//   PCM (global, packed offsets) -> smem -> per frame {DC removal, pre-emphasis, window,
+//   512-pt real FFT as a 256-pt complex FFT (two radix-16 passes in registers, one smem
+//   transpose), power, sparse mel, log} -> smem log-mel tile -> LFR gather + CMVN -> global.
+// PCM is read once and the [T,560] features written once: no intermediate touches HBM.
+//
+// Arithmetic follows torchaudio.compliance.kaldi.fbank (TA:514-645, _get_window TA:154-217) and
+// funasr's apply_lfr / apply_cmvn (VLLM/transformers_utils/processors/funasr.py:40-60,23-37).
+#include <math.h>
+
+#include <cstring>
+
+#include "common.cuh"
+
+namespace fa {
+namespace fe {
+
+constexpr int FRAME_LEN = 400;
+constexpr int SHIFT = 160;
+constexpr int NFFT = 512;
+constexpr int NBIN = NFFT / 2 + 1;
+constexpr int NMEL = 80;
+constexpr int LFR_M = 7;
+constexpr int LFR_N = 6;
+constexpr int LFR_LEFT = (LFR_M - 1) / 2;
+constexpr int FEAT = LFR_M * NMEL;  // 560
+constexpr int TILE_ROWS = FA_FE_TILE_ROWS;
+constexpr int MAX_FRAMES = LFR_N * (TILE_ROWS - 1) + LFR_M;        // 31
+constexpr int RAW_TILE_FRAMES = 30;                                  // raw log-mel mode
+constexpr int MAX_SAMPLES = (MAX_FRAMES - 1) * SHIFT + FRAME_LEN;    // 5200
+constexpr int THREADS = 256;
+constexpr int SLOTS = THREADS / 16;  // frames in flight per CTA (one per half-warp)
+constexpr int MAX_TAPS = 1024;
+
+struct __align__(16) Tables {
+  float window[FRAME_LEN];
+  float2 tw256[256];  // W256^k = (cos, -sin)(2 pi k / 256)
+  float2 tw512[136];  // W512^k, k = 0..128
+  int mel_start[NMEL];
+  int mel_count[NMEL];
+  int mel_woff[NMEL];
+  float mel_w[MAX_TAPS];
+};
+
+struct __align__(16) Smem {
+  float samples[MAX_SAMPLES + 8];
+  float logmel[MAX_FRAMES + 1][NMEL];
+  float2 work[SLOTS][272];  // 16x17 padded transpose buffer, then Z[0..255]
+  float power[SLOTS][264];
+  float window[FRAME_LEN];
+  float2 tw512[136];
+  float mel_w[MAX_TAPS];
+  int mel_start[NMEL];
+  int mel_count[NMEL];
+  int mel_woff[NMEL];
+};
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+  return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+
+// 4-point DFT in place: (a,b,c,d) -> (X0,X1,X2,X3), W4 = -i.
+__device__ __forceinline__ void dft4(float2& a, float2& b, float2& c, float2& d) {
+  float2 s0 = make_float2(a.x + c.x, a.y + c.y), s1 = make_float2(a.x - c.x, a.y - c.y);
+  float2 s2 = make_float2(b.x + d.x, b.y + d.y), s3 = make_float2(b.x - d.x, b.y - d.y);
+  a = make_float2(s0.x + s2.x, s0.y + s2.y);
+  c = make_float2(s0.x - s2.x, s0.y - s2.y);
+  b = make_float2(s1.x + s3.y, s1.y - s3.x);  // s1 - i*s3
+  d = make_float2(s1.x - s3.y, s1.y + s3.x);  // s1 + i*s3
+}
+
+// 16-point DFT, 4x4 Cooley-Tukey in registers.  Input x[j] natural order; output X[q] is left at
+// position POS16(q) = 4*(q&3) + (q>>2).
+#define POS16(q) (4 * ((q)&3) + ((q) >> 2))
+__device__ __forceinline__ void fft16(float2 (&x)[16]) {
+  constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, R = 0.70710678118654752f;
+#pragma unroll
+  for (int j0 = 0; j0 < 4; ++j0) dft4(x[j0], x[4 + j0], x[8 + j0], x[12 + j0]);
+  // A[j0][q0] now sits at x[4*q0 + j0]; multiply by W16^(j0*q0)
+  x[4 * 1 + 1] = cmul(x[4 * 1 + 1], make_float2(C1, -S1));  // W^1
+  x[4 * 2 + 1] = cmul(x[4 * 2 + 1], make_float2(R, -R));    // W^2
+  x[4 * 3 + 1] = cmul(x[4 * 3 + 1], make_float2(S1, -C1));  // W^3
+  x[4 * 1 + 2] = cmul(x[4 * 1 + 2], make_float2(R, -R));    // W^2
+  x[4 * 2 + 2] = make_float2(x[4 * 2 + 2].y, -x[4 * 2 + 2].x);  // W^4 = -i
+  x[4 * 3 + 2] = cmul(x[4 * 3 + 2], make_float2(-R, -R));   // W^6
+  x[4 * 1 + 3] = cmul(x[4 * 1 + 3], make_float2(S1, -C1));  // W^3
+  x[4 * 2 + 3] = cmul(x[4 * 2 + 3], make_float2(-R, -R));   // W^6
+  x[4 * 3 + 3] = cmul(x[4 * 3 + 3], make_float2(-C1, S1));  // W^9
+#pragma unroll
+  for (int q0 = 0; q0 < 4; ++q0) dft4(x[4 * q0 + 0], x[4 * q0 + 1], x[4 * q0 + 2], x[4 * q0 + 3]);
+}
+
+template <int MODE>  // 0: LFR + CMVN rows, 1: raw log-mel rows
+__global__ void __launch_bounds__(THREADS, 2)
+fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, const int64_t* __restrict__ wav_off,
+             const int32_t* __restrict__ out_row, const int32_t* __restrict__ tile_off, int n_utts,
+             const float* __restrict__ cmvn, float* __restrict__ out, int64_t out_ld, float upscale, float preemph,
+             float log_floor) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15;
+
+  int b, ti;
+  if (MODE == 0) {
+    const int id = blockIdx.x;
+    int lo = 0, hi = n_utts;
+    while (hi - lo > 1) {
+      int mid = (lo + hi) >> 1;
+      if (tile_off[mid] <= id) lo = mid; else hi = mid;
+    }
+    b = lo;
+    ti = id - tile_off[b];
+  } else {
+    b = blockIdx.y;
+    ti = blockIdx.x;
+  }
+  const int64_t w0 = wav_off[b];
+  const int n = static_cast<int>(wav_off[b + 1] - w0);
+  if (n < FRAME_LEN) return;
+  const int m = 1 + (n - FRAME_LEN) / SHIFT;  // TA:62-66 snip_edges
+  int i0 = 0, i1 = 0, f_lo, f_hi;
+  if (MODE == 0) {
+    const int T = (m + LFR_N - 1) / LFR_N;  // VLLM:43
+    i0 = ti * TILE_ROWS;
+    if (i0 >= T) return;
+    i1 = min(i0 + TILE_ROWS, T);
+    f_lo = max(LFR_N * i0 - LFR_LEFT, 0);
+    f_hi = min(LFR_N * (i1 - 1) + LFR_M - 1 - LFR_LEFT, m - 1);
+  } else {
+    f_lo = ti * RAW_TILE_FRAMES;
+    if (f_lo >= m) return;
+    f_hi = min(f_lo + RAW_TILE_FRAMES - 1, m - 1);
+  }
+  const int nF = f_hi - f_lo + 1;
+  const int nS = (nF - 1) * SHIFT + FRAME_LEN;
+
+  // ---- stage PCM (x upscale, VLLM:140-141) and tables into shared memory
+  {
+    const float* src = wav + w0 + static_cast<int64_t>(f_lo) * SHIFT;
+    for (int i = tid; i < nS; i += THREADS) s.samples[i] = __ldg(src + i) * upscale;
+    for (int i = tid; i < FRAME_LEN; i += THREADS) s.window[i] = __ldg(&tab->window[i]);
+    for (int i = tid; i < 136; i += THREADS) s.tw512[i] = __ldg(&tab->tw512[i]);
+    for (int i = tid; i < MAX_TAPS; i += THREADS) s.mel_w[i] = __ldg(&tab->mel_w[i]);
+    for (int i = tid; i < NMEL; i += THREADS) {
+      s.mel_start[i] = __ldg(&tab->mel_start[i]);
+      s.mel_count[i] = __ldg(&tab->mel_count[i]);
+      s.mel_woff[i] = __ldg(&tab->mel_woff[i]);
+    }
+  }
+  // inter-pass twiddles W256^(hl*q): fixed per lane for the whole kernel
+  float2 tw[16];
+#pragma unroll
+  for (int q = 1; q < 16; ++q) tw[q] = __ldg(&tab->tw256[(hl * q) & 255]);
+  __syncthreads();
+
+  const int slot = warp * 2 + (lane >> 4);
+  float2* work = s.work[slot];
+  float* power = s.power[slot];
+
+  for (int fb = warp * 2; fb < nF; fb += SLOTS) {
+    const int f_raw = fb + (lane >> 4);
+    const bool active = f_raw < nF;
+    const int f = active ? f_raw : nF - 1;
+    const float* xs = s.samples + f * SHIFT;
+
+    // ---- load 13 sample pairs (complex point n = hl + 16 j  <->  samples 2n, 2n+1), frame mean
+    float2 x[16];
+    float part = 0.f;
+#pragma unroll
+    for (int j = 0; j < 13; ++j) {
+      const int sidx = 2 * hl + 32 * j;
+      float2 v = make_float2(0.f, 0.f);
+      if (j < 12 || hl < 8) v = *reinterpret_cast<const float2*>(xs + sidx);
+      x[j] = v;
+      part += v.x + v.y;
+    }
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    const float mean = part / static_cast<float>(FRAME_LEN);  // TA:183-186
+
+    // ---- DC removal, pre-emphasis (replicate-left, TA:193-198), window (TA:201-204)
+#pragma unroll
+    for (int j = 0; j < 13; ++j) {
+      const int sidx = 2 * hl + 32 * j;
+      if (j < 12 || hl < 8) {
+        const float rp = xs[sidx > 0 ? sidx - 1 : 0];
+        const float a0 = x[j].x - mean, a1 = x[j].y - mean, ap = rp - mean;
+        const float y0 = a0 - preemph * ap;
+        const float y1 = a1 - preemph * a0;
+        x[j] = make_float2(y0 * s.window[sidx], y1 * s.window[sidx + 1]);
+      }
+    }
+    x[13] = x[14] = x[15] = make_float2(0.f, 0.f);  // zero padding 400 -> 512 (TA:207-211)
+
+    // ---- pass 1: DFT16 over j, twiddle W256^(t q), transpose through smem
+    fft16(x);
+    work[0 * 17 + hl] = x[POS16(0)];
+#pragma unroll
+    for (int q = 1; q < 16; ++q) work[q * 17 + hl] = cmul(x[POS16(q)], tw[q]);
+    __syncwarp();
+#pragma unroll
+    for (int t = 0; t < 16; ++t) x[t] = work[hl * 17 + t];
+    // ---- pass 2: DFT16 over t -> Z[hl + 16 p]
+    fft16(x);
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < 16; ++p) work[16 * p + hl] = x[POS16(p)];
+    __syncwarp();
+
+    // ---- split the packed real FFT:  X[k] = Xe + W512^k Xo,  X[256-k] = conj(Xe - W512^k Xo)
+#pragma unroll
+    for (int i = 0; i < 9; ++i) {
+      const int k = hl + 16 * i;
+      if (k <= 128) {
+        const float2 zk = work[k];
+        const float2 zm = work[(256 - k) & 255];
+        const float2 xe = make_float2(0.5f * (zk.x + zm.x), 0.5f * (zk.y - zm.y));
+        const float2 xo = make_float2(0.5f * (zk.y + zm.y), -0.5f * (zk.x - zm.x));
+        const float2 t = cmul(xo, s.tw512[k]);
+        const float ar = xe.x + t.x, ai = xe.y + t.y, br = xe.x - t.x, bi = xe.y - t.y;
+        power[k] = ar * ar + ai * ai;        // TA:616-618 |rfft|^2
+        power[256 - k] = br * br + bi * bi;
+      }
+    }
+    __syncwarp();
+
+    // ---- sparse mel projection + log (TA:621-633); bins hl, hl+16, ..., hl+64
+#pragma unroll
+    for (int i = 0; i < NMEL / 16; ++i) {
+      const int bin = hl + 16 * i;
+      const int st = s.mel_start[bin], cnt = s.mel_count[bin];
+      const float* wv = s.mel_w + s.mel_woff[bin];
+      float acc = 0.f;
+      for (int j = 0; j < cnt; ++j) acc = fmaf(wv[j], power[st + j], acc);
+      if (active) s.logmel[f][bin] = logf(fmaxf(acc, log_floor));
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+
+  if (MODE == 0) {
+    // ---- LFR gather (VLLM:40-60 closed form) + CMVN (VLLM:23-37), coalesced float4 rows
+    const int rows = i1 - i0;
+    constexpr int V = FEAT / 4;  // 140 float4 per row
+    float* obase = out + static_cast<int64_t>(out_row[b] + i0) * out_ld;
+    for (int idx = tid; idx < rows * V; idx += THREADS) {
+      const int r = idx / V, c4 = idx - r * V;
+      const int col = c4 * 4, j = col / NMEL, c = col - j * NMEL;
+      int fr = LFR_N * (i0 + r) + j - LFR_LEFT;
+      fr = min(max(fr, 0), m - 1) - f_lo;
+      float4 v = *reinterpret_cast<const float4*>(&s.logmel[fr][c]);
+      if (cmvn != nullptr) {
+        const float4 mu = __ldg(reinterpret_cast<const float4*>(cmvn + col));
+        const float4 sc = __ldg(reinterpret_cast<const float4*>(cmvn + FEAT + col));
+        v.x = (v.x + mu.x) * sc.x; v.y = (v.y + mu.y) * sc.y;
+        v.z = (v.z + mu.z) * sc.z; v.w = (v.w + mu.w) * sc.w;
+      }
+      *reinterpret_cast<float4*>(obase + static_cast<int64_t>(r) * out_ld + col) = v;
+    }
+  } else {
+    constexpr int V = NMEL / 4;
+    float* obase = out + static_cast<int64_t>(out_row[b] + f_lo) * out_ld;
+    for (int idx = tid; idx < nF * V; idx += THREADS) {
+      const int r = idx / V, c4 = idx - r * V;
+      *reinterpret_cast<float4*>(obase + static_cast<int64_t>(r) * out_ld + c4 * 4) =
+          *reinterpret_cast<const float4*>(&s.logmel[r][c4 * 4]);
+    }
+  }
+}
+
+static int check_cfg(const fa_frontend_cfg* c) {
+  FA_REQUIRE(c != nullptr, "frontend cfg is NULL");
+  FA_REQUIRE(c->frame_len == FRAME_LEN && c->frame_shift == SHIFT && c->n_fft == NFFT && c->n_mels == NMEL &&
+                 c->lfr_m == LFR_M && c->lfr_n == LFR_N,
+             "frontend geometry %d/%d/%d/%d lfr %d/%d is not the compiled one (400/160/512/80 lfr 7/6)", c->frame_len,
+             c->frame_shift, c->n_fft, c->n_mels, c->lfr_m, c->lfr_n);
+  return 0;
+}
+
+}  // namespace fe
+}  // namespace fa
+
+using namespace fa;
+using namespace fa::fe;
+
+extern "C" size_t fa_frontend_tables_bytes(void) { return sizeof(Tables); }
+
+extern "C" int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float* window, const float* mel_banks,
+                                        void* blob_host) {
+  if (int r = check_cfg(cfg)) return r;
+  FA_REQUIRE(window && mel_banks && blob_host, "NULL table pointer");
+  Tables* t = static_cast<Tables*>(blob_host);
+  std::memset(t, 0, sizeof(Tables));
+  for (int i = 0; i < FRAME_LEN; ++i) t->window[i] = window[i];
+  const double two_pi = 6.283185307179586476925286766559;
+  for (int k = 0; k < 256; ++k)
+    t->tw256[k] = make_float2(static_cast<float>(cos(two_pi * k / 256.0)), static_cast<float>(-sin(two_pi * k / 256.0)));
+  for (int k = 0; k <= 128; ++k)
+    t->tw512[k] = make_float2(static_cast<float>(cos(two_pi * k / 512.0)), static_cast<float>(-sin(two_pi * k / 512.0)));
+  int off = 0;
+  for (int b = 0; b < NMEL; ++b) {
+    const float* row = mel_banks + static_cast<size_t>(b) * NBIN;
+    int first = -1, last = -1;
+    for (int k = 0; k < NBIN; ++k)
+      if (row[k] != 0.f) {
+        if (first < 0) first = k;
+        last = k;
+      }
+    const int cnt = first < 0 ? 0 : last - first + 1;
+    FA_REQUIRE(off + cnt <= MAX_TAPS, "mel filterbank has more than %d taps", MAX_TAPS);
+    t->mel_start[b] = first < 0 ? 0 : first;
+    t->mel_count[b] = cnt;
+    t->mel_woff[b] = off;
+    for (int j = 0; j < cnt; ++j) t->mel_w[off + j] = row[first + j];
+    off += cnt;
+  }
+  return 0;
+}
+
+extern "C" int fa_frontend_forward(const fa_frontend_cfg* cfg, const void* tables_dev, const float* wav_dev,
+                                   const int64_t* wav_off_dev, const int32_t* out_row_dev, const int32_t* tile_off_dev,
+                                   int32_t n_utts, int32_t n_tiles, const float* cmvn_dev, float* out_dev,
+                                   int64_t out_ld, fa_stream_t stream) {
+  if (int r = check_cfg(cfg)) return r;
+  FA_REQUIRE(n_utts > 0, "empty batch");
+  FA_REQUIRE(tables_dev && wav_dev && wav_off_dev && out_row_dev && tile_off_dev && out_dev, "NULL device pointer");
+  FA_REQUIRE(out_ld >= FEAT && out_ld % 4 == 0, "out_ld must be >= %d and a multiple of 4", FEAT);
+  FA_REQUIRE((reinterpret_cast<uintptr_t>(out_dev) & 15) == 0, "out_dev must be 16-byte aligned");
+  if (n_tiles <= 0) return 0;
+  static bool attr_done = false;
+  if (!attr_done) {
+    FA_CHECK_CUDA(cudaFuncSetAttribute(fbank_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    FA_CHECK_CUDA(cudaFuncSetAttribute(fbank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    attr_done = true;
+  }
+  fbank_kernel<0><<<n_tiles, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const Tables*>(tables_dev), wav_dev, wav_off_dev, out_row_dev, tile_off_dev, n_utts, cmvn_dev,
+      out_dev, out_ld, cfg->upscale, cfg->preemph, cfg->log_floor);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int fa_frontend_logmel(const fa_frontend_cfg* cfg, const void* tables_dev, const float* wav_dev,
+                                  const int64_t* wav_off_dev, const int32_t* out_row_dev, int32_t n_utts,
+                                  int32_t max_frames, float* out_dev, int64_t out_ld, fa_stream_t stream) {
+  if (int r = check_cfg(cfg)) return r;
+  FA_REQUIRE(n_utts > 0 && max_frames > 0, "empty batch");
+  FA_REQUIRE(tables_dev && wav_dev && wav_off_dev && out_row_dev && out_dev, "NULL device pointer");
+  FA_REQUIRE(out_ld >= NMEL && out_ld % 4 == 0, "out_ld must be >= %d and a multiple of 4", NMEL);
+  static bool attr_done = false;
+  if (!attr_done) {
+    FA_CHECK_CUDA(cudaFuncSetAttribute(fbank_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    FA_CHECK_CUDA(cudaFuncSetAttribute(fbank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    attr_done = true;
+  }
+  dim3 grid(ceil_div(max_frames, RAW_TILE_FRAMES), n_utts);
+  fbank_kernel<1><<<grid, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const Tables*>(tables_dev), wav_dev, wav_off_dev, out_row_dev, nullptr, n_utts, nullptr, out_dev,
+      out_ld, cfg->upscale, cfg->preemph, cfg->log_floor);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int32_t fa_num_frames(int32_t n_samples, int32_t frame_len, int32_t frame_shift) {
+  return n_samples < frame_len ? 0 : 1 + (n_samples - frame_len) / frame_shift;
+}
+extern "C" int32_t fa_num_lfr(int32_t n_frames, int32_t lfr_n) { return (n_frames + lfr_n - 1) / lfr_n; }
+extern "C" int32_t fa_fake_token_len(int32_t n_lfr, int32_t use_low_frame_rate) {
+  if (!use_low_frame_rate) return n_lfr;
+  // /root/reference/model.py:391-394 (python floor division)
+  auto fdiv = [](int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); };
+  int o = 1 + fdiv(n_lfr - 3 + 2, 2);
+  o = 1 + fdiv(o - 3 + 2, 2);
+  return fdiv(o - 1, 2) + 1;
+}

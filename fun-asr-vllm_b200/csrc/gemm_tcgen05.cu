@@ -1,0 +1,414 @@
+// bf16 GEMM  C[M,N] = A[M,K] * W[N,K]^T  (+bias, ReLU, residuals) on sm_100a tensor cores.
+//
+// Persistent, warp-specialised kernel:
+//   warp 0      TMA producer   (cp.async.bulk.tensor 2D, 128B swizzle, mbarrier complete_tx)
+//   warp 1      MMA issuer     (tcgen05.mma cta_group::1 kind::f16, M=128, N=BN, K=16 per instruction,
+//                               fp32 accumulators in TMEM, double buffered: 2 x BN columns)
+//   warps 2..5  epilogue       (tcgen05.ld 32x32b -> registers -> bias/ReLU/residual -> global)
+// Three pipelines: smem full/empty (TMA<->MMA), TMEM full/empty (MMA<->epilogue), static tile
+// scheduler (tile = blockIdx.x + i * gridDim.x).  Both operands are K-major (nn.Linear layout),
+// so no transposes are ever materialised.
+//
+// Replaces the cuBLAS calls behind nn.Linear in VLLM/model_executor/models/funasr.py:164-168 (qkv),
+// :159-163,238 (out), :415-431 (FFN), :543-552,585-587 (adaptor linears).
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace fa {
+namespace gemm {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle span
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 192;
+constexpr int EPI_WARP0 = 2;
+
+template <int BN>
+struct Cfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (power of two >= 32)
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct Params {
+  int M, N, K;
+  int tiles_m, tiles_n;
+  const float* bias;
+  const float* res1;
+  const float* res2;
+  void* c;
+  long long ldc;
+  int relu;
+  int out_f32;
+};
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint32_t bar, int x, int y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(tmap), "r"(bar), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// K-major operand tile, 128B swizzle: 8-row groups are 1024 B apart (SBO), LBO unused (=1),
+// descriptor version 1 (Blackwell), layout type 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at [17,23), M>>4 at [24,29).
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// ---------------------------------------------------------------- kernel
+template <int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const Params p) {
+  using C = Cfg<BN>;
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024B alignment
+  const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::STAGES + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * C::STAGES + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_kb = (p.K + BK - 1) / BK;
+  const int num_tiles = p.tiles_m * p.tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);  // one arrive per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(C::TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+          const uint32_t sb = sa + C::A_BYTES;
+          mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
+          tma_load_2d(sa, &tmap_a, full_bar(stage), kb * BK, tm * BM);
+          tma_load_2d(sb, &tmap_b, full_bar(stage), kb * BK, tn * BN);
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc(BM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(tempty_bar(acc), acc_phase ^ 1);  // epilogue has drained this accumulator
+      tcgen05_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tcgen05_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+          const uint32_t sb = sa + C::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t adesc = make_smem_desc(sa + k * UMMA_K * 2);
+            const uint64_t bdesc = make_smem_desc(sb + k * UMMA_K * 2);
+            umma_f16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
+          }
+          umma_commit(empty_bar(stage));                       // frees the smem slot when the MMAs retire
+          if (kb == num_kb - 1) umma_commit(tfull_bar(acc));   // accumulator complete
+        }
+        __syncwarp();
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue warps =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tcgen05_fence_after();
+      const int row = tm * BM + q * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + c0, r);
+        const int col = tn * BN + c0;
+        if (row_ok) {
+          float v[32];
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            const float4 bv = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col + i)) : make_float4(0, 0, 0, 0);
+            v[i] = __uint_as_float(r[i]) + bv.x;
+            v[i + 1] = __uint_as_float(r[i + 1]) + bv.y;
+            v[i + 2] = __uint_as_float(r[i + 2]) + bv.z;
+            v[i + 3] = __uint_as_float(r[i + 3]) + bv.w;
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+          }
+          if (p.out_f32) {
+            float* crow = static_cast<float*>(p.c) + static_cast<long long>(row) * p.ldc + col;
+            if (p.res1) {
+              const float* rr = p.res1 + static_cast<long long>(row) * p.ldc + col;
+#pragma unroll
+              for (int i = 0; i < 32; i += 4) {
+                const float4 t = *reinterpret_cast<const float4*>(rr + i);
+                v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
+              }
+            }
+            if (p.res2) {
+              const float* rr = p.res2 + static_cast<long long>(row) * p.ldc + col;
+#pragma unroll
+              for (int i = 0; i < 32; i += 4) {
+                const float4 t = *reinterpret_cast<const float4*>(rr + i);
+                v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 32; i += 4)
+              *reinterpret_cast<float4*>(crow + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+          } else {
+            __nv_bfloat16* crow = static_cast<__nv_bfloat16*>(p.c) + static_cast<long long>(row) * p.ldc + col;
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              uint4 o;
+              o.x = pack_bf16x2(v[i], v[i + 1]);
+              o.y = pack_bf16x2(v[i + 2], v[i + 3]);
+              o.z = pack_bf16x2(v[i + 4], v[i + 5]);
+              o.w = pack_bf16x2(v[i + 6], v[i + 7]);
+              *reinterpret_cast<uint4*>(crow + i) = o;
+            }
+          }
+        }
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------- host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* ptr = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess || ptr == nullptr)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  return fn;
+}
+
+template <int BN>
+static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, int M, int N, int K, const GemmEpilogue& epi, void* c,
+                    int64_t ldc, cudaStream_t stream) {
+  using C = Cfg<BN>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    FA_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    attr_done = true;
+  }
+  Params p;
+  p.M = M; p.N = N; p.K = K;
+  p.tiles_m = ceil_div(M, BM);
+  p.tiles_n = N / BN;
+  p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
+  p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32;
+  const int tiles = p.tiles_m * p.tiles_n;
+  const int grid = tiles < sm_count() ? tiles : sm_count();
+  CUtensorMap ma, mb;
+  static_assert(sizeof(CUtensorMap) == sizeof(TensorMap2D::bytes), "CUtensorMap size");
+  memcpy(&ma, ta.bytes, sizeof(ma));
+  memcpy(&mb, tb.bytes, sizeof(mb));
+  gemm_bf16_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, p);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace gemm
+
+int make_tensor_map_bf16(TensorMap2D* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                         uint32_t box_rows) {
+  gemm::EncodeTiledFn fn = gemm::get_encode_fn();
+  FA_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  FA_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
+  FA_REQUIRE((ld * 2) % 16 == 0, "TMA row pitch (%llu bytes) must be a multiple of 16", (unsigned long long)(ld * 2));
+  FA_REQUIRE(box_rows >= 1 && box_rows <= 256, "TMA box rows out of range");
+  CUtensorMap m;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {ld * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(gemm::BK), box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  FA_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows %llu cols %llu ld %llu)", (int)r,
+             (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld);
+  memcpy(out->bytes, &m, sizeof(m));
+  return 0;
+}
+
+int gemm_block_n(int M, int N) {
+  // Fill the 148 SMs: prefer the widest tile that still yields >= ~1 wave of tiles.
+  const int tiles_m = ceil_div(M, gemm::BM);
+  const int sms = sm_count();
+  if (N % 256 == 0 && tiles_m * (N / 256) >= 2 * sms) return 256;
+  if (N % 128 == 0 && tiles_m * (N / 128) >= sms) return 128;
+  if (N % 64 == 0) return 64;
+  if (N % 128 == 0) return 128;
+  return 0;
+}
+
+int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, int block_n, int M, int N, int K, const GemmEpilogue& epi,
+                void* c, int64_t ldc, cudaStream_t stream) {
+  FA_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
+  FA_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "gemm: unsupported tile N %d", block_n);
+  FA_REQUIRE(N % block_n == 0, "gemm: N=%d is not a multiple of the tile %d", N, block_n);
+  FA_REQUIRE(K % 8 == 0, "gemm: K=%d must be a multiple of 8", K);
+  FA_REQUIRE(ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(c) & 15) == 0, "gemm: C must be 16-byte aligned, ldc %% 8 == 0");
+  switch (block_n) {
+    case 64: return gemm::launch_t<64>(ta, tb, M, N, K, epi, c, ldc, stream);
+    case 128: return gemm::launch_t<128>(ta, tb, M, N, K, epi, c, ldc, stream);
+    default: return gemm::launch_t<256>(ta, tb, M, N, K, epi, c, ldc, stream);
+  }
+}
+
+}  // namespace fa
+
+extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev,
+                          const float* res1_dev, const float* res2_dev, void* c_dev, int64_t ldc, int32_t M, int32_t N,
+                          int32_t K, int32_t relu, int32_t out_f32, fa_stream_t stream) {
+  using namespace fa;
+  FA_REQUIRE(a_dev && w_dev && c_dev, "gemm: NULL pointer");
+  const int bn = gemm_block_n(M, N);
+  FA_REQUIRE(bn != 0, "gemm: N=%d must be a multiple of 64", N);
+  TensorMap2D ta, tb;
+  if (int r = make_tensor_map_bf16(&ta, a_dev, M, K, lda, gemm::BM)) return r;
+  if (int r = make_tensor_map_bf16(&tb, w_dev, N, K, ldw, bn)) return r;
+  GemmEpilogue e;
+  e.bias = bias_dev; e.res1 = res1_dev; e.res2 = res2_dev; e.relu = relu; e.out_f32 = out_f32;
+  return launch_gemm(ta, tb, bn, M, N, K, e, c_dev, ldc, static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,220 @@
+/*
+ * funasr_b200.h — C ABI of libfunasr_b200.so: the B200 (sm_100a) audio hot path of Fun-ASR-Nano.
+ *
+ * The reference (duj12/Fun-ASR-vllm) is pure Python and has no FFI of its own; the "binding" it
+ * has for this path is the Python call boundary into funasr/torchaudio.  Each entry point below
+ * names the reference call it replaces (paths under /root/reference; VLLM/ and TA/ are the on-box
+ * copies of the third-party arithmetic, see SURVEY.md "Citation conventions"):
+ *
+ *   fa_frontend_forward   <- extract_fbank(...)            infer.py:446, infer_kaldidata.py:708,897, model.py:372
+ *                            = WavFrontend.forward          VLLM/transformers_utils/processors/funasr.py:128-168
+ *                            = kaldi.fbank + apply_lfr + apply_cmvn   TA/compliance/kaldi.py:514-645, VLLM/...:40-60,23-37
+ *   fa_encoder_forward    <- model.audio_encoder(speech, lens)        infer.py:455, model.py:252,259-263
+ *                            = SenseVoiceEncoderSmall.forward          VLLM/model_executor/models/funasr.py:378-409
+ *   fa_adaptor_forward    <- model.audio_adaptor(enc, lens)           infer.py:458, model.py:253,491
+ *                            = adaptor Transformer.forward             VLLM/model_executor/models/funasr.py:574-595
+ *   fa_encode_adapt       <- FunASRNano.forward_export(speech, lens)  model.py:251-254
+ *   fa_splice_embeds      <- torch.cat([prefix, speech[:len], suffix]) infer.py:462-466 (model.py:513-541)
+ *   fa_fake_token_len     <- fake_token_len arithmetic                model.py:391-396
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every *_dev pointer is device memory owned by the caller;
+ *   - no allocation and no synchronisation inside: every call only enqueues kernels on `stream`
+ *     (a cudaStream_t / CUstream); the caller owns buffers, workspace and the stream;
+ *   - return 0 on success, non-zero on error, message in fa_last_error() (thread local);
+ *   - variable-length batches are PACKED: utterance b owns rows [cu_seqlens[b], cu_seqlens[b+1])
+ *     of every [tokens, dim] matrix; no padding rows exist anywhere inside the library.
+ */
+#ifndef FUNASR_B200_H_
+#define FUNASR_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library is built with -fvisibility=hidden */
+#endif
+
+typedef void* fa_stream_t; /* cudaStream_t */
+
+#define FA_ABI_VERSION 1
+
+int fa_abi_version(void);
+const char* fa_last_error(void);
+/* SM count / compute capability of the current device: fails unless it is sm_100 (B200). */
+int fa_check_device(int32_t* sm_count, int32_t* cc_major, int32_t* cc_minor);
+
+/* ------------------------------------------------------------------ frontend ---------------- */
+typedef struct {
+  int32_t sample_rate; /* 16000 */
+  int32_t frame_len;   /* 400  (25 ms)   TA:135 */
+  int32_t frame_shift; /* 160  (10 ms)   TA:134 */
+  int32_t n_fft;       /* 512            TA:136 */
+  int32_t n_mels;      /* 80 */
+  int32_t lfr_m;       /* 7 */
+  int32_t lfr_n;       /* 6 */
+  float preemph;       /* 0.97           TA:532 */
+  float upscale;       /* 32768 when WavFrontend.upsacle_samples (VLLM:140) else 1 */
+  float log_floor;     /* FLT_EPSILON    TA:22,633 */
+} fa_frontend_cfg;
+
+/* Only this geometry is compiled (the one Fun-ASR-Nano uses); anything else returns an error. */
+#define FA_FE_TILE_ROWS 5 /* LFR rows produced per CTA tile; host builds tile_off with it */
+
+/* Size of the packed table blob (window, FFT twiddles, sparse mel filterbank). */
+size_t fa_frontend_tables_bytes(void);
+/* Build the blob on the HOST into `blob_host` from the reference-side tables:
+ *   window[frame_len]            = _feature_window_function(...)       TA:86-113
+ *   mel_banks[n_mels * (n_fft/2+1)] = get_mel_banks(...) zero Nyquist column appended  TA:436-511,627
+ * The caller uploads the blob to the device once. */
+int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float* window, const float* mel_banks,
+                             void* blob_host);
+
+/* Fused framing + DC removal + pre-emphasis + window + 512-pt rFFT + power + mel + log + LFR + CMVN.
+ *   wav_dev      : packed f32 PCM in [-1,1)
+ *   wav_off_dev  : [n_utts+1] int64 sample offsets into wav_dev
+ *   out_row_dev  : [n_utts]   int32 first output row of each utterance (packed: cu_seqlens[b];
+ *                  padded [B,Tmax,.]: b*Tmax)
+ *   tile_off_dev : [n_utts+1] int32 prefix sum of ceil(T_b / FA_FE_TILE_ROWS)
+ *   cmvn_dev     : [2, lfr_m*n_mels] (means; scales) or NULL            VLLM:23-37
+ *   out_dev      : f32, row stride out_ld (>= lfr_m*n_mels) */
+int fa_frontend_forward(const fa_frontend_cfg* cfg, const void* tables_dev, const float* wav_dev,
+                        const int64_t* wav_off_dev, const int32_t* out_row_dev,
+                        const int32_t* tile_off_dev, int32_t n_utts, int32_t n_tiles,
+                        const float* cmvn_dev, float* out_dev, int64_t out_ld, fa_stream_t stream);
+
+/* Raw 80-bin log-mel (no LFR/CMVN), [m_b, n_mels] rows at out_row_dev[b]; used by parity tests. */
+int fa_frontend_logmel(const fa_frontend_cfg* cfg, const void* tables_dev, const float* wav_dev,
+                       const int64_t* wav_off_dev, const int32_t* out_row_dev, int32_t n_utts,
+                       int32_t max_frames, float* out_dev, int64_t out_ld, fa_stream_t stream);
+
+int32_t fa_num_frames(int32_t n_samples, int32_t frame_len, int32_t frame_shift); /* TA:62-66 */
+int32_t fa_num_lfr(int32_t n_frames, int32_t lfr_n);                              /* VLLM:43 */
+int32_t fa_fake_token_len(int32_t n_lfr, int32_t use_low_frame_rate);             /* model.py:391-396 */
+
+/* ------------------------------------------------------------------ encoder / adaptor ------- */
+typedef struct {
+  /* SenseVoiceEncoderSmall(input_size, **audio_encoder_conf)   VLLM/model_executor/models/funasr.py:293-376 */
+  int32_t d_in;        /* 560 */
+  int32_t d_model;     /* 512  output_size */
+  int32_t n_heads;     /* 4 */
+  int32_t d_ff;        /* 2048 linear_units */
+  int32_t fsmn_kernel; /* 11 */
+  int32_t sanm_shift;  /* 0 */
+  int32_t n_blocks;    /* 50  (encoders0 + encoders) */
+  int32_t n_tp_blocks; /* 20 */
+  /* adaptor Transformer(**audio_adaptor_conf)                  VLLM/...:528-572, 625-637 */
+  int32_t ad_downsample; /* 1 (only 1 is compiled) */
+  int32_t ad_ffn;        /* 2048 */
+  int32_t ad_dim;        /* 1024 llm_dim */
+  int32_t ad_heads;      /* 8 */
+  int32_t ad_layers;     /* 2 */
+  int32_t ad_ff;         /* 256 = llm_dim // 4 */
+} fa_model_cfg;
+
+/* One SAN-M block (EncoderLayerSANM).  Matrices bf16 row-major [out, in] (nn.Linear layout);
+ * vectors and the FSMN taps f32. */
+typedef struct {
+  const float* ln1_g;
+  const float* ln1_b;
+  const void* qkv_w;    /* bf16 [3*d_model, d_in|d_model]   self_attn.linear_q_k_v.weight */
+  const float* qkv_b;   /* [3*d_model] */
+  const float* fsmn_w;  /* f32 [d_model, fsmn_kernel]        self_attn.fsmn_block.weight */
+  const void* out_w;    /* bf16 [d_model, d_model]           self_attn.linear_out.weight */
+  const float* out_b;
+  const float* ln2_g;
+  const float* ln2_b;
+  const void* ffn1_w;   /* bf16 [d_ff, d_model]              feed_forward.w_1.weight */
+  const float* ffn1_b;
+  const void* ffn2_w;   /* bf16 [d_model, d_ff]              feed_forward.w_2.weight */
+  const float* ffn2_b;
+} fa_sanm_layer_w;
+
+typedef struct {
+  const float* ln1_g;
+  const float* ln1_b;
+  const void* qkv_w;    /* bf16 [3*ad_dim, ad_dim] = cat(linear_q, linear_k, linear_v) */
+  const float* qkv_b;
+  const void* out_w;    /* bf16 [ad_dim, ad_dim] */
+  const float* out_b;
+  const float* ln2_g;
+  const float* ln2_b;
+  const void* ffn1_w;   /* bf16 [ad_ff, ad_dim] */
+  const float* ffn1_b;
+  const void* ffn2_w;   /* bf16 [ad_dim, ad_ff] */
+  const float* ffn2_b;
+} fa_adaptor_layer_w;
+
+typedef struct {
+  const fa_sanm_layer_w* layers;       /* HOST array [n_blocks + n_tp_blocks] of device pointers */
+  const float* after_norm_g;
+  const float* after_norm_b;
+  const float* tp_norm_g;
+  const float* tp_norm_b;
+  const float* pe_inv_timescales;      /* f32 [d_in/2]  exp(-k*ln(1e4)/(d_in/2-1))  VLLM/...:268-276 */
+  const void* lin1_w;                  /* bf16 [ad_ffn, d_model] */
+  const float* lin1_b;
+  const void* lin2_w;                  /* bf16 [ad_dim, ad_ffn] */
+  const float* lin2_b;
+  const fa_adaptor_layer_w* ad_layers; /* HOST array [ad_layers] */
+} fa_model_w;
+
+typedef struct fa_plan fa_plan; /* host-side plan: TMA descriptors + workspace carve-up. No device allocation. */
+
+size_t fa_plan_workspace_bytes(const fa_model_cfg* cfg, int32_t max_tokens);
+int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void* workspace_dev, size_t workspace_bytes,
+                   int32_t max_tokens, fa_plan** plan_out);
+void fa_plan_destroy(fa_plan* plan);
+
+/* feats_dev [n_tokens, d_in] f32 packed (NOT modified, unlike the reference's in-place scale,
+ * VLLM/...:388);  enc_out_dev [n_tokens, d_model] f32 (may be NULL: result stays in the plan's
+ * workspace for fa_adaptor_forward(enc_dev = NULL)). */
+int fa_encoder_forward(fa_plan* plan, const float* feats_dev, const int32_t* cu_seqlens_dev, int32_t n_utts,
+                       int32_t n_tokens, int32_t max_len, float* enc_out_dev, fa_stream_t stream);
+/* enc_dev [n_tokens, d_model] f32 packed, or NULL to consume the plan-resident encoder output.
+ * out_dev [n_tokens, ad_dim]: f32 when out_bf16 == 0, bf16 otherwise. */
+int fa_adaptor_forward(fa_plan* plan, const float* enc_dev, const int32_t* cu_seqlens_dev, int32_t n_utts,
+                       int32_t n_tokens, int32_t max_len, void* out_dev, int32_t out_bf16, fa_stream_t stream);
+int fa_encode_adapt(fa_plan* plan, const float* feats_dev, const int32_t* cu_seqlens_dev, int32_t n_utts,
+                    int32_t n_tokens, int32_t max_len, float* enc_out_dev, void* out_dev, int32_t out_bf16,
+                    fa_stream_t stream);
+
+/* out rows: utterance b -> [prefix (P rows) | speech rows [cu[b], cu[b]+take_b) | suffix (S rows)] at
+ * out_off[b].  take_dev == NULL: take all rows.  All matrices [rows, dim]; speech f32 or bf16,
+ * prefix/suffix/out bf16 when *_bf16 is set else f32. */
+int fa_splice_embeds(const void* speech_dev, int32_t speech_bf16, const int32_t* cu_seqlens_dev,
+                     const int32_t* take_dev, const void* prefix_dev, int32_t n_prefix, const void* suffix_dev,
+                     int32_t n_suffix, const int64_t* out_off_dev, int32_t n_utts, int32_t dim, void* out_dev,
+                     int32_t out_bf16, int32_t max_rows_per_utt, fa_stream_t stream);
+
+/* ------------------------------------------------------------------ single ops (parity tests) */
+/* C[M,N] = A[M,K] (bf16) * W[N,K]^T (bf16) + bias; relu optional; then
+ *   out_f32 == 0: bf16 C;   out_f32 == 1: f32 C = acc + bias (+ res1) (+ res2)   (res* f32 [M,N] or NULL) */
+int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev,
+               const float* res1_dev, const float* res2_dev, void* c_dev, int64_t ldc, int32_t M, int32_t N,
+               int32_t K, int32_t relu, int32_t out_f32, fa_stream_t stream);
+/* y = LN(x) (eps 1e-12); y_bf16 and/or y_f32 may be NULL */
+int fa_op_layernorm(const float* x_dev, const float* g_dev, const float* b_dev, void* y_bf16_dev, float* y_f32_dev,
+                    int32_t M, int32_t D, fa_stream_t stream);
+/* y_bf16 = LN(x*scale + PE(pos))  (encoder input stage)   VLLM/...:388-390 + norm1 of encoders0 */
+int fa_op_embed_layernorm(const float* x_dev, const float* inv_ts_dev, const int32_t* cu_seqlens_dev, int32_t n_utts,
+                          float scale, const float* g_dev, const float* b_dev, void* y_bf16_dev, int32_t M, int32_t D,
+                          fa_stream_t stream);
+/* mem[M,D] f32 = v + depthwise_conv_time(v)   v = qkv[:, v_col : v_col+D] bf16    VLLM/...:181-201 */
+int fa_op_fsmn(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, const float* w_dev, const int32_t* cu_seqlens_dev,
+               int32_t n_utts, float* mem_dev, int32_t M, int32_t D, int32_t kernel, int32_t left_pad,
+               fa_stream_t stream);
+/* ctx[M, H*128] bf16 = softmax(q k^T / sqrt(128)) v per utterance and head; q|k|v packed in qkv rows */
+int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqlens_dev, int32_t n_utts,
+                    int32_t max_len, int32_t n_heads, void* ctx_dev, int64_t ld_ctx, fa_stream_t stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* FUNASR_B200_H_ */
