@@ -129,7 +129,8 @@ int check_model_cfg(const fa_model_cfg* c) {
              c->ad_dim, c->ad_heads);
   FA_REQUIRE(c->d_in % 8 == 0 && c->d_in <= 1024 && c->d_model <= 1024 && c->ad_dim <= 1024, "d_in/d_model/ad_dim must be <= 1024, d_in %% 8 == 0");
   FA_REQUIRE(c->d_ff % 64 == 0 && c->ad_ffn % 64 == 0 && c->ad_ff % 64 == 0, "FFN widths must be multiples of 64");
-  FA_REQUIRE(c->n_blocks >= 1 && c->n_tp_blocks >= 0 && c->ad_layers >= 0, "bad block counts");
+  FA_REQUIRE(c->n_blocks >= 0 && c->n_tp_blocks >= 0 && c->ad_layers >= 0, "bad block counts");
+  FA_REQUIRE(c->n_blocks >= 1 || c->n_tp_blocks == 0, "tp blocks need at least one main block");
   FA_REQUIRE(c->ad_downsample == 1, "adaptor downsample_rate %d: only 1 is compiled", c->ad_downsample);
   FA_REQUIRE(c->fsmn_kernel >= 1 && c->fsmn_kernel <= 16 && c->sanm_shift >= 0, "bad FSMN kernel/shift");
   return 0;
@@ -190,8 +191,10 @@ extern "C" int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void
   const int cap = (max_tokens + 127) / 128 * 128;
   Workspace ws = carve(*cfg, cap, static_cast<unsigned char*>(workspace_dev));
   FA_REQUIRE(ws.bytes <= workspace_bytes, "workspace too small: need %zu bytes, got %zu", ws.bytes, workspace_bytes);
-  FA_REQUIRE(w->layers && w->after_norm_g && w->after_norm_b && w->tp_norm_g && w->tp_norm_b && w->pe_inv_timescales,
+  FA_REQUIRE(cfg->n_blocks == 0 ||
+                 (w->layers && w->after_norm_g && w->after_norm_b && w->tp_norm_g && w->tp_norm_b && w->pe_inv_timescales),
              "plan_create: NULL encoder weights");
+  FA_REQUIRE(cfg->n_blocks > 0 || w->lin1_w, "plan_create: neither encoder blocks nor adaptor weights given");
   fa_plan* p = new (std::nothrow) fa_plan();
   FA_REQUIRE(p != nullptr, "out of host memory");
   p->cfg = *cfg;
@@ -245,10 +248,18 @@ static int check_batch(const fa_plan* p, const int32_t* cu, int n_utts, int n_to
   return 0;
 }
 
-extern "C" int fa_encoder_forward(fa_plan* p, const float* feats, const int32_t* cu, int32_t n_utts, int32_t M,
-                                  int32_t max_len, float* enc_out, fa_stream_t stream) {
+static int check_tmax(int tmax, int max_len, const char* what) {
+  FA_REQUIRE(tmax == 0 || tmax >= max_len, "%s: padded row count %d is smaller than the longest utterance %d", what, tmax, max_len);
+  return 0;
+}
+
+extern "C" int fa_encoder_forward(fa_plan* p, const float* feats, int32_t feats_tmax, const int32_t* cu, int32_t n_utts,
+                                  int32_t M, int32_t max_len, float* enc_out, int32_t enc_out_tmax, fa_stream_t stream) {
   if (int r = check_batch(p, cu, n_utts, M, max_len)) return r;
   FA_REQUIRE(feats != nullptr, "NULL feats");
+  FA_REQUIRE(p->cfg.n_blocks > 0, "plan was created without encoder weights");
+  if (int r = check_tmax(feats_tmax, max_len, "feats")) return r;
+  if (int r = check_tmax(enc_out_tmax, max_len, "enc_out")) return r;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const fa_model_cfg& c = p->cfg;
   Workspace& ws = p->ws;
@@ -259,7 +270,7 @@ extern "C" int fa_encoder_forward(fa_plan* p, const float* feats, const int32_t*
   int rc = 0;
 
   // input stage: xs*sqrt(d) + PE, then norm1 of encoders0 (VM:388-390, :121)
-  rc = launch_embed_layernorm(feats, p->w.pe_inv_timescales, cu, n_utts, sqrtf(static_cast<float>(d)), p->layers[0].w.ln1_g,
+  rc = launch_embed_layernorm(feats, feats_tmax, p->w.pe_inv_timescales, cu, n_utts, sqrtf(static_cast<float>(d)), p->layers[0].w.ln1_g,
                               p->layers[0].w.ln1_b, ws.xn0, M, c.d_in, s);
   if (rc) return rc;
   for (int i = 0; i < nl; ++i) {
@@ -307,13 +318,16 @@ extern "C" int fa_encoder_forward(fa_plan* p, const float* feats, const int32_t*
       if ((rc = launch_layernorm(x, Ln.w.ln1_g, Ln.w.ln1_b, nullptr, nullptr, ws.xn, nullptr, M, d, s))) return rc;
     }
   }
-  if (enc_out) rc = launch_copy_f32(ws.enc_f32, enc_out, static_cast<int64_t>(M) * d, s);
+  if (enc_out) rc = launch_repack_rows(ws.enc_f32, 0, enc_out, enc_out_tmax, 0, cu, n_utts, M, d, s);
   return rc;
 }
 
-extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, const int32_t* cu, int32_t n_utts, int32_t M,
-                                  int32_t max_len, void* out, int32_t out_bf16, fa_stream_t stream) {
+extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, int32_t enc_tmax, const int32_t* cu, int32_t n_utts,
+                                  int32_t M, int32_t max_len, void* out, int32_t out_tmax, int32_t out_bf16,
+                                  fa_stream_t stream) {
   if (int r = check_batch(p, cu, n_utts, M, max_len)) return r;
+  if (int r = check_tmax(enc_tmax, max_len, "enc")) return r;
+  if (int r = check_tmax(out_tmax, max_len, "out")) return r;
   FA_REQUIRE(out != nullptr, "NULL out");
   FA_REQUIRE(p->w.lin1_w != nullptr, "plan was created without adaptor weights");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -322,7 +336,7 @@ extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, const int32_t* c
   const int D = c.ad_dim;
   int rc = 0;
   if (enc) {
-    if ((rc = launch_cast_bf16(enc, ws.enc_bf, static_cast<int64_t>(M) * c.d_model, s))) return rc;
+    if ((rc = launch_repack_rows(enc, enc_tmax, ws.enc_bf, 0, 1, cu, n_utts, M, c.d_model, s))) return rc;
   }
   // linear1 + ReLU, linear2                                                 VM:585-587
   GemmEpilogue e;
@@ -353,12 +367,12 @@ extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, const int32_t* c
     e.res1 = xo;
     if ((rc = run_gemm(L.ffn2, M, e, x, D, s))) return rc;
   }
-  if (out_bf16) return launch_cast_bf16(x, static_cast<__nv_bfloat16*>(out), static_cast<int64_t>(M) * D, s);
-  return launch_copy_f32(x, static_cast<float*>(out), static_cast<int64_t>(M) * D, s);
+  return launch_repack_rows(x, 0, out, out_tmax, out_bf16, cu, n_utts, M, D, s);
 }
 
-extern "C" int fa_encode_adapt(fa_plan* p, const float* feats, const int32_t* cu, int32_t n_utts, int32_t M,
-                               int32_t max_len, float* enc_out, void* out, int32_t out_bf16, fa_stream_t stream) {
-  if (int r = fa_encoder_forward(p, feats, cu, n_utts, M, max_len, enc_out, stream)) return r;
-  return fa_adaptor_forward(p, nullptr, cu, n_utts, M, max_len, out, out_bf16, stream);
+extern "C" int fa_encode_adapt(fa_plan* p, const float* feats, int32_t feats_tmax, const int32_t* cu, int32_t n_utts,
+                               int32_t M, int32_t max_len, float* enc_out, int32_t enc_out_tmax, void* out,
+                               int32_t out_tmax, int32_t out_bf16, fa_stream_t stream) {
+  if (int r = fa_encoder_forward(p, feats, feats_tmax, cu, n_utts, M, max_len, enc_out, enc_out_tmax, stream)) return r;
+  return fa_adaptor_forward(p, nullptr, 0, cu, n_utts, M, max_len, out, out_tmax, out_bf16, stream);
 }

@@ -14,12 +14,16 @@ constexpr int LN_VEC = LN_MAX_D / 128;  // float4 per lane
 // ---------------------------------------------------------------- utterance lookup
 // (first row, one-past-last row) of the utterance owning packed row r; cu_seqlens is tiny and
 // L1-resident, so a binary search per row is cheaper than materialising a per-row table.
-__device__ __forceinline__ int2 utt_bounds(const int32_t* __restrict__ cu, int n_utts, int r) {
+__device__ __forceinline__ int utt_index(const int32_t* __restrict__ cu, int n_utts, int r) {
   int lo = 0, hi = n_utts;
   while (hi - lo > 1) {
     const int mid = (lo + hi) >> 1;
     if (__ldg(cu + mid) <= r) lo = mid; else hi = mid;
   }
+  return lo;
+}
+__device__ __forceinline__ int2 utt_bounds(const int32_t* __restrict__ cu, int n_utts, int r) {
+  const int lo = utt_index(cu, n_utts, r);
   return make_int2(__ldg(cu + lo), __ldg(cu + lo + 1));
 }
 
@@ -39,6 +43,7 @@ struct LnArgs {
   int n_utts;
   float scale;
   int M, D;
+  int in_tmax;  // EMBED only: 0 = x is packed [M, D]; else x is padded [n_utts, in_tmax, D]
 };
 
 __device__ __forceinline__ void ln_stats(const float4 (&v)[LN_VEC], int nvec, int lane, int D, float& mean, float& rstd) {
@@ -64,7 +69,14 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= a.M) return;
   const int D = a.D, nvec = D >> 2;
-  const float4* xr = reinterpret_cast<const float4*>(a.x + static_cast<int64_t>(row) * D);
+  int64_t src_row = row;
+  int pos_i = 0;
+  if (EMBED) {
+    const int b = utt_index(a.cu, a.n_utts, row);
+    pos_i = row - __ldg(a.cu + b);
+    if (a.in_tmax > 0) src_row = static_cast<int64_t>(b) * a.in_tmax + pos_i;
+  }
+  const float4* xr = reinterpret_cast<const float4*>(a.x + src_row * D);
   float4 v[LN_VEC];
 #pragma unroll
   for (int i = 0; i < LN_VEC; ++i) {
@@ -74,7 +86,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
   if (EMBED) {
     // xs * sqrt(d_model) + [sin(p*inv) | cos(p*inv)],  p = 1..T within the utterance
     // (VLLM/model_executor/models/funasr.py:388-390, 256-290); fp32 like the reference.
-    const float pos = static_cast<float>(row - utt_bounds(a.cu, a.n_utts, row).x + 1);
+    const float pos = static_cast<float>(pos_i + 1);
     const int half = D >> 1;
 #pragma unroll
     for (int i = 0; i < LN_VEC; ++i) {
@@ -186,6 +198,38 @@ __global__ void copy_f32_kernel(const float4* __restrict__ x, float4* __restrict
     y[i] = x[i];
 }
 
+// Row re-layout + cast: dst row r (packed [M,D] or padded [n_utts, dst_tmax, D]) <- the matching
+// src row (packed or padded [n_utts, src_tmax, D]), f32 -> f32 | bf16; padding rows are zero-filled.
+// This is the only place the padded [B, Tmax, .] layout of the reference API exists.
+__global__ void __launch_bounds__(256)
+repack_rows_kernel(const float* __restrict__ src, int src_tmax, void* __restrict__ dst, int dst_tmax, int dst_bf16,
+                   const int32_t* __restrict__ cu, int n_utts, int dst_rows, int D) {
+  const int lane = threadIdx.x & 31;
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= dst_rows) return;
+  int b, t;
+  bool valid = true;
+  if (dst_tmax > 0) {
+    b = r / dst_tmax;
+    t = r - b * dst_tmax;
+    valid = t < __ldg(cu + b + 1) - __ldg(cu + b);
+  } else {
+    b = utt_index(cu, n_utts, r);
+    t = r - __ldg(cu + b);
+  }
+  const int64_t sr = src_tmax > 0 ? static_cast<int64_t>(b) * src_tmax + t : static_cast<int64_t>(__ldg(cu + b)) + t;
+  const float4* s4 = reinterpret_cast<const float4*>(src + sr * D);
+  const int nvec = D >> 2;
+  for (int c = lane; c < nvec; c += 32) {
+    const float4 v = valid ? __ldg(s4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (dst_bf16)
+      reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(dst) + static_cast<int64_t>(r) * D)[c] =
+          make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+    else
+      reinterpret_cast<float4*>(static_cast<float*>(dst) + static_cast<int64_t>(r) * D)[c] = v;
+  }
+}
+
 template <typename T>
 __device__ __forceinline__ float ld_as_f32(const void* p, int64_t i);
 template <>
@@ -230,16 +274,16 @@ static int ln_check(int D, const void* x) {
 int launch_layernorm(const float* x, const float* g, const float* b, const float* g2, const float* b2,
                      __nv_bfloat16* y_bf16, float* y_f32, int M, int D, cudaStream_t stream) {
   if (int r = ln_check(D, x)) return r;
-  ew::LnArgs a{x, g, b, g2, b2, y_bf16, y_f32, nullptr, nullptr, 0, 1.f, M, D};
+  ew::LnArgs a{x, g, b, g2, b2, y_bf16, y_f32, nullptr, nullptr, 0, 1.f, M, D, 0};
   ew::layernorm_kernel<false><<<ceil_div(M, 8), 256, 0, stream>>>(a);
   FA_CHECK_LAUNCH();
   return 0;
 }
 
-int launch_embed_layernorm(const float* x, const float* inv_ts, const int32_t* cu, int n_utts, float scale,
+int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, const int32_t* cu, int n_utts, float scale,
                            const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream) {
   if (int r = ln_check(D, x)) return r;
-  ew::LnArgs a{x, g, b, nullptr, nullptr, y, nullptr, inv_ts, cu, n_utts, scale, M, D};
+  ew::LnArgs a{x, g, b, nullptr, nullptr, y, nullptr, inv_ts, cu, n_utts, scale, M, D, in_tmax};
   ew::layernorm_kernel<true><<<ceil_div(M, 8), 256, 0, stream>>>(a);
   FA_CHECK_LAUNCH();
   return 0;
@@ -252,6 +296,17 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
   const int threads = 256;
   dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 2, threads));
   ew::fsmn_kernel<<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, mem, M, D, kernel, left_pad);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, int dst_bf16, const int32_t* cu,
+                       int n_utts, int M, int D, cudaStream_t stream) {
+  FA_REQUIRE(D % 4 == 0, "repack: D=%d must be a multiple of 4", D);
+  FA_REQUIRE((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0,
+             "repack: buffers must be 16-byte aligned");
+  const int rows = dst_tmax > 0 ? n_utts * dst_tmax : M;
+  ew::repack_rows_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(src, src_tmax, dst, dst_tmax, dst_bf16, cu, n_utts, rows, D);
   FA_CHECK_LAUNCH();
   return 0;
 }
@@ -290,7 +345,7 @@ extern "C" int fa_op_embed_layernorm(const float* x_dev, const float* inv_ts_dev
                                      void* y_bf16_dev, int32_t M, int32_t D, fa_stream_t stream) {
   FA_REQUIRE(x_dev && inv_ts_dev && cu_seqlens_dev && g_dev && b_dev && y_bf16_dev && M > 0 && n_utts > 0,
              "embed_layernorm: bad arguments");
-  return launch_embed_layernorm(x_dev, inv_ts_dev, cu_seqlens_dev, n_utts, scale, g_dev, b_dev,
+  return launch_embed_layernorm(x_dev, 0, inv_ts_dev, cu_seqlens_dev, n_utts, scale, g_dev, b_dev,
                                 static_cast<__nv_bfloat16*>(y_bf16_dev), M, D, static_cast<cudaStream_t>(stream));
 }
 

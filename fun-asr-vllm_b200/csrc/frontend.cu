@@ -94,8 +94,8 @@ __device__ __forceinline__ void fft16(float2 (&x)[16]) {
 
 template <int MODE>  // 0: LFR + CMVN rows, 1: raw log-mel rows
 __global__ void __launch_bounds__(THREADS, 2)
-fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, const int64_t* __restrict__ wav_off,
-             const int32_t* __restrict__ out_row, const int32_t* __restrict__ tile_off, int n_utts,
+fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, const int64_t* __restrict__ wav_start,
+             const int32_t* __restrict__ wav_len, const int32_t* __restrict__ out_row, const int32_t* __restrict__ tile_off, int n_utts,
              const float* __restrict__ cmvn, float* __restrict__ out, int64_t out_ld, float upscale, float preemph,
              float log_floor) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -116,8 +116,8 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     b = blockIdx.y;
     ti = blockIdx.x;
   }
-  const int64_t w0 = wav_off[b];
-  const int n = static_cast<int>(wav_off[b + 1] - w0);
+  const int64_t w0 = wav_start[b];
+  const int n = wav_len[b];
   if (n < FRAME_LEN) return;
   const int m = 1 + (n - FRAME_LEN) / SHIFT;  // TA:62-66 snip_edges
   int i0 = 0, i1 = 0, f_lo, f_hi;
@@ -320,12 +320,14 @@ extern "C" int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float*
 }
 
 extern "C" int fa_frontend_forward(const fa_frontend_cfg* cfg, const void* tables_dev, const float* wav_dev,
-                                   const int64_t* wav_off_dev, const int32_t* out_row_dev, const int32_t* tile_off_dev,
+                                   const int64_t* wav_start_dev, const int32_t* wav_len_dev,
+                                   const int32_t* out_row_dev, const int32_t* tile_off_dev,
                                    int32_t n_utts, int32_t n_tiles, const float* cmvn_dev, float* out_dev,
                                    int64_t out_ld, fa_stream_t stream) {
   if (int r = check_cfg(cfg)) return r;
   FA_REQUIRE(n_utts > 0, "empty batch");
-  FA_REQUIRE(tables_dev && wav_dev && wav_off_dev && out_row_dev && tile_off_dev && out_dev, "NULL device pointer");
+  FA_REQUIRE(tables_dev && wav_dev && wav_start_dev && wav_len_dev && out_row_dev && tile_off_dev && out_dev,
+             "NULL device pointer");
   FA_REQUIRE(out_ld >= FEAT && out_ld % 4 == 0, "out_ld must be >= %d and a multiple of 4", FEAT);
   FA_REQUIRE((reinterpret_cast<uintptr_t>(out_dev) & 15) == 0, "out_dev must be 16-byte aligned");
   if (n_tiles <= 0) return 0;
@@ -336,18 +338,20 @@ extern "C" int fa_frontend_forward(const fa_frontend_cfg* cfg, const void* table
     attr_done = true;
   }
   fbank_kernel<0><<<n_tiles, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const Tables*>(tables_dev), wav_dev, wav_off_dev, out_row_dev, tile_off_dev, n_utts, cmvn_dev,
+      static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, tile_off_dev, n_utts,
+      cmvn_dev,
       out_dev, out_ld, cfg->upscale, cfg->preemph, cfg->log_floor);
   FA_CHECK_LAUNCH();
   return 0;
 }
 
 extern "C" int fa_frontend_logmel(const fa_frontend_cfg* cfg, const void* tables_dev, const float* wav_dev,
-                                  const int64_t* wav_off_dev, const int32_t* out_row_dev, int32_t n_utts,
+                                  const int64_t* wav_start_dev, const int32_t* wav_len_dev,
+                                  const int32_t* out_row_dev, int32_t n_utts,
                                   int32_t max_frames, float* out_dev, int64_t out_ld, fa_stream_t stream) {
   if (int r = check_cfg(cfg)) return r;
   FA_REQUIRE(n_utts > 0 && max_frames > 0, "empty batch");
-  FA_REQUIRE(tables_dev && wav_dev && wav_off_dev && out_row_dev && out_dev, "NULL device pointer");
+  FA_REQUIRE(tables_dev && wav_dev && wav_start_dev && wav_len_dev && out_row_dev && out_dev, "NULL device pointer");
   FA_REQUIRE(out_ld >= NMEL && out_ld % 4 == 0, "out_ld must be >= %d and a multiple of 4", NMEL);
   static bool attr_done = false;
   if (!attr_done) {
@@ -357,7 +361,8 @@ extern "C" int fa_frontend_logmel(const fa_frontend_cfg* cfg, const void* tables
   }
   dim3 grid(ceil_div(max_frames, RAW_TILE_FRAMES), n_utts);
   fbank_kernel<1><<<grid, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const Tables*>(tables_dev), wav_dev, wav_off_dev, out_row_dev, nullptr, n_utts, nullptr, out_dev,
+      static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, nullptr, n_utts, nullptr,
+      out_dev,
       out_ld, cfg->upscale, cfg->preemph, cfg->log_floor);
   FA_CHECK_LAUNCH();
   return 0;

@@ -1,0 +1,61 @@
+"""End-to-end audio path: host PCM -> pinned staging -> H2D -> fbank/LFR/CMVN -> SAN-M encoder -> adaptor -> bf16
+``prompt_embeds`` rows -> D2H.  This is what ``bench.py`` times as ``e2e`` and what a batched driver
+(``/root/reference/infer.py:444-475``) reduces to once the three seams are patched: the three calls
+``extract_fbank`` / ``audio_encoder`` / ``audio_adaptor`` plus the per-utterance ``cat`` become one packed pass with
+no padded intermediates.  vLLM wants CPU tensors for ``prompt_embeds`` (VLLM/renderers/base.py:755-758), hence the D2H."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .encoder import AudioTower
+from .frontend import WavFrontend
+
+
+class AudioPipeline:
+    def __init__(self, frontend: WavFrontend, tower: AudioTower, device=None):
+        self.frontend, self.tower = frontend, tower
+        self.device = torch.device(device) if device is not None else tower.encoder._device()
+        self._pin_in = self._pin_out = self._dev_in = None
+
+    def _staging(self, n_in: int, n_out_rows: int, dim: int):
+        if self._pin_in is None or self._pin_in.numel() < n_in:
+            self._pin_in = torch.empty(n_in, dtype=torch.float32).pin_memory()
+            self._dev_in = torch.empty(n_in, dtype=torch.float32, device=self.device)
+        if self._pin_out is None or self._pin_out.shape[0] < n_out_rows or self._pin_out.shape[1] != dim:
+            self._pin_out = torch.empty((n_out_rows, dim), dtype=torch.bfloat16).pin_memory()
+
+    @torch.no_grad()
+    def features(self, wav_dev: torch.Tensor, starts: np.ndarray, n_samples: np.ndarray):
+        """Device-resident stage 1: packed PCM -> packed [sum T, 560] fp32 features."""
+        return self.frontend.forward_packed(wav_dev, starts, n_samples)
+
+    @torch.no_grad()
+    def embed_device(self, wav_dev: torch.Tensor, starts: np.ndarray, n_samples: np.ndarray, out: torch.Tensor | None = None):
+        """Device-resident whole path: packed PCM on the GPU -> packed bf16 ``[sum T, llm_dim]`` on the GPU."""
+        feats, cu = self.frontend.forward_packed(wav_dev, starts, n_samples)
+        out, _ = self.tower.forward_packed(feats, np.diff(cu), out=out)
+        return out, cu
+
+    @torch.no_grad()
+    def __call__(self, wavs: list) -> tuple[list[torch.Tensor], np.ndarray]:
+        """list of 1-D fp32 CPU waveforms -> list of CPU bf16 ``[T_b, llm_dim]`` tensors (views of one pinned buffer,
+        valid until the next call) + lengths.  One H2D, one D2H, one stream sync."""
+        lens = np.asarray([int(w.numel()) for w in wavs], dtype=np.int64)
+        starts = np.zeros(len(wavs), np.int64)
+        starts[1:] = np.cumsum((lens[:-1] + 3) // 4 * 4)
+        total = int(starts[-1] + (lens[-1] + 3) // 4 * 4)
+        _, T = self.frontend.lengths(lens)
+        rows = int(T.sum())
+        dim = self.tower.adaptor.llm_dim
+        self._staging(total, rows, dim)
+        host = self._pin_in[:total]
+        for w, s, n in zip(wavs, starts, lens):
+            host[s:s + n] = w.reshape(-1)
+        dev = self._dev_in[:total]
+        dev.copy_(host, non_blocking=True)
+        out, cu = self.embed_device(dev, starts, lens)
+        res = self._pin_out[:rows]
+        res.copy_(out, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return [res[cu[b]:cu[b + 1]] for b in range(len(wavs))], np.diff(cu)

@@ -74,21 +74,22 @@ int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float* window, co
                              void* blob_host);
 
 /* Fused framing + DC removal + pre-emphasis + window + 512-pt rFFT + power + mel + log + LFR + CMVN.
- *   wav_dev      : packed f32 PCM in [-1,1)
- *   wav_off_dev  : [n_utts+1] int64 sample offsets into wav_dev
+ *   wav_dev       : packed f32 PCM in [-1,1)
+ *   wav_start_dev : [n_utts] int64 first sample of each utterance in wav_dev
+ *   wav_len_dev   : [n_utts] int32 samples per utterance (>= frame_len)
  *   out_row_dev  : [n_utts]   int32 first output row of each utterance (packed: cu_seqlens[b];
  *                  padded [B,Tmax,.]: b*Tmax)
  *   tile_off_dev : [n_utts+1] int32 prefix sum of ceil(T_b / FA_FE_TILE_ROWS)
  *   cmvn_dev     : [2, lfr_m*n_mels] (means; scales) or NULL            VLLM:23-37
  *   out_dev      : f32, row stride out_ld (>= lfr_m*n_mels) */
 int fa_frontend_forward(const fa_frontend_cfg* cfg, const void* tables_dev, const float* wav_dev,
-                        const int64_t* wav_off_dev, const int32_t* out_row_dev,
+                        const int64_t* wav_start_dev, const int32_t* wav_len_dev, const int32_t* out_row_dev,
                         const int32_t* tile_off_dev, int32_t n_utts, int32_t n_tiles,
                         const float* cmvn_dev, float* out_dev, int64_t out_ld, fa_stream_t stream);
 
 /* Raw 80-bin log-mel (no LFR/CMVN), [m_b, n_mels] rows at out_row_dev[b]; used by parity tests. */
 int fa_frontend_logmel(const fa_frontend_cfg* cfg, const void* tables_dev, const float* wav_dev,
-                       const int64_t* wav_off_dev, const int32_t* out_row_dev, int32_t n_utts,
+                       const int64_t* wav_start_dev, const int32_t* wav_len_dev, const int32_t* out_row_dev, int32_t n_utts,
                        int32_t max_frames, float* out_dev, int64_t out_ld, fa_stream_t stream);
 
 int32_t fa_num_frames(int32_t n_samples, int32_t frame_len, int32_t frame_shift); /* TA:62-66 */
@@ -162,25 +163,34 @@ typedef struct {
   const fa_adaptor_layer_w* ad_layers; /* HOST array [ad_layers] */
 } fa_model_w;
 
-typedef struct fa_plan fa_plan; /* host-side plan: TMA descriptors + workspace carve-up. No device allocation. */
+/* host-side plan: TMA descriptors + workspace carve-up. No device allocation.  A plan may hold the
+ * encoder only (lin1_w == NULL), the adaptor only (n_blocks == 0, layers == NULL) or both. */
+typedef struct fa_plan fa_plan;
 
 size_t fa_plan_workspace_bytes(const fa_model_cfg* cfg, int32_t max_tokens);
 int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void* workspace_dev, size_t workspace_bytes,
                    int32_t max_tokens, fa_plan** plan_out);
 void fa_plan_destroy(fa_plan* plan);
 
-/* feats_dev [n_tokens, d_in] f32 packed (NOT modified, unlike the reference's in-place scale,
- * VLLM/...:388);  enc_out_dev [n_tokens, d_model] f32 (may be NULL: result stays in the plan's
- * workspace for fa_adaptor_forward(enc_dev = NULL)). */
-int fa_encoder_forward(fa_plan* plan, const float* feats_dev, const int32_t* cu_seqlens_dev, int32_t n_utts,
-                       int32_t n_tokens, int32_t max_len, float* enc_out_dev, fa_stream_t stream);
-/* enc_dev [n_tokens, d_model] f32 packed, or NULL to consume the plan-resident encoder output.
- * out_dev [n_tokens, ad_dim]: f32 when out_bf16 == 0, bf16 otherwise. */
-int fa_adaptor_forward(fa_plan* plan, const float* enc_dev, const int32_t* cu_seqlens_dev, int32_t n_utts,
-                       int32_t n_tokens, int32_t max_len, void* out_dev, int32_t out_bf16, fa_stream_t stream);
-int fa_encode_adapt(fa_plan* plan, const float* feats_dev, const int32_t* cu_seqlens_dev, int32_t n_utts,
-                    int32_t n_tokens, int32_t max_len, float* enc_out_dev, void* out_dev, int32_t out_bf16,
-                    fa_stream_t stream);
+/* Layouts.  Every [rows, dim] activation argument comes with a `*_tmax`:
+ *   tmax == 0 : PACKED  [n_tokens, dim], utterance b at rows [cu_seqlens[b], cu_seqlens[b+1])
+ *   tmax  > 0 : PADDED  [n_utts, tmax, dim] exactly as the reference passes it (xs_pad, infer.py:455);
+ *               on output the padding rows are zero-filled.
+ * feats_dev is NOT modified (the reference scales it in place, VLLM/...:388).
+ * enc_out_dev f32 [.., d_model] may be NULL: the result stays in the plan's workspace for
+ * fa_adaptor_forward(enc_dev = NULL). */
+int fa_encoder_forward(fa_plan* plan, const float* feats_dev, int32_t feats_tmax, const int32_t* cu_seqlens_dev,
+                       int32_t n_utts, int32_t n_tokens, int32_t max_len, float* enc_out_dev, int32_t enc_out_tmax,
+                       fa_stream_t stream);
+/* enc_dev f32 [.., d_model], or NULL to consume the plan-resident encoder output.
+ * out_dev [.., ad_dim]: f32 when out_bf16 == 0, bf16 otherwise. */
+int fa_adaptor_forward(fa_plan* plan, const float* enc_dev, int32_t enc_tmax, const int32_t* cu_seqlens_dev,
+                       int32_t n_utts, int32_t n_tokens, int32_t max_len, void* out_dev, int32_t out_tmax,
+                       int32_t out_bf16, fa_stream_t stream);
+/* FunASRNano.forward_export: encoder then adaptor, the intermediate never leaves the workspace. */
+int fa_encode_adapt(fa_plan* plan, const float* feats_dev, int32_t feats_tmax, const int32_t* cu_seqlens_dev,
+                    int32_t n_utts, int32_t n_tokens, int32_t max_len, float* enc_out_dev, int32_t enc_out_tmax,
+                    void* out_dev, int32_t out_tmax, int32_t out_bf16, fa_stream_t stream);
 
 /* out rows: utterance b -> [prefix (P rows) | speech rows [cu[b], cu[b]+take_b) | suffix (S rows)] at
  * out_off[b].  take_dev == NULL: take all rows.  All matrices [rows, dim]; speech f32 or bf16,

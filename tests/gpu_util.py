@@ -1,0 +1,79 @@
+"""Helpers shared by the -m gpu parity tests (thin ctypes callers of the C ABI)."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from funasr_b200 import _lib
+
+
+def lib():
+    return _lib.load()
+
+
+def stream():
+    return _lib.stream_ptr()
+
+
+def dev(x, dtype=None):
+    t = torch.as_tensor(x)
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.contiguous().cuda()
+
+
+def cu_of(lens):
+    cu = np.zeros(len(lens) + 1, np.int32)
+    cu[1:] = np.cumsum(lens)
+    return cu
+
+
+def op_gemm(a_bf16, w_bf16, bias=None, res1=None, res2=None, relu=False, out_f32=False):
+    M, K = a_bf16.shape
+    N = w_bf16.shape[0]
+    c = torch.empty((M, N), dtype=torch.float32 if out_f32 else torch.bfloat16, device="cuda")
+    _lib.check(lib().fa_op_gemm(a_bf16.data_ptr(), a_bf16.stride(0), w_bf16.data_ptr(), w_bf16.stride(0), _lib.ptr(bias),
+                                _lib.ptr(res1), _lib.ptr(res2), c.data_ptr(), N, M, N, K, int(relu), int(out_f32), stream()),
+               "fa_op_gemm")
+    return c
+
+
+def op_layernorm(x, g, b, want_bf16=True, want_f32=True):
+    M, D = x.shape
+    yb = torch.empty((M, D), dtype=torch.bfloat16, device="cuda") if want_bf16 else None
+    yf = torch.empty((M, D), dtype=torch.float32, device="cuda") if want_f32 else None
+    _lib.check(lib().fa_op_layernorm(x.data_ptr(), g.data_ptr(), b.data_ptr(), _lib.ptr(yb), _lib.ptr(yf), M, D, stream()))
+    return yb, yf
+
+
+def op_embed_layernorm(x, inv_ts, cu, scale, g, b):
+    M, D = x.shape
+    y = torch.empty((M, D), dtype=torch.bfloat16, device="cuda")
+    cu_d = dev(cu)
+    _lib.check(lib().fa_op_embed_layernorm(x.data_ptr(), inv_ts.data_ptr(), cu_d.data_ptr(), len(cu) - 1, C.c_float(scale),
+                                           g.data_ptr(), b.data_ptr(), y.data_ptr(), M, D, stream()))
+    return y
+
+
+def op_fsmn(qkv_bf16, v_col, w, cu, D, K, left):
+    M = qkv_bf16.shape[0]
+    mem = torch.empty((M, D), dtype=torch.float32, device="cuda")
+    cu_d = dev(cu)
+    _lib.check(lib().fa_op_fsmn(qkv_bf16.data_ptr(), qkv_bf16.stride(0), v_col, w.data_ptr(), cu_d.data_ptr(), len(cu) - 1,
+                                mem.data_ptr(), M, D, K, left, stream()))
+    return mem
+
+
+def op_attention(qkv_bf16, cu, n_heads):
+    M = qkv_bf16.shape[0]
+    dm = n_heads * 128
+    ctx = torch.empty((M, dm), dtype=torch.bfloat16, device="cuda")
+    cu_d = dev(cu)
+    _lib.check(lib().fa_op_attention(qkv_bf16.data_ptr(), qkv_bf16.stride(0), cu_d.data_ptr(), len(cu) - 1,
+                                     int(np.diff(cu).max()), n_heads, ctx.data_ptr(), dm, stream()))
+    return ctx
+
+
+def rel_rms(got, want):
+    got, want = got.double().cpu(), want.double().cpu()
+    return float((got - want).pow(2).mean().sqrt() / want.pow(2).mean().sqrt().clamp_min(1e-30))

@@ -1,0 +1,113 @@
+"""-m gpu: SAN-M encoder + adaptor through the drop-in modules (C ABI underneath) vs the fp32 CPU oracle on the same
+bf16-rounded weights.  Tolerance (BASELINE.json: "a stated bf16 relative tolerance"): relative-to-RMS error
+<= 2e-2 after the full stack; bf16 activations feed every GEMM, accumulation / residual stream / LN / softmax are fp32."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 2e-2
+
+
+def _pair(n_blocks, tp_blocks, seed=4321):
+    import funasr_b200 as fb
+    from oracle import encoder as oe
+
+    conf = dict(oe.NANO_ENCODER_CONF, num_blocks=n_blocks, tp_blocks=tp_blocks)
+    o_enc = oe.seeded_init_(oe.SenseVoiceEncoderSmall(560, **conf), seed=seed)
+    o_ad = oe.seeded_init_(oe.Transformer(**oe.NANO_ADAPTOR_CONF), seed=seed + 1)
+    enc = fb.SenseVoiceEncoderSmall(560, **conf)
+    ad = fb.Transformer(**oe.NANO_ADAPTOR_CONF)
+    enc.load_state_dict(o_enc.state_dict(), strict=True)
+    ad.load_state_dict(o_ad.state_dict(), strict=True)
+    return o_enc, o_ad, enc.cuda(), ad.cuda()
+
+
+def _rel(got, want):
+    got, want = got.double().cpu(), want.double()
+    return float((got - want).pow(2).mean().sqrt() / want.pow(2).mean().sqrt())
+
+
+def _batch(lens, seed=55):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(len(lens), max(lens), 560, generator=g)
+    for b, t in enumerate(lens):
+        x[b, t:] = 0
+    return x, torch.tensor(lens, dtype=torch.int32)
+
+
+def test_golden_nano_width_vs_vllm_classes(encoder_golden):
+    """Committed outputs of vLLM's own SenseVoiceEncoderSmall / Transformer (2+1 blocks, Nano widths)."""
+    g = encoder_golden
+    _, _, enc, ad = _pair(2, 1)
+    x, lens = torch.from_numpy(g["B_x"]), torch.from_numpy(g["B_lens"])
+    y, ol = enc(x.cuda(), lens)
+    assert ol.dtype == torch.int32 and tuple(y.shape) == (2, 9, 512)
+    for b in range(2):
+        t = int(lens[b])
+        assert _rel(y[b, :t], torch.from_numpy(g["B_y_pad"][b, :t])) < REL_TOL
+        assert torch.all(y[b, t:] == 0)
+        z, _ = ad(torch.from_numpy(g["B_y_pad"][b:b + 1, :t]).cuda(), lens[b:b + 1])
+        assert _rel(z[0], torch.from_numpy(g[f"B_z_single_{b}"])) < REL_TOL
+
+
+@pytest.mark.parametrize("lens", [[167, 40, 1, 98], [500], [17, 17]])
+def test_encoder_adaptor_vs_oracle_ragged(lens):
+    o_enc, o_ad, enc, ad = _pair(3, 2)
+    x, il = _batch(lens)
+    x0 = x.clone()
+    want_y, _ = o_enc(x, il)
+    want_z, _ = o_ad(want_y, il)
+    xg = x0.cuda()
+    y, ol = enc(xg, il.cuda())
+    assert torch.equal(xg.cpu(), x0)  # input not modified (the reference scales it in place)
+    z, zl = ad(y, ol)
+    for b, t in enumerate(lens):
+        e_y, e_z = _rel(y[b, :t], want_y[b, :t]), _rel(z[b, :t], want_z[b, :t])
+        print(f"len {t}: encoder rel-rms {e_y:.3e}, adaptor rel-rms {e_z:.3e}")
+        assert e_y < REL_TOL and e_z < REL_TOL
+    assert zl.tolist() == lens
+
+
+def test_fused_tower_equals_separate_calls_and_is_batch_invariant():
+    import funasr_b200 as fb
+
+    _, _, enc, ad = _pair(2, 1)
+    x, il = _batch([60, 33, 7])
+    y, ol = enc(x.cuda(), il)
+    z, _ = ad(y, ol)
+    tower = fb.AudioTower(enc, ad)
+    zf, _ = tower.forward_export(x.cuda(), il)
+    for b, t in enumerate(il.tolist()):
+        assert _rel(zf[b, :t], z[b, :t].cpu()) < 5e-3  # the fused path keeps the encoder output in bf16+fp32 workspace
+    # packed == padded, and an utterance's result does not depend on its batch neighbours
+    feats = torch.cat([x[b, :t] for b, t in enumerate(il.tolist())]).cuda()
+    zp, cu = tower.forward_packed(feats, il.numpy(), out_dtype=torch.float32)
+    for b, t in enumerate(il.tolist()):
+        assert torch.equal(zp[cu[b]:cu[b + 1]], zf[b, :t])
+    z1, _ = tower.forward_export(x[1:2, :33].cuda(), il[1:2])
+    assert torch.equal(z1[0], zf[1, :33])
+
+
+def test_full_depth_50_20_one_utterance():
+    """The Nano stack (50 + 20 blocks + adaptor) on one 3 s utterance: error growth through 70 layers stays in budget."""
+    o_enc, o_ad, enc, ad = _pair(50, 20)
+    x, il = _batch([50], seed=9)
+    want_y, _ = o_enc(x, il)
+    want_z, _ = o_ad(want_y, il)
+    y, ol = enc(x.cuda(), il)
+    z, _ = ad(y, ol)
+    e_y, e_z = _rel(y[0], want_y[0]), _rel(z[0], want_z[0])
+    print(f"70 layers: encoder rel-rms {e_y:.3e}, adaptor rel-rms {e_z:.3e}")
+    assert e_y < REL_TOL and e_z < REL_TOL
+
+
+def test_state_dict_reload_invalidates_plan():
+    o_enc, _, enc, _ = _pair(2, 0)
+    x, il = _batch([20])
+    y0, _ = enc(x.cuda(), il)
+    sd = {k: v.clone() for k, v in enc.state_dict().items()}
+    sd["after_norm.bias"] += 1.0
+    enc.load_state_dict(sd)
+    y1, _ = enc(x.cuda(), il)
+    assert not torch.equal(y0, y1)

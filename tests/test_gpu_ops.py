@@ -1,0 +1,125 @@
+"""-m gpu: every single-op entry point of the C ABI against plain PyTorch fp32 math on the same inputs."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def U():
+    import gpu_util
+
+    return gpu_util
+
+
+def bf(x):
+    return x.to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (2672, 1536, 512), (2672, 1536, 560), (2672, 512, 2048), (167, 2048, 512),
+                                   (1, 512, 512), (300, 256, 1024), (1000, 3072, 1024), (19000, 2048, 512), (129, 1024, 256)])
+def test_gemm_bias_vs_fp32(U, M, N, K):
+    g = torch.Generator().manual_seed(M * 7 + N + K)
+    a = bf(torch.randn(M, K, generator=g)).cuda()
+    w = bf(torch.randn(N, K, generator=g) / math.sqrt(K)).cuda()
+    bias = torch.randn(N, generator=g).cuda()
+    want = a.float() @ w.float().t() + bias
+    got = U.op_gemm(a, w, bias, out_f32=True)
+    torch.cuda.synchronize()
+    # fp32 accumulation of exact bf16 products: only summation order differs
+    assert (got - want).abs().max().item() <= 2e-3 * max(1.0, want.abs().max().item())
+    got_bf = U.op_gemm(a, w, bias, relu=True)
+    assert U.rel_rms(got_bf.float(), torch.relu(want)) < 4e-3
+
+
+def test_gemm_residual_epilogues(U):
+    g = torch.Generator().manual_seed(5)
+    M, N, K = 777, 512, 512
+    a = bf(torch.randn(M, K, generator=g)).cuda()
+    w = bf(torch.randn(N, K, generator=g) / math.sqrt(K)).cuda()
+    bias, r1, r2 = torch.randn(N, generator=g).cuda(), torch.randn(M, N, generator=g).cuda(), torch.randn(M, N, generator=g).cuda()
+    want = a.float() @ w.float().t() + bias + r1 + r2
+    got = U.op_gemm(a, w, bias, r1, r2, out_f32=True)
+    assert (got - want).abs().max().item() < 2e-3 * want.abs().max().item()
+    got1 = U.op_gemm(a, w, bias, r1, None, out_f32=True)
+    assert (got1 - (want - r2)).abs().max().item() < 2e-3 * want.abs().max().item()
+
+
+@pytest.mark.parametrize("M,D", [(1, 512), (167, 560), (2672, 512), (1000, 1024), (37, 64)])
+def test_layernorm(U, M, D):
+    g = torch.Generator().manual_seed(M + D)
+    x = (3 * torch.randn(M, D, generator=g) + 1).cuda()
+    gam, bet = (1 + 0.1 * torch.randn(D, generator=g)).cuda(), (0.1 * torch.randn(D, generator=g)).cuda()
+    want = torch.nn.functional.layer_norm(x, (D,), gam, bet, eps=1e-12)
+    yb, yf = U.op_layernorm(x, gam, bet)
+    assert (yf - want).abs().max().item() < 2e-5
+    assert (yb.float() - want).abs().max().item() < 4e-2  # bf16 rounding of O(4) values
+
+
+def test_embed_layernorm_positions_restart_per_utterance(U):
+    g = torch.Generator().manual_seed(3)
+    lens = [167, 1, 500, 17]
+    cu = U.cu_of(lens)
+    M, D = int(cu[-1]), 560
+    x = torch.randn(M, D, generator=g)
+    gam, bet = 1 + 0.1 * torch.randn(D, generator=g), 0.1 * torch.randn(D, generator=g)
+    inc = torch.log(torch.tensor([10000.0])) / (D / 2 - 1)
+    inv = torch.exp(torch.arange(D // 2, dtype=torch.float32) * (-inc))
+    rows = []
+    for b, T in enumerate(lens):  # VLLM/model_executor/models/funasr.py:256-290,388-390
+        pos = torch.arange(1, T + 1, dtype=torch.float32)[:, None] * inv[None]
+        pe = torch.cat([pos.sin(), pos.cos()], 1)
+        rows.append(x[cu[b]:cu[b + 1]] * math.sqrt(512.0) + pe)
+    want = torch.nn.functional.layer_norm(torch.cat(rows), (D,), gam, bet, eps=1e-12)
+    got = U.op_embed_layernorm(x.cuda(), inv.cuda(), cu, math.sqrt(512.0), gam.cuda(), bet.cuda())
+    assert (got.float().cpu() - want).abs().max().item() < 4e-2
+    assert U.rel_rms(got.float(), want) < 4e-3
+
+
+@pytest.mark.parametrize("K,left", [(11, 5), (11, 7), (1, 0), (16, 8)])
+def test_fsmn_respects_utterance_boundaries(U, K, left):
+    g = torch.Generator().manual_seed(K)
+    lens = [40, 3, 1, 167, 12]
+    cu = U.cu_of(lens)
+    M, D = int(cu[-1]), 512
+    qkv = bf(torch.randn(M, 3 * D, generator=g))
+    w = torch.randn(D, K, generator=g) / math.sqrt(K)
+    v = qkv[:, 2 * D:].float()
+    rows = []
+    for b in range(len(lens)):  # VLLM/...:181-201 on one unpadded utterance
+        vb = v[cu[b]:cu[b + 1]].t()[None]
+        y = torch.nn.functional.conv1d(torch.nn.functional.pad(vb, (left, K - 1 - left)), w[:, None, :], groups=D)
+        rows.append((y + vb)[0].t())
+    want = torch.cat(rows)
+    got = U.op_fsmn(qkv.cuda(), 2 * D, w.cuda(), cu, D, K, left)
+    assert (got.cpu() - want).abs().max().item() < 1e-4
+
+
+@pytest.mark.parametrize("lens,H", [([167] * 3, 4), ([1, 64, 65, 128, 500, 17], 4), ([167, 30], 8), ([667], 4)])
+def test_attention_varlen(U, lens, H):
+    g = torch.Generator().manual_seed(sum(lens) + H)
+    cu = U.cu_of(lens)
+    M, dm = int(cu[-1]), H * 128
+    qkv = bf(torch.randn(M, 3 * dm, generator=g))
+    rows = []
+    for b in range(len(lens)):  # VLLM/...:250-252, 222-236 on one unpadded utterance
+        x = qkv[cu[b]:cu[b + 1]].float()
+        q, k, v = (x[:, i * dm:(i + 1) * dm].reshape(-1, H, 128).transpose(0, 1) for i in range(3))
+        p = torch.softmax((q * 128 ** -0.5) @ k.transpose(1, 2), dim=-1)
+        rows.append((p @ v).transpose(0, 1).reshape(-1, dm))
+    want = torch.cat(rows)
+    got = U.op_attention(qkv.cuda(), cu, H)
+    assert (got.float().cpu() - want).abs().max().item() < 3e-2
+    assert U.rel_rms(got.float(), want) < 1e-2
+
+
+def test_errors_are_reported_not_swallowed(U):
+    from funasr_b200 import FunASRB200Error
+
+    a = torch.zeros(8, 64, dtype=torch.bfloat16, device="cuda")
+    w = torch.zeros(48, 64, dtype=torch.bfloat16, device="cuda")  # N not a multiple of 64
+    with pytest.raises(FunASRB200Error, match="multiple of 64"):
+        U.op_gemm(a, w)
