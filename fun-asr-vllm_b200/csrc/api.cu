@@ -27,9 +27,56 @@ int sm_count() {
   return n;
 }
 
+// ---- profiling: event pairs around every launch, aggregated per kernel class on collect ----
+bool g_prof_on = false;
+namespace {
+struct ProfRec { int kind; cudaEvent_t a, b; };
+std::vector<ProfRec> g_prof_recs;
+std::vector<cudaEvent_t> g_prof_pool;
+cudaEvent_t prof_event() {
+  cudaEvent_t e = nullptr;
+  if (!g_prof_pool.empty()) { e = g_prof_pool.back(); g_prof_pool.pop_back(); }
+  else cudaEventCreate(&e);
+  return e;
+}
+}  // namespace
+void prof_mark(int kind, cudaStream_t s, bool begin) {
+  if (begin) {
+    ProfRec r{kind, prof_event(), nullptr};
+    cudaEventRecord(r.a, s);
+    g_prof_recs.push_back(r);
+  } else if (!g_prof_recs.empty()) {
+    ProfRec& r = g_prof_recs.back();
+    r.b = prof_event();
+    cudaEventRecord(r.b, s);
+  }
+}
+
 }  // namespace fa
 
 using namespace fa;
+
+extern "C" int fa_profile_enable(int32_t on) {
+  g_prof_on = on != 0;
+  return 0;
+}
+extern "C" int fa_profile_collect(float* ms_per_kind, int32_t* launches_per_kind, int32_t n_kinds) {
+  FA_REQUIRE(ms_per_kind && launches_per_kind && n_kinds >= K_NUM, "profile_collect: need %d slots", (int)K_NUM);
+  for (int i = 0; i < n_kinds; ++i) { ms_per_kind[i] = 0.f; launches_per_kind[i] = 0; }
+  for (ProfRec& r : g_prof_recs) {
+    if (r.b) {
+      FA_CHECK_CUDA(cudaEventSynchronize(r.b));
+      float ms = 0.f;
+      FA_CHECK_CUDA(cudaEventElapsedTime(&ms, r.a, r.b));
+      ms_per_kind[r.kind] += ms;
+      launches_per_kind[r.kind] += 1;
+      g_prof_pool.push_back(r.b);
+    }
+    g_prof_pool.push_back(r.a);
+  }
+  g_prof_recs.clear();
+  return 0;
+}
 
 extern "C" int fa_abi_version(void) { return FA_ABI_VERSION; }
 extern "C" const char* fa_last_error(void) { return g_err; }

@@ -208,6 +208,7 @@ int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seq
   }
   dim3 grid(ceil_div(max_len, attn::BQ), n_heads, n_utts);
   const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(attn::HD));
+  ProfScope _ps(K_ATTENTION, stream);
   attn::attention_kernel<<<grid, attn::THREADS, attn::SMEM_BYTES, stream>>>(qkv, ld, cu_seqlens, n_heads, ctx, ld_ctx,
                                                                            scale_log2e);
   FA_CHECK_LAUNCH();

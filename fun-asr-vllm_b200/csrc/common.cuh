@@ -36,6 +36,17 @@ void set_error(const char* fmt, ...);
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 int sm_count();
 
+// ---- per-kernel-class device timing (bench / profiling only; off by default, zero cost when off) ----
+enum Kind { K_FRONTEND = 0, K_GEMM, K_ATTENTION, K_LAYERNORM, K_FSMN, K_REPACK, K_SPLICE, K_NUM };
+extern bool g_prof_on;
+void prof_mark(int kind, cudaStream_t s, bool begin);
+struct ProfScope {  // brackets the launches issued during its lifetime with two events on `s`
+  int kind;
+  cudaStream_t s;
+  ProfScope(int k, cudaStream_t st) : kind(k), s(st) { if (g_prof_on) prof_mark(kind, s, true); }
+  ~ProfScope() { if (g_prof_on) prof_mark(kind, s, false); }
+};
+
 // ---- internal launchers shared between api.cu and the op entry points -----------------------
 struct GemmEpilogue {
   const float* bias = nullptr;  // [N]

@@ -275,6 +275,7 @@ int launch_layernorm(const float* x, const float* g, const float* b, const float
                      __nv_bfloat16* y_bf16, float* y_f32, int M, int D, cudaStream_t stream) {
   if (int r = ln_check(D, x)) return r;
   ew::LnArgs a{x, g, b, g2, b2, y_bf16, y_f32, nullptr, nullptr, 0, 1.f, M, D, 0};
+  ProfScope _ps(K_LAYERNORM, stream);
   ew::layernorm_kernel<false><<<ceil_div(M, 8), 256, 0, stream>>>(a);
   FA_CHECK_LAUNCH();
   return 0;
@@ -284,6 +285,7 @@ int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, con
                            const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream) {
   if (int r = ln_check(D, x)) return r;
   ew::LnArgs a{x, g, b, nullptr, nullptr, y, nullptr, inv_ts, cu, n_utts, scale, M, D, in_tmax};
+  ProfScope _ps(K_LAYERNORM, stream);
   ew::layernorm_kernel<true><<<ceil_div(M, 8), 256, 0, stream>>>(a);
   FA_CHECK_LAUNCH();
   return 0;
@@ -295,6 +297,7 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
   FA_REQUIRE(D % 2 == 0 && v_col % 2 == 0 && ld % 2 == 0, "fsmn: D, v_col and ld must be even");
   const int threads = 256;
   dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 2, threads));
+  ProfScope _ps(K_FSMN, stream);
   ew::fsmn_kernel<<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, mem, M, D, kernel, left_pad);
   FA_CHECK_LAUNCH();
   return 0;
@@ -306,6 +309,7 @@ int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, 
   FA_REQUIRE((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0,
              "repack: buffers must be 16-byte aligned");
   const int rows = dst_tmax > 0 ? n_utts * dst_tmax : M;
+  ProfScope _ps(K_REPACK, stream);
   ew::repack_rows_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(src, src_tmax, dst, dst_tmax, dst_bf16, cu, n_utts, rows, D);
   FA_CHECK_LAUNCH();
   return 0;
@@ -366,6 +370,7 @@ extern "C" int fa_splice_embeds(const void* speech_dev, int32_t speech_bf16, con
   FA_REQUIRE((n_prefix == 0 || prefix_dev) && (n_suffix == 0 || suffix_dev), "splice: NULL prefix/suffix");
   FA_REQUIRE(max_rows_per_utt > 0, "splice: max_rows_per_utt must be positive");
   dim3 grid(max_rows_per_utt, n_utts);
+  ProfScope _ps(K_SPLICE, static_cast<cudaStream_t>(stream));
   ew::splice_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(speech_dev, speech_bf16, cu_seqlens_dev,
                                                                          take_dev, prefix_dev, n_prefix, suffix_dev,
                                                                          n_suffix, out_off_dev, dim, out_dev, out_bf16);

@@ -337,6 +337,7 @@ extern "C" int fa_frontend_forward(const fa_frontend_cfg* cfg, const void* table
     FA_CHECK_CUDA(cudaFuncSetAttribute(fbank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
     attr_done = true;
   }
+  ProfScope _ps(K_FRONTEND, static_cast<cudaStream_t>(stream));
   fbank_kernel<0><<<n_tiles, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
       static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, tile_off_dev, n_utts,
       cmvn_dev,
@@ -360,6 +361,7 @@ extern "C" int fa_frontend_logmel(const fa_frontend_cfg* cfg, const void* tables
     attr_done = true;
   }
   dim3 grid(ceil_div(max_frames, RAW_TILE_FRAMES), n_utts);
+  ProfScope _ps(K_FRONTEND, static_cast<cudaStream_t>(stream));
   fbank_kernel<1><<<grid, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
       static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, nullptr, n_utts, nullptr,
       out_dev,

@@ -343,6 +343,7 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, int M, int N, 
   static_assert(sizeof(CUtensorMap) == sizeof(TensorMap2D::bytes), "CUtensorMap size");
   memcpy(&ma, ta.bytes, sizeof(ma));
   memcpy(&mb, tb.bytes, sizeof(mb));
+  ProfScope _ps(K_GEMM, stream);
   gemm_bf16_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, p);
   FA_CHECK_LAUNCH();
   return 0;

@@ -63,6 +63,8 @@ PROTOTYPES = {
     "fa_adaptor_forward": (C.c_int, [vp, vp, i32, vp, i32, i32, i32, vp, i32, i32, vp]),
     "fa_encode_adapt": (C.c_int, [vp, vp, i32, vp, i32, i32, i32, vp, i32, vp, i32, i32, vp]),
     "fa_splice_embeds": (C.c_int, [vp, i32, vp, vp, vp, i32, vp, i32, vp, i32, i32, vp, i32, i32, vp]),
+    "fa_profile_enable": (C.c_int, [i32]),
+    "fa_profile_collect": (C.c_int, [vp, vp, i32]),
     "fa_op_gemm": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, vp, i64, i32, i32, i32, i32, i32, vp]),
     "fa_op_layernorm": (C.c_int, [vp, vp, vp, vp, vp, i32, i32, vp]),
     "fa_op_embed_layernorm": (C.c_int, [vp, vp, vp, i32, f32, vp, vp, vp, i32, i32, vp]),
@@ -70,6 +72,7 @@ PROTOTYPES = {
     "fa_op_attention": (C.c_int, [vp, i64, vp, i32, i32, i32, vp, i64, vp]),
 }
 
+PROFILE_KINDS = ("frontend", "gemm", "attention", "layernorm", "fsmn", "repack", "splice")
 _lib = None
 
 
@@ -133,3 +136,15 @@ def stream_ptr(device=None) -> int:
     import torch
 
     return torch.cuda.current_stream(device).cuda_stream
+
+
+def profile_enable(on: bool) -> None:
+    check(load().fa_profile_enable(1 if on else 0), "fa_profile_enable")
+
+
+def profile_collect() -> dict:
+    """{kernel class: (device ms, launches)} since the last collect (see fa_profile_collect)."""
+    n = len(PROFILE_KINDS)
+    ms, cnt = (f32 * n)(), (i32 * n)()
+    check(load().fa_profile_collect(ms, cnt, n), "fa_profile_collect")
+    return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(PROFILE_KINDS)}

@@ -38,6 +38,19 @@ class AudioPipeline:
         return out, cu
 
     @torch.no_grad()
+    def run_pinned(self, host_pcm: torch.Tensor, starts: np.ndarray, n_samples: np.ndarray, out_host: torch.Tensor):
+        """Pinned packed PCM on the host -> pinned bf16 ``[sum T, llm_dim]`` on the host: H2D, the whole path, D2H, all
+        enqueued on the current stream (no sync here; the caller synchronises once)."""
+        total = host_pcm.numel()
+        if self._dev_in is None or self._dev_in.numel() < total:
+            self._dev_in = torch.empty(total, dtype=torch.float32, device=self.device)
+        dev = self._dev_in[:total]
+        dev.copy_(host_pcm, non_blocking=True)
+        out, cu = self.embed_device(dev, starts, n_samples)
+        out_host[: out.shape[0]].copy_(out, non_blocking=True)
+        return cu
+
+    @torch.no_grad()
     def __call__(self, wavs: list) -> tuple[list[torch.Tensor], np.ndarray]:
         """list of 1-D fp32 CPU waveforms -> list of CPU bf16 ``[T_b, llm_dim]`` tensors (views of one pinned buffer,
         valid until the next call) + lengths.  One H2D, one D2H, one stream sync."""

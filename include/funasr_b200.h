@@ -200,6 +200,16 @@ int fa_splice_embeds(const void* speech_dev, int32_t speech_bf16, const int32_t*
                      int32_t n_suffix, const int64_t* out_off_dev, int32_t n_utts, int32_t dim, void* out_dev,
                      int32_t out_bf16, int32_t max_rows_per_utt, fa_stream_t stream);
 
+/* ------------------------------------------------------------------ device timing (bench.py) */
+/* When enabled, every kernel launch the library makes is bracketed by a CUDA event pair on the
+ * caller's stream.  fa_profile_collect synchronises on them and returns, per kernel class
+ * (0 frontend, 1 gemm, 2 attention, 3 layernorm, 4 fsmn, 5 repack, 6 splice), the summed device time
+ * in ms and the launch count since the last collect.  Not thread safe; off by default.
+ * (New: the reference has no device timing, only time.perf_counter around whole calls, model.py:361-386.) */
+#define FA_PROFILE_KINDS 7
+int fa_profile_enable(int32_t on);
+int fa_profile_collect(float* ms_per_kind, int32_t* launches_per_kind, int32_t n_kinds);
+
 /* ------------------------------------------------------------------ single ops (parity tests) */
 /* C[M,N] = A[M,K] (bf16) * W[N,K]^T (bf16) + bias; relu optional; then
  *   out_f32 == 0: bf16 C;   out_f32 == 1: f32 C = acc + bias (+ res1) (+ res2)   (res* f32 [M,N] or NULL) */

@@ -97,10 +97,20 @@ def test_packed_varlen_batch_vs_oracle():
     wav, starts = pack_waveforms(wavs, "cuda")
     got, cu = fe.forward_packed(wav, starts, lens)
     got = got.cpu().numpy()
+    # Two fp32 implementations each sit up to ~7e-4 from the fp64 truth in the lowest mel bins on 30 s inputs (torchaudio
+    # fp32 vs this oracle fp32: 7.6e-4 on utterance 3), so the bound is stated against the fp64 truth, SURVEY.md §8c (8):
+    # err(kernel, fp64) <= max(1e-3, 1.5 * err(fp32 oracle, fp64)), in the log-mel domain (CMVN scale divided out).
     for b in [0, 1, 2, 3, 10, 33, 63]:
-        want, _ = of.wav_frontend_packed([wavs[b].numpy()], "hamming", cm)
-        assert cu[b + 1] - cu[b] == want.shape[0]
-        assert np.abs(got[cu[b]:cu[b + 1]] - want).max() <= 0.3 * TOL + 1e-6, b
+        w = [wavs[b].numpy()]
+        want32, _ = of.wav_frontend_packed(w, "hamming", cm)
+        want64, _ = of.wav_frontend_packed(w, "hamming", cm.astype(np.float64), dtype=np.float64)
+        assert cu[b + 1] - cu[b] == want32.shape[0]
+        e_ref = (np.abs(want32 - want64) / cm[1]).max()
+        e_got = (np.abs(got[cu[b]:cu[b + 1]] - want64) / cm[1]).max()
+        e_32 = (np.abs(got[cu[b]:cu[b + 1]] - want32) / cm[1]).max()
+        print(f"utt {b} ({lens[b]} samples): oracle32 vs f64 {e_ref:.2e}; kernel vs f64 {e_got:.2e}; kernel vs oracle32 {e_32:.2e}")
+        assert e_got <= max(TOL, 1.5 * e_ref) + 2e-6, b  # 2e-6: fp32 rounding of the CMVN'd output itself
+        assert e_32 <= 2 * TOL, b
     # size-independent property: each LFR row is 7 stacked fbank frames -> slot j of row i equals slot j-6.. of row i+1
     raw = got / cm[1] - cm[0]
     for b in (3, 40):
