@@ -146,41 +146,65 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
 // ---------------------------------------------------------------- FSMN memory block
 // mem[t, c] = v[t, c] + sum_k w[c, k] * v[t + k - left, c]   (zero outside the utterance)
 // (VLLM/model_executor/models/funasr.py:181-201: mask, ConstantPad1d, depthwise Conv1d, +inputs, mask).
-// One thread owns a channel pair and walks FSMN_ROWS consecutive rows with the 2*K-1 tap window
-// held in registers, so every v element is loaded once per CTA (plus the halo).
+// One thread owns 4 adjacent channels (one 8-byte bf16x4 load per row) and FSMN_ROWS consecutive
+// rows: the FSMN_ROWS + K - 1 input rows are loaded up front (independent loads, deep MLP), the tap
+// window then slides through registers, so every v element is read once per CTA plus the halo, a
+// warp reads 256 contiguous bytes per row and writes 512.  Utterance bounds of the CTA's rows are
+// found once per row (16 binary searches per CTA) and shared through smem.
 constexpr int FSMN_ROWS = 16;
 constexpr int FSMN_MAXK = 16;
 
-__global__ void __launch_bounds__(256)
+template <int K>
+__global__ void __launch_bounds__(128)
 fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
-            const int32_t* __restrict__ cu, int n_utts, float* __restrict__ mem, int M, int D, int K, int left) {
-  const int cp = blockIdx.y * blockDim.x + threadIdx.x;  // channel pair
-  if (2 * cp >= D) return;
+            const int32_t* __restrict__ cu, int n_utts, float* __restrict__ mem, int M, int D, int left) {
+  __shared__ int s_lo[FSMN_ROWS], s_hi[FSMN_ROWS];
   const int r0 = blockIdx.x * FSMN_ROWS;
-  float w0[FSMN_MAXK], w1[FSMN_MAXK];
-#pragma unroll
-  for (int k = 0; k < FSMN_MAXK; ++k) {
-    w0[k] = k < K ? __ldg(w + static_cast<int64_t>(2 * cp) * K + k) : 0.f;
-    w1[k] = k < K ? __ldg(w + static_cast<int64_t>(2 * cp + 1) * K + k) : 0.f;
-  }
-  const __nv_bfloat16* vbase = qkv + v_col + 2 * cp;
-  const int r1 = min(r0 + FSMN_ROWS, M);
-  for (int r = r0; r < r1; ++r) {
+  if (threadIdx.x < FSMN_ROWS) {
+    const int r = min(r0 + threadIdx.x, M - 1);
     const int2 ub = utt_bounds(cu, n_utts, r);
-    float a0 = 0.f, a1 = 0.f;
+    s_lo[threadIdx.x] = ub.x;
+    s_hi[threadIdx.x] = ub.y;
+  }
+  const int c4 = blockIdx.y * blockDim.x + threadIdx.x;  // group of 4 channels
+  const bool ch_ok = 4 * c4 < D;
+  constexpr int NIN = FSMN_ROWS + K - 1;
+  // ---- all input rows of this thread's 4 channels: independent 8-byte loads
+  uint2 raw[NIN];
+  const __nv_bfloat16* vbase = qkv + v_col + 4 * c4;
 #pragma unroll
-    for (int k = 0; k < FSMN_MAXK; ++k) {
-      if (k < K) {
-        const int rr = r + k - left;
-        if (rr >= ub.x && rr < ub.y) {
-          const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(vbase + static_cast<int64_t>(rr) * ld));
-          a0 = fmaf(w0[k], f.x, a0);
-          a1 = fmaf(w1[k], f.y, a1);
-        }
+  for (int i = 0; i < NIN; ++i) {
+    const int rr = r0 - left + i;
+    raw[i] = make_uint2(0u, 0u);
+    if (ch_ok && rr >= 0 && rr < M) raw[i] = __ldg(reinterpret_cast<const uint2*>(vbase + static_cast<int64_t>(rr) * ld));
+  }
+  float wt[4][K];
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+#pragma unroll
+    for (int k = 0; k < K; ++k)  // the "+ inputs" term (VLLM/...:199) is tap `left` with weight + 1: row r is always inside its own utterance
+      wt[c][k] = (ch_ok ? __ldg(w + static_cast<int64_t>(4 * c4 + c) * K + k) : 0.f) + (k == left ? 1.f : 0.f);
+  __syncthreads();
+  if (!ch_ok) return;
+#pragma unroll
+  for (int j = 0; j < FSMN_ROWS; ++j) {
+    const int r = r0 + j;
+    if (r >= M) break;
+    const int lo = s_lo[j], hi = s_hi[j];
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const int rr = r + k - left;
+      if (rr >= lo && rr < hi) {  // warp-uniform: the whole CTA shares r
+        const float2 f01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[j + k].x));
+        const float2 f23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[j + k].y));
+        a0 = fmaf(wt[0][k], f01.x, a0);
+        a1 = fmaf(wt[1][k], f01.y, a1);
+        a2 = fmaf(wt[2][k], f23.x, a2);
+        a3 = fmaf(wt[3][k], f23.y, a3);
       }
     }
-    const float2 self = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(vbase + static_cast<int64_t>(r) * ld));
-    *reinterpret_cast<float2*>(mem + static_cast<int64_t>(r) * D + 2 * cp) = make_float2(a0 + self.x, a1 + self.y);
+    *reinterpret_cast<float4*>(mem + static_cast<int64_t>(r) * D + 4 * c4) = make_float4(a0, a1, a2, a3);
   }
 }
 
@@ -294,11 +318,21 @@ int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, con
 int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts,
                 float* mem, int M, int D, int kernel, int left_pad, cudaStream_t stream) {
   FA_REQUIRE(kernel >= 1 && kernel <= ew::FSMN_MAXK, "fsmn: kernel size %d not in [1,%d]", kernel, ew::FSMN_MAXK);
-  FA_REQUIRE(D % 2 == 0 && v_col % 2 == 0 && ld % 2 == 0, "fsmn: D, v_col and ld must be even");
-  const int threads = 256;
-  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 2, threads));
+  FA_REQUIRE(left_pad >= 0 && left_pad < kernel, "fsmn: left pad %d outside the %d-tap window", left_pad, kernel);
+  FA_REQUIRE(D % 4 == 0 && v_col % 4 == 0 && ld % 4 == 0, "fsmn: D, v_col and ld must be multiples of 4");
+  FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 7) == 0 && (reinterpret_cast<uintptr_t>(mem) & 15) == 0,
+             "fsmn: qkv must be 8-byte and mem 16-byte aligned");
+  const int threads = 128;
+  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 4, threads));
   ProfScope _ps(K_FSMN, stream);
-  ew::fsmn_kernel<<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, mem, M, D, kernel, left_pad);
+#define FA_FSMN_CASE(KK) \
+  case KK: ew::fsmn_kernel<KK><<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, mem, M, D, left_pad); break;
+  switch (kernel) {
+    FA_FSMN_CASE(1) FA_FSMN_CASE(2) FA_FSMN_CASE(3) FA_FSMN_CASE(4) FA_FSMN_CASE(5) FA_FSMN_CASE(6) FA_FSMN_CASE(7) FA_FSMN_CASE(8)
+    FA_FSMN_CASE(9) FA_FSMN_CASE(10) FA_FSMN_CASE(11) FA_FSMN_CASE(12) FA_FSMN_CASE(13) FA_FSMN_CASE(14) FA_FSMN_CASE(15)
+    FA_FSMN_CASE(16)
+  }
+#undef FA_FSMN_CASE
   FA_CHECK_LAUNCH();
   return 0;
 }
