@@ -1,6 +1,8 @@
 // C-ABI orchestration: error state, device check, the encoder/adaptor plan (workspace carve-up +
 // TMA descriptors built once) and the layer schedule.  No device allocation, no synchronisation.
+#include <cmath>
 #include <cstring>
+#include <functional>
 #include <new>
 #include <vector>
 
@@ -95,25 +97,9 @@ extern "C" int fa_check_device(int32_t* sm, int32_t* major, int32_t* minor) {
 }
 
 // ------------------------------------------------------------------------------------------ plan
+// A plan is a "program": the exact kernel sequence of the encoder and of the adaptor, built once with every
+// pointer, TMA descriptor and tile choice resolved; the forward calls just replay it on the caller's stream.
 namespace {
-
-struct GemmOp {
-  TensorMap2D ta;     // activations [cap, K], box 128 x 64
-  TensorMap2D tb[3];  // weights [N, K], box {64,128,256} x 64 (one per tile width)
-  bool tb_ok[3] = {false, false, false};
-  int N = 0, K = 0;
-  const float* bias = nullptr;
-};
-
-struct SanmLayerPlan {
-  fa_sanm_layer_w w;
-  GemmOp qkv, out, ffn1, ffn2;
-  int d_in;
-};
-struct AdaptorLayerPlan {
-  fa_adaptor_layer_w w;
-  GemmOp qkv, out, ffn1, ffn2;
-};
 
 size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -183,27 +169,39 @@ int check_model_cfg(const fa_model_cfg* c) {
   return 0;
 }
 
-}  // namespace
+// per-call arguments of a program
+struct RunArgs {
+  int M, n_utts, max_len;
+  const int32_t* cu;
+  cudaStream_t s;
+};
+using Step = std::function<int(const RunArgs&)>;
 
-struct fa_plan {
-  fa_model_cfg cfg;
-  fa_model_w w;
-  int cap;
-  Workspace ws;
-  std::vector<SanmLayerPlan> layers;
-  std::vector<AdaptorLayerPlan> ad_layers;
-  GemmOp lin1, lin2;
-  int fsmn_left;
+// One nn.Linear resolved against fixed workspace buffers: A map (activations), one B map per tile width, C map.
+struct GemmOp {
+  TensorMap2D ta, tc;
+  TensorMap2D tb[3];
+  bool tb_ok[3] = {false, false, false};
+  int N = 0, K = 0;
+  GemmEpilogue epi;
+  void* c = nullptr;
+  int64_t ldc = 0;
 };
 
-namespace {
-
-int make_op(GemmOp* op, const void* a, int lda, const void* w, int N, int K, const float* bias, int cap) {
+int make_gemm_op(GemmOp* op, int cap, const void* a, int lda, const void* w, int N, int K, const float* bias, void* c,
+                 bool out_f32, bool relu, const float* res1, const float* res2) {
   op->N = N;
   op->K = K;
-  op->bias = bias;
+  op->c = c;
+  op->ldc = N;
+  op->epi.bias = bias;
+  op->epi.res1 = res1;
+  op->epi.res2 = res2;
+  op->epi.relu = relu ? 1 : 0;
+  op->epi.out_f32 = out_f32 ? 1 : 0;
   FA_REQUIRE(w != nullptr, "NULL weight pointer (N=%d K=%d)", N, K);
   if (int r = make_tensor_map_bf16(&op->ta, a, cap, K, lda, 128)) return r;
+  if (int r = make_tensor_map(&op->tc, c, out_f32 ? 4 : 2, cap, N, N, 32)) return r;
   for (int i = 0; i < 3; ++i) {
     const int bn = 64 << i;
     if (N % bn != 0) continue;
@@ -213,16 +211,129 @@ int make_op(GemmOp* op, const void* a, int lda, const void* w, int N, int K, con
   return 0;
 }
 
-}  // namespace
-
-static int run_gemm(GemmOp& op, int M, const GemmEpilogue& e_in, void* c, int64_t ldc, cudaStream_t s) {
-  const int bn = gemm_block_n(M, op.N);
+int run_gemm_op(const GemmOp& op, const RunArgs& a) {
+  const int bn = gemm_block_n(a.M, op.N);
   const int idx = bn == 64 ? 0 : (bn == 128 ? 1 : 2);
   FA_REQUIRE(bn != 0 && op.tb_ok[idx], "gemm N=%d unsupported", op.N);
-  GemmEpilogue e = e_in;
-  e.bias = op.bias;
-  return launch_gemm(op.ta, op.tb[idx], bn, M, op.N, op.K, e, c, ldc, s);
+  return launch_gemm(op.ta, op.tb[idx], op.tc, bn, a.M, op.N, op.K, op.epi, op.c, op.ldc, a.s);
 }
+
+}  // namespace
+
+struct fa_plan {
+  fa_model_cfg cfg;
+  fa_model_w w;
+  int cap;
+  Workspace ws;
+  std::vector<Step> enc_prog, ad_prog;
+};
+
+namespace {
+
+struct Builder {
+  fa_plan* p;
+  int rc = 0;
+  void gemm(std::vector<Step>& prog, const void* a, int lda, const void* w, int N, int K, const float* bias, void* c,
+            bool out_f32, bool relu = false, const float* res1 = nullptr, const float* res2 = nullptr) {
+    if (rc) return;
+    GemmOp op;
+    rc = make_gemm_op(&op, p->cap, a, lda, w, N, K, bias, c, out_f32, relu, res1, res2);
+    if (!rc) prog.push_back([op](const RunArgs& r) { return run_gemm_op(op, r); });
+  }
+  void ln(std::vector<Step>& prog, const float* x, const float* g, const float* b, const float* g2, const float* b2,
+          __nv_bfloat16* y_bf16, float* y_f32, int D) {
+    prog.push_back([=](const RunArgs& r) { return launch_layernorm(x, g, b, g2, b2, y_bf16, y_f32, r.M, D, r.s); });
+  }
+};
+
+int build_programs(fa_plan* p) {
+  const fa_model_cfg& c = p->cfg;
+  const fa_model_w& w = p->w;
+  Workspace& ws = p->ws;
+  Builder B{p};
+  const int d = c.d_model;
+  const int nl = c.n_blocks + c.n_tp_blocks;
+  const int left = (c.fsmn_kernel - 1) / 2 + (c.sanm_shift > 0 ? c.sanm_shift : 0);  // VM:175-179
+  // ---------------- encoder: the embed+LN input stage is issued by fa_encoder_forward (it needs the caller's feats)
+  float* x = ws.x;    // current residual stream
+  float* xo = ws.x2;  // next
+  std::vector<Step>& E = p->enc_prog;
+  for (int i = 0; i < nl; ++i) {
+    const fa_sanm_layer_w& L = w.layers[i];
+    const int din = (i == 0) ? c.d_in : d;
+    const void* a_in = (i == 0) ? static_cast<const void*>(ws.xn0) : static_cast<const void*>(ws.xn);
+    // q|k|v = LN1(x) W^T + b                                              VM:206
+    B.gemm(E, a_in, din, L.qkv_w, 3 * d, din, L.qkv_b, ws.qkv, false);
+    // FSMN memory on v                                                     VM:249,181-201
+    {
+      const __nv_bfloat16* qkv = ws.qkv;
+      const float* fw = L.fsmn_w;
+      float* mem = ws.mem;
+      const int K = c.fsmn_kernel;
+      E.push_back([=](const RunArgs& r) { return launch_fsmn(qkv, 3 * d, 2 * d, fw, r.cu, r.n_utts, mem, r.M, d, K, left, r.s); });
+    }
+    // masked MHA                                                           VM:250-252,222-236
+    {
+      const __nv_bfloat16* qkv = ws.qkv;
+      __nv_bfloat16* ctx = ws.ctx;
+      const int H = c.n_heads;
+      E.push_back([=](const RunArgs& r) { return launch_attention(qkv, 3 * d, r.cu, r.n_utts, r.max_len, H, ctx, d, r.s); });
+    }
+    // x' = [x +] ctx Wo^T + b + mem    (no residual when in_size != size)   VM:238,253,123-136
+    B.gemm(E, ws.ctx, d, L.out_w, d, d, L.out_b, xo, true, false, ws.mem, (i == 0) ? nullptr : x);
+    // LN2, FFN                                                              VM:138-140,412-431
+    B.ln(E, xo, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.xn, nullptr, d);
+    B.gemm(E, ws.xn, d, L.ffn1_w, c.d_ff, d, L.ffn1_b, ws.h, false, true);
+    B.gemm(E, ws.h, c.d_ff, L.ffn2_w, d, c.d_ff, L.ffn2_b, x, true, false, xo);  // residual stream back in x
+    // next layer's norm1, with after_norm / tp_norm folded in                VM:400,408
+    const bool last_main = (i == c.n_blocks - 1);
+    const bool last = (i == nl - 1);
+    if (last) {
+      if (c.n_tp_blocks == 0) {  // after_norm then tp_norm back to back (VM:400,408 with an empty tp_encoders list)
+        B.ln(E, x, w.after_norm_g, w.after_norm_b, nullptr, nullptr, nullptr, xo, d);
+        B.ln(E, xo, w.tp_norm_g, w.tp_norm_b, nullptr, nullptr, ws.enc_bf, ws.enc_f32, d);
+      } else {
+        B.ln(E, x, w.tp_norm_g, w.tp_norm_b, nullptr, nullptr, ws.enc_bf, ws.enc_f32, d);
+      }
+    } else if (last_main) {
+      // x <- after_norm(x) becomes the residual stream of the tp blocks; xn <- norm1_next(x)
+      B.ln(E, x, w.after_norm_g, w.after_norm_b, w.layers[i + 1].ln1_g, w.layers[i + 1].ln1_b, ws.xn, xo, d);
+      float* t = x; x = xo; xo = t;
+    } else {
+      B.ln(E, x, w.layers[i + 1].ln1_g, w.layers[i + 1].ln1_b, nullptr, nullptr, ws.xn, nullptr, d);
+    }
+  }
+  // ---------------- adaptor (input: ws.enc_bf)
+  if (w.lin1_w) {
+    std::vector<Step>& A = p->ad_prog;
+    const int D = c.ad_dim;
+    float* ax = ws.ax;
+    float* axo = ws.ax2;
+    // linear1 + ReLU, linear2                                                 VM:585-587
+    B.gemm(A, ws.enc_bf, c.d_model, w.lin1_w, c.ad_ffn, c.d_model, w.lin1_b, ws.h, false, true);
+    B.gemm(A, ws.h, c.ad_ffn, w.lin2_w, D, c.ad_ffn, w.lin2_b, ax, true);
+    for (int i = 0; i < c.ad_layers; ++i) {
+      if (!w.ad_layers) { set_error("plan_create: NULL adaptor layers"); return 2; }
+      const fa_adaptor_layer_w& L = w.ad_layers[i];
+      // pre-LN MHA block                                                       VM:434-455
+      B.ln(A, ax, L.ln1_g, L.ln1_b, nullptr, nullptr, ws.axn, nullptr, D);
+      B.gemm(A, ws.axn, D, L.qkv_w, 3 * D, D, L.qkv_b, ws.aqkv, false);
+      {
+        const __nv_bfloat16* qkv = ws.aqkv;
+        __nv_bfloat16* ctx = ws.actx;
+        const int H = c.ad_heads;
+        A.push_back([=](const RunArgs& r) { return launch_attention(qkv, 3 * D, r.cu, r.n_utts, r.max_len, H, ctx, D, r.s); });
+      }
+      B.gemm(A, ws.actx, D, L.out_w, D, D, L.out_b, axo, true, false, ax);
+      B.ln(A, axo, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.axn, nullptr, D);
+      B.gemm(A, ws.axn, D, L.ffn1_w, c.ad_ff, D, L.ffn1_b, ws.ah, false, true);
+      B.gemm(A, ws.ah, c.ad_ff, L.ffn2_w, D, c.ad_ff, L.ffn2_b, ax, true, false, axo);
+    }
+  }
+  return B.rc;
+}
+
+}  // namespace
 
 extern "C" size_t fa_plan_workspace_bytes(const fa_model_cfg* cfg, int32_t max_tokens) {
   if (check_model_cfg(cfg) != 0 || max_tokens <= 0) return 0;
@@ -248,36 +359,7 @@ extern "C" int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void
   p->w = *w;
   p->cap = cap;
   p->ws = ws;
-  const int left = (cfg->fsmn_kernel - 1) / 2 + (cfg->sanm_shift > 0 ? cfg->sanm_shift : 0);  // VM:175-179
-  p->fsmn_left = left;
-  const int nl = cfg->n_blocks + cfg->n_tp_blocks;
-  p->layers.resize(nl);
-  int rc = 0;
-  for (int i = 0; i < nl && rc == 0; ++i) {
-    SanmLayerPlan& L = p->layers[i];
-    L.w = w->layers[i];
-    L.d_in = (i == 0) ? cfg->d_in : cfg->d_model;
-    const void* a_in = (i == 0) ? static_cast<const void*>(ws.xn0) : static_cast<const void*>(ws.xn);
-    rc = make_op(&L.qkv, a_in, L.d_in, L.w.qkv_w, 3 * cfg->d_model, L.d_in, L.w.qkv_b, cap);
-    if (!rc) rc = make_op(&L.out, ws.ctx, cfg->d_model, L.w.out_w, cfg->d_model, cfg->d_model, L.w.out_b, cap);
-    if (!rc) rc = make_op(&L.ffn1, ws.xn, cfg->d_model, L.w.ffn1_w, cfg->d_ff, cfg->d_model, L.w.ffn1_b, cap);
-    if (!rc) rc = make_op(&L.ffn2, ws.h, cfg->d_ff, L.w.ffn2_w, cfg->d_model, cfg->d_ff, L.w.ffn2_b, cap);
-  }
-  if (!rc && cfg->ad_layers >= 0 && w->lin1_w) {
-    rc = make_op(&p->lin1, ws.enc_bf, cfg->d_model, w->lin1_w, cfg->ad_ffn, cfg->d_model, w->lin1_b, cap);
-    if (!rc) rc = make_op(&p->lin2, ws.h, cfg->ad_ffn, w->lin2_w, cfg->ad_dim, cfg->ad_ffn, w->lin2_b, cap);
-    p->ad_layers.resize(cfg->ad_layers);
-    for (int i = 0; i < cfg->ad_layers && rc == 0; ++i) {
-      AdaptorLayerPlan& L = p->ad_layers[i];
-      if (!w->ad_layers) { set_error("plan_create: NULL adaptor layers"); rc = 2; break; }
-      L.w = w->ad_layers[i];
-      rc = make_op(&L.qkv, ws.axn, cfg->ad_dim, L.w.qkv_w, 3 * cfg->ad_dim, cfg->ad_dim, L.w.qkv_b, cap);
-      if (!rc) rc = make_op(&L.out, ws.actx, cfg->ad_dim, L.w.out_w, cfg->ad_dim, cfg->ad_dim, L.w.out_b, cap);
-      if (!rc) rc = make_op(&L.ffn1, ws.axn, cfg->ad_dim, L.w.ffn1_w, cfg->ad_ff, cfg->ad_dim, L.w.ffn1_b, cap);
-      if (!rc) rc = make_op(&L.ffn2, ws.ah, cfg->ad_ff, L.w.ffn2_w, cfg->ad_dim, cfg->ad_ff, L.w.ffn2_b, cap);
-    }
-  }
-  if (rc) {
+  if (int rc = build_programs(p)) {
     delete p;
     return rc;
   }
@@ -307,66 +389,16 @@ extern "C" int fa_encoder_forward(fa_plan* p, const float* feats, int32_t feats_
   FA_REQUIRE(p->cfg.n_blocks > 0, "plan was created without encoder weights");
   if (int r = check_tmax(feats_tmax, max_len, "feats")) return r;
   if (int r = check_tmax(enc_out_tmax, max_len, "enc_out")) return r;
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const RunArgs a{M, n_utts, max_len, cu, static_cast<cudaStream_t>(stream)};
   const fa_model_cfg& c = p->cfg;
-  Workspace& ws = p->ws;
-  const int d = c.d_model;
-  const int nl = c.n_blocks + c.n_tp_blocks;
-  float* x = ws.x;    // current residual stream
-  float* xo = ws.x2;  // next
-  int rc = 0;
-
   // input stage: xs*sqrt(d) + PE, then norm1 of encoders0 (VM:388-390, :121)
-  rc = launch_embed_layernorm(feats, feats_tmax, p->w.pe_inv_timescales, cu, n_utts, sqrtf(static_cast<float>(d)), p->layers[0].w.ln1_g,
-                              p->layers[0].w.ln1_b, ws.xn0, M, c.d_in, s);
-  if (rc) return rc;
-  for (int i = 0; i < nl; ++i) {
-    SanmLayerPlan& L = p->layers[i];
-    GemmEpilogue e;
-    // q|k|v = LN1(x) W^T + b                                              VM:206
-    if ((rc = run_gemm(L.qkv, M, e, ws.qkv, 3 * d, s))) return rc;
-    // FSMN memory on v                                                     VM:249,181-201
-    if ((rc = launch_fsmn(ws.qkv, 3 * d, 2 * d, L.w.fsmn_w, cu, n_utts, ws.mem, M, d, c.fsmn_kernel, p->fsmn_left, s))) return rc;
-    // masked MHA                                                           VM:250-252,222-236
-    if ((rc = launch_attention(ws.qkv, 3 * d, cu, n_utts, max_len, c.n_heads, ws.ctx, d, s))) return rc;
-    // x' = [x +] ctx Wo^T + b + mem    (no residual when in_size != size)   VM:238,253,123-136
-    e = GemmEpilogue();
-    e.out_f32 = 1;
-    e.res1 = ws.mem;
-    e.res2 = (i == 0) ? nullptr : x;
-    if ((rc = run_gemm(L.out, M, e, xo, d, s))) return rc;
-    // LN2, FFN                                                              VM:138-140,412-431
-    if ((rc = launch_layernorm(xo, L.w.ln2_g, L.w.ln2_b, nullptr, nullptr, ws.xn, nullptr, M, d, s))) return rc;
-    e = GemmEpilogue();
-    e.relu = 1;
-    if ((rc = run_gemm(L.ffn1, M, e, ws.h, c.d_ff, s))) return rc;
-    e = GemmEpilogue();
-    e.out_f32 = 1;
-    e.res1 = xo;
-    if ((rc = run_gemm(L.ffn2, M, e, x, d, s))) return rc;  // residual stream back in x
-    // next layer's norm1, with after_norm / tp_norm folded in                VM:400,408
-    const bool last_main = (i == c.n_blocks - 1);
-    const bool last = (i == nl - 1);
-    if (last) {
-      if (c.n_tp_blocks == 0) {
-        // after_norm then tp_norm back to back (VM:400,408 with an empty tp_encoders list)
-        if ((rc = launch_layernorm(x, p->w.after_norm_g, p->w.after_norm_b, nullptr, nullptr, nullptr, xo, M, d, s))) return rc;
-        if ((rc = launch_layernorm(xo, p->w.tp_norm_g, p->w.tp_norm_b, nullptr, nullptr, ws.enc_bf, ws.enc_f32, M, d, s))) return rc;
-      } else {
-        if ((rc = launch_layernorm(x, p->w.tp_norm_g, p->w.tp_norm_b, nullptr, nullptr, ws.enc_bf, ws.enc_f32, M, d, s))) return rc;
-      }
-    } else if (last_main) {
-      // x <- after_norm(x) becomes the residual stream of the tp blocks; xn <- norm1_next(x)
-      const SanmLayerPlan& Ln = p->layers[i + 1];
-      if ((rc = launch_layernorm(x, p->w.after_norm_g, p->w.after_norm_b, Ln.w.ln1_g, Ln.w.ln1_b, ws.xn, xo, M, d, s))) return rc;
-      float* t = x; x = xo; xo = t;
-    } else {
-      const SanmLayerPlan& Ln = p->layers[i + 1];
-      if ((rc = launch_layernorm(x, Ln.w.ln1_g, Ln.w.ln1_b, nullptr, nullptr, ws.xn, nullptr, M, d, s))) return rc;
-    }
-  }
-  if (enc_out) rc = launch_repack_rows(ws.enc_f32, 0, enc_out, enc_out_tmax, 0, cu, n_utts, M, d, s);
-  return rc;
+  if (int rc = launch_embed_layernorm(feats, feats_tmax, p->w.pe_inv_timescales, cu, n_utts, sqrtf(static_cast<float>(c.d_model)),
+                                      p->w.layers[0].ln1_g, p->w.layers[0].ln1_b, p->ws.xn0, M, c.d_in, a.s))
+    return rc;
+  for (const Step& st : p->enc_prog)
+    if (int rc = st(a)) return rc;
+  if (enc_out) return launch_repack_rows(p->ws.enc_f32, 0, enc_out, enc_out_tmax, 0, cu, n_utts, M, c.d_model, a.s);
+  return 0;
 }
 
 extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, int32_t enc_tmax, const int32_t* cu, int32_t n_utts,
@@ -377,44 +409,13 @@ extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, int32_t enc_tmax
   if (int r = check_tmax(out_tmax, max_len, "out")) return r;
   FA_REQUIRE(out != nullptr, "NULL out");
   FA_REQUIRE(p->w.lin1_w != nullptr, "plan was created without adaptor weights");
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const RunArgs a{M, n_utts, max_len, cu, static_cast<cudaStream_t>(stream)};
   const fa_model_cfg& c = p->cfg;
-  Workspace& ws = p->ws;
-  const int D = c.ad_dim;
-  int rc = 0;
-  if (enc) {
-    if ((rc = launch_repack_rows(enc, enc_tmax, ws.enc_bf, 0, 1, cu, n_utts, M, c.d_model, s))) return rc;
-  }
-  // linear1 + ReLU, linear2                                                 VM:585-587
-  GemmEpilogue e;
-  e.relu = 1;
-  if ((rc = run_gemm(p->lin1, M, e, ws.h, c.ad_ffn, s))) return rc;
-  e = GemmEpilogue();
-  e.out_f32 = 1;
-  float* x = ws.ax;
-  float* xo = ws.ax2;
-  if ((rc = run_gemm(p->lin2, M, e, x, D, s))) return rc;
-  for (int i = 0; i < c.ad_layers; ++i) {
-    AdaptorLayerPlan& L = p->ad_layers[i];
-    // pre-LN MHA block                                                       VM:434-455
-    if ((rc = launch_layernorm(x, L.w.ln1_g, L.w.ln1_b, nullptr, nullptr, ws.axn, nullptr, M, D, s))) return rc;
-    e = GemmEpilogue();
-    if ((rc = run_gemm(L.qkv, M, e, ws.aqkv, 3 * D, s))) return rc;
-    if ((rc = launch_attention(ws.aqkv, 3 * D, cu, n_utts, max_len, c.ad_heads, ws.actx, D, s))) return rc;
-    e = GemmEpilogue();
-    e.out_f32 = 1;
-    e.res1 = x;
-    if ((rc = run_gemm(L.out, M, e, xo, D, s))) return rc;
-    if ((rc = launch_layernorm(xo, L.w.ln2_g, L.w.ln2_b, nullptr, nullptr, ws.axn, nullptr, M, D, s))) return rc;
-    e = GemmEpilogue();
-    e.relu = 1;
-    if ((rc = run_gemm(L.ffn1, M, e, ws.ah, c.ad_ff, s))) return rc;
-    e = GemmEpilogue();
-    e.out_f32 = 1;
-    e.res1 = xo;
-    if ((rc = run_gemm(L.ffn2, M, e, x, D, s))) return rc;
-  }
-  return launch_repack_rows(x, 0, out, out_tmax, out_bf16, cu, n_utts, M, D, s);
+  if (enc)
+    if (int rc = launch_repack_rows(enc, enc_tmax, p->ws.enc_bf, 0, 1, cu, n_utts, M, c.d_model, a.s)) return rc;
+  for (const Step& st : p->ad_prog)
+    if (int rc = st(a)) return rc;
+  return launch_repack_rows(p->ws.ax, 0, out, out_tmax, out_bf16, cu, n_utts, M, c.ad_dim, a.s);
 }
 
 extern "C" int fa_encode_adapt(fa_plan* p, const float* feats, int32_t feats_tmax, const int32_t* cu, int32_t n_utts,

@@ -63,9 +63,12 @@ struct TensorMap2D {  // opaque 128-byte CUtensorMap
 // rows x cols bf16 matrix, row stride ld (elements); box = box_rows x 64 cols, 128B swizzle.
 int make_tensor_map_bf16(TensorMap2D* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
                          uint32_t box_rows);
+// elem_bytes 2 (bf16) or 4 (f32); box = box_rows x (128 / elem_bytes) columns, 128B swizzle.
+int make_tensor_map(TensorMap2D* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld,
+                    uint32_t box_rows);
 
 int gemm_block_n(int M, int N);  // tile-N heuristic (64 / 128 / 256)
-int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, int block_n, int M, int N, int K,
+int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int block_n, int M, int N, int K,
                 const GemmEpilogue& epi, void* c, int64_t ldc, cudaStream_t stream);
 
 int launch_layernorm(const float* x, const float* g, const float* b, const float* g2, const float* b2,

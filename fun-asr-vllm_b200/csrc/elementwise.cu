@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
 }
 
 // ---------------------------------------------------------------- FSMN memory block
-// mem[t, c] = v[t, c] + sum_k w[c, k] * v[t + k - left, c]   (zero outside the utterance)
+// mem[t, c] = v[t, c] + sum_k w[k, c] * v[t + k - left, c]   (zero outside the utterance; w is TAP-MAJOR [K, D])
 // (VLLM/model_executor/models/funasr.py:181-201: mask, ConstantPad1d, depthwise Conv1d, +inputs, mask).
 // One thread owns 4 adjacent channels (one 8-byte bf16x4 load per row) and FSMN_ROWS consecutive
 // rows: the FSMN_ROWS + K - 1 input rows are loaded up front (independent loads, deep MLP), the tap
@@ -178,12 +178,14 @@ fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const 
     raw[i] = make_uint2(0u, 0u);
     if (ch_ok && rr >= 0 && rr < M) raw[i] = __ldg(reinterpret_cast<const uint2*>(vbase + static_cast<int64_t>(rr) * ld));
   }
-  float wt[4][K];
+  // tap-major weights [K, D]: one coalesced float4 per tap.  The "+ inputs" term (VLLM/...:199) is tap `left` with
+  // weight + 1: row r is always inside its own utterance.
+  float4 wt[K];
 #pragma unroll
-  for (int c = 0; c < 4; ++c)
-#pragma unroll
-    for (int k = 0; k < K; ++k)  // the "+ inputs" term (VLLM/...:199) is tap `left` with weight + 1: row r is always inside its own utterance
-      wt[c][k] = (ch_ok ? __ldg(w + static_cast<int64_t>(4 * c4 + c) * K + k) : 0.f) + (k == left ? 1.f : 0.f);
+  for (int k = 0; k < K; ++k) {
+    wt[k] = ch_ok ? __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(k) * D) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k == left) { wt[k].x += 1.f; wt[k].y += 1.f; wt[k].z += 1.f; wt[k].w += 1.f; }
+  }
   __syncthreads();
   if (!ch_ok) return;
 #pragma unroll
@@ -198,10 +200,10 @@ fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const 
       if (rr >= lo && rr < hi) {  // warp-uniform: the whole CTA shares r
         const float2 f01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[j + k].x));
         const float2 f23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[j + k].y));
-        a0 = fmaf(wt[0][k], f01.x, a0);
-        a1 = fmaf(wt[1][k], f01.y, a1);
-        a2 = fmaf(wt[2][k], f23.x, a2);
-        a3 = fmaf(wt[3][k], f23.y, a3);
+        a0 = fmaf(wt[k].x, f01.x, a0);
+        a1 = fmaf(wt[k].y, f01.y, a1);
+        a2 = fmaf(wt[k].z, f23.x, a2);
+        a3 = fmaf(wt[k].w, f23.y, a3);
       }
     }
     *reinterpret_cast<float4*>(mem + static_cast<int64_t>(r) * D + 4 * c4) = make_float4(a0, a1, a2, a3);
@@ -320,8 +322,9 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
   FA_REQUIRE(kernel >= 1 && kernel <= ew::FSMN_MAXK, "fsmn: kernel size %d not in [1,%d]", kernel, ew::FSMN_MAXK);
   FA_REQUIRE(left_pad >= 0 && left_pad < kernel, "fsmn: left pad %d outside the %d-tap window", left_pad, kernel);
   FA_REQUIRE(D % 4 == 0 && v_col % 4 == 0 && ld % 4 == 0, "fsmn: D, v_col and ld must be multiples of 4");
-  FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 7) == 0 && (reinterpret_cast<uintptr_t>(mem) & 15) == 0,
-             "fsmn: qkv must be 8-byte and mem 16-byte aligned");
+  FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 7) == 0 && (reinterpret_cast<uintptr_t>(mem) & 15) == 0 &&
+                 (reinterpret_cast<uintptr_t>(w) & 15) == 0,
+             "fsmn: qkv must be 8-byte, mem and w 16-byte aligned");
   const int threads = 128;
   dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 4, threads));
   ProfScope _ps(K_FSMN, stream);

@@ -4,7 +4,8 @@
 //   warp 0      TMA producer   (cp.async.bulk.tensor 2D, 128B swizzle, mbarrier complete_tx)
 //   warp 1      MMA issuer     (tcgen05.mma cta_group::1 kind::f16, M=128, N=BN, K=16 per instruction,
 //                               fp32 accumulators in TMEM, double buffered: 2 x BN columns)
-//   warps 2..5  epilogue       (tcgen05.ld 32x32b -> registers -> bias/ReLU/residual -> global)
+//   warps 2..   epilogue       (tcgen05.ld 32x32b -> registers -> bias/ReLU -> 128B-swizzled smem slab
+//                               -> [+ f32 residuals, read row-wise and coalesced] -> TMA store)
 // Three pipelines: smem full/empty (TMA<->MMA), TMEM full/empty (MMA<->epilogue), static tile
 // scheduler (tile = blockIdx.x + i * gridDim.x).  Both operands are K-major (nn.Linear layout),
 // so no transposes are ever materialised.
@@ -21,17 +22,21 @@ namespace gemm {
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle span
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 192;
-constexpr int EPI_WARP0 = 2;
+constexpr int EPI_WARPS = 4;                    // one per TMEM lane quarter
+constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;
+constexpr int SLAB_BYTES = 32 * 128;            // 32 rows x 128 B, SWIZZLE_128B (64 bf16 or 32 f32 columns)
+constexpr int SMEM_LIMIT = 227 * 1024;
 
 template <int BN>
 struct Cfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int SLABS_BYTES = EPI_WARPS * 2 * SLAB_BYTES;  // double-buffered staging slab per epilogue warp
+  static constexpr int MAX_STAGES = (SMEM_LIMIT - 1024 - 256 - SLABS_BYTES) / STAGE_BYTES;
+  static constexpr int STAGES = MAX_STAGES > 8 ? 8 : MAX_STAGES;
   static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (power of two >= 32)
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SLABS_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 struct Params {
@@ -78,6 +83,25 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
       "l"(tmap), "r"(bar), "r"(x), "r"(y)
       : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int x, int y) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap), "r"(src), "r"(x),
+               "r"(y)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
 }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -136,11 +160,13 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 // ---------------------------------------------------------------- kernel
 template <int BN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const Params p) {
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ CUtensorMap tmap_c, const Params p) {
   using C = Cfg<BN>;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024B alignment
-  const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES;
+  const uint32_t slab_base = smem_base + C::STAGES * C::STAGE_BYTES;  // 1024-aligned: STAGE_BYTES is a multiple of 1024
+  const uint32_t bar_base = slab_base + C::SLABS_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::STAGES + a); };
@@ -156,13 +182,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_c) : "memory");
     for (int s = 0; s < C::STAGES; ++s) {
       mbar_init(full_bar(s), 1);
       mbar_init(empty_bar(s), 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 4);  // one arrive per epilogue warp
+      mbar_init(tempty_bar(a), EPI_WARPS);  // one arrive per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -227,7 +254,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   } else {
     // ===================== epilogue warps =====================
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    // Each warp owns TMEM lanes [32q, 32q+32) = 32 rows of the tile.  Per "unit" (64 bf16 or 32 f32 output
+    // columns = one 128-byte row segment) it fills a 32x128B slab in the SWIZZLE_128B layout and hands it to TMA,
+    // so every global access of the epilogue is a full-line bulk or row-contiguous access.
+    const int q = warp & 3;
+    const int ew = warp - 2;
+    const uint32_t my_slabs = slab_base + ew * 2 * SLAB_BYTES;
+    const int cols_per_unit = p.out_f32 ? 32 : 64;
+    const int units = BN / cols_per_unit;
+    const uint32_t rsw = static_cast<uint32_t>(lane & 7);  // swizzle phase of this lane's row
+    const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
+    uint32_t fills = 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
@@ -235,66 +272,86 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(tfull_bar(acc), acc_phase);
       tcgen05_fence_after();
-      const int row = tm * BM + q * 32 + lane;
-      const bool row_ok = row < p.M;
+      const int row0 = tm * BM + q * 32;
+      const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + c0, r);
-        const int col = tn * BN + c0;
-        if (row_ok) {
-          float v[32];
+      for (int u = 0; u < units; ++u, ++fills) {
+        const uint32_t slab = my_slabs + (fills & 1) * SLAB_BYTES;
+        const int col0 = tn * BN + u * cols_per_unit;
+        // residual rows for this unit, fetched row-wise (4 rows x 128 B per warp instruction) before the TMEM load
+        float4 rv1[8], rv2[8];
+        if (p.out_f32 && p.res1) {
 #pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            const float4 bv = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col + i)) : make_float4(0, 0, 0, 0);
-            v[i] = __uint_as_float(r[i]) + bv.x;
-            v[i + 1] = __uint_as_float(r[i + 1]) + bv.y;
-            v[i + 2] = __uint_as_float(r[i + 2]) + bv.z;
-            v[i + 3] = __uint_as_float(r[i + 3]) + bv.w;
+          for (int i = 0; i < 8; ++i) {
+            const int grow = row0 + 4 * i + (lane >> 3);
+            const long long off = static_cast<long long>(grow) * p.ldc + col0 + 4 * (lane & 7);
+            rv1[i] = grow < p.M ? *reinterpret_cast<const float4*>(p.res1 + off) : make_float4(0, 0, 0, 0);
+            if (p.res2) rv2[i] = grow < p.M ? *reinterpret_cast<const float4*>(p.res2 + off) : make_float4(0, 0, 0, 0);
           }
-          if (p.relu) {
+        }
+        if (fills >= 2) {  // the TMA store that last read this slab must have drained it
+          if (lane == 0) bulk_wait_read<1>();
+          __syncwarp();
+        }
+        if (p.out_f32) {
+          uint32_t r[32];
+          tmem_ld32(tmem_row + u * 32, r);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+          for (int j = 0; j < 8; ++j) {
+            const float4 bv = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col0) + j) : make_float4(0, 0, 0, 0);
+            float v0 = __uint_as_float(r[4 * j]) + bv.x, v1 = __uint_as_float(r[4 * j + 1]) + bv.y;
+            float v2 = __uint_as_float(r[4 * j + 2]) + bv.z, v3 = __uint_as_float(r[4 * j + 3]) + bv.w;
+            if (p.relu) { v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); v2 = fmaxf(v2, 0.f); v3 = fmaxf(v3, 0.f); }
+            sts128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4), __float_as_uint(v0), __float_as_uint(v1),
+                   __float_as_uint(v2), __float_as_uint(v3));
           }
-          if (p.out_f32) {
-            float* crow = static_cast<float*>(p.c) + static_cast<long long>(row) * p.ldc + col;
-            if (p.res1) {
-              const float* rr = p.res1 + static_cast<long long>(row) * p.ldc + col;
+          if (p.res1) {
+            __syncwarp();
 #pragma unroll
-              for (int i = 0; i < 32; i += 4) {
-                const float4 t = *reinterpret_cast<const float4*>(rr + i);
-                v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t rr = 4 * i + (lane >> 3);
+              const uint32_t addr = slab + rr * 128u + ((static_cast<uint32_t>(lane & 7) ^ (rr & 7)) << 4);
+              float4 v = lds128(addr);
+              v.x += rv1[i].x; v.y += rv1[i].y; v.z += rv1[i].z; v.w += rv1[i].w;
+              if (p.res2) { v.x += rv2[i].x; v.y += rv2[i].y; v.z += rv2[i].z; v.w += rv2[i].w; }
+              sts128(addr, __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w));
+            }
+          }
+        } else {
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t r[32];
+            tmem_ld32(tmem_row + u * 64 + half * 32, r);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float4 b0 = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col0 + half * 32) + 2 * j) : make_float4(0, 0, 0, 0);
+              const float4 b1 = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col0 + half * 32) + 2 * j + 1) : make_float4(0, 0, 0, 0);
+              float v[8] = {__uint_as_float(r[8 * j]) + b0.x,     __uint_as_float(r[8 * j + 1]) + b0.y,
+                            __uint_as_float(r[8 * j + 2]) + b0.z, __uint_as_float(r[8 * j + 3]) + b0.w,
+                            __uint_as_float(r[8 * j + 4]) + b1.x, __uint_as_float(r[8 * j + 5]) + b1.y,
+                            __uint_as_float(r[8 * j + 6]) + b1.z, __uint_as_float(r[8 * j + 7]) + b1.w};
+              if (p.relu) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
               }
-            }
-            if (p.res2) {
-              const float* rr = p.res2 + static_cast<long long>(row) * p.ldc + col;
-#pragma unroll
-              for (int i = 0; i < 32; i += 4) {
-                const float4 t = *reinterpret_cast<const float4*>(rr + i);
-                v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
-              }
-            }
-#pragma unroll
-            for (int i = 0; i < 32; i += 4)
-              *reinterpret_cast<float4*>(crow + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-          } else {
-            __nv_bfloat16* crow = static_cast<__nv_bfloat16*>(p.c) + static_cast<long long>(row) * p.ldc + col;
-#pragma unroll
-            for (int i = 0; i < 32; i += 8) {
-              uint4 o;
-              o.x = pack_bf16x2(v[i], v[i + 1]);
-              o.y = pack_bf16x2(v[i + 2], v[i + 3]);
-              o.z = pack_bf16x2(v[i + 4], v[i + 5]);
-              o.w = pack_bf16x2(v[i + 6], v[i + 7]);
-              *reinterpret_cast<uint4*>(crow + i) = o;
+              sts128(slab + row_off + ((static_cast<uint32_t>(half * 4 + j) ^ rsw) << 4), pack_bf16x2(v[0], v[1]),
+                     pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
             }
           }
+        }
+        fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmap_c, slab, col0, row0);
+          bulk_commit();
         }
       }
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(acc));
     }
+    if (lane == 0) bulk_wait<0>();
+    __syncwarp();
   }
 
   tcgen05_fence_before();
@@ -323,8 +380,8 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 template <int BN>
-static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, int M, int N, int K, const GemmEpilogue& epi, void* c,
-                    int64_t ldc, cudaStream_t stream) {
+static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int M, int N, int K,
+                    const GemmEpilogue& epi, void* c, int64_t ldc, cudaStream_t stream) {
   using C = Cfg<BN>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -339,37 +396,44 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, int M, int N, 
   p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32;
   const int tiles = p.tiles_m * p.tiles_n;
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  CUtensorMap ma, mb;
+  CUtensorMap ma, mb, mc;
   static_assert(sizeof(CUtensorMap) == sizeof(TensorMap2D::bytes), "CUtensorMap size");
   memcpy(&ma, ta.bytes, sizeof(ma));
   memcpy(&mb, tb.bytes, sizeof(mb));
+  memcpy(&mc, tc.bytes, sizeof(mc));
   ProfScope _ps(K_GEMM, stream);
-  gemm_bf16_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, p);
+  gemm_bf16_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, mc, p);
   FA_CHECK_LAUNCH();
   return 0;
 }
 
 }  // namespace gemm
 
-int make_tensor_map_bf16(TensorMap2D* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
-                         uint32_t box_rows) {
+// rows x cols matrix of bf16 (elem_bytes 2) or f32 (4), row stride ld elements; box = box_rows x box_cols with
+// box_cols * elem_bytes == 128 (one SWIZZLE_128B span).
+int make_tensor_map(TensorMap2D* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld,
+                    uint32_t box_rows) {
   gemm::EncodeTiledFn fn = gemm::get_encode_fn();
   FA_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  FA_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "TMA element size must be 2 or 4");
   FA_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
-  FA_REQUIRE((ld * 2) % 16 == 0, "TMA row pitch (%llu bytes) must be a multiple of 16", (unsigned long long)(ld * 2));
+  FA_REQUIRE((ld * elem_bytes) % 16 == 0, "TMA row pitch (%llu bytes) must be a multiple of 16", (unsigned long long)(ld * elem_bytes));
   FA_REQUIRE(box_rows >= 1 && box_rows <= 256, "TMA box rows out of range");
   CUtensorMap m;
   cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstride[1] = {ld * 2};
-  cuuint32_t box[2] = {static_cast<cuuint32_t>(gemm::BK), box_rows};
+  cuuint64_t gstride[1] = {ld * elem_bytes};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / elem_bytes), box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(&m, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                  const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   FA_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows %llu cols %llu ld %llu)", (int)r,
              (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld);
   memcpy(out->bytes, &m, sizeof(m));
   return 0;
+}
+int make_tensor_map_bf16(TensorMap2D* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  return make_tensor_map(out, base, 2, rows, cols, ld, box_rows);
 }
 
 int gemm_block_n(int M, int N) {
@@ -383,17 +447,17 @@ int gemm_block_n(int M, int N) {
   return 0;
 }
 
-int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, int block_n, int M, int N, int K, const GemmEpilogue& epi,
-                void* c, int64_t ldc, cudaStream_t stream) {
+int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int block_n, int M, int N, int K,
+                const GemmEpilogue& epi, void* c, int64_t ldc, cudaStream_t stream) {
   FA_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
   FA_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "gemm: unsupported tile N %d", block_n);
   FA_REQUIRE(N % block_n == 0, "gemm: N=%d is not a multiple of the tile %d", N, block_n);
   FA_REQUIRE(K % 8 == 0, "gemm: K=%d must be a multiple of 8", K);
   FA_REQUIRE(ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(c) & 15) == 0, "gemm: C must be 16-byte aligned, ldc %% 8 == 0");
   switch (block_n) {
-    case 64: return gemm::launch_t<64>(ta, tb, M, N, K, epi, c, ldc, stream);
-    case 128: return gemm::launch_t<128>(ta, tb, M, N, K, epi, c, ldc, stream);
-    default: return gemm::launch_t<256>(ta, tb, M, N, K, epi, c, ldc, stream);
+    case 64: return gemm::launch_t<64>(ta, tb, tc, M, N, K, epi, c, ldc, stream);
+    case 128: return gemm::launch_t<128>(ta, tb, tc, M, N, K, epi, c, ldc, stream);
+    default: return gemm::launch_t<256>(ta, tb, tc, M, N, K, epi, c, ldc, stream);
   }
 }
 
@@ -406,10 +470,11 @@ extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int
   FA_REQUIRE(a_dev && w_dev && c_dev, "gemm: NULL pointer");
   const int bn = gemm_block_n(M, N);
   FA_REQUIRE(bn != 0, "gemm: N=%d must be a multiple of 64", N);
-  TensorMap2D ta, tb;
+  TensorMap2D ta, tb, tc;
   if (int r = make_tensor_map_bf16(&ta, a_dev, M, K, lda, gemm::BM)) return r;
   if (int r = make_tensor_map_bf16(&tb, w_dev, N, K, ldw, bn)) return r;
+  if (int r = make_tensor_map(&tc, c_dev, out_f32 ? 4 : 2, M, N, ldc, 32)) return r;
   GemmEpilogue e;
   e.bias = bias_dev; e.res1 = res1_dev; e.res2 = res2_dev; e.relu = relu; e.out_f32 = out_f32;
-  return launch_gemm(ta, tb, bn, M, N, K, e, c_dev, ldc, static_cast<cudaStream_t>(stream));
+  return launch_gemm(ta, tb, tc, bn, M, N, K, e, c_dev, ldc, static_cast<cudaStream_t>(stream));
 }

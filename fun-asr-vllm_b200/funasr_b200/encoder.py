@@ -134,7 +134,7 @@ class Plan:
                 h["layers"].append(dict(
                     ln1_g=ar.vec(L.norm1.weight), ln1_b=ar.vec(L.norm1.bias),
                     qkv_w=ar.mat(a.linear_q_k_v.weight), qkv_b=ar.vec(a.linear_q_k_v.bias),
-                    fsmn_w=ar.vec(a.fsmn_block.weight),  # [D,1,K] -> [D,K] f32
+                    fsmn_w=ar.vec(a.fsmn_block.weight.squeeze(1).t().contiguous()),  # [D,1,K] -> tap-major [K,D] f32
                     out_w=ar.mat(a.linear_out.weight), out_b=ar.vec(a.linear_out.bias),
                     ln2_g=ar.vec(L.norm2.weight), ln2_b=ar.vec(L.norm2.bias),
                     ffn1_w=ar.mat(f.w_1.weight), ffn1_b=ar.vec(f.w_1.bias),

@@ -123,7 +123,7 @@ typedef struct {
   const float* ln1_b;
   const void* qkv_w;    /* bf16 [3*d_model, d_in|d_model]   self_attn.linear_q_k_v.weight */
   const float* qkv_b;   /* [3*d_model] */
-  const float* fsmn_w;  /* f32 [d_model, fsmn_kernel]        self_attn.fsmn_block.weight */
+  const float* fsmn_w;  /* f32 [fsmn_kernel, d_model] TAP-MAJOR = self_attn.fsmn_block.weight[d_model,1,K] transposed */
   const void* out_w;    /* bf16 [d_model, d_model]           self_attn.linear_out.weight */
   const float* out_b;
   const float* ln2_g;
@@ -223,7 +223,8 @@ int fa_op_layernorm(const float* x_dev, const float* g_dev, const float* b_dev, 
 int fa_op_embed_layernorm(const float* x_dev, const float* inv_ts_dev, const int32_t* cu_seqlens_dev, int32_t n_utts,
                           float scale, const float* g_dev, const float* b_dev, void* y_bf16_dev, int32_t M, int32_t D,
                           fa_stream_t stream);
-/* mem[M,D] f32 = v + depthwise_conv_time(v)   v = qkv[:, v_col : v_col+D] bf16    VLLM/...:181-201 */
+/* mem[M,D] f32 = v + depthwise_conv_time(v)   v = qkv[:, v_col : v_col+D] bf16; w_dev f32 [kernel, D] tap-major
+ * VLLM/...:181-201 */
 int fa_op_fsmn(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, const float* w_dev, const int32_t* cu_seqlens_dev,
                int32_t n_utts, float* mem_dev, int32_t M, int32_t D, int32_t kernel, int32_t left_pad,
                fa_stream_t stream);

@@ -63,7 +63,7 @@ if which in ("attn", "all"):
 if which in ("fsmn", "all"):
     cu = U.cu_of([167] * 360)
     qkv = torch.randn(M, 1536, device="cuda").to(torch.bfloat16)
-    w = torch.randn(512, 11, device="cuda")
+    w = torch.randn(11, 512, device="cuda")
     best, avg = timeit(lambda: U.op_fsmn(qkv, 1024, w, cu, 512, 11, 5))
     print(f"fsmn: best {best*1e3:.1f} us -> {(M*512*6)/best/1e6:.0f} GB/s algorithmic (bf16 in, f32 out)")
 

@@ -94,7 +94,7 @@ def test_fsmn_respects_utterance_boundaries(U, K, left):
         y = torch.nn.functional.conv1d(torch.nn.functional.pad(vb, (left, K - 1 - left)), w[:, None, :], groups=D)
         rows.append((y + vb)[0].t())
     want = torch.cat(rows)
-    got = U.op_fsmn(qkv.cuda(), 2 * D, w.cuda(), cu, D, K, left)
+    got = U.op_fsmn(qkv.cuda(), 2 * D, w.t().contiguous().cuda(), cu, D, K, left)  # tap-major [K, D]
     assert (got.cpu() - want).abs().max().item() < 1e-4
 
 
