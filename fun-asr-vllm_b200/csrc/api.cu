@@ -277,7 +277,7 @@ int build_programs(fa_plan* p) {
       const __nv_bfloat16* qkv = ws.qkv;
       __nv_bfloat16* ctx = ws.ctx;
       const int H = c.n_heads;
-      E.push_back([=](const RunArgs& r) { return launch_attention(qkv, 3 * d, r.cu, r.n_utts, r.max_len, H, ctx, d, r.s); });
+      E.push_back([=](const RunArgs& r) { return launch_attention(qkv, 3 * d, r.cu, r.n_utts, r.max_len, H, ctx, d, r.M, r.s); });
     }
     // x' = [x +] ctx Wo^T + b + mem    (no residual when in_size != size)   VM:238,253,123-136
     B.gemm(E, ws.ctx, d, L.out_w, d, d, L.out_b, xo, true, false, ws.mem, (i == 0) ? nullptr : x);
@@ -322,7 +322,7 @@ int build_programs(fa_plan* p) {
         const __nv_bfloat16* qkv = ws.aqkv;
         __nv_bfloat16* ctx = ws.actx;
         const int H = c.ad_heads;
-        A.push_back([=](const RunArgs& r) { return launch_attention(qkv, 3 * D, r.cu, r.n_utts, r.max_len, H, ctx, D, r.s); });
+        A.push_back([=](const RunArgs& r) { return launch_attention(qkv, 3 * D, r.cu, r.n_utts, r.max_len, H, ctx, D, r.M, r.s); });
       }
       B.gemm(A, ws.actx, D, L.out_w, D, D, L.out_b, axo, true, false, ax);
       B.ln(A, axo, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.axn, nullptr, D);

@@ -1,216 +1,357 @@
-// Variable-length multi-head self-attention over packed utterances, head dim 128.
-//   ctx = softmax(q k^T / sqrt(128)) v   per (utterance, head); keys never cross utterances, which is
-//   exactly the reference's key-masked padded attention on valid rows
+// Variable-length multi-head self-attention over packed utterances, head dim 128, on tcgen05 / TMEM.
+//   ctx = softmax(q k^T / sqrt(128)) v   per (utterance, head); keys never cross utterances, which is exactly the
+//   reference's key-masked padded attention on valid rows
 //   (VLLM/model_executor/models/funasr.py:222-235,250-252; adaptor :506-512).
 //
-// Round-1 kernel: flash-style online softmax, 64 queries per CTA (4 warps x 16 rows), 64-key tiles
-// double-buffered with cp.async, bf16 mma.sync.m16n8k16 with fp32 accumulation, XOR-swizzled smem
-// read by ldmatrix.  (The tcgen05/TMEM version is the next step)
+// One CTA = (utterance b, head h, 128 query rows).  Keys/values stream through shared memory in blocks of 128
+// (TMA, 128B swizzle, two stages); per block
+//     S  = Q K_j^T          tcgen05.mma, A = Q (smem, K-major), B = K_j (smem, K-major), D in TMEM (double buffered)
+//     P  = exp2(S c - m)    softmax warps: thread = row, TMEM -> registers -> bf16 -> swizzled smem (A operand layout)
+//     O += P V_j            tcgen05.mma, A = P (smem, K-major), B = V_j (smem, MN-major: V rows are keys), D in TMEM
+// with an online softmax whose running maximum is only raised when it grows by more than 2^8 (the O accumulator in
+// TMEM is then rescaled once), so most blocks never touch O.  Warp roles: 0 TMA producer, 1 MMA issuer (+ TMEM
+// alloc), 2..5 softmax / epilogue (one TMEM lane quarter each).
+#include <cuda.h>
+
+#include <cstring>
+
 #include "common.cuh"
 
 namespace fa {
 namespace attn {
 
-constexpr int HD = 128;  // head dim
-constexpr int BQ = 64;
-constexpr int BKV = 64;
-constexpr int THREADS = 128;
-constexpr int TILE_BYTES = BKV * HD * 2;  // 16 KB
-constexpr int SMEM_BYTES = BQ * HD * 2 + 4 * TILE_BYTES;
+constexpr int HD = 128;   // head dim
+constexpr int BQ = 128;   // query rows per CTA = UMMA M
+constexpr int BKV = 128;  // keys per block
+constexpr int THREADS = 192;
+constexpr int PANEL = BQ * 128;            // one [128 rows x 64 bf16] 128B-swizzled panel = 16 KB
+constexpr int Q_BYTES = 2 * PANEL;         // d = 128 -> two panels
+constexpr int KV_STAGE = 4 * PANEL;        // K block (2 panels) + V block (2 panels)
+constexpr int P_BYTES = 2 * PANEL;         // 128 keys -> two panels
+constexpr int SMEM_BYTES = Q_BYTES + 2 * KV_STAGE + P_BYTES + 1024 + 256;
+constexpr int TMEM_COLS = 512;             // S0 [0,128) S1 [128,256) O [256,384)
+constexpr float RESCALE_THRESHOLD = 8.f;   // log2 units
 
-__device__ __forceinline__ uint32_t swz(int row, int chunk) {  // byte offset of a 16B chunk
-  return static_cast<uint32_t>(row * (HD * 2) + ((chunk ^ (row & 7)) << 4));
+// ---------------------------------------------------------------- PTX wrappers (same conventions as gemm_tcgen05.cu)
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
-  const int bytes = valid ? 16 : 0;
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
-}
-__device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-
-// rows [row0, row0+64) of one operand (q, k or v slice of head h) -> swizzled smem tile; rows >= row_end zero-filled
-__device__ __forceinline__ void load_tile(uint32_t smem_tile, const __nv_bfloat16* __restrict__ base, int64_t ld,
-                                          int row0, int row_end, int tid) {
-#pragma unroll
-  for (int i = 0; i < (BKV * 16) / THREADS; ++i) {
-    const int idx = tid + i * THREADS;
-    const int r = idx >> 4, c = idx & 15;
-    const int gr = row0 + r;
-    const bool ok = gr < row_end;
-    const __nv_bfloat16* src = base + static_cast<int64_t>(ok ? gr : row0) * ld + c * 8;
-    cp_async16(smem_tile + swz(r, c), src, ok);
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0;
+  while (!ok) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
   }
 }
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint32_t bar, int x, int y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(tmap), "r"(bar), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// K-major operand, 128B swizzle: rows 128 B apart, 8-row groups 1024 B apart (SBO); LBO unused.
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t addr) {
+  return static_cast<uint64_t>((addr & 0x3FFFF) >> 4) | (1ull << 16) | (static_cast<uint64_t>(1024 >> 4) << 32) | (1ull << 46) |
+         (2ull << 61);
+}
+// MN-major operand, 128B swizzle (cute: Swizzle<3,4,3> o ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units): one K index
+// = one 128-byte row of 64 MN elements; 8-row K groups SBO apart; the next 64 MN elements LBO apart.
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return static_cast<uint64_t>((addr & 0x3FFFF) >> 4) | (static_cast<uint64_t>(lbo_bytes >> 4) << 16) |
+         (static_cast<uint64_t>(sbo_bytes >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::f16: D f32, A/B bf16; bit 15/16 = A/B major (0 K, 1 MN); N>>3 at [17,23); M>>4 at [24,29).
+__device__ __forceinline__ uint32_t make_idesc(int m, int n, int b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(b_mn_major) << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
+         (static_cast<uint32_t>(m >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
 
-__global__ void __launch_bounds__(THREADS)
-attention_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, const int32_t* __restrict__ cu, int n_heads,
+// ---------------------------------------------------------------- kernel
+__global__ void __launch_bounds__(THREADS, 1)
+attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __restrict__ cu, int n_heads,
                  __nv_bfloat16* __restrict__ ctx, int64_t ld_ctx, float scale_log2e) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  extern __shared__ unsigned char smem_raw[];
   const int b = blockIdx.z, h = blockIdx.y;
   const int start = cu[b], len = cu[b + 1] - start;
   const int q0 = blockIdx.x * BQ;
-  if (q0 >= len) return;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (q0 >= len) return;  // uniform per CTA, before any barrier / TMEM use
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int dm = n_heads * HD;
+  const int n_blk = (len + BKV - 1) / BKV;
 
-  const uint32_t sQ = smem_u32(smem_raw);
-  const uint32_t sK = sQ + BQ * HD * 2;
-  const uint32_t sV = sK + 2 * TILE_BYTES;
-  const __nv_bfloat16* qbase = qkv + static_cast<int64_t>(start) * ld + h * HD;
-  const __nv_bfloat16* kbase = qbase + dm;
-  const __nv_bfloat16* vbase = qbase + 2 * dm;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = base, sKV = sQ + Q_BYTES, sP = sKV + 2 * KV_STAGE, bars = sP + P_BYTES;
+  const uint32_t q_full = bars, kv_full = bars + 8, kv_empty = bars + 24, s_full = bars + 40, p_full = bars + 56,
+                 p_free = bars + 64, o_full = bars + 72, tmem_slot = bars + 80;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
-  const int n_tiles = (len + BKV - 1) / BKV;
-  load_tile(sQ, qbase, ld, q0, len, tid);
-  load_tile(sK, kbase, ld, 0, len, tid);
-  load_tile(sV, vbase, ld, 0, len, tid);
-  cp_async_commit();
-
-  uint32_t qf[8][4];
-  float o[16][4];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
-  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
-
-  for (int t = 0; t < n_tiles; ++t) {
-    const int buf = t & 1;
-    if (t + 1 < n_tiles) {
-      load_tile(sK + (buf ^ 1) * TILE_BYTES, kbase, ld, (t + 1) * BKV, len, tid);
-      load_tile(sV + (buf ^ 1) * TILE_BYTES, vbase, ld, (t + 1) * BKV, len, tid);
-      cp_async_commit();
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
-    __syncthreads();
-    if (t == 0) {
-#pragma unroll
-      for (int kk = 0; kk < 8; ++kk)
-        ldsm_x4(sQ + swz(warp * 16 + (lane & 15), 2 * kk + (lane >> 4)), qf[kk][0], qf[kk][1], qf[kk][2], qf[kk][3]);
-    }
-    const uint32_t sKt = sK + buf * TILE_BYTES, sVt = sV + buf * TILE_BYTES;
-
-    // ---- S = Q K^T  (16 x 64 per warp)
-    float s[8][4];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
-#pragma unroll
-    for (int kk = 0; kk < 8; ++kk) {
-#pragma unroll
-      for (int nb = 0; nb < 8; nb += 2) {
-        uint32_t b0, b1, b2, b3;
-        const int mi = lane >> 3, r = lane & 7;
-        ldsm_x4(sKt + swz((nb + (mi >> 1)) * 8 + r, 2 * kk + (mi & 1)), b0, b1, b2, b3);
-        mma_bf16(s[nb], qf[kk], b0, b1);
-        mma_bf16(s[nb + 1], qf[kk], b2, b3);
-      }
-    }
-
-    // ---- online softmax (rows g = lane/4 and g+8), keys beyond the utterance masked to -inf
-    const int kv0 = t * BKV;
-    float mx[2] = {-INFINITY, -INFINITY};
-#pragma unroll
-    for (int nb = 0; nb < 8; ++nb) {
-      const int key = kv0 + nb * 8 + 2 * (lane & 3);
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const bool ok = (key + (e & 1)) < len;
-        s[nb][e] = ok ? s[nb][e] * scale_log2e : -INFINITY;
-        mx[e >> 1] = fmaxf(mx[e >> 1], s[nb][e]);
-      }
-    }
-    float alpha[2];
-#pragma unroll
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_qkv) : "memory");
+    mbar_init(q_full, 1);
     for (int i = 0; i < 2; ++i) {
-      mx[i] = fmaxf(mx[i], __shfl_xor_sync(0xffffffffu, mx[i], 1));
-      mx[i] = fmaxf(mx[i], __shfl_xor_sync(0xffffffffu, mx[i], 2));
-      const float m_new = fmaxf(m_run[i], mx[i]);  // finite: every tile holds >= 1 valid key
-      alpha[i] = exp2f(m_run[i] - m_new);
-      m_run[i] = m_new;
+      mbar_init(kv_full + 8 * i, 1);
+      mbar_init(kv_empty + 8 * i, 1);
+      mbar_init(s_full + 8 * i, 1);
     }
-    float rs[2] = {0.f, 0.f};
-    uint32_t pf[4][4];
-#pragma unroll
-    for (int nb = 0; nb < 8; ++nb) {
-      const float p0 = exp2f(s[nb][0] - m_run[0]), p1 = exp2f(s[nb][1] - m_run[0]);
-      const float p2 = exp2f(s[nb][2] - m_run[1]), p3 = exp2f(s[nb][3] - m_run[1]);
-      rs[0] += p0 + p1;
-      rs[1] += p2 + p3;
-      pf[nb >> 1][(nb & 1) * 2 + 0] = pack_bf16x2(p0, p1);
-      pf[nb >> 1][(nb & 1) * 2 + 1] = pack_bf16x2(p2, p3);
-    }
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      rs[i] += __shfl_xor_sync(0xffffffffu, rs[i], 1);
-      rs[i] += __shfl_xor_sync(0xffffffffu, rs[i], 2);
-      l_run[i] = l_run[i] * alpha[i] + rs[i];
-    }
-#pragma unroll
-    for (int dn = 0; dn < 16; ++dn) {
-      o[dn][0] *= alpha[0]; o[dn][1] *= alpha[0];
-      o[dn][2] *= alpha[1]; o[dn][3] *= alpha[1];
-    }
+    mbar_init(p_full, 128);  // every softmax thread arrives
+    mbar_init(p_free, 1);
+    mbar_init(o_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot_ptr;
+  const uint32_t tS = tmem, tO = tmem + 2 * BKV;
 
-    // ---- O += P V
-#pragma unroll
-    for (int kk2 = 0; kk2 < 4; ++kk2) {
-#pragma unroll
-      for (int dn = 0; dn < 16; dn += 2) {
-        uint32_t b0, b1, b2, b3;
-        const int mi = lane >> 3, r = lane & 7;
-        ldsm_x4_t(sVt + swz(kk2 * 16 + (mi & 1) * 8 + r, dn + (mi >> 1)), b0, b1, b2, b3);
-        mma_bf16(o[dn], pf[kk2], b0, b1);
-        mma_bf16(o[dn + 1], pf[kk2], b2, b3);
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      const int xq = h * HD, xk = dm + h * HD, xv = 2 * dm + h * HD;
+      mbar_expect_tx(q_full, Q_BYTES);
+      tma_load_2d(sQ, &tmap_qkv, q_full, xq, start + q0);
+      tma_load_2d(sQ + PANEL, &tmap_qkv, q_full, xq + 64, start + q0);
+      for (int j = 0; j < n_blk; ++j) {
+        const int st = j & 1;
+        mbar_wait(kv_empty + 8 * st, ((j >> 1) & 1) ^ 1);
+        const uint32_t dst = sKV + st * KV_STAGE;
+        const int row = start + j * BKV;
+        mbar_expect_tx(kv_full + 8 * st, KV_STAGE);
+        tma_load_2d(dst, &tmap_qkv, kv_full + 8 * st, xk, row);
+        tma_load_2d(dst + PANEL, &tmap_qkv, kv_full + 8 * st, xk + 64, row);
+        tma_load_2d(dst + 2 * PANEL, &tmap_qkv, kv_full + 8 * st, xv, row);
+        tma_load_2d(dst + 3 * PANEL, &tmap_qkv, kv_full + 8 * st, xv + 64, row);
       }
     }
-    __syncthreads();  // everyone done with buf before the next prefetch overwrites it
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      auto keys_of = [&](int j) { return min(BKV, len - j * BKV); };
+      auto issue_s = [&](int j) {  // S[j&1] = Q K_j^T
+        const int st = j & 1;
+        mbar_wait(kv_full + 8 * st, (j >> 1) & 1);
+        tc_fence_after();
+        const int n = (keys_of(j) + 15) & ~15;
+        const uint32_t idesc = make_idesc(BQ, n, 0);
+        const uint32_t kb = sKV + st * KV_STAGE;
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k) {
+          const uint32_t off = (k >> 2) * PANEL + (k & 3) * 32;
+          umma_f16(tS + st * BKV, desc_kmajor(sQ + off), desc_kmajor(kb + off), idesc, k != 0);
+        }
+        umma_commit(s_full + 8 * st);
+      };
+      mbar_wait(q_full, 0);
+      issue_s(0);
+      for (int j = 0; j < n_blk; ++j) {
+        if (j + 1 < n_blk) issue_s(j + 1);
+        // O (+)= P V_j
+        const int st = j & 1;
+        mbar_wait(p_full, j & 1);
+        tc_fence_after();
+        const int ksteps = (keys_of(j) + 15) >> 4;
+        const uint32_t idesc = make_idesc(BQ, HD, 1);
+        const uint32_t vb = sKV + st * KV_STAGE + 2 * PANEL;
+        for (int k = 0; k < ksteps; ++k) {
+          const uint64_t adesc = desc_kmajor(sP + (k >> 2) * PANEL + (k & 3) * 32);
+          const uint64_t bdesc = desc_mnmajor(vb + k * 16 * 128, PANEL, 1024);
+          umma_f16(tO, adesc, bdesc, idesc, (j | k) != 0);
+        }
+        umma_commit(kv_empty + 8 * st);
+        umma_commit(p_free);
+        if (j == n_blk - 1) umma_commit(o_full);
+      }
+    }
+  } else {
+    // ===================== softmax / epilogue warps: thread = query row =====================
+    const int q = warp & 3;
+    const int row = q * 32 + lane;                 // row within the tile == TMEM lane
+    const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
+    const uint32_t rsw = static_cast<uint32_t>(row & 7);
+    float m_used = -INFINITY, l_run = 0.f;
+    for (int j = 0; j < n_blk; ++j) {
+      const int st = j & 1;
+      const int nkeys = min(BKV, len - j * BKV);
+      const int nch = (nkeys + 31) >> 5;  // 32-column chunks holding valid keys
+      mbar_wait(s_full + 8 * st, (j >> 1) & 1);
+      tc_fence_after();
+      // ---- pass 1: row maximum over the valid keys
+      float mx = -INFINITY;
+      for (int c = 0; c < nch; ++c) {
+        uint32_t r[32];
+        tmem_ld32(tS + lane_sel + st * BKV + c * 32, r);
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (c * 32 + i < nkeys) mx = fmaxf(mx, __uint_as_float(r[i]));
+      }
+      const float m_blk = mx * scale_log2e;
+      // ---- running maximum: only raised when it would grow by more than 2^8 (then O in TMEM is rescaled once)
+      float alpha = 1.f;
+      if (j == 0) {
+        m_used = m_blk;
+      } else if (m_blk - m_used > RESCALE_THRESHOLD) {
+        alpha = exp2f(m_used - m_blk);
+        m_used = m_blk;
+      }
+      const bool any_rescale = __any_sync(0xffffffffu, alpha != 1.f);
+      // P of the previous block must have been consumed (and O be stable) before P / O are touched
+      if (j > 0) {
+        mbar_wait(p_free, (j - 1) & 1);
+        tc_fence_after();
+      }
+      if (any_rescale) {
+        l_run *= alpha;
+#pragma unroll 1
+        for (int c = 0; c < HD / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld32(tO + lane_sel + c * 32, r);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+          tmem_st32(tO + lane_sel + c * 32, r);
+        }
+      }
+      // ---- pass 2: p = exp2(s c - m), row sum, bf16 -> swizzled smem (A operand of the P V MMA)
+      float rs = 0.f;
+      const int nch16 = ((nkeys + 15) >> 4);  // 16-key MMA steps that will be issued
+      for (int c = 0; c < 4; ++c) {
+        if (c * 2 >= nch16) break;  // chunk not read by any MMA step
+        uint32_t r[32];
+        tmem_ld32(tS + lane_sel + st * BKV + c * 32, r);
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          const float p0 = (c * 32 + i < nkeys) ? exp2f(fmaf(__uint_as_float(r[i]), scale_log2e, -m_used)) : 0.f;
+          const float p1 = (c * 32 + i + 1 < nkeys) ? exp2f(fmaf(__uint_as_float(r[i + 1]), scale_log2e, -m_used)) : 0.f;
+          rs += p0 + p1;
+          pk[i >> 1] = pack_bf16x2(p0, p1);
+        }
+        // 32 keys = 64 B = four 16-byte chunks of this row inside panel (c >> 1)
+        const uint32_t prow = sP + (c >> 1) * PANEL + static_cast<uint32_t>(row) * 128u;
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          sts128(prow + ((static_cast<uint32_t>((c & 1) * 4 + g) ^ rsw) << 4), pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+      }
+      l_run += rs;
+      fence_async_smem();
+      tc_fence_before();
+      mbar_arrive(p_full);
+    }
+    // ---- epilogue: O / l -> bf16 -> ctx (head merge = column offset h*128)
+    mbar_wait(o_full, 0);
+    tc_fence_after();
+    const float inv = 1.f / l_run;
+    const bool row_ok = q0 + row < len;
+    __nv_bfloat16* dst = ctx + static_cast<int64_t>(start + q0 + row) * ld_ctx + h * HD;
+#pragma unroll 1
+    for (int c = 0; c < HD / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld32(tO + lane_sel + c * 32, r);
+      if (row_ok) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) {
+          uint4 o;
+          o.x = pack_bf16x2(__uint_as_float(r[i]) * inv, __uint_as_float(r[i + 1]) * inv);
+          o.y = pack_bf16x2(__uint_as_float(r[i + 2]) * inv, __uint_as_float(r[i + 3]) * inv);
+          o.z = pack_bf16x2(__uint_as_float(r[i + 4]) * inv, __uint_as_float(r[i + 5]) * inv);
+          o.w = pack_bf16x2(__uint_as_float(r[i + 6]) * inv, __uint_as_float(r[i + 7]) * inv);
+          *reinterpret_cast<uint4*>(dst + c * 32 + i) = o;
+        }
+      }
+    }
   }
 
-  // ---- normalise and store (head merge = column offset h*128)
-  const int g = lane >> 2;
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int row = q0 + warp * 16 + g + 8 * i;
-    if (row < len) {
-      const float inv = 1.f / l_run[i];
-      __nv_bfloat16* dst = ctx + static_cast<int64_t>(start + row) * ld_ctx + h * HD + 2 * (lane & 3);
-#pragma unroll
-      for (int dn = 0; dn < 16; ++dn)
-        *reinterpret_cast<uint32_t*>(dst + dn * 8) = pack_bf16x2(o[dn][2 * i] * inv, o[dn][2 * i + 1] * inv);
-    }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
   }
 }
 
 }  // namespace attn
 
 int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int max_len,
-                     int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, cudaStream_t stream) {
-  FA_REQUIRE(ld % 8 == 0 && ld_ctx % 2 == 0, "attention: qkv row stride must be a multiple of 8 elements");
-  FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0, "attention: qkv must be 16-byte aligned");
-  FA_REQUIRE(max_len > 0 && n_utts > 0 && n_heads > 0, "attention: empty problem");
+                     int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream) {
+  FA_REQUIRE(ld % 8 == 0 && ld_ctx % 8 == 0, "attention: row strides must be multiples of 8 elements");
+  FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0,
+             "attention: qkv and ctx must be 16-byte aligned");
+  FA_REQUIRE(max_len > 0 && n_utts > 0 && n_heads > 0 && n_rows > 0, "attention: empty problem");
+  FA_REQUIRE(ld >= 3 * n_heads * attn::HD, "attention: qkv rows hold q|k|v of %d heads x 128", n_heads);
   static bool attr_done = false;
   if (!attr_done) {
     FA_CHECK_CUDA(cudaFuncSetAttribute(attn::attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, attn::SMEM_BYTES));
     attr_done = true;
   }
+  // rows = the valid packed rows only: key/value rows past the end are zero-filled by TMA instead of reading workspace
+  // padding (whose contents are undefined and could be NaN, which 0 * NaN would leak into O).
+  TensorMap2D tm;
+  if (int r = make_tensor_map_bf16(&tm, qkv, n_rows, 3 * n_heads * attn::HD, ld, 128)) return r;
+  CUtensorMap m;
+  memcpy(&m, tm.bytes, sizeof(m));
   dim3 grid(ceil_div(max_len, attn::BQ), n_heads, n_utts);
   const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(attn::HD));
   ProfScope _ps(K_ATTENTION, stream);
-  attn::attention_kernel<<<grid, attn::THREADS, attn::SMEM_BYTES, stream>>>(qkv, ld, cu_seqlens, n_heads, ctx, ld_ctx,
-                                                                           scale_log2e);
+  attn::attention_kernel<<<grid, attn::THREADS, attn::SMEM_BYTES, stream>>>(m, cu_seqlens, n_heads, ctx, ld_ctx, scale_log2e);
   FA_CHECK_LAUNCH();
   return 0;
 }
@@ -218,9 +359,10 @@ int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seq
 }  // namespace fa
 
 extern "C" int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqlens_dev, int32_t n_utts,
-                               int32_t max_len, int32_t n_heads, void* ctx_dev, int64_t ld_ctx, fa_stream_t stream) {
+                               int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx,
+                               fa_stream_t stream) {
   using namespace fa;
   FA_REQUIRE(qkv_dev && cu_seqlens_dev && ctx_dev, "attention: NULL pointer");
   return launch_attention(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, cu_seqlens_dev, n_utts, max_len, n_heads,
-                          static_cast<__nv_bfloat16*>(ctx_dev), ld_ctx, static_cast<cudaStream_t>(stream));
+                          static_cast<__nv_bfloat16*>(ctx_dev), ld_ctx, n_rows, static_cast<cudaStream_t>(stream));
 }

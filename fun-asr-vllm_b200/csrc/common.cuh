@@ -78,11 +78,9 @@ int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, con
 int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts,
                 float* mem, int M, int D, int kernel, int left_pad, cudaStream_t stream);
 int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int max_len,
-                     int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, cudaStream_t stream);
+                     int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream);
 int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, int dst_bf16, const int32_t* cu,
                        int n_utts, int M, int D, cudaStream_t stream);
-int launch_cast_bf16(const float* x, __nv_bfloat16* y, int64_t n, cudaStream_t stream);
-int launch_copy_f32(const float* x, float* y, int64_t n, cudaStream_t stream);
 
 }  // namespace fa
 

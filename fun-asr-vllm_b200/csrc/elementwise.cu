@@ -146,16 +146,17 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
 // ---------------------------------------------------------------- FSMN memory block
 // mem[t, c] = v[t, c] + sum_k w[k, c] * v[t + k - left, c]   (zero outside the utterance; w is TAP-MAJOR [K, D])
 // (VLLM/model_executor/models/funasr.py:181-201: mask, ConstantPad1d, depthwise Conv1d, +inputs, mask).
-// One thread owns 4 adjacent channels (one 8-byte bf16x4 load per row) and FSMN_ROWS consecutive
-// rows: the FSMN_ROWS + K - 1 input rows are loaded up front (independent loads, deep MLP), the tap
-// window then slides through registers, so every v element is read once per CTA plus the halo, a
-// warp reads 256 contiguous bytes per row and writes 512.  Utterance bounds of the CTA's rows are
-// found once per row (16 binary searches per CTA) and shared through smem.
+// One thread owns 2 adjacent channels (one bf16x2 load per row) and FSMN_ROWS consecutive rows: the
+// FSMN_ROWS + K - 1 input rows are loaded up front (independent loads, deep MLP) and converted to fp32 ONCE, the
+// tap window then slides through registers (pure FMA inner loop).  Rows of a block that lie in one utterance (the
+// common case) take a predicate-free path: out-of-utterance input rows are zeroed at load time.  Utterance bounds
+// are found once per row (16 binary searches per CTA) and shared through smem.
 constexpr int FSMN_ROWS = 16;
 constexpr int FSMN_MAXK = 16;
+constexpr int FSMN_THREADS = 128;
 
 template <int K>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(FSMN_THREADS)
 fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
             const int32_t* __restrict__ cu, int n_utts, float* __restrict__ mem, int M, int D, int left) {
   __shared__ int s_lo[FSMN_ROWS], s_hi[FSMN_ROWS];
@@ -166,64 +167,72 @@ fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const 
     s_lo[threadIdx.x] = ub.x;
     s_hi[threadIdx.x] = ub.y;
   }
-  const int c4 = blockIdx.y * blockDim.x + threadIdx.x;  // group of 4 channels
-  const bool ch_ok = 4 * c4 < D;
+  const int c2 = blockIdx.y * blockDim.x + threadIdx.x;  // channel pair
+  const bool ch_ok = 2 * c2 < D;
   constexpr int NIN = FSMN_ROWS + K - 1;
-  // ---- all input rows of this thread's 4 channels: independent 8-byte loads
-  uint2 raw[NIN];
-  const __nv_bfloat16* vbase = qkv + v_col + 4 * c4;
+  uint32_t raw[NIN];
+  const __nv_bfloat16* vbase = qkv + v_col + 2 * c2;
 #pragma unroll
   for (int i = 0; i < NIN; ++i) {
     const int rr = r0 - left + i;
-    raw[i] = make_uint2(0u, 0u);
-    if (ch_ok && rr >= 0 && rr < M) raw[i] = __ldg(reinterpret_cast<const uint2*>(vbase + static_cast<int64_t>(rr) * ld));
+    raw[i] = 0u;
+    if (ch_ok && rr >= 0 && rr < M) raw[i] = __ldg(reinterpret_cast<const uint32_t*>(vbase + static_cast<int64_t>(rr) * ld));
   }
-  // tap-major weights [K, D]: one coalesced float4 per tap.  The "+ inputs" term (VLLM/...:199) is tap `left` with
+  // tap-major weights [K, D]: one coalesced float2 per tap.  The "+ inputs" term (VLLM/...:199) is tap `left` with
   // weight + 1: row r is always inside its own utterance.
-  float4 wt[K];
+  float2 wt[K];
 #pragma unroll
   for (int k = 0; k < K; ++k) {
-    wt[k] = ch_ok ? __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(k) * D) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
-    if (k == left) { wt[k].x += 1.f; wt[k].y += 1.f; wt[k].z += 1.f; wt[k].w += 1.f; }
+    wt[k] = ch_ok ? __ldg(reinterpret_cast<const float2*>(w + static_cast<int64_t>(k) * D) + c2) : make_float2(0.f, 0.f);
+    if (k == left) { wt[k].x += 1.f; wt[k].y += 1.f; }
   }
   __syncthreads();
   if (!ch_ok) return;
+  const int nrow = min(FSMN_ROWS, M - r0);
+  const int lo0 = s_lo[0], hi0 = s_hi[0];
+  const bool one_utt = (s_lo[nrow - 1] == lo0);
+  float2 v[NIN];
 #pragma unroll
-  for (int j = 0; j < FSMN_ROWS; ++j) {
-    const int r = r0 + j;
-    if (r >= M) break;
-    const int lo = s_lo[j], hi = s_hi[j];
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  for (int i = 0; i < NIN; ++i) {
+    const int rr = r0 - left + i;
+    v[i] = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[i]));
+    if (one_utt && (rr < lo0 || rr >= hi0)) v[i] = make_float2(0.f, 0.f);
+  }
+  float* obase = mem + static_cast<int64_t>(r0) * D + 2 * c2;
+  if (one_utt) {
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const int rr = r + k - left;
-      if (rr >= lo && rr < hi) {  // warp-uniform: the whole CTA shares r
-        const float2 f01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[j + k].x));
-        const float2 f23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[j + k].y));
-        a0 = fmaf(wt[k].x, f01.x, a0);
-        a1 = fmaf(wt[k].y, f01.y, a1);
-        a2 = fmaf(wt[k].z, f23.x, a2);
-        a3 = fmaf(wt[k].w, f23.y, a3);
+    for (int j = 0; j < FSMN_ROWS; ++j) {
+      if (j < nrow) {
+        float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          a0 = fmaf(wt[k].x, v[j + k].x, a0);
+          a1 = fmaf(wt[k].y, v[j + k].y, a1);
+        }
+        *reinterpret_cast<float2*>(obase + static_cast<int64_t>(j) * D) = make_float2(a0, a1);
       }
     }
-    *reinterpret_cast<float4*>(mem + static_cast<int64_t>(r) * D + 4 * c4) = make_float4(a0, a1, a2, a3);
+  } else {
+#pragma unroll
+    for (int j = 0; j < FSMN_ROWS; ++j) {
+      if (j < nrow) {
+        const int r = r0 + j, lo = s_lo[j], hi = s_hi[j];
+        float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          const int rr = r + k - left;
+          if (rr >= lo && rr < hi) {  // uniform across the CTA
+            a0 = fmaf(wt[k].x, v[j + k].x, a0);
+            a1 = fmaf(wt[k].y, v[j + k].y, a1);
+          }
+        }
+        *reinterpret_cast<float2*>(obase + static_cast<int64_t>(j) * D) = make_float2(a0, a1);
+      }
+    }
   }
 }
 
-// ---------------------------------------------------------------- casts / copies / splice
-__global__ void cast_bf16_kernel(const float4* __restrict__ x, uint2* __restrict__ y, int64_t n4) {
-  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n4;
-       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const float4 v = x[i];
-    y[i] = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
-  }
-}
-__global__ void copy_f32_kernel(const float4* __restrict__ x, float4* __restrict__ y, int64_t n4) {
-  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n4;
-       i += static_cast<int64_t>(gridDim.x) * blockDim.x)
-    y[i] = x[i];
-}
-
+// ---------------------------------------------------------------- row re-layout / splice
 // Row re-layout + cast: dst row r (packed [M,D] or padded [n_utts, dst_tmax, D]) <- the matching
 // src row (packed or padded [n_utts, src_tmax, D]), f32 -> f32 | bf16; padding rows are zero-filled.
 // This is the only place the padded [B, Tmax, .] layout of the reference API exists.
@@ -321,12 +330,12 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
                 float* mem, int M, int D, int kernel, int left_pad, cudaStream_t stream) {
   FA_REQUIRE(kernel >= 1 && kernel <= ew::FSMN_MAXK, "fsmn: kernel size %d not in [1,%d]", kernel, ew::FSMN_MAXK);
   FA_REQUIRE(left_pad >= 0 && left_pad < kernel, "fsmn: left pad %d outside the %d-tap window", left_pad, kernel);
-  FA_REQUIRE(D % 4 == 0 && v_col % 4 == 0 && ld % 4 == 0, "fsmn: D, v_col and ld must be multiples of 4");
-  FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 7) == 0 && (reinterpret_cast<uintptr_t>(mem) & 15) == 0 &&
-                 (reinterpret_cast<uintptr_t>(w) & 15) == 0,
-             "fsmn: qkv must be 8-byte, mem and w 16-byte aligned");
-  const int threads = 128;
-  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 4, threads));
+  FA_REQUIRE(D % 2 == 0 && v_col % 2 == 0 && ld % 2 == 0, "fsmn: D, v_col and ld must be even");
+  FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 3) == 0 && (reinterpret_cast<uintptr_t>(mem) & 7) == 0 &&
+                 (reinterpret_cast<uintptr_t>(w) & 7) == 0,
+             "fsmn: qkv must be 4-byte, mem and w 8-byte aligned");
+  const int threads = ew::FSMN_THREADS;
+  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 2, threads));
   ProfScope _ps(K_FSMN, stream);
 #define FA_FSMN_CASE(KK) \
   case KK: ew::fsmn_kernel<KK><<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, mem, M, D, left_pad); break;
@@ -348,24 +357,6 @@ int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, 
   const int rows = dst_tmax > 0 ? n_utts * dst_tmax : M;
   ProfScope _ps(K_REPACK, stream);
   ew::repack_rows_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(src, src_tmax, dst, dst_tmax, dst_bf16, cu, n_utts, rows, D);
-  FA_CHECK_LAUNCH();
-  return 0;
-}
-
-int launch_cast_bf16(const float* x, __nv_bfloat16* y, int64_t n, cudaStream_t stream) {
-  FA_REQUIRE(n % 4 == 0, "cast: element count must be a multiple of 4");
-  const int64_t n4 = n / 4;
-  const int blocks = static_cast<int>(n4 / 256 + 1 < 148 * 8 ? n4 / 256 + 1 : 148 * 8);
-  ew::cast_bf16_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<uint2*>(y), n4);
-  FA_CHECK_LAUNCH();
-  return 0;
-}
-
-int launch_copy_f32(const float* x, float* y, int64_t n, cudaStream_t stream) {
-  FA_REQUIRE(n % 4 == 0, "copy: element count must be a multiple of 4");
-  const int64_t n4 = n / 4;
-  const int blocks = static_cast<int>(n4 / 256 + 1 < 148 * 8 ? n4 / 256 + 1 : 148 * 8);
-  ew::copy_f32_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), n4);
   FA_CHECK_LAUNCH();
   return 0;
 }

@@ -228,9 +228,9 @@ int fa_op_embed_layernorm(const float* x_dev, const float* inv_ts_dev, const int
 int fa_op_fsmn(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, const float* w_dev, const int32_t* cu_seqlens_dev,
                int32_t n_utts, float* mem_dev, int32_t M, int32_t D, int32_t kernel, int32_t left_pad,
                fa_stream_t stream);
-/* ctx[M, H*128] bf16 = softmax(q k^T / sqrt(128)) v per utterance and head; q|k|v packed in qkv rows */
+/* ctx[M, H*128] bf16 = softmax(q k^T / sqrt(128)) v per utterance and head; q|k|v packed in the n_rows (= M) qkv rows */
 int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqlens_dev, int32_t n_utts,
-                    int32_t max_len, int32_t n_heads, void* ctx_dev, int64_t ld_ctx, fa_stream_t stream);
+                    int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx, fa_stream_t stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -70,7 +70,7 @@ def op_attention(qkv_bf16, cu, n_heads):
     ctx = torch.empty((M, dm), dtype=torch.bfloat16, device="cuda")
     cu_d = dev(cu)
     _lib.check(lib().fa_op_attention(qkv_bf16.data_ptr(), qkv_bf16.stride(0), cu_d.data_ptr(), len(cu) - 1,
-                                     int(np.diff(cu).max()), n_heads, ctx.data_ptr(), dm, stream()))
+                                     int(np.diff(cu).max()), n_heads, M, ctx.data_ptr(), dm, stream()))
     return ctx
 
 

@@ -116,6 +116,32 @@ def test_attention_varlen(U, lens, H):
     assert U.rel_rms(got.float(), want) < 1e-2
 
 
+def test_attention_running_max_rescale_path(U):
+    """Large score range: later key blocks raise the running maximum by more than 2^8, so the O accumulator in TMEM is
+    rescaled; also poisons the rows after the last utterance with NaN (workspace padding must never leak in)."""
+    g = torch.Generator().manual_seed(77)
+    lens, H = [300, 667, 129], 4
+    cu = U.cu_of(lens)
+    M, dm = int(cu[-1]), H * 128
+    qkv = torch.randn(M + 64, 3 * dm, generator=g)
+    qkv[:, :dm] *= 8.0
+    ramp = torch.linspace(0.2, 2.0, M + 64)[:, None]
+    qkv[:, dm:2 * dm] *= ramp  # later keys score higher
+    qkv = bf(qkv)
+    rows = []
+    for b in range(len(lens)):
+        x = qkv[cu[b]:cu[b + 1]].float()
+        q, k, v = (x[:, i * dm:(i + 1) * dm].reshape(-1, H, 128).transpose(0, 1) for i in range(3))
+        p = torch.softmax((q * 128 ** -0.5) @ k.transpose(1, 2), dim=-1)
+        rows.append((p @ v).transpose(0, 1).reshape(-1, dm))
+    want = torch.cat(rows)
+    dev = qkv.cuda()
+    dev[M:] = float("nan")
+    got = U.op_attention(dev[:M], cu, H)
+    assert torch.isfinite(got.float()).all()
+    assert U.rel_rms(got.float(), want) < 1.5e-2
+
+
 def test_errors_are_reported_not_swallowed(U):
     from funasr_b200 import FunASRB200Error
 
