@@ -4,13 +4,16 @@
 //   (VLLM/model_executor/models/funasr.py:222-235,250-252; adaptor :506-512).
 //
 // One CTA = (utterance b, head h, 128 query rows).  Keys/values stream through shared memory in blocks of 128
-// (TMA, 128B swizzle, two stages); per block
-//     S  = Q K_j^T          tcgen05.mma, A = Q (smem, K-major), B = K_j (smem, K-major), D in TMEM (double buffered)
-//     P  = exp2(S c - m)    softmax warps: thread = row, TMEM -> registers -> bf16 -> swizzled smem (A operand layout)
+// (TMA, 128B swizzle); per block
+//     S  = Q K_j^T          tcgen05.mma, A = Q (smem, K-major), B = K_j (smem, K-major), D in TMEM
+//     P  = exp2(S c - m)    softmax warps: thread = row, TMEM -> registers (one pass) -> bf16 -> swizzled smem in the
+//                           A-operand layout, written over K_j (dead once S_j is complete)
 //     O += P V_j            tcgen05.mma, A = P (smem, K-major), B = V_j (smem, MN-major: V rows are keys), D in TMEM
 // with an online softmax whose running maximum is only raised when it grows by more than 2^8 (the O accumulator in
-// TMEM is then rescaled once), so most blocks never touch O.  Warp roles: 0 TMA producer, 1 MMA issuer (+ TMEM
-// alloc), 2..5 softmax / epilogue (one TMEM lane quarter each).
+// TMEM is then rescaled once), so most blocks never touch O.  The CTA is deliberately lean — 97 KB of smem and 256
+// TMEM columns — so that TWO CTAs share an SM and one's TMA / softmax phases overlap the other's MMAs (utterances are
+// short: T = 167 for 10 s, i.e. two key blocks).  Warp roles: 0 TMA producer, 1 MMA issuer (+ TMEM alloc), 2..5
+// softmax / epilogue (one TMEM lane quarter each).
 #include <cuda.h>
 
 #include <cstring>
@@ -26,10 +29,10 @@ constexpr int BKV = 128;  // keys per block
 constexpr int THREADS = 192;
 constexpr int PANEL = BQ * 128;            // one [128 rows x 64 bf16] 128B-swizzled panel = 16 KB
 constexpr int Q_BYTES = 2 * PANEL;         // d = 128 -> two panels
-constexpr int KV_STAGE = 4 * PANEL;        // K block (2 panels) + V block (2 panels)
-constexpr int P_BYTES = 2 * PANEL;         // 128 keys -> two panels
-constexpr int SMEM_BYTES = Q_BYTES + 2 * KV_STAGE + P_BYTES + 1024 + 256;
-constexpr int TMEM_COLS = 512;             // S0 [0,128) S1 [128,256) O [256,384)
+constexpr int K_BYTES = 2 * PANEL;         // K block: two panels; P (128 keys -> two panels) later overwrites it
+constexpr int V_BYTES = 2 * PANEL;
+constexpr int SMEM_BYTES = Q_BYTES + K_BYTES + V_BYTES + 1024 + 256;
+constexpr int TMEM_COLS = 256;             // S [0,128)  O [128,256)
 constexpr float RESCALE_THRESHOLD = 8.f;   // log2 units
 
 // ---------------------------------------------------------------- PTX wrappers (same conventions as gemm_tcgen05.cu)
@@ -123,7 +126,7 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 }
 
 // ---------------------------------------------------------------- kernel
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(THREADS, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __restrict__ cu, int n_heads,
                  __nv_bfloat16* __restrict__ ctx, int64_t ld_ctx, float scale_log2e) {
   extern __shared__ unsigned char smem_raw[];
@@ -136,21 +139,19 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
   const int n_blk = (len + BKV - 1) / BKV;
 
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sQ = base, sKV = sQ + Q_BYTES, sP = sKV + 2 * KV_STAGE, bars = sP + P_BYTES;
-  const uint32_t q_full = bars, kv_full = bars + 8, kv_empty = bars + 24, s_full = bars + 40, p_full = bars + 56,
-                 p_free = bars + 64, o_full = bars + 72, tmem_slot = bars + 80;
+  const uint32_t sQ = base, sK = sQ + Q_BYTES, sV = sK + K_BYTES, sP = sK, bars = sV + V_BYTES;
+  const uint32_t q_full = bars, k_full = bars + 8, v_full = bars + 16, kv_empty = bars + 24, s_full = bars + 32,
+                 p_full = bars + 40, o_full = bars + 48, tmem_slot = bars + 56;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_qkv) : "memory");
     mbar_init(q_full, 1);
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(kv_full + 8 * i, 1);
-      mbar_init(kv_empty + 8 * i, 1);
-      mbar_init(s_full + 8 * i, 1);
-    }
+    mbar_init(k_full, 1);
+    mbar_init(v_full, 1);
+    mbar_init(kv_empty, 1);
+    mbar_init(s_full, 1);
     mbar_init(p_full, 128);  // every softmax thread arrives
-    mbar_init(p_free, 1);
     mbar_init(o_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -162,7 +163,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_ptr;
-  const uint32_t tS = tmem, tO = tmem + 2 * BKV;
+  const uint32_t tS = tmem, tO = tmem + BKV;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -172,54 +173,49 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
       tma_load_2d(sQ, &tmap_qkv, q_full, xq, start + q0);
       tma_load_2d(sQ + PANEL, &tmap_qkv, q_full, xq + 64, start + q0);
       for (int j = 0; j < n_blk; ++j) {
-        const int st = j & 1;
-        mbar_wait(kv_empty + 8 * st, ((j >> 1) & 1) ^ 1);
-        const uint32_t dst = sKV + st * KV_STAGE;
+        mbar_wait(kv_empty, (j & 1) ^ 1);  // P_{j-1} V_{j-1} retired: the K/P and V regions are free
         const int row = start + j * BKV;
-        mbar_expect_tx(kv_full + 8 * st, KV_STAGE);
-        tma_load_2d(dst, &tmap_qkv, kv_full + 8 * st, xk, row);
-        tma_load_2d(dst + PANEL, &tmap_qkv, kv_full + 8 * st, xk + 64, row);
-        tma_load_2d(dst + 2 * PANEL, &tmap_qkv, kv_full + 8 * st, xv, row);
-        tma_load_2d(dst + 3 * PANEL, &tmap_qkv, kv_full + 8 * st, xv + 64, row);
+        mbar_expect_tx(k_full, K_BYTES);
+        tma_load_2d(sK, &tmap_qkv, k_full, xk, row);
+        tma_load_2d(sK + PANEL, &tmap_qkv, k_full, xk + 64, row);
+        mbar_expect_tx(v_full, V_BYTES);
+        tma_load_2d(sV, &tmap_qkv, v_full, xv, row);
+        tma_load_2d(sV + PANEL, &tmap_qkv, v_full, xv + 64, row);
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      auto keys_of = [&](int j) { return min(BKV, len - j * BKV); };
-      auto issue_s = [&](int j) {  // S[j&1] = Q K_j^T
-        const int st = j & 1;
-        mbar_wait(kv_full + 8 * st, (j >> 1) & 1);
-        tc_fence_after();
-        const int n = (keys_of(j) + 15) & ~15;
-        const uint32_t idesc = make_idesc(BQ, n, 0);
-        const uint32_t kb = sKV + st * KV_STAGE;
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k) {
-          const uint32_t off = (k >> 2) * PANEL + (k & 3) * 32;
-          umma_f16(tS + st * BKV, desc_kmajor(sQ + off), desc_kmajor(kb + off), idesc, k != 0);
-        }
-        umma_commit(s_full + 8 * st);
-      };
       mbar_wait(q_full, 0);
-      issue_s(0);
       for (int j = 0; j < n_blk; ++j) {
-        if (j + 1 < n_blk) issue_s(j + 1);
-        // O (+)= P V_j
-        const int st = j & 1;
-        mbar_wait(p_full, j & 1);
+        const int nkeys = min(BKV, len - j * BKV);
+        // S = Q K_j^T
+        mbar_wait(k_full, j & 1);
         tc_fence_after();
-        const int ksteps = (keys_of(j) + 15) >> 4;
-        const uint32_t idesc = make_idesc(BQ, HD, 1);
-        const uint32_t vb = sKV + st * KV_STAGE + 2 * PANEL;
-        for (int k = 0; k < ksteps; ++k) {
-          const uint64_t adesc = desc_kmajor(sP + (k >> 2) * PANEL + (k & 3) * 32);
-          const uint64_t bdesc = desc_mnmajor(vb + k * 16 * 128, PANEL, 1024);
-          umma_f16(tO, adesc, bdesc, idesc, (j | k) != 0);
+        {
+          const uint32_t idesc = make_idesc(BQ, (nkeys + 15) & ~15, 0);
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k) {
+            const uint32_t off = (k >> 2) * PANEL + (k & 3) * 32;
+            umma_f16(tS, desc_kmajor(sQ + off), desc_kmajor(sK + off), idesc, k != 0);
+          }
+          umma_commit(s_full);
         }
-        umma_commit(kv_empty + 8 * st);
-        umma_commit(p_free);
-        if (j == n_blk - 1) umma_commit(o_full);
+        // O (+)= P V_j
+        mbar_wait(p_full, j & 1);
+        mbar_wait(v_full, j & 1);
+        tc_fence_after();
+        {
+          const int ksteps = (nkeys + 15) >> 4;
+          const uint32_t idesc = make_idesc(BQ, HD, 1);
+          for (int k = 0; k < ksteps; ++k) {
+            const uint64_t adesc = desc_kmajor(sP + (k >> 2) * PANEL + (k & 3) * 32);
+            const uint64_t bdesc = desc_mnmajor(sV + k * 16 * 128, PANEL, 1024);
+            umma_f16(tO, adesc, bdesc, idesc, (j | k) != 0);
+          }
+          umma_commit(kv_empty);
+          if (j == n_blk - 1) umma_commit(o_full);
+        }
       }
     }
   } else {
@@ -230,19 +226,21 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
     const uint32_t rsw = static_cast<uint32_t>(row & 7);
     float m_used = -INFINITY, l_run = 0.f;
     for (int j = 0; j < n_blk; ++j) {
-      const int st = j & 1;
       const int nkeys = min(BKV, len - j * BKV);
       const int nch = (nkeys + 31) >> 5;  // 32-column chunks holding valid keys
-      mbar_wait(s_full + 8 * st, (j >> 1) & 1);
+      mbar_wait(s_full, j & 1);           // also implies P_{j-1} V_{j-1} has retired (K_j was loaded after it)
       tc_fence_after();
-      // ---- pass 1: row maximum over the valid keys
+      // ---- the whole S row of this block into registers (one TMEM pass), row maximum over the valid keys
+      uint32_t r[4][32];
       float mx = -INFINITY;
-      for (int c = 0; c < nch; ++c) {
-        uint32_t r[32];
-        tmem_ld32(tS + lane_sel + st * BKV + c * 32, r);
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (c * 32 + i < nkeys) mx = fmaxf(mx, __uint_as_float(r[i]));
+      for (int c = 0; c < 4; ++c) {
+        if (c < nch) {
+          tmem_ld32(tS + lane_sel + c * 32, r[c]);
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (c * 32 + i < nkeys) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+        }
       }
       const float m_blk = mx * scale_log2e;
       // ---- running maximum: only raised when it would grow by more than 2^8 (then O in TMEM is rescaled once)
@@ -253,43 +251,37 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
         alpha = exp2f(m_used - m_blk);
         m_used = m_blk;
       }
-      const bool any_rescale = __any_sync(0xffffffffu, alpha != 1.f);
-      // P of the previous block must have been consumed (and O be stable) before P / O are touched
-      if (j > 0) {
-        mbar_wait(p_free, (j - 1) & 1);
-        tc_fence_after();
-      }
-      if (any_rescale) {
+      if (__any_sync(0xffffffffu, alpha != 1.f)) {
         l_run *= alpha;
 #pragma unroll 1
         for (int c = 0; c < HD / 32; ++c) {
-          uint32_t r[32];
-          tmem_ld32(tO + lane_sel + c * 32, r);
+          uint32_t o[32];
+          tmem_ld32(tO + lane_sel + c * 32, o);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-          tmem_st32(tO + lane_sel + c * 32, r);
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st32(tO + lane_sel + c * 32, o);
         }
       }
-      // ---- pass 2: p = exp2(s c - m), row sum, bf16 -> swizzled smem (A operand of the P V MMA)
+      // ---- p = exp2(s c - m), row sum, bf16 -> swizzled smem (A operand of the P V MMA), over the dead K block
       float rs = 0.f;
-      const int nch16 = ((nkeys + 15) >> 4);  // 16-key MMA steps that will be issued
+      const int nch16 = (nkeys + 15) >> 4;  // 16-key MMA steps that will be issued
+#pragma unroll
       for (int c = 0; c < 4; ++c) {
-        if (c * 2 >= nch16) break;  // chunk not read by any MMA step
-        uint32_t r[32];
-        tmem_ld32(tS + lane_sel + st * BKV + c * 32, r);
-        uint32_t pk[16];
+        if (c * 2 < nch16) {  // chunk read by at least one MMA step
+          uint32_t pk[16];
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          const float p0 = (c * 32 + i < nkeys) ? exp2f(fmaf(__uint_as_float(r[i]), scale_log2e, -m_used)) : 0.f;
-          const float p1 = (c * 32 + i + 1 < nkeys) ? exp2f(fmaf(__uint_as_float(r[i + 1]), scale_log2e, -m_used)) : 0.f;
-          rs += p0 + p1;
-          pk[i >> 1] = pack_bf16x2(p0, p1);
+          for (int i = 0; i < 32; i += 2) {
+            const float p0 = (c * 32 + i < nkeys) ? exp2f(fmaf(__uint_as_float(r[c][i]), scale_log2e, -m_used)) : 0.f;
+            const float p1 = (c * 32 + i + 1 < nkeys) ? exp2f(fmaf(__uint_as_float(r[c][i + 1]), scale_log2e, -m_used)) : 0.f;
+            rs += p0 + p1;
+            pk[i >> 1] = pack_bf16x2(p0, p1);
+          }
+          // 32 keys = 64 B = four 16-byte chunks of this row inside panel (c >> 1)
+          const uint32_t prow = sP + (c >> 1) * PANEL + static_cast<uint32_t>(row) * 128u;
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            sts128(prow + ((static_cast<uint32_t>((c & 1) * 4 + g) ^ rsw) << 4), pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
         }
-        // 32 keys = 64 B = four 16-byte chunks of this row inside panel (c >> 1)
-        const uint32_t prow = sP + (c >> 1) * PANEL + static_cast<uint32_t>(row) * 128u;
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-          sts128(prow + ((static_cast<uint32_t>((c & 1) * 4 + g) ^ rsw) << 4), pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
       }
       l_run += rs;
       fence_async_smem();
@@ -304,17 +296,17 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
     __nv_bfloat16* dst = ctx + static_cast<int64_t>(start + q0 + row) * ld_ctx + h * HD;
 #pragma unroll 1
     for (int c = 0; c < HD / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld32(tO + lane_sel + c * 32, r);
+      uint32_t o[32];
+      tmem_ld32(tO + lane_sel + c * 32, o);
       if (row_ok) {
 #pragma unroll
         for (int i = 0; i < 32; i += 8) {
-          uint4 o;
-          o.x = pack_bf16x2(__uint_as_float(r[i]) * inv, __uint_as_float(r[i + 1]) * inv);
-          o.y = pack_bf16x2(__uint_as_float(r[i + 2]) * inv, __uint_as_float(r[i + 3]) * inv);
-          o.z = pack_bf16x2(__uint_as_float(r[i + 4]) * inv, __uint_as_float(r[i + 5]) * inv);
-          o.w = pack_bf16x2(__uint_as_float(r[i + 6]) * inv, __uint_as_float(r[i + 7]) * inv);
-          *reinterpret_cast<uint4*>(dst + c * 32 + i) = o;
+          uint4 v;
+          v.x = pack_bf16x2(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv);
+          v.y = pack_bf16x2(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
+          v.z = pack_bf16x2(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv);
+          v.w = pack_bf16x2(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
+          *reinterpret_cast<uint4*>(dst + c * 32 + i) = v;
         }
       }
     }
