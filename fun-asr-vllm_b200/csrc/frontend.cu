@@ -3,8 +3,15 @@
 // One CTA produces FA_FE_TILE_ROWS low-frame-rate rows of one utterance:
 //   PCM (global, packed offsets) -> smem -> per frame {DC removal, pre-emphasis, window,
 //   512-pt real FFT as a 256-pt complex FFT (two radix-16 passes in registers, one smem
-//   transpose), power, sparse mel, log} -> smem log-mel tile -> LFR gather + CMVN -> global.
+//   transpose, conjugate-pair split through warp shuffles), power, sparse mel, log}
+//   -> smem log-mel tile -> LFR gather + CMVN -> global.
 // PCM is read once and the [T,560] features written once: no intermediate touches HBM.
+//
+// Precision.  Pre-emphasis leaves the lowest FFT bins ~30x (amplitude) below the loud ones, so fp32 round-off made
+// inside an FFT (relative to the LOUD bins) shows up as up to ~2e-3 in the log-mel of the lowest mel bins on long
+// full-scale inputs (profiles/scripts/fft_noise_study.py) — over the 1e-3 budget.  Therefore the pre-FFT steps follow
+// the reference's fp32 operation order exactly (same roundings as torchaudio: no FMA contraction), and the FFT, the
+// split and |X|^2 run in fp64 (B200 issues FP64 at half the FP32 rate); mel, log, LFR and CMVN are fp32 again.
 //
 // Arithmetic follows torchaudio.compliance.kaldi.fbank (TA:514-645, _get_window TA:154-217) and
 // funasr's apply_lfr / apply_cmvn (VLLM/transformers_utils/processors/funasr.py:40-60,23-37).
@@ -36,8 +43,8 @@ constexpr int MAX_TAPS = 1024;
 
 struct __align__(16) Tables {
   float window[FRAME_LEN];
-  float2 tw256[256];  // W256^k = (cos, -sin)(2 pi k / 256)
-  float2 tw512[136];  // W512^k, k = 0..128
+  double2 tw256[16][16];  // [q][t] = W256^(t q) = (cos, -sin)(2 pi t q / 256): pass-1 -> pass-2 twiddles, lane t reads [q][t]
+  double2 tw512[130];     // W512^k, k = 0..128
   int mel_start[NMEL];
   int mel_count[NMEL];
   int mel_woff[NMEL];
@@ -45,49 +52,50 @@ struct __align__(16) Tables {
 };
 
 struct __align__(16) Smem {
+  double2 tw256[16][16];
+  double2 tw512[130];
+  double work[SLOTS][16 * 17];  // 16x17 padded transpose buffer (real parts, then imaginary parts)
   float samples[MAX_SAMPLES + 8];
   float logmel[MAX_FRAMES + 1][NMEL];
-  float2 work[SLOTS][272];  // 16x17 padded transpose buffer, then Z[0..255]
   float power[SLOTS][264];
   float window[FRAME_LEN];
-  float2 tw512[136];
   float mel_w[MAX_TAPS];
   int mel_start[NMEL];
   int mel_count[NMEL];
   int mel_woff[NMEL];
 };
 
-__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
-  return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
-}
+typedef double2 cplx;
+__device__ __forceinline__ cplx mk(double re, double im) { return make_double2(re, im); }
+__device__ __forceinline__ cplx cmul(cplx a, cplx b) { return mk(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 
 // 4-point DFT in place: (a,b,c,d) -> (X0,X1,X2,X3), W4 = -i.
-__device__ __forceinline__ void dft4(float2& a, float2& b, float2& c, float2& d) {
-  float2 s0 = make_float2(a.x + c.x, a.y + c.y), s1 = make_float2(a.x - c.x, a.y - c.y);
-  float2 s2 = make_float2(b.x + d.x, b.y + d.y), s3 = make_float2(b.x - d.x, b.y - d.y);
-  a = make_float2(s0.x + s2.x, s0.y + s2.y);
-  c = make_float2(s0.x - s2.x, s0.y - s2.y);
-  b = make_float2(s1.x + s3.y, s1.y - s3.x);  // s1 - i*s3
-  d = make_float2(s1.x - s3.y, s1.y + s3.x);  // s1 + i*s3
+__device__ __forceinline__ void dft4(cplx& a, cplx& b, cplx& c, cplx& d) {
+  const cplx s0 = mk(a.x + c.x, a.y + c.y), s1 = mk(a.x - c.x, a.y - c.y);
+  const cplx s2 = mk(b.x + d.x, b.y + d.y), s3 = mk(b.x - d.x, b.y - d.y);
+  a = mk(s0.x + s2.x, s0.y + s2.y);
+  c = mk(s0.x - s2.x, s0.y - s2.y);
+  b = mk(s1.x + s3.y, s1.y - s3.x);  // s1 - i*s3
+  d = mk(s1.x - s3.y, s1.y + s3.x);  // s1 + i*s3
 }
 
 // 16-point DFT, 4x4 Cooley-Tukey in registers.  Input x[j] natural order; output X[q] is left at
 // position POS16(q) = 4*(q&3) + (q>>2).
 #define POS16(q) (4 * ((q)&3) + ((q) >> 2))
-__device__ __forceinline__ void fft16(float2 (&x)[16]) {
-  constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, R = 0.70710678118654752f;
+__device__ __forceinline__ void fft16(cplx (&x)[16]) {
+  constexpr double C1 = 0.92387953251128675613, S1 = 0.38268343236508977173, R = 0.70710678118654752440;
 #pragma unroll
   for (int j0 = 0; j0 < 4; ++j0) dft4(x[j0], x[4 + j0], x[8 + j0], x[12 + j0]);
   // A[j0][q0] now sits at x[4*q0 + j0]; multiply by W16^(j0*q0)
-  x[4 * 1 + 1] = cmul(x[4 * 1 + 1], make_float2(C1, -S1));  // W^1
-  x[4 * 2 + 1] = cmul(x[4 * 2 + 1], make_float2(R, -R));    // W^2
-  x[4 * 3 + 1] = cmul(x[4 * 3 + 1], make_float2(S1, -C1));  // W^3
-  x[4 * 1 + 2] = cmul(x[4 * 1 + 2], make_float2(R, -R));    // W^2
-  x[4 * 2 + 2] = make_float2(x[4 * 2 + 2].y, -x[4 * 2 + 2].x);  // W^4 = -i
-  x[4 * 3 + 2] = cmul(x[4 * 3 + 2], make_float2(-R, -R));   // W^6
-  x[4 * 1 + 3] = cmul(x[4 * 1 + 3], make_float2(S1, -C1));  // W^3
-  x[4 * 2 + 3] = cmul(x[4 * 2 + 3], make_float2(-R, -R));   // W^6
-  x[4 * 3 + 3] = cmul(x[4 * 3 + 3], make_float2(-C1, S1));  // W^9
+  x[4 * 1 + 1] = cmul(x[4 * 1 + 1], mk(C1, -S1));  // W^1
+  x[4 * 2 + 1] = mk(R * (x[4 * 2 + 1].x + x[4 * 2 + 1].y), R * (x[4 * 2 + 1].y - x[4 * 2 + 1].x));  // W^2 = R(1 - i)
+  x[4 * 3 + 1] = cmul(x[4 * 3 + 1], mk(S1, -C1));  // W^3
+  x[4 * 1 + 2] = mk(R * (x[4 * 1 + 2].x + x[4 * 1 + 2].y), R * (x[4 * 1 + 2].y - x[4 * 1 + 2].x));  // W^2
+  x[4 * 2 + 2] = mk(x[4 * 2 + 2].y, -x[4 * 2 + 2].x);                                               // W^4 = -i
+  x[4 * 3 + 2] = mk(R * (x[4 * 3 + 2].y - x[4 * 3 + 2].x), -R * (x[4 * 3 + 2].x + x[4 * 3 + 2].y));  // W^6 = -R(1 + i)
+  x[4 * 1 + 3] = cmul(x[4 * 1 + 3], mk(S1, -C1));  // W^3
+  x[4 * 2 + 3] = mk(R * (x[4 * 2 + 3].y - x[4 * 2 + 3].x), -R * (x[4 * 2 + 3].x + x[4 * 2 + 3].y));  // W^6
+  x[4 * 3 + 3] = cmul(x[4 * 3 + 3], mk(-C1, S1));  // W^9
 #pragma unroll
   for (int q0 = 0; q0 < 4; ++q0) dft4(x[4 * q0 + 0], x[4 * q0 + 1], x[4 * q0 + 2], x[4 * q0 + 3]);
 }
@@ -141,7 +149,8 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     const float* src = wav + w0 + static_cast<int64_t>(f_lo) * SHIFT;
     for (int i = tid; i < nS; i += THREADS) s.samples[i] = __ldg(src + i) * upscale;
     for (int i = tid; i < FRAME_LEN; i += THREADS) s.window[i] = __ldg(&tab->window[i]);
-    for (int i = tid; i < 136; i += THREADS) s.tw512[i] = __ldg(&tab->tw512[i]);
+    for (int i = tid; i < 130; i += THREADS) s.tw512[i] = tab->tw512[i];
+    for (int i = tid; i < 256; i += THREADS) (&s.tw256[0][0])[i] = (&tab->tw256[0][0])[i];
     for (int i = tid; i < MAX_TAPS; i += THREADS) s.mel_w[i] = __ldg(&tab->mel_w[i]);
     for (int i = tid; i < NMEL; i += THREADS) {
       s.mel_start[i] = __ldg(&tab->mel_start[i]);
@@ -149,15 +158,12 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
       s.mel_woff[i] = __ldg(&tab->mel_woff[i]);
     }
   }
-  // inter-pass twiddles W256^(hl*q): fixed per lane for the whole kernel
-  float2 tw[16];
-#pragma unroll
-  for (int q = 1; q < 16; ++q) tw[q] = __ldg(&tab->tw256[(hl * q) & 255]);
   __syncthreads();
 
   const int slot = warp * 2 + (lane >> 4);
-  float2* work = s.work[slot];
+  double* work = s.work[slot];
   float* power = s.power[slot];
+  const int partner = (16 - hl) & 15;  // lane holding Z[256 - k] for this lane's k = hl + 16 p
 
   for (int fb = warp * 2; fb < nF; fb += SLOTS) {
     const int f_raw = fb + (lane >> 4);
@@ -166,62 +172,81 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     const float* xs = s.samples + f * SHIFT;
 
     // ---- load 13 sample pairs (complex point n = hl + 16 j  <->  samples 2n, 2n+1), frame mean
-    float2 x[16];
-    float part = 0.f;
+    float2 xf[13];
+    double part = 0.0;
 #pragma unroll
     for (int j = 0; j < 13; ++j) {
       const int sidx = 2 * hl + 32 * j;
       float2 v = make_float2(0.f, 0.f);
       if (j < 12 || hl < 8) v = *reinterpret_cast<const float2*>(xs + sidx);
-      x[j] = v;
-      part += v.x + v.y;
+      xf[j] = v;
+      part += static_cast<double>(v.x) + static_cast<double>(v.y);
     }
 #pragma unroll
     for (int o = 8; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-    const float mean = part / static_cast<float>(FRAME_LEN);  // TA:183-186
+    const float mean = static_cast<float>(part / static_cast<double>(FRAME_LEN));  // TA:183-186, correctly rounded
 
-    // ---- DC removal, pre-emphasis (replicate-left, TA:193-198), window (TA:201-204)
+    // ---- DC removal, pre-emphasis (replicate-left, TA:193-198), window (TA:201-204): the reference's fp32 operation
+    // sequence, one rounding per torch op (no FMA contraction), so the frames entering the FFT carry the same bits.
+    cplx x[16];
 #pragma unroll
     for (int j = 0; j < 13; ++j) {
       const int sidx = 2 * hl + 32 * j;
       if (j < 12 || hl < 8) {
         const float rp = xs[sidx > 0 ? sidx - 1 : 0];
-        const float a0 = x[j].x - mean, a1 = x[j].y - mean, ap = rp - mean;
-        const float y0 = a0 - preemph * ap;
-        const float y1 = a1 - preemph * a0;
-        x[j] = make_float2(y0 * s.window[sidx], y1 * s.window[sidx + 1]);
+        const float a0 = __fsub_rn(xf[j].x, mean), a1 = __fsub_rn(xf[j].y, mean), ap = __fsub_rn(rp, mean);
+        const float y0 = __fsub_rn(a0, __fmul_rn(preemph, ap));
+        const float y1 = __fsub_rn(a1, __fmul_rn(preemph, a0));
+        x[j] = mk(static_cast<double>(__fmul_rn(y0, s.window[sidx])), static_cast<double>(__fmul_rn(y1, s.window[sidx + 1])));
+      } else {
+        x[j] = mk(0.0, 0.0);
       }
     }
-    x[13] = x[14] = x[15] = make_float2(0.f, 0.f);  // zero padding 400 -> 512 (TA:207-211)
+    x[13] = x[14] = x[15] = mk(0.0, 0.0);  // zero padding 400 -> 512 (TA:207-211)
 
-    // ---- pass 1: DFT16 over j, twiddle W256^(t q), transpose through smem
+    // ---- pass 1: DFT16 over j, twiddle W256^(t q), transpose through smem (real parts, then imaginary parts)
     fft16(x);
-    work[0 * 17 + hl] = x[POS16(0)];
 #pragma unroll
-    for (int q = 1; q < 16; ++q) work[q * 17 + hl] = cmul(x[POS16(q)], tw[q]);
-    __syncwarp();
+    for (int q = 1; q < 16; ++q) x[POS16(q)] = cmul(x[POS16(q)], s.tw256[q][hl]);
+    {
+      double im[16];
 #pragma unroll
-    for (int t = 0; t < 16; ++t) x[t] = work[hl * 17 + t];
-    // ---- pass 2: DFT16 over t -> Z[hl + 16 p]
+      for (int q = 0; q < 16; ++q) {
+        work[q * 17 + hl] = x[POS16(q)].x;
+        im[q] = x[POS16(q)].y;
+      }
+      __syncwarp();
+#pragma unroll
+      for (int t = 0; t < 16; ++t) x[t].x = work[hl * 17 + t];
+      __syncwarp();
+#pragma unroll
+      for (int q = 0; q < 16; ++q) work[q * 17 + hl] = im[q];
+      __syncwarp();
+#pragma unroll
+      for (int t = 0; t < 16; ++t) x[t].y = work[hl * 17 + t];
+      __syncwarp();
+    }
+    // ---- pass 2: DFT16 over t -> Z[hl + 16 p] at x[POS16(p)]
     fft16(x);
-    __syncwarp();
-#pragma unroll
-    for (int p = 0; p < 16; ++p) work[16 * p + hl] = x[POS16(p)];
-    __syncwarp();
 
-    // ---- split the packed real FFT:  X[k] = Xe + W512^k Xo,  X[256-k] = conj(Xe - W512^k Xo)
+    // ---- split the packed real FFT:  X[k] = Xe + W512^k Xo,  X[256-k] = conj(Xe - W512^k Xo),  k = hl + 16 p.
+    // Z[256 - k] = Z[(16 - hl) + 16 (15 - p)] lives in lane (16 - hl) & 15 at p' = 15 - p; for hl == 0 it is this
+    // lane's own Z[16 ((16 - p) & 15)].
 #pragma unroll
-    for (int i = 0; i < 9; ++i) {
-      const int k = hl + 16 * i;
+    for (int p = 0; p < 9; ++p) {
+      const cplx own = x[POS16((16 - p) & 15)];
+      const cplx snd = x[POS16(15 - (p & 7))];  // p == 8 is only used by hl == 0 (k = 128), which reads `own`
+      cplx zm = mk(__shfl_sync(0xffffffffu, snd.x, partner, 16), __shfl_sync(0xffffffffu, snd.y, partner, 16));
+      if (hl == 0) zm = own;
+      const int k = hl + 16 * p;
       if (k <= 128) {
-        const float2 zk = work[k];
-        const float2 zm = work[(256 - k) & 255];
-        const float2 xe = make_float2(0.5f * (zk.x + zm.x), 0.5f * (zk.y - zm.y));
-        const float2 xo = make_float2(0.5f * (zk.y + zm.y), -0.5f * (zk.x - zm.x));
-        const float2 t = cmul(xo, s.tw512[k]);
-        const float ar = xe.x + t.x, ai = xe.y + t.y, br = xe.x - t.x, bi = xe.y - t.y;
-        power[k] = ar * ar + ai * ai;        // TA:616-618 |rfft|^2
-        power[256 - k] = br * br + bi * bi;
+        const cplx zk = x[POS16(p & 15)];
+        const cplx xe = mk(0.5 * (zk.x + zm.x), 0.5 * (zk.y - zm.y));
+        const cplx xo = mk(0.5 * (zk.y + zm.y), -0.5 * (zk.x - zm.x));
+        const cplx t = cmul(xo, s.tw512[k]);
+        const double ar = xe.x + t.x, ai = xe.y + t.y, br = xe.x - t.x, bi = xe.y - t.y;
+        power[k] = static_cast<float>(ar * ar + ai * ai);  // TA:616-618 |rfft|^2
+        power[256 - k] = static_cast<float>(br * br + bi * bi);
       }
     }
     __syncwarp();
@@ -295,10 +320,9 @@ extern "C" int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float*
   std::memset(t, 0, sizeof(Tables));
   for (int i = 0; i < FRAME_LEN; ++i) t->window[i] = window[i];
   const double two_pi = 6.283185307179586476925286766559;
-  for (int k = 0; k < 256; ++k)
-    t->tw256[k] = make_float2(static_cast<float>(cos(two_pi * k / 256.0)), static_cast<float>(-sin(two_pi * k / 256.0)));
-  for (int k = 0; k <= 128; ++k)
-    t->tw512[k] = make_float2(static_cast<float>(cos(two_pi * k / 512.0)), static_cast<float>(-sin(two_pi * k / 512.0)));
+  for (int q = 0; q < 16; ++q)
+    for (int l = 0; l < 16; ++l) t->tw256[q][l] = make_double2(cos(two_pi * (q * l) / 256.0), -sin(two_pi * (q * l) / 256.0));
+  for (int k = 0; k <= 128; ++k) t->tw512[k] = make_double2(cos(two_pi * k / 512.0), -sin(two_pi * k / 512.0));
   int off = 0;
   for (int b = 0; b < NMEL; ++b) {
     const float* row = mel_banks + static_cast<size_t>(b) * NBIN;

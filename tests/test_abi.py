@@ -74,9 +74,15 @@ def test_tables_blob_is_sparse_mel(frontend_golden):
     _lib.check(lib.fa_frontend_tables_build(C.byref(cfg), win.ctypes.data, mel.ctypes.data, blob.ctypes.data))
     f = blob.view(np.float32)
     np.testing.assert_array_equal(f[:400], win)
-    tw256 = f[400:400 + 512].reshape(256, 2)
-    np.testing.assert_allclose(tw256[:, 0], np.cos(2 * np.pi * np.arange(256) / 256), atol=1e-7)
-    np.testing.assert_allclose(tw256[:, 1], -np.sin(2 * np.pi * np.arange(256) / 256), atol=1e-7)
+    # fp64 twiddles: tw256[q][t] = W256^(t q) (16 x 16 double2), then W512^k for k = 0..128
+    d = blob[1600:1600 + 16 * 16 * 16 + 129 * 16].view(np.float64)
+    tw256 = d[:512].reshape(16, 16, 2)
+    ang = 2 * np.pi * np.outer(np.arange(16), np.arange(16)) / 256
+    np.testing.assert_allclose(tw256[..., 0], np.cos(ang), atol=1e-15)
+    np.testing.assert_allclose(tw256[..., 1], -np.sin(ang), atol=1e-15)
+    tw512 = d[512:].reshape(129, 2)
+    np.testing.assert_allclose(tw512[:, 0], np.cos(2 * np.pi * np.arange(129) / 512), atol=1e-15)
+    np.testing.assert_allclose(tw512[:, 1], -np.sin(2 * np.pi * np.arange(129) / 512), atol=1e-15)
     bad = _lib.FrontendCfg(16000, 320, 160, 512, 80, 7, 6, 0.97, 32768.0, FLT_EPS)
     assert lib.fa_frontend_tables_build(C.byref(bad), win.ctypes.data, mel.ctypes.data, blob.ctypes.data) != 0
     assert b"not the compiled one" in lib.fa_last_error()

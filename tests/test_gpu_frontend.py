@@ -82,7 +82,7 @@ def test_config1_10s(frontend_golden, win):
     np.testing.assert_allclose(got.astype(np.float64).sum(0), g[f"cfg1_{win}_colsum"], atol=2e-2)
 
 
-def test_packed_varlen_batch_vs_oracle():
+def test_packed_varlen_batch_vs_oracle(frontend_golden):
     """config 3 shape: 64 utterances of 1-30 s, packed offsets; every row against the oracle."""
     from funasr_b200 import pack_waveforms
     from oracle import frontend as of
@@ -97,20 +97,23 @@ def test_packed_varlen_batch_vs_oracle():
     wav, starts = pack_waveforms(wavs, "cuda")
     got, cu = fe.forward_packed(wav, starts, lens)
     got = got.cpu().numpy()
-    # Two fp32 implementations each sit up to ~7e-4 from the fp64 truth in the lowest mel bins on 30 s inputs (torchaudio
-    # fp32 vs this oracle fp32: 7.6e-4 on utterance 3), so the bound is stated against the fp64 truth, SURVEY.md §8c (8):
-    # err(kernel, fp64) <= max(1e-3, 1.5 * err(fp32 oracle, fp64)), in the log-mel domain (CMVN scale divided out).
+    # Oracle on the reference's own fp32 tables (torch's fp32 window is up to 2.3e-7 off the exact one, worth ~1e-3 in the
+    # lowest log-mel bins of a 30 s full-scale input; numpy cannot reproduce its last bits, see oracle.frontend.fbank).
+    # Two fp32 implementations each sit up to ~7e-4 from the fp64 truth there, so the bound is also stated against the
+    # fp64 truth, SURVEY.md §8c (8): err(kernel, fp64) <= max(1e-3, 1.5 * err(fp32 oracle, fp64)), in the log-mel
+    # domain (CMVN scale divided out).
+    tables = {"window": frontend_golden["window_hamming"], "mel": frontend_golden["mel_banks"]}
     for b in [0, 1, 2, 3, 10, 33, 63]:
         w = [wavs[b].numpy()]
-        want32, _ = of.wav_frontend_packed(w, "hamming", cm)
-        want64, _ = of.wav_frontend_packed(w, "hamming", cm.astype(np.float64), dtype=np.float64)
+        want32, _ = of.wav_frontend_packed(w, "hamming", cm, tables=tables)
+        want64, _ = of.wav_frontend_packed(w, "hamming", cm.astype(np.float64), dtype=np.float64, tables=tables)
         assert cu[b + 1] - cu[b] == want32.shape[0]
         e_ref = (np.abs(want32 - want64) / cm[1]).max()
         e_got = (np.abs(got[cu[b]:cu[b + 1]] - want64) / cm[1]).max()
         e_32 = (np.abs(got[cu[b]:cu[b + 1]] - want32) / cm[1]).max()
         print(f"utt {b} ({lens[b]} samples): oracle32 vs f64 {e_ref:.2e}; kernel vs f64 {e_got:.2e}; kernel vs oracle32 {e_32:.2e}")
         assert e_got <= max(TOL, 1.5 * e_ref) + 2e-6, b  # 2e-6: fp32 rounding of the CMVN'd output itself
-        assert e_32 <= 2 * TOL, b
+        assert e_32 <= TOL, b
     # size-independent property: each LFR row is 7 stacked fbank frames -> slot j of row i equals slot j-6.. of row i+1
     raw = got / cm[1] - cm[0]
     for b in (3, 40):
