@@ -1,6 +1,7 @@
 // C-ABI orchestration: error state, device check, the encoder/adaptor plan (workspace carve-up +
 // TMA descriptors built once) and the layer schedule.  No device allocation, no synchronisation.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <new>
@@ -169,9 +170,10 @@ int check_model_cfg(const fa_model_cfg* c) {
   return 0;
 }
 
-// per-call arguments of a program
+// per-call arguments of a program: one SLAB = rows [row0, row0 + M) of every workspace matrix, holding the n_utts
+// utterances cu[0..n_utts] (cu already points at the slab's first utterance and keeps absolute row numbers).
 struct RunArgs {
-  int M, n_utts, max_len;
+  int M, n_utts, max_len, row0;
   const int32_t* cu;
   cudaStream_t s;
 };
@@ -215,7 +217,11 @@ int run_gemm_op(const GemmOp& op, const RunArgs& a) {
   const int bn = gemm_block_n(a.M, op.N);
   const int idx = bn == 64 ? 0 : (bn == 128 ? 1 : 2);
   FA_REQUIRE(bn != 0 && op.tb_ok[idx], "gemm N=%d unsupported", op.N);
-  return launch_gemm(op.ta, op.tb[idx], op.tc, bn, a.M, op.N, op.K, op.epi, op.c, op.ldc, a.s);
+  GemmEpilogue e = op.epi;
+  const int64_t off = static_cast<int64_t>(a.row0) * op.ldc;
+  if (e.res1) e.res1 += off;
+  if (e.res2) e.res2 += off;
+  return launch_gemm(op.ta, op.tb[idx], op.tc, bn, a.M, op.N, op.K, e, op.c, op.ldc, a.row0, a.s);
 }
 
 }  // namespace
@@ -224,6 +230,7 @@ struct fa_plan {
   fa_model_cfg cfg;
   fa_model_w w;
   int cap;
+  int chunk_tokens;  // 0: never split a batch
   Workspace ws;
   std::vector<Step> enc_prog, ad_prog;
 };
@@ -242,7 +249,16 @@ struct Builder {
   }
   void ln(std::vector<Step>& prog, const float* x, const float* g, const float* b, const float* g2, const float* b2,
           __nv_bfloat16* y_bf16, float* y_f32, int D) {
-    prog.push_back([=](const RunArgs& r) { return launch_layernorm(x, g, b, g2, b2, y_bf16, y_f32, r.M, D, r.s); });
+    prog.push_back([=](const RunArgs& r) {
+      const int64_t o = static_cast<int64_t>(r.row0) * D;
+      return launch_layernorm(x + o, g, b, g2, b2, y_bf16 ? y_bf16 + o : nullptr, y_f32 ? y_f32 + o : nullptr, r.M, D, r.s);
+    });
+  }
+  void attention(std::vector<Step>& prog, const __nv_bfloat16* qkv, __nv_bfloat16* ctx, int H, int D) {
+    prog.push_back([=](const RunArgs& r) {
+      return launch_attention(qkv + static_cast<int64_t>(r.row0) * 3 * D, 3 * D, r.cu, r.n_utts, r.row0, r.max_len, H,
+                              ctx + static_cast<int64_t>(r.row0) * D, D, r.M, r.s);
+    });
   }
 };
 
@@ -254,7 +270,7 @@ int build_programs(fa_plan* p) {
   const int d = c.d_model;
   const int nl = c.n_blocks + c.n_tp_blocks;
   const int left = (c.fsmn_kernel - 1) / 2 + (c.sanm_shift > 0 ? c.sanm_shift : 0);  // VM:175-179
-  // ---------------- encoder: the embed+LN input stage is issued by fa_encoder_forward (it needs the caller's feats)
+  // ---------------- encoder: the embed+LN input stage is issued by run_encoder (it needs the caller's feats)
   float* x = ws.x;    // current residual stream
   float* xo = ws.x2;  // next
   std::vector<Step>& E = p->enc_prog;
@@ -270,15 +286,13 @@ int build_programs(fa_plan* p) {
       const float* fw = L.fsmn_w;
       float* mem = ws.mem;
       const int K = c.fsmn_kernel;
-      E.push_back([=](const RunArgs& r) { return launch_fsmn(qkv, 3 * d, 2 * d, fw, r.cu, r.n_utts, mem, r.M, d, K, left, r.s); });
+      E.push_back([=](const RunArgs& r) {
+        return launch_fsmn(qkv + static_cast<int64_t>(r.row0) * 3 * d, 3 * d, 2 * d, fw, r.cu, r.n_utts, r.row0,
+                           mem + static_cast<int64_t>(r.row0) * d, r.M, d, K, left, r.s);
+      });
     }
     // masked MHA                                                           VM:250-252,222-236
-    {
-      const __nv_bfloat16* qkv = ws.qkv;
-      __nv_bfloat16* ctx = ws.ctx;
-      const int H = c.n_heads;
-      E.push_back([=](const RunArgs& r) { return launch_attention(qkv, 3 * d, r.cu, r.n_utts, r.max_len, H, ctx, d, r.M, r.s); });
-    }
+    B.attention(E, ws.qkv, ws.ctx, c.n_heads, d);
     // x' = [x +] ctx Wo^T + b + mem    (no residual when in_size != size)   VM:238,253,123-136
     B.gemm(E, ws.ctx, d, L.out_w, d, d, L.out_b, xo, true, false, ws.mem, (i == 0) ? nullptr : x);
     // LN2, FFN                                                              VM:138-140,412-431
@@ -318,12 +332,7 @@ int build_programs(fa_plan* p) {
       // pre-LN MHA block                                                       VM:434-455
       B.ln(A, ax, L.ln1_g, L.ln1_b, nullptr, nullptr, ws.axn, nullptr, D);
       B.gemm(A, ws.axn, D, L.qkv_w, 3 * D, D, L.qkv_b, ws.aqkv, false);
-      {
-        const __nv_bfloat16* qkv = ws.aqkv;
-        __nv_bfloat16* ctx = ws.actx;
-        const int H = c.ad_heads;
-        A.push_back([=](const RunArgs& r) { return launch_attention(qkv, 3 * D, r.cu, r.n_utts, r.max_len, H, ctx, D, r.M, r.s); });
-      }
+      B.attention(A, ws.aqkv, ws.actx, c.ad_heads, D);
       B.gemm(A, ws.actx, D, L.out_w, D, D, L.out_b, axo, true, false, ax);
       B.ln(A, axo, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.axn, nullptr, D);
       B.gemm(A, ws.axn, D, L.ffn1_w, c.ad_ff, D, L.ffn1_b, ws.ah, false, true);
@@ -331,6 +340,14 @@ int build_programs(fa_plan* p) {
     }
   }
   return B.rc;
+}
+
+int default_chunk_tokens() {
+  // Measured on B200 (profiles/r01_b_slab_sweep.md): with ~580 dependent launches per slab, every extra slab costs ~5 ms
+  // of per-kernel ramp-up/drain, more than the L2 residency it buys (cfg5: 59.9 ms unsplit, 90.5 ms at 8704-row slabs).
+  // The schedule is therefore OFF by default; FA_CHUNK_TOKENS=<n> or fa_plan_set_chunk_tokens turn it on.
+  if (const char* e = getenv("FA_CHUNK_TOKENS")) return atoi(e);
+  return 0;
 }
 
 }  // namespace
@@ -358,6 +375,7 @@ extern "C" int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void
   p->cfg = *cfg;
   p->w = *w;
   p->cap = cap;
+  p->chunk_tokens = default_chunk_tokens();
   p->ws = ws;
   if (int rc = build_programs(p)) {
     delete p;
@@ -369,7 +387,15 @@ extern "C" int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void
 
 extern "C" void fa_plan_destroy(fa_plan* plan) { delete plan; }
 
-static int check_batch(const fa_plan* p, const int32_t* cu, int n_utts, int n_tokens, int max_len) {
+extern "C" int fa_plan_set_chunk_tokens(fa_plan* plan, int32_t chunk_tokens) {
+  FA_REQUIRE(plan != nullptr && chunk_tokens >= 0, "set_chunk_tokens: bad arguments");
+  plan->chunk_tokens = chunk_tokens;
+  return 0;
+}
+
+namespace {
+
+int check_batch(const fa_plan* p, const int32_t* cu, int n_utts, int n_tokens, int max_len) {
   FA_REQUIRE(p != nullptr, "NULL plan");
   FA_REQUIRE(cu != nullptr && n_utts > 0, "empty batch");
   FA_REQUIRE(n_tokens > 0 && n_tokens <= p->cap, "n_tokens %d exceeds the plan capacity %d", n_tokens, p->cap);
@@ -377,50 +403,127 @@ static int check_batch(const fa_plan* p, const int32_t* cu, int n_utts, int n_to
   return 0;
 }
 
-static int check_tmax(int tmax, int max_len, const char* what) {
+int check_tmax(int tmax, int max_len, const char* what) {
   FA_REQUIRE(tmax == 0 || tmax >= max_len, "%s: padded row count %d is smaller than the longest utterance %d", what, tmax, max_len);
   return 0;
 }
 
-extern "C" int fa_encoder_forward(fa_plan* p, const float* feats, int32_t feats_tmax, const int32_t* cu, int32_t n_utts,
-                                  int32_t M, int32_t max_len, float* enc_out, int32_t enc_out_tmax, fa_stream_t stream) {
+// A slab of consecutive utterances [b0, b1) = packed rows [row0, row0 + M).
+struct Slab { int b0, b1, row0, M, max_len; };
+
+// Split the batch into slabs of about plan->chunk_tokens rows on utterance boundaries (utterances are independent, so any
+// split computes the same rows).  Needs the HOST copy of cu_seqlens; without it (or with chunking off) the batch is one slab.
+int make_slabs(const fa_plan* p, const int32_t* cu_host, int n_utts, int M, int max_len, std::vector<Slab>* out) {
+  out->clear();
+  if (cu_host == nullptr || p->chunk_tokens <= 0 || M <= p->chunk_tokens + p->chunk_tokens / 4) {
+    out->push_back(Slab{0, n_utts, 0, M, max_len});
+    return 0;
+  }
+  FA_REQUIRE(cu_host[0] == 0 && cu_host[n_utts] == M, "cu_seqlens_host does not describe %d rows", M);
+  const int n_slabs = (M + p->chunk_tokens - 1) / p->chunk_tokens;
+  int b = 0;
+  for (int i = 0; i < n_slabs && b < n_utts; ++i) {
+    const int64_t want_end = static_cast<int64_t>(M) * (i + 1) / n_slabs;  // even split, snapped to an utterance boundary
+    int e = b + 1;
+    while (e < n_utts && (i == n_slabs - 1 || cu_host[e + 1] - want_end <= want_end - cu_host[e])) ++e;
+    if (i == n_slabs - 1) e = n_utts;
+    int ml = 0;
+    for (int u = b; u < e; ++u) {
+      const int len = cu_host[u + 1] - cu_host[u];
+      FA_REQUIRE(len > 0, "utterance %d has %d rows", u, len);
+      ml = len > ml ? len : ml;
+    }
+    out->push_back(Slab{b, e, cu_host[b], cu_host[e] - cu_host[b], ml});
+    b = e;
+  }
+  return 0;
+}
+
+int run_encoder(fa_plan* p, const Slab& sl, const float* feats, int feats_tmax, const int32_t* cu, float* enc_out,
+                int enc_out_tmax, cudaStream_t s) {
+  const fa_model_cfg& c = p->cfg;
+  const RunArgs a{sl.M, sl.b1 - sl.b0, sl.max_len, sl.row0, cu + sl.b0, s};
+  const float* f = feats + (feats_tmax > 0 ? static_cast<int64_t>(sl.b0) * feats_tmax : static_cast<int64_t>(sl.row0)) * c.d_in;
+  // input stage: xs*sqrt(d) + PE, then norm1 of encoders0 (VM:388-390, :121)
+  if (int rc = launch_embed_layernorm(f, feats_tmax, p->w.pe_inv_timescales, a.cu, a.n_utts, a.row0, sqrtf(static_cast<float>(c.d_model)),
+                                      p->w.layers[0].ln1_g, p->w.layers[0].ln1_b, p->ws.xn0 + static_cast<int64_t>(a.row0) * c.d_in,
+                                      a.M, c.d_in, s))
+    return rc;
+  for (const Step& st : p->enc_prog)
+    if (int rc = st(a)) return rc;
+  if (enc_out) {
+    float* dst = enc_out + (enc_out_tmax > 0 ? static_cast<int64_t>(sl.b0) * enc_out_tmax : static_cast<int64_t>(sl.row0)) * c.d_model;
+    return launch_repack_rows(p->ws.enc_f32 + static_cast<int64_t>(a.row0) * c.d_model, 0, dst, enc_out_tmax, 0, a.cu, a.n_utts,
+                              a.row0, a.M, c.d_model, s);
+  }
+  return 0;
+}
+
+int run_adaptor(fa_plan* p, const Slab& sl, const float* enc, int enc_tmax, const int32_t* cu, void* out, int out_tmax,
+                int out_bf16, cudaStream_t s) {
+  const fa_model_cfg& c = p->cfg;
+  const RunArgs a{sl.M, sl.b1 - sl.b0, sl.max_len, sl.row0, cu + sl.b0, s};
+  if (enc) {
+    const float* src = enc + (enc_tmax > 0 ? static_cast<int64_t>(sl.b0) * enc_tmax : static_cast<int64_t>(sl.row0)) * c.d_model;
+    if (int rc = launch_repack_rows(src, enc_tmax, p->ws.enc_bf + static_cast<int64_t>(a.row0) * c.d_model, 0, 1, a.cu, a.n_utts,
+                                    a.row0, a.M, c.d_model, s))
+      return rc;
+  }
+  for (const Step& st : p->ad_prog)
+    if (int rc = st(a)) return rc;
+  const int64_t dst_row = out_tmax > 0 ? static_cast<int64_t>(sl.b0) * out_tmax : static_cast<int64_t>(sl.row0);
+  void* dst = static_cast<unsigned char*>(out) + dst_row * c.ad_dim * (out_bf16 ? 2 : 4);
+  return launch_repack_rows(p->ws.ax + static_cast<int64_t>(a.row0) * c.ad_dim, 0, dst, out_tmax, out_bf16, a.cu, a.n_utts, a.row0,
+                            a.M, c.ad_dim, s);
+}
+
+}  // namespace
+
+extern "C" int fa_encoder_forward(fa_plan* p, const float* feats, int32_t feats_tmax, const int32_t* cu,
+                                  const int32_t* cu_host, int32_t n_utts, int32_t M, int32_t max_len, float* enc_out,
+                                  int32_t enc_out_tmax, fa_stream_t stream) {
   if (int r = check_batch(p, cu, n_utts, M, max_len)) return r;
   FA_REQUIRE(feats != nullptr, "NULL feats");
   FA_REQUIRE(p->cfg.n_blocks > 0, "plan was created without encoder weights");
   if (int r = check_tmax(feats_tmax, max_len, "feats")) return r;
   if (int r = check_tmax(enc_out_tmax, max_len, "enc_out")) return r;
-  const RunArgs a{M, n_utts, max_len, cu, static_cast<cudaStream_t>(stream)};
-  const fa_model_cfg& c = p->cfg;
-  // input stage: xs*sqrt(d) + PE, then norm1 of encoders0 (VM:388-390, :121)
-  if (int rc = launch_embed_layernorm(feats, feats_tmax, p->w.pe_inv_timescales, cu, n_utts, sqrtf(static_cast<float>(c.d_model)),
-                                      p->w.layers[0].ln1_g, p->w.layers[0].ln1_b, p->ws.xn0, M, c.d_in, a.s))
-    return rc;
-  for (const Step& st : p->enc_prog)
-    if (int rc = st(a)) return rc;
-  if (enc_out) return launch_repack_rows(p->ws.enc_f32, 0, enc_out, enc_out_tmax, 0, cu, n_utts, M, c.d_model, a.s);
+  std::vector<Slab> slabs;
+  if (int r = make_slabs(p, cu_host, n_utts, M, max_len, &slabs)) return r;
+  for (const Slab& sl : slabs)
+    if (int rc = run_encoder(p, sl, feats, feats_tmax, cu, enc_out, enc_out_tmax, static_cast<cudaStream_t>(stream))) return rc;
   return 0;
 }
 
-extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, int32_t enc_tmax, const int32_t* cu, int32_t n_utts,
-                                  int32_t M, int32_t max_len, void* out, int32_t out_tmax, int32_t out_bf16,
+extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, int32_t enc_tmax, const int32_t* cu, const int32_t* cu_host,
+                                  int32_t n_utts, int32_t M, int32_t max_len, void* out, int32_t out_tmax, int32_t out_bf16,
                                   fa_stream_t stream) {
   if (int r = check_batch(p, cu, n_utts, M, max_len)) return r;
   if (int r = check_tmax(enc_tmax, max_len, "enc")) return r;
   if (int r = check_tmax(out_tmax, max_len, "out")) return r;
   FA_REQUIRE(out != nullptr, "NULL out");
   FA_REQUIRE(p->w.lin1_w != nullptr, "plan was created without adaptor weights");
-  const RunArgs a{M, n_utts, max_len, cu, static_cast<cudaStream_t>(stream)};
-  const fa_model_cfg& c = p->cfg;
-  if (enc)
-    if (int rc = launch_repack_rows(enc, enc_tmax, p->ws.enc_bf, 0, 1, cu, n_utts, M, c.d_model, a.s)) return rc;
-  for (const Step& st : p->ad_prog)
-    if (int rc = st(a)) return rc;
-  return launch_repack_rows(p->ws.ax, 0, out, out_tmax, out_bf16, cu, n_utts, M, c.ad_dim, a.s);
+  std::vector<Slab> slabs;
+  if (int r = make_slabs(p, cu_host, n_utts, M, max_len, &slabs)) return r;
+  for (const Slab& sl : slabs)
+    if (int rc = run_adaptor(p, sl, enc, enc_tmax, cu, out, out_tmax, out_bf16, static_cast<cudaStream_t>(stream))) return rc;
+  return 0;
 }
 
-extern "C" int fa_encode_adapt(fa_plan* p, const float* feats, int32_t feats_tmax, const int32_t* cu, int32_t n_utts,
-                               int32_t M, int32_t max_len, float* enc_out, int32_t enc_out_tmax, void* out,
+extern "C" int fa_encode_adapt(fa_plan* p, const float* feats, int32_t feats_tmax, const int32_t* cu, const int32_t* cu_host,
+                               int32_t n_utts, int32_t M, int32_t max_len, float* enc_out, int32_t enc_out_tmax, void* out,
                                int32_t out_tmax, int32_t out_bf16, fa_stream_t stream) {
-  if (int r = fa_encoder_forward(p, feats, feats_tmax, cu, n_utts, M, max_len, enc_out, enc_out_tmax, stream)) return r;
-  return fa_adaptor_forward(p, nullptr, 0, cu, n_utts, M, max_len, out, out_tmax, out_bf16, stream);
+  if (int r = check_batch(p, cu, n_utts, M, max_len)) return r;
+  FA_REQUIRE(feats != nullptr && out != nullptr, "NULL feats / out");
+  FA_REQUIRE(p->cfg.n_blocks > 0 && p->w.lin1_w != nullptr, "plan needs both encoder and adaptor weights");
+  if (int r = check_tmax(feats_tmax, max_len, "feats")) return r;
+  if (int r = check_tmax(enc_out_tmax, max_len, "enc_out")) return r;
+  if (int r = check_tmax(out_tmax, max_len, "out")) return r;
+  std::vector<Slab> slabs;
+  if (int r = make_slabs(p, cu_host, n_utts, M, max_len, &slabs)) return r;
+  const cudaStream_t s = static_cast<cudaStream_t>(stream);
+  for (const Slab& sl : slabs) {  // slab-major: a slab's encoder output is still in L2 when its adaptor runs
+    if (int rc = run_encoder(p, sl, feats, feats_tmax, cu, enc_out, enc_out_tmax, s)) return rc;
+    if (int rc = run_adaptor(p, sl, nullptr, 0, cu, out, out_tmax, out_bf16, s)) return rc;
+  }
+  return 0;
 }

@@ -3,17 +3,18 @@
 //   reference's key-masked padded attention on valid rows
 //   (VLLM/model_executor/models/funasr.py:222-235,250-252; adaptor :506-512).
 //
-// One CTA = (utterance b, head h, 128 query rows).  Keys/values stream through shared memory in blocks of 128
-// (TMA, 128B swizzle); per block
-//     S  = Q K_j^T          tcgen05.mma, A = Q (smem, K-major), B = K_j (smem, K-major), D in TMEM
-//     P  = exp2(S c - m)    softmax warps: thread = row, TMEM -> registers (one pass) -> bf16 -> swizzled smem in the
+// One CTA = (utterance b, head h, 128 query rows).  Keys/values stream through a 2-stage shared-memory ring in blocks of
+// 64 keys (TMA, 128B swizzle); per block j
+//     S_j = Q K_j^T         tcgen05.mma, A = Q (smem, K-major), B = K_j (smem, K-major), D in TMEM (two S buffers)
+//     P_j = exp2(S c - m)   softmax warps: thread = row, TMEM -> registers (one pass) -> bf16 -> swizzled smem in the
 //                           A-operand layout, written over K_j (dead once S_j is complete)
-//     O += P V_j            tcgen05.mma, A = P (smem, K-major), B = V_j (smem, MN-major: V rows are keys), D in TMEM
-// with an online softmax whose running maximum is only raised when it grows by more than 2^8 (the O accumulator in
-// TMEM is then rescaled once), so most blocks never touch O.  The CTA is deliberately lean — 97 KB of smem and 256
-// TMEM columns — so that TWO CTAs share an SM and one's TMA / softmax phases overlap the other's MMAs (utterances are
-// short: T = 167 for 10 s, i.e. two key blocks).  Warp roles: 0 TMA producer, 1 MMA issuer (+ TMEM alloc), 2..5
-// softmax / epilogue (one TMEM lane quarter each).
+//     O  += P_j V_j         tcgen05.mma, A = P (smem, K-major), B = V_j (smem, MN-major: V rows are keys), D in TMEM
+// software-pipelined: S_{j+1} is issued before the softmax of block j finishes, so the tensor pipe, the MUFU/ALU softmax
+// and the TMA of block j+2 overlap inside one CTA; the online softmax only raises its running maximum when it grows by
+// more than 2^8 (the O accumulator in TMEM is then rescaled once), so most blocks never touch O.  The CTA is lean —
+// 97 KB of smem and 256 TMEM columns — so that TWO CTAs share an SM (utterances are short: T = 167 for 10 s = three
+// key blocks).  Warp roles: 0 TMA producer, 1 MMA issuer (+ TMEM alloc), 2..5 softmax / epilogue (one TMEM lane quarter
+// each).
 #include <cuda.h>
 
 #include <cstring>
@@ -25,14 +26,16 @@ namespace attn {
 
 constexpr int HD = 128;   // head dim
 constexpr int BQ = 128;   // query rows per CTA = UMMA M
-constexpr int BKV = 128;  // keys per block
+constexpr int BKV = 64;   // keys per block
+constexpr int STAGES = 2;
 constexpr int THREADS = 192;
-constexpr int PANEL = BQ * 128;            // one [128 rows x 64 bf16] 128B-swizzled panel = 16 KB
-constexpr int Q_BYTES = 2 * PANEL;         // d = 128 -> two panels
-constexpr int K_BYTES = 2 * PANEL;         // K block: two panels; P (128 keys -> two panels) later overwrites it
-constexpr int V_BYTES = 2 * PANEL;
-constexpr int SMEM_BYTES = Q_BYTES + K_BYTES + V_BYTES + 1024 + 256;
-constexpr int TMEM_COLS = 256;             // S [0,128)  O [128,256)
+constexpr int QPANEL = BQ * 128;           // [128 rows x 64 bf16] 128B-swizzled panel = 16 KB
+constexpr int KPANEL = BKV * 128;          // [64 rows x 64 bf16] panel = 8 KB
+constexpr int Q_BYTES = 2 * QPANEL;        // d = 128 -> two panels
+constexpr int K_BYTES = 2 * KPANEL;        // one K block; P_j (128 rows x 64 keys = one 16 KB panel) later overwrites it
+constexpr int V_BYTES = 2 * KPANEL;
+constexpr int SMEM_BYTES = Q_BYTES + STAGES * (K_BYTES + V_BYTES) + 1024 + 256;
+constexpr int TMEM_COLS = 256;             // S0 [0,64)  S1 [64,128)  O [128,256)
 constexpr float RESCALE_THRESHOLD = 8.f;   // log2 units
 
 // ---------------------------------------------------------------- PTX wrappers (same conventions as gemm_tcgen05.cu)
@@ -58,6 +61,19 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "r"(bar), "r"(parity)
         : "memory");
   }
+}
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint32_t bar, int x, int y) {
   asm volatile(
@@ -121,38 +137,64 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
       : "memory");
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
+// 2^x on the MUFU pipe, one instruction (x <= 0 here; results below 2^-126 flush to zero, far under bf16 resolution of P)
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define TRACE(slot)                                                                              \
+  do {                                                                                           \
+    if (trace && cta_lin < 512) trace[cta_lin * 16 + (slot)] = gtime();                          \
+  } while (0)
+
 // ---------------------------------------------------------------- kernel
 __global__ void __launch_bounds__(THREADS, 2)
-attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __restrict__ cu, int n_heads,
-                 __nv_bfloat16* __restrict__ ctx, int64_t ld_ctx, float scale_log2e) {
+attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __restrict__ cu, int base, int n_heads,
+                 __nv_bfloat16* __restrict__ ctx, int64_t ld_ctx, float scale_log2e, unsigned long long* trace) {
   extern __shared__ unsigned char smem_raw[];
+  const int cta_lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  if (threadIdx.x == 0) TRACE(0);
   const int b = blockIdx.z, h = blockIdx.y;
-  const int start = cu[b], len = cu[b + 1] - start;
+  const int start = cu[b] - base, len = cu[b + 1] - cu[b];
   const int q0 = blockIdx.x * BQ;
   if (q0 >= len) return;  // uniform per CTA, before any barrier / TMEM use
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int dm = n_heads * HD;
   const int n_blk = (len + BKV - 1) / BKV;
 
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sQ = base, sK = sQ + Q_BYTES, sV = sK + K_BYTES, sP = sK, bars = sV + V_BYTES;
-  const uint32_t q_full = bars, k_full = bars + 8, v_full = bars + 16, kv_empty = bars + 24, s_full = bars + 32,
-                 p_full = bars + 40, o_full = bars + 48, tmem_slot = bars + 56;
+  const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = sbase, sK0 = sQ + Q_BYTES, sV0 = sK0 + STAGES * K_BYTES, bars = sV0 + STAGES * V_BYTES;
+  auto sK = [&](int st) { return sK0 + st * K_BYTES; };
+  auto sV = [&](int st) { return sV0 + st * V_BYTES; };
+  const uint32_t q_full = bars, o_full = bars + 8, tmem_slot = bars + 16;
+  auto k_full = [&](int st) { return bars + 24 + 8 * st; };
+  auto v_full = [&](int st) { return bars + 40 + 8 * st; };
+  auto kv_empty = [&](int st) { return bars + 56 + 8 * st; };
+  auto s_full = [&](int st) { return bars + 72 + 8 * st; };
+  auto p_full = [&](int st) { return bars + 88 + 8 * st; };
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_qkv) : "memory");
     mbar_init(q_full, 1);
-    mbar_init(k_full, 1);
-    mbar_init(v_full, 1);
-    mbar_init(kv_empty, 1);
-    mbar_init(s_full, 1);
-    mbar_init(p_full, 128);  // every softmax thread arrives
     mbar_init(o_full, 1);
+    for (int st = 0; st < STAGES; ++st) {
+      mbar_init(k_full(st), 1);
+      mbar_init(v_full(st), 1);
+      mbar_init(kv_empty(st), 1);
+      mbar_init(s_full(st), 1);
+      mbar_init(p_full(st), 128);  // every softmax thread arrives
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -162,59 +204,74 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (threadIdx.x == 0) TRACE(1);
   const uint32_t tmem = *tmem_slot_ptr;
-  const uint32_t tS = tmem, tO = tmem + BKV;
+  const uint32_t tO = tmem + 2 * BKV;
+  auto tS = [&](int st) { return tmem + st * BKV; };
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       const int xq = h * HD, xk = dm + h * HD, xv = 2 * dm + h * HD;
       mbar_expect_tx(q_full, Q_BYTES);
-      tma_load_2d(sQ, &tmap_qkv, q_full, xq, start + q0);
-      tma_load_2d(sQ + PANEL, &tmap_qkv, q_full, xq + 64, start + q0);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)  // (panel, row half): box = 64 rows x 64 columns
+        tma_load_2d(sQ + (i >> 1) * QPANEL + (i & 1) * KPANEL, &tmap_qkv, q_full, xq + (i >> 1) * 64, start + q0 + (i & 1) * 64);
       for (int j = 0; j < n_blk; ++j) {
-        mbar_wait(kv_empty, (j & 1) ^ 1);  // P_{j-1} V_{j-1} retired: the K/P and V regions are free
+        const int st = j & 1;
+        mbar_wait(kv_empty(st), ((j >> 1) & 1) ^ 1);  // P_{j-2} V_{j-2} retired: the K/P and V slots of this stage are free
         const int row = start + j * BKV;
-        mbar_expect_tx(k_full, K_BYTES);
-        tma_load_2d(sK, &tmap_qkv, k_full, xk, row);
-        tma_load_2d(sK + PANEL, &tmap_qkv, k_full, xk + 64, row);
-        mbar_expect_tx(v_full, V_BYTES);
-        tma_load_2d(sV, &tmap_qkv, v_full, xv, row);
-        tma_load_2d(sV + PANEL, &tmap_qkv, v_full, xv + 64, row);
+        mbar_expect_tx(k_full(st), K_BYTES);
+        tma_load_2d(sK(st), &tmap_qkv, k_full(st), xk, row);
+        tma_load_2d(sK(st) + KPANEL, &tmap_qkv, k_full(st), xk + 64, row);
+        mbar_expect_tx(v_full(st), V_BYTES);
+        tma_load_2d(sV(st), &tmap_qkv, v_full(st), xv, row);
+        tma_load_2d(sV(st) + KPANEL, &tmap_qkv, v_full(st), xv + 64, row);
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      mbar_wait(q_full, 0);
-      for (int j = 0; j < n_blk; ++j) {
+      auto issue_s = [&](int j) {  // S_j = Q K_j^T into S buffer j & 1
+        const int st = j & 1;
         const int nkeys = min(BKV, len - j * BKV);
-        // S = Q K_j^T
-        mbar_wait(k_full, j & 1);
         tc_fence_after();
-        {
-          const uint32_t idesc = make_idesc(BQ, (nkeys + 15) & ~15, 0);
+        const uint32_t idesc = make_idesc(BQ, (nkeys + 15) & ~15, 0);
 #pragma unroll
-          for (int k = 0; k < HD / 16; ++k) {
-            const uint32_t off = (k >> 2) * PANEL + (k & 3) * 32;
-            umma_f16(tS, desc_kmajor(sQ + off), desc_kmajor(sK + off), idesc, k != 0);
-          }
-          umma_commit(s_full);
+        for (int k = 0; k < HD / 16; ++k)
+          umma_f16(tS(st), desc_kmajor(sQ + (k >> 2) * QPANEL + (k & 3) * 32), desc_kmajor(sK(st) + (k >> 2) * KPANEL + (k & 3) * 32),
+                   idesc, k != 0);
+        umma_commit(s_full(st));
+      };
+      mbar_wait(q_full, 0);
+      mbar_wait(k_full(0), 0);
+      TRACE(2);
+      issue_s(0);
+      for (int j = 0; j < n_blk; ++j) {
+        const int st = j & 1, nx = (j + 1) & 1;
+        const uint32_t nx_phase = ((j + 1) >> 1) & 1;
+        // S_{j+1} first if its K block has landed (it then overlaps the softmax of block j); otherwise after P_j V_j
+        bool s_next_done = (j + 1 >= n_blk);
+        if (!s_next_done && mbar_test(k_full(nx), nx_phase)) {
+          issue_s(j + 1);
+          s_next_done = true;
         }
-        // O (+)= P V_j
-        mbar_wait(p_full, j & 1);
-        mbar_wait(v_full, j & 1);
+        // O (+)= P_j V_j
+        mbar_wait(p_full(st), (j >> 1) & 1);
+        mbar_wait(v_full(st), (j >> 1) & 1);
         tc_fence_after();
         {
+          const int nkeys = min(BKV, len - j * BKV);
           const int ksteps = (nkeys + 15) >> 4;
           const uint32_t idesc = make_idesc(BQ, HD, 1);
-          for (int k = 0; k < ksteps; ++k) {
-            const uint64_t adesc = desc_kmajor(sP + (k >> 2) * PANEL + (k & 3) * 32);
-            const uint64_t bdesc = desc_mnmajor(sV + k * 16 * 128, PANEL, 1024);
-            umma_f16(tO, adesc, bdesc, idesc, (j | k) != 0);
-          }
-          umma_commit(kv_empty);
+          for (int k = 0; k < ksteps; ++k)
+            umma_f16(tO, desc_kmajor(sK(st) + k * 32), desc_mnmajor(sV(st) + k * 16 * 128, KPANEL, 1024), idesc, (j | k) != 0);
+          umma_commit(kv_empty(st));
           if (j == n_blk - 1) umma_commit(o_full);
+        }
+        if (!s_next_done) {
+          mbar_wait(k_full(nx), nx_phase);
+          issue_s(j + 1);
         }
       }
     }
@@ -224,34 +281,55 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
     const int row = q * 32 + lane;                 // row within the tile == TMEM lane
     const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
     const uint32_t rsw = static_cast<uint32_t>(row & 7);
+    const bool row_ok = q0 + row < len;
     float m_used = -INFINITY, l_run = 0.f;
     for (int j = 0; j < n_blk; ++j) {
+      const int st = j & 1;
       const int nkeys = min(BKV, len - j * BKV);
-      const int nch = (nkeys + 31) >> 5;  // 32-column chunks holding valid keys
-      mbar_wait(s_full, j & 1);           // also implies P_{j-1} V_{j-1} has retired (K_j was loaded after it)
+      mbar_wait(s_full(st), (j >> 1) & 1);
       tc_fence_after();
-      // ---- the whole S row of this block into registers (one TMEM pass), row maximum over the valid keys
-      uint32_t r[4][32];
-      float mx = -INFINITY;
+      if (threadIdx.x == 64 && j < 3) TRACE(3 + j);
+      // ---- the whole S row of this block into registers (one TMEM pass); keys past the end of the utterance become
+      // -inf once, so the arithmetic below is predicate-free; row maximum with four independent chains
+      float r[2][32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        if (c < nch) {
-          tmem_ld32(tS + lane_sel + c * 32, r[c]);
+      for (int c = 0; c < 2; ++c) {
+        if (c * 32 < nkeys) {
+          uint32_t t[32];
+          tmem_ld32(tS(st) + lane_sel + c * 32, t);
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (c * 32 + i < nkeys) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+          for (int i = 0; i < 32; ++i) r[c][i] = __uint_as_float(t[i]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[c][i] = -INFINITY;
         }
       }
+      if (nkeys < BKV) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (c * 32 + i >= nkeys) r[c][i] = -INFINITY;
+      }
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], r[c][i]);
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_blk = mx * scale_log2e;
       // ---- running maximum: only raised when it would grow by more than 2^8 (then O in TMEM is rescaled once)
       float alpha = 1.f;
       if (j == 0) {
         m_used = m_blk;
-      } else if (m_blk - m_used > RESCALE_THRESHOLD) {
-        alpha = exp2f(m_used - m_blk);
+      } else if (row_ok && m_blk - m_used > RESCALE_THRESHOLD) {
+        alpha = ex2(m_used - m_blk);
         m_used = m_blk;
       }
       if (__any_sync(0xffffffffu, alpha != 1.f)) {
+        // O holds blocks 0..j-1: P_{j-1} V_{j-1} must have retired (its commit is this stage ring's "empty" barrier)
+        mbar_wait(kv_empty((j - 1) & 1), ((j - 1) >> 1) & 1);
+        tc_fence_after();
         l_run *= alpha;
 #pragma unroll 1
         for (int c = 0; c < HD / 32; ++c) {
@@ -262,37 +340,40 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
           tmem_st32(tO + lane_sel + c * 32, o);
         }
       }
-      // ---- p = exp2(s c - m), row sum, bf16 -> swizzled smem (A operand of the P V MMA), over the dead K block
-      float rs = 0.f;
-      const int nch16 = (nkeys + 15) >> 4;  // 16-key MMA steps that will be issued
+      // ---- p = exp2(s c - m), row sum, bf16 -> swizzled smem (A operand of the P V MMA), over the dead K block.
+      // Rows past the end of the utterance skip the arithmetic: their P rows only feed O rows that are never stored.
+      if (row_ok) {
+        float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+        const int nch16 = (nkeys + 15) >> 4;  // 16-key MMA steps that will be issued
+        const uint32_t prow = sK(st) + static_cast<uint32_t>(row) * 128u;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        if (c * 2 < nch16) {  // chunk read by at least one MMA step
-          uint32_t pk[16];
+        for (int c = 0; c < 2; ++c) {
+          if (c * 2 < nch16) {  // chunk read by at least one MMA step
+            uint32_t pk[16];
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            const float p0 = (c * 32 + i < nkeys) ? exp2f(fmaf(__uint_as_float(r[c][i]), scale_log2e, -m_used)) : 0.f;
-            const float p1 = (c * 32 + i + 1 < nkeys) ? exp2f(fmaf(__uint_as_float(r[c][i + 1]), scale_log2e, -m_used)) : 0.f;
-            rs += p0 + p1;
-            pk[i >> 1] = pack_bf16x2(p0, p1);
+            for (int i = 0; i < 32; i += 2) {
+              const float p0 = ex2(fmaf(r[c][i], scale_log2e, -m_used));      // masked keys: 2^-inf = 0
+              const float p1 = ex2(fmaf(r[c][i + 1], scale_log2e, -m_used));
+              rs4[(i >> 1) & 3] += p0 + p1;
+              pk[i >> 1] = pack_bf16x2(p0, p1);
+            }
+#pragma unroll
+            for (int g = 0; g < 4; ++g)  // 32 keys = 64 B = four 16-byte chunks of this row
+              sts128(prow + ((static_cast<uint32_t>(c * 4 + g) ^ rsw) << 4), pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
           }
-          // 32 keys = 64 B = four 16-byte chunks of this row inside panel (c >> 1)
-          const uint32_t prow = sP + (c >> 1) * PANEL + static_cast<uint32_t>(row) * 128u;
-#pragma unroll
-          for (int g = 0; g < 4; ++g)
-            sts128(prow + ((static_cast<uint32_t>((c & 1) * 4 + g) ^ rsw) << 4), pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
         }
+        l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
       }
-      l_run += rs;
       fence_async_smem();
       tc_fence_before();
-      mbar_arrive(p_full);
+      mbar_arrive(p_full(st));
+      if (threadIdx.x == 64 && j < 3) TRACE(6 + j);
     }
     // ---- epilogue: O / l -> bf16 -> ctx (head merge = column offset h*128)
     mbar_wait(o_full, 0);
     tc_fence_after();
+    if (threadIdx.x == 64) TRACE(9);
     const float inv = 1.f / l_run;
-    const bool row_ok = q0 + row < len;
     __nv_bfloat16* dst = ctx + static_cast<int64_t>(start + q0 + row) * ld_ctx + h * HD;
 #pragma unroll 1
     for (int c = 0; c < HD / 32; ++c) {
@@ -312,17 +393,27 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
     }
   }
 
+  if (threadIdx.x == 64) TRACE(10);
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
   }
+  if (threadIdx.x == 0) {
+    TRACE(11);
+    if (trace && cta_lin < 512) {
+      unsigned smid;
+      asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+      trace[cta_lin * 16 + 12] = smid;
+    }
+  }
 }
+unsigned long long* g_trace = nullptr;
 
 }  // namespace attn
 
-int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int max_len,
+int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base, int max_len,
                      int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream) {
   FA_REQUIRE(ld % 8 == 0 && ld_ctx % 8 == 0, "attention: row strides must be multiples of 8 elements");
   FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0,
@@ -337,13 +428,13 @@ int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seq
   // rows = the valid packed rows only: key/value rows past the end are zero-filled by TMA instead of reading workspace
   // padding (whose contents are undefined and could be NaN, which 0 * NaN would leak into O).
   TensorMap2D tm;
-  if (int r = make_tensor_map_bf16(&tm, qkv, n_rows, 3 * n_heads * attn::HD, ld, 128)) return r;
+  if (int r = make_tensor_map_bf16(&tm, qkv, n_rows, 3 * n_heads * attn::HD, ld, attn::BKV)) return r;
   CUtensorMap m;
   memcpy(&m, tm.bytes, sizeof(m));
   dim3 grid(ceil_div(max_len, attn::BQ), n_heads, n_utts);
   const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(attn::HD));
   ProfScope _ps(K_ATTENTION, stream);
-  attn::attention_kernel<<<grid, attn::THREADS, attn::SMEM_BYTES, stream>>>(m, cu_seqlens, n_heads, ctx, ld_ctx, scale_log2e);
+  attn::attention_kernel<<<grid, attn::THREADS, attn::SMEM_BYTES, stream>>>(m, cu_seqlens, base, n_heads, ctx, ld_ctx, scale_log2e, attn::g_trace);
   FA_CHECK_LAUNCH();
   return 0;
 }
@@ -355,6 +446,11 @@ extern "C" int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_
                                fa_stream_t stream) {
   using namespace fa;
   FA_REQUIRE(qkv_dev && cu_seqlens_dev && ctx_dev, "attention: NULL pointer");
-  return launch_attention(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, cu_seqlens_dev, n_utts, max_len, n_heads,
+  return launch_attention(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, cu_seqlens_dev, n_utts, 0, max_len, n_heads,
                           static_cast<__nv_bfloat16*>(ctx_dev), ld_ctx, n_rows, static_cast<cudaStream_t>(stream));
+}
+
+// debug only (not in the public header): device buffer of 512 x 16 u64 receiving per-CTA %globaltimer stamps
+extern "C" __attribute__((visibility("default"))) void fa_debug_attention_trace(void* buf) {
+  fa::attn::g_trace = static_cast<unsigned long long*>(buf);
 }

@@ -68,19 +68,23 @@ int make_tensor_map(TensorMap2D* out, const void* base, int elem_bytes, uint64_t
                     uint32_t box_rows);
 
 int gemm_block_n(int M, int N);  // tile-N heuristic (64 / 128 / 256)
+// Rows [row0, row0 + M) of the A / C matrices the maps describe; epi.res* point at row row0 already.
 int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int block_n, int M, int N, int K,
-                const GemmEpilogue& epi, void* c, int64_t ldc, cudaStream_t stream);
+                const GemmEpilogue& epi, void* c, int64_t ldc, int row0, cudaStream_t stream);
 
 int launch_layernorm(const float* x, const float* g, const float* b, const float* g2, const float* b2,
                      __nv_bfloat16* y_bf16, float* y_f32, int M, int D, cudaStream_t stream);
-int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, const int32_t* cu, int n_utts, float scale,
-                           const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream);
-int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts,
+// Row-range convention of the kernels below: every data pointer addresses LOCAL row 0 of a slab of M rows holding the
+// n_utts utterances cu[0..n_utts]; cu keeps ABSOLUTE packed row numbers and `base` (= cu[0] of the slab) is subtracted
+// inside the kernel.  base == 0 for a whole batch; the chunked schedule in api.cu passes slabs.
+int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, const int32_t* cu, int n_utts, int base,
+                           float scale, const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream);
+int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts, int base,
                 float* mem, int M, int D, int kernel, int left_pad, cudaStream_t stream);
-int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int max_len,
+int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base, int max_len,
                      int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream);
 int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, int dst_bf16, const int32_t* cu,
-                       int n_utts, int M, int D, cudaStream_t stream);
+                       int n_utts, int base, int M, int D, cudaStream_t stream);
 
 }  // namespace fa
 

@@ -41,6 +41,7 @@ struct LnArgs {
   const float* inv_ts;    // positional encoding (nullable)
   const int32_t* cu;
   int n_utts;
+  int base;  // absolute packed row of local row 0
   float scale;
   int M, D;
   int in_tmax;  // EMBED only: 0 = x is packed [M, D]; else x is padded [n_utts, in_tmax, D]
@@ -72,8 +73,8 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
   int64_t src_row = row;
   int pos_i = 0;
   if (EMBED) {
-    const int b = utt_index(a.cu, a.n_utts, row);
-    pos_i = row - __ldg(a.cu + b);
+    const int b = utt_index(a.cu, a.n_utts, row + a.base);
+    pos_i = row + a.base - __ldg(a.cu + b);
     if (a.in_tmax > 0) src_row = static_cast<int64_t>(b) * a.in_tmax + pos_i;
   }
   const float4* xr = reinterpret_cast<const float4*>(a.x + src_row * D);
@@ -158,14 +159,14 @@ constexpr int FSMN_THREADS = 128;
 template <int K>
 __global__ void __launch_bounds__(FSMN_THREADS)
 fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
-            const int32_t* __restrict__ cu, int n_utts, float* __restrict__ mem, int M, int D, int left) {
+            const int32_t* __restrict__ cu, int n_utts, int base, float* __restrict__ mem, int M, int D, int left) {
   __shared__ int s_lo[FSMN_ROWS], s_hi[FSMN_ROWS];
   const int r0 = blockIdx.x * FSMN_ROWS;
   if (threadIdx.x < FSMN_ROWS) {
     const int r = min(r0 + threadIdx.x, M - 1);
-    const int2 ub = utt_bounds(cu, n_utts, r);
-    s_lo[threadIdx.x] = ub.x;
-    s_hi[threadIdx.x] = ub.y;
+    const int2 ub = utt_bounds(cu, n_utts, r + base);
+    s_lo[threadIdx.x] = ub.x - base;
+    s_hi[threadIdx.x] = ub.y - base;
   }
   const int c2 = blockIdx.y * blockDim.x + threadIdx.x;  // channel pair
   const bool ch_ok = 2 * c2 < D;
@@ -238,7 +239,7 @@ fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const 
 // This is the only place the padded [B, Tmax, .] layout of the reference API exists.
 __global__ void __launch_bounds__(256)
 repack_rows_kernel(const float* __restrict__ src, int src_tmax, void* __restrict__ dst, int dst_tmax, int dst_bf16,
-                   const int32_t* __restrict__ cu, int n_utts, int dst_rows, int D) {
+                   const int32_t* __restrict__ cu, int n_utts, int base, int dst_rows, int D) {
   const int lane = threadIdx.x & 31;
   const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (r >= dst_rows) return;
@@ -249,10 +250,10 @@ repack_rows_kernel(const float* __restrict__ src, int src_tmax, void* __restrict
     t = r - b * dst_tmax;
     valid = t < __ldg(cu + b + 1) - __ldg(cu + b);
   } else {
-    b = utt_index(cu, n_utts, r);
-    t = r - __ldg(cu + b);
+    b = utt_index(cu, n_utts, r + base);
+    t = r + base - __ldg(cu + b);
   }
-  const int64_t sr = src_tmax > 0 ? static_cast<int64_t>(b) * src_tmax + t : static_cast<int64_t>(__ldg(cu + b)) + t;
+  const int64_t sr = src_tmax > 0 ? static_cast<int64_t>(b) * src_tmax + t : static_cast<int64_t>(__ldg(cu + b) - base) + t;
   const float4* s4 = reinterpret_cast<const float4*>(src + sr * D);
   const int nvec = D >> 2;
   for (int c = lane; c < nvec; c += 32) {
@@ -309,24 +310,24 @@ static int ln_check(int D, const void* x) {
 int launch_layernorm(const float* x, const float* g, const float* b, const float* g2, const float* b2,
                      __nv_bfloat16* y_bf16, float* y_f32, int M, int D, cudaStream_t stream) {
   if (int r = ln_check(D, x)) return r;
-  ew::LnArgs a{x, g, b, g2, b2, y_bf16, y_f32, nullptr, nullptr, 0, 1.f, M, D, 0};
+  ew::LnArgs a{x, g, b, g2, b2, y_bf16, y_f32, nullptr, nullptr, 0, 0, 1.f, M, D, 0};
   ProfScope _ps(K_LAYERNORM, stream);
   ew::layernorm_kernel<false><<<ceil_div(M, 8), 256, 0, stream>>>(a);
   FA_CHECK_LAUNCH();
   return 0;
 }
 
-int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, const int32_t* cu, int n_utts, float scale,
-                           const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream) {
+int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, const int32_t* cu, int n_utts, int base,
+                           float scale, const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream) {
   if (int r = ln_check(D, x)) return r;
-  ew::LnArgs a{x, g, b, nullptr, nullptr, y, nullptr, inv_ts, cu, n_utts, scale, M, D, in_tmax};
+  ew::LnArgs a{x, g, b, nullptr, nullptr, y, nullptr, inv_ts, cu, n_utts, base, scale, M, D, in_tmax};
   ProfScope _ps(K_LAYERNORM, stream);
   ew::layernorm_kernel<true><<<ceil_div(M, 8), 256, 0, stream>>>(a);
   FA_CHECK_LAUNCH();
   return 0;
 }
 
-int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts,
+int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts, int base,
                 float* mem, int M, int D, int kernel, int left_pad, cudaStream_t stream) {
   FA_REQUIRE(kernel >= 1 && kernel <= ew::FSMN_MAXK, "fsmn: kernel size %d not in [1,%d]", kernel, ew::FSMN_MAXK);
   FA_REQUIRE(left_pad >= 0 && left_pad < kernel, "fsmn: left pad %d outside the %d-tap window", left_pad, kernel);
@@ -338,7 +339,7 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
   dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 2, threads));
   ProfScope _ps(K_FSMN, stream);
 #define FA_FSMN_CASE(KK) \
-  case KK: ew::fsmn_kernel<KK><<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, mem, M, D, left_pad); break;
+  case KK: ew::fsmn_kernel<KK><<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, base, mem, M, D, left_pad); break;
   switch (kernel) {
     FA_FSMN_CASE(1) FA_FSMN_CASE(2) FA_FSMN_CASE(3) FA_FSMN_CASE(4) FA_FSMN_CASE(5) FA_FSMN_CASE(6) FA_FSMN_CASE(7) FA_FSMN_CASE(8)
     FA_FSMN_CASE(9) FA_FSMN_CASE(10) FA_FSMN_CASE(11) FA_FSMN_CASE(12) FA_FSMN_CASE(13) FA_FSMN_CASE(14) FA_FSMN_CASE(15)
@@ -350,13 +351,13 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
 }
 
 int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, int dst_bf16, const int32_t* cu,
-                       int n_utts, int M, int D, cudaStream_t stream) {
+                       int n_utts, int base, int M, int D, cudaStream_t stream) {
   FA_REQUIRE(D % 4 == 0, "repack: D=%d must be a multiple of 4", D);
   FA_REQUIRE((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0,
              "repack: buffers must be 16-byte aligned");
   const int rows = dst_tmax > 0 ? n_utts * dst_tmax : M;
   ProfScope _ps(K_REPACK, stream);
-  ew::repack_rows_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(src, src_tmax, dst, dst_tmax, dst_bf16, cu, n_utts, rows, D);
+  ew::repack_rows_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(src, src_tmax, dst, dst_tmax, dst_bf16, cu, n_utts, base, rows, D);
   FA_CHECK_LAUNCH();
   return 0;
 }
@@ -377,7 +378,7 @@ extern "C" int fa_op_embed_layernorm(const float* x_dev, const float* inv_ts_dev
                                      void* y_bf16_dev, int32_t M, int32_t D, fa_stream_t stream) {
   FA_REQUIRE(x_dev && inv_ts_dev && cu_seqlens_dev && g_dev && b_dev && y_bf16_dev && M > 0 && n_utts > 0,
              "embed_layernorm: bad arguments");
-  return launch_embed_layernorm(x_dev, 0, inv_ts_dev, cu_seqlens_dev, n_utts, scale, g_dev, b_dev,
+  return launch_embed_layernorm(x_dev, 0, inv_ts_dev, cu_seqlens_dev, n_utts, 0, scale, g_dev, b_dev,
                                 static_cast<__nv_bfloat16*>(y_bf16_dev), M, D, static_cast<cudaStream_t>(stream));
 }
 
@@ -385,7 +386,7 @@ extern "C" int fa_op_fsmn(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, co
                           const int32_t* cu_seqlens_dev, int32_t n_utts, float* mem_dev, int32_t M, int32_t D,
                           int32_t kernel, int32_t left_pad, fa_stream_t stream) {
   FA_REQUIRE(qkv_dev && w_dev && cu_seqlens_dev && mem_dev && M > 0 && n_utts > 0, "fsmn: bad arguments");
-  return launch_fsmn(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, v_col, w_dev, cu_seqlens_dev, n_utts, mem_dev,
+  return launch_fsmn(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, v_col, w_dev, cu_seqlens_dev, n_utts, 0, mem_dev,
                      M, D, kernel, left_pad, static_cast<cudaStream_t>(stream));
 }
 

@@ -41,6 +41,7 @@ struct Cfg {
 
 struct Params {
   int M, N, K;
+  int row0;  // first row of A / C inside the matrices the tensor maps describe
   int tiles_m, tiles_n;
   const float* bias;
   const float* res1;
@@ -215,7 +216,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
           const uint32_t sb = sa + C::A_BYTES;
           mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
-          tma_load_2d(sa, &tmap_a, full_bar(stage), kb * BK, tm * BM);
+          tma_load_2d(sa, &tmap_a, full_bar(stage), kb * BK, p.row0 + tm * BM);
           tma_load_2d(sb, &tmap_b, full_bar(stage), kb * BK, tn * BN);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
@@ -342,7 +343,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
         __syncwarp();
         if (lane == 0) {
-          tma_store_2d(&tmap_c, slab, col0, row0);
+          tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
           bulk_commit();
         }
       }
@@ -381,7 +382,7 @@ static EncodeTiledFn get_encode_fn() {
 
 template <int BN>
 static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int M, int N, int K,
-                    const GemmEpilogue& epi, void* c, int64_t ldc, cudaStream_t stream) {
+                    const GemmEpilogue& epi, void* c, int64_t ldc, int row0, cudaStream_t stream) {
   using C = Cfg<BN>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -390,6 +391,7 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   }
   Params p;
   p.M = M; p.N = N; p.K = K;
+  p.row0 = row0;
   p.tiles_m = ceil_div(M, BM);
   p.tiles_n = N / BN;
   p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
@@ -448,16 +450,16 @@ int gemm_block_n(int M, int N) {
 }
 
 int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int block_n, int M, int N, int K,
-                const GemmEpilogue& epi, void* c, int64_t ldc, cudaStream_t stream) {
-  FA_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
+                const GemmEpilogue& epi, void* c, int64_t ldc, int row0, cudaStream_t stream) {
+  FA_REQUIRE(M > 0 && N > 0 && K > 0 && row0 >= 0, "gemm: empty problem %dx%dx%d", M, N, K);
   FA_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "gemm: unsupported tile N %d", block_n);
   FA_REQUIRE(N % block_n == 0, "gemm: N=%d is not a multiple of the tile %d", N, block_n);
   FA_REQUIRE(K % 8 == 0, "gemm: K=%d must be a multiple of 8", K);
   FA_REQUIRE(ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(c) & 15) == 0, "gemm: C must be 16-byte aligned, ldc %% 8 == 0");
   switch (block_n) {
-    case 64: return gemm::launch_t<64>(ta, tb, tc, M, N, K, epi, c, ldc, stream);
-    case 128: return gemm::launch_t<128>(ta, tb, tc, M, N, K, epi, c, ldc, stream);
-    default: return gemm::launch_t<256>(ta, tb, tc, M, N, K, epi, c, ldc, stream);
+    case 64: return gemm::launch_t<64>(ta, tb, tc, M, N, K, epi, c, ldc, row0, stream);
+    case 128: return gemm::launch_t<128>(ta, tb, tc, M, N, K, epi, c, ldc, row0, stream);
+    default: return gemm::launch_t<256>(ta, tb, tc, M, N, K, epi, c, ldc, row0, stream);
   }
 }
 
@@ -476,5 +478,5 @@ extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int
   if (int r = make_tensor_map(&tc, c_dev, out_f32 ? 4 : 2, M, N, ldc, 32)) return r;
   GemmEpilogue e;
   e.bias = bias_dev; e.res1 = res1_dev; e.res2 = res2_dev; e.relu = relu; e.out_f32 = out_f32;
-  return launch_gemm(ta, tb, tc, bn, M, N, K, e, c_dev, ldc, static_cast<cudaStream_t>(stream));
+  return launch_gemm(ta, tb, tc, bn, M, N, K, e, c_dev, ldc, 0, static_cast<cudaStream_t>(stream));
 }

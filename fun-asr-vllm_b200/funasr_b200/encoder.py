@@ -200,6 +200,13 @@ class Plan:
         with torch.cuda.device(self.device):
             _lib.check(lib.fa_plan_create(C.byref(self.cfg), C.byref(self.w), base, nbytes, cap, C.byref(self.handle)), "fa_plan_create")
         self.cap = cap
+        if getattr(self, "chunk_tokens", None) is not None:
+            _lib.check(lib.fa_plan_set_chunk_tokens(self.handle, self.chunk_tokens), "fa_plan_set_chunk_tokens")
+
+    def set_chunk_tokens(self, n: int):
+        """Slab size of the layer schedule (``fa_plan_set_chunk_tokens``); 0 runs every layer over the whole batch."""
+        self.chunk_tokens = int(n)
+        _lib.check(_lib.load().fa_plan_set_chunk_tokens(self.handle, int(n)), "fa_plan_set_chunk_tokens")
 
     def ensure(self, n_tokens: int):
         if n_tokens > self.cap:
@@ -232,7 +239,7 @@ class Plan:
         cu_d = cu_dev if cu_dev is not None else cu_d
         self.ensure(M)
         with torch.cuda.device(self.device):
-            _lib.check(_lib.load().fa_encoder_forward(self.handle, feats.data_ptr(), feats_tmax, cu_d.data_ptr(), len(cu) - 1, M,
+            _lib.check(_lib.load().fa_encoder_forward(self.handle, feats.data_ptr(), feats_tmax, cu_d.data_ptr(), cu.ctypes.data, len(cu) - 1, M,
                                                       tmax, _lib.ptr(out), out_tmax, _lib.stream_ptr(self.device)),
                        "fa_encoder_forward")
         self._keep = cu_d
@@ -243,7 +250,7 @@ class Plan:
         cu_d = cu_dev if cu_dev is not None else cu_d
         self.ensure(M)
         with torch.cuda.device(self.device):
-            _lib.check(_lib.load().fa_adaptor_forward(self.handle, _lib.ptr(enc), enc_tmax, cu_d.data_ptr(), len(cu) - 1, M, tmax,
+            _lib.check(_lib.load().fa_adaptor_forward(self.handle, _lib.ptr(enc), enc_tmax, cu_d.data_ptr(), cu.ctypes.data, len(cu) - 1, M, tmax,
                                                       out.data_ptr(), out_tmax, 1 if out.dtype == torch.bfloat16 else 0,
                                                       _lib.stream_ptr(self.device)), "fa_adaptor_forward")
         self._keep = cu_d
@@ -254,7 +261,7 @@ class Plan:
         cu_d = cu_dev if cu_dev is not None else cu_d
         self.ensure(M)
         with torch.cuda.device(self.device):
-            _lib.check(_lib.load().fa_encode_adapt(self.handle, feats.data_ptr(), feats_tmax, cu_d.data_ptr(), len(cu) - 1, M, tmax,
+            _lib.check(_lib.load().fa_encode_adapt(self.handle, feats.data_ptr(), feats_tmax, cu_d.data_ptr(), cu.ctypes.data, len(cu) - 1, M, tmax,
                                                    _lib.ptr(enc_out), enc_out_tmax, out.data_ptr(), out_tmax,
                                                    1 if out.dtype == torch.bfloat16 else 0, _lib.stream_ptr(self.device)),
                        "fa_encode_adapt")

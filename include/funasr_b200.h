@@ -40,7 +40,7 @@ extern "C" {
 
 typedef void* fa_stream_t; /* cudaStream_t */
 
-#define FA_ABI_VERSION 1
+#define FA_ABI_VERSION 2
 
 int fa_abi_version(void);
 const char* fa_last_error(void);
@@ -171,6 +171,13 @@ size_t fa_plan_workspace_bytes(const fa_model_cfg* cfg, int32_t max_tokens);
 int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void* workspace_dev, size_t workspace_bytes,
                    int32_t max_tokens, fa_plan** plan_out);
 void fa_plan_destroy(fa_plan* plan);
+/* Slab schedule (new; the reference runs every layer over the whole padded batch, infer.py:455).  A batch larger than
+ * ~chunk_tokens packed rows is cut on utterance boundaries into slabs of about that many rows, and each slab runs through
+ * ALL layers before the next one starts, so a layer's activations are read back from the 126 MB L2 instead of HBM.
+ * Utterances are independent, so the result does not depend on the split.  Needs cu_seqlens_host in the forward calls.
+ * Default 0 = never split (the split costs more in per-launch ramp-up than it saves on B200); environment
+ * override at plan creation: FA_CHUNK_TOKENS. */
+int fa_plan_set_chunk_tokens(fa_plan* plan, int32_t chunk_tokens);
 
 /* Layouts.  Every [rows, dim] activation argument comes with a `*_tmax`:
  *   tmax == 0 : PACKED  [n_tokens, dim], utterance b at rows [cu_seqlens[b], cu_seqlens[b+1])
@@ -178,19 +185,21 @@ void fa_plan_destroy(fa_plan* plan);
  *               on output the padding rows are zero-filled.
  * feats_dev is NOT modified (the reference scales it in place, VLLM/...:388).
  * enc_out_dev f32 [.., d_model] may be NULL: the result stays in the plan's workspace for
- * fa_adaptor_forward(enc_dev = NULL). */
+ * fa_adaptor_forward(enc_dev = NULL).
+ * cu_seqlens_host: HOST copy of cu_seqlens_dev ([n_utts + 1] int32), or NULL.  It is only used to cut the batch into slabs
+ * (fa_plan_set_chunk_tokens); with NULL the batch runs as one slab. */
 int fa_encoder_forward(fa_plan* plan, const float* feats_dev, int32_t feats_tmax, const int32_t* cu_seqlens_dev,
-                       int32_t n_utts, int32_t n_tokens, int32_t max_len, float* enc_out_dev, int32_t enc_out_tmax,
-                       fa_stream_t stream);
+                       const int32_t* cu_seqlens_host, int32_t n_utts, int32_t n_tokens, int32_t max_len,
+                       float* enc_out_dev, int32_t enc_out_tmax, fa_stream_t stream);
 /* enc_dev f32 [.., d_model], or NULL to consume the plan-resident encoder output.
  * out_dev [.., ad_dim]: f32 when out_bf16 == 0, bf16 otherwise. */
 int fa_adaptor_forward(fa_plan* plan, const float* enc_dev, int32_t enc_tmax, const int32_t* cu_seqlens_dev,
-                       int32_t n_utts, int32_t n_tokens, int32_t max_len, void* out_dev, int32_t out_tmax,
-                       int32_t out_bf16, fa_stream_t stream);
+                       const int32_t* cu_seqlens_host, int32_t n_utts, int32_t n_tokens, int32_t max_len, void* out_dev,
+                       int32_t out_tmax, int32_t out_bf16, fa_stream_t stream);
 /* FunASRNano.forward_export: encoder then adaptor, the intermediate never leaves the workspace. */
 int fa_encode_adapt(fa_plan* plan, const float* feats_dev, int32_t feats_tmax, const int32_t* cu_seqlens_dev,
-                    int32_t n_utts, int32_t n_tokens, int32_t max_len, float* enc_out_dev, int32_t enc_out_tmax,
-                    void* out_dev, int32_t out_tmax, int32_t out_bf16, fa_stream_t stream);
+                    const int32_t* cu_seqlens_host, int32_t n_utts, int32_t n_tokens, int32_t max_len, float* enc_out_dev,
+                    int32_t enc_out_tmax, void* out_dev, int32_t out_tmax, int32_t out_bf16, fa_stream_t stream);
 
 /* out rows: utterance b -> [prefix (P rows) | speech rows [cu[b], cu[b]+take_b) | suffix (S rows)] at
  * out_off[b].  take_dev == NULL: take all rows.  All matrices [rows, dim]; speech f32 or bf16,

@@ -89,6 +89,42 @@ def test_fused_tower_equals_separate_calls_and_is_batch_invariant():
     assert torch.equal(z1[0], zf[1, :33])
 
 
+@pytest.mark.parametrize("chunk", [64, 200, 1000])
+def test_slab_schedule_is_invisible(chunk):
+    """fa_plan_set_chunk_tokens: cutting the batch into L2-sized slabs on utterance boundaries must not change a single
+    bit (utterances are independent; row tiles that straddle a slab end only write rows the next slab recomputes)."""
+    import funasr_b200 as fb
+
+    _, _, enc, ad = _pair(2, 1)
+    lens = [167, 40, 1, 98, 130, 5, 64, 129, 33, 255, 17, 80]
+    x, il = _batch(lens)
+    feats = torch.cat([x[b, :t] for b, t in enumerate(lens)]).cuda()
+    tower = fb.AudioTower(enc, ad)
+    tower.plan().set_chunk_tokens(0)
+    want, cu = tower.forward_packed(feats, il.numpy(), out_dtype=torch.float32)
+    want = want.clone()
+    tower.plan().set_chunk_tokens(chunk)
+    got, _ = tower.forward_packed(feats, il.numpy(), out_dtype=torch.float32)
+    assert torch.equal(got, want)
+    # padded in / padded out through the same slabs (forward_export = /root/reference/model.py:251-254)
+    zp, _ = tower.forward_export(x.cuda(), il)
+    for b, t in enumerate(lens):
+        assert torch.equal(zp[b, :t], want[cu[b]:cu[b + 1]])
+        assert torch.all(zp[b, t:] == 0)
+    # separate encoder / adaptor calls with their own plans and padded fp32 hand-over
+    enc._shared_plan = ad._shared_plan = None
+    enc.plan().set_chunk_tokens(chunk)
+    ad.plan().set_chunk_tokens(chunk)
+    y, ol = enc(x.cuda(), il)
+    enc.plan().set_chunk_tokens(0)
+    y0, _ = enc(x.cuda(), il)
+    assert torch.equal(y, y0)
+    z, _ = ad(y, ol)
+    ad.plan().set_chunk_tokens(0)
+    z0, _ = ad(y, ol)
+    assert torch.equal(z, z0)
+
+
 def test_full_depth_50_20_one_utterance():
     """The Nano stack (50 + 20 blocks + adaptor) on one 3 s utterance: error growth through 70 layers stays in budget."""
     o_enc, o_ad, enc, ad = _pair(50, 20)
