@@ -152,10 +152,15 @@ __device__ __forceinline__ unsigned long long gtime() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
+// Per-CTA timeline for profiles/scripts/trace_attention.py: compiled in only with -DFA_ATTN_TRACE (make TRACE=1).
+#ifdef FA_ATTN_TRACE
 #define TRACE(slot)                                                                              \
   do {                                                                                           \
     if (trace && cta_lin < 512) trace[cta_lin * 16 + (slot)] = gtime();                          \
   } while (0)
+#else
+#define TRACE(slot) do { } while (0)
+#endif
 
 // ---------------------------------------------------------------- kernel
 __global__ void __launch_bounds__(THREADS, 2)
@@ -402,11 +407,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
   }
   if (threadIdx.x == 0) {
     TRACE(11);
+#ifdef FA_ATTN_TRACE
     if (trace && cta_lin < 512) {
       unsigned smid;
       asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
       trace[cta_lin * 16 + 12] = smid;
     }
+#endif
   }
 }
 unsigned long long* g_trace = nullptr;
@@ -450,7 +457,9 @@ extern "C" int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_
                           static_cast<__nv_bfloat16*>(ctx_dev), ld_ctx, n_rows, static_cast<cudaStream_t>(stream));
 }
 
+#ifdef FA_ATTN_TRACE
 // debug only (not in the public header): device buffer of 512 x 16 u64 receiving per-CTA %globaltimer stamps
 extern "C" __attribute__((visibility("default"))) void fa_debug_attention_trace(void* buf) {
   fa::attn::g_trace = static_cast<unsigned long long*>(buf);
 }
+#endif
