@@ -4,8 +4,11 @@
 //   warp 0      TMA producer   (cp.async.bulk.tensor 2D, 128B swizzle, mbarrier complete_tx)
 //   warp 1      MMA issuer     (tcgen05.mma cta_group::1 kind::f16, M=128, N=BN, K=16 per instruction,
 //                               fp32 accumulators in TMEM, double buffered: 2 x BN columns)
-//   warps 2..   epilogue       (tcgen05.ld 32x32b -> registers -> bias/ReLU -> 128B-swizzled smem slab
-//                               -> [+ f32 residuals, read row-wise and coalesced] -> TMA store)
+//   warps 2..9  epilogue       (tcgen05.ld 32x32b -> registers -> bias/ReLU -> 128B-swizzled smem slab
+//                               -> [+ f32 residuals, read row-wise and coalesced] -> TMA store);
+//                               two warps per TMEM lane quarter (= per SM sub-partition), each taking every other
+//                               128-byte column unit: ncu showed the 4-warp epilogue (1500 instr/tile/warp, one warp
+//                               per scheduler) pacing the tensor pipe at 51 % active (profiles/r01_b_gemm.md)
 // Three pipelines: smem full/empty (TMA<->MMA), TMEM full/empty (MMA<->epilogue), static tile
 // scheduler (tile = blockIdx.x + i * gridDim.x).  Both operands are K-major (nn.Linear layout),
 // so no transposes are ever materialised.
@@ -22,7 +25,7 @@ namespace gemm {
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle span
 constexpr int UMMA_K = 16;
-constexpr int EPI_WARPS = 4;                    // one per TMEM lane quarter
+constexpr int EPI_WARPS = 8;                    // two per TMEM lane quarter
 constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;
 constexpr int SLAB_BYTES = 32 * 128;            // 32 rows x 128 B, SWIZZLE_128B (64 bf16 or 32 f32 columns)
 constexpr int SMEM_LIMIT = 227 * 1024;
@@ -32,7 +35,7 @@ struct Cfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int SLABS_BYTES = EPI_WARPS * 2 * SLAB_BYTES;  // double-buffered staging slab per epilogue warp
+  static constexpr int SLABS_BYTES = EPI_WARPS * SLAB_BYTES;  // one staging slab per epilogue warp
   static constexpr int MAX_STAGES = (SMEM_LIMIT - 1024 - 256 - SLABS_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = MAX_STAGES > 8 ? 8 : MAX_STAGES;
   static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (power of two >= 32)
@@ -159,7 +162,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 
 // ---------------------------------------------------------------- kernel
-template <int BN>
+// Epilogue variants are compile-time: OUT_F32 (f32 C, optional NRES f32 residuals) or bf16 C (optional RELU).
+template <int BN, bool OUT_F32, bool RELU, int NRES>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_c, const Params p) {
@@ -255,17 +259,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   } else {
     // ===================== epilogue warps =====================
-    // Each warp owns TMEM lanes [32q, 32q+32) = 32 rows of the tile.  Per "unit" (64 bf16 or 32 f32 output
-    // columns = one 128-byte row segment) it fills a 32x128B slab in the SWIZZLE_128B layout and hands it to TMA,
-    // so every global access of the epilogue is a full-line bulk or row-contiguous access.
+    // Warp w owns TMEM lanes [32 (w & 3), +32) = 32 rows of the tile (hardware rule: lane quarter = warp id mod 4) and
+    // every other "unit" (64 bf16 or 32 f32 output columns = one 128-byte row segment) of those rows.  Per unit it fills
+    // a 32x128B slab in the SWIZZLE_128B layout and hands it to TMA, so every global access of the epilogue is a
+    // full-line bulk or row-contiguous access.
     const int q = warp & 3;
-    const int ew = warp - 2;
-    const uint32_t my_slabs = slab_base + ew * 2 * SLAB_BYTES;
-    const int cols_per_unit = p.out_f32 ? 32 : 64;
-    const int units = BN / cols_per_unit;
+    const int hf = (warp - 2) >> 2;  // which half of the units
+    const uint32_t slab = slab_base + (warp - 2) * SLAB_BYTES;
+    constexpr int COLS = OUT_F32 ? 32 : 64;
+    constexpr int UNITS = BN / COLS;
     const uint32_t rsw = static_cast<uint32_t>(lane & 7);  // swizzle phase of this lane's row
     const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
-    uint32_t fills = 0;
+    bool slab_busy = false;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
@@ -276,37 +281,36 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const int row0 = tm * BM + q * 32;
       const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-      for (int u = 0; u < units; ++u, ++fills) {
-        const uint32_t slab = my_slabs + (fills & 1) * SLAB_BYTES;
-        const int col0 = tn * BN + u * cols_per_unit;
+      for (int u = hf; u < UNITS; u += 2) {
+        const int col0 = tn * BN + u * COLS;
         // residual rows for this unit, fetched row-wise (4 rows x 128 B per warp instruction) before the TMEM load
-        float4 rv1[8], rv2[8];
-        if (p.out_f32 && p.res1) {
+        float4 rv1[NRES >= 1 ? 8 : 1], rv2[NRES >= 2 ? 8 : 1];
+        if constexpr (OUT_F32 && NRES >= 1) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const int grow = row0 + 4 * i + (lane >> 3);
             const long long off = static_cast<long long>(grow) * p.ldc + col0 + 4 * (lane & 7);
-            rv1[i] = grow < p.M ? *reinterpret_cast<const float4*>(p.res1 + off) : make_float4(0, 0, 0, 0);
-            if (p.res2) rv2[i] = grow < p.M ? *reinterpret_cast<const float4*>(p.res2 + off) : make_float4(0, 0, 0, 0);
+            rv1[i] = grow < p.M ? __ldg(reinterpret_cast<const float4*>(p.res1 + off)) : make_float4(0, 0, 0, 0);
+            if constexpr (NRES >= 2)
+              rv2[i] = grow < p.M ? __ldg(reinterpret_cast<const float4*>(p.res2 + off)) : make_float4(0, 0, 0, 0);
           }
         }
-        if (fills >= 2) {  // the TMA store that last read this slab must have drained it
-          if (lane == 0) bulk_wait_read<1>();
+        if (slab_busy) {  // the TMA store that last read this slab must have drained it
+          if (lane == 0) bulk_wait_read<0>();
           __syncwarp();
         }
-        if (p.out_f32) {
+        if constexpr (OUT_F32) {
           uint32_t r[32];
           tmem_ld32(tmem_row + u * 32, r);
+          const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float4 bv = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col0) + j) : make_float4(0, 0, 0, 0);
-            float v0 = __uint_as_float(r[4 * j]) + bv.x, v1 = __uint_as_float(r[4 * j + 1]) + bv.y;
-            float v2 = __uint_as_float(r[4 * j + 2]) + bv.z, v3 = __uint_as_float(r[4 * j + 3]) + bv.w;
-            if (p.relu) { v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); v2 = fmaxf(v2, 0.f); v3 = fmaxf(v3, 0.f); }
-            sts128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4), __float_as_uint(v0), __float_as_uint(v1),
-                   __float_as_uint(v2), __float_as_uint(v3));
+            const float4 bv = __ldg(bp + j);
+            sts128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4), __float_as_uint(__uint_as_float(r[4 * j]) + bv.x),
+                   __float_as_uint(__uint_as_float(r[4 * j + 1]) + bv.y), __float_as_uint(__uint_as_float(r[4 * j + 2]) + bv.z),
+                   __float_as_uint(__uint_as_float(r[4 * j + 3]) + bv.w));
           }
-          if (p.res1) {
+          if constexpr (NRES >= 1) {
             __syncwarp();
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -314,7 +318,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               const uint32_t addr = slab + rr * 128u + ((static_cast<uint32_t>(lane & 7) ^ (rr & 7)) << 4);
               float4 v = lds128(addr);
               v.x += rv1[i].x; v.y += rv1[i].y; v.z += rv1[i].z; v.w += rv1[i].w;
-              if (p.res2) { v.x += rv2[i].x; v.y += rv2[i].y; v.z += rv2[i].z; v.w += rv2[i].w; }
+              if constexpr (NRES >= 2) { v.x += rv2[i].x; v.y += rv2[i].y; v.z += rv2[i].z; v.w += rv2[i].w; }
               sts128(addr, __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w));
             }
           }
@@ -323,15 +327,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           for (int half = 0; half < 2; ++half) {
             uint32_t r[32];
             tmem_ld32(tmem_row + u * 64 + half * 32, r);
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + col0 + half * 32);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const float4 b0 = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col0 + half * 32) + 2 * j) : make_float4(0, 0, 0, 0);
-              const float4 b1 = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col0 + half * 32) + 2 * j + 1) : make_float4(0, 0, 0, 0);
+              const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
               float v[8] = {__uint_as_float(r[8 * j]) + b0.x,     __uint_as_float(r[8 * j + 1]) + b0.y,
                             __uint_as_float(r[8 * j + 2]) + b0.z, __uint_as_float(r[8 * j + 3]) + b0.w,
                             __uint_as_float(r[8 * j + 4]) + b1.x, __uint_as_float(r[8 * j + 5]) + b1.y,
                             __uint_as_float(r[8 * j + 6]) + b1.z, __uint_as_float(r[8 * j + 7]) + b1.w};
-              if (p.relu) {
+              if constexpr (RELU) {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
               }
@@ -346,6 +350,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
           bulk_commit();
         }
+        slab_busy = true;
       }
       tcgen05_fence_before();
       __syncwarp();
@@ -380,15 +385,24 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-template <int BN>
-static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int M, int N, int K,
-                    const GemmEpilogue& epi, void* c, int64_t ldc, int row0, cudaStream_t stream) {
+template <int BN, bool OUT_F32, bool RELU, int NRES>
+static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const Params& p, int grid,
+                    cudaStream_t stream) {
   using C = Cfg<BN>;
   static bool attr_done = false;
   if (!attr_done) {
-    FA_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    FA_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, OUT_F32, RELU, NRES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       C::SMEM_BYTES));
     attr_done = true;
   }
+  gemm_bf16_kernel<BN, OUT_F32, RELU, NRES><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, mc, p);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+template <int BN>
+static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int M, int N, int K,
+                    const GemmEpilogue& epi, void* c, int64_t ldc, int row0, cudaStream_t stream) {
   Params p;
   p.M = M; p.N = N; p.K = K;
   p.row0 = row0;
@@ -404,9 +418,16 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   memcpy(&mb, tb.bytes, sizeof(mb));
   memcpy(&mc, tc.bytes, sizeof(mc));
   ProfScope _ps(K_GEMM, stream);
-  gemm_bf16_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, mc, p);
-  FA_CHECK_LAUNCH();
-  return 0;
+  if (epi.out_f32) {
+    FA_REQUIRE(!epi.relu, "gemm: ReLU is only compiled for the bf16 output");
+    FA_REQUIRE(epi.res1 || !epi.res2, "gemm: res2 without res1");
+    if (epi.res2) return launch_v<BN, true, false, 2>(ma, mb, mc, p, grid, stream);
+    if (epi.res1) return launch_v<BN, true, false, 1>(ma, mb, mc, p, grid, stream);
+    return launch_v<BN, true, false, 0>(ma, mb, mc, p, grid, stream);
+  }
+  FA_REQUIRE(!epi.res1 && !epi.res2, "gemm: residuals are only compiled for the f32 output");
+  if (epi.relu) return launch_v<BN, false, true, 0>(ma, mb, mc, p, grid, stream);
+  return launch_v<BN, false, false, 0>(ma, mb, mc, p, grid, stream);
 }
 
 }  // namespace gemm
@@ -455,6 +476,7 @@ int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D&
   FA_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "gemm: unsupported tile N %d", block_n);
   FA_REQUIRE(N % block_n == 0, "gemm: N=%d is not a multiple of the tile %d", N, block_n);
   FA_REQUIRE(K % 8 == 0, "gemm: K=%d must be a multiple of 8", K);
+  FA_REQUIRE(epi.bias != nullptr, "gemm: bias is required (nn.Linear of the reference always has one)");
   FA_REQUIRE(ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(c) & 15) == 0, "gemm: C must be 16-byte aligned, ldc %% 8 == 0");
   switch (block_n) {
     case 64: return gemm::launch_t<64>(ta, tb, tc, M, N, K, epi, c, ldc, row0, stream);
