@@ -226,6 +226,8 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
     pipe = fb.AudioPipeline(fe, tower, dev)
     if args.chunk_tokens is not None:
         tower.plan().set_chunk_tokens(args.chunk_tokens)
+    if args.streams is not None:
+        tower.plan().set_streams(args.streams)
     # distinct seeded noise per utterance and rank (a few base waves re-used cyclically keep host set-up short)
     base = [synth_wave(int(lengths.max()), 1000 + 97 * rank + i) for i in range(min(8, len(lengths)))]
     wavs = [base[i % len(base)][: int(n)] for i, n in enumerate(lengths)]
@@ -307,7 +309,8 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
                        "tokens_per_gpu": rows, "model": "SenseVoice SAN-M 50+20 blocks d512 ff2048 + adaptor 2x(d1024,8h), random init",
                        "frontend": "povey, 80 mel, LFR 7/6, CMVN", "l2": "256 MiB flush before every timed step; weights 467 MB > L2",
                        "sharding": "by utterance, no collective",
-                       "slab_tokens": args.chunk_tokens if args.chunk_tokens is not None else "off (library default)"},
+                       "slab_tokens": args.chunk_tokens if args.chunk_tokens is not None else "off (library default)",
+                       "streams": args.streams if args.streams is not None else "library default"},
             "e2e": {"value": world * audio_s / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": int(host_pcm.numel() * 4), "d2h_bytes_per_step": int(out_host.numel() * 2)},
             "gpu_launches": int(sum(n for _, n in prof.values())),
@@ -340,6 +343,7 @@ def main():
     ap.add_argument("--workload", default="cfg5", choices=["cfg5", "cfg2", "cfg3"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk-tokens", type=int, default=None, help="slab size of the layer schedule (0 = whole batch per layer)")
+    ap.add_argument("--streams", type=int, default=None, help="1 = single stream, 2 = dual-stream half-batch schedule")
     args = ap.parse_args()
     rank, local_rank, world = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("LOCAL_RANK", 0), ("WORLD_SIZE", 1)))
     if args.impl == "reference":

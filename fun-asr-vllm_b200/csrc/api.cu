@@ -2,6 +2,7 @@
 // TMA descriptors built once) and the layer schedule.  No device allocation, no synchronisation.
 #include <cmath>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <functional>
 #include <new>
@@ -231,8 +232,17 @@ struct fa_plan {
   fa_model_w w;
   int cap;
   int chunk_tokens;  // 0: never split a batch
+  int n_streams;     // 1: everything on the caller's stream; 2: two half-batches, the second on `aux` (fork/join by events)
+  int lag;           // dual-stream issue order: half 1 trails half 0 by this many program steps
+  cudaStream_t aux = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   Workspace ws;
   std::vector<Step> enc_prog, ad_prog;
+  ~fa_plan() {
+    if (aux) cudaStreamDestroy(aux);
+    if (ev_fork) cudaEventDestroy(ev_fork);
+    if (ev_join) cudaEventDestroy(ev_join);
+  }
 };
 
 namespace {
@@ -350,6 +360,13 @@ int default_chunk_tokens() {
   return 0;
 }
 
+int default_streams() {
+  // Measured on B200 (profiles/r01_d_dual_stream.md): cfg3 (16 k rows) 16.9 -> 15.2 ms, cfg5 (60 k rows) 52.4 -> 52.3 ms
+  // (power-capped either way).  On by default; FA_STREAMS=1 or fa_plan_set_streams(plan, 1) turn it off.
+  if (const char* e = getenv("FA_STREAMS")) return atoi(e) >= 2 ? 2 : 1;
+  return 2;
+}
+
 }  // namespace
 
 extern "C" size_t fa_plan_workspace_bytes(const fa_model_cfg* cfg, int32_t max_tokens) {
@@ -376,6 +393,8 @@ extern "C" int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void
   p->w = *w;
   p->cap = cap;
   p->chunk_tokens = default_chunk_tokens();
+  p->n_streams = default_streams();
+  p->lag = getenv("FA_STREAM_LAG") ? atoi(getenv("FA_STREAM_LAG")) : 0;
   p->ws = ws;
   if (int rc = build_programs(p)) {
     delete p;
@@ -390,6 +409,12 @@ extern "C" void fa_plan_destroy(fa_plan* plan) { delete plan; }
 extern "C" int fa_plan_set_chunk_tokens(fa_plan* plan, int32_t chunk_tokens) {
   FA_REQUIRE(plan != nullptr && chunk_tokens >= 0, "set_chunk_tokens: bad arguments");
   plan->chunk_tokens = chunk_tokens;
+  return 0;
+}
+
+extern "C" int fa_plan_set_streams(fa_plan* plan, int32_t n_streams) {
+  FA_REQUIRE(plan != nullptr && (n_streams == 1 || n_streams == 2), "set_streams: 1 or 2 streams");
+  plan->n_streams = n_streams;
   return 0;
 }
 
@@ -439,42 +464,130 @@ int make_slabs(const fa_plan* p, const int32_t* cu_host, int n_utts, int M, int 
   return 0;
 }
 
+RunArgs args_of(const Slab& sl, const int32_t* cu, cudaStream_t s) {
+  return RunArgs{sl.M, sl.b1 - sl.b0, sl.max_len, sl.row0, cu + sl.b0, s};
+}
+
+// input stage: xs*sqrt(d) + PE, then norm1 of encoders0 (VM:388-390, :121)
+int encoder_pre(fa_plan* p, const Slab& sl, const RunArgs& a, const float* feats, int feats_tmax) {
+  const fa_model_cfg& c = p->cfg;
+  const float* f = feats + (feats_tmax > 0 ? static_cast<int64_t>(sl.b0) * feats_tmax : static_cast<int64_t>(sl.row0)) * c.d_in;
+  return launch_embed_layernorm(f, feats_tmax, p->w.pe_inv_timescales, a.cu, a.n_utts, a.row0, sqrtf(static_cast<float>(c.d_model)),
+                                p->w.layers[0].ln1_g, p->w.layers[0].ln1_b, p->ws.xn0 + static_cast<int64_t>(a.row0) * c.d_in,
+                                a.M, c.d_in, a.s);
+}
+
+int encoder_post(fa_plan* p, const Slab& sl, const RunArgs& a, float* enc_out, int enc_out_tmax) {
+  const fa_model_cfg& c = p->cfg;
+  if (!enc_out) return 0;
+  float* dst = enc_out + (enc_out_tmax > 0 ? static_cast<int64_t>(sl.b0) * enc_out_tmax : static_cast<int64_t>(sl.row0)) * c.d_model;
+  return launch_repack_rows(p->ws.enc_f32 + static_cast<int64_t>(a.row0) * c.d_model, 0, dst, enc_out_tmax, 0, a.cu, a.n_utts,
+                            a.row0, a.M, c.d_model, a.s);
+}
+
+int adaptor_pre(fa_plan* p, const Slab& sl, const RunArgs& a, const float* enc, int enc_tmax) {
+  const fa_model_cfg& c = p->cfg;
+  if (!enc) return 0;
+  const float* src = enc + (enc_tmax > 0 ? static_cast<int64_t>(sl.b0) * enc_tmax : static_cast<int64_t>(sl.row0)) * c.d_model;
+  return launch_repack_rows(src, enc_tmax, p->ws.enc_bf + static_cast<int64_t>(a.row0) * c.d_model, 0, 1, a.cu, a.n_utts, a.row0,
+                            a.M, c.d_model, a.s);
+}
+
+int adaptor_post(fa_plan* p, const Slab& sl, const RunArgs& a, void* out, int out_tmax, int out_bf16) {
+  const fa_model_cfg& c = p->cfg;
+  const int64_t dst_row = out_tmax > 0 ? static_cast<int64_t>(sl.b0) * out_tmax : static_cast<int64_t>(sl.row0);
+  void* dst = static_cast<unsigned char*>(out) + dst_row * c.ad_dim * (out_bf16 ? 2 : 4);
+  return launch_repack_rows(p->ws.ax + static_cast<int64_t>(a.row0) * c.ad_dim, 0, dst, out_tmax, out_bf16, a.cu, a.n_utts, a.row0,
+                            a.M, c.ad_dim, a.s);
+}
+
 int run_encoder(fa_plan* p, const Slab& sl, const float* feats, int feats_tmax, const int32_t* cu, float* enc_out,
                 int enc_out_tmax, cudaStream_t s) {
-  const fa_model_cfg& c = p->cfg;
-  const RunArgs a{sl.M, sl.b1 - sl.b0, sl.max_len, sl.row0, cu + sl.b0, s};
-  const float* f = feats + (feats_tmax > 0 ? static_cast<int64_t>(sl.b0) * feats_tmax : static_cast<int64_t>(sl.row0)) * c.d_in;
-  // input stage: xs*sqrt(d) + PE, then norm1 of encoders0 (VM:388-390, :121)
-  if (int rc = launch_embed_layernorm(f, feats_tmax, p->w.pe_inv_timescales, a.cu, a.n_utts, a.row0, sqrtf(static_cast<float>(c.d_model)),
-                                      p->w.layers[0].ln1_g, p->w.layers[0].ln1_b, p->ws.xn0 + static_cast<int64_t>(a.row0) * c.d_in,
-                                      a.M, c.d_in, s))
-    return rc;
+  const RunArgs a = args_of(sl, cu, s);
+  if (int rc = encoder_pre(p, sl, a, feats, feats_tmax)) return rc;
   for (const Step& st : p->enc_prog)
     if (int rc = st(a)) return rc;
-  if (enc_out) {
-    float* dst = enc_out + (enc_out_tmax > 0 ? static_cast<int64_t>(sl.b0) * enc_out_tmax : static_cast<int64_t>(sl.row0)) * c.d_model;
-    return launch_repack_rows(p->ws.enc_f32 + static_cast<int64_t>(a.row0) * c.d_model, 0, dst, enc_out_tmax, 0, a.cu, a.n_utts,
-                              a.row0, a.M, c.d_model, s);
-  }
-  return 0;
+  return encoder_post(p, sl, a, enc_out, enc_out_tmax);
 }
 
 int run_adaptor(fa_plan* p, const Slab& sl, const float* enc, int enc_tmax, const int32_t* cu, void* out, int out_tmax,
                 int out_bf16, cudaStream_t s) {
-  const fa_model_cfg& c = p->cfg;
-  const RunArgs a{sl.M, sl.b1 - sl.b0, sl.max_len, sl.row0, cu + sl.b0, s};
-  if (enc) {
-    const float* src = enc + (enc_tmax > 0 ? static_cast<int64_t>(sl.b0) * enc_tmax : static_cast<int64_t>(sl.row0)) * c.d_model;
-    if (int rc = launch_repack_rows(src, enc_tmax, p->ws.enc_bf + static_cast<int64_t>(a.row0) * c.d_model, 0, 1, a.cu, a.n_utts,
-                                    a.row0, a.M, c.d_model, s))
-      return rc;
-  }
+  const RunArgs a = args_of(sl, cu, s);
+  if (int rc = adaptor_pre(p, sl, a, enc, enc_tmax)) return rc;
   for (const Step& st : p->ad_prog)
     if (int rc = st(a)) return rc;
-  const int64_t dst_row = out_tmax > 0 ? static_cast<int64_t>(sl.b0) * out_tmax : static_cast<int64_t>(sl.row0);
-  void* dst = static_cast<unsigned char*>(out) + dst_row * c.ad_dim * (out_bf16 ? 2 : 4);
-  return launch_repack_rows(p->ws.ax + static_cast<int64_t>(a.row0) * c.ad_dim, 0, dst, out_tmax, out_bf16, a.cu, a.n_utts, a.row0,
-                            a.M, c.ad_dim, s);
+  return adaptor_post(p, sl, a, out, out_tmax, out_bf16);
+}
+
+// ---- dual-stream schedule -------------------------------------------------------------------------------------------
+// The batch is cut on an utterance boundary into two halves of about equal cost; half 0 runs on the caller's stream, half 1
+// on the plan's auxiliary stream (forked and joined with events, so for the caller everything is still "enqueued on
+// `stream`").  Utterances are independent, so the result is bit-identical to the single-stream schedule.  The point: the
+// HBM-bound kernels of one half (LayerNorm, FSMN, attention softmax phases) co-reside on the SMs with the tensor-bound GEMM
+// of the other half, and the ramp-up / drain of every dependent launch is covered by the other stream's work.
+bool split_two(const fa_plan* p, const int32_t* cu_host, int n_utts, int M, Slab (&out)[2]) {
+  if (p->n_streams < 2 || cu_host == nullptr || n_utts < 2 || M < 2048) return false;
+  if (cu_host[0] != 0 || cu_host[n_utts] != M) return false;
+  // cost ~ 0.4657 T + 1.5155e-4 T^2 GFLOP per utterance
+  double total = 0.0;
+  for (int b = 0; b < n_utts; ++b) {
+    const double T = cu_host[b + 1] - cu_host[b];
+    if (T <= 0) return false;
+    total += 0.4657152 * T + 1.51552e-4 * T * T;
+  }
+  double acc = 0.0;
+  int cut = 1;
+  for (int b = 0; b < n_utts - 1; ++b) {
+    const double T = cu_host[b + 1] - cu_host[b];
+    const double c = 0.4657152 * T + 1.51552e-4 * T * T;
+    if (acc + 0.5 * c >= 0.5 * total) break;
+    acc += c;
+    cut = b + 1;
+  }
+  auto mk = [&](int b0, int b1) {
+    int ml = 0;
+    for (int u = b0; u < b1; ++u) ml = std::max(ml, cu_host[u + 1] - cu_host[u]);
+    return Slab{b0, b1, cu_host[b0], cu_host[b1] - cu_host[b0], ml};
+  };
+  out[0] = mk(0, cut);
+  out[1] = mk(cut, n_utts);
+  return true;
+}
+
+int ensure_streams(fa_plan* p) {
+  if (p->aux) return 0;
+  FA_CHECK_CUDA(cudaStreamCreateWithFlags(&p->aux, cudaStreamNonBlocking));
+  FA_CHECK_CUDA(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+  FA_CHECK_CUDA(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+  return 0;
+}
+
+// Issue `progs` (each a list of steps) for both halves, half 1 trailing by p->lag steps in issue order.
+int run_dual(fa_plan* p, const Slab (&sl)[2], const int32_t* cu, cudaStream_t s, const std::function<int(int, const RunArgs&)>& pre,
+             const std::vector<const std::vector<Step>*>& progs, const std::function<int(int, const RunArgs&)>& mid,
+             const std::function<int(int, const RunArgs&)>& post) {
+  if (int rc = ensure_streams(p)) return rc;
+  FA_CHECK_CUDA(cudaEventRecord(p->ev_fork, s));
+  FA_CHECK_CUDA(cudaStreamWaitEvent(p->aux, p->ev_fork, 0));
+  const RunArgs a[2] = {args_of(sl[0], cu, s), args_of(sl[1], cu, p->aux)};
+  // flatten: pre, prog[0]..., mid (between programs), prog[1]..., post
+  std::vector<std::function<int(int)>> seq;
+  seq.push_back([&](int k) { return pre(k, a[k]); });
+  for (size_t pi = 0; pi < progs.size(); ++pi) {
+    if (pi > 0) seq.push_back([&](int k) { return mid(k, a[k]); });
+    for (const Step& st : *progs[pi]) seq.push_back([&a, &st](int k) { return st(a[k]); });
+  }
+  seq.push_back([&](int k) { return post(k, a[k]); });
+  const int n = static_cast<int>(seq.size()), lag = std::max(0, p->lag);
+  for (int i = 0; i < n + lag; ++i) {
+    if (i < n)
+      if (int rc = seq[i](0)) return rc;
+    if (i >= lag)
+      if (int rc = seq[i - lag](1)) return rc;
+  }
+  FA_CHECK_CUDA(cudaEventRecord(p->ev_join, p->aux));
+  FA_CHECK_CUDA(cudaStreamWaitEvent(s, p->ev_join, 0));
+  return 0;
 }
 
 }  // namespace
@@ -487,6 +600,13 @@ extern "C" int fa_encoder_forward(fa_plan* p, const float* feats, int32_t feats_
   FA_REQUIRE(p->cfg.n_blocks > 0, "plan was created without encoder weights");
   if (int r = check_tmax(feats_tmax, max_len, "feats")) return r;
   if (int r = check_tmax(enc_out_tmax, max_len, "enc_out")) return r;
+  Slab two[2];
+  if (split_two(p, cu_host, n_utts, M, two)) {
+    const auto none = [](int, const RunArgs&) { return 0; };
+    return run_dual(p, two, cu, static_cast<cudaStream_t>(stream),
+                    [&](int k, const RunArgs& a) { return encoder_pre(p, two[k], a, feats, feats_tmax); }, {&p->enc_prog}, none,
+                    [&](int k, const RunArgs& a) { return encoder_post(p, two[k], a, enc_out, enc_out_tmax); });
+  }
   std::vector<Slab> slabs;
   if (int r = make_slabs(p, cu_host, n_utts, M, max_len, &slabs)) return r;
   for (const Slab& sl : slabs)
@@ -502,6 +622,13 @@ extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, int32_t enc_tmax
   if (int r = check_tmax(out_tmax, max_len, "out")) return r;
   FA_REQUIRE(out != nullptr, "NULL out");
   FA_REQUIRE(p->w.lin1_w != nullptr, "plan was created without adaptor weights");
+  Slab two[2];
+  if (split_two(p, cu_host, n_utts, M, two)) {
+    const auto none = [](int, const RunArgs&) { return 0; };
+    return run_dual(p, two, cu, static_cast<cudaStream_t>(stream),
+                    [&](int k, const RunArgs& a) { return adaptor_pre(p, two[k], a, enc, enc_tmax); }, {&p->ad_prog}, none,
+                    [&](int k, const RunArgs& a) { return adaptor_post(p, two[k], a, out, out_tmax, out_bf16); });
+  }
   std::vector<Slab> slabs;
   if (int r = make_slabs(p, cu_host, n_utts, M, max_len, &slabs)) return r;
   for (const Slab& sl : slabs)
@@ -518,9 +645,15 @@ extern "C" int fa_encode_adapt(fa_plan* p, const float* feats, int32_t feats_tma
   if (int r = check_tmax(feats_tmax, max_len, "feats")) return r;
   if (int r = check_tmax(enc_out_tmax, max_len, "enc_out")) return r;
   if (int r = check_tmax(out_tmax, max_len, "out")) return r;
+  const cudaStream_t s = static_cast<cudaStream_t>(stream);
+  Slab two[2];
+  if (split_two(p, cu_host, n_utts, M, two)) {
+    return run_dual(p, two, cu, s, [&](int k, const RunArgs& a) { return encoder_pre(p, two[k], a, feats, feats_tmax); },
+                    {&p->enc_prog, &p->ad_prog}, [&](int k, const RunArgs& a) { return encoder_post(p, two[k], a, enc_out, enc_out_tmax); },
+                    [&](int k, const RunArgs& a) { return adaptor_post(p, two[k], a, out, out_tmax, out_bf16); });
+  }
   std::vector<Slab> slabs;
   if (int r = make_slabs(p, cu_host, n_utts, M, max_len, &slabs)) return r;
-  const cudaStream_t s = static_cast<cudaStream_t>(stream);
   for (const Slab& sl : slabs) {  // slab-major: a slab's encoder output is still in L2 when its adaptor runs
     if (int rc = run_encoder(p, sl, feats, feats_tmax, cu, enc_out, enc_out_tmax, s)) return rc;
     if (int rc = run_adaptor(p, sl, nullptr, 0, cu, out, out_tmax, out_bf16, s)) return rc;

@@ -344,13 +344,30 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
           }
         }
-        fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
-        __syncwarp();
-        if (lane == 0) {
-          tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
-          bulk_commit();
+        if (row0 + 32 <= p.M) {
+          fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
+            bulk_commit();
+          }
+          slab_busy = true;
+        } else {
+          // The 32-row box straddles the end of this launch's rows (the last rows of a slab): rows >= M belong to the
+          // next slab, which may be running concurrently on another stream, so they must not be written.  Lane = row.
+          __syncwarp();
+          if (row0 + lane < p.M) {
+            unsigned char* g = static_cast<unsigned char*>(p.c) +
+                               (static_cast<long long>(p.row0 + row0 + lane) * p.ldc + col0) * (OUT_F32 ? 4 : 2);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 v = lds128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4));
+              *reinterpret_cast<float4*>(g + 16 * j) = v;
+            }
+          }
+          __syncwarp();
+          slab_busy = false;
         }
-        slab_busy = true;
       }
       tcgen05_fence_before();
       __syncwarp();

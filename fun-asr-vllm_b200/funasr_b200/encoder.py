@@ -202,11 +202,18 @@ class Plan:
         self.cap = cap
         if getattr(self, "chunk_tokens", None) is not None:
             _lib.check(lib.fa_plan_set_chunk_tokens(self.handle, self.chunk_tokens), "fa_plan_set_chunk_tokens")
+        if getattr(self, "n_streams", None) is not None:
+            _lib.check(lib.fa_plan_set_streams(self.handle, self.n_streams), "fa_plan_set_streams")
 
     def set_chunk_tokens(self, n: int):
         """Slab size of the layer schedule (``fa_plan_set_chunk_tokens``); 0 runs every layer over the whole batch."""
         self.chunk_tokens = int(n)
         _lib.check(_lib.load().fa_plan_set_chunk_tokens(self.handle, int(n)), "fa_plan_set_chunk_tokens")
+
+    def set_streams(self, n: int):
+        """1 = everything on the caller's stream; 2 = two half-batches on two streams (``fa_plan_set_streams``)."""
+        self.n_streams = int(n)
+        _lib.check(_lib.load().fa_plan_set_streams(self.handle, int(n)), "fa_plan_set_streams")
 
     def ensure(self, n_tokens: int):
         if n_tokens > self.cap:

@@ -40,7 +40,7 @@ extern "C" {
 
 typedef void* fa_stream_t; /* cudaStream_t */
 
-#define FA_ABI_VERSION 2
+#define FA_ABI_VERSION 3
 
 int fa_abi_version(void);
 const char* fa_last_error(void);
@@ -178,6 +178,12 @@ void fa_plan_destroy(fa_plan* plan);
  * Default 0 = never split (the split costs more in per-launch ramp-up than it saves on B200); environment
  * override at plan creation: FA_CHUNK_TOKENS. */
 int fa_plan_set_chunk_tokens(fa_plan* plan, int32_t chunk_tokens);
+/* Dual-stream schedule (new).  n_streams == 2: a batch of >= 2 utterances and >= 2048 rows is cut on an utterance boundary
+ * into two halves of equal cost; half 0 runs on the caller's stream, half 1 on a plan-owned auxiliary stream that is forked
+ * from and joined back into the caller's stream with events inside the same call, so the call still only ENQUEUES work
+ * ordered on `stream`.  The HBM-bound kernels of one half then share the SMs with the tensor-bound GEMMs of the other.
+ * Results are bit-identical to n_streams == 1.  Needs cu_seqlens_host.  Environment override at plan creation: FA_STREAMS. */
+int fa_plan_set_streams(fa_plan* plan, int32_t n_streams);
 
 /* Layouts.  Every [rows, dim] activation argument comes with a `*_tmax`:
  *   tmax == 0 : PACKED  [n_tokens, dim], utterance b at rows [cu_seqlens[b], cu_seqlens[b+1])

@@ -125,6 +125,39 @@ def test_slab_schedule_is_invisible(chunk):
     assert torch.equal(z, z0)
 
 
+@pytest.mark.parametrize("lag", [0, 3])
+def test_dual_stream_schedule_is_invisible(lag, monkeypatch):
+    """fa_plan_set_streams(2): the two half-batches run on two streams (forked / joined inside the call); results are
+    bit-identical to the single-stream schedule, for the fused tower and for separate encoder / adaptor calls."""
+    import funasr_b200 as fb
+
+    monkeypatch.setenv("FA_STREAM_LAG", str(lag))
+    _, _, enc, ad = _pair(2, 1)
+    lens = [167] * 9 + [40, 500, 98, 130, 5, 64, 129, 333, 255, 17, 80]  # 2854 rows >= the 2048-row threshold
+    x, il = _batch(lens)
+    feats = torch.cat([x[b, :t] for b, t in enumerate(lens)]).cuda()
+    tower = fb.AudioTower(enc, ad)
+    tower.plan().set_streams(1)
+    want, cu = tower.forward_packed(feats, il.numpy(), out_dtype=torch.float32)
+    want = want.clone()
+    tower.plan().set_streams(2)
+    for _ in range(3):  # repeated calls re-use the plan's auxiliary stream / events
+        got, _ = tower.forward_packed(feats, il.numpy(), out_dtype=torch.float32)
+        assert torch.equal(got, want)
+    zp, _ = tower.forward_export(x.cuda(), il)
+    for b, t in enumerate(lens):
+        assert torch.equal(zp[b, :t], want[cu[b]:cu[b + 1]])
+        assert torch.all(zp[b, t:] == 0)
+    enc._shared_plan = ad._shared_plan = None
+    y0, ol = enc(x.cuda(), il)
+    z0, _ = ad(y0, ol)
+    enc.plan().set_streams(2)
+    ad.plan().set_streams(2)
+    y, _ = enc(x.cuda(), il)
+    z, _ = ad(y, ol)
+    assert torch.equal(y, y0) and torch.equal(z, z0)
+
+
 def test_full_depth_50_20_one_utterance():
     """The Nano stack (50 + 20 blocks + adaptor) on one 3 s utterance: error growth through 70 layers stays in budget."""
     o_enc, o_ad, enc, ad = _pair(50, 20)
