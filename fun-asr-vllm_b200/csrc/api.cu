@@ -182,7 +182,7 @@ using Step = std::function<int(const RunArgs&)>;
 
 // One nn.Linear resolved against fixed workspace buffers: A map (activations), one B map per tile width, C map.
 struct GemmOp {
-  TensorMap2D ta, tc;
+  TensorMap2D ta, tc, tr1, tr2;
   TensorMap2D tb[3];
   bool tb_ok[3] = {false, false, false};
   int N = 0, K = 0;
@@ -205,6 +205,9 @@ int make_gemm_op(GemmOp* op, int cap, const void* a, int lda, const void* w, int
   FA_REQUIRE(w != nullptr, "NULL weight pointer (N=%d K=%d)", N, K);
   if (int r = make_tensor_map_bf16(&op->ta, a, cap, K, lda, 128)) return r;
   if (int r = make_tensor_map(&op->tc, c, out_f32 ? 4 : 2, cap, N, N, 32)) return r;
+  FA_REQUIRE(out_f32 || (!res1 && !res2), "residuals need the f32 output");
+  if (res1) if (int r = make_tensor_map(&op->tr1, res1, 4, cap, N, N, 32)) return r;
+  if (res2) if (int r = make_tensor_map(&op->tr2, res2, 4, cap, N, N, 32)) return r;
   for (int i = 0; i < 3; ++i) {
     const int bn = 64 << i;
     if (N % bn != 0) continue;
@@ -215,14 +218,11 @@ int make_gemm_op(GemmOp* op, int cap, const void* a, int lda, const void* w, int
 }
 
 int run_gemm_op(const GemmOp& op, const RunArgs& a) {
-  const int bn = gemm_block_n(a.M, op.N);
+  const int bn = gemm_block_n(a.M, op.N, (op.epi.res1 ? 1 : 0) + (op.epi.res2 ? 1 : 0));
   const int idx = bn == 64 ? 0 : (bn == 128 ? 1 : 2);
   FA_REQUIRE(bn != 0 && op.tb_ok[idx], "gemm N=%d unsupported", op.N);
-  GemmEpilogue e = op.epi;
-  const int64_t off = static_cast<int64_t>(a.row0) * op.ldc;
-  if (e.res1) e.res1 += off;
-  if (e.res2) e.res2 += off;
-  return launch_gemm(op.ta, op.tb[idx], op.tc, bn, a.M, op.N, op.K, e, op.c, op.ldc, a.row0, a.s);
+  return launch_gemm(op.ta, op.tb[idx], op.tc, op.epi.res1 ? &op.tr1 : nullptr, op.epi.res2 ? &op.tr2 : nullptr, bn, a.M, op.N,
+                     op.K, op.epi, op.c, op.ldc, a.row0, a.s);
 }
 
 }  // namespace

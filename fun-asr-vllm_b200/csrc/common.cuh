@@ -67,10 +67,12 @@ int make_tensor_map_bf16(TensorMap2D* out, const void* base, uint64_t rows, uint
 int make_tensor_map(TensorMap2D* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld,
                     uint32_t box_rows);
 
-int gemm_block_n(int M, int N);  // tile-N heuristic (64 / 128 / 256)
-// Rows [row0, row0 + M) of the A / C matrices the maps describe; epi.res* point at row row0 already.
-int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int block_n, int M, int N, int K,
-                const GemmEpilogue& epi, void* c, int64_t ldc, int row0, cudaStream_t stream);
+int gemm_block_n(int M, int N, int n_res);  // tile-N heuristic (64 / 128 / 256); n_res = f32 residuals in the epilogue
+// Rows [row0, row0 + M) of the A / C / residual matrices the maps describe (tr1 / tr2: f32 maps like tc, NULL when
+// epi.res1 / epi.res2 are; the epi.res* pointers only select the epilogue variant).
+int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, const TensorMap2D* tr1,
+                const TensorMap2D* tr2, int block_n, int M, int N, int K, const GemmEpilogue& epi, void* c, int64_t ldc,
+                int row0, cudaStream_t stream);
 
 int launch_layernorm(const float* x, const float* g, const float* b, const float* g2, const float* b2,
                      __nv_bfloat16* y_bf16, float* y_f32, int M, int D, cudaStream_t stream);

@@ -4,8 +4,10 @@
 //   warp 0      TMA producer   (cp.async.bulk.tensor 2D, 128B swizzle, mbarrier complete_tx)
 //   warp 1      MMA issuer     (tcgen05.mma cta_group::1 kind::f16, M=128, N=BN, K=16 per instruction,
 //                               fp32 accumulators in TMEM, double buffered: 2 x BN columns)
-//   warps 2..9  epilogue       (tcgen05.ld 32x32b -> registers -> bias/ReLU -> 128B-swizzled smem slab
-//                               -> [+ f32 residuals, read row-wise and coalesced] -> TMA store);
+//   warps 2..9  epilogue       (tcgen05.ld 32x32b -> registers -> bias/ReLU -> 128B-swizzled smem slab -> TMA store).
+//                               f32 residuals are PREFETCHED by TMA into the very slab the result leaves from (a 2-slot
+//                               ring per warp, loads issued two units ahead), so the epilogue is lds + add + sts in place
+//                               and no warp ever waits on a global load it has just issued;
 //                               two warps per TMEM lane quarter (= per SM sub-partition), each taking every other
 //                               128-byte column unit: ncu showed the 4-warp epilogue (1500 instr/tile/warp, one warp
 //                               per scheduler) pacing the tensor pipe at 51 % active (profiles/r01_b_gemm.md)
@@ -16,6 +18,8 @@
 // Replaces the cuBLAS calls behind nn.Linear in VLLM/model_executor/models/funasr.py:164-168 (qkv),
 // :159-163,238 (out), :415-431 (FFN), :543-552,585-587 (adaptor linears).
 #include <cuda.h>
+
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -30,16 +34,23 @@ constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;
 constexpr int SLAB_BYTES = 32 * 128;            // 32 rows x 128 B, SWIZZLE_128B (64 bf16 or 32 f32 columns)
 constexpr int SMEM_LIMIT = 227 * 1024;
 
-template <int BN>
+constexpr int RES_RING = 2;   // residual / output slots per epilogue warp (f32 epilogue with residuals)
+constexpr int BAR_BYTES = 512;
+
+template <int BN, int NRES>
 struct Cfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int SLABS_BYTES = EPI_WARPS * SLAB_BYTES;  // one staging slab per epilogue warp
-  static constexpr int MAX_STAGES = (SMEM_LIMIT - 1024 - 256 - SLABS_BYTES) / STAGE_BYTES;
+  // staging slabs per epilogue warp: one (no residual) or RES_RING slots of NRES slabs (slab 0 of a slot receives
+  // residual 1 and then holds the result; slab 1 receives residual 2)
+  static constexpr int SLABS_PER_WARP = NRES == 0 ? 1 : RES_RING * NRES;
+  static constexpr int SLABS_BYTES = EPI_WARPS * SLABS_PER_WARP * SLAB_BYTES;
+  static constexpr int MAX_STAGES = (SMEM_LIMIT - 1024 - BAR_BYTES - SLABS_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = MAX_STAGES > 8 ? 8 : MAX_STAGES;
+  static_assert(STAGES >= 2, "not enough shared memory left for the operand ring");
   static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (power of two >= 32)
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SLABS_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SLABS_BYTES + 1024 /*align slack*/ + BAR_BYTES;
 };
 
 struct Params {
@@ -166,8 +177,9 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 template <int BN, bool OUT_F32, bool RELU, int NRES>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const __grid_constant__ CUtensorMap tmap_c, const Params p) {
-  using C = Cfg<BN>;
+                 const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_r1,
+                 const __grid_constant__ CUtensorMap tmap_r2, const Params p) {
+  using C = Cfg<BN, NRES>;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024B alignment
   const uint32_t slab_base = smem_base + C::STAGES * C::STAGE_BYTES;  // 1024-aligned: STAGE_BYTES is a multiple of 1024
@@ -177,6 +189,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::STAGES + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * C::STAGES + 2 + a); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 4);
+  auto res_bar = [&](int w, int slot) { return bar_base + 8u * (2 * C::STAGES + 5 + w * RES_RING + slot); };
+  static_assert(8 * (2 * C::STAGES + 5 + EPI_WARPS * RES_RING) <= BAR_BYTES, "barrier region too small");
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -195,6 +209,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
       mbar_init(tempty_bar(a), EPI_WARPS);  // one arrive per epilogue warp
+    }
+    if (NRES > 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_r1) : "memory");
+      if (NRES > 1) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_r2) : "memory");
+      for (int w = 0; w < EPI_WARPS; ++w)
+        for (int sl = 0; sl < RES_RING; ++sl) mbar_init(res_bar(w, sl), 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -262,87 +282,93 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // Warp w owns TMEM lanes [32 (w & 3), +32) = 32 rows of the tile (hardware rule: lane quarter = warp id mod 4) and
     // every other "unit" (64 bf16 or 32 f32 output columns = one 128-byte row segment) of those rows.  Per unit it fills
     // a 32x128B slab in the SWIZZLE_128B layout and hands it to TMA, so every global access of the epilogue is a
-    // full-line bulk or row-contiguous access.
+    // full-line bulk access.
     const int q = warp & 3;
-    const int hf = (warp - 2) >> 2;  // which half of the units
-    const uint32_t slab = slab_base + (warp - 2) * SLAB_BYTES;
+    const int ew = warp - 2;
+    const int hf = ew >> 2;  // which half of the units
     constexpr int COLS = OUT_F32 ? 32 : 64;
     constexpr int UNITS = BN / COLS;
     const uint32_t rsw = static_cast<uint32_t>(lane & 7);  // swizzle phase of this lane's row
     const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
-    bool slab_busy = false;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
-      const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1;
-      mbar_wait(tfull_bar(acc), acc_phase);
-      tcgen05_fence_after();
-      const int row0 = tm * BM + q * 32;
-      const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
-#pragma unroll 1
-      for (int u = hf; u < UNITS; u += 2) {
-        const int col0 = tn * BN + u * COLS;
-        // residual rows for this unit, fetched row-wise (4 rows x 128 B per warp instruction) before the TMEM load
-        float4 rv1[NRES >= 1 ? 8 : 1], rv2[NRES >= 2 ? 8 : 1];
-        if constexpr (OUT_F32 && NRES >= 1) {
+    // a 32-row box that straddles the end of this launch's rows (the last rows of a slab) must not be written by TMA:
+    // rows >= M belong to the next slab, which may be running concurrently on another stream.  Lane = row.
+    auto store_rows_guarded = [&](uint32_t slab, int row0, int col0) {
+      __syncwarp();
+      if (row0 + lane < p.M) {
+        unsigned char* g = static_cast<unsigned char*>(p.c) +
+                           (static_cast<long long>(p.row0 + row0 + lane) * p.ldc + col0) * (OUT_F32 ? 4 : 2);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int grow = row0 + 4 * i + (lane >> 3);
-            const long long off = static_cast<long long>(grow) * p.ldc + col0 + 4 * (lane & 7);
-            rv1[i] = grow < p.M ? __ldg(reinterpret_cast<const float4*>(p.res1 + off)) : make_float4(0, 0, 0, 0);
-            if constexpr (NRES >= 2)
-              rv2[i] = grow < p.M ? __ldg(reinterpret_cast<const float4*>(p.res2 + off)) : make_float4(0, 0, 0, 0);
-          }
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(g + 16 * j) = lds128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4));
+      }
+      fence_async_smem();
+      __syncwarp();
+    };
+    if constexpr (OUT_F32 && NRES >= 1) {
+      // ---- f32 result with TMA-prefetched residuals.  This warp's units form one flat sequence n = it * UH + i over its
+      // tiles; unit n lives in ring slot n % RES_RING.
+      constexpr int UH = UNITS / 2;
+      constexpr uint32_t SLOT_BYTES = NRES * SLAB_BYTES;
+      const uint32_t ring = slab_base + ew * RES_RING * SLOT_BYTES;
+      const int my_tiles = (num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+      const int total = my_tiles * UH;
+      auto coords = [&](int n, int& row0, int& col0, int& u) {
+        const int it = n / UH, i = n - it * UH;
+        const int tile = blockIdx.x + it * gridDim.x;
+        const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
+        u = hf + 2 * i;
+        row0 = tm * BM + q * 32;
+        col0 = tn * BN + u * COLS;
+      };
+      auto issue_load = [&](int n) {  // lane 0 only
+        if (n >= total) return;
+        int row0, col0, u;
+        coords(n, row0, col0, u);
+        const int slot = n % RES_RING;
+        const uint32_t dst = ring + slot * SLOT_BYTES;
+        mbar_expect_tx(res_bar(ew, slot), SLOT_BYTES);
+        tma_load_2d(dst, &tmap_r1, res_bar(ew, slot), col0, p.row0 + row0);
+        if constexpr (NRES >= 2) tma_load_2d(dst + SLAB_BYTES, &tmap_r2, res_bar(ew, slot), col0, p.row0 + row0);
+      };
+      if (lane == 0) {
+#pragma unroll
+        for (int n = 0; n < RES_RING; ++n) issue_load(n);
+      }
+      for (int n = 0; n < total; ++n) {
+        const int it = n / UH, i = n - it * UH;
+        const int acc = it & 1;
+        int row0, col0, u;
+        coords(n, row0, col0, u);
+        const int slot = n % RES_RING;
+        const uint32_t slab = ring + slot * SLOT_BYTES;
+        if (i == 0) {
+          mbar_wait(tfull_bar(acc), (it >> 1) & 1);
+          tcgen05_fence_after();
         }
-        if (slab_busy) {  // the TMA store that last read this slab must have drained it
-          if (lane == 0) bulk_wait_read<0>();
+        mbar_wait(res_bar(ew, slot), (n / RES_RING) & 1);  // residual slab(s) of this unit have landed
+        const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+        uint32_t r[32];
+        tmem_ld32(tmem_row + u * 32, r);
+        const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t addr = slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4);
+          const float4 bv = __ldg(bp + j);
+          float4 v = lds128(addr);
+          v.x += __uint_as_float(r[4 * j]) + bv.x;
+          v.y += __uint_as_float(r[4 * j + 1]) + bv.y;
+          v.z += __uint_as_float(r[4 * j + 2]) + bv.z;
+          v.w += __uint_as_float(r[4 * j + 3]) + bv.w;
+          if constexpr (NRES >= 2) {
+            const float4 w2 = lds128(addr + SLAB_BYTES);
+            v.x += w2.x; v.y += w2.y; v.z += w2.z; v.w += w2.w;
+          }
+          sts128(addr, __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w));
+        }
+        if (i == UH - 1) {  // last TMEM read of this tile: hand the accumulator back to the MMA warp
+          tcgen05_fence_before();
           __syncwarp();
-        }
-        if constexpr (OUT_F32) {
-          uint32_t r[32];
-          tmem_ld32(tmem_row + u * 32, r);
-          const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 bv = __ldg(bp + j);
-            sts128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4), __float_as_uint(__uint_as_float(r[4 * j]) + bv.x),
-                   __float_as_uint(__uint_as_float(r[4 * j + 1]) + bv.y), __float_as_uint(__uint_as_float(r[4 * j + 2]) + bv.z),
-                   __float_as_uint(__uint_as_float(r[4 * j + 3]) + bv.w));
-          }
-          if constexpr (NRES >= 1) {
-            __syncwarp();
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const uint32_t rr = 4 * i + (lane >> 3);
-              const uint32_t addr = slab + rr * 128u + ((static_cast<uint32_t>(lane & 7) ^ (rr & 7)) << 4);
-              float4 v = lds128(addr);
-              v.x += rv1[i].x; v.y += rv1[i].y; v.z += rv1[i].z; v.w += rv1[i].w;
-              if constexpr (NRES >= 2) { v.x += rv2[i].x; v.y += rv2[i].y; v.z += rv2[i].z; v.w += rv2[i].w; }
-              sts128(addr, __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w));
-            }
-          }
-        } else {
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            uint32_t r[32];
-            tmem_ld32(tmem_row + u * 64 + half * 32, r);
-            const float4* bp = reinterpret_cast<const float4*>(p.bias + col0 + half * 32);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
-              float v[8] = {__uint_as_float(r[8 * j]) + b0.x,     __uint_as_float(r[8 * j + 1]) + b0.y,
-                            __uint_as_float(r[8 * j + 2]) + b0.z, __uint_as_float(r[8 * j + 3]) + b0.w,
-                            __uint_as_float(r[8 * j + 4]) + b1.x, __uint_as_float(r[8 * j + 5]) + b1.y,
-                            __uint_as_float(r[8 * j + 6]) + b1.z, __uint_as_float(r[8 * j + 7]) + b1.w};
-              if constexpr (RELU) {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
-              }
-              sts128(slab + row_off + ((static_cast<uint32_t>(half * 4 + j) ^ rsw) << 4), pack_bf16x2(v[0], v[1]),
-                     pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-            }
-          }
+          if (lane == 0) mbar_arrive(tempty_bar(acc));
         }
         if (row0 + 32 <= p.M) {
           fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
@@ -350,28 +376,83 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if (lane == 0) {
             tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
             bulk_commit();
+            bulk_wait_read<0>();  // the slot may be refilled once the store has read it
           }
-          slab_busy = true;
         } else {
-          // The 32-row box straddles the end of this launch's rows (the last rows of a slab): rows >= M belong to the
-          // next slab, which may be running concurrently on another stream, so they must not be written.  Lane = row.
-          __syncwarp();
-          if (row0 + lane < p.M) {
-            unsigned char* g = static_cast<unsigned char*>(p.c) +
-                               (static_cast<long long>(p.row0 + row0 + lane) * p.ldc + col0) * (OUT_F32 ? 4 : 2);
+          store_rows_guarded(slab, row0, col0);
+        }
+        if (lane == 0) issue_load(n + RES_RING);
+        __syncwarp();
+      }
+    } else {
+      const uint32_t slab = slab_base + ew * SLAB_BYTES;
+      bool slab_busy = false;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(tfull_bar(acc), acc_phase);
+        tcgen05_fence_after();
+        const int row0 = tm * BM + q * 32;
+        const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+        for (int u = hf; u < UNITS; u += 2) {
+          const int col0 = tn * BN + u * COLS;
+          if (slab_busy) {  // the TMA store that last read this slab must have drained it
+            if (lane == 0) bulk_wait_read<0>();
+            __syncwarp();
+          }
+          if constexpr (OUT_F32) {
+            uint32_t r[32];
+            tmem_ld32(tmem_row + u * 32, r);
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 v = lds128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4));
-              *reinterpret_cast<float4*>(g + 16 * j) = v;
+              const float4 bv = __ldg(bp + j);
+              sts128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4), __float_as_uint(__uint_as_float(r[4 * j]) + bv.x),
+                     __float_as_uint(__uint_as_float(r[4 * j + 1]) + bv.y), __float_as_uint(__uint_as_float(r[4 * j + 2]) + bv.z),
+                     __float_as_uint(__uint_as_float(r[4 * j + 3]) + bv.w));
+            }
+          } else {
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              uint32_t r[32];
+              tmem_ld32(tmem_row + u * 64 + half * 32, r);
+              const float4* bp = reinterpret_cast<const float4*>(p.bias + col0 + half * 32);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
+                float v[8] = {__uint_as_float(r[8 * j]) + b0.x,     __uint_as_float(r[8 * j + 1]) + b0.y,
+                              __uint_as_float(r[8 * j + 2]) + b0.z, __uint_as_float(r[8 * j + 3]) + b0.w,
+                              __uint_as_float(r[8 * j + 4]) + b1.x, __uint_as_float(r[8 * j + 5]) + b1.y,
+                              __uint_as_float(r[8 * j + 6]) + b1.z, __uint_as_float(r[8 * j + 7]) + b1.w};
+                if constexpr (RELU) {
+#pragma unroll
+                  for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+                }
+                sts128(slab + row_off + ((static_cast<uint32_t>(half * 4 + j) ^ rsw) << 4), pack_bf16x2(v[0], v[1]),
+                       pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+              }
             }
           }
-          __syncwarp();
-          slab_busy = false;
+          if (row0 + 32 <= p.M) {
+            fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
+              bulk_commit();
+            }
+            slab_busy = true;
+          } else {
+            store_rows_guarded(slab, row0, col0);
+            slab_busy = false;
+          }
         }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(acc));
       }
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(acc));
     }
     if (lane == 0) bulk_wait<0>();
     __syncwarp();
@@ -403,23 +484,24 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 template <int BN, bool OUT_F32, bool RELU, int NRES>
-static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const Params& p, int grid,
-                    cudaStream_t stream) {
-  using C = Cfg<BN>;
+static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mr1,
+                    const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
+  using C = Cfg<BN, NRES>;
   static bool attr_done = false;
   if (!attr_done) {
     FA_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, OUT_F32, RELU, NRES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        C::SMEM_BYTES));
     attr_done = true;
   }
-  gemm_bf16_kernel<BN, OUT_F32, RELU, NRES><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, mc, p);
+  gemm_bf16_kernel<BN, OUT_F32, RELU, NRES><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, mc, mr1, mr2, p);
   FA_CHECK_LAUNCH();
   return 0;
 }
 
 template <int BN>
-static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int M, int N, int K,
-                    const GemmEpilogue& epi, void* c, int64_t ldc, int row0, cudaStream_t stream) {
+static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, const TensorMap2D* tr1,
+                    const TensorMap2D* tr2, int M, int N, int K, const GemmEpilogue& epi, void* c, int64_t ldc, int row0,
+                    cudaStream_t stream) {
   Params p;
   p.M = M; p.N = N; p.K = K;
   p.row0 = row0;
@@ -429,22 +511,29 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32;
   const int tiles = p.tiles_m * p.tiles_n;
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  CUtensorMap ma, mb, mc;
+  CUtensorMap ma, mb, mc, mr1, mr2;
   static_assert(sizeof(CUtensorMap) == sizeof(TensorMap2D::bytes), "CUtensorMap size");
   memcpy(&ma, ta.bytes, sizeof(ma));
   memcpy(&mb, tb.bytes, sizeof(mb));
   memcpy(&mc, tc.bytes, sizeof(mc));
+  memcpy(&mr1, (tr1 ? tr1 : &tc)->bytes, sizeof(mr1));
+  memcpy(&mr2, (tr2 ? tr2 : &tc)->bytes, sizeof(mr2));
+  FA_REQUIRE((epi.res1 == nullptr) == (tr1 == nullptr) && (epi.res2 == nullptr) == (tr2 == nullptr),
+             "gemm: every residual needs its tensor map");
   ProfScope _ps(K_GEMM, stream);
   if (epi.out_f32) {
     FA_REQUIRE(!epi.relu, "gemm: ReLU is only compiled for the bf16 output");
     FA_REQUIRE(epi.res1 || !epi.res2, "gemm: res2 without res1");
-    if (epi.res2) return launch_v<BN, true, false, 2>(ma, mb, mc, p, grid, stream);
-    if (epi.res1) return launch_v<BN, true, false, 1>(ma, mb, mc, p, grid, stream);
-    return launch_v<BN, true, false, 0>(ma, mb, mc, p, grid, stream);
+    if (epi.res2) {
+      if constexpr (BN <= 128) return launch_v<BN, true, false, 2>(ma, mb, mc, mr1, mr2, p, grid, stream);
+      else FA_REQUIRE(false, "gemm: two residuals are compiled for tile N <= 128 only");
+    }
+    if (epi.res1) return launch_v<BN, true, false, 1>(ma, mb, mc, mr1, mr2, p, grid, stream);
+    return launch_v<BN, true, false, 0>(ma, mb, mc, mr1, mr2, p, grid, stream);
   }
   FA_REQUIRE(!epi.res1 && !epi.res2, "gemm: residuals are only compiled for the f32 output");
-  if (epi.relu) return launch_v<BN, false, true, 0>(ma, mb, mc, p, grid, stream);
-  return launch_v<BN, false, false, 0>(ma, mb, mc, p, grid, stream);
+  if (epi.relu) return launch_v<BN, false, true, 0>(ma, mb, mc, mr1, mr2, p, grid, stream);
+  return launch_v<BN, false, false, 0>(ma, mb, mc, mr1, mr2, p, grid, stream);
 }
 
 }  // namespace gemm
@@ -476,19 +565,25 @@ int make_tensor_map_bf16(TensorMap2D* out, const void* base, uint64_t rows, uint
   return make_tensor_map(out, base, 2, rows, cols, ld, box_rows);
 }
 
-int gemm_block_n(int M, int N) {
-  // Fill the 148 SMs: prefer the widest tile that still yields >= ~1 wave of tiles.
+int gemm_block_n(int M, int N, int n_res) {
+  // Fill the 148 SMs: prefer the widest tile that still yields >= ~1 wave of tiles.  Two prefetched residuals leave
+  // room for the 256-wide operand ring only twice, so those GEMMs (K = d_model, HBM-bound anyway) use 128.
   const int tiles_m = ceil_div(M, gemm::BM);
   const int sms = sm_count();
-  if (N % 256 == 0 && tiles_m * (N / 256) >= 2 * sms) return 256;
+  if (const char* e = getenv("FA_GEMM_BN")) {  // probe override (profiles/scripts/probe_kernels.py)
+    const int bn = atoi(e);
+    if ((bn == 64 || bn == 128 || (bn == 256 && n_res < 2)) && N % bn == 0) return bn;
+  }
+  if (N % 256 == 0 && tiles_m * (N / 256) >= 2 * sms && n_res < 2) return 256;
   if (N % 128 == 0 && tiles_m * (N / 128) >= sms) return 128;
   if (N % 64 == 0) return 64;
   if (N % 128 == 0) return 128;
   return 0;
 }
 
-int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, int block_n, int M, int N, int K,
-                const GemmEpilogue& epi, void* c, int64_t ldc, int row0, cudaStream_t stream) {
+int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, const TensorMap2D* tr1,
+                const TensorMap2D* tr2, int block_n, int M, int N, int K, const GemmEpilogue& epi, void* c, int64_t ldc,
+                int row0, cudaStream_t stream) {
   FA_REQUIRE(M > 0 && N > 0 && K > 0 && row0 >= 0, "gemm: empty problem %dx%dx%d", M, N, K);
   FA_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "gemm: unsupported tile N %d", block_n);
   FA_REQUIRE(N % block_n == 0, "gemm: N=%d is not a multiple of the tile %d", N, block_n);
@@ -496,9 +591,9 @@ int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D&
   FA_REQUIRE(epi.bias != nullptr, "gemm: bias is required (nn.Linear of the reference always has one)");
   FA_REQUIRE(ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(c) & 15) == 0, "gemm: C must be 16-byte aligned, ldc %% 8 == 0");
   switch (block_n) {
-    case 64: return gemm::launch_t<64>(ta, tb, tc, M, N, K, epi, c, ldc, row0, stream);
-    case 128: return gemm::launch_t<128>(ta, tb, tc, M, N, K, epi, c, ldc, row0, stream);
-    default: return gemm::launch_t<256>(ta, tb, tc, M, N, K, epi, c, ldc, row0, stream);
+    case 64: return gemm::launch_t<64>(ta, tb, tc, tr1, tr2, M, N, K, epi, c, ldc, row0, stream);
+    case 128: return gemm::launch_t<128>(ta, tb, tc, tr1, tr2, M, N, K, epi, c, ldc, row0, stream);
+    default: return gemm::launch_t<256>(ta, tb, tc, tr1, tr2, M, N, K, epi, c, ldc, row0, stream);
   }
 }
 
@@ -509,13 +604,18 @@ extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int
                           int32_t K, int32_t relu, int32_t out_f32, fa_stream_t stream) {
   using namespace fa;
   FA_REQUIRE(a_dev && w_dev && c_dev, "gemm: NULL pointer");
-  const int bn = gemm_block_n(M, N);
+  const int n_res = (res1_dev ? 1 : 0) + (res2_dev ? 1 : 0);
+  const int bn = gemm_block_n(M, N, n_res);
   FA_REQUIRE(bn != 0, "gemm: N=%d must be a multiple of 64", N);
-  TensorMap2D ta, tb, tc;
+  FA_REQUIRE(n_res == 0 || out_f32, "gemm: residuals need the f32 output");
+  TensorMap2D ta, tb, tc, tr1, tr2;
+  if (res1_dev) if (int r = make_tensor_map(&tr1, res1_dev, 4, M, N, ldc, 32)) return r;
+  if (res2_dev) if (int r = make_tensor_map(&tr2, res2_dev, 4, M, N, ldc, 32)) return r;
   if (int r = make_tensor_map_bf16(&ta, a_dev, M, K, lda, gemm::BM)) return r;
   if (int r = make_tensor_map_bf16(&tb, w_dev, N, K, ldw, bn)) return r;
   if (int r = make_tensor_map(&tc, c_dev, out_f32 ? 4 : 2, M, N, ldc, 32)) return r;
   GemmEpilogue e;
   e.bias = bias_dev; e.res1 = res1_dev; e.res2 = res2_dev; e.relu = relu; e.out_f32 = out_f32;
-  return launch_gemm(ta, tb, tc, bn, M, N, K, e, c_dev, ldc, 0, static_cast<cudaStream_t>(stream));
+  return launch_gemm(ta, tb, tc, res1_dev ? &tr1 : nullptr, res2_dev ? &tr2 : nullptr, bn, M, N, K, e, c_dev, ldc, 0,
+                     static_cast<cudaStream_t>(stream));
 }
