@@ -266,12 +266,16 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
         step_device()
     torch.cuda.synchronize()
     # ---- launches per step + per-kernel-class device time (profiled steps, NOT the timed ones)
+    # (single-stream schedule while profiling: event pairs around launches that overlap on two streams would double count)
+    tower.plan().set_streams(1)
     _lib.profile_enable(True)
     for _ in range(2):
         flush.zero_()
         step_device()
     prof = _lib.profile_collect()
     _lib.profile_enable(False)
+    tower.plan().set_streams(args.streams if args.streams is not None else 2)
+    step_device()
     prof = {k: (ms / 2, n // 2) for k, (ms, n) in prof.items()}
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -310,7 +314,7 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
                        "frontend": "povey, 80 mel, LFR 7/6, CMVN", "l2": "256 MiB flush before every timed step; weights 467 MB > L2",
                        "sharding": "by utterance, no collective",
                        "slab_tokens": args.chunk_tokens if args.chunk_tokens is not None else "off (library default)",
-                       "streams": args.streams if args.streams is not None else "library default"},
+                       "streams": args.streams if args.streams is not None else 2},
             "e2e": {"value": world * audio_s / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": int(host_pcm.numel() * 4), "d2h_bytes_per_step": int(out_host.numel() * 2)},
             "gpu_launches": int(sum(n for _, n in prof.values())),

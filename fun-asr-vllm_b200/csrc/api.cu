@@ -118,7 +118,6 @@ struct Workspace {
   __nv_bfloat16* enc_bf; // [cap, d_model]   encoder output, bf16 (adaptor input)
   float* enc_f32;        // [cap, d_model]   encoder output, f32
   float* ax;             // [cap, ad_dim]
-  float* ax2;            // [cap, ad_dim]
   __nv_bfloat16* axn;    // [cap, ad_dim]
   __nv_bfloat16* aqkv;   // [cap, 3*ad_dim]
   __nv_bfloat16* actx;   // [cap, ad_dim]
@@ -147,7 +146,6 @@ Workspace carve(const fa_model_cfg& c, int cap, unsigned char* base) {
   w.enc_bf = reinterpret_cast<__nv_bfloat16*>(take(n * c.d_model * 2));
   w.enc_f32 = reinterpret_cast<float*>(take(n * c.d_model * 4));
   w.ax = reinterpret_cast<float*>(take(n * c.ad_dim * 4));
-  w.ax2 = reinterpret_cast<float*>(take(n * c.ad_dim * 4));
   w.axn = reinterpret_cast<__nv_bfloat16*>(take(n * c.ad_dim * 2));
   w.aqkv = reinterpret_cast<__nv_bfloat16*>(take(n * 3 * c.ad_dim * 2));
   w.actx = reinterpret_cast<__nv_bfloat16*>(take(n * c.ad_dim * 2));
@@ -192,7 +190,7 @@ struct GemmOp {
 };
 
 int make_gemm_op(GemmOp* op, int cap, const void* a, int lda, const void* w, int N, int K, const float* bias, void* c,
-                 bool out_f32, bool relu, const float* res1, const float* res2) {
+                 bool out_f32, bool relu, const float* res1, const float* res2, bool accumulate) {
   op->N = N;
   op->K = K;
   op->c = c;
@@ -202,6 +200,7 @@ int make_gemm_op(GemmOp* op, int cap, const void* a, int lda, const void* w, int
   op->epi.res2 = res2;
   op->epi.relu = relu ? 1 : 0;
   op->epi.out_f32 = out_f32 ? 1 : 0;
+  op->epi.accumulate = accumulate ? 1 : 0;
   FA_REQUIRE(w != nullptr, "NULL weight pointer (N=%d K=%d)", N, K);
   if (int r = make_tensor_map_bf16(&op->ta, a, cap, K, lda, 128)) return r;
   if (int r = make_tensor_map(&op->tc, c, out_f32 ? 4 : 2, cap, N, N, 32)) return r;
@@ -251,10 +250,10 @@ struct Builder {
   fa_plan* p;
   int rc = 0;
   void gemm(std::vector<Step>& prog, const void* a, int lda, const void* w, int N, int K, const float* bias, void* c,
-            bool out_f32, bool relu = false, const float* res1 = nullptr, const float* res2 = nullptr) {
+            bool out_f32, bool relu = false, const float* res1 = nullptr, const float* res2 = nullptr, bool accumulate = false) {
     if (rc) return;
     GemmOp op;
-    rc = make_gemm_op(&op, p->cap, a, lda, w, N, K, bias, c, out_f32, relu, res1, res2);
+    rc = make_gemm_op(&op, p->cap, a, lda, w, N, K, bias, c, out_f32, relu, res1, res2, accumulate);
     if (!rc) prog.push_back([op](const RunArgs& r) { return run_gemm_op(op, r); });
   }
   void ln(std::vector<Step>& prog, const float* x, const float* g, const float* b, const float* g2, const float* b2,
@@ -303,12 +302,14 @@ int build_programs(fa_plan* p) {
     }
     // masked MHA                                                           VM:250-252,222-236
     B.attention(E, ws.qkv, ws.ctx, c.n_heads, d);
-    // x' = [x +] ctx Wo^T + b + mem    (no residual when in_size != size)   VM:238,253,123-136
-    B.gemm(E, ws.ctx, d, L.out_w, d, d, L.out_b, xo, true, false, ws.mem, (i == 0) ? nullptr : x);
+    // x (+)= ctx Wo^T + b + mem   (no residual when in_size != size: layer 0 overwrites x)   VM:238,253,123-136
+    // The residual stream is updated IN PLACE: the epilogue hands acc + bias + mem to a TMA reduce-add, so x is never
+    // staged through the SM.
+    B.gemm(E, ws.ctx, d, L.out_w, d, d, L.out_b, x, true, false, ws.mem, nullptr, /*accumulate=*/i != 0);
     // LN2, FFN                                                              VM:138-140,412-431
-    B.ln(E, xo, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.xn, nullptr, d);
+    B.ln(E, x, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.xn, nullptr, d);
     B.gemm(E, ws.xn, d, L.ffn1_w, c.d_ff, d, L.ffn1_b, ws.h, false, true);
-    B.gemm(E, ws.h, c.d_ff, L.ffn2_w, d, c.d_ff, L.ffn2_b, x, true, false, xo);  // residual stream back in x
+    B.gemm(E, ws.h, c.d_ff, L.ffn2_w, d, c.d_ff, L.ffn2_b, x, true, false, nullptr, nullptr, /*accumulate=*/true);
     // next layer's norm1, with after_norm / tp_norm folded in                VM:400,408
     const bool last_main = (i == c.n_blocks - 1);
     const bool last = (i == nl - 1);
@@ -332,7 +333,6 @@ int build_programs(fa_plan* p) {
     std::vector<Step>& A = p->ad_prog;
     const int D = c.ad_dim;
     float* ax = ws.ax;
-    float* axo = ws.ax2;
     // linear1 + ReLU, linear2                                                 VM:585-587
     B.gemm(A, ws.enc_bf, c.d_model, w.lin1_w, c.ad_ffn, c.d_model, w.lin1_b, ws.h, false, true);
     B.gemm(A, ws.h, c.ad_ffn, w.lin2_w, D, c.ad_ffn, w.lin2_b, ax, true);
@@ -343,10 +343,10 @@ int build_programs(fa_plan* p) {
       B.ln(A, ax, L.ln1_g, L.ln1_b, nullptr, nullptr, ws.axn, nullptr, D);
       B.gemm(A, ws.axn, D, L.qkv_w, 3 * D, D, L.qkv_b, ws.aqkv, false);
       B.attention(A, ws.aqkv, ws.actx, c.ad_heads, D);
-      B.gemm(A, ws.actx, D, L.out_w, D, D, L.out_b, axo, true, false, ax);
-      B.ln(A, axo, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.axn, nullptr, D);
+      B.gemm(A, ws.actx, D, L.out_w, D, D, L.out_b, ax, true, false, nullptr, nullptr, /*accumulate=*/true);
+      B.ln(A, ax, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.axn, nullptr, D);
       B.gemm(A, ws.axn, D, L.ffn1_w, c.ad_ff, D, L.ffn1_b, ws.ah, false, true);
-      B.gemm(A, ws.ah, c.ad_ff, L.ffn2_w, D, c.ad_ff, L.ffn2_b, ax, true, false, axo);
+      B.gemm(A, ws.ah, c.ad_ff, L.ffn2_w, D, c.ad_ff, L.ffn2_b, ax, true, false, nullptr, nullptr, /*accumulate=*/true);
     }
   }
   return B.rc;

@@ -54,6 +54,7 @@ struct GemmEpilogue {
   const float* res2 = nullptr;  // f32 [M, N]
   int relu = 0;
   int out_f32 = 0;
+  int accumulate = 0;  // f32 output only: C += acc + bias (+ res*) instead of C = ...; the residual stream is updated in place
 };
 
 struct TensorMap2D {  // opaque 128-byte CUtensorMap

@@ -64,6 +64,7 @@ struct Params {
   long long ldc;
   int relu;
   int out_f32;
+  int accumulate;  // C += result (TMA reduce-add in L2) instead of C = result
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -102,6 +103,12 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int x, int y) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap), "r"(src), "r"(x),
                "r"(y)
+               : "memory");
+}
+// C tile += smem tile: the f32 add happens in the L2 (one add per element per launch -> deterministic)
+__device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, uint32_t src, int x, int y) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap), "r"(src),
+               "r"(x), "r"(y)
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
@@ -298,8 +305,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         unsigned char* g = static_cast<unsigned char*>(p.c) +
                            (static_cast<long long>(p.row0 + row0 + lane) * p.ldc + col0) * (OUT_F32 ? 4 : 2);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4*>(g + 16 * j) = lds128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4));
+        for (int j = 0; j < 8; ++j) {
+          float4 v = lds128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4));
+          float4* gp = reinterpret_cast<float4*>(g + 16 * j);
+          if (OUT_F32 && p.accumulate) {  // these elements have no other writer in this launch
+            const float4 o = *gp;
+            v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+          }
+          *gp = v;
+        }
       }
       fence_async_smem();
       __syncwarp();
@@ -374,7 +388,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
+            if (p.accumulate) tma_reduce_add_2d(&tmap_c, slab, col0, p.row0 + row0);
+            else tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
             bulk_commit();
             bulk_wait_read<0>();  // the slot may be refilled once the store has read it
           }
@@ -440,7 +455,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
             __syncwarp();
             if (lane == 0) {
-              tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
+              if (OUT_F32 && p.accumulate) tma_reduce_add_2d(&tmap_c, slab, col0, p.row0 + row0);
+              else tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
               bulk_commit();
             }
             slab_busy = true;
@@ -508,7 +524,8 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   p.tiles_m = ceil_div(M, BM);
   p.tiles_n = N / BN;
   p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
-  p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32;
+  p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32; p.accumulate = epi.accumulate;
+  FA_REQUIRE(!epi.accumulate || epi.out_f32, "gemm: accumulate needs the f32 output");
   const int tiles = p.tiles_m * p.tiles_n;
   const int grid = tiles < sm_count() ? tiles : sm_count();
   CUtensorMap ma, mb, mc, mr1, mr2;
@@ -604,6 +621,10 @@ extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int
                           int32_t K, int32_t relu, int32_t out_f32, fa_stream_t stream) {
   using namespace fa;
   FA_REQUIRE(a_dev && w_dev && c_dev, "gemm: NULL pointer");
+  // a residual that IS the output buffer is applied as an in-place accumulate (C += ...)
+  int accumulate = 0;
+  if (res2_dev && res2_dev == c_dev) { res2_dev = nullptr; accumulate = 1; }
+  if (res1_dev && res1_dev == c_dev) { res1_dev = res2_dev; res2_dev = nullptr; accumulate = 1; }
   const int n_res = (res1_dev ? 1 : 0) + (res2_dev ? 1 : 0);
   const int bn = gemm_block_n(M, N, n_res);
   FA_REQUIRE(bn != 0, "gemm: N=%d must be a multiple of 64", N);
@@ -615,7 +636,7 @@ extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int
   if (int r = make_tensor_map_bf16(&tb, w_dev, N, K, ldw, bn)) return r;
   if (int r = make_tensor_map(&tc, c_dev, out_f32 ? 4 : 2, M, N, ldc, 32)) return r;
   GemmEpilogue e;
-  e.bias = bias_dev; e.res1 = res1_dev; e.res2 = res2_dev; e.relu = relu; e.out_f32 = out_f32;
+  e.bias = bias_dev; e.res1 = res1_dev; e.res2 = res2_dev; e.relu = relu; e.out_f32 = out_f32; e.accumulate = accumulate;
   return launch_gemm(ta, tb, tc, res1_dev ? &tr1 : nullptr, res2_dev ? &tr2 : nullptr, bn, M, N, K, e, c_dev, ldc, 0,
                      static_cast<cudaStream_t>(stream));
 }

