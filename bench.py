@@ -303,6 +303,16 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
             pass
         peak_tf, peak_src = (peaks.get("bf16_tflops_sustained"), "measured sustained") if peaks else (1400.0, "fallback sustained")
         gemm_flop, attn_flop = flops_of(T)
+        # DRAM traffic per launch from the committed `ncu --set full` capture (profiles/ncu_traffic.json; bytes, cfg5-sized
+        # launches only: the capture ran each kernel alone on 60 120 rows)
+        traffic_gemm = traffic_fe = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            if args.workload == "cfg5":
+                traffic_gemm = tr["gemm_mean_layer_launch_MB"] * 1e6
+                traffic_fe = (tr["kernels"]["frontend_1h"]["dram_read_MB"] + tr["kernels"]["frontend_1h"]["dram_write_MB"]) * 1e6
+        except Exception:
+            pass
         gemm_ms, gemm_n = prof["gemm"]
         achieved = gemm_flop / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
         line = {
@@ -319,7 +329,7 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
                     "h2d_bytes_per_step": int(host_pcm.numel() * 4), "d2h_bytes_per_step": int(out_host.numel() * 2)},
             "gpu_launches": int(sum(n for _, n in prof.values())),
             "roofline": {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05, all 70x4+10 GEMMs of a step)", "achieved": achieved,
-                         "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf if peak_tf else None, "traffic": None,
+                         "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf if peak_tf else None, "traffic": traffic_gemm,
                          "peak_source": peak_src, "launches": gemm_n, "ms_per_step": gemm_ms},
             "kernel_ms_per_step": {k: round(ms, 4) for k, (ms, n) in prof.items()},
             "kernel_launches_per_step": {k: n for k, (ms, n) in prof.items()},
@@ -330,7 +340,7 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
             fe_bytes = float(4 * lengths.sum() + 4 * 560 * T.sum())
             hbm = peaks.get("hbm_gbs", 6650.0)
             line["roofline_frontend"] = {"bound": "hbm", "kernel": "fbank_kernel<0>", "achieved": fe_bytes / (fe_ms * 1e-3) / 1e9,
-                                         "peak": hbm, "unit": "GB/s", "frac": fe_bytes / (fe_ms * 1e-3) / 1e9 / hbm, "traffic": None}
+                                         "peak": hbm, "unit": "GB/s", "frac": fe_bytes / (fe_ms * 1e-3) / 1e9 / hbm, "traffic": traffic_fe}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(lengths, cmvn)
         print(json.dumps(line))
