@@ -220,8 +220,9 @@ int run_gemm_op(const GemmOp& op, const RunArgs& a) {
   const int bn = gemm_block_n(a.M, op.N, (op.epi.res1 ? 1 : 0) + (op.epi.res2 ? 1 : 0));
   const int idx = bn == 64 ? 0 : (bn == 128 ? 1 : 2);
   FA_REQUIRE(bn != 0 && op.tb_ok[idx], "gemm N=%d unsupported", op.N);
-  return launch_gemm(op.ta, op.tb[idx], op.tc, op.epi.res1 ? &op.tr1 : nullptr, op.epi.res2 ? &op.tr2 : nullptr, bn, a.M, op.N,
-                     op.K, op.epi, op.c, op.ldc, a.row0, a.s);
+  const bool pair = gemm_use_pair(a.M, bn) && op.tb_ok[1];
+  return launch_gemm(op.ta, op.tb[pair ? 1 : idx], op.tc, op.epi.res1 ? &op.tr1 : nullptr, op.epi.res2 ? &op.tr2 : nullptr, bn, a.M,
+                     op.N, op.K, op.epi, op.c, op.ldc, a.row0, pair, a.s);
 }
 
 }  // namespace

@@ -71,9 +71,10 @@ int make_tensor_map(TensorMap2D* out, const void* base, int elem_bytes, uint64_t
 int gemm_block_n(int M, int N, int n_res);  // tile-N heuristic (64 / 128 / 256); n_res = f32 residuals in the epilogue
 // Rows [row0, row0 + M) of the A / C / residual matrices the maps describe (tr1 / tr2: f32 maps like tc, NULL when
 // epi.res1 / epi.res2 are; the epi.res* pointers only select the epilogue variant).
+bool gemm_use_pair(int M, int block_n);  // CTA-pair (cta_group::2) kernel for this launch? then tb must box block_n / 2 rows
 int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, const TensorMap2D* tr1,
                 const TensorMap2D* tr2, int block_n, int M, int N, int K, const GemmEpilogue& epi, void* c, int64_t ldc,
-                int row0, cudaStream_t stream);
+                int row0, bool pair, cudaStream_t stream);
 
 int launch_layernorm(const float* x, const float* g, const float* b, const float* g2, const float* b2,
                      __nv_bfloat16* y_bf16, float* y_f32, int M, int D, cudaStream_t stream);

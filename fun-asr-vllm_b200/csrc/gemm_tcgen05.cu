@@ -37,10 +37,14 @@ constexpr int SMEM_LIMIT = 227 * 1024;
 constexpr int RES_RING = 2;   // residual / output slots per epilogue warp (f32 epilogue with residuals)
 constexpr int BAR_BYTES = 512;
 
-template <int BN, int NRES>
+// CTAS = 2: a CTA pair (one cluster, the two SMs of a TPC) computes a 256 x BN tile with tcgen05.mma.cta_group::2.  Each
+// CTA stages its own 128 rows of A and only HALF of the B tile, so the operand bytes an SM pulls through its 64 B/clk
+// L2 port drop from 48 KB to 32 KB per 128x256x64 of MMA work (ncu, profiles/r01_e_campaign.md: the 1-CTA kernel moves
+// 54 B/clk/SM into the SMs at 63 % tensor-pipe activity, i.e. it is L2->SM ingress bound).
+template <int BN, int NRES, int CTAS>
 struct Cfg {
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = BN / CTAS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   // staging slabs per epilogue warp: one (no residual) or RES_RING slots of NRES slabs (slab 0 of a slot receives
   // residual 1 and then holds the result; slab 1 receives residual 2)
@@ -140,6 +144,46 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
       : "memory");
 }
+// ---- CTA-pair (cta_group::2) variants
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// shared::cta address -> shared::cluster address of the same offset in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+// TMA load whose completion bytes are signalled on a barrier of the pair's leader CTA (cluster address)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const void* tmap, uint32_t cluster_bar, int x, int y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(tmap), "r"(cluster_bar), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {  // arrives on the same barrier offset in both CTAs
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"(static_cast<uint16_t>(3))
+               : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(
@@ -181,12 +225,12 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 
 // ---------------------------------------------------------------- kernel
 // Epilogue variants are compile-time: OUT_F32 (f32 C, optional NRES f32 residuals) or bf16 C (optional RELU).
-template <int BN, bool OUT_F32, bool RELU, int NRES>
+template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_r1,
                  const __grid_constant__ CUtensorMap tmap_r2, const Params p) {
-  using C = Cfg<BN, NRES>;
+  using C = Cfg<BN, NRES, CTAS>;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024B alignment
   const uint32_t slab_base = smem_base + C::STAGES * C::STAGE_BYTES;  // 1024-aligned: STAGE_BYTES is a multiple of 1024
@@ -203,7 +247,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_kb = (p.K + BK - 1) / BK;
-  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int num_tiles = p.tiles_m * p.tiles_n;  // tiles of (BM * CTAS) x BN
+  const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;  // position in the CTA pair; rank 0 issues the MMAs
+  const int cl = CTAS == 2 ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);    // tile-scheduler slot
+  const int ncl = CTAS == 2 ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  auto tile_row = [&](int tm) { return (tm * CTAS + static_cast<int>(rank)) * BM; };  // first row this CTA owns in tile row tm
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
@@ -215,7 +263,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), EPI_WARPS);  // one arrive per epilogue warp
+      mbar_init(tempty_bar(a), EPI_WARPS * CTAS);  // one arrive per epilogue warp (of both CTAs of a pair)
     }
     if (NRES > 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_r1) : "memory");
@@ -226,12 +274,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(C::TMEM_COLS)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if constexpr (CTAS == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(C::TMEM_COLS)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(C::TMEM_COLS)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if constexpr (CTAS == 2) cluster_sync(); else __syncthreads();  // barriers of BOTH CTAs are initialised past this point
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -240,26 +294,34 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = cl; tile < num_tiles; tile += ncl) {
         const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
           const uint32_t sb = sa + C::A_BYTES;
-          mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
-          tma_load_2d(sa, &tmap_a, full_bar(stage), kb * BK, p.row0 + tm * BM);
-          tma_load_2d(sb, &tmap_b, full_bar(stage), kb * BK, tn * BN);
+          if constexpr (CTAS == 2) {
+            // both CTAs' bytes are counted on the LEADER's full barrier (the only one the MMA warp waits on)
+            const uint32_t lead_bar = mapa(full_bar(stage), 0);
+            if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
+            tma_load_2d_pair(sa, &tmap_a, lead_bar, kb * BK, p.row0 + tile_row(tm));
+            tma_load_2d_pair(sb, &tmap_b, lead_bar, kb * BK, tn * BN + static_cast<int>(rank) * (BN / 2));
+          } else {
+            mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
+            tma_load_2d(sa, &tmap_a, full_bar(stage), kb * BK, p.row0 + tm * BM);
+            tma_load_2d(sb, &tmap_b, full_bar(stage), kb * BK, tn * BN);
+          }
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc(BM, BN);
+    // ===================== MMA issuer (the pair's leader only) =====================
+    constexpr uint32_t idesc = make_idesc(BM * CTAS, BN);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = (rank == 0 ? cl : num_tiles); tile < num_tiles; tile += ncl, ++it) {
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(tempty_bar(acc), acc_phase ^ 1);  // epilogue has drained this accumulator
@@ -275,10 +337,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t adesc = make_smem_desc(sa + k * UMMA_K * 2);
             const uint64_t bdesc = make_smem_desc(sb + k * UMMA_K * 2);
-            umma_f16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
+            if constexpr (CTAS == 2) umma_f16_pair(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
+            else umma_f16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
           }
-          umma_commit(empty_bar(stage));                       // frees the smem slot when the MMAs retire
-          if (kb == num_kb - 1) umma_commit(tfull_bar(acc));   // accumulator complete
+          if constexpr (CTAS == 2) {
+            umma_commit_pair(empty_bar(stage));                       // frees the slot in BOTH CTAs
+            if (kb == num_kb - 1) umma_commit_pair(tfull_bar(acc));   // both epilogues may drain their half
+          } else {
+            umma_commit(empty_bar(stage));                       // frees the smem slot when the MMAs retire
+            if (kb == num_kb - 1) umma_commit(tfull_bar(acc));   // accumulator complete
+          }
         }
         __syncwarp();
         if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
@@ -324,14 +392,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       constexpr int UH = UNITS / 2;
       constexpr uint32_t SLOT_BYTES = NRES * SLAB_BYTES;
       const uint32_t ring = slab_base + ew * RES_RING * SLOT_BYTES;
-      const int my_tiles = (num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+      const int my_tiles = (num_tiles - cl + ncl - 1) / ncl;
       const int total = my_tiles * UH;
       auto coords = [&](int n, int& row0, int& col0, int& u) {
         const int it = n / UH, i = n - it * UH;
-        const int tile = blockIdx.x + it * gridDim.x;
+        const int tile = cl + it * ncl;
         const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
         u = hf + 2 * i;
-        row0 = tm * BM + q * 32;
+        row0 = tile_row(tm) + q * 32;
         col0 = tn * BN + u * COLS;
       };
       auto issue_load = [&](int n) {  // lane 0 only
@@ -382,7 +450,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (i == UH - 1) {  // last TMEM read of this tile: hand the accumulator back to the MMA warp
           tcgen05_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty_bar(acc));
+          if (lane == 0) {
+            if constexpr (CTAS == 2) mbar_arrive_cluster(mapa(tempty_bar(acc), 0));
+            else mbar_arrive(tempty_bar(acc));
+          }
         }
         if (row0 + 32 <= p.M) {
           fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
@@ -403,13 +474,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const uint32_t slab = slab_base + ew * SLAB_BYTES;
       bool slab_busy = false;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = cl; tile < num_tiles; tile += ncl, ++it) {
         const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(tfull_bar(acc), acc_phase);
         tcgen05_fence_after();
-        const int row0 = tm * BM + q * 32;
+        const int row0 = tile_row(tm) + q * 32;
         const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
 #pragma unroll 1
         for (int u = hf; u < UNITS; u += 2) {
@@ -467,7 +538,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tempty_bar(acc));
+        if (lane == 0) {
+          if constexpr (CTAS == 2) mbar_arrive_cluster(mapa(tempty_bar(acc), 0));
+          else mbar_arrive(tempty_bar(acc));
+        }
       }
     }
     if (lane == 0) bulk_wait<0>();
@@ -475,10 +549,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   }
 
   tcgen05_fence_before();
-  __syncthreads();
+  if constexpr (CTAS == 2) cluster_sync(); else __syncthreads();  // the leader's MMAs read the peer's smem until here
   if (warp == 1) {
     tcgen05_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS) : "memory");
+    if constexpr (CTAS == 2)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS) : "memory");
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS) : "memory");
   }
 }
 
@@ -499,35 +576,58 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-template <int BN, bool OUT_F32, bool RELU, int NRES>
+template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS>
 static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mr1,
                     const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
-  using C = Cfg<BN, NRES>;
+  using C = Cfg<BN, NRES, CTAS>;
+  auto kern = gemm_bf16_kernel<BN, OUT_F32, RELU, NRES, CTAS>;
   static bool attr_done = false;
   if (!attr_done) {
-    FA_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, OUT_F32, RELU, NRES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       C::SMEM_BYTES));
+    FA_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_done = true;
   }
-  gemm_bf16_kernel<BN, OUT_F32, RELU, NRES><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, mc, mr1, mr2, p);
-  FA_CHECK_LAUNCH();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = C::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;  // the CTA pair of cta_group::2 is one cluster
+  attr[0].val.clusterDim.x = CTAS;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  FA_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, mr1, mr2, p));
   return 0;
+}
+
+// pair == true: BN is 256 and `mb` boxes BN/2 rows (each CTA of a pair stages half of the B tile)
+template <int BN, bool OUT_F32, bool RELU, int NRES>
+static int launch_p(bool pair, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mr1,
+                    const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
+  if constexpr (BN == 256) {
+    if (pair) return launch_v<BN, OUT_F32, RELU, NRES, 2>(ma, mb, mc, mr1, mr2, p, grid, stream);
+  }
+  return launch_v<BN, OUT_F32, RELU, NRES, 1>(ma, mb, mc, mr1, mr2, p, grid, stream);
 }
 
 template <int BN>
 static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, const TensorMap2D* tr1,
                     const TensorMap2D* tr2, int M, int N, int K, const GemmEpilogue& epi, void* c, int64_t ldc, int row0,
-                    cudaStream_t stream) {
+                    bool pair, cudaStream_t stream) {
   Params p;
   p.M = M; p.N = N; p.K = K;
   p.row0 = row0;
-  p.tiles_m = ceil_div(M, BM);
+  FA_REQUIRE(!pair || BN == 256, "gemm: the CTA-pair kernel is compiled for tile N 256 only");
+  p.tiles_m = ceil_div(M, pair ? 2 * BM : BM);
   p.tiles_n = N / BN;
   p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
   p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32; p.accumulate = epi.accumulate;
   FA_REQUIRE(!epi.accumulate || epi.out_f32, "gemm: accumulate needs the f32 output");
   const int tiles = p.tiles_m * p.tiles_n;
-  const int grid = tiles < sm_count() ? tiles : sm_count();
+  int grid = tiles < sm_count() ? tiles : sm_count();
+  if (pair) grid = 2 * (tiles < sm_count() / 2 ? tiles : sm_count() / 2);
   CUtensorMap ma, mb, mc, mr1, mr2;
   static_assert(sizeof(CUtensorMap) == sizeof(TensorMap2D::bytes), "CUtensorMap size");
   memcpy(&ma, ta.bytes, sizeof(ma));
@@ -542,15 +642,15 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
     FA_REQUIRE(!epi.relu, "gemm: ReLU is only compiled for the bf16 output");
     FA_REQUIRE(epi.res1 || !epi.res2, "gemm: res2 without res1");
     if (epi.res2) {
-      if constexpr (BN <= 128) return launch_v<BN, true, false, 2>(ma, mb, mc, mr1, mr2, p, grid, stream);
+      if constexpr (BN <= 128) return launch_p<BN, true, false, 2>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
       else FA_REQUIRE(false, "gemm: two residuals are compiled for tile N <= 128 only");
     }
-    if (epi.res1) return launch_v<BN, true, false, 1>(ma, mb, mc, mr1, mr2, p, grid, stream);
-    return launch_v<BN, true, false, 0>(ma, mb, mc, mr1, mr2, p, grid, stream);
+    if (epi.res1) return launch_p<BN, true, false, 1>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
+    return launch_p<BN, true, false, 0>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
   }
   FA_REQUIRE(!epi.res1 && !epi.res2, "gemm: residuals are only compiled for the f32 output");
-  if (epi.relu) return launch_v<BN, false, true, 0>(ma, mb, mc, mr1, mr2, p, grid, stream);
-  return launch_v<BN, false, false, 0>(ma, mb, mc, mr1, mr2, p, grid, stream);
+  if (epi.relu) return launch_p<BN, false, true, 0>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
+  return launch_p<BN, false, false, 0>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
 }
 
 }  // namespace gemm
@@ -598,9 +698,16 @@ int gemm_block_n(int M, int N, int n_res) {
   return 0;
 }
 
+// CTA pairs (cta_group::2, 256 x 256 tiles) for the wide tile once there are enough rows; FA_GEMM_PAIR=0/1 overrides.
+bool gemm_use_pair(int M, int block_n) {
+  if (block_n != 256) return false;
+  if (const char* e = getenv("FA_GEMM_PAIR")) return atoi(e) != 0;
+  return M >= 1024;
+}
+
 int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, const TensorMap2D* tr1,
                 const TensorMap2D* tr2, int block_n, int M, int N, int K, const GemmEpilogue& epi, void* c, int64_t ldc,
-                int row0, cudaStream_t stream) {
+                int row0, bool pair, cudaStream_t stream) {
   FA_REQUIRE(M > 0 && N > 0 && K > 0 && row0 >= 0, "gemm: empty problem %dx%dx%d", M, N, K);
   FA_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "gemm: unsupported tile N %d", block_n);
   FA_REQUIRE(N % block_n == 0, "gemm: N=%d is not a multiple of the tile %d", N, block_n);
@@ -608,9 +715,9 @@ int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D&
   FA_REQUIRE(epi.bias != nullptr, "gemm: bias is required (nn.Linear of the reference always has one)");
   FA_REQUIRE(ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(c) & 15) == 0, "gemm: C must be 16-byte aligned, ldc %% 8 == 0");
   switch (block_n) {
-    case 64: return gemm::launch_t<64>(ta, tb, tc, tr1, tr2, M, N, K, epi, c, ldc, row0, stream);
-    case 128: return gemm::launch_t<128>(ta, tb, tc, tr1, tr2, M, N, K, epi, c, ldc, row0, stream);
-    default: return gemm::launch_t<256>(ta, tb, tc, tr1, tr2, M, N, K, epi, c, ldc, row0, stream);
+    case 64: return gemm::launch_t<64>(ta, tb, tc, tr1, tr2, M, N, K, epi, c, ldc, row0, false, stream);
+    case 128: return gemm::launch_t<128>(ta, tb, tc, tr1, tr2, M, N, K, epi, c, ldc, row0, false, stream);
+    default: return gemm::launch_t<256>(ta, tb, tc, tr1, tr2, M, N, K, epi, c, ldc, row0, pair, stream);
   }
 }
 
@@ -633,10 +740,11 @@ extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int
   if (res1_dev) if (int r = make_tensor_map(&tr1, res1_dev, 4, M, N, ldc, 32)) return r;
   if (res2_dev) if (int r = make_tensor_map(&tr2, res2_dev, 4, M, N, ldc, 32)) return r;
   if (int r = make_tensor_map_bf16(&ta, a_dev, M, K, lda, gemm::BM)) return r;
-  if (int r = make_tensor_map_bf16(&tb, w_dev, N, K, ldw, bn)) return r;
+  const bool pair = gemm_use_pair(M, bn);
+  if (int r = make_tensor_map_bf16(&tb, w_dev, N, K, ldw, pair ? bn / 2 : bn)) return r;
   if (int r = make_tensor_map(&tc, c_dev, out_f32 ? 4 : 2, M, N, ldc, 32)) return r;
   GemmEpilogue e;
   e.bias = bias_dev; e.res1 = res1_dev; e.res2 = res2_dev; e.relu = relu; e.out_f32 = out_f32; e.accumulate = accumulate;
-  return launch_gemm(ta, tb, tc, res1_dev ? &tr1 : nullptr, res2_dev ? &tr2 : nullptr, bn, M, N, K, e, c_dev, ldc, 0,
+  return launch_gemm(ta, tb, tc, res1_dev ? &tr1 : nullptr, res2_dev ? &tr2 : nullptr, bn, M, N, K, e, c_dev, ldc, 0, pair,
                      static_cast<cudaStream_t>(stream));
 }

@@ -35,9 +35,10 @@ def test_gemm_bias_vs_fp32(U, M, N, K):
     assert U.rel_rms(got_bf.float(), torch.relu(want)) < 4e-3
 
 
-def test_gemm_residual_epilogues(U):
+@pytest.mark.parametrize("M", [777, 40001])  # 40001 rows: 256-wide tiles on CTA pairs (cta_group::2), ragged last tile
+def test_gemm_residual_epilogues(U, M):
     g = torch.Generator().manual_seed(5)
-    M, N, K = 777, 512, 512
+    N, K = 512, 512
     a = bf(torch.randn(M, K, generator=g)).cuda()
     w = bf(torch.randn(N, K, generator=g) / math.sqrt(K)).cuda()
     bias, r1, r2 = torch.randn(N, generator=g).cuda(), torch.randn(M, N, generator=g).cuda(), torch.randn(M, N, generator=g).cuda()
