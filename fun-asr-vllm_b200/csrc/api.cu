@@ -112,8 +112,8 @@ struct Workspace {
   __nv_bfloat16* xn0;    // [cap, d_in]      LN'd input of layer 0
   __nv_bfloat16* xn;     // [cap, d_model]   LN output (GEMM A operand)
   __nv_bfloat16* qkv;    // [cap, 3*d_model]
-  float* mem;            // [cap, d_model]   FSMN memory
-  __nv_bfloat16* ctx;    // [cap, d_model]
+  float* mem;            // [cap, d_model]   FSMN memory (f32 form, layers without out_w_ext)
+  __nv_bfloat16* ctx;    // [cap, 2*d_model] [attention context | bf16 FSMN memory] = A operand of the out-projection
   __nv_bfloat16* h;      // [cap, max(d_ff, ad_ffn)]
   __nv_bfloat16* enc_bf; // [cap, d_model]   encoder output, bf16 (adaptor input)
   float* enc_f32;        // [cap, d_model]   encoder output, f32
@@ -141,7 +141,7 @@ Workspace carve(const fa_model_cfg& c, int cap, unsigned char* base) {
   w.xn = reinterpret_cast<__nv_bfloat16*>(take(n * c.d_model * 2));
   w.qkv = reinterpret_cast<__nv_bfloat16*>(take(n * 3 * c.d_model * 2));
   w.mem = reinterpret_cast<float*>(take(n * c.d_model * 4));
-  w.ctx = reinterpret_cast<__nv_bfloat16*>(take(n * c.d_model * 2));
+  w.ctx = reinterpret_cast<__nv_bfloat16*>(take(n * 2 * c.d_model * 2));
   w.h = reinterpret_cast<__nv_bfloat16*>(take(n * hmax * 2));
   w.enc_bf = reinterpret_cast<__nv_bfloat16*>(take(n * c.d_model * 2));
   w.enc_f32 = reinterpret_cast<float*>(take(n * c.d_model * 4));
@@ -264,10 +264,10 @@ struct Builder {
       return launch_layernorm(x + o, g, b, g2, b2, y_bf16 ? y_bf16 + o : nullptr, y_f32 ? y_f32 + o : nullptr, r.M, D, r.s);
     });
   }
-  void attention(std::vector<Step>& prog, const __nv_bfloat16* qkv, __nv_bfloat16* ctx, int H, int D) {
+  void attention(std::vector<Step>& prog, const __nv_bfloat16* qkv, __nv_bfloat16* ctx, int H, int D, int ld_ctx) {
     prog.push_back([=](const RunArgs& r) {
       return launch_attention(qkv + static_cast<int64_t>(r.row0) * 3 * D, 3 * D, r.cu, r.n_utts, r.row0, r.max_len, H,
-                              ctx + static_cast<int64_t>(r.row0) * D, D, r.M, r.s);
+                              ctx + static_cast<int64_t>(r.row0) * ld_ctx, ld_ctx, r.M, r.s);
     });
   }
 };
@@ -291,22 +291,30 @@ int build_programs(fa_plan* p) {
     // q|k|v = LN1(x) W^T + b                                              VM:206
     B.gemm(E, a_in, din, L.qkv_w, 3 * d, din, L.qkv_b, ws.qkv, false);
     // FSMN memory on v                                                     VM:249,181-201
+    // ext: bf16 memory written beside the attention context (row = [ctx | mem]); the out-projection multiplies it by the
+    // identity block of out_w_ext, i.e. adds it in the f32 accumulator.  Otherwise f32 memory, added by the epilogue.
+    const bool ext = L.out_w_ext != nullptr;
     {
       const __nv_bfloat16* qkv = ws.qkv;
       const float* fw = L.fsmn_w;
       float* mem = ws.mem;
+      __nv_bfloat16* cm = ws.ctx;
       const int K = c.fsmn_kernel;
       E.push_back([=](const RunArgs& r) {
+        if (ext)
+          return launch_fsmn(qkv + static_cast<int64_t>(r.row0) * 3 * d, 3 * d, 2 * d, fw, r.cu, r.n_utts, r.row0,
+                             cm + static_cast<int64_t>(r.row0) * 2 * d + d, 1, 2 * d, r.M, d, K, left, r.s);
         return launch_fsmn(qkv + static_cast<int64_t>(r.row0) * 3 * d, 3 * d, 2 * d, fw, r.cu, r.n_utts, r.row0,
-                           mem + static_cast<int64_t>(r.row0) * d, r.M, d, K, left, r.s);
+                           mem + static_cast<int64_t>(r.row0) * d, 0, d, r.M, d, K, left, r.s);
       });
     }
     // masked MHA                                                           VM:250-252,222-236
-    B.attention(E, ws.qkv, ws.ctx, c.n_heads, d);
+    B.attention(E, ws.qkv, ws.ctx, c.n_heads, d, 2 * d);
     // x (+)= ctx Wo^T + b + mem   (no residual when in_size != size: layer 0 overwrites x)   VM:238,253,123-136
     // The residual stream is updated IN PLACE: the epilogue hands acc + bias + mem to a TMA reduce-add, so x is never
     // staged through the SM.
-    B.gemm(E, ws.ctx, d, L.out_w, d, d, L.out_b, x, true, false, ws.mem, nullptr, /*accumulate=*/i != 0);
+    if (ext) B.gemm(E, ws.ctx, 2 * d, L.out_w_ext, d, 2 * d, L.out_b, x, true, false, nullptr, nullptr, /*accumulate=*/i != 0);
+    else B.gemm(E, ws.ctx, 2 * d, L.out_w, d, d, L.out_b, x, true, false, ws.mem, nullptr, /*accumulate=*/i != 0);
     // LN2, FFN                                                              VM:138-140,412-431
     B.ln(E, x, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.xn, nullptr, d);
     B.gemm(E, ws.xn, d, L.ffn1_w, c.d_ff, d, L.ffn1_b, ws.h, false, true);
@@ -343,7 +351,7 @@ int build_programs(fa_plan* p) {
       // pre-LN MHA block                                                       VM:434-455
       B.ln(A, ax, L.ln1_g, L.ln1_b, nullptr, nullptr, ws.axn, nullptr, D);
       B.gemm(A, ws.axn, D, L.qkv_w, 3 * D, D, L.qkv_b, ws.aqkv, false);
-      B.attention(A, ws.aqkv, ws.actx, c.ad_heads, D);
+      B.attention(A, ws.aqkv, ws.actx, c.ad_heads, D, D);
       B.gemm(A, ws.actx, D, L.out_w, D, D, L.out_b, ax, true, false, nullptr, nullptr, /*accumulate=*/true);
       B.ln(A, ax, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.axn, nullptr, D);
       B.gemm(A, ws.axn, D, L.ffn1_w, c.ad_ff, D, L.ffn1_b, ws.ah, false, true);

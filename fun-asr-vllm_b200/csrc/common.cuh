@@ -84,7 +84,7 @@ int launch_layernorm(const float* x, const float* g, const float* b, const float
 int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, const int32_t* cu, int n_utts, int base,
                            float scale, const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream);
 int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts, int base,
-                float* mem, int M, int D, int kernel, int left_pad, cudaStream_t stream);
+                void* mem, int out_bf16, int64_t ld_out, int M, int D, int kernel, int left_pad, cudaStream_t stream);
 int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base, int max_len,
                      int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream);
 int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, int dst_bf16, const int32_t* cu,

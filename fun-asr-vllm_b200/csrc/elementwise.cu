@@ -147,89 +147,75 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
 // ---------------------------------------------------------------- FSMN memory block
 // mem[t, c] = v[t, c] + sum_k w[k, c] * v[t + k - left, c]   (zero outside the utterance; w is TAP-MAJOR [K, D])
 // (VLLM/model_executor/models/funasr.py:181-201: mask, ConstantPad1d, depthwise Conv1d, +inputs, mask).
-// One thread owns 2 adjacent channels (one bf16x2 load per row) and FSMN_ROWS consecutive rows: the
-// FSMN_ROWS + K - 1 input rows are loaded up front (independent loads, deep MLP) and converted to fp32 ONCE, the
-// tap window then slides through registers (pure FMA inner loop).  Rows of a block that lie in one utterance (the
-// common case) take a predicate-free path: out-of-utterance input rows are zeroed at load time.  Utterance bounds
-// are found once per row (16 binary searches per CTA) and shared through smem.
-constexpr int FSMN_ROWS = 16;
+// One thread owns 4 adjacent channels (one 8-byte load per row) and walks FSMN_ROWS consecutive rows with a K-row
+// sliding window held in registers; the row loop is unrolled K times so the window rotates through compile-time
+// register names (no moves), and the K loads of an unrolled block are issued before its FMAs.  A CTA's rows are cut
+// into per-utterance segments (one binary search per segment): rows outside the segment's utterance enter the window
+// as zeros, so the inner loop carries no per-tap predicates.  The "+ inputs" term is tap `left` with weight + 1.
+// Output: f32 [M, ld_out] or bf16 (the plan writes bf16 straight into the right half of the out-projection's A operand).
+constexpr int FSMN_ROWS = 32;
 constexpr int FSMN_MAXK = 16;
 constexpr int FSMN_THREADS = 128;
 
-template <int K>
+__device__ __forceinline__ float4 bf16x4_to_f32(uint2 r) {
+  return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
+                     __uint_as_float(r.y & 0xffff0000u));
+}
+
+template <int K, bool OUT_BF16>
 __global__ void __launch_bounds__(FSMN_THREADS)
 fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
-            const int32_t* __restrict__ cu, int n_utts, int base, float* __restrict__ mem, int M, int D, int left) {
-  __shared__ int s_lo[FSMN_ROWS], s_hi[FSMN_ROWS];
-  const int r0 = blockIdx.x * FSMN_ROWS;
-  if (threadIdx.x < FSMN_ROWS) {
-    const int r = min(r0 + threadIdx.x, M - 1);
-    const int2 ub = utt_bounds(cu, n_utts, r + base);
-    s_lo[threadIdx.x] = ub.x - base;
-    s_hi[threadIdx.x] = ub.y - base;
-  }
-  const int c2 = blockIdx.y * blockDim.x + threadIdx.x;  // channel pair
-  const bool ch_ok = 2 * c2 < D;
-  constexpr int NIN = FSMN_ROWS + K - 1;
-  uint32_t raw[NIN];
-  const __nv_bfloat16* vbase = qkv + v_col + 2 * c2;
-#pragma unroll
-  for (int i = 0; i < NIN; ++i) {
-    const int rr = r0 - left + i;
-    raw[i] = 0u;
-    if (ch_ok && rr >= 0 && rr < M) raw[i] = __ldg(reinterpret_cast<const uint32_t*>(vbase + static_cast<int64_t>(rr) * ld));
-  }
-  // tap-major weights [K, D]: one coalesced float2 per tap.  The "+ inputs" term (VLLM/...:199) is tap `left` with
-  // weight + 1: row r is always inside its own utterance.
-  float2 wt[K];
+            const int32_t* __restrict__ cu, int n_utts, int base, void* __restrict__ mem, int64_t ld_out, int M, int D, int left) {
+  const int c4 = blockIdx.y * FSMN_THREADS + threadIdx.x;  // channel quad
+  if (4 * c4 >= D) return;
+  float4 wt[K];
 #pragma unroll
   for (int k = 0; k < K; ++k) {
-    wt[k] = ch_ok ? __ldg(reinterpret_cast<const float2*>(w + static_cast<int64_t>(k) * D) + c2) : make_float2(0.f, 0.f);
-    if (k == left) { wt[k].x += 1.f; wt[k].y += 1.f; }
+    wt[k] = __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(k) * D) + c4);
+    const float one = (k == left) ? 1.f : 0.f;  // a select, not a dynamically indexed update (keeps wt[] in registers)
+    wt[k].x += one; wt[k].y += one; wt[k].z += one; wt[k].w += one;
   }
-  __syncthreads();
-  if (!ch_ok) return;
-  const int nrow = min(FSMN_ROWS, M - r0);
-  const int lo0 = s_lo[0], hi0 = s_hi[0];
-  const bool one_utt = (s_lo[nrow - 1] == lo0);
-  float2 v[NIN];
+  const __nv_bfloat16* vcol = qkv + v_col + 4 * c4;
+  const int ahead = K - 1 - left;  // newest input row of output row t is t + ahead
+  const int r_end = min(M, (static_cast<int>(blockIdx.x) + 1) * FSMN_ROWS);
+  int r = blockIdx.x * FSMN_ROWS;
+  while (r < r_end) {
+    const int2 ub = utt_bounds(cu, n_utts, r + base);
+    const int lo = ub.x - base, hi = ub.y - base;  // this utterance's rows (local numbering; lo may be < 0 of this launch)
+    const int seg_end = min(r_end, hi);
+    // input row `row` as 4 floats, zero outside [lo, hi) (and outside this launch's rows)
+    auto load_raw = [&](int row) -> uint2 {
+      uint2 v = make_uint2(0u, 0u);
+      if (row >= lo && row < hi && row >= 0 && row < M) v = __ldg(reinterpret_cast<const uint2*>(vcol + static_cast<int64_t>(row) * ld));
+      return v;
+    };
+    float4 win[K];
 #pragma unroll
-  for (int i = 0; i < NIN; ++i) {
-    const int rr = r0 - left + i;
-    v[i] = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[i]));
-    if (one_utt && (rr < lo0 || rr >= hi0)) v[i] = make_float2(0.f, 0.f);
-  }
-  float* obase = mem + static_cast<int64_t>(r0) * D + 2 * c2;
-  if (one_utt) {
+    for (int i = 0; i < K - 1; ++i) win[i] = bf16x4_to_f32(load_raw(r - left + i));
+    for (int tb = r; tb < seg_end; tb += K) {
+      uint2 raw[K];
 #pragma unroll
-    for (int j = 0; j < FSMN_ROWS; ++j) {
-      if (j < nrow) {
-        float a0 = 0.f, a1 = 0.f;
+      for (int j = 0; j < K; ++j) raw[j] = (tb + j < seg_end) ? load_raw(tb + j + ahead) : make_uint2(0u, 0u);
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-          a0 = fmaf(wt[k].x, v[j + k].x, a0);
-          a1 = fmaf(wt[k].y, v[j + k].y, a1);
-        }
-        *reinterpret_cast<float2*>(obase + static_cast<int64_t>(j) * D) = make_float2(a0, a1);
-      }
-    }
-  } else {
+      for (int j = 0; j < K; ++j) {
+        if (tb + j < seg_end) {
+          win[(j + K - 1) % K] = bf16x4_to_f32(raw[j]);
+          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-    for (int j = 0; j < FSMN_ROWS; ++j) {
-      if (j < nrow) {
-        const int r = r0 + j, lo = s_lo[j], hi = s_hi[j];
-        float a0 = 0.f, a1 = 0.f;
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-          const int rr = r + k - left;
-          if (rr >= lo && rr < hi) {  // uniform across the CTA
-            a0 = fmaf(wt[k].x, v[j + k].x, a0);
-            a1 = fmaf(wt[k].y, v[j + k].y, a1);
+          for (int k = 0; k < K; ++k) {
+            const float4 x = win[(j + k) % K];
+            a.x = fmaf(wt[k].x, x.x, a.x);
+            a.y = fmaf(wt[k].y, x.y, a.y);
+            a.z = fmaf(wt[k].z, x.z, a.z);
+            a.w = fmaf(wt[k].w, x.w, a.w);
           }
+          const int64_t o = static_cast<int64_t>(tb + j) * ld_out + 4 * c4;
+          if (OUT_BF16) *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(mem) + o) = make_uint2(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w));
+          else *reinterpret_cast<float4*>(static_cast<float*>(mem) + o) = a;
         }
-        *reinterpret_cast<float2*>(obase + static_cast<int64_t>(j) * D) = make_float2(a0, a1);
       }
     }
+    r = seg_end;
   }
 }
 
@@ -328,18 +314,21 @@ int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, con
 }
 
 int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts, int base,
-                float* mem, int M, int D, int kernel, int left_pad, cudaStream_t stream) {
+                void* mem, int out_bf16, int64_t ld_out, int M, int D, int kernel, int left_pad, cudaStream_t stream) {
   FA_REQUIRE(kernel >= 1 && kernel <= ew::FSMN_MAXK, "fsmn: kernel size %d not in [1,%d]", kernel, ew::FSMN_MAXK);
   FA_REQUIRE(left_pad >= 0 && left_pad < kernel, "fsmn: left pad %d outside the %d-tap window", left_pad, kernel);
-  FA_REQUIRE(D % 2 == 0 && v_col % 2 == 0 && ld % 2 == 0, "fsmn: D, v_col and ld must be even");
-  FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 3) == 0 && (reinterpret_cast<uintptr_t>(mem) & 7) == 0 &&
-                 (reinterpret_cast<uintptr_t>(w) & 7) == 0,
-             "fsmn: qkv must be 4-byte, mem and w 8-byte aligned");
+  FA_REQUIRE(D % 4 == 0 && v_col % 4 == 0 && ld % 4 == 0 && ld_out % 4 == 0 && ld_out >= D, "fsmn: D, v_col, ld and ld_out must be multiples of 4");
+  FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 7) == 0 && (reinterpret_cast<uintptr_t>(mem) & 15) == 0 &&
+                 (reinterpret_cast<uintptr_t>(w) & 15) == 0,
+             "fsmn: qkv must be 8-byte, mem and w 16-byte aligned");
   const int threads = ew::FSMN_THREADS;
-  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 2, threads));
+  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 4, threads));
   ProfScope _ps(K_FSMN, stream);
-#define FA_FSMN_CASE(KK) \
-  case KK: ew::fsmn_kernel<KK><<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, base, mem, M, D, left_pad); break;
+#define FA_FSMN_CASE(KK)                                                                                                           \
+  case KK:                                                                                                                         \
+    if (out_bf16) ew::fsmn_kernel<KK, true><<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, base, mem, ld_out, M, D, left_pad); \
+    else ew::fsmn_kernel<KK, false><<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, base, mem, ld_out, M, D, left_pad);         \
+    break;
   switch (kernel) {
     FA_FSMN_CASE(1) FA_FSMN_CASE(2) FA_FSMN_CASE(3) FA_FSMN_CASE(4) FA_FSMN_CASE(5) FA_FSMN_CASE(6) FA_FSMN_CASE(7) FA_FSMN_CASE(8)
     FA_FSMN_CASE(9) FA_FSMN_CASE(10) FA_FSMN_CASE(11) FA_FSMN_CASE(12) FA_FSMN_CASE(13) FA_FSMN_CASE(14) FA_FSMN_CASE(15)
@@ -386,8 +375,16 @@ extern "C" int fa_op_fsmn(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, co
                           const int32_t* cu_seqlens_dev, int32_t n_utts, float* mem_dev, int32_t M, int32_t D,
                           int32_t kernel, int32_t left_pad, fa_stream_t stream) {
   FA_REQUIRE(qkv_dev && w_dev && cu_seqlens_dev && mem_dev && M > 0 && n_utts > 0, "fsmn: bad arguments");
-  return launch_fsmn(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, v_col, w_dev, cu_seqlens_dev, n_utts, 0, mem_dev,
+  return launch_fsmn(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, v_col, w_dev, cu_seqlens_dev, n_utts, 0, mem_dev, 0, D,
                      M, D, kernel, left_pad, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int fa_op_fsmn_bf16(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, const float* w_dev,
+                               const int32_t* cu_seqlens_dev, int32_t n_utts, void* mem_bf16_dev, int64_t ld_mem, int32_t M,
+                               int32_t D, int32_t kernel, int32_t left_pad, fa_stream_t stream) {
+  FA_REQUIRE(qkv_dev && w_dev && cu_seqlens_dev && mem_bf16_dev && M > 0 && n_utts > 0, "fsmn: bad arguments");
+  return launch_fsmn(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, v_col, w_dev, cu_seqlens_dev, n_utts, 0, mem_bf16_dev, 1,
+                     ld_mem, M, D, kernel, left_pad, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int fa_splice_embeds(const void* speech_dev, int32_t speech_bf16, const int32_t* cu_seqlens_dev,

@@ -41,14 +41,16 @@ constexpr int BAR_BYTES = 512;
 // CTA stages its own 128 rows of A and only HALF of the B tile, so the operand bytes an SM pulls through its 64 B/clk
 // L2 port drop from 48 KB to 32 KB per 128x256x64 of MMA work (ncu, profiles/r01_e_campaign.md: the 1-CTA kernel moves
 // 54 B/clk/SM into the SMs at 63 % tensor-pipe activity, i.e. it is L2->SM ingress bound).
-template <int BN, int NRES, int CTAS>
+template <int BN, int NRES, int CTAS, bool OUT_F32>
 struct Cfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN / CTAS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   // staging slabs per epilogue warp: one (no residual) or RES_RING slots of NRES slabs (slab 0 of a slot receives
   // residual 1 and then holds the result; slab 1 receives residual 2)
-  static constexpr int SLABS_PER_WARP = NRES == 0 ? 1 : RES_RING * NRES;
+  // no residual: bf16 output (K = d_model GEMMs, little main-loop time per tile) gets two slabs so a store drains while the
+  // next unit is produced; the f32 accumulate output (K = d_ff) keeps one slab and one more operand stage
+  static constexpr int SLABS_PER_WARP = NRES == 0 ? (OUT_F32 ? 1 : 2) : RES_RING * NRES;
   static constexpr int SLABS_BYTES = EPI_WARPS * SLABS_PER_WARP * SLAB_BYTES;
   static constexpr int MAX_STAGES = (SMEM_LIMIT - 1024 - BAR_BYTES - SLABS_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = MAX_STAGES > 8 ? 8 : MAX_STAGES;
@@ -210,6 +212,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
 __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
+// issues the load only: tmem_ld_wait() must follow before r[] is read
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -220,8 +223,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
         "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---------------------------------------------------------------- kernel
 // Epilogue variants are compile-time: OUT_F32 (f32 C, optional NRES f32 residuals) or bf16 C (optional RELU).
@@ -230,7 +233,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_r1,
                  const __grid_constant__ CUtensorMap tmap_r2, const Params p) {
-  using C = Cfg<BN, NRES, CTAS>;
+  using C = Cfg<BN, NRES, CTAS, OUT_F32>;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024B alignment
   const uint32_t slab_base = smem_base + C::STAGES * C::STAGE_BYTES;  // 1024-aligned: STAGE_BYTES is a multiple of 1024
@@ -431,6 +434,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
         uint32_t r[32];
         tmem_ld32(tmem_row + u * 32, r);
+        tmem_ld_wait();
         const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -471,8 +475,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         __syncwarp();
       }
     } else {
-      const uint32_t slab = slab_base + ew * SLAB_BYTES;
-      bool slab_busy = false;
+      // two slabs per warp: unit n fills slab n & 1 while the TMA store of unit n - 1 still reads the other one
+      constexpr int NSLAB = C::SLABS_PER_WARP;
+      const uint32_t slab2 = slab_base + ew * NSLAB * SLAB_BYTES;
+      int pending = 0;  // bulk groups (TMA stores) this warp's lane 0 has committed and not yet waited for
+      int n = 0;        // units this warp has produced
       int it = 0;
       for (int tile = cl; tile < num_tiles; tile += ncl, ++it) {
         const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
@@ -483,28 +490,41 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int row0 = tile_row(tm) + q * 32;
         const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-        for (int u = hf; u < UNITS; u += 2) {
+        for (int u = hf; u < UNITS; u += 2, ++n) {
           const int col0 = tn * BN + u * COLS;
-          if (slab_busy) {  // the TMA store that last read this slab must have drained it
-            if (lane == 0) bulk_wait_read<0>();
-            __syncwarp();
-          }
+          const uint32_t slab = slab2 + (n % NSLAB) * SLAB_BYTES;
           if constexpr (OUT_F32) {
             uint32_t r[32];
             tmem_ld32(tmem_row + u * 32, r);
+            float4 bv[8];
             const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
+            for (int j = 0; j < 8; ++j) bv[j] = __ldg(bp + j);
+            if (pending >= NSLAB) {  // the store that read this slab NSLAB units ago must have drained it
+              if (lane == 0) bulk_wait_read<NSLAB - 1>();
+              pending = NSLAB - 1;
+            }
+            __syncwarp();
+            tmem_ld_wait();
+#pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 bv = __ldg(bp + j);
-              sts128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4), __float_as_uint(__uint_as_float(r[4 * j]) + bv.x),
-                     __float_as_uint(__uint_as_float(r[4 * j + 1]) + bv.y), __float_as_uint(__uint_as_float(r[4 * j + 2]) + bv.z),
-                     __float_as_uint(__uint_as_float(r[4 * j + 3]) + bv.w));
+              sts128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4), __float_as_uint(__uint_as_float(r[4 * j]) + bv[j].x),
+                     __float_as_uint(__uint_as_float(r[4 * j + 1]) + bv[j].y), __float_as_uint(__uint_as_float(r[4 * j + 2]) + bv[j].z),
+                     __float_as_uint(__uint_as_float(r[4 * j + 3]) + bv[j].w));
             }
           } else {
+            uint32_t r0[32], r1[32];
+            tmem_ld32(tmem_row + u * 64, r0);
+            tmem_ld32(tmem_row + u * 64 + 32, r1);
+            if (pending >= NSLAB) {
+              if (lane == 0) bulk_wait_read<NSLAB - 1>();
+              pending = NSLAB - 1;
+            }
+            __syncwarp();
+            tmem_ld_wait();
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
-              uint32_t r[32];
-              tmem_ld32(tmem_row + u * 64 + half * 32, r);
+              const uint32_t(&r)[32] = half ? r1 : r0;
               const float4* bp = reinterpret_cast<const float4*>(p.bias + col0 + half * 32);
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
@@ -522,6 +542,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               }
             }
           }
+          if (u + 2 >= UNITS) {  // last TMEM read of this tile: hand the accumulator back before the stores go out
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if constexpr (CTAS == 2) mbar_arrive_cluster(mapa(tempty_bar(acc), 0));
+              else mbar_arrive(tempty_bar(acc));
+            }
+          }
           if (row0 + 32 <= p.M) {
             fence_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
             __syncwarp();
@@ -530,17 +558,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               else tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
               bulk_commit();
             }
-            slab_busy = true;
+            ++pending;
           } else {
             store_rows_guarded(slab, row0, col0);
-            slab_busy = false;
+            if (lane == 0) bulk_wait_read<0>();  // rare (ragged last row tile): restart the two-slab bookkeeping
+            pending = 0;
+            __syncwarp();
           }
-        }
-        tcgen05_fence_before();
-        __syncwarp();
-        if (lane == 0) {
-          if constexpr (CTAS == 2) mbar_arrive_cluster(mapa(tempty_bar(acc), 0));
-          else mbar_arrive(tempty_bar(acc));
         }
       }
     }
@@ -579,7 +603,7 @@ static EncodeTiledFn get_encode_fn() {
 template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS>
 static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mr1,
                     const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
-  using C = Cfg<BN, NRES, CTAS>;
+  using C = Cfg<BN, NRES, CTAS, OUT_F32>;
   auto kern = gemm_bf16_kernel<BN, OUT_F32, RELU, NRES, CTAS>;
   static bool attr_done = false;
   if (!attr_done) {

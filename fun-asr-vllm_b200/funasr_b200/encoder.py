@@ -136,6 +136,9 @@ class Plan:
                     qkv_w=ar.mat(a.linear_q_k_v.weight), qkv_b=ar.vec(a.linear_q_k_v.bias),
                     fsmn_w=ar.vec(a.fsmn_block.weight.squeeze(1).t().contiguous()),  # [D,1,K] -> tap-major [K,D] f32
                     out_w=ar.mat(a.linear_out.weight), out_b=ar.vec(a.linear_out.bias),
+                    # [Wo | I]: the out-projection adds the bf16 FSMN memory on the tensor cores (fa_sanm_layer_w.out_w_ext)
+                    out_w_ext=ar.mat(torch.cat([a.linear_out.weight.detach().float(),
+                                                torch.eye(a.linear_out.weight.shape[0], device=a.linear_out.weight.device)], dim=1)),
                     ln2_g=ar.vec(L.norm2.weight), ln2_b=ar.vec(L.norm2.bias),
                     ffn1_w=ar.mat(f.w_1.weight), ffn1_b=ar.vec(f.w_1.bias),
                     ffn2_w=ar.mat(f.w_2.weight), ffn2_b=ar.vec(f.w_2.bias)))

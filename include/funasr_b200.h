@@ -40,7 +40,7 @@ extern "C" {
 
 typedef void* fa_stream_t; /* cudaStream_t */
 
-#define FA_ABI_VERSION 3
+#define FA_ABI_VERSION 4
 
 int fa_abi_version(void);
 const char* fa_last_error(void);
@@ -132,6 +132,10 @@ typedef struct {
   const float* ffn1_b;
   const void* ffn2_w;   /* bf16 [d_model, d_ff]              feed_forward.w_2.weight */
   const float* ffn2_b;
+  /* optional (ABI 4): bf16 [d_model, 2*d_model] = [out_w | I].  When non-NULL the plan keeps the FSMN memory in bf16 next
+     to the attention context ([ctx | mem], K = 2*d_model) and the out-projection's tensor-core pass adds it
+     (VLLM/model_executor/models/funasr.py:253 `att_outs + fsmn_memory`), instead of an f32 memory buffer read by the epilogue. */
+  const void* out_w_ext;
 } fa_sanm_layer_w;
 
 typedef struct {
@@ -243,6 +247,10 @@ int fa_op_embed_layernorm(const float* x_dev, const float* inv_ts_dev, const int
 int fa_op_fsmn(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, const float* w_dev, const int32_t* cu_seqlens_dev,
                int32_t n_utts, float* mem_dev, int32_t M, int32_t D, int32_t kernel, int32_t left_pad,
                fa_stream_t stream);
+/* same, bf16 output with row stride ld_mem (the form the plan uses: memory written beside the attention context) */
+int fa_op_fsmn_bf16(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, const float* w_dev, const int32_t* cu_seqlens_dev,
+                    int32_t n_utts, void* mem_bf16_dev, int64_t ld_mem, int32_t M, int32_t D, int32_t kernel,
+                    int32_t left_pad, fa_stream_t stream);
 /* ctx[M, H*128] bf16 = softmax(q k^T / sqrt(128)) v per utterance and head; q|k|v packed in the n_rows (= M) qkv rows */
 int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqlens_dev, int32_t n_utts,
                     int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx, fa_stream_t stream);

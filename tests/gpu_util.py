@@ -65,6 +65,16 @@ def op_fsmn(qkv_bf16, v_col, w, cu, D, K, left):
     return mem
 
 
+def op_fsmn_bf16(qkv_bf16, v_col, w, cu, D, K, left, out=None, cu_d=None):
+    """bf16 memory written into the right half of a [M, 2D] buffer (the plan's [ctx | mem] layout)."""
+    M = qkv_bf16.shape[0]
+    cm = torch.zeros((M, 2 * D), dtype=torch.bfloat16, device="cuda") if out is None else out
+    cu_d = dev(cu) if cu_d is None else cu_d
+    _lib.check(lib().fa_op_fsmn_bf16(qkv_bf16.data_ptr(), qkv_bf16.stride(0), v_col, w.data_ptr(), cu_d.data_ptr(), len(cu) - 1,
+                                     cm.data_ptr() + 2 * D, 2 * D, M, D, K, left, stream()))
+    return cm
+
+
 def op_attention(qkv_bf16, cu, n_heads):
     M = qkv_bf16.shape[0]
     dm = n_heads * 128

@@ -105,6 +105,27 @@ def test_fsmn_respects_utterance_boundaries(U, K, left):
     want = torch.cat(rows)
     got = U.op_fsmn(qkv.cuda(), 2 * D, w.t().contiguous().cuda(), cu, D, K, left)  # tap-major [K, D]
     assert (got.cpu() - want).abs().max().item() < 1e-4
+    cm = U.op_fsmn_bf16(qkv.cuda(), 2 * D, w.t().contiguous().cuda(), cu, D, K, left).cpu()
+    assert torch.equal(cm[:, D:], got.cpu().to(torch.bfloat16))  # same f32 arithmetic, one rounding
+    assert not cm[:, :D].any()  # the context half is not touched
+
+
+def test_fsmn_many_utterances_per_row_block(U):
+    """Row blocks of 32 that hold several whole utterances, utterances that straddle blocks, 1-row utterances."""
+    g = torch.Generator().manual_seed(11)
+    lens = [1, 1, 2, 5, 31, 32, 33, 64, 7, 1, 100, 3, 3, 3, 29]
+    cu = U.cu_of(lens)
+    M, D, K, left = int(cu[-1]), 1024, 11, 5
+    qkv = bf(torch.randn(M, 3 * D, generator=g))
+    w = torch.randn(D, K, generator=g) / math.sqrt(K)
+    v = qkv[:, 2 * D:].float()
+    rows = []
+    for b in range(len(lens)):
+        vb = v[cu[b]:cu[b + 1]].t()[None]
+        y = torch.nn.functional.conv1d(torch.nn.functional.pad(vb, (left, K - 1 - left)), w[:, None, :], groups=D)
+        rows.append((y + vb)[0].t())
+    got = U.op_fsmn(qkv.cuda(), 2 * D, w.t().contiguous().cuda(), cu, D, K, left)
+    assert (got.cpu() - torch.cat(rows)).abs().max().item() < 1e-4
 
 
 @pytest.mark.parametrize("lens,H", [([167] * 3, 4), ([1, 64, 65, 128, 500, 17], 4), ([167, 30], 8), ([667], 4)])
