@@ -110,7 +110,8 @@ struct Workspace {
   float* x;              // [cap, d_model]   residual stream (f32)
   float* x2;             // [cap, d_model]   ping-pong for the residual stream
   __nv_bfloat16* xn0;    // [cap, d_in]      LN'd input of layer 0
-  __nv_bfloat16* xn;     // [cap, d_model]   LN output (GEMM A operand)
+  __nv_bfloat16* xn;     // [cap, d_model]   LN output, or (folded LN) the raw bf16 copy of the residual stream
+  float2* stats;         // [cap, 16]        folded LN: per-row partial (sum, sum of squares), <= 16 slots
   __nv_bfloat16* qkv;    // [cap, 3*d_model]
   float* mem;            // [cap, d_model]   FSMN memory (f32 form, layers without out_w_ext)
   __nv_bfloat16* ctx;    // [cap, 2*d_model] [attention context | bf16 FSMN memory] = A operand of the out-projection
@@ -139,6 +140,7 @@ Workspace carve(const fa_model_cfg& c, int cap, unsigned char* base) {
   w.x2 = reinterpret_cast<float*>(take(n * c.d_model * 4));
   w.xn0 = reinterpret_cast<__nv_bfloat16*>(take(n * c.d_in * 2));
   w.xn = reinterpret_cast<__nv_bfloat16*>(take(n * c.d_model * 2));
+  w.stats = reinterpret_cast<float2*>(take(n * 16 * sizeof(float2)));
   w.qkv = reinterpret_cast<__nv_bfloat16*>(take(n * 3 * c.d_model * 2));
   w.mem = reinterpret_cast<float*>(take(n * c.d_model * 4));
   w.ctx = reinterpret_cast<__nv_bfloat16*>(take(n * 2 * c.d_model * 2));
@@ -187,6 +189,7 @@ struct GemmOp {
   GemmEpilogue epi;
   void* c = nullptr;
   int64_t ldc = 0;
+  int prod_N = 0;  // folded-LN consumer: width of the GEMM that produced the statistics (its tile choice fixes ln_slots)
 };
 
 int make_gemm_op(GemmOp* op, int cap, const void* a, int lda, const void* w, int N, int K, const float* bias, void* c,
@@ -221,8 +224,14 @@ int run_gemm_op(const GemmOp& op, const RunArgs& a) {
   const int idx = bn == 64 ? 0 : (bn == 128 ? 1 : 2);
   FA_REQUIRE(bn != 0 && op.tb_ok[idx], "gemm N=%d unsupported", op.N);
   const bool pair = gemm_use_pair(a.M, bn) && op.tb_ok[1];
-  return launch_gemm(op.ta, op.tb[pair ? 1 : idx], op.tc, op.epi.res1 ? &op.tr1 : nullptr, op.epi.res2 ? &op.tr2 : nullptr, bn, a.M,
-                     op.N, op.K, op.epi, op.c, op.ldc, a.row0, pair, a.s);
+  GemmEpilogue epi = op.epi;
+  if (epi.ln_mode == 1) {  // the producer ran on the same rows just before: same tile heuristic -> same slot count
+    const int pbn = gemm_block_n(a.M, op.prod_N, 1);
+    FA_REQUIRE(pbn != 0, "gemm: producer width %d unsupported", op.prod_N);
+    epi.ln_slots = 2 * (op.prod_N / pbn);
+  }
+  return launch_gemm(op.ta, op.tb[pair ? 1 : idx], op.tc, epi.res1 ? &op.tr1 : nullptr, epi.res2 ? &op.tr2 : nullptr, bn, a.M,
+                     op.N, op.K, epi, op.c, op.ldc, a.row0, pair, a.s);
 }
 
 }  // namespace
@@ -251,10 +260,15 @@ struct Builder {
   fa_plan* p;
   int rc = 0;
   void gemm(std::vector<Step>& prog, const void* a, int lda, const void* w, int N, int K, const float* bias, void* c,
-            bool out_f32, bool relu = false, const float* res1 = nullptr, const float* res2 = nullptr, bool accumulate = false) {
+            bool out_f32, bool relu = false, const float* res1 = nullptr, const float* res2 = nullptr, bool accumulate = false,
+            int ln_mode = 0, const float* colsum = nullptr, int ln_dim = 0, int prod_N = 0) {
     if (rc) return;
     GemmOp op;
     rc = make_gemm_op(&op, p->cap, a, lda, w, N, K, bias, c, out_f32, relu, res1, res2, accumulate);
+    op.epi.ln_mode = ln_mode;
+    if (ln_mode != 0) op.epi.ln_stats = p->ws.stats;
+    if (ln_mode == 1) { op.epi.colsum = colsum; op.epi.ln_dim = ln_dim; op.prod_N = prod_N; }
+    if (ln_mode == 2) { op.epi.xb = p->ws.xn; op.epi.ld_xb = N; }
     if (!rc) prog.push_back([op](const RunArgs& r) { return run_gemm_op(op, r); });
   }
   void ln(std::vector<Step>& prog, const float* x, const float* g, const float* b, const float* g2, const float* b2,
@@ -288,8 +302,15 @@ int build_programs(fa_plan* p) {
     const fa_sanm_layer_w& L = w.layers[i];
     const int din = (i == 0) ? c.d_in : d;
     const void* a_in = (i == 0) ? static_cast<const void*>(ws.xn0) : static_cast<const void*>(ws.xn);
+    // Folded LayerNorm (fa_sanm_layer_w.qkv_colsum / ffn1_colsum): the GEMM that updates the residual stream also emits
+    // its bf16 copy and row statistics, the next GEMM normalises in its epilogue -> no LN kernel, x is not re-read.
+    const bool fold_qkv = L.qkv_colsum != nullptr, fold_ffn1 = L.ffn1_colsum != nullptr;
+    const bool fold_next = (i + 1 < nl) && w.layers[i + 1].qkv_colsum != nullptr;
+    if (fold_qkv && (i == 0 || i == c.n_blocks)) { set_error("plan_create: layer %d takes its input from a LayerNorm kernel; its qkv weights must not be LN-folded", i); return 2; }
+    if (fold_ffn1 && (i == 0 || L.out_w_ext == nullptr)) { set_error("plan_create: layer %d: LN-folded ffn1 needs out_w_ext and a residual out-projection", i); return 2; }
     // q|k|v = LN1(x) W^T + b                                              VM:206
-    B.gemm(E, a_in, din, L.qkv_w, 3 * d, din, L.qkv_b, ws.qkv, false);
+    if (fold_qkv) B.gemm(E, ws.xn, d, L.qkv_w, 3 * d, d, L.qkv_b, ws.qkv, false, false, nullptr, nullptr, false, 1, L.qkv_colsum, d, d);
+    else B.gemm(E, a_in, din, L.qkv_w, 3 * d, din, L.qkv_b, ws.qkv, false);
     // FSMN memory on v                                                     VM:249,181-201
     // ext: bf16 memory written beside the attention context (row = [ctx | mem]); the out-projection multiplies it by the
     // identity block of out_w_ext, i.e. adds it in the f32 accumulator.  Otherwise f32 memory, added by the epilogue.
@@ -313,12 +334,18 @@ int build_programs(fa_plan* p) {
     // x (+)= ctx Wo^T + b + mem   (no residual when in_size != size: layer 0 overwrites x)   VM:238,253,123-136
     // The residual stream is updated IN PLACE: the epilogue hands acc + bias + mem to a TMA reduce-add, so x is never
     // staged through the SM.
-    if (ext) B.gemm(E, ws.ctx, 2 * d, L.out_w_ext, d, 2 * d, L.out_b, x, true, false, nullptr, nullptr, /*accumulate=*/i != 0);
+    if (fold_ffn1) B.gemm(E, ws.ctx, 2 * d, L.out_w_ext, d, 2 * d, L.out_b, x, true, false, x, nullptr, false, 2);
+    else if (ext) B.gemm(E, ws.ctx, 2 * d, L.out_w_ext, d, 2 * d, L.out_b, x, true, false, nullptr, nullptr, /*accumulate=*/i != 0);
     else B.gemm(E, ws.ctx, 2 * d, L.out_w, d, d, L.out_b, x, true, false, ws.mem, nullptr, /*accumulate=*/i != 0);
     // LN2, FFN                                                              VM:138-140,412-431
-    B.ln(E, x, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.xn, nullptr, d);
-    B.gemm(E, ws.xn, d, L.ffn1_w, c.d_ff, d, L.ffn1_b, ws.h, false, true);
-    B.gemm(E, ws.h, c.d_ff, L.ffn2_w, d, c.d_ff, L.ffn2_b, x, true, false, nullptr, nullptr, /*accumulate=*/true);
+    if (fold_ffn1) {
+      B.gemm(E, ws.xn, d, L.ffn1_w, c.d_ff, d, L.ffn1_b, ws.h, false, true, nullptr, nullptr, false, 1, L.ffn1_colsum, d, d);
+    } else {
+      B.ln(E, x, L.ln2_g, L.ln2_b, nullptr, nullptr, ws.xn, nullptr, d);
+      B.gemm(E, ws.xn, d, L.ffn1_w, c.d_ff, d, L.ffn1_b, ws.h, false, true);
+    }
+    if (fold_next) B.gemm(E, ws.h, c.d_ff, L.ffn2_w, d, c.d_ff, L.ffn2_b, x, true, false, x, nullptr, false, 2);
+    else B.gemm(E, ws.h, c.d_ff, L.ffn2_w, d, c.d_ff, L.ffn2_b, x, true, false, nullptr, nullptr, /*accumulate=*/true);
     // next layer's norm1, with after_norm / tp_norm folded in                VM:400,408
     const bool last_main = (i == c.n_blocks - 1);
     const bool last = (i == nl - 1);
@@ -333,7 +360,7 @@ int build_programs(fa_plan* p) {
       // x <- after_norm(x) becomes the residual stream of the tp blocks; xn <- norm1_next(x)
       B.ln(E, x, w.after_norm_g, w.after_norm_b, w.layers[i + 1].ln1_g, w.layers[i + 1].ln1_b, ws.xn, xo, d);
       float* t = x; x = xo; xo = t;
-    } else {
+    } else if (!fold_next) {
       B.ln(E, x, w.layers[i + 1].ln1_g, w.layers[i + 1].ln1_b, nullptr, nullptr, ws.xn, nullptr, d);
     }
   }

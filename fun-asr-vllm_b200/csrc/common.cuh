@@ -55,6 +55,19 @@ struct GemmEpilogue {
   int relu = 0;
   int out_f32 = 0;
   int accumulate = 0;  // f32 output only: C += acc + bias (+ res*) instead of C = ...; the residual stream is updated in place
+  // LayerNorm folded into the GEMMs around it (no LN kernel, no second pass over the f32 residual stream):
+  //  ln_mode 2 (producer; f32 output with res1 = the old residual stream): besides C = x_new the epilogue writes
+  //    xb = bf16(x_new) (the consumer's A operand) and per-row partial sums (sum, sum of squares of the bf16 values) into
+  //    ln_stats[row * ln_slots + slot], slot = (n tile, epilogue half): plain stores, no atomics, no zeroing.
+  //  ln_mode 1 (consumer; bf16 output): A is the raw xb, the weight is W * gamma, bias is b + W beta, and the epilogue
+  //    applies  rstd_r * (acc - mean_r * colsum[n]) + bias[n]  with mean/rstd from the ln_slots partials (eps 1e-12).
+  int ln_mode = 0;
+  float2* ln_stats = nullptr;
+  int ln_slots = 0;             // consumer: partials per row (= 2 * N_producer / BN_producer); producer: set by the launcher
+  int ln_dim = 0;               // consumer: row length the statistics are over
+  const float* colsum = nullptr;  // consumer: [N] row sums of the bf16 weight
+  __nv_bfloat16* xb = nullptr;  // producer: bf16 copy of C, row stride ld_xb
+  int64_t ld_xb = 0;
 };
 
 struct TensorMap2D {  // opaque 128-byte CUtensorMap

@@ -52,11 +52,14 @@ struct Cfg {
   // next unit is produced; the f32 accumulate output (K = d_ff) keeps one slab and one more operand stage
   static constexpr int SLABS_PER_WARP = NRES == 0 ? (OUT_F32 ? 1 : 2) : RES_RING * NRES;
   static constexpr int SLABS_BYTES = EPI_WARPS * SLABS_PER_WARP * SLAB_BYTES;
-  static constexpr int MAX_STAGES = (SMEM_LIMIT - 1024 - BAR_BYTES - SLABS_BYTES) / STAGE_BYTES;
+  // bf16 output: bias (and the folded-LN column sums) of all N columns are staged in smem once per CTA, so the epilogue's
+  // per-column constants are short-latency broadcast LDS instead of L1 round trips (ncu: a fifth of its stall samples)
+  static constexpr int CVEC_BYTES = OUT_F32 ? 0 : 16384;
+  static constexpr int MAX_STAGES = (SMEM_LIMIT - 1024 - BAR_BYTES - SLABS_BYTES - CVEC_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = MAX_STAGES > 8 ? 8 : MAX_STAGES;
   static_assert(STAGES >= 2, "not enough shared memory left for the operand ring");
   static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (power of two >= 32)
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SLABS_BYTES + 1024 /*align slack*/ + BAR_BYTES;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SLABS_BYTES + CVEC_BYTES + 1024 /*align slack*/ + BAR_BYTES;
 };
 
 struct Params {
@@ -71,6 +74,12 @@ struct Params {
   int relu;
   int out_f32;
   int accumulate;  // C += result (TMA reduce-add in L2) instead of C = result
+  float2* ln_stats;  // see GemmEpilogue
+  int ln_slots;
+  float ln_inv_dim;
+  const float* colsum;
+  __nv_bfloat16* xb;
+  long long ld_xb;
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -162,7 +171,9 @@ __device__ __forceinline__ void cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+  // relaxed: the barrier only orders TMEM reads (tcgen05.fence::before_thread_sync precedes it), no memory is published;
+  // the release.cluster form costs MEMBAR.ALL.GPU + ERRBAR per tile per warp (ncu: 19 % of the epilogue's stall samples)
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 // TMA load whose completion bytes are signalled on a barrier of the pair's leader CTA (cluster address)
 __device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const void* tmap, uint32_t cluster_bar, int x, int y) {
@@ -185,6 +196,23 @@ __device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, u
       "}" ::"r"(tmem_d),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
       : "memory");
+}
+// (d0, d1) = s * (a0, a1) + (t * (c0, c1) + (b0, b1)) with packed fma.rn.f32x2
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float s, float a0, float a1, float t, float c0, float c1, float b0,
+                                      float b1) {
+  asm("{\n\t"
+      ".reg .b64 ss, tt, aa, cc, bb, uu, dd;\n\t"
+      "mov.b64 ss, {%2, %2};\n\t"
+      "mov.b64 tt, {%5, %5};\n\t"
+      "mov.b64 aa, {%3, %4};\n\t"
+      "mov.b64 cc, {%6, %7};\n\t"
+      "mov.b64 bb, {%8, %9};\n\t"
+      "fma.rn.f32x2 uu, tt, cc, bb;\n\t"
+      "fma.rn.f32x2 dd, ss, aa, uu;\n\t"
+      "mov.b64 {%0, %1}, dd;\n\t"
+      "}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(s), "f"(a0), "f"(a1), "f"(t), "f"(c0), "f"(c1), "f"(b0), "f"(b1));
 }
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
@@ -228,7 +256,8 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 // ---------------------------------------------------------------- kernel
 // Epilogue variants are compile-time: OUT_F32 (f32 C, optional NRES f32 residuals) or bf16 C (optional RELU).
-template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS>
+// LN: 0 none, 1 consumer (bf16 output), 2 producer (f32 output, NRES == 1) of a folded LayerNorm.
+template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS, int LN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_r1,
@@ -237,7 +266,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   extern __shared__ unsigned char smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024B alignment
   const uint32_t slab_base = smem_base + C::STAGES * C::STAGE_BYTES;  // 1024-aligned: STAGE_BYTES is a multiple of 1024
-  const uint32_t bar_base = slab_base + C::SLABS_BYTES;
+  const uint32_t cvec_base = slab_base + C::SLABS_BYTES;  // [bias[N] | colsum[N]] (bf16 output only)
+  const uint32_t bar_base = cvec_base + C::CVEC_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::STAGES + a); };
@@ -275,6 +305,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         for (int sl = 0; sl < RES_RING; ++sl) mbar_init(res_bar(w, sl), 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if constexpr (!OUT_F32) {
+    for (int i = threadIdx.x; i < p.N; i += NUM_THREADS) {
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(cvec_base + 4u * i), "f"(__ldg(p.bias + i)) : "memory");
+      if constexpr (LN == 1) asm volatile("st.shared.f32 [%0], %1;" ::"r"(cvec_base + 4u * (p.N + i)), "f"(__ldg(p.colsum + i)) : "memory");
+    }
   }
   if (warp == 1) {
     if constexpr (CTAS == 2) {
@@ -419,6 +455,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
         for (int n = 0; n < RES_RING; ++n) issue_load(n);
       }
+      float ln_s = 0.f, ln_ss = 0.f;  // LN == 2: this lane's row, sums over the warp's units of the current tile
       for (int n = 0; n < total; ++n) {
         const int it = n / UH, i = n - it * UH;
         const int acc = it & 1;
@@ -436,6 +473,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         tmem_ld32(tmem_row + u * 32, r);
         tmem_ld_wait();
         const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
+        [[maybe_unused]] uint32_t xbp[4];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const uint32_t addr = slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4);
@@ -450,6 +488,27 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             v.x += w2.x; v.y += w2.y; v.z += w2.z; v.w += w2.w;
           }
           sts128(addr, __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w));
+          if constexpr (LN == 2) {  // bf16 copy for the next GEMM + the statistics of exactly those bf16 values
+            const uint32_t lo = pack_bf16x2(v.x, v.y), hi = pack_bf16x2(v.z, v.w);
+            xbp[2 * (j & 1)] = lo;
+            xbp[2 * (j & 1) + 1] = hi;
+            const float b0 = __uint_as_float(lo << 16), b1 = __uint_as_float(lo & 0xffff0000u);
+            const float b2 = __uint_as_float(hi << 16), b3 = __uint_as_float(hi & 0xffff0000u);
+            ln_s += (b0 + b1) + (b2 + b3);
+            ln_ss = fmaf(b0, b0, fmaf(b1, b1, fmaf(b2, b2, fmaf(b3, b3, ln_ss))));
+            if ((j & 1) && row0 + lane < p.M)
+              *reinterpret_cast<uint4*>(p.xb + static_cast<long long>(p.row0 + row0 + lane) * p.ld_xb + col0 + 4 * (j - 1)) =
+                  make_uint4(xbp[0], xbp[1], xbp[2], xbp[3]);
+          }
+        }
+        if constexpr (LN == 2) {
+          if (i == UH - 1) {  // this warp's share of the row is complete for this tile: one partial per (n tile, half)
+            const int tile = cl + it * ncl;
+            const int tn = tile % p.tiles_n;
+            if (row0 + lane < p.M)
+              p.ln_stats[static_cast<long long>(p.row0 + row0 + lane) * p.ln_slots + 2 * tn + hf] = make_float2(ln_s, ln_ss);
+            ln_s = ln_ss = 0.f;
+          }
         }
         if (i == UH - 1) {  // last TMEM read of this tile: hand the accumulator back to the MMA warp
           tcgen05_fence_before();
@@ -476,6 +535,28 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
     } else {
       // two slabs per warp: unit n fills slab n & 1 while the TMA store of unit n - 1 still reads the other one
+      // folded-LN consumer: the row partials (sum, sum of squares) of a tile are fetched one tile ahead
+      [[maybe_unused]] float4 pa = make_float4(0.f, 0.f, 0.f, 0.f), pb = pa;
+      [[maybe_unused]] auto ld_stats = [&](int tile_, float4& a, float4& b) {
+        a = make_float4(0.f, 0.f, 0.f, 0.f);
+        b = a;
+        const int r_ = tile_row(tile_ / p.tiles_n) + q * 32 + lane;
+        if (r_ >= p.M) return;
+        const float2* sp = p.ln_stats + static_cast<long long>(p.row0 + r_) * p.ln_slots;  // written by the previous kernel
+        if (p.ln_slots == 4) {  // 256-wide producer tiles over 512 columns: two 16-byte loads
+          a = *reinterpret_cast<const float4*>(sp);
+          b = *reinterpret_cast<const float4*>(sp + 2);
+        } else {
+          for (int k = 0; k < p.ln_slots; ++k) {
+            const float2 t = sp[k];
+            a.x += t.x;
+            a.y += t.y;
+          }
+        }
+      };
+      if constexpr (LN == 1) {
+        if (cl < num_tiles) ld_stats(cl, pa, pb);
+      }
       constexpr int NSLAB = C::SLABS_PER_WARP;
       const uint32_t slab2 = slab_base + ew * NSLAB * SLAB_BYTES;
       int pending = 0;  // bulk groups (TMA stores) this warp's lane 0 has committed and not yet waited for
@@ -485,10 +566,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
-        mbar_wait(tfull_bar(acc), acc_phase);
-        tcgen05_fence_after();
         const int row0 = tile_row(tm) + q * 32;
         const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+        [[maybe_unused]] float ln_rs = 1.f, ln_nm = 0.f;  // LN == 1: rstd and -rstd * mean of this lane's row
+        if constexpr (LN == 1) {
+          // partials of THIS tile's row were requested one tile ago (or before the loop); request the next tile's now
+          const float s = (pa.x + pa.z) + (pb.x + pb.z), ss = (pa.y + pa.w) + (pb.y + pb.w);
+          if (tile + ncl < num_tiles) ld_stats(tile + ncl, pa, pb);
+          const float mu = s * p.ln_inv_dim;
+          ln_rs = rsqrtf(fmaxf(fmaf(-mu, mu, ss * p.ln_inv_dim), 0.f) + 1e-12f);  // VLLM/model_executor/models/funasr.py:85 eps
+          ln_nm = -ln_rs * mu;
+        }
+        mbar_wait(tfull_bar(acc), acc_phase);
+        tcgen05_fence_after();
 #pragma unroll 1
         for (int u = hf; u < UNITS; u += 2, ++n) {
           const int col0 = tn * BN + u * COLS;
@@ -525,14 +615,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
               const uint32_t(&r)[32] = half ? r1 : r0;
-              const float4* bp = reinterpret_cast<const float4*>(p.bias + col0 + half * 32);
+              const uint32_t bp = cvec_base + 4u * (col0 + half * 32);
+              [[maybe_unused]] const uint32_t cp = bp + 4u * p.N;
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
-                float v[8] = {__uint_as_float(r[8 * j]) + b0.x,     __uint_as_float(r[8 * j + 1]) + b0.y,
-                              __uint_as_float(r[8 * j + 2]) + b0.z, __uint_as_float(r[8 * j + 3]) + b0.w,
-                              __uint_as_float(r[8 * j + 4]) + b1.x, __uint_as_float(r[8 * j + 5]) + b1.y,
-                              __uint_as_float(r[8 * j + 6]) + b1.z, __uint_as_float(r[8 * j + 7]) + b1.w};
+                const float4 b0 = lds128(bp + 32 * j), b1 = lds128(bp + 32 * j + 16);
+                float v[8];
+                if constexpr (LN == 1) {  // rstd * (acc - mean * colsum) + bias
+                  const float4 c0 = lds128(cp + 32 * j), c1 = lds128(cp + 32 * j + 16);
+                  const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+                  const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                  for (int e = 0; e < 8; e += 2)  // two packed f32x2 FMAs per column pair (Blackwell FFMA2)
+                    ffma2(v[e], v[e + 1], ln_rs, __uint_as_float(r[8 * j + e]), __uint_as_float(r[8 * j + e + 1]), ln_nm, cs[e], cs[e + 1],
+                          bb[e], bb[e + 1]);
+                } else {
+                  v[0] = __uint_as_float(r[8 * j]) + b0.x;     v[1] = __uint_as_float(r[8 * j + 1]) + b0.y;
+                  v[2] = __uint_as_float(r[8 * j + 2]) + b0.z; v[3] = __uint_as_float(r[8 * j + 3]) + b0.w;
+                  v[4] = __uint_as_float(r[8 * j + 4]) + b1.x; v[5] = __uint_as_float(r[8 * j + 5]) + b1.y;
+                  v[6] = __uint_as_float(r[8 * j + 6]) + b1.z; v[7] = __uint_as_float(r[8 * j + 7]) + b1.w;
+                }
                 if constexpr (RELU) {
 #pragma unroll
                   for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
@@ -600,11 +702,11 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS>
+template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS, int LN>
 static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mr1,
                     const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
   using C = Cfg<BN, NRES, CTAS, OUT_F32>;
-  auto kern = gemm_bf16_kernel<BN, OUT_F32, RELU, NRES, CTAS>;
+  auto kern = gemm_bf16_kernel<BN, OUT_F32, RELU, NRES, CTAS, LN>;
   static bool attr_done = false;
   if (!attr_done) {
     FA_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
@@ -627,13 +729,13 @@ static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensor
 }
 
 // pair == true: BN is 256 and `mb` boxes BN/2 rows (each CTA of a pair stages half of the B tile)
-template <int BN, bool OUT_F32, bool RELU, int NRES>
+template <int BN, bool OUT_F32, bool RELU, int NRES, int LN = 0>
 static int launch_p(bool pair, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mr1,
                     const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
   if constexpr (BN == 256) {
-    if (pair) return launch_v<BN, OUT_F32, RELU, NRES, 2>(ma, mb, mc, mr1, mr2, p, grid, stream);
+    if (pair) return launch_v<BN, OUT_F32, RELU, NRES, 2, LN>(ma, mb, mc, mr1, mr2, p, grid, stream);
   }
-  return launch_v<BN, OUT_F32, RELU, NRES, 1>(ma, mb, mc, mr1, mr2, p, grid, stream);
+  return launch_v<BN, OUT_F32, RELU, NRES, 1, LN>(ma, mb, mc, mr1, mr2, p, grid, stream);
 }
 
 template <int BN>
@@ -648,6 +750,15 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   p.tiles_n = N / BN;
   p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
   p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32; p.accumulate = epi.accumulate;
+  p.ln_stats = epi.ln_stats; p.colsum = epi.colsum; p.xb = epi.xb; p.ld_xb = epi.ld_xb;
+  p.ln_slots = epi.ln_mode == 2 ? 2 * (N / BN) : epi.ln_slots;
+  p.ln_inv_dim = epi.ln_dim > 0 ? 1.f / static_cast<float>(epi.ln_dim) : 0.f;
+  FA_REQUIRE(epi.out_f32 || N * 4 * (epi.ln_mode == 1 ? 2 : 1) <= 16384, "gemm: N=%d too wide for the staged epilogue constants", N);
+  if (epi.ln_mode == 1)
+    FA_REQUIRE(!epi.out_f32 && epi.ln_stats && epi.colsum && epi.ln_slots > 0 && epi.ln_dim > 0, "gemm: folded-LN consumer needs the bf16 output, ln_stats, colsum, ln_slots and ln_dim");
+  if (epi.ln_mode == 2)
+    FA_REQUIRE(epi.out_f32 && epi.res1 && !epi.res2 && !epi.accumulate && epi.ln_stats && epi.xb && epi.ld_xb % 8 == 0 && 2 * (N / BN) <= 16,
+               "gemm: folded-LN producer needs the f32 output with exactly one staged residual, ln_stats and xb");
   FA_REQUIRE(!epi.accumulate || epi.out_f32, "gemm: accumulate needs the f32 output");
   const int tiles = p.tiles_m * p.tiles_n;
   int grid = tiles < sm_count() ? tiles : sm_count();
@@ -669,10 +780,15 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
       if constexpr (BN <= 128) return launch_p<BN, true, false, 2>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
       else FA_REQUIRE(false, "gemm: two residuals are compiled for tile N <= 128 only");
     }
+    if (epi.res1 && epi.ln_mode == 2) return launch_p<BN, true, false, 1, 2>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
     if (epi.res1) return launch_p<BN, true, false, 1>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
     return launch_p<BN, true, false, 0>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
   }
   FA_REQUIRE(!epi.res1 && !epi.res2, "gemm: residuals are only compiled for the f32 output");
+  if (epi.ln_mode == 1) {
+    if (epi.relu) return launch_p<BN, false, true, 0, 1>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
+    return launch_p<BN, false, false, 0, 1>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
+  }
   if (epi.relu) return launch_p<BN, false, true, 0>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
   return launch_p<BN, false, false, 0>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
 }
@@ -746,6 +862,33 @@ int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D&
 }
 
 }  // namespace fa
+
+// One GEMM with the folded-LayerNorm epilogues (GemmEpilogue::ln_mode).  ln_mode 2: res1_dev is the old residual stream,
+// c_dev (f32, may alias res1_dev) receives x_new, xb_dev its bf16 copy and ln_stats_dev [M, *n_slots] the row partials
+// (*n_slots is written).  ln_mode 1: a_dev is the raw bf16 stream, w/bias are LN-folded, *n_slots partials are read.
+extern "C" int fa_op_gemm_ln(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev,
+                             const float* res1_dev, void* c_dev, int64_t ldc, int32_t M, int32_t N, int32_t K, int32_t relu,
+                             int32_t out_f32, int32_t ln_mode, void* ln_stats_dev, int32_t* n_slots, int32_t ln_dim,
+                             const float* colsum_dev, void* xb_dev, int64_t ld_xb, fa_stream_t stream) {
+  using namespace fa;
+  FA_REQUIRE(a_dev && w_dev && c_dev && n_slots && (ln_mode == 1 || ln_mode == 2), "gemm_ln: bad arguments");
+  const int bn = gemm_block_n(M, N, res1_dev ? 1 : 0);
+  FA_REQUIRE(bn != 0, "gemm: N=%d must be a multiple of 64", N);
+  TensorMap2D ta, tb, tc, tr1;
+  if (res1_dev) if (int r = make_tensor_map(&tr1, res1_dev, 4, M, N, ldc, 32)) return r;
+  if (int r = make_tensor_map_bf16(&ta, a_dev, M, K, lda, gemm::BM)) return r;
+  const bool pair = gemm_use_pair(M, bn);
+  if (int r = make_tensor_map_bf16(&tb, w_dev, N, K, ldw, pair ? bn / 2 : bn)) return r;
+  if (int r = make_tensor_map(&tc, c_dev, out_f32 ? 4 : 2, M, N, ldc, 32)) return r;
+  GemmEpilogue e;
+  e.bias = bias_dev; e.res1 = res1_dev; e.relu = relu; e.out_f32 = out_f32;
+  e.ln_mode = ln_mode; e.ln_stats = static_cast<float2*>(ln_stats_dev); e.ln_dim = ln_dim; e.colsum = colsum_dev;
+  e.xb = static_cast<__nv_bfloat16*>(xb_dev); e.ld_xb = ld_xb;
+  if (ln_mode == 2) *n_slots = 2 * (N / bn);
+  e.ln_slots = *n_slots;
+  return launch_gemm(ta, tb, tc, res1_dev ? &tr1 : nullptr, nullptr, bn, M, N, K, e, c_dev, ldc, 0, pair,
+                     static_cast<cudaStream_t>(stream));
+}
 
 extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev,
                           const float* res1_dev, const float* res2_dev, void* c_dev, int64_t ldc, int32_t M, int32_t N,

@@ -29,7 +29,7 @@ class ModelCfg(C.Structure):
 
 class SanmLayerW(C.Structure):
     _fields_ = [(n, vp) for n in ("ln1_g", "ln1_b", "qkv_w", "qkv_b", "fsmn_w", "out_w", "out_b", "ln2_g", "ln2_b",
-                                  "ffn1_w", "ffn1_b", "ffn2_w", "ffn2_b", "out_w_ext")]
+                                  "ffn1_w", "ffn1_b", "ffn2_w", "ffn2_b", "out_w_ext", "qkv_colsum", "ffn1_colsum")]
 
 
 class AdaptorLayerW(C.Structure):
@@ -70,6 +70,7 @@ PROTOTYPES = {
     "fa_op_gemm": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, vp, i64, i32, i32, i32, i32, i32, vp]),
     "fa_op_layernorm": (C.c_int, [vp, vp, vp, vp, vp, i32, i32, vp]),
     "fa_op_embed_layernorm": (C.c_int, [vp, vp, vp, i32, f32, vp, vp, vp, i32, i32, vp]),
+    "fa_op_gemm_ln": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, i64, i32, i32, i32, i32, i32, i32, vp, C.POINTER(C.c_int32), i32, vp, vp, i64, vp]),
     "fa_op_fsmn": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, i32, i32, i32, i32, vp]),
     "fa_op_fsmn_bf16": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, i64, i32, i32, i32, i32, vp]),
     "fa_op_attention": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, vp, i64, vp]),

@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import numpy as np
 import torch
@@ -66,6 +67,15 @@ class _AdaptorLayerParams(nn.Module):
         self.feed_forward = _FFNParams(size, ff)
         self.norm1 = nn.LayerNorm(size, eps=1e-12)
         self.norm2 = nn.LayerNorm(size, eps=1e-12)
+
+
+def _fold_ln(norm, weight, bias):
+    """LayerNorm(x) W^T + b  ==  rstd * (x (W*gamma)^T - mean * colsum) + (b + W beta): returns the folded weight (fp32, the
+    arena rounds it to bf16), the folded bias and the row sums of the bf16-rounded folded weight (what the GEMM multiplies)."""
+    w = weight.detach().float()
+    wg = w * norm.weight.detach().float()[None, :]
+    b = bias.detach().float() + w @ norm.bias.detach().float()
+    return wg, b, wg.to(torch.bfloat16).float().sum(dim=1)
 
 
 # ----------------------------------------------------------------------------- plan (weights arena + workspace)
@@ -129,18 +139,29 @@ class Plan:
             cfg.fsmn_kernel, cfg.sanm_shift = enc.kernel_size, enc.sanm_shift
             cfg.n_blocks, cfg.n_tp_blocks = 1 + len(enc.encoders), len(enc.tp_encoders)
             h["layers"] = []
-            for L in layers:
+            fold = os.environ.get("FA_LN_FOLD", "1") != "0"
+            for li, L in enumerate(layers):
                 a, f = L.self_attn, L.feed_forward
+                d = dict()
+                # LayerNorm folded into the GEMM it feeds (fa_sanm_layer_w.qkv_colsum / ffn1_colsum): every layer except
+                # those whose input comes out of a LayerNorm kernel (layer 0: embed stage; first tp block: after_norm)
+                qkv_w, qkv_b, ffn1_w, ffn1_b = a.linear_q_k_v.weight, a.linear_q_k_v.bias, f.w_1.weight, f.w_1.bias
+                if fold and li != 0 and li != cfg.n_blocks:
+                    qkv_w, qkv_b, cs = _fold_ln(L.norm1, qkv_w, qkv_b)
+                    d["qkv_colsum"] = ar.vec(cs)
+                if fold and li != 0:
+                    ffn1_w, ffn1_b, cs = _fold_ln(L.norm2, ffn1_w, ffn1_b)
+                    d["ffn1_colsum"] = ar.vec(cs)
                 h["layers"].append(dict(
-                    ln1_g=ar.vec(L.norm1.weight), ln1_b=ar.vec(L.norm1.bias),
-                    qkv_w=ar.mat(a.linear_q_k_v.weight), qkv_b=ar.vec(a.linear_q_k_v.bias),
+                    d, ln1_g=ar.vec(L.norm1.weight), ln1_b=ar.vec(L.norm1.bias),
+                    qkv_w=ar.mat(qkv_w), qkv_b=ar.vec(qkv_b),
                     fsmn_w=ar.vec(a.fsmn_block.weight.squeeze(1).t().contiguous()),  # [D,1,K] -> tap-major [K,D] f32
                     out_w=ar.mat(a.linear_out.weight), out_b=ar.vec(a.linear_out.bias),
                     # [Wo | I]: the out-projection adds the bf16 FSMN memory on the tensor cores (fa_sanm_layer_w.out_w_ext)
                     out_w_ext=ar.mat(torch.cat([a.linear_out.weight.detach().float(),
                                                 torch.eye(a.linear_out.weight.shape[0], device=a.linear_out.weight.device)], dim=1)),
                     ln2_g=ar.vec(L.norm2.weight), ln2_b=ar.vec(L.norm2.bias),
-                    ffn1_w=ar.mat(f.w_1.weight), ffn1_b=ar.vec(f.w_1.bias),
+                    ffn1_w=ar.mat(ffn1_w), ffn1_b=ar.vec(ffn1_b),
                     ffn2_w=ar.mat(f.w_2.weight), ffn2_b=ar.vec(f.w_2.bias)))
             h["after_norm_g"], h["after_norm_b"] = ar.vec(enc.after_norm.weight), ar.vec(enc.after_norm.bias)
             h["tp_norm_g"], h["tp_norm_b"] = ar.vec(enc.tp_norm.weight), ar.vec(enc.tp_norm.bias)

@@ -136,6 +136,13 @@ typedef struct {
      to the attention context ([ctx | mem], K = 2*d_model) and the out-projection's tensor-core pass adds it
      (VLLM/model_executor/models/funasr.py:253 `att_outs + fsmn_memory`), instead of an f32 memory buffer read by the epilogue. */
   const void* out_w_ext;
+  /* optional (ABI 4): LayerNorm folded into the GEMMs (norm1 -> qkv, norm2 -> ffn1; VLLM/...:83-91,120,138).  When
+     qkv_colsum is non-NULL, qkv_w holds bf16(W * gamma1) (column k scaled by gamma1[k]), qkv_b holds b + W beta1 and
+     qkv_colsum[n] = sum_k float(qkv_w[n, k]); the plan then feeds the GEMM the raw bf16 residual stream and applies
+     rstd * (acc - mean * colsum) + bias in the epilogue.  Same for ffn1_colsum / ffn1_w / ffn1_b with norm2.  Not allowed
+     on layers whose input comes from a LayerNorm kernel (layer 0, and qkv of the first tp block). */
+  const float* qkv_colsum;
+  const float* ffn1_colsum;
 } fa_sanm_layer_w;
 
 typedef struct {
@@ -235,6 +242,14 @@ int fa_profile_collect(float* ms_per_kind, int32_t* launches_per_kind, int32_t n
 int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev,
                const float* res1_dev, const float* res2_dev, void* c_dev, int64_t ldc, int32_t M, int32_t N,
                int32_t K, int32_t relu, int32_t out_f32, fa_stream_t stream);
+/* One GEMM with a folded-LayerNorm epilogue (how the plan runs norm1 -> qkv and norm2 -> ffn1 without an LN kernel).
+   ln_mode 2 (producer): c (f32, may alias res1) = a w^T + bias + res1; xb = bf16(c); ln_stats[M, *n_slots] (float2 = sum, sum
+   of squares of the bf16 row pieces; *n_slots is written).  ln_mode 1 (consumer): a = raw bf16 rows, w = bf16(W * gamma),
+   bias = b + W beta, colsum[n] = sum_k w[n, k]; c = rstd * (a w^T - mean * colsum) + bias over ln_dim columns, eps 1e-12. */
+int fa_op_gemm_ln(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev, const float* res1_dev,
+                  void* c_dev, int64_t ldc, int32_t M, int32_t N, int32_t K, int32_t relu, int32_t out_f32, int32_t ln_mode,
+                  void* ln_stats_dev, int32_t* n_slots, int32_t ln_dim, const float* colsum_dev, void* xb_dev, int64_t ld_xb,
+                  fa_stream_t stream);
 /* y = LN(x) (eps 1e-12); y_bf16 and/or y_f32 may be NULL */
 int fa_op_layernorm(const float* x_dev, const float* g_dev, const float* b_dev, void* y_bf16_dev, float* y_f32_dev,
                     int32_t M, int32_t D, fa_stream_t stream);

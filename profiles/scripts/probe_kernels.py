@@ -55,6 +55,28 @@ if which in ("gemm", "all"):
         best, avg = timeit(lambda: U.op_gemm(a, w, bias, r1, r2, relu=bool(relu), out_f32=bool(f32), out=out))
         print(f"gemm {name:5s} M={M} N={N} K={K}: best {best*1e3:.1f} us avg {avg*1e3:.1f} us -> {2*M*N*K/best/1e9:.0f} TFLOP/s")
 
+if which in ("gemmln", "all"):
+    # folded-LayerNorm epilogues: producer (x += ..., bf16 copy, row partials) and consumer (normalise in the epilogue)
+    for name, K in [("out+ln", 1024), ("ffn2+ln", 2048)]:
+        a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+        w = (torch.randn(512, K, device="cuda") / math.sqrt(K)).to(torch.bfloat16)
+        bias, x = torch.randn(512, device="cuda"), torch.randn(M, 512, device="cuda")
+        xb_, st_ = torch.empty(M, 512, device="cuda", dtype=torch.bfloat16), torch.zeros(M, 16, 2, device="cuda")
+        best, avg = timeit(lambda: U.op_gemm_ln_producer(a, w, bias, x, xb=xb_, stats=st_))
+        print(f"gemm {name:8s} M={M} N=512 K={K}: best {best*1e3:.1f} us avg {avg*1e3:.1f} us (producer)")
+        r1 = torch.randn(M, 512, device="cuda")
+        best, avg = timeit(lambda: U.op_gemm(a, w, bias, r1, None, out_f32=True, out=x))
+        print(f"gemm {name[:-3]:8s} M={M} N=512 K={K}: best {best*1e3:.1f} us (staged residual, no LN outputs)")
+        best, avg = timeit(lambda: U.op_gemm(a, w, bias, x, None, out_f32=True, out=x))
+        print(f"gemm {name[:-3]:8s} M={M} N=512 K={K}: best {best*1e3:.1f} us (accumulate)")
+    _, xb, stats, n = U.op_gemm_ln_producer(a, w, bias, x)
+    for name, N, relu in [("ln+qkv", 1536, False), ("ln+ffn1", 2048, True)]:
+        wf = (torch.randn(N, 512, device="cuda") / math.sqrt(512)).to(torch.bfloat16)
+        bb, cs = torch.randn(N, device="cuda"), wf.float().sum(dim=1)
+        out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        best, avg = timeit(lambda: U.op_gemm_ln_consumer(xb, wf, bb, cs, stats, n, relu=relu, out=out))
+        print(f"gemm {name:8s} M={M} N={N} K=512: best {best*1e3:.1f} us avg {avg*1e3:.1f} us -> {2*M*N*512/best/1e9:.0f} TFLOP/s (consumer)")
+
 if which in ("attn", "all"):
     for H, lens in [(4, [167] * 360), (8, [167] * 360), (4, [500] * 120)]:
         cu = U.cu_of(lens)

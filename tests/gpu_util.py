@@ -39,6 +39,34 @@ def op_gemm(a_bf16, w_bf16, bias=None, res1=None, res2=None, relu=False, out_f32
     return c
 
 
+def op_gemm_ln_producer(a_bf16, w_bf16, bias, x, inplace=True, xb=None, stats=None):
+    """x_new = a w^T + bias + x (f32, written over x when inplace), its bf16 copy and the row partials [M, n_slots, 2]."""
+    import ctypes
+    M, K = a_bf16.shape
+    N = w_bf16.shape[0]
+    c = x if inplace else torch.empty_like(x)
+    xb = torch.empty((M, N), dtype=torch.bfloat16, device="cuda") if xb is None else xb
+    stats = torch.zeros((M, 16, 2), dtype=torch.float32, device="cuda") if stats is None else stats
+    ns = ctypes.c_int32(0)
+    _lib.check(lib().fa_op_gemm_ln(a_bf16.data_ptr(), a_bf16.stride(0), w_bf16.data_ptr(), w_bf16.stride(0), bias.data_ptr(),
+                                   x.data_ptr(), c.data_ptr(), N, M, N, K, 0, 1, 2, stats.data_ptr(), ctypes.byref(ns), N, None,
+                                   xb.data_ptr(), N, stream()), "fa_op_gemm_ln")
+    n = ns.value
+    return c, xb, stats.view(-1)[: M * n * 2].view(M, n, 2), n
+
+
+def op_gemm_ln_consumer(xb, w_fold_bf16, bias_fold, colsum, stats, n_slots, relu=False, out=None):
+    import ctypes
+    M, K = xb.shape
+    N = w_fold_bf16.shape[0]
+    c = out if out is not None else torch.empty((M, N), dtype=torch.bfloat16, device="cuda")
+    ns = ctypes.c_int32(n_slots)
+    _lib.check(lib().fa_op_gemm_ln(xb.data_ptr(), xb.stride(0), w_fold_bf16.data_ptr(), w_fold_bf16.stride(0), bias_fold.data_ptr(),
+                                   None, c.data_ptr(), N, M, N, K, int(relu), 0, 1, stats.data_ptr(), ctypes.byref(ns), K,
+                                   colsum.data_ptr(), None, 0, stream()), "fa_op_gemm_ln")
+    return c
+
+
 def op_layernorm(x, g, b, want_bf16=True, want_f32=True):
     M, D = x.shape
     yb = torch.empty((M, D), dtype=torch.bfloat16, device="cuda") if want_bf16 else None

@@ -57,6 +57,36 @@ def test_gemm_residual_epilogues(U, M):
     assert (acc1 - (want - r2)).abs().max().item() < 2e-3 * want.abs().max().item()
 
 
+@pytest.mark.parametrize("M", [300, 2672, 40001])  # 64-, 128- and 256-wide (CTA pair) producer tiles: 16, 8, 4 partials per row
+def test_gemm_folded_layernorm(U, M):
+    """x += a W2^T + b2 ; y = relu(LN(x) W1^T + b1) with the LayerNorm folded into the two GEMM epilogues
+    (VLLM/model_executor/models/funasr.py:138-140 norm2 -> feed_forward) against torch's layer_norm on the same x."""
+    from funasr_b200.encoder import _fold_ln
+    g = torch.Generator().manual_seed(M)
+    D, F = 512, 2048
+    a = bf(torch.randn(M, F, generator=g)).cuda()
+    w2 = bf(torch.randn(D, F, generator=g) / math.sqrt(F)).cuda()
+    b2 = torch.randn(D, generator=g).cuda()
+    x0 = (2 * torch.randn(M, D, generator=g) + 0.5).cuda()
+    want_x = a.float() @ w2.float().t() + b2 + x0
+    x, xb, stats, n = U.op_gemm_ln_producer(a, w2, b2, x0.clone())
+    assert (x - want_x).abs().max().item() < 2e-3 * want_x.abs().max().item()
+    assert torch.equal(xb, x.to(torch.bfloat16))
+    s = stats.sum(dim=1)
+    assert torch.allclose(s[:, 0], xb.float().sum(dim=1), rtol=1e-4, atol=1e-2)
+    assert torch.allclose(s[:, 1], xb.float().pow(2).sum(dim=1), rtol=1e-4)
+    norm = torch.nn.LayerNorm(D, eps=1e-12)
+    with torch.no_grad():
+        norm.weight.copy_(1 + 0.1 * torch.randn(D, generator=g))
+        norm.bias.copy_(0.1 * torch.randn(D, generator=g))
+    w1 = torch.randn(F, D, generator=g) / math.sqrt(D)
+    b1 = torch.randn(F, generator=g)
+    wf, bfold, cs = _fold_ln(norm, w1, b1)
+    y = U.op_gemm_ln_consumer(xb, bf(wf).cuda(), bfold.cuda(), cs.cuda(), stats, n, relu=True)
+    want_y = torch.relu(torch.nn.functional.layer_norm(x.cpu(), (D,), norm.weight, norm.bias, 1e-12) @ w1.t() + b1)
+    assert U.rel_rms(y.float().cpu(), want_y) < 6e-3  # bf16 rounding of x, of W * gamma and of y
+
+
 @pytest.mark.parametrize("M,D", [(1, 512), (167, 560), (2672, 512), (1000, 1024), (37, 64)])
 def test_layernorm(U, M, D):
     g = torch.Generator().manual_seed(M + D)
