@@ -14,6 +14,15 @@ namespace fa {
 
 static thread_local char g_err[1024] = "";
 
+bool pdl_enabled() {  // FA_PDL=0 turns programmatic dependent launch off (A/B measurements)
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("FA_PDL");
+    on = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  return on == 1;
+}
+
 void set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);

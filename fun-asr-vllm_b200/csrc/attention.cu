@@ -169,7 +169,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
   extern __shared__ unsigned char smem_raw[];
   const int cta_lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
   if (threadIdx.x == 0) TRACE(0);
-  const int b = blockIdx.z, h = blockIdx.y;
+  pdl_launch_dependents();
+  const int b = blockIdx.z, h = blockIdx.y;  // (cu_seqlens is an input of the whole forward call, not a kernel's output)
   const int start = cu[b] - base, len = cu[b + 1] - cu[b];
   const int q0 = blockIdx.x * BQ;
   if (q0 >= len) return;  // uniform per CTA, before any barrier / TMEM use
@@ -211,6 +212,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
   tc_fence_after();
   if (threadIdx.x == 0) TRACE(1);
   const uint32_t tmem = *tmem_slot_ptr;
+  pdl_wait();
   const uint32_t tO = tmem + 2 * BKV;
   auto tS = [&](int st) { return tmem + st * BKV; };
 
@@ -441,8 +443,8 @@ int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seq
   dim3 grid(ceil_div(max_len, attn::BQ), n_heads, n_utts);
   const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(attn::HD));
   ProfScope _ps(K_ATTENTION, stream);
-  attn::attention_kernel<<<grid, attn::THREADS, attn::SMEM_BYTES, stream>>>(m, cu_seqlens, base, n_heads, ctx, ld_ctx, scale_log2e, attn::g_trace);
-  FA_CHECK_LAUNCH();
+  FA_CHECK_CUDA(launch_pdl(attn::attention_kernel, grid, dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, cu_seqlens, base, n_heads,
+                           ctx, ld_ctx, scale_log2e, attn::g_trace));
   return 0;
 }
 

@@ -66,6 +66,8 @@ __device__ __forceinline__ void ln_stats(const float4 (&v)[LN_VEC], int nvec, in
 
 template <bool EMBED>
 __global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= a.M) return;
@@ -166,6 +168,7 @@ template <int K, bool OUT_BF16>
 __global__ void __launch_bounds__(FSMN_THREADS)
 fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
             const int32_t* __restrict__ cu, int n_utts, int base, void* __restrict__ mem, int64_t ld_out, int M, int D, int left) {
+  pdl_launch_dependents();
   const int c4 = blockIdx.y * FSMN_THREADS + threadIdx.x;  // channel quad
   if (4 * c4 >= D) return;
   float4 wt[K];
@@ -175,6 +178,7 @@ fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const 
     const float one = (k == left) ? 1.f : 0.f;  // a select, not a dynamically indexed update (keeps wt[] in registers)
     wt[k].x += one; wt[k].y += one; wt[k].z += one; wt[k].w += one;
   }
+  pdl_wait();  // the taps are constants; v comes from the previous kernel
   const __nv_bfloat16* vcol = qkv + v_col + 4 * c4;
   const int ahead = K - 1 - left;  // newest input row of output row t is t + ahead
   const int r_end = min(M, (static_cast<int>(blockIdx.x) + 1) * FSMN_ROWS);
@@ -226,6 +230,8 @@ fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const 
 __global__ void __launch_bounds__(256)
 repack_rows_kernel(const float* __restrict__ src, int src_tmax, void* __restrict__ dst, int dst_tmax, int dst_bf16,
                    const int32_t* __restrict__ cu, int n_utts, int base, int dst_rows, int D) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (r >= dst_rows) return;
@@ -298,8 +304,7 @@ int launch_layernorm(const float* x, const float* g, const float* b, const float
   if (int r = ln_check(D, x)) return r;
   ew::LnArgs a{x, g, b, g2, b2, y_bf16, y_f32, nullptr, nullptr, 0, 0, 1.f, M, D, 0};
   ProfScope _ps(K_LAYERNORM, stream);
-  ew::layernorm_kernel<false><<<ceil_div(M, 8), 256, 0, stream>>>(a);
-  FA_CHECK_LAUNCH();
+  FA_CHECK_CUDA(launch_pdl(ew::layernorm_kernel<false>, dim3(ceil_div(M, 8)), dim3(256), 0, stream, 1, a));
   return 0;
 }
 
@@ -308,8 +313,7 @@ int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, con
   if (int r = ln_check(D, x)) return r;
   ew::LnArgs a{x, g, b, nullptr, nullptr, y, nullptr, inv_ts, cu, n_utts, base, scale, M, D, in_tmax};
   ProfScope _ps(K_LAYERNORM, stream);
-  ew::layernorm_kernel<true><<<ceil_div(M, 8), 256, 0, stream>>>(a);
-  FA_CHECK_LAUNCH();
+  FA_CHECK_CUDA(launch_pdl(ew::layernorm_kernel<true>, dim3(ceil_div(M, 8)), dim3(256), 0, stream, 1, a));
   return 0;
 }
 
@@ -326,8 +330,10 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
   ProfScope _ps(K_FSMN, stream);
 #define FA_FSMN_CASE(KK)                                                                                                           \
   case KK:                                                                                                                         \
-    if (out_bf16) ew::fsmn_kernel<KK, true><<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, base, mem, ld_out, M, D, left_pad); \
-    else ew::fsmn_kernel<KK, false><<<grid, threads, 0, stream>>>(qkv, ld, v_col, w, cu, n_utts, base, mem, ld_out, M, D, left_pad);         \
+    FA_CHECK_CUDA(out_bf16 ? launch_pdl(ew::fsmn_kernel<KK, true>, grid, dim3(threads), 0, stream, 1, qkv, ld, v_col, w, cu, n_utts,  \
+                                        base, mem, ld_out, M, D, left_pad)                                                          \
+                           : launch_pdl(ew::fsmn_kernel<KK, false>, grid, dim3(threads), 0, stream, 1, qkv, ld, v_col, w, cu, n_utts, \
+                                        base, mem, ld_out, M, D, left_pad));                                                        \
     break;
   switch (kernel) {
     FA_FSMN_CASE(1) FA_FSMN_CASE(2) FA_FSMN_CASE(3) FA_FSMN_CASE(4) FA_FSMN_CASE(5) FA_FSMN_CASE(6) FA_FSMN_CASE(7) FA_FSMN_CASE(8)
@@ -346,8 +352,8 @@ int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, 
              "repack: buffers must be 16-byte aligned");
   const int rows = dst_tmax > 0 ? n_utts * dst_tmax : M;
   ProfScope _ps(K_REPACK, stream);
-  ew::repack_rows_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(src, src_tmax, dst, dst_tmax, dst_bf16, cu, n_utts, base, rows, D);
-  FA_CHECK_LAUNCH();
+  FA_CHECK_CUDA(launch_pdl(ew::repack_rows_kernel, dim3(ceil_div(rows, 8)), dim3(256), 0, stream, 1, src, src_tmax, dst, dst_tmax,
+                           dst_bf16, cu, n_utts, base, rows, D));
   return 0;
 }
 

@@ -109,6 +109,7 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15;
+  pdl_launch_dependents();  // the first kernel of the path: its successor's prologue may overlap it
 
   int b, ti;
   if (MODE == 0) {

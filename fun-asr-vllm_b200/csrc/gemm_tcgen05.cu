@@ -278,6 +278,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_kb = (p.K + BK - 1) / BK;
   const int num_tiles = p.tiles_m * p.tiles_n;  // tiles of (BM * CTAS) x BN
@@ -327,6 +328,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if constexpr (CTAS == 2) cluster_sync(); else __syncthreads();  // barriers of BOTH CTAs are initialised past this point
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();  // prologue done (weights / bias are constants); activations of the previous kernel are visible from here
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -712,19 +714,8 @@ static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensor
     FA_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_done = true;
   }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(NUM_THREADS);
-  cfg.dynamicSmemBytes = C::SMEM_BYTES;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;  // the CTA pair of cta_group::2 is one cluster
-  attr[0].val.clusterDim.x = CTAS;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  FA_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, mr1, mr2, p));
+  // the CTA pair of cta_group::2 is one cluster
+  FA_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), C::SMEM_BYTES, stream, CTAS, ma, mb, mc, mr1, mr2, p));
   return 0;
 }
 
