@@ -34,7 +34,10 @@ constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;
 constexpr int SLAB_BYTES = 32 * 128;            // 32 rows x 128 B, SWIZZLE_128B (64 bf16 or 32 f32 columns)
 constexpr int SMEM_LIMIT = 227 * 1024;
 
-constexpr int RES_RING = 2;   // residual / output slots per epilogue warp (f32 epilogue with residuals)
+// residual / output slots per epilogue warp (f32 epilogue with residuals): loads run RING - 1 units ahead; a slot is
+// refilled only after the store that left from it has been read.  One residual: 3 slots (no exposed store drain).
+constexpr int res_ring(int nres) { return nres >= 1 ? 2 : 2; }  // (3 slots for one residual measured slower: one operand stage less)
+constexpr int RES_RING_MAX = 3;
 constexpr int BAR_BYTES = 512;
 
 // CTAS = 2: a CTA pair (one cluster, the two SMs of a TPC) computes a 256 x BN tile with tcgen05.mma.cta_group::2.  Each
@@ -50,7 +53,8 @@ struct Cfg {
   // residual 1 and then holds the result; slab 1 receives residual 2)
   // no residual: bf16 output (K = d_model GEMMs, little main-loop time per tile) gets two slabs so a store drains while the
   // next unit is produced; the f32 accumulate output (K = d_ff) keeps one slab and one more operand stage
-  static constexpr int SLABS_PER_WARP = NRES == 0 ? (OUT_F32 ? 1 : 2) : RES_RING * NRES;
+  static constexpr int RING = res_ring(NRES);
+  static constexpr int SLABS_PER_WARP = NRES == 0 ? (OUT_F32 ? 1 : 2) : RING * NRES;
   static constexpr int SLABS_BYTES = EPI_WARPS * SLABS_PER_WARP * SLAB_BYTES;
   // bf16 output: bias (and the folded-LN column sums) of all N columns are staged in smem once per CTA, so the epilogue's
   // per-column constants are short-latency broadcast LDS instead of L1 round trips (ncu: a fifth of its stall samples)
@@ -80,6 +84,7 @@ struct Params {
   const float* colsum;
   __nv_bfloat16* xb;
   long long ld_xb;
+  int prefetch_kb;  // A k-blocks requested into L2 this far ahead of the TMA load that consumes them (0 = off)
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -114,6 +119,9 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
       "l"(tmap), "r"(bar), "r"(x), "r"(y)
       : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_2d(const void* tmap, int x, int y) {  // global -> L2 only
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(tmap), "r"(x), "r"(y) : "memory");
 }
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int x, int y) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap), "r"(src), "r"(x),
@@ -273,8 +281,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::STAGES + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * C::STAGES + 2 + a); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 4);
-  auto res_bar = [&](int w, int slot) { return bar_base + 8u * (2 * C::STAGES + 5 + w * RES_RING + slot); };
-  static_assert(8 * (2 * C::STAGES + 5 + EPI_WARPS * RES_RING) <= BAR_BYTES, "barrier region too small");
+  auto res_bar = [&](int w, int slot) { return bar_base + 8u * (2 * C::STAGES + 5 + w * RES_RING_MAX + slot); };
+  static_assert(8 * (2 * C::STAGES + 5 + EPI_WARPS * RES_RING_MAX) <= BAR_BYTES, "barrier region too small");
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -303,7 +311,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_r1) : "memory");
       if (NRES > 1) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_r2) : "memory");
       for (int w = 0; w < EPI_WARPS; ++w)
-        for (int sl = 0; sl < RES_RING; ++sl) mbar_init(res_bar(w, sl), 1);
+        for (int sl = 0; sl < RES_RING_MAX; ++sl) mbar_init(res_bar(w, sl), 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -338,6 +346,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       for (int tile = cl; tile < num_tiles; tile += ncl) {
         const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
         for (int kb = 0; kb < num_kb; ++kb) {
+          if (p.prefetch_kb > 0) {  // the activation stream comes from HBM: have it in L2 before its TMA load is issued
+            int pk = kb + p.prefetch_kb, pt = tile;
+            while (pk >= num_kb) { pk -= num_kb; pt += ncl; }
+            if (pt < num_tiles) tma_prefetch_2d(&tmap_a, pk * BK, p.row0 + tile_row(pt / p.tiles_n));
+          }
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
           const uint32_t sb = sa + C::A_BYTES;
@@ -431,6 +444,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       // ---- f32 result with TMA-prefetched residuals.  This warp's units form one flat sequence n = it * UH + i over its
       // tiles; unit n lives in ring slot n % RES_RING.
       constexpr int UH = UNITS / 2;
+      constexpr int RES_RING = C::RING;
+      constexpr int LAG = RES_RING >= 3 ? 1 : 0;  // stores allowed to be still reading their slab when the next load is issued
       constexpr uint32_t SLOT_BYTES = NRES * SLAB_BYTES;
       const uint32_t ring = slab_base + ew * RES_RING * SLOT_BYTES;
       const int my_tiles = (num_tiles - cl + ncl - 1) / ncl;
@@ -455,7 +470,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       };
       if (lane == 0) {
 #pragma unroll
-        for (int n = 0; n < RES_RING; ++n) issue_load(n);
+        for (int n = 0; n < RES_RING - LAG; ++n) issue_load(n);
       }
       float ln_s = 0.f, ln_ss = 0.f;  // LN == 2: this lane's row, sums over the warp's units of the current tile
       for (int n = 0; n < total; ++n) {
@@ -527,12 +542,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             if (p.accumulate) tma_reduce_add_2d(&tmap_c, slab, col0, p.row0 + row0);
             else tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
             bulk_commit();
-            bulk_wait_read<0>();  // the slot may be refilled once the store has read it
+            bulk_wait_read<LAG>();  // the store that left slot (n + RES_RING - LAG) % RES_RING has read its slab
           }
         } else {
           store_rows_guarded(slab, row0, col0);
+          if (lane == 0) bulk_wait_read<0>();
         }
-        if (lane == 0) issue_load(n + RES_RING);
+        if (lane == 0) issue_load(n + RES_RING - LAG);
         __syncwarp();
       }
     } else {
@@ -741,6 +757,11 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   p.tiles_n = N / BN;
   p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
   p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32; p.accumulate = epi.accumulate;
+  {
+    static int pf = -1;
+    if (pf < 0) pf = getenv("FA_GEMM_PF") ? atoi(getenv("FA_GEMM_PF")) : 12;
+    p.prefetch_kb = pf;
+  }
   p.ln_stats = epi.ln_stats; p.colsum = epi.colsum; p.xb = epi.xb; p.ld_xb = epi.ld_xb;
   p.ln_slots = epi.ln_mode == 2 ? 2 * (N / BN) : epi.ln_slots;
   p.ln_inv_dim = epi.ln_dim > 0 ? 1.f / static_cast<float>(epi.ln_dim) : 0.f;
