@@ -36,7 +36,7 @@ constexpr int SMEM_LIMIT = 227 * 1024;
 
 // residual / output slots per epilogue warp (f32 epilogue with residuals): loads run RING - 1 units ahead; a slot is
 // refilled only after the store that left from it has been read.  One residual: 3 slots (no exposed store drain).
-constexpr int res_ring(int nres) { return nres >= 1 ? 2 : 2; }  // (3 slots for one residual measured slower: one operand stage less)
+constexpr int res_ring(int) { return 2; }  // (3 slots, i.e. no exposed store drain, measured slower: one operand stage less)
 constexpr int RES_RING_MAX = 3;
 constexpr int BAR_BYTES = 512;
 
@@ -84,7 +84,6 @@ struct Params {
   const float* colsum;
   __nv_bfloat16* xb;
   long long ld_xb;
-  int prefetch_kb;  // A k-blocks requested into L2 this far ahead of the TMA load that consumes them (0 = off)
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -119,9 +118,6 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
       "l"(tmap), "r"(bar), "r"(x), "r"(y)
       : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_2d(const void* tmap, int x, int y) {  // global -> L2 only
-  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(tmap), "r"(x), "r"(y) : "memory");
 }
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int x, int y) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap), "r"(src), "r"(x),
@@ -346,11 +342,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       for (int tile = cl; tile < num_tiles; tile += ncl) {
         const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
         for (int kb = 0; kb < num_kb; ++kb) {
-          if (p.prefetch_kb > 0) {  // the activation stream comes from HBM: have it in L2 before its TMA load is issued
-            int pk = kb + p.prefetch_kb, pt = tile;
-            while (pk >= num_kb) { pk -= num_kb; pt += ncl; }
-            if (pt < num_tiles) tma_prefetch_2d(&tmap_a, pk * BK, p.row0 + tile_row(pt / p.tiles_n));
-          }
+          // (an L2 prefetch of the A stream 8-32 k-blocks ahead was measured 8-12 % SLOWER on every shape: the ring is not
+          // waiting on HBM latency)
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
           const uint32_t sb = sa + C::A_BYTES;
@@ -757,11 +750,6 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   p.tiles_n = N / BN;
   p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
   p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32; p.accumulate = epi.accumulate;
-  {
-    static int pf = -1;
-    if (pf < 0) pf = getenv("FA_GEMM_PF") ? atoi(getenv("FA_GEMM_PF")) : 12;
-    p.prefetch_kb = pf;
-  }
   p.ln_stats = epi.ln_stats; p.colsum = epi.colsum; p.xb = epi.xb; p.ld_xb = epi.ld_xb;
   p.ln_slots = epi.ln_mode == 2 ? 2 * (N / BN) : epi.ln_slots;
   p.ln_inv_dim = epi.ln_dim > 0 ? 1.f / static_cast<float>(epi.ln_dim) : 0.f;
