@@ -15,6 +15,9 @@
 // 97 KB of smem and 256 TMEM columns — so that TWO CTAs share an SM (utterances are short: T = 167 for 10 s = three
 // key blocks).  Warp roles: 0 TMA producer, 1 MMA issuer (+ TMEM alloc), 2..5 softmax / epilogue (one TMEM lane quarter
 // each).
+// Measured alternative (kept out): one CTA per SM owning BOTH 128-row query tiles of an utterance with a 3-stage ring and
+// two softmax warpgroups (K/V loaded once, all 512 TMEM columns): 138 us instead of 121 us at T = 167 -- with a single
+// CTA per SM the load phase of one work item no longer overlaps the compute phase of another.
 #include <cuda.h>
 
 #include <cstring>
@@ -190,6 +193,16 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
   auto p_full = [&](int st) { return bars + 88 + 8 * st; };
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
+  auto issue_kv = [&](int j) {  // K_j and V_j into stage j & 1 (the caller has made sure the stage is free)
+    const int st = j & 1;
+    const int xk = dm + h * HD, xv = 2 * dm + h * HD, row = start + j * BKV;
+    mbar_expect_tx(k_full(st), K_BYTES);
+    tma_load_2d(sK(st), &tmap_qkv, k_full(st), xk, row);
+    tma_load_2d(sK(st) + KPANEL, &tmap_qkv, k_full(st), xk + 64, row);
+    mbar_expect_tx(v_full(st), V_BYTES);
+    tma_load_2d(sV(st), &tmap_qkv, v_full(st), xv, row);
+    tma_load_2d(sV(st) + KPANEL, &tmap_qkv, v_full(st), xv + 64, row);
+  };
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_qkv) : "memory");
     mbar_init(q_full, 1);
@@ -202,6 +215,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
       mbar_init(p_full(st), 128);  // every softmax thread arrives
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // Q and the first two K/V blocks are requested right here, before the TMEM allocation and the CTA-wide sync
+    // (the producer only needs its own barriers): ~0.4 us of the 1.7 us Q+K0 wait leaves the critical path
+    pdl_wait();
+    mbar_expect_tx(q_full, Q_BYTES);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)  // (panel, row half): box = 64 rows x 64 columns
+      tma_load_2d(sQ + (i >> 1) * QPANEL + (i & 1) * KPANEL, &tmap_qkv, q_full, h * HD + (i >> 1) * 64, start + q0 + (i & 1) * 64);
+    for (int j = 0; j < min(n_blk, STAGES); ++j) issue_kv(j);
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(TMEM_COLS) : "memory");
@@ -217,23 +238,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
   auto tS = [&](int st) { return tmem + st * BKV; };
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
+    // ===================== TMA producer (blocks 0 and 1 were requested during set-up) =====================
     if (lane == 0) {
-      const int xq = h * HD, xk = dm + h * HD, xv = 2 * dm + h * HD;
-      mbar_expect_tx(q_full, Q_BYTES);
-#pragma unroll
-      for (int i = 0; i < 4; ++i)  // (panel, row half): box = 64 rows x 64 columns
-        tma_load_2d(sQ + (i >> 1) * QPANEL + (i & 1) * KPANEL, &tmap_qkv, q_full, xq + (i >> 1) * 64, start + q0 + (i & 1) * 64);
-      for (int j = 0; j < n_blk; ++j) {
-        const int st = j & 1;
-        mbar_wait(kv_empty(st), ((j >> 1) & 1) ^ 1);  // P_{j-2} V_{j-2} retired: the K/P and V slots of this stage are free
-        const int row = start + j * BKV;
-        mbar_expect_tx(k_full(st), K_BYTES);
-        tma_load_2d(sK(st), &tmap_qkv, k_full(st), xk, row);
-        tma_load_2d(sK(st) + KPANEL, &tmap_qkv, k_full(st), xk + 64, row);
-        mbar_expect_tx(v_full(st), V_BYTES);
-        tma_load_2d(sV(st), &tmap_qkv, v_full(st), xv, row);
-        tma_load_2d(sV(st) + KPANEL, &tmap_qkv, v_full(st), xv + 64, row);
+      for (int j = STAGES; j < n_blk; ++j) {
+        mbar_wait(kv_empty(j & 1), ((j >> 1) & 1) ^ 1);  // P_{j-2} V_{j-2} retired: the K/P and V slots of this stage are free
+        issue_kv(j);
       }
     }
   } else if (warp == 1) {
