@@ -247,7 +247,7 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
         pipe.embed_device(dev_pcm, starts, lengths, out=out_dev)
 
     def step_e2e():
-        pipe.run_pinned(host_pcm, starts, lengths, out_host)
+        pipe.run_pinned(host_pcm, starts, lengths, out_host, overlap=False if args.no_overlap else None)
 
     def timed(fn, k):
         """K steps, each bracketed by CUDA events on the launching stream; L2 flushed (untimed) before every step."""
@@ -324,7 +324,9 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
                        "frontend": "povey, 80 mel, LFR 7/6, CMVN", "l2": "256 MiB flush before every timed step; weights 467 MB > L2",
                        "sharding": "by utterance, no collective",
                        "slab_tokens": args.chunk_tokens if args.chunk_tokens is not None else "off (library default)",
-                       "streams": args.streams if args.streams is not None else 2},
+                       "streams": args.streams if args.streams is not None else 2,
+                       "e2e_schedule": "single pass" if (args.no_overlap or rows < 8192 or len(lengths) < 8) else
+                       "two half-batches on two streams: H2D of half 2 and D2H of half 1 under compute"},
             "e2e": {"value": world * audio_s / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": int(host_pcm.numel() * 4), "d2h_bytes_per_step": int(out_host.numel() * 2)},
             "gpu_launches": int(sum(n for _, n in prof.values())),
@@ -356,6 +358,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg5", choices=["cfg5", "cfg2", "cfg3"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="e2e leg: one pass instead of the two-half overlapped schedule")
     ap.add_argument("--chunk-tokens", type=int, default=None, help="slab size of the layer schedule (0 = whole batch per layer)")
     ap.add_argument("--streams", type=int, default=None, help="1 = single stream, 2 = dual-stream half-batch schedule")
     args = ap.parse_args()

@@ -125,6 +125,20 @@ class Plan:
         self._pack()
         self._create(max_tokens)
 
+    def twin(self, max_tokens: int | None = None) -> "Plan":
+        """A second ``fa_plan`` over the SAME weight arena with its own workspace, so that two half-batches can be in
+        flight on two streams (``pipeline.AudioPipeline.run_pinned``); settings (streams, slab size) are inherited."""
+        t = Plan.__new__(Plan)
+        t.device, t.encoder, t.adaptor = self.device, self.encoder, self.adaptor
+        t.handle, t.cap = C.c_void_p(None), 0
+        t.arena, t.cfg, t.w = self.arena, self.cfg, self.w
+        t._layers, t._ad_layers = getattr(self, "_layers", None), getattr(self, "_ad_layers", None)
+        for k in ("chunk_tokens", "n_streams"):
+            if getattr(self, k, None) is not None:
+                setattr(t, k, getattr(self, k))
+        t._create(self.cap if max_tokens is None else max_tokens)
+        return t
+
     def _pack(self):
         enc, ad = self.encoder, self.adaptor
         ar = _Arena(self.device)

@@ -180,3 +180,35 @@ def test_state_dict_reload_invalidates_plan():
     enc.load_state_dict(sd)
     y1, _ = enc(x.cuda(), il)
     assert not torch.equal(y0, y1)
+
+
+def test_overlapped_pipeline_is_invisible():
+    """AudioPipeline.run_pinned(overlap=True): two half-batches, each with its own stream and workspace (Plan.twin shares the
+    weights), H2D of the second half and D2H of the first half under the other half's compute.  Rows must be bit-identical
+    to the single-pass schedule, call after call."""
+    import funasr_b200 as fb
+
+    _, _, enc, ad = _pair(2, 1)
+    fe = fb.WavFrontend(fs=16000, window="povey", n_mels=80, frame_length=25, frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0,
+                        cmvn=None, device="cuda")
+    g = torch.Generator().manual_seed(8)
+    n = np.array([16000, 48000, 160000, 8000, 24007, 33333, 100000, 400, 64000, 16001], np.int64)
+    starts = np.zeros(len(n), np.int64)
+    starts[1:] = np.cumsum((n[:-1] + 3) // 4 * 4)
+    total = int(starts[-1] + (n[-1] + 3) // 4 * 4)
+    host = torch.zeros(total).pin_memory()
+    for s0, k in zip(starts, n):
+        host[s0:s0 + k] = 0.5 * (2 * torch.rand(int(k), generator=g) - 1)
+    pipe = fb.AudioPipeline(fe, fb.AudioTower(enc, ad), "cuda")
+    _, T = fe.lengths(n)
+    rows = int(T.sum())
+    want = torch.empty((rows, 1024), dtype=torch.bfloat16).pin_memory()
+    cu0 = pipe.run_pinned(host, starts, n, want, overlap=False)
+    torch.cuda.synchronize()
+    assert 0 < pipe._cut(T) < len(n)
+    for _ in range(3):
+        got = torch.zeros((rows, 1024), dtype=torch.bfloat16).pin_memory()
+        cu1 = pipe.run_pinned(host, starts, n, got, overlap=True)
+        torch.cuda.synchronize()
+        assert np.array_equal(cu0, cu1)
+        assert torch.equal(got, want)
