@@ -37,14 +37,19 @@ class AudioPipeline:
         out, _ = self.tower.forward_packed(feats, np.diff(cu), out=out)
         return out, cu
 
-    def _twin(self, n_tokens: int):
-        """Second plan (own workspace, shared weights) + auxiliary stream for the overlapped schedule."""
+    def _twins(self, n0: int, n1: int):
+        """Two plans (own workspaces, the tower's weights) + auxiliary stream for the overlapped schedule.  Each runs its half
+        on ONE stream: the two halves already are the two streams (measured: letting each half split again doubles the
+        launches and loses 5 ms at cfg5, 5 ms at cfg3)."""
         plan = self.tower.plan()
         if getattr(self, "_twin_of", None) is not plan:
-            self._twin_plan, self._twin_of = plan.twin(max(n_tokens, 128)), plan
+            self._twin_plans = (plan.twin(max(n0, 128)), plan.twin(max(n1, 128)))
+            for t in self._twin_plans:
+                t.set_streams(1)
+            self._twin_of = plan
             self._aux = torch.cuda.Stream(self.device)
             self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
-        return self._twin_plan
+        return self._twin_plans
 
     @staticmethod
     def _cut(T: np.ndarray) -> int:
@@ -78,7 +83,7 @@ class AudioPipeline:
             return cu
         cut = self._cut(T)
         r_cut, s_cut = int(T[:cut].sum()), int(starts[cut])
-        plans = (self.tower.plan(), self._twin(rows - r_cut))
+        plans = self._twins(r_cut, rows - r_cut)
         main = torch.cuda.current_stream(self.device)
         dim = self.tower.adaptor.llm_dim
         if getattr(self, "_dev_out", None) is None or self._dev_out.shape[0] < rows or self._dev_out.shape[1] != dim:
