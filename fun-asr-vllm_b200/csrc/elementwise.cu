@@ -2,6 +2,7 @@
 // encoding, + fused second LayerNorm), FSMN depthwise memory block, row metadata, casts, splice.
 // All work on PACKED rows; utterance boundaries come from cu_seqlens / row_meta.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -223,6 +224,113 @@ fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const 
   }
 }
 
+// ---------------------------------------------------------------- FSMN, shared-memory staged (the default path)
+// Same arithmetic as fsmn_kernel, different data movement: a CTA owns R consecutive rows x 512 channels and pulls ALL the
+// input rows it needs (R + K - 1, one 1 KB bulk copy per row: cp.async.bulk global -> shared, completion on one mbarrier)
+// in a single round trip, instead of ~4 dependent rounds of per-thread 8-byte global loads.  The sliding window then
+// reads shared memory (one conflict-free LDS.64 per row and thread); rows outside the utterance enter the window as zeros.
+__device__ __forceinline__ void fs_mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void fs_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void fs_mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0;
+  while (!ok) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void fs_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ uint2 fs_lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+template <int K, int R, bool OUT_BF16>
+__global__ void __launch_bounds__(FSMN_THREADS)
+fsmn_staged_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
+                   const int32_t* __restrict__ cu, int n_utts, int base, void* __restrict__ mem, int64_t ld_out, int M, int D,
+                   int left) {
+  extern __shared__ __align__(128) unsigned char fs_smem[];
+  pdl_launch_dependents();
+  const int ch0 = blockIdx.y * (4 * FSMN_THREADS);  // first channel of this CTA's 512-channel chunk
+  const int wch = min(4 * FSMN_THREADS, D - ch0);   // channels in the chunk (multiple of 8: 16-byte bulk copies)
+  const int r0 = blockIdx.x * R, r_end = min(M, r0 + R);
+  const int ahead = K - 1 - left;  // newest input row of output row t is t + ahead
+  const int in0 = max(r0 - left, 0), in1 = min(r_end + ahead, M);  // input rows staged: [in0, in1), at most R + K - 1
+  const uint32_t tile = smem_u32(fs_smem), bar = tile + (R + K - 1) * 1024;
+  if (threadIdx.x == 0) {
+    fs_mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fs_mbar_expect_tx(bar, static_cast<uint32_t>(in1 - in0) * wch * 2);  // the only arrival: the phase cannot end before it
+  }
+  const bool active = 4 * static_cast<int>(threadIdx.x) < wch;
+  float4 wt[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    wt[k] = active ? __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(k) * D + ch0) + threadIdx.x)
+                   : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float one = (k == left) ? 1.f : 0.f;  // "+ inputs" = tap `left` with weight + 1
+    wt[k].x += one; wt[k].y += one; wt[k].z += one; wt[k].w += one;
+  }
+  __syncthreads();  // barrier initialised and armed
+  pdl_wait();       // the taps are constants; v comes from the previous kernel
+  if (static_cast<int>(threadIdx.x) < in1 - in0)
+    fs_bulk_g2s(tile + threadIdx.x * 1024, qkv + static_cast<int64_t>(in0 + threadIdx.x) * ld + v_col + ch0, wch * 2, bar);
+  if (!active) return;
+  int2 ub = utt_bounds(cu, n_utts, r0 + base);  // overlaps the copies
+  fs_mbar_wait(bar, 0);
+  const uint32_t col = tile + threadIdx.x * 8;
+  int r = r0;
+  while (r < r_end) {
+    if (r != r0) ub = utt_bounds(cu, n_utts, r + base);
+    const int lo = max(ub.x - base, in0), hi = min(ub.y - base, in1);  // rows of this utterance that exist in the tile
+    const int seg_end = min(r_end, ub.y - base);
+    auto load = [&](int row) -> float4 {
+      uint2 v = make_uint2(0u, 0u);
+      if (row >= lo && row < hi) v = fs_lds64(col + static_cast<uint32_t>(row - in0) * 1024u);
+      return bf16x4_to_f32(v);
+    };
+    float4 win[K];
+#pragma unroll
+    for (int i = 0; i < K - 1; ++i) win[i] = load(r - left + i);
+    for (int tb = r; tb < seg_end; tb += K) {
+#pragma unroll
+      for (int j = 0; j < K; ++j) {
+        if (tb + j < seg_end) {
+          win[(j + K - 1) % K] = load(tb + j + ahead);
+          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int k = 0; k < K; ++k) {
+            const float4 x = win[(j + k) % K];
+            a.x = fmaf(wt[k].x, x.x, a.x);
+            a.y = fmaf(wt[k].y, x.y, a.y);
+            a.z = fmaf(wt[k].z, x.z, a.z);
+            a.w = fmaf(wt[k].w, x.w, a.w);
+          }
+          const int64_t o = static_cast<int64_t>(tb + j) * ld_out + ch0 + 4 * threadIdx.x;
+          if (OUT_BF16) *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(mem) + o) = make_uint2(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w));
+          else *reinterpret_cast<float4*>(static_cast<float*>(mem) + o) = a;
+        }
+      }
+    }
+    r = seg_end;
+  }
+}
+
 // ---------------------------------------------------------------- row re-layout / splice
 // Row re-layout + cast: dst row r (packed [M,D] or padded [n_utts, dst_tmax, D]) <- the matching
 // src row (packed or padded [n_utts, src_tmax, D]), f32 -> f32 | bf16; padding rows are zero-filled.
@@ -326,8 +434,40 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
                  (reinterpret_cast<uintptr_t>(w) & 15) == 0,
              "fsmn: qkv must be 8-byte, mem and w 16-byte aligned");
   const int threads = ew::FSMN_THREADS;
-  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 4, threads));
   ProfScope _ps(K_FSMN, stream);
+  // Staged path (bulk copies into shared memory): the model's 11-tap kernel, 16-byte aligned rows.  FA_FSMN_STAGED=0 keeps the
+  // register-window kernel (A/B measurements); FA_FSMN_ROWS=32|64 picks the rows per CTA.
+  static const int staged_rows = [] {
+    const char* e = getenv("FA_FSMN_STAGED");
+    if (e && atoi(e) == 0) return 0;
+    const char* r = getenv("FA_FSMN_ROWS");
+    return (r && atoi(r) == 64) ? 64 : 32;
+  }();
+  if (staged_rows && kernel == 11 && D % 8 == 0 && v_col % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(qkv) & 15) == 0) {
+    const int R = staged_rows;
+    const size_t smem = static_cast<size_t>(R + kernel - 1) * 1024 + 16;
+    dim3 sgrid(ceil_div(M, R), ceil_div(D, 4 * threads));
+#define FA_FSMN_STAGED_LAUNCH(RR, BF)                                                                                              \
+  do {                                                                                                                             \
+    static bool attr = false;                                                                                                      \
+    if (!attr) {                                                                                                                   \
+      FA_CHECK_CUDA(cudaFuncSetAttribute(ew::fsmn_staged_kernel<11, RR, BF>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
+                                         static_cast<int>(smem)));                                                                 \
+      attr = true;                                                                                                                 \
+    }                                                                                                                              \
+    FA_CHECK_CUDA(launch_pdl(ew::fsmn_staged_kernel<11, RR, BF>, sgrid, dim3(threads), smem, stream, 1, qkv, ld, v_col, w, cu,     \
+                             n_utts, base, mem, ld_out, M, D, left_pad));                                                          \
+  } while (0)
+    if (R == 64) {
+      if (out_bf16) FA_FSMN_STAGED_LAUNCH(64, true); else FA_FSMN_STAGED_LAUNCH(64, false);
+    } else {
+      if (out_bf16) FA_FSMN_STAGED_LAUNCH(32, true); else FA_FSMN_STAGED_LAUNCH(32, false);
+    }
+#undef FA_FSMN_STAGED_LAUNCH
+    FA_CHECK_LAUNCH();
+    return 0;
+  }
+  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 4, threads));
 #define FA_FSMN_CASE(KK)                                                                                                           \
   case KK:                                                                                                                         \
     FA_CHECK_CUDA(out_bf16 ? launch_pdl(ew::fsmn_kernel<KK, true>, grid, dim3(threads), 0, stream, 1, qkv, ld, v_col, w, cu, n_utts,  \
