@@ -10,12 +10,13 @@ Importing this package never touches ``oracle/`` and never falls back to CPU/eag
 from . import _lib
 from ._lib import FunASRB200Error, LIB_PATH
 from .encoder import AudioTower, SenseVoiceEncoderSmall, Transformer
+from .ingest import Resample
 from .frontend import WavFrontend, extract_fbank, fake_token_len, load_cmvn, pack_waveforms
 from .pipeline import AudioPipeline
 from .registry import install, patch, tables
 from .sharding import gather_results, shard_contiguous, shard_lpt
 from .splice import splice_embeds
 
-__all__ = ["AudioPipeline", "AudioTower", "FunASRB200Error", "LIB_PATH", "SenseVoiceEncoderSmall", "Transformer",
+__all__ = ["AudioPipeline", "AudioTower", "FunASRB200Error", "LIB_PATH", "Resample", "SenseVoiceEncoderSmall", "Transformer",
            "WavFrontend", "extract_fbank", "fake_token_len", "gather_results", "install", "load_cmvn", "pack_waveforms",
            "patch", "shard_contiguous", "shard_lpt", "splice_embeds", "tables"]

@@ -65,6 +65,7 @@ PROTOTYPES = {
     "fa_adaptor_forward": (C.c_int, [vp, vp, i32, vp, vp, i32, i32, i32, vp, i32, i32, vp]),
     "fa_encode_adapt": (C.c_int, [vp, vp, i32, vp, vp, i32, i32, i32, vp, i32, vp, i32, i32, vp]),
     "fa_splice_embeds": (C.c_int, [vp, i32, vp, vp, vp, i32, vp, i32, vp, i32, i32, vp, i32, i32, vp]),
+    "fa_resample_sinc": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp]),
     "fa_profile_enable": (C.c_int, [i32]),
     "fa_profile_collect": (C.c_int, [vp, vp, i32]),
     "fa_op_gemm": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, vp, i64, i32, i32, i32, i32, i32, vp]),

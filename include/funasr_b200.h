@@ -16,6 +16,8 @@
  *   fa_encode_adapt       <- FunASRNano.forward_export(speech, lens)  model.py:251-254
  *   fa_splice_embeds      <- torch.cat([prefix, speech[:len], suffix]) infer.py:462-466 (model.py:513-541)
  *   fa_fake_token_len     <- fake_token_len arithmetic                model.py:391-396
+ *   fa_resample_sinc      <- torchaudio.transforms.Resample(sr, 16000)(audio)   infer.py:328-329, infer_kaldidata.py:454-455
+ *                            = _apply_sinc_resample_kernel             TA/functional/functional.py:1405-1432   
  *
  * Conventions
  *   - plain pointers and sizes only; every *_dev pointer is device memory owned by the caller;
@@ -225,6 +227,16 @@ int fa_splice_embeds(const void* speech_dev, int32_t speech_bf16, const int32_t*
                      const int32_t* take_dev, const void* prefix_dev, int32_t n_prefix, const void* suffix_dev,
                      int32_t n_suffix, const int64_t* out_off_dev, int32_t n_utts, int32_t dim, void* out_dev,
                      int32_t out_bf16, int32_t max_rows_per_utt, fa_stream_t stream);
+
+/* Audio ingest: polyphase windowed-sinc resampling of a packed batch (utterance b = in_len[b] samples at in_start[b]) to
+ * out_start[b] .. + ceil(new*len/orig).  `kernel_dev` is the [new_freq, taps_padded] f32 table (rows zero-padded from 2*width+orig taps to a multiple of 4) of
+ * TA/functional/functional.py:1305-1402 (orig/new already divided by their gcd), computed once on the host.  One CTA
+ * produces `frames_per_tile` (multiple of 32 * 8/min(8, pow2 <= new_freq)) output frames of `new_freq` samples; tile_off_dev [n_utts+1] is the prefix sum
+ * of ceil((len/orig + 1) / frames_per_tile) per utterance and n_tiles its last entry. */
+int fa_resample_sinc(const float* in_dev, const int64_t* in_start_dev, const int32_t* in_len_dev, const float* kernel_dev,
+                     int32_t orig, int32_t new_freq, int32_t width, int32_t taps_padded, int32_t frames_per_tile,
+                     float* out_dev, const int64_t* out_start_dev, const int32_t* tile_off_dev, int32_t n_utts,
+                     int32_t n_tiles, fa_stream_t stream);
 
 /* ------------------------------------------------------------------ device timing (bench.py) */
 /* When enabled, every kernel launch the library makes is bracketed by a CUDA event pair on the

@@ -98,3 +98,16 @@ if which in ("ln", "all"):
     g, b = torch.ones(512, device="cuda"), torch.zeros(512, device="cuda")
     best, avg = timeit(lambda: U.op_layernorm(x, g, b, True, False))
     print(f"layernorm: best {best*1e3:.1f} us -> {(M*512*6)/best/1e6:.0f} GB/s algorithmic (f32 in, bf16 out)")
+
+if which in ("resample", "all"):
+    for sr in (44100, 48000, 8000):
+        rs = fb.Resample(sr, 16000)
+        n = np.full(360, 10 * sr, np.int64)
+        starts = np.arange(360, dtype=np.int64) * (10 * sr)
+        wav = torch.rand(int(n.sum()), device="cuda") - 0.5
+        on = rs.out_lengths(n)
+        out = torch.zeros(int(((on + 3) // 4 * 4).sum()), device="cuda")
+        best, avg = timeit(lambda: rs.forward_packed(wav, starts, n, out=out))
+        byt = 4 * (n.sum() + on.sum())
+        print(f"resample {sr}->16000 1h ({rs.orig}/{rs.new}, {2*rs.width+rs.orig} taps): best {best*1e3:.1f} us -> {byt/best/1e6:.0f} GB/s algorithmic, "
+              f"{2*on.sum()*(2*rs.width+rs.orig)/best/1e9:.1f} TFLOP/s fp32")
