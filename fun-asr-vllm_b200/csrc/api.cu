@@ -14,6 +14,13 @@ namespace fa {
 
 static thread_local char g_err[1024] = "";
 
+namespace { thread_local bool t_launch_reverse = false; }
+bool launch_reverse() { return t_launch_reverse; }
+void set_launch_reverse(bool on) { t_launch_reverse = on; }
+bool serpentine_enabled() {
+  static const bool on = [] { const char* e = getenv("FA_SERPENTINE"); return e && atoi(e) != 0; }();
+  return on;
+}
 bool pdl_enabled() {  // FA_PDL=0 turns programmatic dependent launch off (A/B measurements)
   static int on = -1;
   if (on < 0) {
@@ -546,12 +553,23 @@ int adaptor_post(fa_plan* p, const Slab& sl, const RunArgs& a, void* out, int ou
                             a.M, c.ad_dim, a.s);
 }
 
+// One program on one stream; with the serpentine schedule every other step walks its rows last-to-first.
+int run_prog(const std::vector<Step>& prog, const RunArgs& a) {
+  const bool serp = serpentine_enabled();
+  int i = 0, rc = 0;
+  for (const Step& st : prog) {
+    set_launch_reverse(serp && (i++ & 1));
+    if ((rc = st(a))) break;
+  }
+  set_launch_reverse(false);
+  return rc;
+}
+
 int run_encoder(fa_plan* p, const Slab& sl, const float* feats, int feats_tmax, const int32_t* cu, float* enc_out,
                 int enc_out_tmax, cudaStream_t s) {
   const RunArgs a = args_of(sl, cu, s);
   if (int rc = encoder_pre(p, sl, a, feats, feats_tmax)) return rc;
-  for (const Step& st : p->enc_prog)
-    if (int rc = st(a)) return rc;
+  if (int rc = run_prog(p->enc_prog, a)) return rc;
   return encoder_post(p, sl, a, enc_out, enc_out_tmax);
 }
 
@@ -559,8 +577,7 @@ int run_adaptor(fa_plan* p, const Slab& sl, const float* enc, int enc_tmax, cons
                 int out_bf16, cudaStream_t s) {
   const RunArgs a = args_of(sl, cu, s);
   if (int rc = adaptor_pre(p, sl, a, enc, enc_tmax)) return rc;
-  for (const Step& st : p->ad_prog)
-    if (int rc = st(a)) return rc;
+  if (int rc = run_prog(p->ad_prog, a)) return rc;
   return adaptor_post(p, sl, a, out, out_tmax, out_bf16);
 }
 
@@ -624,12 +641,18 @@ int run_dual(fa_plan* p, const Slab (&sl)[2], const int32_t* cu, cudaStream_t s,
   }
   seq.push_back([&](int k) { return post(k, a[k]); });
   const int n = static_cast<int>(seq.size()), lag = std::max(0, p->lag);
+  const bool serp = serpentine_enabled();
   for (int i = 0; i < n + lag; ++i) {
-    if (i < n)
-      if (int rc = seq[i](0)) return rc;
-    if (i >= lag)
-      if (int rc = seq[i - lag](1)) return rc;
+    if (i < n) {
+      set_launch_reverse(serp && (i & 1));
+      if (int rc = seq[i](0)) { set_launch_reverse(false); return rc; }
+    }
+    if (i >= lag) {
+      set_launch_reverse(serp && ((i - lag) & 1));
+      if (int rc = seq[i - lag](1)) { set_launch_reverse(false); return rc; }
+    }
   }
+  set_launch_reverse(false);
   FA_CHECK_CUDA(cudaEventRecord(p->ev_join, p->aux));
   FA_CHECK_CUDA(cudaStreamWaitEvent(s, p->ev_join, 0));
   return 0;

@@ -168,12 +168,12 @@ __device__ __forceinline__ unsigned long long gtime() {
 // ---------------------------------------------------------------- kernel
 __global__ void __launch_bounds__(THREADS, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __restrict__ cu, int base, int n_heads,
-                 __nv_bfloat16* __restrict__ ctx, int64_t ld_ctx, float scale_log2e, unsigned long long* trace) {
+                 __nv_bfloat16* __restrict__ ctx, int64_t ld_ctx, float scale_log2e, int reverse, unsigned long long* trace) {
   extern __shared__ unsigned char smem_raw[];
   const int cta_lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
   if (threadIdx.x == 0) TRACE(0);
   pdl_launch_dependents();
-  const int b = blockIdx.z, h = blockIdx.y;  // (cu_seqlens is an input of the whole forward call, not a kernel's output)
+  const int b = reverse ? gridDim.z - 1 - blockIdx.z : blockIdx.z, h = blockIdx.y;  // serpentine: last utterance first  // (cu_seqlens is an input of the whole forward call, not a kernel's output)
   const int start = cu[b] - base, len = cu[b + 1] - cu[b];
   const int q0 = blockIdx.x * BQ;
   if (q0 >= len) return;  // uniform per CTA, before any barrier / TMEM use
@@ -453,7 +453,7 @@ int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seq
   const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(attn::HD));
   ProfScope _ps(K_ATTENTION, stream);
   FA_CHECK_CUDA(launch_pdl(attn::attention_kernel, grid, dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, cu_seqlens, base, n_heads,
-                           ctx, ld_ctx, scale_log2e, attn::g_trace));
+                           ctx, ld_ctx, scale_log2e, launch_reverse() ? 1 : 0, attn::g_trace));
   return 0;
 }
 

@@ -68,6 +68,7 @@ struct GemmEpilogue {
   const float* colsum = nullptr;  // consumer: [N] row sums of the bf16 weight
   __nv_bfloat16* xb = nullptr;  // producer: bf16 copy of C, row stride ld_xb
   int64_t ld_xb = 0;
+  int reverse = 0;  // walk the tile rows last-to-first (serpentine schedule)
 };
 
 struct TensorMap2D {  // opaque 128-byte CUtensorMap
@@ -118,6 +119,11 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 
 // Launch with the programmatic-stream-serialization attribute (and an optional cluster width).
 bool pdl_enabled();
+// Serpentine schedule (FA_SERPENTINE=1): the plan's step executor flips this before every other launch; a launch that sees it
+// walks its rows last-to-first, i.e. starts on the rows its predecessor wrote last (still in the 126 MB L2).
+bool launch_reverse();
+void set_launch_reverse(bool on);
+bool serpentine_enabled();
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, int cluster_x,
                               Args&&... args) {

@@ -263,12 +263,12 @@ template <int K, int R, bool OUT_BF16>
 __global__ void __launch_bounds__(FSMN_THREADS)
 fsmn_staged_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
                    const int32_t* __restrict__ cu, int n_utts, int base, void* __restrict__ mem, int64_t ld_out, int M, int D,
-                   int left) {
+                   int left, int reverse) {
   extern __shared__ __align__(128) unsigned char fs_smem[];
   pdl_launch_dependents();
   const int ch0 = blockIdx.y * (4 * FSMN_THREADS);  // first channel of this CTA's 512-channel chunk
   const int wch = min(4 * FSMN_THREADS, D - ch0);   // channels in the chunk (multiple of 8: 16-byte bulk copies)
-  const int r0 = blockIdx.x * R, r_end = min(M, r0 + R);
+  const int r0 = (reverse ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * R, r_end = min(M, r0 + R);  // serpentine: last rows first
   const int ahead = K - 1 - left;  // newest input row of output row t is t + ahead
   const int in0 = max(r0 - left, 0), in1 = min(r_end + ahead, M);  // input rows staged: [in0, in1), at most R + K - 1
   const uint32_t tile = smem_u32(fs_smem), bar = tile + (R + K - 1) * 1024;
@@ -456,7 +456,7 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
       attr = true;                                                                                                                 \
     }                                                                                                                              \
     FA_CHECK_CUDA(launch_pdl(ew::fsmn_staged_kernel<11, RR, BF>, sgrid, dim3(threads), smem, stream, 1, qkv, ld, v_col, w, cu,     \
-                             n_utts, base, mem, ld_out, M, D, left_pad));                                                          \
+                             n_utts, base, mem, ld_out, M, D, left_pad, launch_reverse() ? 1 : 0));                                \
   } while (0)
     if (R == 64) {
       if (out_bf16) FA_FSMN_STAGED_LAUNCH(64, true); else FA_FSMN_STAGED_LAUNCH(64, false);

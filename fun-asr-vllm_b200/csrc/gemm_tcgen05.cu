@@ -84,6 +84,7 @@ struct Params {
   const float* colsum;
   __nv_bfloat16* xb;
   long long ld_xb;
+  int reverse;  // walk the tile rows last-to-first
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -290,6 +291,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int cl = CTAS == 2 ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);    // tile-scheduler slot
   const int ncl = CTAS == 2 ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
   auto tile_row = [&](int tm) { return (tm * CTAS + static_cast<int>(rank)) * BM; };  // first row this CTA owns in tile row tm
+  // serpentine schedule: a launch may walk the tile rows last-to-first, so that it starts on the rows its predecessor wrote last
+  // (still in L2); the tile -> CTA assignment is otherwise unchanged
+  auto tm_of = [&](int tile) { const int t = tile / p.tiles_n; return p.reverse ? p.tiles_m - 1 - t : t; };
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
@@ -340,7 +344,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = cl; tile < num_tiles; tile += ncl) {
-        const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
+        const int tm = tm_of(tile), tn = tile % p.tiles_n;
         for (int kb = 0; kb < num_kb; ++kb) {
           // (an L2 prefetch of the A stream 8-32 k-blocks ahead was measured 8-12 % SLOWER on every shape: the ring is not
           // waiting on HBM latency)
@@ -446,7 +450,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       auto coords = [&](int n, int& row0, int& col0, int& u) {
         const int it = n / UH, i = n - it * UH;
         const int tile = cl + it * ncl;
-        const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
+        const int tm = tm_of(tile), tn = tile % p.tiles_n;
         u = hf + 2 * i;
         row0 = tile_row(tm) + q * 32;
         col0 = tn * BN + u * COLS;
@@ -551,7 +555,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       [[maybe_unused]] auto ld_stats = [&](int tile_, float4& a, float4& b) {
         a = make_float4(0.f, 0.f, 0.f, 0.f);
         b = a;
-        const int r_ = tile_row(tile_ / p.tiles_n) + q * 32 + lane;
+        const int r_ = tile_row(tm_of(tile_)) + q * 32 + lane;
         if (r_ >= p.M) return;
         const float2* sp = p.ln_stats + static_cast<long long>(p.row0 + r_) * p.ln_slots;  // written by the previous kernel
         if (p.ln_slots == 4) {  // 256-wide producer tiles over 512 columns: two 16-byte loads
@@ -574,7 +578,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       int n = 0;        // units this warp has produced
       int it = 0;
       for (int tile = cl; tile < num_tiles; tile += ncl, ++it) {
-        const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
+        const int tm = tm_of(tile), tn = tile % p.tiles_n;
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         const int row0 = tile_row(tm) + q * 32;
@@ -751,6 +755,7 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
   p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32; p.accumulate = epi.accumulate;
   p.ln_stats = epi.ln_stats; p.colsum = epi.colsum; p.xb = epi.xb; p.ld_xb = epi.ld_xb;
+  p.reverse = (epi.reverse || launch_reverse()) ? 1 : 0;
   p.ln_slots = epi.ln_mode == 2 ? 2 * (N / BN) : epi.ln_slots;
   p.ln_inv_dim = epi.ln_dim > 0 ? 1.f / static_cast<float>(epi.ln_dim) : 0.f;
   FA_REQUIRE(epi.out_f32 || N * 4 * (epi.ln_mode == 1 ? 2 : 1) <= 16384, "gemm: N=%d too wide for the staged epilogue constants", N);
