@@ -18,6 +18,10 @@
 // Measured alternative (kept out): one CTA per SM owning BOTH 128-row query tiles of an utterance with a 3-stage ring and
 // two softmax warpgroups (K/V loaded once, all 512 TMEM columns): 138 us instead of 121 us at T = 167 -- with a single
 // CTA per SM the load phase of one work item no longer overlaps the compute phase of another.
+// Second measured alternative (kept out, profiles/r01_m_attention_short.md): a single-pass kernel for utterances of <= 192 keys
+// (S for all keys in one MMA series, exact softmax, V loaded over Q, O over S's TMEM columns; still two CTAs per SM):
+// 115.7 us instead of 118.8 us at T = 167 -- the three block rounds are not what bounds the kernel -- and it would break the
+// bit-identity of the slab / whole-batch schedules (two kernels, two roundings), so the block loop stays the only path.
 #include <cuda.h>
 
 #include <cstring>
