@@ -312,15 +312,14 @@ fsmn_staged_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col,
       for (int j = 0; j < K; ++j) {
         if (tb + j < seg_end) {
           win[(j + K - 1) % K] = load(tb + j + ahead);
-          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+          float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);
 #pragma unroll
-          for (int k = 0; k < K; ++k) {
+          for (int k = 0; k < K; ++k) {  // packed f32x2 FMAs (Blackwell FFMA2): same IEEE fma per channel, half the issue slots
             const float4 x = win[(j + k) % K];
-            a.x = fmaf(wt[k].x, x.x, a.x);
-            a.y = fmaf(wt[k].y, x.y, a.y);
-            a.z = fmaf(wt[k].z, x.z, a.z);
-            a.w = fmaf(wt[k].w, x.w, a.w);
+            a01 = __ffma2_rn(make_float2(wt[k].x, wt[k].y), make_float2(x.x, x.y), a01);
+            a23 = __ffma2_rn(make_float2(wt[k].z, wt[k].w), make_float2(x.z, x.w), a23);
           }
+          const float4 a = make_float4(a01.x, a01.y, a23.x, a23.y);
           const int64_t o = static_cast<int64_t>(tb + j) * ld_out + ch0 + 4 * threadIdx.x;
           if (OUT_BF16) *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(mem) + o) = make_uint2(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w));
           else *reinterpret_cast<float4*>(static_cast<float*>(mem) + o) = a;
