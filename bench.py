@@ -205,7 +205,11 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
 
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
+    numa_cores = None
     if world > 1:
+        from funasr_b200.sharding import bind_to_gpu_numa
+
+        numa_cores = bind_to_gpu_numa(local_rank)  # pinned staging buffers on the GPU's own NUMA node
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -323,6 +327,7 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
                        "tokens_per_gpu": rows, "model": "SenseVoice SAN-M 50+20 blocks d512 ff2048 + adaptor 2x(d1024,8h), random init",
                        "frontend": "povey, 80 mel, LFR 7/6, CMVN", "l2": "256 MiB flush before every timed step; weights 467 MB > L2",
                        "sharding": "by utterance, no collective",
+                       "host_binding": (f"rank bound to {len(numa_cores)} GPU-local cores" if numa_cores else "none"),
                        "slab_tokens": args.chunk_tokens if args.chunk_tokens is not None else "off (library default)",
                        "streams": args.streams if args.streams is not None else 2,
                        "e2e_schedule": "single pass" if (args.no_overlap or rows < 8192 or len(lengths) < 8) else

@@ -53,3 +53,33 @@ def gather_results(local: dict, group=None) -> dict:
     for p in parts:
         merged.update(p)
     return dict(sorted(merged.items()))
+
+
+def bind_to_gpu_numa(device_index: int) -> list[int] | None:
+    """One process per GPU (``/root/reference/infer_kaldidata.py:1116-1122``): pin this process to the CPU cores NVML reports as
+    local to GPU ``device_index`` (``CUDA_VISIBLE_DEVICES`` order is honoured), so that the pinned staging buffers it allocates
+    next land on the NUMA node of that GPU's PCIe root.  Best effort: returns the cores used, or ``None`` when NVML or the
+    affinity call is unavailable or the intersection with the allowed cores is empty (nothing is changed then)."""
+    import os
+
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = device_index
+        if vis:
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if device_index < len(ids) and ids[device_index].isdigit():
+                phys = int(ids[device_index])
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        n_cpu = os.cpu_count() or 64
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        ideal = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        cores = sorted(ideal & os.sched_getaffinity(0))
+        if not cores:
+            return None
+        os.sched_setaffinity(0, cores)
+        return cores
+    except Exception:
+        return None
