@@ -60,10 +60,17 @@ resample_kernel(const float* __restrict__ in, const int64_t* __restrict__ in_sta
     for (int a = 0; a < J; ++a)
 #pragma unroll
       for (int f = 0; f < F; ++f) acc[a][f] = 0.f;
+    float4 wn[J];  // taps of the next 4-tap step, requested one step ahead (the table is L2-resident, not L1-resident)
+#pragma unroll
+    for (int a = 0; a < J; ++a) wn[a] = __ldg(kj[a]);
     for (int k = 0; k < Kp; k += 4) {
       float4 w[J];
 #pragma unroll
-      for (int a = 0; a < J; ++a) w[a] = __ldg(kj[a] + (k >> 2));
+      for (int a = 0; a < J; ++a) w[a] = wn[a];
+      if (k + 4 < Kp) {
+#pragma unroll
+        for (int a = 0; a < J; ++a) wn[a] = __ldg(kj[a] + ((k + 4) >> 2));
+      }
 #pragma unroll
       for (int f = 0; f < F; ++f) {
         const float x0v = xf[f][k], x1v = xf[f][k + 1], x2v = xf[f][k + 2], x3v = xf[f][k + 3];
