@@ -83,3 +83,15 @@ def test_two_ranks_gloo_shard_and_merge():
     assert keys == sorted(keys) and len(keys) == n  # ordered by utterance id like the reference's merged files
     T = [17 + (7 * i) % 480 for i in range(n)]
     assert all(v == (T[int(k[3:])], (T[int(k[3:])] * 2654435761) % 9973) for k, v in merged0)
+
+
+def test_bind_to_gpu_numa_is_best_effort():
+    """No GPU / no NVML here: the helper must change nothing and say so (None); with NVML it returns the cores it bound to."""
+    import os
+
+    from funasr_b200.sharding import bind_to_gpu_numa
+
+    before = os.sched_getaffinity(0)
+    got = bind_to_gpu_numa(0)
+    after = os.sched_getaffinity(0)
+    assert got is None and after == before or set(got) == after and after <= before
