@@ -436,14 +436,19 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
   ProfScope _ps(K_FSMN, stream);
   // Staged path (bulk copies into shared memory): the model's 11-tap kernel, 16-byte aligned rows.  FA_FSMN_STAGED=0 keeps the
   // register-window kernel (A/B measurements); FA_FSMN_ROWS=32|64 picks the rows per CTA.
-  static const int staged_rows = [] {
+  static const int staged_rows = [] {  // 0 = off, -1 = by size (default), else forced
     const char* e = getenv("FA_FSMN_STAGED");
     if (e && atoi(e) == 0) return 0;
     const char* r = getenv("FA_FSMN_ROWS");
-    return (r && atoi(r) == 64) ? 64 : 32;
+    const int v = r ? atoi(r) : -1;
+    return (v == 8 || v == 16 || v == 32 || v == 64) ? v : -1;
   }();
   if (staged_rows && kernel == 11 && D % 8 == 0 && v_col % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(qkv) & 15) == 0) {
-    const int R = staged_rows;
+    // rows per CTA: the largest of 32 / 16 / 8 that still gives every SM a CTA.  For small batches the serial walk over a
+    // CTA's rows is the kernel's whole duration (cfg2 half-batch: 1 336 rows = 42 CTAs of 32 rows, 10.6 us per launch; 167
+    // CTAs of 8 rows, 8.6 us); once every SM has work, more and smaller CTAs only add halo reads (measured: cfg3, r01-s).
+    const int sms = sm_count();
+    const int R = staged_rows > 0 ? staged_rows : (M >= 32 * sms ? 32 : M >= 16 * sms ? 16 : 8);
     const size_t smem = static_cast<size_t>(R + kernel - 1) * 1024 + 16;
     dim3 sgrid(ceil_div(M, R), ceil_div(D, 4 * threads));
 #define FA_FSMN_STAGED_LAUNCH(RR, BF)                                                                                              \
@@ -457,11 +462,13 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
     FA_CHECK_CUDA(launch_pdl(ew::fsmn_staged_kernel<11, RR, BF>, sgrid, dim3(threads), smem, stream, 1, qkv, ld, v_col, w, cu,     \
                              n_utts, base, mem, ld_out, M, D, left_pad, launch_reverse() ? 1 : 0));                                \
   } while (0)
-    if (R == 64) {
-      if (out_bf16) FA_FSMN_STAGED_LAUNCH(64, true); else FA_FSMN_STAGED_LAUNCH(64, false);
-    } else {
-      if (out_bf16) FA_FSMN_STAGED_LAUNCH(32, true); else FA_FSMN_STAGED_LAUNCH(32, false);
-    }
+#define FA_FSMN_STAGED_ROWS(RR) \
+  do { if (out_bf16) FA_FSMN_STAGED_LAUNCH(RR, true); else FA_FSMN_STAGED_LAUNCH(RR, false); } while (0)
+    if (R == 64) FA_FSMN_STAGED_ROWS(64);
+    else if (R == 32) FA_FSMN_STAGED_ROWS(32);
+    else if (R == 16) FA_FSMN_STAGED_ROWS(16);
+    else FA_FSMN_STAGED_ROWS(8);
+#undef FA_FSMN_STAGED_ROWS
 #undef FA_FSMN_STAGED_LAUNCH
     FA_CHECK_LAUNCH();
     return 0;
