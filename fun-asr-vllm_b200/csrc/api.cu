@@ -5,6 +5,8 @@
 #include <algorithm>
 #include <cstring>
 #include <functional>
+#include <list>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -14,13 +16,6 @@ namespace fa {
 
 static thread_local char g_err[1024] = "";
 
-namespace { thread_local bool t_launch_reverse = false; }
-bool launch_reverse() { return t_launch_reverse; }
-void set_launch_reverse(bool on) { t_launch_reverse = on; }
-bool serpentine_enabled() {
-  static const bool on = [] { const char* e = getenv("FA_SERPENTINE"); return e && atoi(e) != 0; }();
-  return on;
-}
 bool pdl_enabled() {  // FA_PDL=0 turns programmatic dependent launch off (A/B measurements)
   static int on = -1;
   if (on < 0) {
@@ -37,13 +32,17 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-      n = 148;
+int sm_count() {  // of the current device; cached per device (a process may drive several GPUs)
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev >= 0 && dev < 64) {
+    const int c = cache[dev].load(std::memory_order_relaxed);
+    if (c > 0) return c;
   }
+  int n = 0;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  if (dev >= 0 && dev < 64) cache[dev].store(n, std::memory_order_relaxed);
   return n;
 }
 
@@ -51,6 +50,7 @@ int sm_count() {
 bool g_prof_on = false;
 namespace {
 struct ProfRec { int kind; cudaEvent_t a, b; };
+std::mutex g_prof_mu;  // the records are process-wide; launches may come from several host threads
 std::vector<ProfRec> g_prof_recs;
 std::vector<cudaEvent_t> g_prof_pool;
 cudaEvent_t prof_event() {
@@ -61,6 +61,7 @@ cudaEvent_t prof_event() {
 }
 }  // namespace
 void prof_mark(int kind, cudaStream_t s, bool begin) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   if (begin) {
     ProfRec r{kind, prof_event(), nullptr};
     cudaEventRecord(r.a, s);
@@ -82,6 +83,7 @@ extern "C" int fa_profile_enable(int32_t on) {
 }
 extern "C" int fa_profile_collect(float* ms_per_kind, int32_t* launches_per_kind, int32_t n_kinds) {
   FA_REQUIRE(ms_per_kind && launches_per_kind && n_kinds >= K_NUM, "profile_collect: need %d slots", (int)K_NUM);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   for (int i = 0; i < n_kinds; ++i) { ms_per_kind[i] = 0.f; launches_per_kind[i] = 0; }
   for (ProfRec& r : g_prof_recs) {
     if (r.b) {
@@ -139,6 +141,7 @@ struct Workspace {
   __nv_bfloat16* aqkv;   // [cap, 3*ad_dim]
   __nv_bfloat16* actx;   // [cap, ad_dim]
   __nv_bfloat16* ah;     // [cap, ad_ff]
+  int32_t* cu;           // [cap + 8]        cu_seqlens at a FIXED address, padded to the utterance bucket (graph replay)
   size_t bytes;
 };
 
@@ -168,6 +171,7 @@ Workspace carve(const fa_model_cfg& c, int cap, unsigned char* base) {
   w.aqkv = reinterpret_cast<__nv_bfloat16*>(take(n * 3 * c.ad_dim * 2));
   w.actx = reinterpret_cast<__nv_bfloat16*>(take(n * c.ad_dim * 2));
   w.ah = reinterpret_cast<__nv_bfloat16*>(take(n * c.ad_ff * 2));
+  w.cu = reinterpret_cast<int32_t*>(take((n + 8) * 4));
   w.bytes = off;
   return w;
 }
@@ -241,30 +245,35 @@ int run_gemm_op(const GemmOp& op, const RunArgs& a) {
   FA_REQUIRE(bn != 0 && op.tb_ok[idx], "gemm N=%d unsupported", op.N);
   const bool pair = gemm_use_pair(a.M, bn) && op.tb_ok[1];
   GemmEpilogue epi = op.epi;
-  if (epi.ln_mode == 1) {  // the producer ran on the same rows just before: same tile heuristic -> same slot count
-    const int pbn = gemm_block_n(a.M, op.prod_N, 1);
-    FA_REQUIRE(pbn != 0, "gemm: producer width %d unsupported", op.prod_N);
-    epi.ln_slots = 2 * (op.prod_N / pbn);
-  }
+  if (epi.ln_mode == 1) epi.ln_slots = op.prod_N / 32;  // the producer leaves one partial per 32 columns of its output
   return launch_gemm(op.ta, op.tb[pair ? 1 : idx], op.tc, epi.res1 ? &op.tr1 : nullptr, epi.res2 ? &op.tr2 : nullptr, bn, a.M,
                      op.N, op.K, epi, op.c, op.ldc, a.row0, pair, a.s);
 }
 
 }  // namespace
 
+// One instantiated CUDA graph of a program for one (rows, utterances, longest utterance) bucket.
+struct GraphEntry {
+  int prog, rows, utts, max_len;
+  cudaGraphExec_t exec;
+};
+
 struct fa_plan {
   fa_model_cfg cfg;
   fa_model_w w;
   int cap;
-  int chunk_tokens;  // 0: never split a batch
-  int n_streams;     // 1: everything on the caller's stream; 2: two half-batches, the second on `aux` (fork/join by events)
-  int lag;           // dual-stream issue order: half 1 trails half 0 by this many program steps
+  int n_streams;        // 1: everything on the caller's stream; 2: two half-batches, the second on `aux` (fork/join by events)
+  int graph_max_rows;   // batches of up to this many rows replay a captured CUDA graph of the program (0: never)
   cudaStream_t aux = nullptr;
+  cudaStream_t cap_stream = nullptr;  // only ever used in capture mode: nothing executes on it
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   Workspace ws;
   std::vector<Step> enc_prog, ad_prog;
+  std::list<GraphEntry> graphs;  // most recently used first
   ~fa_plan() {
+    for (GraphEntry& g : graphs) cudaGraphExecDestroy(g.exec);
     if (aux) cudaStreamDestroy(aux);
+    if (cap_stream) cudaStreamDestroy(cap_stream);
     if (ev_fork) cudaEventDestroy(ev_fork);
     if (ev_join) cudaEventDestroy(ev_join);
   }
@@ -295,9 +304,16 @@ struct Builder {
     });
   }
   void attention(std::vector<Step>& prog, const __nv_bfloat16* qkv, __nv_bfloat16* ctx, int H, int D, int ld_ctx) {
-    prog.push_back([=](const RunArgs& r) {
-      return launch_attention(qkv + static_cast<int64_t>(r.row0) * 3 * D, 3 * D, r.cu, r.n_utts, r.row0, r.max_len, H,
-                              ctx + static_cast<int64_t>(r.row0) * ld_ctx, ld_ctx, r.M, r.s);
+    if (rc) return;
+    // one tensor map over the whole qkv buffer, encoded once per plan: utterances are addressed by their ABSOLUTE packed rows
+    // (base 0).  Key / value rows past the end of a batch are workspace rows, which hold finite values (the caller hands in a
+    // zero-filled workspace and every kernel keeps them finite), so 0 * garbage stays 0 in P V.
+    TensorMap2D tm;
+    const int cap = p->cap;
+    rc = make_tensor_map_bf16(&tm, qkv, cap, 3 * D, 3 * D, attention_kv_box());
+    if (rc) return;
+    prog.push_back([tm, qkv, ctx, H, D, ld_ctx, cap](const RunArgs& r) {
+      return launch_attention(&tm, qkv, 3 * D, r.cu, r.n_utts, 0, r.max_len, H, ctx, ld_ctx, cap, r.s);
     });
   }
 };
@@ -404,17 +420,9 @@ int build_programs(fa_plan* p) {
   return B.rc;
 }
 
-int default_chunk_tokens() {
-  // Measured on B200 (profiles/r01_b_slab_sweep.md): with ~580 dependent launches per slab, every extra slab costs ~5 ms
-  // of per-kernel ramp-up/drain, more than the L2 residency it buys (cfg5: 59.9 ms unsplit, 90.5 ms at 8704-row slabs).
-  // The schedule is therefore OFF by default; FA_CHUNK_TOKENS=<n> or fa_plan_set_chunk_tokens turn it on.
-  if (const char* e = getenv("FA_CHUNK_TOKENS")) return atoi(e);
-  return 0;
-}
-
 int default_streams() {
-  // Measured on B200 (profiles/r01_d_dual_stream.md): cfg3 (16 k rows) 16.9 -> 15.2 ms, cfg5 (60 k rows) 52.4 -> 52.3 ms
-  // (power-capped either way).  On by default; FA_STREAMS=1 or fa_plan_set_streams(plan, 1) turn it off.
+  // Measured on B200 (profiles/r01_d_dual_stream.md): cfg3 (16 k rows) 16.9 -> 15.2 ms.  On by default; FA_STREAMS=1 or
+  // fa_plan_set_streams(plan, 1) turn it off.
   if (const char* e = getenv("FA_STREAMS")) return atoi(e) >= 2 ? 2 : 1;
   return 2;
 }
@@ -444,9 +452,8 @@ extern "C" int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void
   p->cfg = *cfg;
   p->w = *w;
   p->cap = cap;
-  p->chunk_tokens = default_chunk_tokens();
   p->n_streams = default_streams();
-  p->lag = getenv("FA_STREAM_LAG") ? atoi(getenv("FA_STREAM_LAG")) : 0;
+  p->graph_max_rows = FA_DEFAULT_GRAPH_ROWS;
   p->ws = ws;
   if (int rc = build_programs(p)) {
     delete p;
@@ -458,15 +465,15 @@ extern "C" int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void
 
 extern "C" void fa_plan_destroy(fa_plan* plan) { delete plan; }
 
-extern "C" int fa_plan_set_chunk_tokens(fa_plan* plan, int32_t chunk_tokens) {
-  FA_REQUIRE(plan != nullptr && chunk_tokens >= 0, "set_chunk_tokens: bad arguments");
-  plan->chunk_tokens = chunk_tokens;
-  return 0;
-}
-
 extern "C" int fa_plan_set_streams(fa_plan* plan, int32_t n_streams) {
   FA_REQUIRE(plan != nullptr && (n_streams == 1 || n_streams == 2), "set_streams: 1 or 2 streams");
   plan->n_streams = n_streams;
+  return 0;
+}
+
+extern "C" int fa_plan_set_graph_rows(fa_plan* plan, int32_t max_rows) {
+  FA_REQUIRE(plan != nullptr && max_rows >= 0, "set_graph_rows: bad arguments");
+  plan->graph_max_rows = max_rows;
   return 0;
 }
 
@@ -477,6 +484,7 @@ int check_batch(const fa_plan* p, const int32_t* cu, int n_utts, int n_tokens, i
   FA_REQUIRE(cu != nullptr && n_utts > 0, "empty batch");
   FA_REQUIRE(n_tokens > 0 && n_tokens <= p->cap, "n_tokens %d exceeds the plan capacity %d", n_tokens, p->cap);
   FA_REQUIRE(max_len > 0 && max_len <= n_tokens, "max_len %d out of range", max_len);
+  FA_REQUIRE(n_utts <= n_tokens, "%d utterances in %d rows", n_utts, n_tokens);
   return 0;
 }
 
@@ -485,36 +493,8 @@ int check_tmax(int tmax, int max_len, const char* what) {
   return 0;
 }
 
-// A slab of consecutive utterances [b0, b1) = packed rows [row0, row0 + M).
+// A run of consecutive utterances [b0, b1) = packed rows [row0, row0 + M).
 struct Slab { int b0, b1, row0, M, max_len; };
-
-// Split the batch into slabs of about plan->chunk_tokens rows on utterance boundaries (utterances are independent, so any
-// split computes the same rows).  Needs the HOST copy of cu_seqlens; without it (or with chunking off) the batch is one slab.
-int make_slabs(const fa_plan* p, const int32_t* cu_host, int n_utts, int M, int max_len, std::vector<Slab>* out) {
-  out->clear();
-  if (cu_host == nullptr || p->chunk_tokens <= 0 || M <= p->chunk_tokens + p->chunk_tokens / 4) {
-    out->push_back(Slab{0, n_utts, 0, M, max_len});
-    return 0;
-  }
-  FA_REQUIRE(cu_host[0] == 0 && cu_host[n_utts] == M, "cu_seqlens_host does not describe %d rows", M);
-  const int n_slabs = (M + p->chunk_tokens - 1) / p->chunk_tokens;
-  int b = 0;
-  for (int i = 0; i < n_slabs && b < n_utts; ++i) {
-    const int64_t want_end = static_cast<int64_t>(M) * (i + 1) / n_slabs;  // even split, snapped to an utterance boundary
-    int e = b + 1;
-    while (e < n_utts && (i == n_slabs - 1 || cu_host[e + 1] - want_end <= want_end - cu_host[e])) ++e;
-    if (i == n_slabs - 1) e = n_utts;
-    int ml = 0;
-    for (int u = b; u < e; ++u) {
-      const int len = cu_host[u + 1] - cu_host[u];
-      FA_REQUIRE(len > 0, "utterance %d has %d rows", u, len);
-      ml = len > ml ? len : ml;
-    }
-    out->push_back(Slab{b, e, cu_host[b], cu_host[e] - cu_host[b], ml});
-    b = e;
-  }
-  return 0;
-}
 
 RunArgs args_of(const Slab& sl, const int32_t* cu, cudaStream_t s) {
   return RunArgs{sl.M, sl.b1 - sl.b0, sl.max_len, sl.row0, cu + sl.b0, s};
@@ -553,32 +533,97 @@ int adaptor_post(fa_plan* p, const Slab& sl, const RunArgs& a, void* out, int ou
                             a.M, c.ad_dim, a.s);
 }
 
-// One program on one stream; with the serpentine schedule every other step walks its rows last-to-first.
 int run_prog(const std::vector<Step>& prog, const RunArgs& a) {
-  const bool serp = serpentine_enabled();
-  int i = 0, rc = 0;
-  for (const Step& st : prog) {
-    set_launch_reverse(serp && (i++ & 1));
-    if ((rc = st(a))) break;
+  for (const Step& st : prog)
+    if (int rc = st(a)) return rc;
+  return 0;
+}
+
+// ---- CUDA-graph replay ------------------------------------------------------------------------------------------------
+// A program is ~440 dependent launches; at the reference's own batch sizes (16 x 10 s = 2 672 rows, infer.py:415) a launch
+// runs for 5-10 us, about what the host needs to issue it, so the step is launch-bound.  The program of a plan is static
+// (fixed workspace pointers, prebuilt tensor maps), and everything that varies per batch is either read from cu_seqlens ON
+// THE DEVICE (utterance boundaries, the true row count) or only sizes a grid.  So the program is captured once per BUCKET
+// (rows rounded up to ~1/8 octave, utterances to a multiple of 8, longest utterance to a multiple of 128 rows) with
+// cu_seqlens at a fixed workspace address, and replayed with one cudaGraphLaunch.  Per call a tiny kernel copies the caller's
+// cu_seqlens there, padded with the total row count: padded utterances are empty (their CTAs exit), rows between the true
+// count and the bucket are computed on finite workspace contents and never read.  The programmatic-dependent-launch edges
+// survive capture.  (The reference's vLLM side captures graphs the same way: infer_kaldidata.py:655-656.)
+int bucket_rows(int M, int cap) {
+  int gran = 128;
+  while (gran < 4096 && gran * 16 <= M) gran *= 2;  // 128 below 2048 rows, then ~1/8 .. 1/16 of M
+  const int b = (M + gran - 1) / gran * gran;
+  return b < cap ? b : cap;
+}
+int bucket_utts(int n, int rows) {
+  const int g = n <= 64 ? 8 : 32;
+  const int b = (n + g - 1) / g * g;
+  return b < rows ? b : rows;
+}
+
+int ensure_capture_stream(fa_plan* p) {
+  if (p->cap_stream) return 0;
+  FA_CHECK_CUDA(cudaStreamCreateWithFlags(&p->cap_stream, cudaStreamNonBlocking));
+  return 0;
+}
+
+constexpr size_t MAX_GRAPHS = 48;
+
+int graph_for(fa_plan* p, int prog_id, const std::vector<Step>& prog, int rows, int utts, int max_len, cudaGraphExec_t* out) {
+  for (auto it = p->graphs.begin(); it != p->graphs.end(); ++it) {
+    if (it->prog == prog_id && it->rows == rows && it->utts == utts && it->max_len == max_len) {
+      p->graphs.splice(p->graphs.begin(), p->graphs, it);
+      *out = p->graphs.front().exec;
+      return 0;
+    }
   }
-  set_launch_reverse(false);
-  return rc;
+  if (int rc = ensure_capture_stream(p)) return rc;
+  FA_CHECK_CUDA(cudaStreamBeginCapture(p->cap_stream, cudaStreamCaptureModeThreadLocal));
+  const RunArgs a{rows, utts, max_len, 0, p->ws.cu, p->cap_stream};
+  const int rc = run_prog(prog, a);
+  cudaGraph_t g = nullptr;
+  const cudaError_t e = cudaStreamEndCapture(p->cap_stream, &g);
+  if (rc) {
+    if (g) cudaGraphDestroy(g);
+    return rc;
+  }
+  if (e != cudaSuccess) {
+    set_error("cudaStreamEndCapture failed: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  cudaGraphExec_t exec = nullptr;
+  const cudaError_t ei = cudaGraphInstantiate(&exec, g, 0);
+  cudaGraphDestroy(g);
+  if (ei != cudaSuccess) {
+    set_error("cudaGraphInstantiate failed: %s", cudaGetErrorString(ei));
+    return 1;
+  }
+  if (p->graphs.size() >= MAX_GRAPHS) {  // the in-flight replays of an evicted graph keep it alive until they finish
+    cudaGraphExecDestroy(p->graphs.back().exec);
+    p->graphs.pop_back();
+  }
+  p->graphs.push_front(GraphEntry{prog_id, rows, utts, max_len, exec});
+  *out = exec;
+  return 0;
 }
 
-int run_encoder(fa_plan* p, const Slab& sl, const float* feats, int feats_tmax, const int32_t* cu, float* enc_out,
-                int enc_out_tmax, cudaStream_t s) {
-  const RunArgs a = args_of(sl, cu, s);
-  if (int rc = encoder_pre(p, sl, a, feats, feats_tmax)) return rc;
-  if (int rc = run_prog(p->enc_prog, a)) return rc;
-  return encoder_post(p, sl, a, enc_out, enc_out_tmax);
-}
+// true when this call replays graphs; then a.cu of the returned bucket args points at the plan's padded copy
+bool use_graph(const fa_plan* p, int M) { return p->graph_max_rows > 0 && M <= p->graph_max_rows && !g_prof_on; }
 
-int run_adaptor(fa_plan* p, const Slab& sl, const float* enc, int enc_tmax, const int32_t* cu, void* out, int out_tmax,
-                int out_bf16, cudaStream_t s) {
-  const RunArgs a = args_of(sl, cu, s);
-  if (int rc = adaptor_pre(p, sl, a, enc, enc_tmax)) return rc;
-  if (int rc = run_prog(p->ad_prog, a)) return rc;
-  return adaptor_post(p, sl, a, out, out_tmax, out_bf16);
+int run_graphed(fa_plan* p, int n_utts, int M, int max_len, const int32_t* cu, cudaStream_t s, const std::function<int(const RunArgs&)>& pre,
+                const std::vector<std::pair<int, const std::vector<Step>*>>& progs, const std::function<int(const RunArgs&)>& mid,
+                const std::function<int(const RunArgs&)>& post) {
+  const int rows = bucket_rows(M, p->cap), utts = bucket_utts(n_utts, rows), ml = std::min(rows, (max_len + 127) / 128 * 128);
+  const RunArgs a{M, n_utts, max_len, 0, cu, s};
+  if (int rc = launch_pad_cu(cu, n_utts, p->ws.cu, utts, s)) return rc;
+  if (int rc = pre(a)) return rc;
+  for (size_t i = 0; i < progs.size(); ++i) {
+    if (i > 0) if (int rc = mid(a)) return rc;
+    cudaGraphExec_t exec = nullptr;
+    if (int rc = graph_for(p, progs[i].first, *progs[i].second, rows, utts, ml, &exec)) return rc;
+    FA_CHECK_CUDA(cudaGraphLaunch(exec, s));
+  }
+  return post(a);
 }
 
 // ---- dual-stream schedule -------------------------------------------------------------------------------------------
@@ -624,7 +669,7 @@ int ensure_streams(fa_plan* p) {
   return 0;
 }
 
-// Issue `progs` (each a list of steps) for both halves, half 1 trailing by p->lag steps in issue order.
+// Issue pre, the programs (mid between them) and post for both halves, alternating step by step.
 int run_dual(fa_plan* p, const Slab (&sl)[2], const int32_t* cu, cudaStream_t s, const std::function<int(int, const RunArgs&)>& pre,
              const std::vector<const std::vector<Step>*>& progs, const std::function<int(int, const RunArgs&)>& mid,
              const std::function<int(int, const RunArgs&)>& post) {
@@ -632,31 +677,29 @@ int run_dual(fa_plan* p, const Slab (&sl)[2], const int32_t* cu, cudaStream_t s,
   FA_CHECK_CUDA(cudaEventRecord(p->ev_fork, s));
   FA_CHECK_CUDA(cudaStreamWaitEvent(p->aux, p->ev_fork, 0));
   const RunArgs a[2] = {args_of(sl[0], cu, s), args_of(sl[1], cu, p->aux)};
-  // flatten: pre, prog[0]..., mid (between programs), prog[1]..., post
-  std::vector<std::function<int(int)>> seq;
-  seq.push_back([&](int k) { return pre(k, a[k]); });
-  for (size_t pi = 0; pi < progs.size(); ++pi) {
-    if (pi > 0) seq.push_back([&](int k) { return mid(k, a[k]); });
-    for (const Step& st : *progs[pi]) seq.push_back([&a, &st](int k) { return st(a[k]); });
-  }
-  seq.push_back([&](int k) { return post(k, a[k]); });
-  const int n = static_cast<int>(seq.size()), lag = std::max(0, p->lag);
-  const bool serp = serpentine_enabled();
-  for (int i = 0; i < n + lag; ++i) {
-    if (i < n) {
-      set_launch_reverse(serp && (i & 1));
-      if (int rc = seq[i](0)) { set_launch_reverse(false); return rc; }
-    }
-    if (i >= lag) {
-      set_launch_reverse(serp && ((i - lag) & 1));
-      if (int rc = seq[i - lag](1)) { set_launch_reverse(false); return rc; }
+  int rc = 0;
+  auto both = [&](const std::function<int(int)>& f) {
+    for (int k = 0; k < 2 && !rc; ++k) rc = f(k);
+  };
+  both([&](int k) { return pre(k, a[k]); });
+  for (size_t pi = 0; pi < progs.size() && !rc; ++pi) {
+    if (pi > 0) both([&](int k) { return mid(k, a[k]); });
+    for (const Step& st : *progs[pi]) {
+      if (rc) break;
+      both([&](int k) { return st(a[k]); });
     }
   }
-  set_launch_reverse(false);
-  FA_CHECK_CUDA(cudaEventRecord(p->ev_join, p->aux));
-  FA_CHECK_CUDA(cudaStreamWaitEvent(s, p->ev_join, 0));
+  if (!rc) both([&](int k) { return post(k, a[k]); });
+  // join ALSO on the error path: work already enqueued on `aux` must stay ordered before whatever the caller does next on
+  // `s` (it may free or reuse the buffers once this call has returned an error)
+  const cudaError_t e1 = cudaEventRecord(p->ev_join, p->aux);
+  const cudaError_t e2 = e1 == cudaSuccess ? cudaStreamWaitEvent(s, p->ev_join, 0) : e1;
+  if (rc) return rc;
+  FA_CHECK_CUDA(e2);
   return 0;
 }
+
+const Slab whole(int n_utts, int M, int max_len) { return Slab{0, n_utts, 0, M, max_len}; }
 
 }  // namespace
 
@@ -668,18 +711,22 @@ extern "C" int fa_encoder_forward(fa_plan* p, const float* feats, int32_t feats_
   FA_REQUIRE(p->cfg.n_blocks > 0, "plan was created without encoder weights");
   if (int r = check_tmax(feats_tmax, max_len, "feats")) return r;
   if (int r = check_tmax(enc_out_tmax, max_len, "enc_out")) return r;
+  const cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const Slab all = whole(n_utts, M, max_len);
+  if (use_graph(p, M))
+    return run_graphed(p, n_utts, M, max_len, cu, s, [&](const RunArgs& a) { return encoder_pre(p, all, a, feats, feats_tmax); },
+                       {{0, &p->enc_prog}}, [](const RunArgs&) { return 0; },
+                       [&](const RunArgs& a) { return encoder_post(p, all, a, enc_out, enc_out_tmax); });
   Slab two[2];
   if (split_two(p, cu_host, n_utts, M, two)) {
     const auto none = [](int, const RunArgs&) { return 0; };
-    return run_dual(p, two, cu, static_cast<cudaStream_t>(stream),
-                    [&](int k, const RunArgs& a) { return encoder_pre(p, two[k], a, feats, feats_tmax); }, {&p->enc_prog}, none,
-                    [&](int k, const RunArgs& a) { return encoder_post(p, two[k], a, enc_out, enc_out_tmax); });
+    return run_dual(p, two, cu, s, [&](int k, const RunArgs& a) { return encoder_pre(p, two[k], a, feats, feats_tmax); },
+                    {&p->enc_prog}, none, [&](int k, const RunArgs& a) { return encoder_post(p, two[k], a, enc_out, enc_out_tmax); });
   }
-  std::vector<Slab> slabs;
-  if (int r = make_slabs(p, cu_host, n_utts, M, max_len, &slabs)) return r;
-  for (const Slab& sl : slabs)
-    if (int rc = run_encoder(p, sl, feats, feats_tmax, cu, enc_out, enc_out_tmax, static_cast<cudaStream_t>(stream))) return rc;
-  return 0;
+  const RunArgs a = args_of(all, cu, s);
+  if (int rc = encoder_pre(p, all, a, feats, feats_tmax)) return rc;
+  if (int rc = run_prog(p->enc_prog, a)) return rc;
+  return encoder_post(p, all, a, enc_out, enc_out_tmax);
 }
 
 extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, int32_t enc_tmax, const int32_t* cu, const int32_t* cu_host,
@@ -690,18 +737,22 @@ extern "C" int fa_adaptor_forward(fa_plan* p, const float* enc, int32_t enc_tmax
   if (int r = check_tmax(out_tmax, max_len, "out")) return r;
   FA_REQUIRE(out != nullptr, "NULL out");
   FA_REQUIRE(p->w.lin1_w != nullptr, "plan was created without adaptor weights");
+  const cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const Slab all = whole(n_utts, M, max_len);
+  if (use_graph(p, M))
+    return run_graphed(p, n_utts, M, max_len, cu, s, [&](const RunArgs& a) { return adaptor_pre(p, all, a, enc, enc_tmax); },
+                       {{1, &p->ad_prog}}, [](const RunArgs&) { return 0; },
+                       [&](const RunArgs& a) { return adaptor_post(p, all, a, out, out_tmax, out_bf16); });
   Slab two[2];
   if (split_two(p, cu_host, n_utts, M, two)) {
     const auto none = [](int, const RunArgs&) { return 0; };
-    return run_dual(p, two, cu, static_cast<cudaStream_t>(stream),
-                    [&](int k, const RunArgs& a) { return adaptor_pre(p, two[k], a, enc, enc_tmax); }, {&p->ad_prog}, none,
-                    [&](int k, const RunArgs& a) { return adaptor_post(p, two[k], a, out, out_tmax, out_bf16); });
+    return run_dual(p, two, cu, s, [&](int k, const RunArgs& a) { return adaptor_pre(p, two[k], a, enc, enc_tmax); }, {&p->ad_prog},
+                    none, [&](int k, const RunArgs& a) { return adaptor_post(p, two[k], a, out, out_tmax, out_bf16); });
   }
-  std::vector<Slab> slabs;
-  if (int r = make_slabs(p, cu_host, n_utts, M, max_len, &slabs)) return r;
-  for (const Slab& sl : slabs)
-    if (int rc = run_adaptor(p, sl, enc, enc_tmax, cu, out, out_tmax, out_bf16, static_cast<cudaStream_t>(stream))) return rc;
-  return 0;
+  const RunArgs a = args_of(all, cu, s);
+  if (int rc = adaptor_pre(p, all, a, enc, enc_tmax)) return rc;
+  if (int rc = run_prog(p->ad_prog, a)) return rc;
+  return adaptor_post(p, all, a, out, out_tmax, out_bf16);
 }
 
 extern "C" int fa_encode_adapt(fa_plan* p, const float* feats, int32_t feats_tmax, const int32_t* cu, const int32_t* cu_host,
@@ -714,17 +765,22 @@ extern "C" int fa_encode_adapt(fa_plan* p, const float* feats, int32_t feats_tma
   if (int r = check_tmax(enc_out_tmax, max_len, "enc_out")) return r;
   if (int r = check_tmax(out_tmax, max_len, "out")) return r;
   const cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const Slab all = whole(n_utts, M, max_len);
+  if (use_graph(p, M))
+    return run_graphed(p, n_utts, M, max_len, cu, s, [&](const RunArgs& a) { return encoder_pre(p, all, a, feats, feats_tmax); },
+                       {{0, &p->enc_prog}, {1, &p->ad_prog}},
+                       [&](const RunArgs& a) { return encoder_post(p, all, a, enc_out, enc_out_tmax); },
+                       [&](const RunArgs& a) { return adaptor_post(p, all, a, out, out_tmax, out_bf16); });
   Slab two[2];
   if (split_two(p, cu_host, n_utts, M, two)) {
     return run_dual(p, two, cu, s, [&](int k, const RunArgs& a) { return encoder_pre(p, two[k], a, feats, feats_tmax); },
                     {&p->enc_prog, &p->ad_prog}, [&](int k, const RunArgs& a) { return encoder_post(p, two[k], a, enc_out, enc_out_tmax); },
                     [&](int k, const RunArgs& a) { return adaptor_post(p, two[k], a, out, out_tmax, out_bf16); });
   }
-  std::vector<Slab> slabs;
-  if (int r = make_slabs(p, cu_host, n_utts, M, max_len, &slabs)) return r;
-  for (const Slab& sl : slabs) {  // slab-major: a slab's encoder output is still in L2 when its adaptor runs
-    if (int rc = run_encoder(p, sl, feats, feats_tmax, cu, enc_out, enc_out_tmax, s)) return rc;
-    if (int rc = run_adaptor(p, sl, nullptr, 0, cu, out, out_tmax, out_bf16, s)) return rc;
-  }
-  return 0;
+  const RunArgs a = args_of(all, cu, s);
+  if (int rc = encoder_pre(p, all, a, feats, feats_tmax)) return rc;
+  if (int rc = run_prog(p->enc_prog, a)) return rc;
+  if (int rc = encoder_post(p, all, a, enc_out, enc_out_tmax)) return rc;
+  if (int rc = run_prog(p->ad_prog, a)) return rc;
+  return adaptor_post(p, all, a, out, out_tmax, out_bf16);
 }

@@ -45,114 +45,7 @@ constexpr int SMEM_BYTES = Q_BYTES + STAGES * (K_BYTES + V_BYTES) + 1024 + 256;
 constexpr int TMEM_COLS = 256;             // S0 [0,64)  S1 [64,128)  O [128,256)
 constexpr float RESCALE_THRESHOLD = 8.f;   // log2 units
 
-// ---------------------------------------------------------------- PTX wrappers (same conventions as gemm_tcgen05.cu)
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok = 0;
-  while (!ok) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t"
-        "}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-  }
-}
-__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t"
-      "}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint32_t bar, int x, int y) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-      "l"(tmap), "r"(bar), "r"(x), "r"(y)
-      : "memory");
-}
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-      : "memory");
-}
-// K-major operand, 128B swizzle: rows 128 B apart, 8-row groups 1024 B apart (SBO); LBO unused.
-__device__ __forceinline__ uint64_t desc_kmajor(uint32_t addr) {
-  return static_cast<uint64_t>((addr & 0x3FFFF) >> 4) | (1ull << 16) | (static_cast<uint64_t>(1024 >> 4) << 32) | (1ull << 46) |
-         (2ull << 61);
-}
-// MN-major operand, 128B swizzle (cute: Swizzle<3,4,3> o ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units): one K index
-// = one 128-byte row of 64 MN elements; 8-row K groups SBO apart; the next 64 MN elements LBO apart.
-__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  return static_cast<uint64_t>((addr & 0x3FFFF) >> 4) | (static_cast<uint64_t>(lbo_bytes >> 4) << 16) |
-         (static_cast<uint64_t>(sbo_bytes >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
-// kind::f16: D f32, A/B bf16; bit 15/16 = A/B major (0 K, 1 MN); N>>3 at [17,23); M>>4 at [24,29).
-__device__ __forceinline__ uint32_t make_idesc(int m, int n, int b_mn_major) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(b_mn_major) << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
-         (static_cast<uint32_t>(m >> 4) << 24);
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
-      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
-      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
-      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
-      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
-      : "memory");
-  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-}
-// 2^x on the MUFU pipe, one instruction (x <= 0 here; results below 2^-126 flush to zero, far under bf16 resolution of P)
-__device__ __forceinline__ float ex2(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
+using namespace fa::ptx;  // shared inline-PTX wrappers (ptx.cuh)
 
 __device__ __forceinline__ unsigned long long gtime() {
   unsigned long long t;
@@ -172,12 +65,12 @@ __device__ __forceinline__ unsigned long long gtime() {
 // ---------------------------------------------------------------- kernel
 __global__ void __launch_bounds__(THREADS, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __restrict__ cu, int base, int n_heads,
-                 __nv_bfloat16* __restrict__ ctx, int64_t ld_ctx, float scale_log2e, int reverse, unsigned long long* trace) {
+                 __nv_bfloat16* __restrict__ ctx, int64_t ld_ctx, float scale_log2e, unsigned long long* trace) {
   extern __shared__ unsigned char smem_raw[];
   const int cta_lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
   if (threadIdx.x == 0) TRACE(0);
   pdl_launch_dependents();
-  const int b = reverse ? gridDim.z - 1 - blockIdx.z : blockIdx.z, h = blockIdx.y;  // serpentine: last utterance first  // (cu_seqlens is an input of the whole forward call, not a kernel's output)
+  const int b = blockIdx.z, h = blockIdx.y;  // (cu_seqlens is an input of the whole forward call, not a kernel's output)
   const int start = cu[b] - base, len = cu[b + 1] - cu[b];
   const int q0 = blockIdx.x * BQ;
   if (q0 >= len) return;  // uniform per CTA, before any barrier / TMEM use
@@ -208,7 +101,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
     tma_load_2d(sV(st) + KPANEL, &tmap_qkv, v_full(st), xv + 64, row);
   };
   if (warp == 0 && lane == 0) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_qkv) : "memory");
+    prefetch_tmap(&tmap_qkv);
     mbar_init(q_full, 1);
     mbar_init(o_full, 1);
     for (int st = 0; st < STAGES; ++st) {
@@ -218,7 +111,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
       mbar_init(s_full(st), 1);
       mbar_init(p_full(st), 128);  // every softmax thread arrives
     }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_mbar_init();
     // Q and the first two K/V blocks are requested right here, before the TMEM allocation and the CTA-wide sync
     // (the producer only needs its own barriers): ~0.4 us of the 1.7 us Q+K0 wait leaves the critical path
     pdl_wait();
@@ -229,8 +122,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
     for (int j = 0; j < min(n_blk, STAGES); ++j) issue_kv(j);
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(TMEM_COLS) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    tmem_alloc<TMEM_COLS>(tmem_slot);
   }
   tc_fence_before();
   __syncthreads();
@@ -418,7 +310,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
+    tmem_dealloc<TMEM_COLS>(tmem);
   }
   if (threadIdx.x == 0) {
     TRACE(11);
@@ -435,29 +327,31 @@ unsigned long long* g_trace = nullptr;
 
 }  // namespace attn
 
-int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base, int max_len,
-                     int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream) {
+int attention_kv_box() { return attn::BKV; }
+
+int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base,
+                     int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream) {
   FA_REQUIRE(ld % 8 == 0 && ld_ctx % 8 == 0, "attention: row strides must be multiples of 8 elements");
   FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0,
              "attention: qkv and ctx must be 16-byte aligned");
   FA_REQUIRE(max_len > 0 && n_utts > 0 && n_heads > 0 && n_rows > 0, "attention: empty problem");
   FA_REQUIRE(ld >= 3 * n_heads * attn::HD, "attention: qkv rows hold q|k|v of %d heads x 128", n_heads);
-  static bool attr_done = false;
-  if (!attr_done) {
-    FA_CHECK_CUDA(cudaFuncSetAttribute(attn::attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, attn::SMEM_BYTES));
-    attr_done = true;
-  }
-  // rows = the valid packed rows only: key/value rows past the end are zero-filled by TMA instead of reading workspace
-  // padding (whose contents are undefined and could be NaN, which 0 * NaN would leak into O).
+  static SmemOptIn opt;
+  if (int r = opt_in_smem(attn::attention_kernel, attn::SMEM_BYTES, opt)) return r;
+  // Without a prebuilt map: rows = the valid packed rows only, so key/value rows past the end are zero-filled by TMA instead
+  // of reading memory whose contents are undefined (NaN there would leak into O through 0 * NaN).
   TensorMap2D tm;
-  if (int r = make_tensor_map_bf16(&tm, qkv, n_rows, 3 * n_heads * attn::HD, ld, attn::BKV)) return r;
+  if (tm_in == nullptr) {
+    if (int r = make_tensor_map_bf16(&tm, qkv, n_rows, 3 * n_heads * attn::HD, ld, attn::BKV)) return r;
+    tm_in = &tm;
+  }
   CUtensorMap m;
-  memcpy(&m, tm.bytes, sizeof(m));
+  memcpy(&m, tm_in->bytes, sizeof(m));
   dim3 grid(ceil_div(max_len, attn::BQ), n_heads, n_utts);
   const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(attn::HD));
   ProfScope _ps(K_ATTENTION, stream);
   FA_CHECK_CUDA(launch_pdl(attn::attention_kernel, grid, dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, cu_seqlens, base, n_heads,
-                           ctx, ld_ctx, scale_log2e, launch_reverse() ? 1 : 0, attn::g_trace));
+                           ctx, ld_ctx, scale_log2e, attn::g_trace));
   return 0;
 }
 
@@ -468,7 +362,7 @@ extern "C" int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_
                                fa_stream_t stream) {
   using namespace fa;
   FA_REQUIRE(qkv_dev && cu_seqlens_dev && ctx_dev, "attention: NULL pointer");
-  return launch_attention(static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, cu_seqlens_dev, n_utts, 0, max_len, n_heads,
+  return launch_attention(nullptr, static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, cu_seqlens_dev, n_utts, 0, max_len, n_heads,
                           static_cast<__nv_bfloat16*>(ctx_dev), ld_ctx, n_rows, static_cast<cudaStream_t>(stream));
 }
 

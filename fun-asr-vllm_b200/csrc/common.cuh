@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 
@@ -34,7 +35,23 @@ void set_error(const char* fmt, ...);
 #define FA_CHECK_LAUNCH() FA_CHECK_CUDA(cudaGetLastError())
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
-int sm_count();
+int sm_count();  // of the CURRENT device (cached per device)
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE attribute of a kernel: remember, per kernel, the devices it has
+// been opted in on (one process may drive several GPUs; host threads may race here - setting it twice is harmless).
+struct SmemOptIn {
+  std::atomic<unsigned long long> done{0};
+};
+template <typename Kernel>
+inline int opt_in_smem(Kernel kernel, int bytes, SmemOptIn& st) {
+  int dev = 0;
+  FA_CHECK_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = dev < 64 ? (1ull << dev) : 0ull;
+  if (bit && (st.done.load(std::memory_order_acquire) & bit)) return 0;
+  FA_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  if (bit) st.done.fetch_or(bit, std::memory_order_release);
+  return 0;
+}
 
 // ---- per-kernel-class device timing (bench / profiling only; off by default, zero cost when off) ----
 enum Kind { K_FRONTEND = 0, K_GEMM, K_ATTENTION, K_LAYERNORM, K_FSMN, K_REPACK, K_SPLICE, K_NUM };
@@ -68,7 +85,6 @@ struct GemmEpilogue {
   const float* colsum = nullptr;  // consumer: [N] row sums of the bf16 weight
   __nv_bfloat16* xb = nullptr;  // producer: bf16 copy of C, row stride ld_xb
   int64_t ld_xb = 0;
-  int reverse = 0;  // walk the tile rows last-to-first (serpentine schedule)
 };
 
 struct TensorMap2D {  // opaque 128-byte CUtensorMap
@@ -99,8 +115,12 @@ int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, con
                            float scale, const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream);
 int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts, int base,
                 void* mem, int out_bf16, int64_t ld_out, int M, int D, int kernel, int left_pad, cudaStream_t stream);
-int launch_attention(const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base, int max_len,
-                     int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream);
+// tm: prebuilt tensor map over qkv (box = attention_kv_box() rows x 64 columns), or NULL to encode one over n_rows rows here
+int attention_kv_box();
+int launch_attention(const TensorMap2D* tm, const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base,
+                     int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream);
+// dst[i] = cu[min(i, n_utts)], i = 0..n_pad: cu_seqlens copied to a fixed address, padded with the total row count
+int launch_pad_cu(const int32_t* cu, int n_utts, int32_t* dst, int n_pad, cudaStream_t stream);
 int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, int dst_bf16, const int32_t* cu,
                        int n_utts, int base, int M, int D, cudaStream_t stream);
 
@@ -108,6 +128,7 @@ int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, 
 
 // ---- device helpers --------------------------------------------------------------------------
 #ifdef __CUDACC__
+#include "ptx.cuh"
 namespace fa {
 
 // Programmatic dependent launch: every kernel of the path lets its successor in the stream start early
@@ -119,11 +140,6 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 
 // Launch with the programmatic-stream-serialization attribute (and an optional cluster width).
 bool pdl_enabled();
-// Serpentine schedule (FA_SERPENTINE=1): the plan's step executor flips this before every other launch; a launch that sees it
-// walks its rows last-to-first, i.e. starts on the rows its predecessor wrote last (still in the 126 MB L2).
-bool launch_reverse();
-void set_launch_reverse(bool on);
-bool serpentine_enabled();
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, int cluster_x,
                               Args&&... args) {

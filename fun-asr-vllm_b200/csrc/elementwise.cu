@@ -2,7 +2,6 @@
 // encoding, + fused second LayerNorm), FSMN depthwise memory block, row metadata, casts, splice.
 // All work on PACKED rows; utterance boundaries come from cu_seqlens / row_meta.
 #include <math.h>
-#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -150,13 +149,9 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnArgs a) {
 // ---------------------------------------------------------------- FSMN memory block
 // mem[t, c] = v[t, c] + sum_k w[k, c] * v[t + k - left, c]   (zero outside the utterance; w is TAP-MAJOR [K, D])
 // (VLLM/model_executor/models/funasr.py:181-201: mask, ConstantPad1d, depthwise Conv1d, +inputs, mask).
-// One thread owns 4 adjacent channels (one 8-byte load per row) and walks FSMN_ROWS consecutive rows with a K-row
-// sliding window held in registers; the row loop is unrolled K times so the window rotates through compile-time
-// register names (no moves), and the K loads of an unrolled block are issued before its FMAs.  A CTA's rows are cut
-// into per-utterance segments (one binary search per segment): rows outside the segment's utterance enter the window
-// as zeros, so the inner loop carries no per-tap predicates.  The "+ inputs" term is tap `left` with weight + 1.
 // Output: f32 [M, ld_out] or bf16 (the plan writes bf16 straight into the right half of the out-projection's A operand).
-constexpr int FSMN_ROWS = 32;
+// The row count of a launch is min(M, cu[n_utts] - base): a launch captured in a CUDA graph for a row BUCKET (api.cu) still
+// stops at the batch's true last row, which it reads from cu_seqlens on the device.
 constexpr int FSMN_MAXK = 16;
 constexpr int FSMN_THREADS = 128;
 
@@ -165,117 +160,62 @@ __device__ __forceinline__ float4 bf16x4_to_f32(uint2 r) {
                      __uint_as_float(r.y & 0xffff0000u));
 }
 
-template <int K, bool OUT_BF16>
+// Generic fallback (any tap count <= 16, rows only 8-byte aligned): one thread = one output row x 4 channels, taps read
+// straight from global memory.  The model's own geometry (11 taps, 16-byte aligned rows) takes fsmn_staged_kernel below.
+template <bool OUT_BF16>
 __global__ void __launch_bounds__(FSMN_THREADS)
-fsmn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
-            const int32_t* __restrict__ cu, int n_utts, int base, void* __restrict__ mem, int64_t ld_out, int M, int D, int left) {
+fsmn_generic_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
+                    const int32_t* __restrict__ cu, int n_utts, int base, void* __restrict__ mem, int64_t ld_out, int M, int D,
+                    int K, int left) {
   pdl_launch_dependents();
   const int c4 = blockIdx.y * FSMN_THREADS + threadIdx.x;  // channel quad
+  const int r = blockIdx.x;
   if (4 * c4 >= D) return;
-  float4 wt[K];
-#pragma unroll
-  for (int k = 0; k < K; ++k) {
-    wt[k] = __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(k) * D) + c4);
-    const float one = (k == left) ? 1.f : 0.f;  // a select, not a dynamically indexed update (keeps wt[] in registers)
-    wt[k].x += one; wt[k].y += one; wt[k].z += one; wt[k].w += one;
-  }
-  pdl_wait();  // the taps are constants; v comes from the previous kernel
+  M = min(M, __ldg(cu + n_utts) - base);
+  if (r >= M) return;
+  pdl_wait();
+  const int2 ub = utt_bounds(cu, n_utts, r + base);
+  const int lo = max(ub.x - base, 0), hi = min(ub.y - base, M);
   const __nv_bfloat16* vcol = qkv + v_col + 4 * c4;
-  const int ahead = K - 1 - left;  // newest input row of output row t is t + ahead
-  const int r_end = min(M, (static_cast<int>(blockIdx.x) + 1) * FSMN_ROWS);
-  int r = blockIdx.x * FSMN_ROWS;
-  while (r < r_end) {
-    const int2 ub = utt_bounds(cu, n_utts, r + base);
-    const int lo = ub.x - base, hi = ub.y - base;  // this utterance's rows (local numbering; lo may be < 0 of this launch)
-    const int seg_end = min(r_end, hi);
-    // input row `row` as 4 floats, zero outside [lo, hi) (and outside this launch's rows)
-    auto load_raw = [&](int row) -> uint2 {
-      uint2 v = make_uint2(0u, 0u);
-      if (row >= lo && row < hi && row >= 0 && row < M) v = __ldg(reinterpret_cast<const uint2*>(vcol + static_cast<int64_t>(row) * ld));
-      return v;
-    };
-    float4 win[K];
-#pragma unroll
-    for (int i = 0; i < K - 1; ++i) win[i] = bf16x4_to_f32(load_raw(r - left + i));
-    for (int tb = r; tb < seg_end; tb += K) {
-      uint2 raw[K];
-#pragma unroll
-      for (int j = 0; j < K; ++j) raw[j] = (tb + j < seg_end) ? load_raw(tb + j + ahead) : make_uint2(0u, 0u);
-#pragma unroll
-      for (int j = 0; j < K; ++j) {
-        if (tb + j < seg_end) {
-          win[(j + K - 1) % K] = bf16x4_to_f32(raw[j]);
-          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-          for (int k = 0; k < K; ++k) {
-            const float4 x = win[(j + k) % K];
-            a.x = fmaf(wt[k].x, x.x, a.x);
-            a.y = fmaf(wt[k].y, x.y, a.y);
-            a.z = fmaf(wt[k].z, x.z, a.z);
-            a.w = fmaf(wt[k].w, x.w, a.w);
-          }
-          const int64_t o = static_cast<int64_t>(tb + j) * ld_out + 4 * c4;
-          if (OUT_BF16) *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(mem) + o) = make_uint2(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w));
-          else *reinterpret_cast<float4*>(static_cast<float*>(mem) + o) = a;
-        }
-      }
-    }
-    r = seg_end;
+  float4 a = bf16x4_to_f32(__ldg(reinterpret_cast<const uint2*>(vcol + static_cast<int64_t>(r) * ld)));  // "+ inputs"
+  for (int k = 0; k < K; ++k) {
+    const int row = r + k - left;
+    if (row < lo || row >= hi) continue;
+    const float4 x = bf16x4_to_f32(__ldg(reinterpret_cast<const uint2*>(vcol + static_cast<int64_t>(row) * ld)));
+    const float4 wt = __ldg(reinterpret_cast<const float4*>(w + static_cast<int64_t>(k) * D) + c4);
+    a.x = fmaf(wt.x, x.x, a.x); a.y = fmaf(wt.y, x.y, a.y); a.z = fmaf(wt.z, x.z, a.z); a.w = fmaf(wt.w, x.w, a.w);
   }
+  const int64_t o = static_cast<int64_t>(r) * ld_out + 4 * c4;
+  if (OUT_BF16) *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(mem) + o) = make_uint2(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w));
+  else *reinterpret_cast<float4*>(static_cast<float*>(mem) + o) = a;
 }
 
 // ---------------------------------------------------------------- FSMN, shared-memory staged (the default path)
-// Same arithmetic as fsmn_kernel, different data movement: a CTA owns R consecutive rows x 512 channels and pulls ALL the
-// input rows it needs (R + K - 1, one 1 KB bulk copy per row: cp.async.bulk global -> shared, completion on one mbarrier)
-// in a single round trip, instead of ~4 dependent rounds of per-thread 8-byte global loads.  The sliding window then
-// reads shared memory (one conflict-free LDS.64 per row and thread); rows outside the utterance enter the window as zeros.
-__device__ __forceinline__ void fs_mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void fs_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void fs_mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok = 0;
-  while (!ok) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t"
-        "}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-  }
-}
-__device__ __forceinline__ void fs_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
-               "r"(bytes), "r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ uint2 fs_lds64(uint32_t addr) {
-  uint2 v;
-  asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
-  return v;
-}
+// A CTA owns R consecutive rows x 512 channels and pulls ALL the input rows it needs (R + K - 1, one 1 KB bulk copy per
+// row: cp.async.bulk global -> shared, completion on one mbarrier) in a single round trip.  One thread owns 4 adjacent
+// channels and walks the rows with a K-row sliding window held in registers (the row loop is unrolled K times so the window
+// rotates through compile-time register names), fed by one conflict-free LDS.64 per row; a CTA's rows are cut into
+// per-utterance segments and rows outside the segment's utterance enter the window as zeros, so the inner loop carries no
+// per-tap predicates.  The "+ inputs" term is tap `left` with weight + 1.
 template <int K, int R, bool OUT_BF16>
 __global__ void __launch_bounds__(FSMN_THREADS)
 fsmn_staged_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col, const float* __restrict__ w,
                    const int32_t* __restrict__ cu, int n_utts, int base, void* __restrict__ mem, int64_t ld_out, int M, int D,
-                   int left, int reverse) {
+                   int left) {
   extern __shared__ __align__(128) unsigned char fs_smem[];
   pdl_launch_dependents();
   const int ch0 = blockIdx.y * (4 * FSMN_THREADS);  // first channel of this CTA's 512-channel chunk
   const int wch = min(4 * FSMN_THREADS, D - ch0);   // channels in the chunk (multiple of 8: 16-byte bulk copies)
-  const int r0 = (reverse ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * R, r_end = min(M, r0 + R);  // serpentine: last rows first
+  M = min(M, __ldg(cu + n_utts) - base);  // cu_seqlens is an input of the forward call, not a predecessor's output
+  const int r0 = blockIdx.x * R, r_end = min(M, r0 + R);
+  if (r0 >= M) return;  // uniform per CTA, before any barrier use
   const int ahead = K - 1 - left;  // newest input row of output row t is t + ahead
   const int in0 = max(r0 - left, 0), in1 = min(r_end + ahead, M);  // input rows staged: [in0, in1), at most R + K - 1
   const uint32_t tile = smem_u32(fs_smem), bar = tile + (R + K - 1) * 1024;
   if (threadIdx.x == 0) {
-    fs_mbar_init(bar, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    fs_mbar_expect_tx(bar, static_cast<uint32_t>(in1 - in0) * wch * 2);  // the only arrival: the phase cannot end before it
+    ptx::mbar_init(bar, 1);
+    ptx::fence_mbar_init();
+    ptx::mbar_expect_tx(bar, static_cast<uint32_t>(in1 - in0) * wch * 2);  // the only arrival: the phase cannot end before it
   }
   const bool active = 4 * static_cast<int>(threadIdx.x) < wch;
   float4 wt[K];
@@ -289,10 +229,10 @@ fsmn_staged_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col,
   __syncthreads();  // barrier initialised and armed
   pdl_wait();       // the taps are constants; v comes from the previous kernel
   if (static_cast<int>(threadIdx.x) < in1 - in0)
-    fs_bulk_g2s(tile + threadIdx.x * 1024, qkv + static_cast<int64_t>(in0 + threadIdx.x) * ld + v_col + ch0, wch * 2, bar);
+    ptx::bulk_g2s(tile + threadIdx.x * 1024, qkv + static_cast<int64_t>(in0 + threadIdx.x) * ld + v_col + ch0, wch * 2, bar);
   if (!active) return;
   int2 ub = utt_bounds(cu, n_utts, r0 + base);  // overlaps the copies
-  fs_mbar_wait(bar, 0);
+  ptx::mbar_wait(bar, 0);
   const uint32_t col = tile + threadIdx.x * 8;
   int r = r0;
   while (r < r_end) {
@@ -301,7 +241,7 @@ fsmn_staged_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int v_col,
     const int seg_end = min(r_end, ub.y - base);
     auto load = [&](int row) -> float4 {
       uint2 v = make_uint2(0u, 0u);
-      if (row >= lo && row < hi) v = fs_lds64(col + static_cast<uint32_t>(row - in0) * 1024u);
+      if (row >= lo && row < hi) v = ptx::lds64(col + static_cast<uint32_t>(row - in0) * 1024u);
       return bf16x4_to_f32(v);
     };
     float4 win[K];
@@ -398,7 +338,20 @@ splice_kernel(const void* __restrict__ speech, int speech_bf16, const int32_t* _
   }
 }
 
+__global__ void pad_cu_kernel(const int32_t* __restrict__ cu, int n_utts, int32_t* __restrict__ dst, int n_pad) {
+  pdl_launch_dependents();
+  pdl_wait();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= n_pad; i += gridDim.x * blockDim.x) dst[i] = __ldg(cu + min(i, n_utts));
+}
+
 }  // namespace ew
+
+int launch_pad_cu(const int32_t* cu, int n_utts, int32_t* dst, int n_pad, cudaStream_t stream) {
+  FA_REQUIRE(cu && dst && n_utts > 0 && n_pad >= n_utts, "pad_cu: bad arguments");
+  ew::pad_cu_kernel<<<ceil_div(n_pad + 1, 256), 256, 0, stream>>>(cu, n_utts, dst, n_pad);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
 
 static int ln_check(int D, const void* x) {
   FA_REQUIRE(D % 4 == 0 && D <= ew::LN_MAX_D, "layernorm: D=%d must be a multiple of 4 and <= %d", D, ew::LN_MAX_D);
@@ -434,60 +387,37 @@ int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w,
              "fsmn: qkv must be 8-byte, mem and w 16-byte aligned");
   const int threads = ew::FSMN_THREADS;
   ProfScope _ps(K_FSMN, stream);
-  // Staged path (bulk copies into shared memory): the model's 11-tap kernel, 16-byte aligned rows.  FA_FSMN_STAGED=0 keeps the
-  // register-window kernel (A/B measurements); FA_FSMN_ROWS=32|64 picks the rows per CTA.
-  static const int staged_rows = [] {  // 0 = off, -1 = by size (default), else forced
-    const char* e = getenv("FA_FSMN_STAGED");
-    if (e && atoi(e) == 0) return 0;
-    const char* r = getenv("FA_FSMN_ROWS");
-    const int v = r ? atoi(r) : -1;
-    return (v == 8 || v == 16 || v == 32 || v == 64) ? v : -1;
-  }();
-  if (staged_rows && kernel == 11 && D % 8 == 0 && v_col % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(qkv) & 15) == 0) {
+  if (kernel == 11 && D % 8 == 0 && v_col % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(qkv) & 15) == 0) {
     // rows per CTA: the largest of 32 / 16 / 8 that still gives every SM a CTA.  For small batches the serial walk over a
     // CTA's rows is the kernel's whole duration (cfg2 half-batch: 1 336 rows = 42 CTAs of 32 rows, 10.6 us per launch; 167
-    // CTAs of 8 rows, 8.6 us); once every SM has work, more and smaller CTAs only add halo reads (measured: cfg3, r01-s).
+    // CTAs of 8 rows, 8.6 us); once every SM has work, more and smaller CTAs only add halo reads (profiles/r01_s_fsmn_rows.md).
     const int sms = sm_count();
-    const int R = staged_rows > 0 ? staged_rows : (M >= 32 * sms ? 32 : M >= 16 * sms ? 16 : 8);
+    const int R = M >= 32 * sms ? 32 : M >= 16 * sms ? 16 : 8;
     const size_t smem = static_cast<size_t>(R + kernel - 1) * 1024 + 16;
     dim3 sgrid(ceil_div(M, R), ceil_div(D, 4 * threads));
 #define FA_FSMN_STAGED_LAUNCH(RR, BF)                                                                                              \
   do {                                                                                                                             \
-    static bool attr = false;                                                                                                      \
-    if (!attr) {                                                                                                                   \
-      FA_CHECK_CUDA(cudaFuncSetAttribute(ew::fsmn_staged_kernel<11, RR, BF>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
-                                         static_cast<int>(smem)));                                                                 \
-      attr = true;                                                                                                                 \
-    }                                                                                                                              \
+    static SmemOptIn opt;                                                                                                          \
+    if (int r_ = opt_in_smem(ew::fsmn_staged_kernel<11, RR, BF>, static_cast<int>(smem), opt)) return r_;                          \
     FA_CHECK_CUDA(launch_pdl(ew::fsmn_staged_kernel<11, RR, BF>, sgrid, dim3(threads), smem, stream, 1, qkv, ld, v_col, w, cu,     \
-                             n_utts, base, mem, ld_out, M, D, left_pad, launch_reverse() ? 1 : 0));                                \
+                             n_utts, base, mem, ld_out, M, D, left_pad));                                                          \
   } while (0)
 #define FA_FSMN_STAGED_ROWS(RR) \
   do { if (out_bf16) FA_FSMN_STAGED_LAUNCH(RR, true); else FA_FSMN_STAGED_LAUNCH(RR, false); } while (0)
-    if (R == 64) FA_FSMN_STAGED_ROWS(64);
-    else if (R == 32) FA_FSMN_STAGED_ROWS(32);
+    if (R == 32) FA_FSMN_STAGED_ROWS(32);
     else if (R == 16) FA_FSMN_STAGED_ROWS(16);
     else FA_FSMN_STAGED_ROWS(8);
 #undef FA_FSMN_STAGED_ROWS
 #undef FA_FSMN_STAGED_LAUNCH
-    FA_CHECK_LAUNCH();
     return 0;
   }
-  dim3 grid(ceil_div(M, ew::FSMN_ROWS), ceil_div(D / 4, threads));
-#define FA_FSMN_CASE(KK)                                                                                                           \
-  case KK:                                                                                                                         \
-    FA_CHECK_CUDA(out_bf16 ? launch_pdl(ew::fsmn_kernel<KK, true>, grid, dim3(threads), 0, stream, 1, qkv, ld, v_col, w, cu, n_utts,  \
-                                        base, mem, ld_out, M, D, left_pad)                                                          \
-                           : launch_pdl(ew::fsmn_kernel<KK, false>, grid, dim3(threads), 0, stream, 1, qkv, ld, v_col, w, cu, n_utts, \
-                                        base, mem, ld_out, M, D, left_pad));                                                        \
-    break;
-  switch (kernel) {
-    FA_FSMN_CASE(1) FA_FSMN_CASE(2) FA_FSMN_CASE(3) FA_FSMN_CASE(4) FA_FSMN_CASE(5) FA_FSMN_CASE(6) FA_FSMN_CASE(7) FA_FSMN_CASE(8)
-    FA_FSMN_CASE(9) FA_FSMN_CASE(10) FA_FSMN_CASE(11) FA_FSMN_CASE(12) FA_FSMN_CASE(13) FA_FSMN_CASE(14) FA_FSMN_CASE(15)
-    FA_FSMN_CASE(16)
-  }
-#undef FA_FSMN_CASE
-  FA_CHECK_LAUNCH();
+  dim3 grid(M, ceil_div(D / 4, threads));
+  if (out_bf16)
+    FA_CHECK_CUDA(launch_pdl(ew::fsmn_generic_kernel<true>, grid, dim3(threads), 0, stream, 1, qkv, ld, v_col, w, cu, n_utts, base, mem,
+                             ld_out, M, D, kernel, left_pad));
+  else
+    FA_CHECK_CUDA(launch_pdl(ew::fsmn_generic_kernel<false>, grid, dim3(threads), 0, stream, 1, qkv, ld, v_col, w, cu, n_utts, base, mem,
+                             ld_out, M, D, kernel, left_pad));
   return 0;
 }
 

@@ -356,12 +356,8 @@ extern "C" int fa_frontend_forward(const fa_frontend_cfg* cfg, const void* table
   FA_REQUIRE(out_ld >= FEAT && out_ld % 4 == 0, "out_ld must be >= %d and a multiple of 4", FEAT);
   FA_REQUIRE((reinterpret_cast<uintptr_t>(out_dev) & 15) == 0, "out_dev must be 16-byte aligned");
   if (n_tiles <= 0) return 0;
-  static bool attr_done = false;
-  if (!attr_done) {
-    FA_CHECK_CUDA(cudaFuncSetAttribute(fbank_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-    FA_CHECK_CUDA(cudaFuncSetAttribute(fbank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-    attr_done = true;
-  }
+  static SmemOptIn opt0;
+  if (int r = opt_in_smem(fbank_kernel<0>, (int)sizeof(Smem), opt0)) return r;
   ProfScope _ps(K_FRONTEND, static_cast<cudaStream_t>(stream));
   fbank_kernel<0><<<n_tiles, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
       static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, tile_off_dev, n_utts,
@@ -379,12 +375,8 @@ extern "C" int fa_frontend_logmel(const fa_frontend_cfg* cfg, const void* tables
   FA_REQUIRE(n_utts > 0 && max_frames > 0, "empty batch");
   FA_REQUIRE(tables_dev && wav_dev && wav_start_dev && wav_len_dev && out_row_dev && out_dev, "NULL device pointer");
   FA_REQUIRE(out_ld >= NMEL && out_ld % 4 == 0, "out_ld must be >= %d and a multiple of 4", NMEL);
-  static bool attr_done = false;
-  if (!attr_done) {
-    FA_CHECK_CUDA(cudaFuncSetAttribute(fbank_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-    FA_CHECK_CUDA(cudaFuncSetAttribute(fbank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-    attr_done = true;
-  }
+  static SmemOptIn opt1;
+  if (int r = opt_in_smem(fbank_kernel<1>, (int)sizeof(Smem), opt1)) return r;
   dim3 grid(ceil_div(max_frames, RAW_TILE_FRAMES), n_utts);
   ProfScope _ps(K_FRONTEND, static_cast<cudaStream_t>(stream));
   fbank_kernel<1><<<grid, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(

@@ -84,180 +84,10 @@ struct Params {
   const float* colsum;
   __nv_bfloat16* xb;
   long long ld_xb;
-  int reverse;  // walk the tile rows last-to-first
 };
 
-// ---------------------------------------------------------------- PTX wrappers
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t"
-      "}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
-  }
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint32_t bar, int x, int y) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-      "l"(tmap), "r"(bar), "r"(x), "r"(y)
-      : "memory");
-}
-__device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int x, int y) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap), "r"(src), "r"(x),
-               "r"(y)
-               : "memory");
-}
-// C tile += smem tile: the f32 add happens in the L2 (one add per element per launch -> deterministic)
-__device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, uint32_t src, int x, int y) {
-  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap), "r"(src),
-               "r"(x), "r"(y)
-               : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-__device__ __forceinline__ float4 lds128(uint32_t addr) {
-  float4 v;
-  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
-  return v;
-}
-__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-      : "memory");
-}
-// ---- CTA-pair (cta_group::2) variants
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-// shared::cta address -> shared::cluster address of the same offset in CTA `rank` of the cluster
-__device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
-  // relaxed: the barrier only orders TMEM reads (tcgen05.fence::before_thread_sync precedes it), no memory is published;
-  // the release.cluster form costs MEMBAR.ALL.GPU + ERRBAR per tile per warp (ncu: 19 % of the epilogue's stall samples)
-  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
-}
-// TMA load whose completion bytes are signalled on a barrier of the pair's leader CTA (cluster address)
-__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const void* tmap, uint32_t cluster_bar, int x, int y) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-      "l"(tmap), "r"(cluster_bar), "r"(x), "r"(y)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {  // arrives on the same barrier offset in both CTAs
-  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-               "h"(static_cast<uint16_t>(3))
-               : "memory");
-}
-__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-      : "memory");
-}
-// (d0, d1) = s * (a0, a1) + (t * (c0, c1) + (b0, b1)) with packed fma.rn.f32x2
-__device__ __forceinline__ void ffma2(float& d0, float& d1, float s, float a0, float a1, float t, float c0, float c1, float b0,
-                                      float b1) {
-  asm("{\n\t"
-      ".reg .b64 ss, tt, aa, cc, bb, uu, dd;\n\t"
-      "mov.b64 ss, {%2, %2};\n\t"
-      "mov.b64 tt, {%5, %5};\n\t"
-      "mov.b64 aa, {%3, %4};\n\t"
-      "mov.b64 cc, {%6, %7};\n\t"
-      "mov.b64 bb, {%8, %9};\n\t"
-      "fma.rn.f32x2 uu, tt, cc, bb;\n\t"
-      "fma.rn.f32x2 dd, ss, aa, uu;\n\t"
-      "mov.b64 {%0, %1}, dd;\n\t"
-      "}"
-      : "=f"(d0), "=f"(d1)
-      : "f"(s), "f"(a0), "f"(a1), "f"(t), "f"(c0), "f"(c1), "f"(b0), "f"(b1));
-}
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile(
-      "{\n\t"
-      ".reg .pred P;\n\t"
-      "elect.sync _|P, 0xffffffff;\n\t"
-      "selp.u32 %0, 1, 0, P;\n\t"
-      "}"
-      : "=r"(pred));
-  return pred != 0;
-}
-// K-major operand tile, 128B swizzle: 8-row groups are 1024 B apart (SBO), LBO unused (=1),
-// descriptor version 1 (Blackwell), layout type 2 = SWIZZLE_128B.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
-  uint64_t d = 0;
-  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
-  d |= static_cast<uint64_t>(1) << 16;
-  d |= static_cast<uint64_t>(1024 >> 4) << 32;
-  d |= static_cast<uint64_t>(1) << 46;
-  d |= static_cast<uint64_t>(2) << 61;
-  return d;
-}
-// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at [17,23), M>>4 at [24,29).
-__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
-}
-// issues the load only: tmem_ld_wait() must follow before r[] is read
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+using namespace fa::ptx;  // shared inline-PTX wrappers (ptx.cuh)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t a) { return desc_kmajor(a); }
 
 // ---------------------------------------------------------------- kernel
 // Epilogue variants are compile-time: OUT_F32 (f32 C, optional NRES f32 residuals) or bf16 C (optional RELU).
@@ -291,14 +121,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int cl = CTAS == 2 ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);    // tile-scheduler slot
   const int ncl = CTAS == 2 ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
   auto tile_row = [&](int tm) { return (tm * CTAS + static_cast<int>(rank)) * BM; };  // first row this CTA owns in tile row tm
-  // serpentine schedule: a launch may walk the tile rows last-to-first, so that it starts on the rows its predecessor wrote last
-  // (still in L2); the tile -> CTA assignment is otherwise unchanged
-  auto tm_of = [&](int tile) { const int t = tile / p.tiles_n; return p.reverse ? p.tiles_m - 1 - t : t; };
+  auto tm_of = [&](int tile) { return tile / p.tiles_n; };
 
   if (warp == 0 && lane == 0) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_c) : "memory");
+    prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_b);
+    prefetch_tmap(&tmap_c);
     for (int s = 0; s < C::STAGES; ++s) {
       mbar_init(full_bar(s), 1);
       mbar_init(empty_bar(s), 1);
@@ -308,12 +136,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       mbar_init(tempty_bar(a), EPI_WARPS * CTAS);  // one arrive per epilogue warp (of both CTAs of a pair)
     }
     if (NRES > 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_r1) : "memory");
-      if (NRES > 1) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_r2) : "memory");
+      prefetch_tmap(&tmap_r1);
+      if (NRES > 1) prefetch_tmap(&tmap_r2);
       for (int w = 0; w < EPI_WARPS; ++w)
         for (int sl = 0; sl < RES_RING_MAX; ++sl) mbar_init(res_bar(w, sl), 1);
     }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_mbar_init();
   }
   if constexpr (!OUT_F32) {
     for (int i = threadIdx.x; i < p.N; i += NUM_THREADS) {
@@ -322,19 +150,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   }
   if (warp == 1) {
-    if constexpr (CTAS == 2) {
-      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(C::TMEM_COLS)
-                   : "memory");
-      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-    } else {
-      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(C::TMEM_COLS)
-                   : "memory");
-      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    }
+    if constexpr (CTAS == 2) tmem_alloc_pair<C::TMEM_COLS>(tmem_slot);
+    else tmem_alloc<C::TMEM_COLS>(tmem_slot);
   }
-  tcgen05_fence_before();
+  tc_fence_before();
   if constexpr (CTAS == 2) cluster_sync(); else __syncthreads();  // barriers of BOTH CTAs are initialised past this point
-  tcgen05_fence_after();
+  tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
   pdl_wait();  // prologue done (weights / bias are constants); activations of the previous kernel are visible from here
 
@@ -368,7 +189,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (the pair's leader only) =====================
-    constexpr uint32_t idesc = make_idesc(BM * CTAS, BN);
+    constexpr uint32_t idesc = make_idesc(BM * CTAS, BN, 0);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
@@ -376,11 +197,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(tempty_bar(acc), acc_phase ^ 1);  // epilogue has drained this accumulator
-      tcgen05_fence_after();
+      tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * BN;
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(full_bar(stage), phase);
-        tcgen05_fence_after();
+        tc_fence_after();
         if (elect_one()) {
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
           const uint32_t sb = sa + C::A_BYTES;
@@ -469,8 +290,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
         for (int n = 0; n < RES_RING - LAG; ++n) issue_load(n);
       }
-      float ln_s = 0.f, ln_ss = 0.f;  // LN == 2: this lane's row, sums over the warp's units of the current tile
       for (int n = 0; n < total; ++n) {
+        [[maybe_unused]] float ln_s = 0.f, ln_ss = 0.f;  // LN == 2: this lane's row, sums over the 32 columns of this unit
         const int it = n / UH, i = n - it * UH;
         const int acc = it & 1;
         int row0, col0, u;
@@ -479,12 +300,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const uint32_t slab = ring + slot * SLOT_BYTES;
         if (i == 0) {
           mbar_wait(tfull_bar(acc), (it >> 1) & 1);
-          tcgen05_fence_after();
+          tc_fence_after();
         }
         mbar_wait(res_bar(ew, slot), (n / RES_RING) & 1);  // residual slab(s) of this unit have landed
         const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
         uint32_t r[32];
-        tmem_ld32(tmem_row + u * 32, r);
+        tmem_ld32_nowait(tmem_row + u * 32, r);
         tmem_ld_wait();
         const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
         [[maybe_unused]] uint32_t xbp[4];
@@ -516,16 +337,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           }
         }
         if constexpr (LN == 2) {
-          if (i == UH - 1) {  // this warp's share of the row is complete for this tile: one partial per (n tile, half)
-            const int tile = cl + it * ncl;
-            const int tn = tile % p.tiles_n;
-            if (row0 + lane < p.M)
-              p.ln_stats[static_cast<long long>(p.row0 + row0 + lane) * p.ln_slots + 2 * tn + hf] = make_float2(ln_s, ln_ss);
-            ln_s = ln_ss = 0.f;
-          }
+          // one partial per 32-column unit, whatever the tile width: the consumer adds the N / 32 partials of a row in a
+          // fixed order, so the statistics (and everything downstream) do not depend on the tile choice of this launch
+          if (row0 + lane < p.M)
+            p.ln_stats[static_cast<long long>(p.row0 + row0 + lane) * p.ln_slots + (col0 >> 5)] = make_float2(ln_s, ln_ss);
         }
         if (i == UH - 1) {  // last TMEM read of this tile: hand the accumulator back to the MMA warp
-          tcgen05_fence_before();
+          tc_fence_before();
           __syncwarp();
           if (lane == 0) {
             if constexpr (CTAS == 2) mbar_arrive_cluster(mapa(tempty_bar(acc), 0));
@@ -551,26 +369,30 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     } else {
       // two slabs per warp: unit n fills slab n & 1 while the TMA store of unit n - 1 still reads the other one
       // folded-LN consumer: the row partials (sum, sum of squares) of a tile are fetched one tile ahead
-      [[maybe_unused]] float4 pa = make_float4(0.f, 0.f, 0.f, 0.f), pb = pa;
-      [[maybe_unused]] auto ld_stats = [&](int tile_, float4& a, float4& b) {
-        a = make_float4(0.f, 0.f, 0.f, 0.f);
-        b = a;
+      // folded-LN consumer: the row partials (sum, sum of squares per 32-column unit of the producer's output) of a tile are
+      // fetched one tile ahead and added in slot order
+      [[maybe_unused]] float4 st[8];
+      [[maybe_unused]] auto ld_stats = [&](int tile_) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) st[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         const int r_ = tile_row(tm_of(tile_)) + q * 32 + lane;
         if (r_ >= p.M) return;
         const float2* sp = p.ln_stats + static_cast<long long>(p.row0 + r_) * p.ln_slots;  // written by the previous kernel
-        if (p.ln_slots == 4) {  // 256-wide producer tiles over 512 columns: two 16-byte loads
-          a = *reinterpret_cast<const float4*>(sp);
-          b = *reinterpret_cast<const float4*>(sp + 2);
+        if (p.ln_slots == 16) {  // 512 columns: eight 16-byte loads
+#pragma unroll
+          for (int k = 0; k < 8; ++k) st[k] = *reinterpret_cast<const float4*>(sp + 2 * k);
         } else {
+          float s_ = 0.f, ss_ = 0.f;
           for (int k = 0; k < p.ln_slots; ++k) {
             const float2 t = sp[k];
-            a.x += t.x;
-            a.y += t.y;
+            s_ += t.x;
+            ss_ += t.y;
           }
+          st[0] = make_float4(s_, ss_, 0.f, 0.f);
         }
       };
       if constexpr (LN == 1) {
-        if (cl < num_tiles) ld_stats(cl, pa, pb);
+        if (cl < num_tiles) ld_stats(cl);
       }
       constexpr int NSLAB = C::SLABS_PER_WARP;
       const uint32_t slab2 = slab_base + ew * NSLAB * SLAB_BYTES;
@@ -586,21 +408,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         [[maybe_unused]] float ln_rs = 1.f, ln_nm = 0.f;  // LN == 1: rstd and -rstd * mean of this lane's row
         if constexpr (LN == 1) {
           // partials of THIS tile's row were requested one tile ago (or before the loop); request the next tile's now
-          const float s = (pa.x + pa.z) + (pb.x + pb.z), ss = (pa.y + pa.w) + (pb.y + pb.w);
-          if (tile + ncl < num_tiles) ld_stats(tile + ncl, pa, pb);
+          float s = 0.f, ss = 0.f;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            s += st[k].x; ss += st[k].y;
+            s += st[k].z; ss += st[k].w;
+          }
+          if (tile + ncl < num_tiles) ld_stats(tile + ncl);
           const float mu = s * p.ln_inv_dim;
           ln_rs = rsqrtf(fmaxf(fmaf(-mu, mu, ss * p.ln_inv_dim), 0.f) + 1e-12f);  // VLLM/model_executor/models/funasr.py:85 eps
           ln_nm = -ln_rs * mu;
         }
         mbar_wait(tfull_bar(acc), acc_phase);
-        tcgen05_fence_after();
+        tc_fence_after();
 #pragma unroll 1
         for (int u = hf; u < UNITS; u += 2, ++n) {
           const int col0 = tn * BN + u * COLS;
           const uint32_t slab = slab2 + (n % NSLAB) * SLAB_BYTES;
           if constexpr (OUT_F32) {
             uint32_t r[32];
-            tmem_ld32(tmem_row + u * 32, r);
+            tmem_ld32_nowait(tmem_row + u * 32, r);
             float4 bv[8];
             const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
@@ -619,8 +446,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
           } else {
             uint32_t r0[32], r1[32];
-            tmem_ld32(tmem_row + u * 64, r0);
-            tmem_ld32(tmem_row + u * 64 + 32, r1);
+            tmem_ld32_nowait(tmem_row + u * 64, r0);
+            tmem_ld32_nowait(tmem_row + u * 64 + 32, r1);
             if (pending >= NSLAB) {
               if (lane == 0) bulk_wait_read<NSLAB - 1>();
               pending = NSLAB - 1;
@@ -660,7 +487,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
           }
           if (u + 2 >= UNITS) {  // last TMEM read of this tile: hand the accumulator back before the stores go out
-            tcgen05_fence_before();
+            tc_fence_before();
             __syncwarp();
             if (lane == 0) {
               if constexpr (CTAS == 2) mbar_arrive_cluster(mapa(tempty_bar(acc), 0));
@@ -689,14 +516,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     __syncwarp();
   }
 
-  tcgen05_fence_before();
+  tc_fence_before();
   if constexpr (CTAS == 2) cluster_sync(); else __syncthreads();  // the leader's MMAs read the peer's smem until here
   if (warp == 1) {
-    tcgen05_fence_after();
-    if constexpr (CTAS == 2)
-      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS) : "memory");
-    else
-      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS) : "memory");
+    tc_fence_after();
+    if constexpr (CTAS == 2) tmem_dealloc_pair<C::TMEM_COLS>(tmem_base);
+    else tmem_dealloc<C::TMEM_COLS>(tmem_base);
   }
 }
 
@@ -722,11 +547,8 @@ static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensor
                     const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
   using C = Cfg<BN, NRES, CTAS, OUT_F32>;
   auto kern = gemm_bf16_kernel<BN, OUT_F32, RELU, NRES, CTAS, LN>;
-  static bool attr_done = false;
-  if (!attr_done) {
-    FA_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    attr_done = true;
-  }
+  static SmemOptIn opt;  // one per kernel instantiation
+  if (int r = opt_in_smem(kern, C::SMEM_BYTES, opt)) return r;
   // the CTA pair of cta_group::2 is one cluster
   FA_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), C::SMEM_BYTES, stream, CTAS, ma, mb, mc, mr1, mr2, p));
   return 0;
@@ -755,14 +577,13 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
   p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32; p.accumulate = epi.accumulate;
   p.ln_stats = epi.ln_stats; p.colsum = epi.colsum; p.xb = epi.xb; p.ld_xb = epi.ld_xb;
-  p.reverse = (epi.reverse || launch_reverse()) ? 1 : 0;
-  p.ln_slots = epi.ln_mode == 2 ? 2 * (N / BN) : epi.ln_slots;
+  p.ln_slots = epi.ln_mode == 2 ? N / 32 : epi.ln_slots;
   p.ln_inv_dim = epi.ln_dim > 0 ? 1.f / static_cast<float>(epi.ln_dim) : 0.f;
   FA_REQUIRE(epi.out_f32 || N * 4 * (epi.ln_mode == 1 ? 2 : 1) <= 16384, "gemm: N=%d too wide for the staged epilogue constants", N);
   if (epi.ln_mode == 1)
     FA_REQUIRE(!epi.out_f32 && epi.ln_stats && epi.colsum && epi.ln_slots > 0 && epi.ln_dim > 0, "gemm: folded-LN consumer needs the bf16 output, ln_stats, colsum, ln_slots and ln_dim");
   if (epi.ln_mode == 2)
-    FA_REQUIRE(epi.out_f32 && epi.res1 && !epi.res2 && !epi.accumulate && epi.ln_stats && epi.xb && epi.ld_xb % 8 == 0 && 2 * (N / BN) <= 16,
+    FA_REQUIRE(epi.out_f32 && epi.res1 && !epi.res2 && !epi.accumulate && epi.ln_stats && epi.xb && epi.ld_xb % 8 == 0 && N / 32 <= 16,
                "gemm: folded-LN producer needs the f32 output with exactly one staged residual, ln_stats and xb");
   FA_REQUIRE(!epi.accumulate || epi.out_f32, "gemm: accumulate needs the f32 output");
   const int tiles = p.tiles_m * p.tiles_n;
@@ -827,27 +648,27 @@ int make_tensor_map_bf16(TensorMap2D* out, const void* base, uint64_t rows, uint
   return make_tensor_map(out, base, 2, rows, cols, ld, box_rows);
 }
 
-int gemm_block_n(int M, int N, int n_res) {
-  // Fill the 148 SMs: prefer the widest tile that still yields >= ~1 wave of tiles.  Two prefetched residuals leave
-  // room for the 256-wide operand ring only twice, so those GEMMs (K = d_model, HBM-bound anyway) use 128.
-  const int tiles_m = ceil_div(M, gemm::BM);
-  const int sms = sm_count();
-  if (const char* e = getenv("FA_GEMM_BN")) {  // probe override (profiles/scripts/probe_kernels.py)
-    const int bn = atoi(e);
-    if ((bn == 64 || bn == 128 || (bn == 256 && n_res < 2)) && N % bn == 0) return bn;
-  }
-  if (N % 256 == 0 && tiles_m * (N / 256) >= 2 * sms && n_res < 2) return 256;
-  if (N % 128 == 0 && tiles_m * (N / 128) >= sms) return 128;
-  if (N % 64 == 0) return 64;
-  if (N % 128 == 0) return 128;
-  return 0;
-}
+// CTA pairs (cta_group::2, 256 x 256 tiles) for the wide tile once there are enough rows.
+bool gemm_use_pair(int M, int block_n) { return block_n == 256 && M >= 1024; }
 
-// CTA pairs (cta_group::2, 256 x 256 tiles) for the wide tile once there are enough rows; FA_GEMM_PAIR=0/1 overrides.
-bool gemm_use_pair(int M, int block_n) {
-  if (block_n != 256) return false;
-  if (const char* e = getenv("FA_GEMM_PAIR")) return atoi(e) != 0;
-  return M >= 1024;
+int gemm_block_n(int M, int N, int n_res) {
+  // Every SM works on 128 rows x BN columns per round (a CTA pair: 256 x 256 over two SMs), tiles are dealt round-robin, so
+  // a launch takes ceil(tiles / slots) rounds of a duration that grows with BN plus a fixed per-tile part (pipeline fill,
+  // epilogue drain: about 48 columns' worth).  Pick the width with the least rounds x duration; ties go to the wider tile
+  // (fewer B re-reads).  Two prefetched f32 residuals leave room for the 256-wide operand ring only twice: they use <= 128.
+  // The result of a GEMM does not depend on the choice (same k order per element, LN partials per 32-column unit).
+  const int sms = sm_count();
+  int best = 0;
+  long best_cost = 0;
+  for (int bn = 256; bn >= 64; bn >>= 1) {
+    if (N % bn != 0 || (bn == 256 && n_res >= 2)) continue;
+    const bool pair = gemm_use_pair(M, bn);
+    const long tiles = static_cast<long>(ceil_div(M, pair ? 2 * gemm::BM : gemm::BM)) * (N / bn);
+    const long slots = pair ? sms / 2 : sms;
+    const long cost = ((tiles + slots - 1) / slots) * (bn + 48);
+    if (best == 0 || cost < best_cost) { best = bn; best_cost = cost; }
+  }
+  return best;
 }
 
 int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D& tc, const TensorMap2D* tr1,
@@ -889,7 +710,7 @@ extern "C" int fa_op_gemm_ln(const void* a_dev, int64_t lda, const void* w_dev, 
   e.bias = bias_dev; e.res1 = res1_dev; e.relu = relu; e.out_f32 = out_f32;
   e.ln_mode = ln_mode; e.ln_stats = static_cast<float2*>(ln_stats_dev); e.ln_dim = ln_dim; e.colsum = colsum_dev;
   e.xb = static_cast<__nv_bfloat16*>(xb_dev); e.ld_xb = ld_xb;
-  if (ln_mode == 2) *n_slots = 2 * (N / bn);
+  if (ln_mode == 2) *n_slots = N / 32;
   e.ln_slots = *n_slots;
   return launch_gemm(ta, tb, tc, res1_dev ? &tr1 : nullptr, nullptr, bn, M, N, K, e, c_dev, ldc, 0, pair,
                      static_cast<cudaStream_t>(stream));

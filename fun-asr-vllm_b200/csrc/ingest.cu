@@ -120,11 +120,8 @@ extern "C" int fa_resample_sinc(const float* in_dev, const int64_t* in_start_dev
   const cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define FA_RS_LAUNCH(JJ, FF)                                                                                                        \
   do {                                                                                                                              \
-    static bool attr = false;                                                                                                       \
-    if (!attr) {                                                                                                                    \
-      FA_CHECK_CUDA(cudaFuncSetAttribute(ingest::resample_kernel<JJ, FF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
-      attr = true;                                                                                                                  \
-    }                                                                                                                               \
+    static SmemOptIn opt;                                                                                                           \
+    if (int r_ = opt_in_smem(ingest::resample_kernel<JJ, FF>, 200 * 1024, opt)) return r_;                                          \
     ingest::resample_kernel<JJ, FF><<<n_tiles, ingest::THREADS, smem, st>>>(in_dev, in_start_dev, in_len_dev, kernel_dev, orig,      \
                                                                              new_freq, width, taps_padded, fw, out_dev, out_start_dev, \
                                                                              tile_off_dev, n_utts);                                  \

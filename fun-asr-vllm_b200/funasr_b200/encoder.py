@@ -114,7 +114,11 @@ class _Arena:
 
 
 class Plan:
-    """One ``fa_plan``: encoder and/or adaptor weights + workspace for up to ``max_tokens`` packed rows."""
+    """One ``fa_plan``: encoder and/or adaptor weights + workspace for up to ``max_tokens`` packed rows.
+
+    The weight arena is a SNAPSHOT of the module parameters taken when the plan is built (bf16-rounded matrices, LayerNorm
+    folded into the GEMMs): ``load_state_dict`` / ``.to()`` on the module drop the plan (``_PlannedModule.invalidate``), but
+    in-place edits of a parameter tensor are not seen until ``invalidate()`` is called."""
 
     def __init__(self, encoder: "SenseVoiceEncoderSmall | None", adaptor: "Transformer | None", device, max_tokens: int = 4096):
         _lib.require_device(device)
@@ -133,7 +137,7 @@ class Plan:
         t.handle, t.cap = C.c_void_p(None), 0
         t.arena, t.cfg, t.w = self.arena, self.cfg, self.w
         t._layers, t._ad_layers = getattr(self, "_layers", None), getattr(self, "_ad_layers", None)
-        for k in ("chunk_tokens", "n_streams"):
+        for k in ("graph_rows", "n_streams"):
             if getattr(self, k, None) is not None:
                 setattr(t, k, getattr(self, k))
         t._create(self.cap if max_tokens is None else max_tokens)
@@ -170,8 +174,9 @@ class Plan:
                     d, ln1_g=ar.vec(L.norm1.weight), ln1_b=ar.vec(L.norm1.bias),
                     qkv_w=ar.mat(qkv_w), qkv_b=ar.vec(qkv_b),
                     fsmn_w=ar.vec(a.fsmn_block.weight.squeeze(1).t().contiguous()),  # [D,1,K] -> tap-major [K,D] f32
-                    out_w=ar.mat(a.linear_out.weight), out_b=ar.vec(a.linear_out.bias),
-                    # [Wo | I]: the out-projection adds the bf16 FSMN memory on the tensor cores (fa_sanm_layer_w.out_w_ext)
+                    out_b=ar.vec(a.linear_out.bias),
+                    # [Wo | I]: the out-projection adds the bf16 FSMN memory on the tensor cores (fa_sanm_layer_w.out_w_ext);
+                    # the plain Wo (fa_sanm_layer_w.out_w) stays NULL
                     out_w_ext=ar.mat(torch.cat([a.linear_out.weight.detach().float(),
                                                 torch.eye(a.linear_out.weight.shape[0], device=a.linear_out.weight.device)], dim=1)),
                     ln2_g=ar.vec(L.norm2.weight), ln2_b=ar.vec(L.norm2.bias),
@@ -233,20 +238,22 @@ class Plan:
         nbytes = int(lib.fa_plan_workspace_bytes(C.byref(self.cfg), cap))
         if nbytes == 0:
             raise _lib.FunASRB200Error("fa_plan_workspace_bytes rejected the model config: " + lib.fa_last_error().decode())
-        self.workspace = torch.empty(nbytes + 1024, dtype=torch.uint8, device=self.device)
+        # zero-filled: rows past the end of a batch must hold finite values (fa_plan_set_graph_rows, include/funasr_b200.h)
+        self.workspace = torch.zeros(nbytes + 1024, dtype=torch.uint8, device=self.device)
         base = (self.workspace.data_ptr() + 1023) // 1024 * 1024
         with torch.cuda.device(self.device):
             _lib.check(lib.fa_plan_create(C.byref(self.cfg), C.byref(self.w), base, nbytes, cap, C.byref(self.handle)), "fa_plan_create")
         self.cap = cap
-        if getattr(self, "chunk_tokens", None) is not None:
-            _lib.check(lib.fa_plan_set_chunk_tokens(self.handle, self.chunk_tokens), "fa_plan_set_chunk_tokens")
+        if getattr(self, "graph_rows", None) is not None:
+            _lib.check(lib.fa_plan_set_graph_rows(self.handle, self.graph_rows), "fa_plan_set_graph_rows")
         if getattr(self, "n_streams", None) is not None:
             _lib.check(lib.fa_plan_set_streams(self.handle, self.n_streams), "fa_plan_set_streams")
 
-    def set_chunk_tokens(self, n: int):
-        """Slab size of the layer schedule (``fa_plan_set_chunk_tokens``); 0 runs every layer over the whole batch."""
-        self.chunk_tokens = int(n)
-        _lib.check(_lib.load().fa_plan_set_chunk_tokens(self.handle, int(n)), "fa_plan_set_chunk_tokens")
+    def set_graph_rows(self, n: int):
+        """Batches of up to ``n`` packed rows replay a captured CUDA graph of the launch program (``fa_plan_set_graph_rows``);
+        0 turns replay off."""
+        self.graph_rows = int(n)
+        _lib.check(_lib.load().fa_plan_set_graph_rows(self.handle, int(n)), "fa_plan_set_graph_rows")
 
     def set_streams(self, n: int):
         """1 = everything on the caller's stream; 2 = two half-batches on two streams (``fa_plan_set_streams``)."""

@@ -9,7 +9,9 @@ and ``extract_fbank`` (``:292-317``), the functions the reference imports at
 instead of a Python loop over utterances.
 
 Differences, all deliberate and stated in DESIGN.md:
-  * ``dither`` must be 0.0 (dither is random noise; parity needs it off — SURVEY.md §9 Q1);
+  * the kernel runs dither-off whatever ``dither`` says (dither is random noise added per call, VLLM:123 default 1.0,
+    TA:179-181; the path under test is the deterministic one — SURVEY.md §9 Q1); a non-zero ``dither`` is kept as an
+    attribute and warned about once;
   * only the 25 ms / 10 ms / 80-mel / LFR 7-6 geometry is compiled;
   * utterances shorter than one frame raise ``ValueError`` (torchaudio asserts, TA:142).
 """
@@ -87,6 +89,21 @@ def fake_token_len(n_lfr: int, use_low_frame_rate: bool) -> int:
     return int(_lib.load().fa_fake_token_len(int(n_lfr), 1 if use_low_frame_rate else 0))
 
 
+_dither_warned = False
+
+
+def _warn_dither(dither) -> None:
+    """funasr's default ``dither=1.0`` adds N(0,1) noise to the x32768 samples of every call; the CUDA frontend is
+    deterministic and ignores it.  Said once per process, so that an unchanged config.yaml still builds."""
+    global _dither_warned
+    if not _dither_warned:
+        import warnings
+
+        warnings.warn(f"funasr_b200.WavFrontend: dither={dither} is ignored, the CUDA frontend runs dither-off "
+                      "(set dither: 0.0 in frontend_conf to silence this)", stacklevel=3)
+        _dither_warned = True
+
+
 # ----------------------------------------------------------------------------- frontend
 class WavFrontend(torch.nn.Module):
     """Same surface as funasr's ``WavFrontend`` (VLLM:89-168)."""
@@ -106,8 +123,7 @@ class WavFrontend(torch.nn.Module):
         self.device = torch.device(device)
         self._tables = {}  # device index -> (tables blob, cmvn) device tensors
         if dither != 0.0:
-            raise ValueError("funasr_b200.WavFrontend needs dither=0.0 (random dither cannot be parity-checked; "
-                             "the reference path under test is dither-off)")
+            _warn_dither(dither)
         if not snip_edges:
             raise ValueError("only snip_edges=True is compiled")
         self._cfg = _lib.FrontendCfg(fs, int(frame_length * fs / 1000), int(frame_shift * fs / 1000), 512, n_mels,

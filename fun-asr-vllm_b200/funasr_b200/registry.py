@@ -61,12 +61,22 @@ def install(override: bool = False):
     return tables
 
 
+def _sanm_shift_of(attn, kernel_size: int) -> int:
+    """funasr keeps the FSMN left pad in ``pad_fn = ConstantPad1d((left, right), 0)`` with ``left = (k-1)//2 + sanm_shfit``
+    (VLLM/model_executor/models/funasr.py:175-179); recover the shift from it (the oracle classes keep ``pad``)."""
+    pad = getattr(getattr(attn, "pad_fn", None), "padding", None) or getattr(attn, "pad", None)
+    if pad is None:
+        return 0
+    return max(int(pad[0]) - (kernel_size - 1) // 2, 0)
+
+
 def _conf_of_encoder(enc) -> dict:
     l0 = enc.encoders0[0]
     a = l0.self_attn
+    k = a.fsmn_block.weight.shape[-1]
     return dict(input_size=l0.norm1.weight.numel(), output_size=l0.norm2.weight.numel(), attention_heads=a.h,
                 linear_units=l0.feed_forward.w_1.weight.shape[0], num_blocks=1 + len(enc.encoders),
-                tp_blocks=len(getattr(enc, "tp_encoders", [])), kernel_size=a.fsmn_block.weight.shape[-1])
+                tp_blocks=len(getattr(enc, "tp_encoders", [])), kernel_size=k, sanm_shfit=_sanm_shift_of(a, k))
 
 
 def _conf_of_adaptor(ad) -> dict:
@@ -98,6 +108,10 @@ def patch(model, kwargs: dict | None = None, device=None, max_tokens: int = 4096
     model.audio_tower_b200 = tower
     if kwargs is not None and kwargs.get("frontend") is not None and not isinstance(kwargs["frontend"], WavFrontend):
         f = kwargs["frontend"]
+        if getattr(f, "dither", 0.0) != 0.0:
+            from .frontend import _warn_dither
+
+            _warn_dither(f.dither)  # the reference's default adds random dither; the CUDA frontend does not
         kwargs["frontend"] = WavFrontend(cmvn_file=getattr(f, "cmvn_file", None), fs=f.fs, window=f.window, n_mels=f.n_mels,
                                          frame_length=f.frame_length, frame_shift=f.frame_shift, lfr_m=f.lfr_m, lfr_n=f.lfr_n,
                                          dither=0.0, upsacle_samples=getattr(f, "upsacle_samples", True), device=device,

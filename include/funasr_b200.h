@@ -42,7 +42,7 @@ extern "C" {
 
 typedef void* fa_stream_t; /* cudaStream_t */
 
-#define FA_ABI_VERSION 4
+#define FA_ABI_VERSION 5
 
 int fa_abi_version(void);
 const char* fa_last_error(void);
@@ -177,26 +177,33 @@ typedef struct {
 } fa_model_w;
 
 /* host-side plan: TMA descriptors + workspace carve-up. No device allocation.  A plan may hold the
- * encoder only (lin1_w == NULL), the adaptor only (n_blocks == 0, layers == NULL) or both. */
+ * encoder only (lin1_w == NULL), the adaptor only (n_blocks == 0, layers == NULL) or both.
+ * The weights are read through the pointers in `w` at every forward call (nothing is copied), so they must stay alive
+ * and unchanged for the life of the plan; the workspace must be zero-filled by the caller before fa_plan_create.
+ * A plan is not thread safe: one host thread (or external locking) per plan. */
 typedef struct fa_plan fa_plan;
 
 size_t fa_plan_workspace_bytes(const fa_model_cfg* cfg, int32_t max_tokens);
 int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void* workspace_dev, size_t workspace_bytes,
                    int32_t max_tokens, fa_plan** plan_out);
 void fa_plan_destroy(fa_plan* plan);
-/* Slab schedule (new; the reference runs every layer over the whole padded batch, infer.py:455).  A batch larger than
- * ~chunk_tokens packed rows is cut on utterance boundaries into slabs of about that many rows, and each slab runs through
- * ALL layers before the next one starts, so a layer's activations are read back from the 126 MB L2 instead of HBM.
- * Utterances are independent, so the result does not depend on the split.  Needs cu_seqlens_host in the forward calls.
- * Default 0 = never split (the split costs more in per-launch ramp-up than it saves on B200); environment
- * override at plan creation: FA_CHUNK_TOKENS. */
-int fa_plan_set_chunk_tokens(fa_plan* plan, int32_t chunk_tokens);
 /* Dual-stream schedule (new).  n_streams == 2: a batch of >= 2 utterances and >= 2048 rows is cut on an utterance boundary
  * into two halves of equal cost; half 0 runs on the caller's stream, half 1 on a plan-owned auxiliary stream that is forked
  * from and joined back into the caller's stream with events inside the same call, so the call still only ENQUEUES work
  * ordered on `stream`.  The HBM-bound kernels of one half then share the SMs with the tensor-bound GEMMs of the other.
  * Results are bit-identical to n_streams == 1.  Needs cu_seqlens_host.  Environment override at plan creation: FA_STREAMS. */
 int fa_plan_set_streams(fa_plan* plan, int32_t n_streams);
+/* CUDA-graph replay (new; the reference's vLLM side captures graphs for its decode batches, infer_kaldidata.py:655-656).
+ * A batch of at most max_rows packed rows does not issue the ~440 launches of a forward pass one by one: the plan's launch
+ * program is captured once per BUCKET (rows rounded up to 1/8..1/16 of their size, utterances to a multiple of 8, the longest
+ * utterance to a multiple of 128 rows) and replayed with one cudaGraphLaunch; utterance boundaries and the true row count
+ * are read from cu_seqlens on the device, so one captured graph serves every batch of its bucket.  Results are bit-identical
+ * to the launch-by-launch schedule.  Capturing instantiates a CUDA graph (the one place the library lets the driver allocate);
+ * up to 48 graphs are kept per plan, least recently used first out.  max_rows == 0 turns replay off; larger batches use the
+ * dual-stream schedule above.  Needs a workspace that was zero-filled before fa_plan_create (rows past the end of a batch
+ * are computed on whatever the workspace holds and must stay finite). */
+#define FA_DEFAULT_GRAPH_ROWS 8192
+int fa_plan_set_graph_rows(fa_plan* plan, int32_t max_rows);
 
 /* Layouts.  Every [rows, dim] activation argument comes with a `*_tmax`:
  *   tmax == 0 : PACKED  [n_tokens, dim], utterance b at rows [cu_seqlens[b], cu_seqlens[b+1])
@@ -205,8 +212,8 @@ int fa_plan_set_streams(fa_plan* plan, int32_t n_streams);
  * feats_dev is NOT modified (the reference scales it in place, VLLM/...:388).
  * enc_out_dev f32 [.., d_model] may be NULL: the result stays in the plan's workspace for
  * fa_adaptor_forward(enc_dev = NULL).
- * cu_seqlens_host: HOST copy of cu_seqlens_dev ([n_utts + 1] int32), or NULL.  It is only used to cut the batch into slabs
- * (fa_plan_set_chunk_tokens); with NULL the batch runs as one slab. */
+ * cu_seqlens_host: HOST copy of cu_seqlens_dev ([n_utts + 1] int32), or NULL.  It is only used to cut the batch into the two
+ * halves of the dual-stream schedule (fa_plan_set_streams); with NULL the batch runs on the caller's stream alone. */
 int fa_encoder_forward(fa_plan* plan, const float* feats_dev, int32_t feats_tmax, const int32_t* cu_seqlens_dev,
                        const int32_t* cu_seqlens_host, int32_t n_utts, int32_t n_tokens, int32_t max_len,
                        float* enc_out_dev, int32_t enc_out_tmax, fa_stream_t stream);
