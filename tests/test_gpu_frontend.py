@@ -145,5 +145,10 @@ def test_short_or_empty_input_raises():
         extract_fbank([torch.zeros(399)], frontend=fe)
     with pytest.raises(ValueError):
         extract_fbank([], frontend=fe)
-    with pytest.raises(ValueError):
+    import funasr_b200.frontend as ff
+
+    ff._dither_warned = False
+    with pytest.warns(UserWarning, match="dither"):  # funasr's default dither=1.0 builds, and says that it is ignored
         type(fe)(dither=1.0, lfr_m=7, lfr_n=6)
+    with pytest.raises(ValueError):
+        type(fe)(snip_edges=False, dither=0.0)

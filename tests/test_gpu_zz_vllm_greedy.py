@@ -2,14 +2,16 @@
 the CUDA path and from those of the fp32 CPU oracle (north_star: "greedy token agreement of vLLM decoding from both sets
 of embeddings"; hand-off as in /root/reference/infer.py:381-388,462-475).
 
-The engine runs in its own process (tests/vllm_greedy_worker.py) under a hard timeout so that a vLLM start-up problem on
-the box can never hang or poison the rest of the GPU suite: if the engine cannot start the test is SKIPPED with the
-reason; if it runs, the agreement is asserted.  Set FA_SKIP_VLLM=1 to leave it out.
+The engine runs in its own process (tests/vllm_greedy_worker.py) under a hard timeout so that a vLLM start-up problem can
+never hang or poison the rest of the GPU suite.  When vllm is importable the test does not skip: a worker that dies, times
+out or prints no result FAILS (set FA_SKIP_VLLM=1 to leave the test out explicitly).
 
-Bar: with a random-init LLM the top-1/top-2 logit margin is small, so agreement is judged against the engine's own
-noise floor (the oracle embeddings submitted twice in different batch slots).  Measured on B200 (profiles/r01_g_cfg4_vllm_greedy.json,
-16 x 10 s, full 50+20 encoder, 16 new tokens): embeddings differ by 0.65 % relative RMS, first token agrees for 13/16 utterances,
-12/16 sequences agree on all 16 tokens, control 16/16.  Asserted: first token >= 60 %, mean common prefix >= half the tokens."""
+Bar ("exact agreement ... mismatches listed individually").  With a random-init LLM a fraction of the greedy
+decisions are near-ties, which no embedding path of finite precision can reproduce; the worker therefore measures, in fp32
+with HF transformers, the oracle's top-1/top-2 logit margin at every generated position and the shift of that gap caused by
+the CUDA path's embeddings, and the test asserts EXACT agreement of the engine's tokens at every position whose margin
+exceeds the measured perturbation (theta = largest gap shift + 3 x the engine's own bf16 gap noise): `violations` must be
+empty, every mismatch is listed with its margin, and the control run (oracle embeddings twice) must agree exactly."""
 import json
 import os
 import subprocess
@@ -47,22 +49,25 @@ def test_cfg4_vllm_greedy_agreement():
             pass
         proc.wait()
     if r is None:
-        pytest.skip("vLLM worker timed out")
+        pytest.fail("cfg4: the vLLM worker timed out")
     out = os.path.join(ROOT, "gpurun_out")
     if os.path.isdir(out):
         with open(os.path.join(out, "cfg4_worker.log"), "w") as f:
             f.write(r.stdout[-4000:] + "\n---- stderr ----\n" + r.stderr[-12000:])
     line = next((l for l in reversed(r.stdout.splitlines()) if l.startswith('{"cfg4"')), None)
     if r.returncode != 0 or line is None:
-        tail = (r.stderr or "")[-1500:]
-        if "funasr_b200" in tail or "AssertionError" in tail:
-            pytest.fail("cfg4 worker failed inside the audio path:\n" + tail)
-        pytest.skip("vLLM engine did not run on this box:\n" + tail[-600:])
+        started = "FA_CFG4_ENGINE_STARTED" in (r.stdout or "")
+        pytest.fail(f"cfg4 worker failed (rc {r.returncode}, engine started: {started}):\n" + (r.stderr or "")[-1500:])
     res = json.loads(line)
     print(line)
     if os.path.isdir(out):
         with open(os.path.join(out, "cfg4_vllm_greedy.json"), "w") as f:
             f.write(line + "\n")
+    ma = res["margin_analysis"]
     assert res["embed_rel_rms_max"] < 2.5e-2
+    assert res["control_exact"] == 1.0, "the engine is not deterministic across batch slots: the comparison is void"
+    assert ma["violations"] == [], f"greedy tokens differ at positions whose margin exceeds the measured perturbation: {ma['violations']}"
+    assert ma["decidable_fraction"] > 0.0, ma  # the bound must leave positions to decide
+    # the loose round-1 bar stays as a floor
     assert res["first_token"] >= 0.6, res
     assert res["prefix_mean"] >= 0.5 * res["max_tokens"], res
