@@ -303,7 +303,9 @@ struct Builder {
       return launch_layernorm(x + o, g, b, g2, b2, y_bf16 ? y_bf16 + o : nullptr, y_f32 ? y_f32 + o : nullptr, r.M, D, r.s);
     });
   }
-  void attention(std::vector<Step>& prog, const __nv_bfloat16* qkv, __nv_bfloat16* ctx, int H, int D, int ld_ctx) {
+  // fsmn_w != nullptr: the FSMN memory is produced by the attention kernel itself (bf16, beside the context: column D + c)
+  void attention(std::vector<Step>& prog, const __nv_bfloat16* qkv, __nv_bfloat16* ctx, int H, int D, int ld_ctx,
+                 const float* fsmn_w = nullptr, int fsmn_left = 0) {
     if (rc) return;
     // one tensor map over the whole qkv buffer, encoded once per plan: utterances are addressed by their ABSOLUTE packed rows
     // (base 0).  Key / value rows past the end of a batch are workspace rows, which hold finite values (the caller hands in a
@@ -312,8 +314,9 @@ struct Builder {
     const int cap = p->cap;
     rc = make_tensor_map_bf16(&tm, qkv, cap, 3 * D, 3 * D, attention_kv_box());
     if (rc) return;
-    prog.push_back([tm, qkv, ctx, H, D, ld_ctx, cap](const RunArgs& r) {
-      return launch_attention(&tm, qkv, 3 * D, r.cu, r.n_utts, 0, r.max_len, H, ctx, ld_ctx, cap, r.s);
+    prog.push_back([tm, qkv, ctx, H, D, ld_ctx, cap, fsmn_w, fsmn_left](const RunArgs& r) {
+      return launch_attention(&tm, qkv, 3 * D, r.cu, r.n_utts, 0, r.max_len, H, ctx, ld_ctx, cap, fsmn_w, fsmn_left,
+                              fsmn_w ? ctx + D : nullptr, ld_ctx, r.s);
     });
   }
 };
@@ -347,7 +350,10 @@ int build_programs(fa_plan* p) {
     // ext: bf16 memory written beside the attention context (row = [ctx | mem]); the out-projection multiplies it by the
     // identity block of out_w_ext, i.e. adds it in the f32 accumulator.  Otherwise f32 memory, added by the epilogue.
     const bool ext = L.out_w_ext != nullptr;
-    {
+    // With the bf16 memory and the model's 11-tap kernel the FSMN runs inside the attention kernel, on the V blocks that are
+    // in shared memory for P V anyway: no FSMN launch, V is read once.
+    const bool fuse_fsmn = ext && attention_can_fuse_fsmn(c.fsmn_kernel, 2 * d, ws.ctx + d);
+    if (!fuse_fsmn) {
       const __nv_bfloat16* qkv = ws.qkv;
       const float* fw = L.fsmn_w;
       float* mem = ws.mem;
@@ -362,7 +368,7 @@ int build_programs(fa_plan* p) {
       });
     }
     // masked MHA                                                           VM:250-252,222-236
-    B.attention(E, ws.qkv, ws.ctx, c.n_heads, d, 2 * d);
+    B.attention(E, ws.qkv, ws.ctx, c.n_heads, d, 2 * d, fuse_fsmn ? L.fsmn_w : nullptr, left);
     // x (+)= ctx Wo^T + b + mem   (no residual when in_size != size: layer 0 overwrites x)   VM:238,253,123-136
     // The residual stream is updated IN PLACE: the epilogue hands acc + bias + mem to a TMA reduce-add, so x is never
     // staged through the SM.

@@ -1,27 +1,28 @@
-// Variable-length multi-head self-attention over packed utterances, head dim 128, on tcgen05 / TMEM.
+// Variable-length multi-head self-attention over packed utterances, head dim 128, fused with the FSMN memory block of
+// SAN-M, on tcgen05 / TMEM.  One persistent kernel per layer:
 //   ctx = softmax(q k^T / sqrt(128)) v   per (utterance, head); keys never cross utterances, which is exactly the
-//   reference's key-masked padded attention on valid rows
-//   (VLLM/model_executor/models/funasr.py:222-235,250-252; adaptor :506-512).
+//         reference's key-masked padded attention on valid rows (VLLM/model_executor/models/funasr.py:222-235,250-252;
+//         adaptor :506-512)
+//   mem = v + depthwise_conv_time(v)     the FSMN memory on the SAME value rows (VLLM/...:181-201), computed by two filler
+//         warps of the same CTAs while the attention pipeline pulls those rows through L2, so V crosses HBM once per layer
+//         and the separate FSMN pass (one launch and one more read of V per layer) is gone.
 //
-// One CTA = (utterance b, head h, 128 query rows).  Keys/values stream through a 2-stage shared-memory ring in blocks of
-// 64 keys (TMA, 128B swizzle); per block j
-//     S_j = Q K_j^T         tcgen05.mma, A = Q (smem, K-major), B = K_j (smem, K-major), D in TMEM (two S buffers)
-//     P_j = exp2(S c - m)   softmax warps: thread = row, TMEM -> registers (one pass) -> bf16 -> swizzled smem in the
-//                           A-operand layout, written over K_j (dead once S_j is complete)
-//     O  += P_j V_j         tcgen05.mma, A = P (smem, K-major), B = V_j (smem, MN-major: V rows are keys), D in TMEM
-// software-pipelined: S_{j+1} is issued before the softmax of block j finishes, so the tensor pipe, the MUFU/ALU softmax
-// and the TMA of block j+2 overlap inside one CTA; the online softmax only raises its running maximum when it grows by
-// more than 2^8 (the O accumulator in TMEM is then rescaled once), so most blocks never touch O.  The CTA is lean —
-// 97 KB of smem and 256 TMEM columns — so that TWO CTAs share an SM (utterances are short: T = 167 for 10 s = three
-// key blocks).  Warp roles: 0 TMA producer, 1 MMA issuer (+ TMEM alloc), 2..5 softmax / epilogue (one TMEM lane quarter
-// each).
-// Measured alternative (kept out): one CTA per SM owning BOTH 128-row query tiles of an utterance with a 3-stage ring and
-// two softmax warpgroups (K/V loaded once, all 512 TMEM columns): 138 us instead of 121 us at T = 167 -- with a single
-// CTA per SM the load phase of one work item no longer overlaps the compute phase of another.
-// Second measured alternative (kept out, profiles/r01_m_attention_short.md): a single-pass kernel for utterances of <= 192 keys
-// (S for all keys in one MMA series, exact softmax, V loaded over Q, O over S's TMEM columns; still two CTAs per SM):
-// 115.7 us instead of 118.8 us at T = 167 -- the three block rounds are not what bounds the kernel -- and it would break the
-// bit-identity of the slab / whole-batch schedules (two kernels, two roundings), so the block loop stays the only path.
+// Persistent CTAs (one per SM, static round-robin over work items).  A work item = (utterance b, head h, group of GQ <= 2
+// query tiles of 128 rows): the K/V blocks (64 keys each) of the utterance stream ONCE through a 3-stage shared-memory ring
+// (TMA, 128B swizzle) and serve both query tiles; per block j and query tile q
+//     S_qj = Q_q K_j^T       tcgen05.mma, A = Q_q (smem, K-major), B = K_j (smem, K-major), D in TMEM (2 buffers per tile)
+//     P_qj = exp2(S c - m)   softmax warpgroup q: thread = row, TMEM -> registers (one pass) -> bf16 -> swizzled smem in the
+//                            A-operand layout (2 buffers per tile)
+//     O_q += P_qj V_j        tcgen05.mma, A = P (smem, K-major), B = V_j (smem, MN-major: V rows are keys), D in TMEM
+// S and P are both double-buffered, so a softmax warpgroup never waits for the P V product of the block before it: the only
+// MMA results it waits for are S of its own block (issued two blocks ahead) and, on the rare block that raises the running
+// maximum by more than 2^8, the P V products so far (O is then rescaled once in TMEM).  All 512 TMEM columns are used:
+// S[2 tiles][2 buffers] x 64 + O[2 tiles] x 128.
+// Warp roles (12 warps): 0..1 FSMN, 2..5 softmax / epilogue of query tile 0, 6..9 of query tile 1, 10 TMA producer, 11 MMA
+// issuer (+ TMEM alloc).  The producer runs ahead across work items (next item's Q as soon as the last S of the current one
+// has been issued, K/V as stages free up), every role has the next item's cu_seqlens loads in flight while it works on the
+// current one, and the epilogue of one item (O -> ctx) overlaps the first S MMAs of the next: nothing is set up or torn
+// down per work item.
 #include <cuda.h>
 
 #include <cstring>
@@ -31,311 +32,511 @@
 namespace fa {
 namespace attn {
 
+using namespace fa::ptx;
+
 constexpr int HD = 128;   // head dim
-constexpr int BQ = 128;   // query rows per CTA = UMMA M
+constexpr int BQ = 128;   // query rows per tile = UMMA M
 constexpr int BKV = 64;   // keys per block
-constexpr int STAGES = 2;
-constexpr int THREADS = 192;
+constexpr int NST = 3;    // K/V stages
+constexpr int NQ = 2;     // query tiles per work item (at most)
+constexpr int FSMN_WARPS = 2;   // filler warps: each takes every other FSMN item of its CTA
+constexpr int THREADS = (10 + FSMN_WARPS) * 32;
+// Warp ids by role.  The issue arbiter of a sub-partition favours its higher warp ids: the two latency-critical single-lane
+// roles sit on top, the FSMN filler warps at the bottom (they only take slots nobody else wants); the softmax warps keep
+// ids 2..9 (TMEM lane quarter = warp id mod 4).
+constexpr int W_FSMN = 0, W_PRODUCER = 10, W_MMA = 11;
+constexpr int FSMN_K = 11;                 // taps compiled into the fused path (the model's kernel_size)
 constexpr int QPANEL = BQ * 128;           // [128 rows x 64 bf16] 128B-swizzled panel = 16 KB
 constexpr int KPANEL = BKV * 128;          // [64 rows x 64 bf16] panel = 8 KB
-constexpr int Q_BYTES = 2 * QPANEL;        // d = 128 -> two panels
-constexpr int K_BYTES = 2 * KPANEL;        // one K block; P_j (128 rows x 64 keys = one 16 KB panel) later overwrites it
+constexpr int QT_BYTES = 2 * QPANEL;       // one query tile: d = 128 -> two panels
+constexpr int K_BYTES = 2 * KPANEL;
 constexpr int V_BYTES = 2 * KPANEL;
-constexpr int SMEM_BYTES = Q_BYTES + STAGES * (K_BYTES + V_BYTES) + 1024 + 256;
-constexpr int TMEM_COLS = 256;             // S0 [0,64)  S1 [64,128)  O [128,256)
+constexpr int P_BYTES = QPANEL;            // P_qj: 128 rows x 64 keys bf16, one panel
+constexpr int BAR_BYTES = 512;
+constexpr int SMEM_BYTES = NQ * QT_BYTES + NST * (K_BYTES + V_BYTES) + NQ * 2 * P_BYTES + 1024 + BAR_BYTES;
+constexpr int TMEM_COLS = 512;             // S[q][buf] at (2q + buf) * 64, O[q] at 256 + 128 q
 constexpr float RESCALE_THRESHOLD = 8.f;   // log2 units
+static_assert(SMEM_BYTES <= 227 * 1024, "attention: shared memory budget");
 
-using namespace fa::ptx;  // shared inline-PTX wrappers (ptx.cuh)
+struct Params {
+  const int32_t* cu;
+  int base;       // absolute packed row of local row 0 of qkv / ctx
+  int n_utts, n_heads;
+  int groups;     // query-tile groups per utterance (ceil(max_len / (128 GQ)))
+  int gq;         // query tiles per group: 1 or 2
+  __nv_bfloat16* ctx;
+  long long ld_ctx;
+  float scale_log2e;
+  // fused FSMN (nullptr: plain attention, e.g. the adaptor)
+  const __nv_bfloat16* qkv;  // local row 0 (the FSMN warps read the value rows directly)
+  long long ld_qkv;
+  const float* fsmn_w;  // f32 [FSMN_K, dm] tap-major
+  int fsmn_left;
+  __nv_bfloat16* mem;   // bf16 [rows, ld_mem], column h * 128 + c
+  long long ld_mem;
+};
 
-__device__ __forceinline__ unsigned long long gtime() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
+struct Item {  // decoded identically by every warp role
+  int h, start, len, q_row0, nq, nb;
+  bool fsmn;
+};
+
+// cu_seqlens[b], cu_seqlens[b + 1] of work item i (an input of the forward call, not a predecessor's output).  Every role
+// issues these loads one item early, so their latency is spent under the current item.
+__device__ __forceinline__ void fetch_bounds(const Params& p, int i, int n_items, int& c0, int& c1) {
+  if (i < n_items) {
+    const int b = i / (p.n_heads * p.groups);
+    c0 = __ldg(p.cu + b);
+    c1 = __ldg(p.cu + b + 1);
+  }
 }
-// Per-CTA timeline for profiles/scripts/trace_attention.py: compiled in only with -DFA_ATTN_TRACE (make TRACE=1).
+
+__device__ __forceinline__ bool decode_item(const Params& p, int i, int c0, int c1, Item& it) {
+  it.h = i % p.n_heads;
+  const int g = (i / p.n_heads) % p.groups;
+  it.start = c0 - p.base;
+  it.len = c1 - c0;
+  it.q_row0 = g * p.gq * BQ;
+  if (it.q_row0 >= it.len) return false;
+  it.nq = min(p.gq, (it.len - it.q_row0 + BQ - 1) / BQ);
+  it.nb = (it.len + BKV - 1) / BKV;
+  it.fsmn = p.fsmn_w != nullptr && g == 0;  // the first group of an utterance streams every V block: it owns the FSMN rows
+  return true;
+}
+
+// Runs body(it) for every work item of this CTA (static round-robin); items whose query group lies past the end of the
+// utterance are skipped by every role alike.
+template <typename Body>
+__device__ __forceinline__ void for_items(const Params& p, int n_items, Body&& body) {
+  int c0n = 0, c1n = 0;
+  fetch_bounds(p, blockIdx.x, n_items, c0n, c1n);
+  for (int i = blockIdx.x; i < n_items; i += gridDim.x) {
+    Item it;
+    const bool ok = decode_item(p, i, c0n, c1n, it);
+    fetch_bounds(p, i + gridDim.x, n_items, c0n, c1n);
+    if (ok) body(it);
+  }
+}
+
+// ---------------------------------------------------------------- pipeline trace (make TRACE=1: profiling builds only)
 #ifdef FA_ATTN_TRACE
-#define TRACE(slot)                                                                              \
-  do {                                                                                           \
-    if (trace && cta_lin < 512) trace[cta_lin * 16 + (slot)] = gtime();                          \
-  } while (0)
+__device__ unsigned long long g_trace[1 << 16];
+__device__ unsigned int g_trace_n;
+// event | item | block/tile | SM clock, CTA 0 only
+__device__ __forceinline__ void trace(int ev, int a, int b) {
+  if (blockIdx.x == 0 && ((threadIdx.x & 31) == 0 || threadIdx.x >= 64)) {
+    const unsigned int i = atomicAdd(&g_trace_n, 1u);
+    if (i < (1u << 16)) g_trace[i] = (static_cast<unsigned long long>(clock64()) << 24) | ((ev & 0xff) << 16) | ((a & 0xff) << 8) | (b & 0xff);
+  }
+}
+#define FA_TRACE(ev, a, b) trace(ev, a, b)
 #else
-#define TRACE(slot) do { } while (0)
+#define FA_TRACE(ev, a, b)
 #endif
 
 // ---------------------------------------------------------------- kernel
-__global__ void __launch_bounds__(THREADS, 2)
-attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const int32_t* __restrict__ cu, int base, int n_heads,
-                 __nv_bfloat16* __restrict__ ctx, int64_t ld_ctx, float scale_log2e, unsigned long long* trace) {
+__global__ void __launch_bounds__(THREADS, 1)
+attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
   extern __shared__ unsigned char smem_raw[];
-  const int cta_lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-  if (threadIdx.x == 0) TRACE(0);
   pdl_launch_dependents();
-  const int b = blockIdx.z, h = blockIdx.y;  // (cu_seqlens is an input of the whole forward call, not a kernel's output)
-  const int start = cu[b] - base, len = cu[b + 1] - cu[b];
-  const int q0 = blockIdx.x * BQ;
-  if (q0 >= len) return;  // uniform per CTA, before any barrier / TMEM use
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int dm = n_heads * HD;
-  const int n_blk = (len + BKV - 1) / BKV;
+  const int dm = p.n_heads * HD;
+  const int n_items = p.n_utts * p.groups * p.n_heads;
 
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sQ = sbase, sK0 = sQ + Q_BYTES, sV0 = sK0 + STAGES * K_BYTES, bars = sV0 + STAGES * V_BYTES;
+  const uint32_t sQ0 = sbase, sK0 = sQ0 + NQ * QT_BYTES, sV0 = sK0 + NST * K_BYTES, sP0 = sV0 + NST * V_BYTES;
+  const uint32_t bars = sP0 + NQ * 2 * P_BYTES;
+  auto sQ = [&](int q) { return sQ0 + q * QT_BYTES; };
   auto sK = [&](int st) { return sK0 + st * K_BYTES; };
   auto sV = [&](int st) { return sV0 + st * V_BYTES; };
-  const uint32_t q_full = bars, o_full = bars + 8, tmem_slot = bars + 16;
-  auto k_full = [&](int st) { return bars + 24 + 8 * st; };
-  auto v_full = [&](int st) { return bars + 40 + 8 * st; };
-  auto kv_empty = [&](int st) { return bars + 56 + 8 * st; };
-  auto s_full = [&](int st) { return bars + 72 + 8 * st; };
-  auto p_full = [&](int st) { return bars + 88 + 8 * st; };
+  auto sP = [&](int q, int buf) { return sP0 + (2 * q + buf) * P_BYTES; };
+  const uint32_t q_full = bars, q_empty = bars + 8, tmem_slot = bars + 16;
+  auto k_full = [&](int st) { return bars + 32 + 8 * st; };
+  auto v_full = [&](int st) { return bars + 64 + 8 * st; };
+  auto kv_empty = [&](int st) { return bars + 96 + 8 * st; };
+  auto s_full = [&](int q, int buf) { return bars + 128 + 8 * (2 * q + buf); };   // S_q[buf] written by the MMA
+  auto p_full = [&](int q, int buf) { return bars + 160 + 8 * (2 * q + buf); };   // P_q[buf] written by the softmax (and S_q[buf] read)
+  auto pv_done = [&](int q, int buf) { return bars + 192 + 8 * (2 * q + buf); };  // the P V product that read P_q[buf] retired
+  static_assert(224 <= BAR_BYTES, "barrier region");
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+  const bool fsmn_on = p.fsmn_w != nullptr;
 
-  auto issue_kv = [&](int j) {  // K_j and V_j into stage j & 1 (the caller has made sure the stage is free)
-    const int st = j & 1;
-    const int xk = dm + h * HD, xv = 2 * dm + h * HD, row = start + j * BKV;
-    mbar_expect_tx(k_full(st), K_BYTES);
-    tma_load_2d(sK(st), &tmap_qkv, k_full(st), xk, row);
-    tma_load_2d(sK(st) + KPANEL, &tmap_qkv, k_full(st), xk + 64, row);
-    mbar_expect_tx(v_full(st), V_BYTES);
-    tma_load_2d(sV(st), &tmap_qkv, v_full(st), xv, row);
-    tma_load_2d(sV(st) + KPANEL, &tmap_qkv, v_full(st), xv + 64, row);
-  };
-  if (warp == 0 && lane == 0) {
+  if (warp == W_PRODUCER && lane == 0) {
     prefetch_tmap(&tmap_qkv);
     mbar_init(q_full, 1);
-    mbar_init(o_full, 1);
-    for (int st = 0; st < STAGES; ++st) {
+    mbar_init(q_empty, 1);
+    for (int st = 0; st < NST; ++st) {
       mbar_init(k_full(st), 1);
       mbar_init(v_full(st), 1);
-      mbar_init(kv_empty(st), 1);
-      mbar_init(s_full(st), 1);
-      mbar_init(p_full(st), 128);  // every softmax thread arrives
+      mbar_init(kv_empty(st), 1);  // the last P V of the block retired
+    }
+    for (int q = 0; q < NQ; ++q) {
+      for (int buf = 0; buf < 2; ++buf) {
+        mbar_init(s_full(q, buf), 1);
+        mbar_init(p_full(q, buf), 128);  // every softmax thread of the tile arrives
+        mbar_init(pv_done(q, buf), 1);
+      }
     }
     fence_mbar_init();
-    // Q and the first two K/V blocks are requested right here, before the TMEM allocation and the CTA-wide sync
-    // (the producer only needs its own barriers): ~0.4 us of the 1.7 us Q+K0 wait leaves the critical path
-    pdl_wait();
-    mbar_expect_tx(q_full, Q_BYTES);
-#pragma unroll
-    for (int i = 0; i < 4; ++i)  // (panel, row half): box = 64 rows x 64 columns
-      tma_load_2d(sQ + (i >> 1) * QPANEL + (i & 1) * KPANEL, &tmap_qkv, q_full, h * HD + (i >> 1) * 64, start + q0 + (i & 1) * 64);
-    for (int j = 0; j < min(n_blk, STAGES); ++j) issue_kv(j);
   }
-  if (warp == 1) {
-    tmem_alloc<TMEM_COLS>(tmem_slot);
-  }
+  if (warp == W_MMA) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (threadIdx.x == 0) TRACE(1);
   const uint32_t tmem = *tmem_slot_ptr;
-  pdl_wait();
-  const uint32_t tO = tmem + 2 * BKV;
-  auto tS = [&](int st) { return tmem + st * BKV; };
+  auto tS = [&](int q, int buf) { return tmem + (2 * q + buf) * BKV; };
+  auto tO = [&](int q) { return tmem + 4 * BKV + q * HD; };
+  pdl_wait();  // qkv comes from the previous kernel
 
-  if (warp == 0) {
-    // ===================== TMA producer (blocks 0 and 1 were requested during set-up) =====================
-    if (lane == 0) {
-      for (int j = STAGES; j < n_blk; ++j) {
-        mbar_wait(kv_empty(j & 1), ((j >> 1) & 1) ^ 1);  // P_{j-2} V_{j-2} retired: the K/P and V slots of this stage are free
-        issue_kv(j);
+  if (warp == W_PRODUCER) {
+    // ===================== TMA producer =====================
+    // (producer and MMA warps run their loops with all 32 lanes - waits and counters are warp-uniform - and elect one lane
+    // only around the TMA / MMA instructions: inside a lane-0-only region the compiler has to wrap every such instruction
+    // in an elect loop and feed its uniform-register operands through R2UR, ~12 instructions per MMA)
+    int n_it = 0, gk = 0;
+    for_items(p, n_items, [&](const Item& it) {
+      if (n_it > 0) mbar_wait(q_empty, (n_it - 1) & 1);  // every S MMA of the previous item has read Q
+      FA_TRACE(1, n_it, 0);
+      if (elect_one()) {
+        mbar_expect_tx(q_full, it.nq * QT_BYTES);
+        for (int q = 0; q < it.nq; ++q)
+#pragma unroll
+          for (int x = 0; x < 4; ++x)  // (panel, row half): box = 64 rows x 64 columns
+            tma_load_2d(sQ(q) + (x >> 1) * QPANEL + (x & 1) * KPANEL, &tmap_qkv, q_full, it.h * HD + (x >> 1) * 64,
+                        it.start + it.q_row0 + q * BQ + (x & 1) * 64);
       }
-    }
-  } else if (warp == 1) {
+      __syncwarp();
+      const int xk = dm + it.h * HD, xv = 2 * dm + it.h * HD;
+      for (int j = 0; j < it.nb; ++j, ++gk) {
+        const int st = gk % NST;
+        if (gk >= NST) mbar_wait(kv_empty(st), ((gk / NST) - 1) & 1);
+        const int row = it.start + j * BKV;
+        FA_TRACE(2, n_it, j);
+        if (elect_one()) {
+          mbar_expect_tx(k_full(st), K_BYTES);
+          tma_load_2d(sK(st), &tmap_qkv, k_full(st), xk, row);
+          tma_load_2d(sK(st) + KPANEL, &tmap_qkv, k_full(st), xk + 64, row);
+          mbar_expect_tx(v_full(st), V_BYTES);
+          tma_load_2d(sV(st), &tmap_qkv, v_full(st), xv, row);
+          tma_load_2d(sV(st) + KPANEL, &tmap_qkv, v_full(st), xv + 64, row);
+        }
+        __syncwarp();
+      }
+      ++n_it;
+    });
+  } else if (warp == W_MMA) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      auto issue_s = [&](int j) {  // S_j = Q K_j^T into S buffer j & 1
-        const int st = j & 1;
-        const int nkeys = min(BKV, len - j * BKV);
-        tc_fence_after();
-        const uint32_t idesc = make_idesc(BQ, (nkeys + 15) & ~15, 0);
+    int n_it = 0, gk0 = 0;
+    int cs0 = 0, cs1 = 0;  // S blocks issued per query tile
+    int cp0 = 0, cp1 = 0;  // P V blocks issued per query tile
+    for_items(p, n_items, [&](const Item& it) {
+      auto stage_of = [&](int j) { return (gk0 + j) % NST; };
+      auto phase_of = [&](int j) { return static_cast<uint32_t>(((gk0 + j) / NST) & 1); };
+      auto issue_s = [&](int q, int j) {  // S_qj = Q_q K_j^T into S buffer cs & 1
+        int& cs = q ? cs1 : cs0;
+        if (elect_one()) {
+          const int st = stage_of(j);
+          const int nkeys = min(BKV, it.len - j * BKV);
+          const uint32_t idesc = make_idesc(BQ, (nkeys + 15) & ~15, 0);
+          const uint32_t d = tS(q, cs & 1);
 #pragma unroll
-        for (int k = 0; k < HD / 16; ++k)
-          umma_f16(tS(st), desc_kmajor(sQ + (k >> 2) * QPANEL + (k & 3) * 32), desc_kmajor(sK(st) + (k >> 2) * KPANEL + (k & 3) * 32),
-                   idesc, k != 0);
-        umma_commit(s_full(st));
+          for (int k = 0; k < HD / 16; ++k)
+            umma_f16(d, desc_kmajor(sQ(q) + (k >> 2) * QPANEL + (k & 3) * 32), desc_kmajor(sK(st) + (k >> 2) * KPANEL + (k & 3) * 32),
+                     idesc, k != 0);
+          umma_commit(s_full(q, cs & 1));
+          if (j == it.nb - 1 && q == it.nq - 1) umma_commit(q_empty);  // the producer may overwrite Q
+        }
+        __syncwarp();
+        FA_TRACE(3, n_it, 2 * j + q);
+        ++cs;
       };
-      mbar_wait(q_full, 0);
-      mbar_wait(k_full(0), 0);
-      TRACE(2);
-      issue_s(0);
-      for (int j = 0; j < n_blk; ++j) {
-        const int st = j & 1, nx = (j + 1) & 1;
-        const uint32_t nx_phase = ((j + 1) >> 1) & 1;
-        // S_{j+1} first if its K block has landed (it then overlaps the softmax of block j); otherwise after P_j V_j
-        bool s_next_done = (j + 1 >= n_blk);
-        if (!s_next_done && mbar_test(k_full(nx), nx_phase)) {
-          issue_s(j + 1);
-          s_next_done = true;
-        }
-        // O (+)= P_j V_j
-        mbar_wait(p_full(st), (j >> 1) & 1);
-        mbar_wait(v_full(st), (j >> 1) & 1);
+      FA_TRACE(11, n_it, 0);
+      mbar_wait(q_full, n_it & 1);
+      FA_TRACE(12, n_it, 0);
+      for (int j = 0; j < min(2, it.nb); ++j) {
+        mbar_wait(k_full(stage_of(j)), phase_of(j));
         tc_fence_after();
-        {
-          const int nkeys = min(BKV, len - j * BKV);
-          const int ksteps = (nkeys + 15) >> 4;
-          const uint32_t idesc = make_idesc(BQ, HD, 1);
-          for (int k = 0; k < ksteps; ++k)
-            umma_f16(tO, desc_kmajor(sK(st) + k * 32), desc_mnmajor(sV(st) + k * 16 * 128, KPANEL, 1024), idesc, (j | k) != 0);
-          umma_commit(kv_empty(st));
-          if (j == n_blk - 1) umma_commit(o_full);
+        for (int q = 0; q < it.nq; ++q) issue_s(q, j);
+      }
+      for (int j = 0; j < it.nb; ++j) {
+        const int st = stage_of(j);
+        mbar_wait(v_full(st), phase_of(j));
+        const int nkeys = min(BKV, it.len - j * BKV);
+        const int ksteps = (nkeys + 15) >> 4;
+        for (int q = 0; q < it.nq; ++q) {
+          int& cp = q ? cp1 : cp0;
+          mbar_wait(p_full(q, cp & 1), (cp >> 1) & 1);
+          // (j == 0 overwrites O_q: the previous item's epilogue has read it, because the same threads read O, waited for
+          // the TMEM loads and only then produced the P this MMA waits for)
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t idesc = make_idesc(BQ, HD, 1);
+            for (int k = 0; k < ksteps; ++k)  // O_q (+)= P_qj V_j
+              umma_f16(tO(q), desc_kmajor(sP(q, cp & 1) + k * 32), desc_mnmajor(sV(st) + k * 16 * 128, KPANEL, 1024), idesc, (j | k) != 0);
+            umma_commit(pv_done(q, cp & 1));
+            if (q == it.nq - 1) umma_commit(kv_empty(st));  // K_j / V_j are free once everything issued so far has retired
+          }
+          __syncwarp();
+          FA_TRACE(4, n_it, 2 * j + q);
+          ++cp;
         }
-        if (!s_next_done) {
-          mbar_wait(k_full(nx), nx_phase);
-          issue_s(j + 1);
+        if (j + 2 < it.nb) {        // S two blocks ahead: its buffer was read by the softmax of block j (p_full above)
+          mbar_wait(k_full(stage_of(j + 2)), phase_of(j + 2));
+          tc_fence_after();
+          for (int q = 0; q < it.nq; ++q) issue_s(q, j + 2);
         }
       }
-    }
-  } else {
-    // ===================== softmax / epilogue warps: thread = query row =====================
-    const int q = warp & 3;
-    const int row = q * 32 + lane;                 // row within the tile == TMEM lane
-    const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
+      gk0 += it.nb;
+      ++n_it;
+    });
+  } else if (warp >= 2 && warp < 10) {
+    // ===================== softmax / epilogue warpgroups: thread = query row of tile q =====================
+    const int q = (warp - 2) >> 2;
+    const int quarter = warp & 3;                   // TMEM lane quarter this warp may access (hardware: warp id mod 4)
+    const int row = quarter * 32 + lane;            // row within the tile == TMEM lane
+    const uint32_t lane_sel = static_cast<uint32_t>(quarter * 32) << 16;
     const uint32_t rsw = static_cast<uint32_t>(row & 7);
-    const bool row_ok = q0 + row < len;
-    float m_used = -INFINITY, l_run = 0.f;
-    for (int j = 0; j < n_blk; ++j) {
-      const int st = j & 1;
-      const int nkeys = min(BKV, len - j * BKV);
-      mbar_wait(s_full(st), (j >> 1) & 1);
-      tc_fence_after();
-      if (threadIdx.x == 64 && j < 3) TRACE(3 + j);
-      // ---- the whole S row of this block into registers (one TMEM pass); keys past the end of the utterance become
-      // -inf once, so the arithmetic below is predicate-free; row maximum with four independent chains
-      float r[2][32];
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        if (c * 32 < nkeys) {
-          uint32_t t[32];
-          tmem_ld32(tS(st) + lane_sel + c * 32, t);
-#pragma unroll
-          for (int i = 0; i < 32; ++i) r[c][i] = __uint_as_float(t[i]);
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) r[c][i] = -INFINITY;
-        }
-      }
-      if (nkeys < BKV) {
-#pragma unroll
-        for (int c = 0; c < 2; ++c)
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (c * 32 + i >= nkeys) r[c][i] = -INFINITY;
-      }
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-      for (int c = 0; c < 2; ++c)
-#pragma unroll
-        for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], r[c][i]);
-      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-      const float m_blk = mx * scale_log2e;
-      // ---- running maximum: only raised when it would grow by more than 2^8 (then O in TMEM is rescaled once)
-      float alpha = 1.f;
-      if (j == 0) {
-        m_used = m_blk;
-      } else if (row_ok && m_blk - m_used > RESCALE_THRESHOLD) {
-        alpha = ex2(m_used - m_blk);
-        m_used = m_blk;
-      }
-      if (__any_sync(0xffffffffu, alpha != 1.f)) {
-        // O holds blocks 0..j-1: P_{j-1} V_{j-1} must have retired (its commit is this stage ring's "empty" barrier)
-        mbar_wait(kv_empty((j - 1) & 1), ((j - 1) >> 1) & 1);
+    int c = 0;     // blocks this warpgroup has processed (buffer / phase counter)
+    for_items(p, n_items, [&](const Item& it) {
+      if (q >= it.nq) return;
+      const int q0 = it.q_row0 + q * BQ;
+      const bool row_ok = q0 + row < it.len;
+      float m_used = -INFINITY, l_run = 0.f;
+      for (int j = 0; j < it.nb; ++j, ++c) {
+        const int buf = c & 1;
+        const uint32_t par = static_cast<uint32_t>(c >> 1) & 1u;
+        const int nkeys = min(BKV, it.len - j * BKV);
+        if ((threadIdx.x & 127) == 64) FA_TRACE(5, c, q);
+        mbar_wait(s_full(q, buf), par);
+        if ((threadIdx.x & 127) == 64) FA_TRACE(6, c, q);
         tc_fence_after();
-        l_run *= alpha;
-#pragma unroll 1
-        for (int c = 0; c < HD / 32; ++c) {
-          uint32_t o[32];
-          tmem_ld32(tO + lane_sel + c * 32, o);
+        // ---- the whole S row of this block into registers (one TMEM pass); keys past the end of the utterance become
+        // -inf once, so the arithmetic below is predicate-free
+        float r[2][32];
+        {
+          uint32_t t0[32], t1[32];
+          tmem_ld32_nowait(tS(q, buf) + lane_sel, t0);
+          if (nkeys > 32) tmem_ld32_nowait(tS(q, buf) + lane_sel + 32, t1);
+          tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-          tmem_st32(tO + lane_sel + c * 32, o);
-        }
-      }
-      // ---- p = exp2(s c - m), row sum, bf16 -> swizzled smem (A operand of the P V MMA), over the dead K block.
-      // Rows past the end of the utterance skip the arithmetic: their P rows only feed O rows that are never stored.
-      if (row_ok) {
-        float rs4[4] = {0.f, 0.f, 0.f, 0.f};
-        const int nch16 = (nkeys + 15) >> 4;  // 16-key MMA steps that will be issued
-        const uint32_t prow = sK(st) + static_cast<uint32_t>(row) * 128u;
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          if (c * 2 < nch16) {  // chunk read by at least one MMA step
-            uint32_t pk[16];
-#pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-              const float p0 = ex2(fmaf(r[c][i], scale_log2e, -m_used));      // masked keys: 2^-inf = 0
-              const float p1 = ex2(fmaf(r[c][i + 1], scale_log2e, -m_used));
-              rs4[(i >> 1) & 3] += p0 + p1;
-              pk[i >> 1] = pack_bf16x2(p0, p1);
-            }
-#pragma unroll
-            for (int g = 0; g < 4; ++g)  // 32 keys = 64 B = four 16-byte chunks of this row
-              sts128(prow + ((static_cast<uint32_t>(c * 4 + g) ^ rsw) << 4), pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+          for (int x = 0; x < 32; ++x) {
+            r[0][x] = __uint_as_float(t0[x]);
+            r[1][x] = nkeys > 32 ? __uint_as_float(t1[x]) : -INFINITY;
           }
         }
-        l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
-      }
-      fence_async_smem();
-      tc_fence_before();
-      mbar_arrive(p_full(st));
-      if (threadIdx.x == 64 && j < 3) TRACE(6 + j);
-    }
-    // ---- epilogue: O / l -> bf16 -> ctx (head merge = column offset h*128)
-    mbar_wait(o_full, 0);
-    tc_fence_after();
-    if (threadIdx.x == 64) TRACE(9);
-    const float inv = 1.f / l_run;
-    __nv_bfloat16* dst = ctx + static_cast<int64_t>(start + q0 + row) * ld_ctx + h * HD;
-#pragma unroll 1
-    for (int c = 0; c < HD / 32; ++c) {
-      uint32_t o[32];
-      tmem_ld32(tO + lane_sel + c * 32, o);
-      if (row_ok) {
+        if (nkeys < BKV) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 8) {
-          uint4 v;
-          v.x = pack_bf16x2(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv);
-          v.y = pack_bf16x2(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
-          v.z = pack_bf16x2(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv);
-          v.w = pack_bf16x2(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
-          *reinterpret_cast<uint4*>(dst + c * 32 + i) = v;
+          for (int h2 = 0; h2 < 2; ++h2)
+#pragma unroll
+            for (int x = 0; x < 32; ++x)
+              if (h2 * 32 + x >= nkeys) r[h2][x] = -INFINITY;
+        }
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int h2 = 0; h2 < 2; ++h2)
+#pragma unroll
+          for (int x = 0; x < 32; ++x) mx4[x & 3] = fmaxf(mx4[x & 3], r[h2][x]);
+        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        const float m_blk = mx * p.scale_log2e;
+        // ---- running maximum: only raised when it would grow by more than 2^8 (then O in TMEM is rescaled once)
+        float alpha = 1.f;
+        if (j == 0) {
+          m_used = m_blk;
+        } else if (row_ok && m_blk - m_used > RESCALE_THRESHOLD) {
+          alpha = ex2(m_used - m_blk);
+          m_used = m_blk;
+        }
+        if (__any_sync(0xffffffffu, alpha != 1.f)) {
+          // O_q holds blocks 0..j-1: the P V product of the block before this one (and with it every earlier one) must have
+          // retired before O is read, scaled and written back; the MMA thread only issues this block's P V after p_full.
+          mbar_wait(pv_done(q, buf ^ 1), static_cast<uint32_t>((c - 1) >> 1) & 1u);
+          tc_fence_after();
+          l_run *= alpha;
+#pragma unroll 1
+          for (int x = 0; x < HD / 32; ++x) {
+            uint32_t o[32];
+            tmem_ld32(tO(q) + lane_sel + x * 32, o);
+#pragma unroll
+            for (int y = 0; y < 32; ++y) o[y] = __float_as_uint(__uint_as_float(o[y]) * alpha);
+            tmem_st32(tO(q) + lane_sel + x * 32, o);
+          }
+        }
+        // P_q[buf] was last read by the P V product of block c - 2
+        if (c >= 2) mbar_wait(pv_done(q, buf), par ^ 1u);
+        // ---- p = exp2(s c - m), row sum, bf16 -> swizzled smem (A operand of the P V MMA).
+        // Rows past the end of the utterance skip the arithmetic: their P rows only feed O rows that are never stored.
+        if (row_ok) {
+          float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+          const int nch16 = (nkeys + 15) >> 4;  // 16-key MMA steps that will be issued
+          const uint32_t prow = sP(q, buf) + static_cast<uint32_t>(row) * 128u;
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2) {
+            if (h2 * 2 < nch16) {  // chunk read by at least one MMA step
+              uint32_t pk[16];
+#pragma unroll
+              for (int x = 0; x < 32; x += 2) {
+                const float p0 = ex2(fmaf(r[h2][x], p.scale_log2e, -m_used));      // masked keys: 2^-inf = 0
+                const float p1 = ex2(fmaf(r[h2][x + 1], p.scale_log2e, -m_used));
+                rs4[(x >> 1) & 3] += p0 + p1;
+                pk[x >> 1] = pack_bf16x2(p0, p1);
+              }
+#pragma unroll
+              for (int g = 0; g < 4; ++g)  // 32 keys = 64 B = four 16-byte chunks of this row
+                sts128(prow + ((static_cast<uint32_t>(h2 * 4 + g) ^ rsw) << 4), pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+            }
+          }
+          l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
+        }
+        fence_async_smem();
+        tc_fence_before();
+        mbar_arrive(p_full(q, buf));
+        if ((threadIdx.x & 127) == 64) FA_TRACE(7, c, q);
+      }
+      // ---- epilogue: O / l -> bf16 -> ctx (head merge = column offset h*128)
+      mbar_wait(pv_done(q, (c - 1) & 1), static_cast<uint32_t>((c - 1) >> 1) & 1u);
+      tc_fence_after();
+      if ((threadIdx.x & 127) == 64) FA_TRACE(8, c, q);
+      const float inv = 1.f / l_run;
+      __nv_bfloat16* dst = p.ctx + static_cast<long long>(it.start + q0 + row) * p.ld_ctx + it.h * HD;
+#pragma unroll 1
+      for (int x = 0; x < 2; ++x) {
+        uint32_t o0[32], o1[32];
+        tmem_ld32_nowait(tO(q) + lane_sel + x * 64, o0);
+        tmem_ld32_nowait(tO(q) + lane_sel + x * 64 + 32, o1);
+        tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int y = 0; y < 32; y += 8) {
+            uint4 v;
+            v.x = pack_bf16x2(__uint_as_float(o0[y]) * inv, __uint_as_float(o0[y + 1]) * inv);
+            v.y = pack_bf16x2(__uint_as_float(o0[y + 2]) * inv, __uint_as_float(o0[y + 3]) * inv);
+            v.z = pack_bf16x2(__uint_as_float(o0[y + 4]) * inv, __uint_as_float(o0[y + 5]) * inv);
+            v.w = pack_bf16x2(__uint_as_float(o0[y + 6]) * inv, __uint_as_float(o0[y + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + x * 64 + y) = v;
+          }
+#pragma unroll
+          for (int y = 0; y < 32; y += 8) {
+            uint4 v;
+            v.x = pack_bf16x2(__uint_as_float(o1[y]) * inv, __uint_as_float(o1[y + 1]) * inv);
+            v.y = pack_bf16x2(__uint_as_float(o1[y + 2]) * inv, __uint_as_float(o1[y + 3]) * inv);
+            v.z = pack_bf16x2(__uint_as_float(o1[y + 4]) * inv, __uint_as_float(o1[y + 5]) * inv);
+            v.w = pack_bf16x2(__uint_as_float(o1[y + 6]) * inv, __uint_as_float(o1[y + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + x * 64 + 32 + y) = v;
+          }
         }
       }
-    }
+    });
+  } else if (fsmn_on) {
+    // ===================== FSMN warps: mem[t, c] = v[t, c] + sum_k w[k, c] v[t + k - left, c] ==============================
+    // Two filler warps that share NOTHING with the attention pipeline (no barrier, no shared memory): warp f takes every
+    // other FSMN item of this CTA and streams its value rows straight from global memory - the same rows the TMA producer
+    // pulls for P V at about the same time, so one of the two reads hits L2 and V still crosses HBM once per layer - using
+    // issue slots the softmax warps leave idle.  lane = 4 adjacent channels of the head's 128 (one 8-byte load per row);
+    // rows are walked ONCE, in order: input row r is scattered into the K outputs it feeds (K independent packed FMAs per
+    // channel pair into a ring of K accumulators, slot = (r - k) mod K, so the unrolled-by-K loop indexes registers
+    // statically); output t = r - ahead has then seen its last tap and is stored.  Every output sums its taps in the order
+    // k = 0 .. K-1 with fma, the same arithmetic as the stand-alone kernel.  Rows outside the utterance enter as zeros (VLLM/...:181-201: mask, ConstantPad1d,
+    // depthwise Conv1d, + inputs, mask).
+    constexpr int K = FSMN_K;
+    const int f = warp - W_FSMN;
+    const int left = p.fsmn_left, ahead = K - 1 - left;
+    int n_fs = 0;  // FSMN items of this CTA so far
+    for_items(p, n_items, [&](const Item& it) {
+      if (!it.fsmn) return;
+      if ((n_fs++ & 1) != f) return;
+      float4 w4[K];
+      float2 a01[K], a23[K];
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        w4[k] = __ldg(reinterpret_cast<const float4*>(p.fsmn_w + static_cast<long long>(k) * dm + it.h * HD) + lane);
+        const float one = (k == left) ? 1.f : 0.f;  // "+ inputs" = tap `left` with weight + 1
+        w4[k].x += one; w4[k].y += one; w4[k].z += one; w4[k].w += one;
+        a01[k] = make_float2(0.f, 0.f);
+        a23[k] = make_float2(0.f, 0.f);
+      }
+      const char* vnext = reinterpret_cast<const char*>(p.qkv + static_cast<long long>(it.start) * p.ld_qkv + 2 * dm + it.h * HD + 4 * lane);
+      char* mrow = reinterpret_cast<char*>(p.mem + static_cast<long long>(it.start - ahead) * p.ld_mem + it.h * HD + 4 * lane);  // output of input row 0
+      const long long vstep = p.ld_qkv * 2, mstep = p.ld_mem * 2;
+      const int len = it.len, total = it.len + ahead;  // input rows walked: the utterance + `ahead` zero rows that flush the tail
+      auto load_row = [&](int r) -> uint2 {  // next value row in walking order (zeros past the utterance)
+        uint2 v = make_uint2(0u, 0u);
+        if (r < len) v = __ldg(reinterpret_cast<const uint2*>(vnext));
+        vnext += vstep;
+        return v;
+      };
+      auto row_step = [&](const uint2 raw, int x, bool store) {  // x = input row mod K (compile-time after unrolling)
+        const float2 v01 = make_float2(__uint_as_float(raw.x << 16), __uint_as_float(raw.x & 0xffff0000u));
+        const float2 v23 = make_float2(__uint_as_float(raw.y << 16), __uint_as_float(raw.y & 0xffff0000u));
+        // tap 0 opens output r + left in the slot that row r - 1 has just retired: fma(w, v, 0), no reset needed.
+        // Packed f32x2 FMAs: measured faster here than scalar FFMA (106.6 vs 114.8 us per layer at 1 h of 10 s utterances) -
+        // these warps are bound by issue slots shared with the softmax warps, not by the FMA pipe.
+        a01[x] = __ffma2_rn(make_float2(w4[0].x, w4[0].y), v01, make_float2(0.f, 0.f));
+        a23[x] = __ffma2_rn(make_float2(w4[0].z, w4[0].w), v23, make_float2(0.f, 0.f));
+#pragma unroll
+        for (int k = 1; k < K; ++k) {
+          const int sl = (x - k + K) % K;
+          a01[sl] = __ffma2_rn(make_float2(w4[k].x, w4[k].y), v01, a01[sl]);
+          a23[sl] = __ffma2_rn(make_float2(w4[k].z, w4[k].w), v23, a23[sl]);
+        }
+        const int sd = (x + 1) % K;  // output r - ahead has now seen tap K - 1
+        if (store) *reinterpret_cast<uint2*>(mrow) = make_uint2(pack_bf16x2(a01[sd].x, a01[sd].y), pack_bf16x2(a23[sd].x, a23[sd].y));
+        mrow += mstep;
+      };
+      // a ring of K rows in registers: row r + K is requested as soon as row r has been consumed, so K - 1 rows of
+      // arithmetic cover each load's latency
+      uint2 ring[K];
+#pragma unroll
+      for (int x = 0; x < K; ++x) ring[x] = load_row(x);
+      for (int rb = 0; rb < total; rb += K) {
+        if (rb >= ahead && rb + K <= total) {  // interior chunk: every row is walked and every output exists
+#pragma unroll
+          for (int x = 0; x < K; ++x) {
+            const uint2 raw = ring[x];
+            ring[x] = load_row(rb + K + x);
+            row_step(raw, x, true);
+          }
+        } else {
+#pragma unroll
+          for (int x = 0; x < K; ++x) {
+            const uint2 raw = ring[x];
+            ring[x] = load_row(rb + K + x);
+            if (rb + x < total) row_step(raw, x, rb + x >= ahead);
+          }
+        }
+      }
+    });
   }
 
-  if (threadIdx.x == 64) TRACE(10);
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == W_MMA) {
     tc_fence_after();
     tmem_dealloc<TMEM_COLS>(tmem);
   }
-  if (threadIdx.x == 0) {
-    TRACE(11);
-#ifdef FA_ATTN_TRACE
-    if (trace && cta_lin < 512) {
-      unsigned smid;
-      asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
-      trace[cta_lin * 16 + 12] = smid;
-    }
-#endif
-  }
 }
-unsigned long long* g_trace = nullptr;
 
 }  // namespace attn
 
 int attention_kv_box() { return attn::BKV; }
 
+// Fused FSMN (fsmn_w != NULL): the compiled tap count, 8-byte aligned memory rows.
+bool attention_can_fuse_fsmn(int kernel, int64_t ld_mem, const void* mem) {
+  return kernel == attn::FSMN_K && ld_mem % 4 == 0 && (reinterpret_cast<uintptr_t>(mem) & 7) == 0;
+}
+
 int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base,
-                     int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream) {
+                     int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, const float* fsmn_w, int fsmn_left,
+                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream) {
   FA_REQUIRE(ld % 8 == 0 && ld_ctx % 8 == 0, "attention: row strides must be multiples of 8 elements");
   FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0,
              "attention: qkv and ctx must be 16-byte aligned");
   FA_REQUIRE(max_len > 0 && n_utts > 0 && n_heads > 0 && n_rows > 0, "attention: empty problem");
   FA_REQUIRE(ld >= 3 * n_heads * attn::HD, "attention: qkv rows hold q|k|v of %d heads x 128", n_heads);
+  if (fsmn_w != nullptr) {
+    FA_REQUIRE(mem != nullptr && attention_can_fuse_fsmn(attn::FSMN_K, ld_mem, mem) && (reinterpret_cast<uintptr_t>(fsmn_w) & 15) == 0,
+               "attention: fused FSMN needs an 8-byte aligned bf16 memory buffer and 16-byte aligned taps");
+    FA_REQUIRE(fsmn_left >= 0 && fsmn_left < attn::FSMN_K, "attention: FSMN left pad %d outside the %d-tap window", fsmn_left, attn::FSMN_K);
+  }
   static SmemOptIn opt;
   if (int r = opt_in_smem(attn::attention_kernel, attn::SMEM_BYTES, opt)) return r;
   // Without a prebuilt map: rows = the valid packed rows only, so key/value rows past the end are zero-filled by TMA instead
@@ -347,11 +548,22 @@ int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t
   }
   CUtensorMap m;
   memcpy(&m, tm_in->bytes, sizeof(m));
-  dim3 grid(ceil_div(max_len, attn::BQ), n_heads, n_utts);
-  const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(attn::HD));
+  const int sms = sm_count();
+  // Query tiles per work item: two (K/V streamed once for both) unless that leaves SMs without an item.
+  const int tiles = ceil_div(max_len, attn::BQ);
+  int gq = tiles >= 2 ? 2 : 1;
+  if (gq == 2 && n_utts * n_heads * ceil_div(tiles, 2) < sms) gq = 1;
+  attn::Params p;
+  p.cu = cu_seqlens; p.base = base; p.n_utts = n_utts; p.n_heads = n_heads;
+  p.gq = gq; p.groups = ceil_div(tiles, gq);
+  p.ctx = ctx; p.ld_ctx = ld_ctx;
+  p.scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(attn::HD));
+  p.qkv = qkv; p.ld_qkv = ld;
+  p.fsmn_w = fsmn_w; p.fsmn_left = fsmn_left; p.mem = mem; p.ld_mem = ld_mem;
+  const int n_items = n_utts * p.groups * n_heads;
+  const int grid = n_items < sms ? n_items : sms;
   ProfScope _ps(K_ATTENTION, stream);
-  FA_CHECK_CUDA(launch_pdl(attn::attention_kernel, grid, dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, cu_seqlens, base, n_heads,
-                           ctx, ld_ctx, scale_log2e, attn::g_trace));
+  FA_CHECK_CUDA(launch_pdl(attn::attention_kernel, dim3(grid), dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, p));
   return 0;
 }
 
@@ -363,12 +575,33 @@ extern "C" int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_
   using namespace fa;
   FA_REQUIRE(qkv_dev && cu_seqlens_dev && ctx_dev, "attention: NULL pointer");
   return launch_attention(nullptr, static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, cu_seqlens_dev, n_utts, 0, max_len, n_heads,
-                          static_cast<__nv_bfloat16*>(ctx_dev), ld_ctx, n_rows, static_cast<cudaStream_t>(stream));
+                          static_cast<__nv_bfloat16*>(ctx_dev), ld_ctx, n_rows, nullptr, 0, nullptr, 0, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int fa_op_attention_fsmn(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqlens_dev, int32_t n_utts,
+                                    int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx,
+                                    const float* fsmn_w_dev, int32_t fsmn_kernel, int32_t fsmn_left, void* mem_bf16_dev, int64_t ld_mem,
+                                    fa_stream_t stream) {
+  using namespace fa;
+  FA_REQUIRE(qkv_dev && cu_seqlens_dev && ctx_dev && fsmn_w_dev && mem_bf16_dev, "attention_fsmn: NULL pointer");
+  FA_REQUIRE(attention_can_fuse_fsmn(fsmn_kernel, ld_mem, mem_bf16_dev), "attention_fsmn: only the %d-tap kernel with 8-byte aligned memory rows is fused",
+             attn::FSMN_K);
+  return launch_attention(nullptr, static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, cu_seqlens_dev, n_utts, 0, max_len, n_heads,
+                          static_cast<__nv_bfloat16*>(ctx_dev), ld_ctx, n_rows, fsmn_w_dev, fsmn_left, static_cast<__nv_bfloat16*>(mem_bf16_dev),
+                          ld_mem, static_cast<cudaStream_t>(stream));
 }
 
 #ifdef FA_ATTN_TRACE
-// debug only (not in the public header): device buffer of 512 x 16 u64 receiving per-CTA %globaltimer stamps
-extern "C" __attribute__((visibility("default"))) void fa_debug_attention_trace(void* buf) {
-  fa::attn::g_trace = static_cast<unsigned long long*>(buf);
+// profiling builds only: copies the trace of CTA 0 to the host and clears it; returns the number of events
+extern "C" __attribute__((visibility("default"))) int fa_debug_attention_trace(unsigned long long* dst_host, int cap) {
+  unsigned int n = 0;
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(&n, fa::attn::g_trace_n, sizeof(n));
+  if (n > (1u << 16)) n = 1u << 16;
+  if (static_cast<int>(n) > cap) n = cap;
+  cudaMemcpyFromSymbol(dst_host, fa::attn::g_trace, n * sizeof(unsigned long long));
+  const unsigned int zero = 0;
+  cudaMemcpyToSymbol(fa::attn::g_trace_n, &zero, sizeof(zero));
+  return static_cast<int>(n);
 }
 #endif

@@ -115,10 +115,14 @@ int launch_embed_layernorm(const float* x, int in_tmax, const float* inv_ts, con
                            float scale, const float* g, const float* b, __nv_bfloat16* y, int M, int D, cudaStream_t stream);
 int launch_fsmn(const __nv_bfloat16* qkv, int64_t ld, int v_col, const float* w, const int32_t* cu, int n_utts, int base,
                 void* mem, int out_bf16, int64_t ld_out, int M, int D, int kernel, int left_pad, cudaStream_t stream);
-// tm: prebuilt tensor map over qkv (box = attention_kv_box() rows x 64 columns), or NULL to encode one over n_rows rows here
+// tm: prebuilt tensor map over qkv (box = attention_kv_box() rows x 64 columns), or NULL to encode one over n_rows rows here.
+// fsmn_w != NULL: the FSMN memory of the same value rows (f32 taps [11, n_heads * 128] tap-major, `fsmn_left` rows of left
+// context) is computed inside the attention kernel and written as bf16 to mem[row, h * 128 + c] (row stride ld_mem).
 int attention_kv_box();
+bool attention_can_fuse_fsmn(int kernel, int64_t ld_mem, const void* mem);
 int launch_attention(const TensorMap2D* tm, const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base,
-                     int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, cudaStream_t stream);
+                     int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, const float* fsmn_w, int fsmn_left,
+                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream);
 // dst[i] = cu[min(i, n_utts)], i = 0..n_pad: cu_seqlens copied to a fixed address, padded with the total row count
 int launch_pad_cu(const int32_t* cu, int n_utts, int32_t* dst, int n_pad, cudaStream_t stream);
 int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, int dst_bf16, const int32_t* cu,

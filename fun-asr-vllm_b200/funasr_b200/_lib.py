@@ -75,6 +75,7 @@ PROTOTYPES = {
     "fa_op_fsmn": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, i32, i32, i32, i32, vp]),
     "fa_op_fsmn_bf16": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, i64, i32, i32, i32, i32, vp]),
     "fa_op_attention": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, vp, i64, vp]),
+    "fa_op_attention_fsmn": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, vp, i64, vp, i32, i32, vp, i64, vp]),
 }
 
 PROFILE_KINDS = ("frontend", "gemm", "attention", "layernorm", "fsmn", "repack", "splice")

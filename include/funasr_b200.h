@@ -288,6 +288,13 @@ int fa_op_fsmn_bf16(const void* qkv_dev, int64_t ld_qkv, int32_t v_col, const fl
 /* ctx[M, H*128] bf16 = softmax(q k^T / sqrt(128)) v per utterance and head; q|k|v packed in the n_rows (= M) qkv rows */
 int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqlens_dev, int32_t n_utts,
                     int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx, fa_stream_t stream);
+/* attention and the FSMN memory of the same value rows in ONE kernel (the plan's form): ctx as above, and
+ * mem[r, h*128 + c] bf16 (row stride ld_mem) = v + depthwise_conv_time(v), w f32 [11, H*128] tap-major, `fsmn_left` rows of
+ * left context.  Only the model's 11-tap kernel is fused (FA_ERR_INVALID otherwise).  VLLM/...:181-201,222-252 */
+int fa_op_attention_fsmn(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqlens_dev, int32_t n_utts,
+                         int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx,
+                         const float* fsmn_w_dev, int32_t fsmn_kernel, int32_t fsmn_left, void* mem_bf16_dev,
+                         int64_t ld_mem, fa_stream_t stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

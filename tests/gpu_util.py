@@ -113,6 +113,18 @@ def op_attention(qkv_bf16, cu, n_heads):
     return ctx
 
 
+def op_attention_fsmn(qkv_bf16, w, cu, n_heads, left):
+    """ctx|mem [M, 2*dm] bf16 from the fused kernel (the plan's layout: memory beside the context)."""
+    M = qkv_bf16.shape[0]
+    dm = n_heads * 128
+    cm = torch.zeros((M, 2 * dm), dtype=torch.bfloat16, device="cuda")
+    cu_d = dev(cu)
+    _lib.check(lib().fa_op_attention_fsmn(qkv_bf16.data_ptr(), qkv_bf16.stride(0), cu_d.data_ptr(), len(cu) - 1,
+                                          int(np.diff(cu).max()), n_heads, M, cm.data_ptr(), 2 * dm, w.data_ptr(), w.shape[0], left,
+                                          cm.data_ptr() + 2 * dm, 2 * dm, stream()))
+    return cm
+
+
 def rel_rms(got, want):
     got, want = got.double().cpu(), want.double().cpu()
     return float((got - want).pow(2).mean().sqrt() / want.pow(2).mean().sqrt().clamp_min(1e-30))

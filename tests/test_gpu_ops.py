@@ -239,6 +239,53 @@ def test_attention_running_max_rescale_path(U):
     assert U.rel_rms(got.float(), want) < 1.5e-2
 
 
+def _attn_fsmn_reference(qkv, cu, H, w, left):
+    dm, K = H * 128, w.shape[1]
+    ctx, mem = [], []
+    for b in range(len(cu) - 1):
+        x = qkv[cu[b]:cu[b + 1]].float()
+        q, k, v = (x[:, i * dm:(i + 1) * dm].reshape(-1, H, 128).transpose(0, 1) for i in range(3))
+        p = torch.softmax((q * 128 ** -0.5) @ k.transpose(1, 2), dim=-1)
+        ctx.append((p @ v).transpose(0, 1).reshape(-1, dm))
+        vb = x[:, 2 * dm:].t()[None]
+        y = torch.nn.functional.conv1d(torch.nn.functional.pad(vb, (left, K - 1 - left)), w[:, None, :], groups=dm)
+        mem.append((y + vb)[0].t())
+    return torch.cat(ctx), torch.cat(mem)
+
+
+@pytest.mark.parametrize("lens,H,left", [([167] * 3, 4, 5), ([1, 64, 65, 128, 500, 17, 2, 63, 129], 4, 5), ([667, 1, 300], 4, 7),
+                                         ([167, 30], 8, 5), ([167] * 160, 4, 5), ([3000, 256, 257], 4, 5)])
+def test_attention_fsmn_fused(U, lens, H, left):
+    """One kernel: context AND the FSMN memory of the same value rows (VLLM/...:181-201 + 222-252).  Covers 1-row utterances,
+    block-edge lengths (63/64/65/128/129), utterances longer than one work item's two query tiles (groups > 1: only group 0
+    computes the memory), more work items than SMs (the persistent loop, barrier phases carried across items) and the adaptor's
+    8 heads.  The memory must equal the stand-alone FSMN kernel bit for bit (same f32 tap order, one rounding)."""
+    g = torch.Generator().manual_seed(sum(lens) % 9973 + H)
+    cu = U.cu_of(lens)
+    M, dm, K = int(cu[-1]), H * 128, 11
+    qkv = bf(torch.randn(M, 3 * dm, generator=g))
+    w = torch.randn(dm, K, generator=g) / math.sqrt(K)
+    want_ctx, want_mem = _attn_fsmn_reference(qkv, cu, H, w, left)
+    wt = w.t().contiguous().cuda()
+    cm = U.op_attention_fsmn(qkv.cuda(), wt, cu, H, left)
+    got_ctx, got_mem = cm[:, :dm].float().cpu(), cm[:, dm:].float().cpu()
+    assert (got_ctx - want_ctx).abs().max().item() < 3e-2
+    assert U.rel_rms(got_ctx, want_ctx) < 1e-2
+    assert (got_mem - want_mem).abs().max().item() < 4e-2  # bf16 rounding of |mem| <~ 8
+    assert U.rel_rms(got_mem, want_mem) < 3e-3
+    alone = U.op_fsmn_bf16(qkv.cuda(), 2 * dm, wt, cu, dm, K, left).cpu()
+    assert torch.equal(cm[:, dm:].cpu(), alone[:, dm:])
+    assert torch.equal(cm[:, :dm].cpu(), U.op_attention(qkv.cuda(), cu, H).cpu())  # the FSMN warps do not perturb attention
+
+
+def test_attention_fsmn_rejects_other_kernels(U):
+    from funasr_b200 import FunASRB200Error
+
+    qkv = torch.zeros(64, 3 * 512, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(FunASRB200Error, match="11-tap"):
+        U.op_attention_fsmn(qkv, torch.zeros(9, 512, device="cuda"), U.cu_of([64]), 4, 4)
+
+
 def test_errors_are_reported_not_swallowed(U):
     from funasr_b200 import FunASRB200Error
 
