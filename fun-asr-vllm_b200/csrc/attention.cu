@@ -74,11 +74,11 @@ struct Params {
   int fsmn_left;
   __nv_bfloat16* mem;   // bf16 [rows, ld_mem], column h * 128 + c
   long long ld_mem;
+  int fsmn_rows, fsmn_chunks;  // FSMN work unit = fsmn_rows output rows of one (utterance, head); chunks = ceil(max_len / rows)
 };
 
 struct Item {  // decoded identically by every warp role
   int h, start, len, q_row0, nq, nb;
-  bool fsmn;
 };
 
 // cu_seqlens[b], cu_seqlens[b + 1] of work item i (an input of the forward call, not a predecessor's output).  Every role
@@ -100,7 +100,6 @@ __device__ __forceinline__ bool decode_item(const Params& p, int i, int c0, int 
   if (it.q_row0 >= it.len) return false;
   it.nq = min(p.gq, (it.len - it.q_row0 + BQ - 1) / BQ);
   it.nb = (it.len + BKV - 1) / BKV;
-  it.fsmn = p.fsmn_w != nullptr && g == 0;  // the first group of an utterance streams every V block: it owns the FSMN rows
   return true;
 }
 
@@ -428,48 +427,54 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
     });
   } else if (fsmn_on) {
     // ===================== FSMN warps: mem[t, c] = v[t, c] + sum_k w[k, c] v[t + k - left, c] ==============================
-    // Two filler warps that share NOTHING with the attention pipeline (no barrier, no shared memory): warp f takes every
-    // other FSMN item of this CTA and streams its value rows straight from global memory - the same rows the TMA producer
-    // pulls for P V at about the same time, so one of the two reads hits L2 and V still crosses HBM once per layer - using
-    // issue slots the softmax warps leave idle.  lane = 4 adjacent channels of the head's 128 (one 8-byte load per row);
-    // rows are walked ONCE, in order: input row r is scattered into the K outputs it feeds (K independent packed FMAs per
-    // channel pair into a ring of K accumulators, slot = (r - k) mod K, so the unrolled-by-K loop indexes registers
-    // statically); output t = r - ahead has then seen its last tap and is stored.  Every output sums its taps in the order
-    // k = 0 .. K-1 with fma, the same arithmetic as the stand-alone kernel.  Rows outside the utterance enter as zeros (VLLM/...:181-201: mask, ConstantPad1d,
-    // depthwise Conv1d, + inputs, mask).
+    // Two filler warps per CTA that share NOTHING with the attention pipeline (no barrier, no shared memory): they stream
+    // value rows straight from global memory - the same rows the TMA producers pull for P V at about the same time, so one
+    // of the two reads hits L2 and V still crosses HBM once per layer - using issue slots the softmax warps leave idle.
+    // lane = 4 adjacent channels of the head's 128 (one 8-byte load per row); a unit's rows are walked ONCE, in order: an
+    // input row is scattered into the K outputs it feeds (K independent packed FMAs per channel pair into a ring of K
+    // accumulators, slot = (walk index - k) mod K, so the unrolled-by-K loop indexes registers statically); the output that
+    // has then seen its last tap is stored.  Every output sums its taps in the order k = 0 .. K-1 with fma, the same
+    // arithmetic as the stand-alone kernel.  Rows outside the utterance enter as zeros (VLLM/...:181-201: mask,
+    // ConstantPad1d, depthwise Conv1d, + inputs, mask).
     constexpr int K = FSMN_K;
     const int f = warp - W_FSMN;
-    const int left = p.fsmn_left, ahead = K - 1 - left;
-    int n_fs = 0;  // FSMN items of this CTA so far
-    for_items(p, n_items, [&](const Item& it) {
-      if (!it.fsmn) return;
-      if ((n_fs++ & 1) != f) return;
+    const int left = p.fsmn_left;
+    // FSMN work units are independent of the attention work items: (utterance, head, chunk of fsmn_rows output rows), dealt
+    // round-robin to every FSMN warp of the grid, so that a small batch still spreads over all of them.
+    const int n_units = p.n_utts * p.n_heads * p.fsmn_chunks;
+    for (int u = blockIdx.x * FSMN_WARPS + f; u < n_units; u += gridDim.x * FSMN_WARPS) {
+      const int h = u % p.n_heads, c = (u / p.n_heads) % p.fsmn_chunks, b = u / (p.n_heads * p.fsmn_chunks);
+      const int c0 = __ldg(p.cu + b), c1 = __ldg(p.cu + b + 1);
+      const int start = c0 - p.base, len = c1 - c0;
+      const int t0 = c * p.fsmn_rows;  // output rows [t0, t1) of the utterance
+      if (t0 >= len) continue;
+      const int t1 = min(len, t0 + p.fsmn_rows);
       float4 w4[K];
       float2 a01[K], a23[K];
 #pragma unroll
       for (int k = 0; k < K; ++k) {
-        w4[k] = __ldg(reinterpret_cast<const float4*>(p.fsmn_w + static_cast<long long>(k) * dm + it.h * HD) + lane);
+        w4[k] = __ldg(reinterpret_cast<const float4*>(p.fsmn_w + static_cast<long long>(k) * dm + h * HD) + lane);
         const float one = (k == left) ? 1.f : 0.f;  // "+ inputs" = tap `left` with weight + 1
         w4[k].x += one; w4[k].y += one; w4[k].z += one; w4[k].w += one;
         a01[k] = make_float2(0.f, 0.f);
         a23[k] = make_float2(0.f, 0.f);
       }
-      const char* vnext = reinterpret_cast<const char*>(p.qkv + static_cast<long long>(it.start) * p.ld_qkv + 2 * dm + it.h * HD + 4 * lane);
-      char* mrow = reinterpret_cast<char*>(p.mem + static_cast<long long>(it.start - ahead) * p.ld_mem + it.h * HD + 4 * lane);  // output of input row 0
+      // walk i = 0 .. total-1 reads input row t0 - left + i and completes output row t0 + i - (K - 1)
+      const int r0 = t0 - left, total = (t1 - t0) + K - 1;
+      const char* vnext = reinterpret_cast<const char*>(p.qkv + static_cast<long long>(start + r0) * p.ld_qkv + 2 * dm + h * HD + 4 * lane);
+      char* mrow = reinterpret_cast<char*>(p.mem + static_cast<long long>(start + t0 - (K - 1)) * p.ld_mem + h * HD + 4 * lane);
       const long long vstep = p.ld_qkv * 2, mstep = p.ld_mem * 2;
-      const int len = it.len, total = it.len + ahead;  // input rows walked: the utterance + `ahead` zero rows that flush the tail
-      auto load_row = [&](int r) -> uint2 {  // next value row in walking order (zeros past the utterance)
+      auto load_row = [&](int i) -> uint2 {  // next value row in walking order (zeros outside the utterance)
         uint2 v = make_uint2(0u, 0u);
-        if (r < len) v = __ldg(reinterpret_cast<const uint2*>(vnext));
+        if (static_cast<unsigned>(r0 + i) < static_cast<unsigned>(len)) v = __ldg(reinterpret_cast<const uint2*>(vnext));
         vnext += vstep;
         return v;
       };
-      auto row_step = [&](const uint2 raw, int x, bool store) {  // x = input row mod K (compile-time after unrolling)
+      auto row_step = [&](const uint2 raw, int x, bool store) {  // x = walk index mod K (compile-time after unrolling)
         const float2 v01 = make_float2(__uint_as_float(raw.x << 16), __uint_as_float(raw.x & 0xffff0000u));
         const float2 v23 = make_float2(__uint_as_float(raw.y << 16), __uint_as_float(raw.y & 0xffff0000u));
-        // tap 0 opens output r + left in the slot that row r - 1 has just retired: fma(w, v, 0), no reset needed.
-        // Packed f32x2 FMAs: measured faster here than scalar FFMA (106.6 vs 114.8 us per layer at 1 h of 10 s utterances) -
-        // these warps are bound by issue slots shared with the softmax warps, not by the FMA pipe.
+        // tap 0 opens a new output in the slot the previous row has just retired: fma(w, v, 0), no reset needed.
+        // Packed f32x2 FMAs: measured faster here than scalar FFMA (106.6 vs 114.8 us per layer at 1 h of 10 s utterances).
         a01[x] = __ffma2_rn(make_float2(w4[0].x, w4[0].y), v01, make_float2(0.f, 0.f));
         a23[x] = __ffma2_rn(make_float2(w4[0].z, w4[0].w), v23, make_float2(0.f, 0.f));
 #pragma unroll
@@ -478,33 +483,33 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
           a01[sl] = __ffma2_rn(make_float2(w4[k].x, w4[k].y), v01, a01[sl]);
           a23[sl] = __ffma2_rn(make_float2(w4[k].z, w4[k].w), v23, a23[sl]);
         }
-        const int sd = (x + 1) % K;  // output r - ahead has now seen tap K - 1
+        const int sd = (x + 1) % K;  // this output has now seen tap K - 1
         if (store) *reinterpret_cast<uint2*>(mrow) = make_uint2(pack_bf16x2(a01[sd].x, a01[sd].y), pack_bf16x2(a23[sd].x, a23[sd].y));
         mrow += mstep;
       };
-      // a ring of K rows in registers: row r + K is requested as soon as row r has been consumed, so K - 1 rows of
+      // a ring of K rows in registers: row i + K is requested as soon as row i has been consumed, so K - 1 rows of
       // arithmetic cover each load's latency
       uint2 ring[K];
 #pragma unroll
       for (int x = 0; x < K; ++x) ring[x] = load_row(x);
-      for (int rb = 0; rb < total; rb += K) {
-        if (rb >= ahead && rb + K <= total) {  // interior chunk: every row is walked and every output exists
+      for (int ib = 0; ib < total; ib += K) {
+        if (ib >= K - 1 && ib + K <= total) {  // interior: every row is walked and every output exists
 #pragma unroll
           for (int x = 0; x < K; ++x) {
             const uint2 raw = ring[x];
-            ring[x] = load_row(rb + K + x);
+            ring[x] = load_row(ib + K + x);
             row_step(raw, x, true);
           }
         } else {
 #pragma unroll
           for (int x = 0; x < K; ++x) {
             const uint2 raw = ring[x];
-            ring[x] = load_row(rb + K + x);
-            if (rb + x < total) row_step(raw, x, rb + x >= ahead);
+            ring[x] = load_row(ib + K + x);
+            if (ib + x < total) row_step(raw, x, ib + x >= K - 1);
           }
         }
       }
-    });
+    }
   }
 
   tc_fence_before();
@@ -562,6 +567,15 @@ int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t
   p.fsmn_w = fsmn_w; p.fsmn_left = fsmn_left; p.mem = mem; p.ld_mem = ld_mem;
   const int n_items = n_utts * p.groups * n_heads;
   const int grid = n_items < sms ? n_items : sms;
+  // FSMN units (each chunk re-reads K - 1 halo rows, so no smaller than 32 rows): whole utterances when every FSMN warp of
+  // the grid gets several; one chunk per warp when there are at most half as many (utterance, head) pairs as warps;
+  // otherwise about four chunks per warp, which evens out utterances of different lengths.
+  const int fs_warps = grid * attn::FSMN_WARPS, fs_items = n_utts * n_heads;
+  int fs_chunks = 1;
+  if (2 * fs_items <= fs_warps) fs_chunks = fs_warps / fs_items;
+  else if (fs_items < 4 * fs_warps) fs_chunks = ceil_div(4 * fs_warps, fs_items);
+  p.fsmn_rows = ceil_div(max_len, fs_chunks) < 32 ? 32 : ceil_div(max_len, fs_chunks);
+  p.fsmn_chunks = ceil_div(max_len, p.fsmn_rows);
   ProfScope _ps(K_ATTENTION, stream);
   FA_CHECK_CUDA(launch_pdl(attn::attention_kernel, dim3(grid), dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, p));
   return 0;
