@@ -280,7 +280,19 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
         from funasr_b200.sharding import bind_to_gpu_numa
 
         numa_cores = bind_to_gpu_numa(local_rank)  # pinned staging buffers on the GPU's own NUMA node
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on fd 1 when the communicator comes up; stdout carries ONE JSON line, so the banner
+        # goes to stderr
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     def barrier():
         if world > 1:

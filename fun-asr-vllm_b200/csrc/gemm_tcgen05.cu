@@ -157,6 +157,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if constexpr (CTAS == 2) cluster_sync(); else __syncthreads();  // barriers of BOTH CTAs are initialised past this point
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  // The weight tiles of this CTA's first k-blocks do not depend on the previous kernel: their TMA loads go out BEFORE the
+  // grid dependency resolves, so in a PDL chain (and in a replayed graph) the operand ring is already half full when the
+  // activations become visible.  Small batches are a chain of ~10 us kernels; this takes a load round trip off each.
+  const int pre_kb = (cl < num_tiles) ? (num_kb < C::STAGES ? num_kb : C::STAGES) : 0;
+  if (warp == 0 && lane == 0) {
+    const int tn = cl % p.tiles_n;
+    for (int kb = 0; kb < pre_kb; ++kb) {
+      const uint32_t sb = smem_base + kb * C::STAGE_BYTES + C::A_BYTES;
+      if constexpr (CTAS == 2) {
+        if (rank == 0) mbar_expect_tx(full_bar(kb), 2 * C::STAGE_BYTES);
+        tma_load_2d_pair(sb, &tmap_b, mapa(full_bar(kb), 0), kb * BK, tn * BN + static_cast<int>(rank) * (BN / 2));
+      } else {
+        mbar_expect_tx(full_bar(kb), C::STAGE_BYTES);
+        tma_load_2d(sb, &tmap_b, full_bar(kb), kb * BK, tn * BN);
+      }
+    }
+  }
   pdl_wait();  // prologue done (weights / bias are constants); activations of the previous kernel are visible from here
 
   if (warp == 0) {
@@ -172,7 +189,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
           const uint32_t sb = sa + C::A_BYTES;
-          if constexpr (CTAS == 2) {
+          if (tile == cl && kb < pre_kb) {  // weights already under way (above): only the activations are missing
+            if constexpr (CTAS == 2) tma_load_2d_pair(sa, &tmap_a, mapa(full_bar(stage), 0), kb * BK, p.row0 + tile_row(tm));
+            else tma_load_2d(sa, &tmap_a, full_bar(stage), kb * BK, p.row0 + tm * BM);
+          } else if constexpr (CTAS == 2) {
             // both CTAs' bytes are counted on the LEADER's full barrier (the only one the MMA warp waits on)
             const uint32_t lead_bar = mapa(full_bar(stage), 0);
             if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
