@@ -60,9 +60,6 @@ struct __align__(16) Smem {
   float power[SLOTS][264];
   float window[FRAME_LEN];
   float mel_w[MAX_TAPS];
-  int mel_start[NMEL];
-  int mel_count[NMEL];
-  int mel_woff[NMEL];
 };
 
 typedef double2 cplx;
@@ -104,16 +101,35 @@ template <int MODE>  // 0: LFR + CMVN rows, 1: raw log-mel rows
 __global__ void __launch_bounds__(THREADS, 2)
 fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, const int64_t* __restrict__ wav_start,
              const int32_t* __restrict__ wav_len, const int32_t* __restrict__ out_row, const int32_t* __restrict__ tile_off, int n_utts,
-             const float* __restrict__ cmvn, float* __restrict__ out, int64_t out_ld, float upscale, float preemph,
+             int n_tiles, const float* __restrict__ cmvn, float* __restrict__ out, int64_t out_ld, float upscale, float preemph,
              float log_floor) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15;
   pdl_launch_dependents();  // the first kernel of the path: its successor's prologue may overlap it
 
+  // ---- tables into shared memory, once per CTA (MODE 0 CTAs are persistent over tiles)
+  for (int i = tid; i < FRAME_LEN; i += THREADS) s.window[i] = __ldg(&tab->window[i]);
+  for (int i = tid; i < 130; i += THREADS) s.tw512[i] = tab->tw512[i];
+  for (int i = tid; i < 256; i += THREADS) (&s.tw256[0][0])[i] = (&tab->tw256[0][0])[i];
+  for (int i = tid; i < MAX_TAPS / 4; i += THREADS)
+    reinterpret_cast<float4*>(s.mel_w)[i] = __ldg(reinterpret_cast<const float4*>(tab->mel_w) + i);
+  for (int i = tid; i < SLOTS * 8; i += THREADS) s.power[i >> 3][256 + (i & 7)] = 0.f;  // read (x 0) by the padded mel taps
+  // this lane's five mel bins (hl, hl + 16, ..., hl + 64): first FFT bin, taps padded to a multiple of 4, weight offset
+  int mel_st[NMEL / 16], mel_n4[NMEL / 16], mel_wo[NMEL / 16];
+#pragma unroll
+  for (int i = 0; i < NMEL / 16; ++i) {
+    mel_st[i] = __ldg(&tab->mel_start[hl + 16 * i]);
+    mel_n4[i] = (__ldg(&tab->mel_count[hl + 16 * i]) + 3) >> 2;
+    mel_wo[i] = __ldg(&tab->mel_woff[hl + 16 * i]);
+  }
+
+  const int first_tile = MODE == 0 ? static_cast<int>(blockIdx.x) : 0;
+  const int tile_step = MODE == 0 ? static_cast<int>(gridDim.x) : 1;
+  const int tile_end = MODE == 0 ? n_tiles : 1;
+  for (int id = first_tile; id < tile_end; id += tile_step) {
   int b, ti;
   if (MODE == 0) {
-    const int id = blockIdx.x;
     int lo = 0, hi = n_utts;
     while (hi - lo > 1) {
       int mid = (lo + hi) >> 1;
@@ -127,36 +143,35 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
   }
   const int64_t w0 = wav_start[b];
   const int n = wav_len[b];
-  if (n < FRAME_LEN) return;
+  if (n < FRAME_LEN) continue;
   const int m = 1 + (n - FRAME_LEN) / SHIFT;  // TA:62-66 snip_edges
   int i0 = 0, i1 = 0, f_lo, f_hi;
   if (MODE == 0) {
     const int T = (m + LFR_N - 1) / LFR_N;  // VLLM:43
     i0 = ti * TILE_ROWS;
-    if (i0 >= T) return;
+    if (i0 >= T) continue;
     i1 = min(i0 + TILE_ROWS, T);
     f_lo = max(LFR_N * i0 - LFR_LEFT, 0);
     f_hi = min(LFR_N * (i1 - 1) + LFR_M - 1 - LFR_LEFT, m - 1);
   } else {
     f_lo = ti * RAW_TILE_FRAMES;
-    if (f_lo >= m) return;
+    if (f_lo >= m) continue;
     f_hi = min(f_lo + RAW_TILE_FRAMES - 1, m - 1);
   }
   const int nF = f_hi - f_lo + 1;
   const int nS = (nF - 1) * SHIFT + FRAME_LEN;
 
-  // ---- stage PCM (x upscale, VLLM:140-141) and tables into shared memory
+  // ---- stage PCM (x upscale, VLLM:140-141) into shared memory; nS is a multiple of 8
   {
     const float* src = wav + w0 + static_cast<int64_t>(f_lo) * SHIFT;
-    for (int i = tid; i < nS; i += THREADS) s.samples[i] = __ldg(src + i) * upscale;
-    for (int i = tid; i < FRAME_LEN; i += THREADS) s.window[i] = __ldg(&tab->window[i]);
-    for (int i = tid; i < 130; i += THREADS) s.tw512[i] = tab->tw512[i];
-    for (int i = tid; i < 256; i += THREADS) (&s.tw256[0][0])[i] = (&tab->tw256[0][0])[i];
-    for (int i = tid; i < MAX_TAPS; i += THREADS) s.mel_w[i] = __ldg(&tab->mel_w[i]);
-    for (int i = tid; i < NMEL; i += THREADS) {
-      s.mel_start[i] = __ldg(&tab->mel_start[i]);
-      s.mel_count[i] = __ldg(&tab->mel_count[i]);
-      s.mel_woff[i] = __ldg(&tab->mel_woff[i]);
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+      for (int i = tid; i < nS / 4; i += THREADS) {
+        float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
+        v.x *= upscale; v.y *= upscale; v.z *= upscale; v.w *= upscale;
+        reinterpret_cast<float4*>(s.samples)[i] = v;
+      }
+    } else {
+      for (int i = tid; i < nS; i += THREADS) s.samples[i] = __ldg(src + i) * upscale;
     }
   }
   __syncthreads();
@@ -253,14 +268,21 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     __syncwarp();
 
     // ---- sparse mel projection + log (TA:621-633); bins hl, hl+16, ..., hl+64
+    // (each band is padded to a multiple of four taps with zero weights: one 16-byte weight load per four FMAs, same
+    // summation order)
 #pragma unroll
     for (int i = 0; i < NMEL / 16; ++i) {
-      const int bin = hl + 16 * i;
-      const int st = s.mel_start[bin], cnt = s.mel_count[bin];
-      const float* wv = s.mel_w + s.mel_woff[bin];
+      const float4* wv = reinterpret_cast<const float4*>(s.mel_w + mel_wo[i]);
+      const float* pw = power + mel_st[i];
       float acc = 0.f;
-      for (int j = 0; j < cnt; ++j) acc = fmaf(wv[j], power[st + j], acc);
-      if (active) s.logmel[f][bin] = logf(fmaxf(acc, log_floor));
+      for (int j = 0; j < mel_n4[i]; ++j) {
+        const float4 w = wv[j];
+        acc = fmaf(w.x, pw[4 * j], acc);
+        acc = fmaf(w.y, pw[4 * j + 1], acc);
+        acc = fmaf(w.z, pw[4 * j + 2], acc);
+        acc = fmaf(w.w, pw[4 * j + 3], acc);
+      }
+      if (active) s.logmel[f][hl + 16 * i] = logf(fmaxf(acc, log_floor));
     }
     __syncwarp();
   }
@@ -293,6 +315,8 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
       *reinterpret_cast<float4*>(obase + static_cast<int64_t>(r) * out_ld + c4 * 4) =
           *reinterpret_cast<const float4*>(&s.logmel[r][c4 * 4]);
     }
+  }
+  __syncthreads();  // samples / logmel are rewritten by the next tile
   }
 }
 
@@ -334,12 +358,13 @@ extern "C" int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float*
         last = k;
       }
     const int cnt = first < 0 ? 0 : last - first + 1;
-    FA_REQUIRE(off + cnt <= MAX_TAPS, "mel filterbank has more than %d taps", MAX_TAPS);
+    const int cnt4 = (cnt + 3) & ~3;  // the kernel reads each band four taps at a time; the padding weights are zero
+    FA_REQUIRE(off + cnt4 <= MAX_TAPS, "mel filterbank has more than %d taps", MAX_TAPS);
     t->mel_start[b] = first < 0 ? 0 : first;
     t->mel_count[b] = cnt;
     t->mel_woff[b] = off;
     for (int j = 0; j < cnt; ++j) t->mel_w[off + j] = row[first + j];
-    off += cnt;
+    off += cnt4;
   }
   return 0;
 }
@@ -359,8 +384,10 @@ extern "C" int fa_frontend_forward(const fa_frontend_cfg* cfg, const void* table
   static SmemOptIn opt0;
   if (int r = opt_in_smem(fbank_kernel<0>, (int)sizeof(Smem), opt0)) return r;
   ProfScope _ps(K_FRONTEND, static_cast<cudaStream_t>(stream));
-  fbank_kernel<0><<<n_tiles, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, tile_off_dev, n_utts,
+  // persistent CTAs (two per SM: registers and shared memory), tiles dealt round-robin: the tables are staged once per CTA
+  const int grid = n_tiles < 2 * sm_count() ? n_tiles : 2 * sm_count();
+  fbank_kernel<0><<<grid, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, tile_off_dev, n_utts, n_tiles,
       cmvn_dev,
       out_dev, out_ld, cfg->upscale, cfg->preemph, cfg->log_floor);
   FA_CHECK_LAUNCH();
@@ -380,7 +407,7 @@ extern "C" int fa_frontend_logmel(const fa_frontend_cfg* cfg, const void* tables
   dim3 grid(ceil_div(max_frames, RAW_TILE_FRAMES), n_utts);
   ProfScope _ps(K_FRONTEND, static_cast<cudaStream_t>(stream));
   fbank_kernel<1><<<grid, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, nullptr, n_utts, nullptr,
+      static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, nullptr, n_utts, 1, nullptr,
       out_dev,
       out_ld, cfg->upscale, cfg->preemph, cfg->log_floor);
   FA_CHECK_LAUNCH();
