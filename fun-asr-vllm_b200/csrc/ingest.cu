@@ -16,12 +16,41 @@ namespace ingest {
 
 constexpr int THREADS = 256;
 
+// One mono f32 sample from interleaved raw PCM frame `frame` (FA_PCM_*): every channel is converted to f32 (int16: exact,
+// f64: round to nearest = torch's .float(), /root/reference/infer.py:321-324), scaled (1/32768 reproduces what soundfile
+// hands librosa.load for 16-bit files, infer_kaldidata.py:101), the channels are summed in order and divided by their count
+// (librosa.to_mono = np.mean over the channel axis).
+__device__ __forceinline__ float load_pcm(const void* __restrict__ in, int fmt, int ch, float scale, int64_t frame) {
+  float s = 0.f;
+  for (int c = 0; c < ch; ++c) {
+    const int64_t i = frame * ch + c;
+    float v;
+    if (fmt == FA_PCM_S16) v = static_cast<float>(__ldg(static_cast<const int16_t*>(in) + i));
+    else if (fmt == FA_PCM_F64) v = __double2float_rn(__ldg(static_cast<const double*>(in) + i));
+    else v = __ldg(static_cast<const float*>(in) + i);
+    v = __fmul_rn(v, scale);
+    s = c == 0 ? v : __fadd_rn(s, v);
+  }
+  return ch > 1 ? __fdiv_rn(s, static_cast<float>(ch)) : s;
+}
+
+// out[out_start[b] + s] = mono f32 of frame in_start[b] + s, s < in_len[b]   (grid: x = blocks of frames, y = utterance)
+__global__ void __launch_bounds__(THREADS)
+pcm_to_mono_kernel(const void* __restrict__ in, int fmt, int ch, float scale, const int64_t* __restrict__ in_start,
+                   const int32_t* __restrict__ in_len, float* __restrict__ out, const int64_t* __restrict__ out_start) {
+  const int b = blockIdx.y;
+  const int L = in_len[b];
+  const int64_t i0 = in_start[b];
+  float* dst = out + out_start[b];
+  for (int s = blockIdx.x * THREADS + threadIdx.x; s < L; s += gridDim.x * THREADS) dst[s] = load_pcm(in, fmt, ch, scale, i0 + s);
+}
+
 // Register blocking: a lane owns J phases x F frames (frames 32 apart), so every 4 taps cost J 16-byte broadcast loads of the
 // (row-padded) table and 4*F shared-memory loads for 16*J*F/4 FMAs.  J*F = 8; J follows the number of phases (new_freq).
 template <int J, int F>
 __global__ void __launch_bounds__(THREADS)
-resample_kernel(const float* __restrict__ in, const int64_t* __restrict__ in_start, const int32_t* __restrict__ in_len,
-                const float* __restrict__ kern, int orig, int nw, int width, int Kp, int fw, float* __restrict__ out,
+resample_kernel(const void* __restrict__ in, int fmt, int ch, float scale, const int64_t* __restrict__ in_start,
+                const int32_t* __restrict__ in_len, const float* __restrict__ kern, int orig, int nw, int width, int Kp, int fw, float* __restrict__ out,
                 const int64_t* __restrict__ out_start, const int32_t* __restrict__ tile_off, int n_utts) {
   extern __shared__ float rs_smem[];
   // utterance of this tile: last b with tile_off[b] <= blockIdx.x
@@ -38,11 +67,11 @@ resample_kernel(const float* __restrict__ in, const int64_t* __restrict__ in_sta
   const int n_in = (FI - 1) * orig + Kp;  // the table rows are zero-padded to Kp taps: the extra samples only need to be finite
   float* xs = rs_smem;
   float* ys = rs_smem + ((n_in + 3) & ~3);
-  const float* src = in + in_start[b];
+  const int64_t src0 = in_start[b];
   const int64_t x0 = i0 * orig - width;  // sample index of xs[0]
-  for (int q = threadIdx.x; q < n_in; q += THREADS) {
+  for (int q = threadIdx.x; q < n_in; q += THREADS) {  // conversion and down-mix happen here: raw PCM is read once
     const int64_t s = x0 + q;
-    xs[q] = (s >= 0 && s < L) ? __ldg(src + s) : 0.f;
+    xs[q] = (s >= 0 && s < L) ? load_pcm(in, fmt, ch, scale, src0 + s) : 0.f;
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -99,12 +128,37 @@ resample_kernel(const float* __restrict__ in, const int64_t* __restrict__ in_sta
 }  // namespace ingest
 }  // namespace fa
 
-// Replaces `torchaudio.transforms.Resample(sr, 16000)(audio_tensor)` (/root/reference/infer.py:328-329) for a packed batch.
-extern "C" int fa_resample_sinc(const float* in_dev, const int64_t* in_start_dev, const int32_t* in_len_dev, const float* kernel_dev,
-                                int32_t orig, int32_t new_freq, int32_t width, int32_t taps_padded, int32_t frames_per_tile,
-                                float* out_dev, const int64_t* out_start_dev, const int32_t* tile_off_dev, int32_t n_utts,
-                                int32_t n_tiles, fa_stream_t stream) {
+static int check_pcm(int32_t format, int32_t channels, float scale) {
+  FA_REQUIRE(format == FA_PCM_F32 || format == FA_PCM_S16 || format == FA_PCM_F64, "ingest: unknown PCM format %d", format);
+  FA_REQUIRE(channels >= 1 && channels <= 64, "ingest: %d channels", channels);
+  FA_REQUIRE(scale == scale && scale != 0.f, "ingest: scale must be a non-zero number");
+  return 0;
+}
+
+// Replaces `torch.from_numpy(audio).float()` (/root/reference/infer.py:320-324) and librosa.load's mono mix
+// (/root/reference/infer_kaldidata.py:101) for a packed batch of raw interleaved PCM.
+extern "C" int fa_pcm_to_mono_f32(const void* in_dev, int32_t format, int32_t channels, float scale, const int64_t* in_start_dev,
+                                  const int32_t* in_len_dev, float* out_dev, const int64_t* out_start_dev, int32_t n_utts,
+                                  int32_t max_len, fa_stream_t stream) {
   using namespace fa;
+  FA_REQUIRE(in_dev && in_start_dev && in_len_dev && out_dev && out_start_dev, "pcm_to_mono: NULL pointer");
+  FA_REQUIRE(n_utts >= 1 && max_len >= 1, "pcm_to_mono: empty problem");
+  if (int r = check_pcm(format, channels, scale)) return r;
+  const int blocks = ceil_div(max_len, ingest::THREADS * 8);
+  ingest::pcm_to_mono_kernel<<<dim3(blocks, n_utts), ingest::THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      in_dev, format, channels, scale, in_start_dev, in_len_dev, out_dev, out_start_dev);
+  FA_CHECK_LAUNCH();
+  return 0;
+}
+
+// Replaces `torchaudio.transforms.Resample(sr, 16000)(audio_tensor)` (/root/reference/infer.py:328-329) for a packed batch,
+// reading raw PCM (format / channels / scale as above; in_start / in_len count FRAMES).
+extern "C" int fa_resample_sinc_pcm(const void* in_dev, int32_t format, int32_t channels, float scale, const int64_t* in_start_dev,
+                                    const int32_t* in_len_dev, const float* kernel_dev, int32_t orig, int32_t new_freq, int32_t width,
+                                    int32_t taps_padded, int32_t frames_per_tile, float* out_dev, const int64_t* out_start_dev,
+                                    const int32_t* tile_off_dev, int32_t n_utts, int32_t n_tiles, fa_stream_t stream) {
+  using namespace fa;
+  if (int r = check_pcm(format, channels, scale)) return r;
   FA_REQUIRE(in_dev && in_start_dev && in_len_dev && kernel_dev && out_dev && out_start_dev && tile_off_dev, "resample: NULL pointer");
   FA_REQUIRE(orig >= 1 && new_freq >= 1 && width >= 1 && n_utts >= 1 && n_tiles >= 1, "resample: empty problem");
   FA_REQUIRE(taps_padded % 4 == 0 && taps_padded >= 2 * width + orig && (reinterpret_cast<uintptr_t>(kernel_dev) & 15) == 0,
@@ -122,7 +176,7 @@ extern "C" int fa_resample_sinc(const float* in_dev, const int64_t* in_start_dev
   do {                                                                                                                              \
     static SmemOptIn opt;                                                                                                           \
     if (int r_ = opt_in_smem(ingest::resample_kernel<JJ, FF>, 200 * 1024, opt)) return r_;                                          \
-    ingest::resample_kernel<JJ, FF><<<n_tiles, ingest::THREADS, smem, st>>>(in_dev, in_start_dev, in_len_dev, kernel_dev, orig,      \
+    ingest::resample_kernel<JJ, FF><<<n_tiles, ingest::THREADS, smem, st>>>(in_dev, format, channels, scale, in_start_dev, in_len_dev, kernel_dev, orig, \
                                                                              new_freq, width, taps_padded, fw, out_dev, out_start_dev, \
                                                                              tile_off_dev, n_utts);                                  \
   } while (0)
@@ -133,4 +187,13 @@ extern "C" int fa_resample_sinc(const float* in_dev, const int64_t* in_start_dev
 #undef FA_RS_LAUNCH
   FA_CHECK_LAUNCH();
   return 0;
+}
+
+// f32 mono input: `torchaudio.transforms.Resample(sr, 16000)(audio_tensor)` on what the reference's collator hands it
+extern "C" int fa_resample_sinc(const float* in_dev, const int64_t* in_start_dev, const int32_t* in_len_dev, const float* kernel_dev,
+                                int32_t orig, int32_t new_freq, int32_t width, int32_t taps_padded, int32_t frames_per_tile,
+                                float* out_dev, const int64_t* out_start_dev, const int32_t* tile_off_dev, int32_t n_utts,
+                                int32_t n_tiles, fa_stream_t stream) {
+  return fa_resample_sinc_pcm(in_dev, FA_PCM_F32, 1, 1.f, in_start_dev, in_len_dev, kernel_dev, orig, new_freq, width, taps_padded,
+                              frames_per_tile, out_dev, out_start_dev, tile_off_dev, n_utts, n_tiles, stream);
 }

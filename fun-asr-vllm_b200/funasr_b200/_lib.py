@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfunasr_b200.so")
-ABI_VERSION = 5
+ABI_VERSION = 6
 FE_TILE_ROWS = 5  # FA_FE_TILE_ROWS
 
 i32, i64, f32, vp, sz = C.c_int32, C.c_int64, C.c_float, C.c_void_p, C.c_size_t
@@ -66,6 +66,8 @@ PROTOTYPES = {
     "fa_encode_adapt": (C.c_int, [vp, vp, i32, vp, vp, i32, i32, i32, vp, i32, vp, i32, i32, vp]),
     "fa_splice_embeds": (C.c_int, [vp, i32, vp, vp, vp, i32, vp, i32, vp, i32, i32, vp, i32, i32, vp]),
     "fa_resample_sinc": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp]),
+    "fa_pcm_to_mono_f32": (C.c_int, [vp, i32, i32, f32, vp, vp, vp, vp, i32, i32, vp]),
+    "fa_resample_sinc_pcm": (C.c_int, [vp, i32, i32, f32, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp]),
     "fa_profile_enable": (C.c_int, [i32]),
     "fa_profile_collect": (C.c_int, [vp, vp, i32]),
     "fa_op_gemm": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, vp, i64, i32, i32, i32, i32, i32, vp]),

@@ -18,6 +18,8 @@
  *   fa_fake_token_len     <- fake_token_len arithmetic                model.py:391-396
  *   fa_resample_sinc      <- torchaudio.transforms.Resample(sr, 16000)(audio)   infer.py:328-329, infer_kaldidata.py:454-455
  *                            = _apply_sinc_resample_kernel             TA/functional/functional.py:1405-1432   
+ *   fa_pcm_to_mono_f32    <- torch.from_numpy(audio).float()           infer.py:320-324; librosa.load mono mix, infer_kaldidata.py:101
+ *   fa_resample_sinc_pcm  <- both of the above in one pass
  *
  * Conventions
  *   - plain pointers and sizes only; every *_dev pointer is device memory owned by the caller;
@@ -42,7 +44,7 @@ extern "C" {
 
 typedef void* fa_stream_t; /* cudaStream_t */
 
-#define FA_ABI_VERSION 5
+#define FA_ABI_VERSION 6
 
 int fa_abi_version(void);
 const char* fa_last_error(void);
@@ -244,6 +246,23 @@ int fa_resample_sinc(const float* in_dev, const int64_t* in_start_dev, const int
                      int32_t orig, int32_t new_freq, int32_t width, int32_t taps_padded, int32_t frames_per_tile,
                      float* out_dev, const int64_t* out_start_dev, const int32_t* tile_off_dev, int32_t n_utts,
                      int32_t n_tiles, fa_stream_t stream);
+
+/* Raw PCM in: interleaved frames of `channels` samples (in_start / in_len count FRAMES), one of */
+#define FA_PCM_F32 0
+#define FA_PCM_S16 1
+#define FA_PCM_F64 2
+/* mono[s] = (sum over channels, in order, of f32(x[s][c]) * scale) / channels  -  `torch.from_numpy(audio).float()`
+ * (infer.py:320-324; scale 1) and librosa.load's soundfile scaling (1/32768 for 16-bit files) + to_mono mean
+ * (infer_kaldidata.py:101).  Output utterance b starts at out_start[b] (f32 samples). */
+int fa_pcm_to_mono_f32(const void* in_dev, int32_t format, int32_t channels, float scale, const int64_t* in_start_dev,
+                       const int32_t* in_len_dev, float* out_dev, const int64_t* out_start_dev, int32_t n_utts,
+                       int32_t max_len, fa_stream_t stream);
+/* fa_resample_sinc reading raw PCM: conversion and down-mix happen while the input span is staged, so the raw samples
+ * cross HBM once and no f32 mono copy at the source rate is ever written. */
+int fa_resample_sinc_pcm(const void* in_dev, int32_t format, int32_t channels, float scale, const int64_t* in_start_dev,
+                         const int32_t* in_len_dev, const float* kernel_dev, int32_t orig, int32_t new_freq, int32_t width,
+                         int32_t taps_padded, int32_t frames_per_tile, float* out_dev, const int64_t* out_start_dev,
+                         const int32_t* tile_off_dev, int32_t n_utts, int32_t n_tiles, fa_stream_t stream);
 
 /* ------------------------------------------------------------------ device timing (bench.py) */
 /* When enabled, every kernel launch the library makes is bracketed by a CUDA event pair on the

@@ -47,3 +47,22 @@ def resample(wave: np.ndarray, orig_freq: int, new_freq: int) -> np.ndarray:
     out = (frames.astype(np.float64) @ k.astype(np.float64).T).astype(np.float32)  # [frames, new]
     target = -(-new * L // orig)
     return out.reshape(-1)[:target]
+
+
+def pcm_to_mono_f32(wave: np.ndarray, scale: float = 1.0) -> np.ndarray:
+    """Raw PCM ``[L]`` or ``[L, C]`` (frames x channels, int16 / float32 / float64) -> mono float32.
+
+    * ``torch.from_numpy(audio).float()`` (/root/reference/infer.py:320-324): value-preserving cast to float32 (int16 exact,
+      float64 rounded to nearest); scale 1.  Pinned in tests/test_ingest.py against torch itself.
+    * ``librosa.load(path, sr=16000)`` (/root/reference/infer_kaldidata.py:101): soundfile hands 16-bit files over as
+      float32 ``x / 32768`` (scale 1/32768) and ``librosa.to_mono`` is ``np.mean`` over the channel axis, i.e. the channels
+      summed in order in float32 and divided by their count.  librosa / soundfile are not on this box: this part restates
+      their documented arithmetic (librosa 0.10 ``core/audio.py:to_mono``) and is parity-unpinned."""
+    x = np.asarray(wave)
+    if x.ndim == 1:
+        x = x[:, None]
+    v = x.astype(np.float32) * np.float32(scale)
+    s = v[:, 0].copy()
+    for c in range(1, v.shape[1]):
+        s = s + v[:, c]
+    return (s / np.float32(v.shape[1])).astype(np.float32) if v.shape[1] > 1 else s

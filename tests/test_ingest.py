@@ -96,3 +96,70 @@ def test_gpu_resample_packed_ragged_vs_oracle(sr):
                         cmvn=None, device="cuda")
     feats, cu = fe.forward_packed(torch.from_numpy(out).cuda(), ostarts[keep], on[keep])
     assert feats.shape[0] == cu[-1] and torch.isfinite(feats).all()
+
+
+def test_oracle_pcm_to_mono_matches_torch_and_numpy_mean():
+    """The collator's cast is torch's (.float(), infer.py:320-324); the mono mix is numpy's mean over channels."""
+    from oracle import ingest as oi
+
+    rng = np.random.default_rng(5)
+    s16 = rng.integers(-32768, 32767, size=(1001, 2), dtype=np.int16)
+    f64 = rng.standard_normal(777) * 0.3
+    f32 = (rng.standard_normal((640, 3)) * 0.2).astype(np.float32)
+    assert np.array_equal(oi.pcm_to_mono_f32(s16[:, 0]), torch.from_numpy(s16[:, 0].copy()).float().numpy())
+    assert np.array_equal(oi.pcm_to_mono_f32(f64), torch.from_numpy(f64).float().numpy())
+    for x, sc in ((s16, 1.0 / 32768), (f32, 1.0)):
+        want = np.mean(x.astype(np.float32).T * np.float32(sc), axis=0)  # librosa.to_mono on soundfile's [L, C] transposed
+        assert np.array_equal(oi.pcm_to_mono_f32(x, sc), want.astype(np.float32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,ch,scale", [(np.int16, 1, 1.0), (np.int16, 2, 1.0 / 32768), (np.float64, 1, 1.0), (np.float32, 3, 1.0),
+                                            (np.int16, 6, 1.0 / 32768)])
+def test_gpu_pcm_to_mono_bit_exact(dtype, ch, scale):
+    import funasr_b200 as fb
+    from oracle import ingest as oi
+
+    rng = np.random.default_rng(ch * 7 + np.dtype(dtype).itemsize)
+    lens = [1, 4097, 160000, 333, 16]
+    shape = (lambda n: (n,) if ch == 1 else (n, ch))
+    if dtype == np.int16:
+        waves = [rng.integers(-32768, 32767, size=shape(n), dtype=np.int16) for n in lens]
+    else:
+        waves = [(rng.standard_normal(shape(n)) * 0.3).astype(dtype) for n in lens]
+    host, fmt, c, starts, n = fb.pack_pcm(waves)
+    assert c == ch
+    out, ostarts, on = fb.pcm_to_mono(host.cuda(), fmt, c, starts, n, scale)
+    out = out.cpu().numpy()
+    for w, s0, k in zip(waves, ostarts, on):
+        assert np.array_equal(out[s0:s0 + k], oi.pcm_to_mono_f32(w, scale))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sr,dtype,ch,scale", [(44100, np.int16, 2, 1.0 / 32768), (48000, np.float64, 1, 1.0), (8000, np.int16, 1, 1.0)])
+def test_gpu_resample_from_raw_pcm_is_the_two_step_result(sr, dtype, ch, scale):
+    """fa_resample_sinc_pcm = fa_resample_sinc(fa_pcm_to_mono_f32(raw)) bit for bit (same staged values, same taps), and
+    both follow the oracle (float cast + mono mean, then torchaudio's polyphase sinc)."""
+    import funasr_b200 as fb
+    from oracle import ingest as oi
+
+    rng = np.random.default_rng(sr)
+    lens = [sr // 3, sr * 2 + 17, 5]
+    shape = (lambda n: (n,) if ch == 1 else (n, ch))
+    if dtype == np.int16:
+        waves = [rng.integers(-20000, 20000, size=shape(n), dtype=np.int16) for n in lens]
+    else:
+        waves = [(rng.standard_normal(shape(n)) * 0.3).astype(dtype) for n in lens]
+    host, fmt, c, starts, n = fb.pack_pcm(waves)
+    rs = fb.Resample(sr, 16000)
+    fused, fs, fn = rs.forward_packed_pcm(host.cuda(), fmt, c, starts, n, scale)
+    mono, ms, mn = fb.pcm_to_mono(host.cuda(), fmt, c, starts, n, scale)
+    two, ts, tn = rs.forward_packed(mono, ms, mn)
+    assert np.array_equal(fs, ts) and np.array_equal(fn, tn)
+    fused, two = fused.cpu().numpy(), two.cpu().numpy()
+    for w, s0, k in zip(waves, fs, fn):
+        assert np.array_equal(fused[s0:s0 + k], two[s0:s0 + k])
+        want = oi.resample(oi.pcm_to_mono_f32(w, scale), sr, 16000)
+        assert k == len(want)
+        tol = 2e-6 * max(1.0, float(np.abs(want).max()))
+        assert np.abs(fused[s0:s0 + k] - want).max() <= 20 * tol
