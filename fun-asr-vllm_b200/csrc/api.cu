@@ -131,8 +131,7 @@ struct Workspace {
   __nv_bfloat16* xn;     // [cap, d_model]   LN output, or (folded LN) the raw bf16 copy of the residual stream
   float2* stats;         // [cap, 16]        folded LN: per-row partial (sum, sum of squares), <= 16 slots
   __nv_bfloat16* qkv;    // [cap, 3*d_model]
-  float* mem;            // [cap, d_model]   FSMN memory (f32 form, layers without out_w_ext)
-  __nv_bfloat16* ctx;    // [cap, 2*d_model] [attention context | bf16 FSMN memory] = A operand of the out-projection
+  __nv_bfloat16* ctx;    // [cap, 2*d_model] [attention context | bf16 FSMN memory]: A operand and bf16 residual of the out-projection
   __nv_bfloat16* h;      // [cap, max(d_ff, ad_ffn)]
   __nv_bfloat16* enc_bf; // [cap, d_model]   encoder output, bf16 (adaptor input)
   float* enc_f32;        // [cap, d_model]   encoder output, f32
@@ -161,7 +160,6 @@ Workspace carve(const fa_model_cfg& c, int cap, unsigned char* base) {
   w.xn = reinterpret_cast<__nv_bfloat16*>(take(n * c.d_model * 2));
   w.stats = reinterpret_cast<float2*>(take(n * 16 * sizeof(float2)));
   w.qkv = reinterpret_cast<__nv_bfloat16*>(take(n * 3 * c.d_model * 2));
-  w.mem = reinterpret_cast<float*>(take(n * c.d_model * 4));
   w.ctx = reinterpret_cast<__nv_bfloat16*>(take(n * 2 * c.d_model * 2));
   w.h = reinterpret_cast<__nv_bfloat16*>(take(n * hmax * 2));
   w.enc_bf = reinterpret_cast<__nv_bfloat16*>(take(n * c.d_model * 2));
@@ -286,10 +284,13 @@ struct Builder {
   int rc = 0;
   void gemm(std::vector<Step>& prog, const void* a, int lda, const void* w, int N, int K, const float* bias, void* c,
             bool out_f32, bool relu = false, const float* res1 = nullptr, const float* res2 = nullptr, bool accumulate = false,
-            int ln_mode = 0, const float* colsum = nullptr, int ln_dim = 0, int prod_N = 0) {
+            int ln_mode = 0, const float* colsum = nullptr, int ln_dim = 0, int prod_N = 0, const __nv_bfloat16* res_bf16 = nullptr,
+            int ld_res_bf16 = 0) {
     if (rc) return;
     GemmOp op;
     rc = make_gemm_op(&op, p->cap, a, lda, w, N, K, bias, c, out_f32, relu, res1, res2, accumulate);
+    op.epi.res_bf16 = res_bf16;
+    op.epi.ld_res_bf16 = ld_res_bf16;
     op.epi.ln_mode = ln_mode;
     if (ln_mode != 0) op.epi.ln_stats = p->ws.stats;
     if (ln_mode == 1) { op.epi.colsum = colsum; op.epi.ln_dim = ln_dim; op.prod_N = prod_N; }
@@ -342,39 +343,33 @@ int build_programs(fa_plan* p) {
     const bool fold_qkv = L.qkv_colsum != nullptr, fold_ffn1 = L.ffn1_colsum != nullptr;
     const bool fold_next = (i + 1 < nl) && w.layers[i + 1].qkv_colsum != nullptr;
     if (fold_qkv && (i == 0 || i == c.n_blocks)) { set_error("plan_create: layer %d takes its input from a LayerNorm kernel; its qkv weights must not be LN-folded", i); return 2; }
-    if (fold_ffn1 && (i == 0 || L.out_w_ext == nullptr)) { set_error("plan_create: layer %d: LN-folded ffn1 needs out_w_ext and a residual out-projection", i); return 2; }
+    if (fold_ffn1 && i == 0) { set_error("plan_create: layer 0 has no residual out-projection; its ffn1 weights must not be LN-folded"); return 2; }
     // q|k|v = LN1(x) W^T + b                                              VM:206
     if (fold_qkv) B.gemm(E, ws.xn, d, L.qkv_w, 3 * d, d, L.qkv_b, ws.qkv, false, false, nullptr, nullptr, false, 1, L.qkv_colsum, d, d);
     else B.gemm(E, a_in, din, L.qkv_w, 3 * d, din, L.qkv_b, ws.qkv, false);
     // FSMN memory on v                                                     VM:249,181-201
-    // ext: bf16 memory written beside the attention context (row = [ctx | mem]); the out-projection multiplies it by the
-    // identity block of out_w_ext, i.e. adds it in the f32 accumulator.  Otherwise f32 memory, added by the epilogue.
-    const bool ext = L.out_w_ext != nullptr;
-    // With the bf16 memory and the model's 11-tap kernel the FSMN runs inside the attention kernel, on the V blocks that are
-    // in shared memory for P V anyway: no FSMN launch, V is read once.
-    const bool fuse_fsmn = ext && attention_can_fuse_fsmn(c.fsmn_kernel, 2 * d, ws.ctx + d);
+    // The memory is kept in bf16 beside the attention context (row = [ctx | mem]); the out-projection's epilogue adds it to
+    // the f32 result (GemmEpilogue::res_bf16).  With the model's 11-tap kernel the FSMN runs inside the attention kernel, on
+    // the V blocks that are in shared memory for P V anyway: no FSMN launch, V is read once.
+    __nv_bfloat16* mem = ws.ctx + d;
+    const bool fuse_fsmn = attention_can_fuse_fsmn(c.fsmn_kernel, 2 * d, mem);
     if (!fuse_fsmn) {
       const __nv_bfloat16* qkv = ws.qkv;
       const float* fw = L.fsmn_w;
-      float* mem = ws.mem;
       __nv_bfloat16* cm = ws.ctx;
       const int K = c.fsmn_kernel;
       E.push_back([=](const RunArgs& r) {
-        if (ext)
-          return launch_fsmn(qkv + static_cast<int64_t>(r.row0) * 3 * d, 3 * d, 2 * d, fw, r.cu, r.n_utts, r.row0,
-                             cm + static_cast<int64_t>(r.row0) * 2 * d + d, 1, 2 * d, r.M, d, K, left, r.s);
         return launch_fsmn(qkv + static_cast<int64_t>(r.row0) * 3 * d, 3 * d, 2 * d, fw, r.cu, r.n_utts, r.row0,
-                           mem + static_cast<int64_t>(r.row0) * d, 0, d, r.M, d, K, left, r.s);
+                           cm + static_cast<int64_t>(r.row0) * 2 * d + d, 1, 2 * d, r.M, d, K, left, r.s);
       });
     }
     // masked MHA                                                           VM:250-252,222-236
     B.attention(E, ws.qkv, ws.ctx, c.n_heads, d, 2 * d, fuse_fsmn ? L.fsmn_w : nullptr, left);
     // x (+)= ctx Wo^T + b + mem   (no residual when in_size != size: layer 0 overwrites x)   VM:238,253,123-136
-    // The residual stream is updated IN PLACE: the epilogue hands acc + bias + mem to a TMA reduce-add, so x is never
-    // staged through the SM.
-    if (fold_ffn1) B.gemm(E, ws.ctx, 2 * d, L.out_w_ext, d, 2 * d, L.out_b, x, true, false, x, nullptr, false, 2);
-    else if (ext) B.gemm(E, ws.ctx, 2 * d, L.out_w_ext, d, 2 * d, L.out_b, x, true, false, nullptr, nullptr, /*accumulate=*/i != 0);
-    else B.gemm(E, ws.ctx, 2 * d, L.out_w, d, d, L.out_b, x, true, false, ws.mem, nullptr, /*accumulate=*/i != 0);
+    // Folded-LN form: the epilogue reads the old x through its TMA ring and writes x_new, its bf16 copy and the row
+    // statistics.  Otherwise the residual stream is updated IN PLACE by a TMA reduce-add of acc + bias + mem.
+    if (fold_ffn1) B.gemm(E, ws.ctx, 2 * d, L.out_w, d, d, L.out_b, x, true, false, x, nullptr, false, 2, nullptr, 0, 0, mem, 2 * d);
+    else B.gemm(E, ws.ctx, 2 * d, L.out_w, d, d, L.out_b, x, true, false, nullptr, nullptr, /*accumulate=*/i != 0, 0, nullptr, 0, 0, mem, 2 * d);
     // LN2, FFN                                                              VM:138-140,412-431
     if (fold_ffn1) {
       B.gemm(E, ws.xn, d, L.ffn1_w, c.d_ff, d, L.ffn1_b, ws.h, false, true, nullptr, nullptr, false, 1, L.ffn1_colsum, d, d);

@@ -69,6 +69,10 @@ struct GemmEpilogue {
   const float* bias = nullptr;  // [N]
   const float* res1 = nullptr;  // f32 [M, N] (row stride ldc)
   const float* res2 = nullptr;  // f32 [M, N]
+  // f32 output: one more residual kept in bf16, [M, N] with row stride ld_res_bf16 (the FSMN memory the attention kernel
+  // leaves beside its context): read straight from global by the epilogue lane that owns the row, one unit ahead
+  const __nv_bfloat16* res_bf16 = nullptr;
+  int64_t ld_res_bf16 = 0;
   int relu = 0;
   int out_f32 = 0;
   int accumulate = 0;  // f32 output only: C += acc + bias (+ res*) instead of C = ...; the residual stream is updated in place

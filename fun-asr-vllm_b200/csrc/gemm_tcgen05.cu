@@ -84,6 +84,8 @@ struct Params {
   const float* colsum;
   __nv_bfloat16* xb;
   long long ld_xb;
+  const __nv_bfloat16* rb;  // f32 output: optional bf16 residual (the FSMN memory beside the attention context), row stride ld_rb
+  long long ld_rb;
 };
 
 using namespace fa::ptx;  // shared inline-PTX wrappers (ptx.cuh)
@@ -310,8 +312,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
         for (int n = 0; n < RES_RING - LAG; ++n) issue_load(n);
       }
+      // bf16 residual (p.rb): this lane's row, the 32 columns of a unit = four 16-byte loads, requested one unit ahead
+      auto ld_rb = [&](int n_, uint4 (&v)[4]) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = make_uint4(0u, 0u, 0u, 0u);
+        if (p.rb == nullptr || n_ >= total) return;
+        int row0_, col0_, u_;
+        coords(n_, row0_, col0_, u_);
+        if (row0_ + lane < p.M) {
+          const uint4* g = reinterpret_cast<const uint4*>(p.rb + static_cast<long long>(p.row0 + row0_ + lane) * p.ld_rb + col0_);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) v[k] = ldg_nc_v4(g + k);
+        }
+      };
+      uint4 rbv[4];
+      ld_rb(0, rbv);
       for (int n = 0; n < total; ++n) {
         [[maybe_unused]] float ln_s = 0.f, ln_ss = 0.f;  // LN == 2: this lane's row, sums over the 32 columns of this unit
+        uint4 rbn[4];
+        ld_rb(n + 1, rbn);
         const int it = n / UH, i = n - it * UH;
         const int acc = it & 1;
         int row0, col0, u;
@@ -341,6 +360,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if constexpr (NRES >= 2) {
             const float4 w2 = lds128(addr + SLAB_BYTES);
             v.x += w2.x; v.y += w2.y; v.z += w2.z; v.w += w2.w;
+          }
+          {  // bf16 residual: columns 4j .. 4j+3 = half of rbv[j / 2] (zeros when there is none)
+            const uint32_t m0 = (j & 1) ? rbv[j >> 1].z : rbv[j >> 1].x, m1 = (j & 1) ? rbv[j >> 1].w : rbv[j >> 1].y;
+            v.x += __uint_as_float(m0 << 16); v.y += __uint_as_float(m0 & 0xffff0000u);
+            v.z += __uint_as_float(m1 << 16); v.w += __uint_as_float(m1 & 0xffff0000u);
           }
           sts128(addr, __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w));
           if constexpr (LN == 2) {  // bf16 copy for the next GEMM + the statistics of exactly those bf16 values
@@ -384,6 +408,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if (lane == 0) bulk_wait_read<0>();
         }
         if (lane == 0) issue_load(n + RES_RING - LAG);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) rbv[k] = rbn[k];
         __syncwarp();
       }
     } else {
@@ -452,6 +478,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
             for (int j = 0; j < 8; ++j) bv[j] = __ldg(bp + j);
+            uint4 rbv[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) rbv[k] = make_uint4(0u, 0u, 0u, 0u);
+            if (p.rb != nullptr && row0 + lane < p.M) {  // bf16 residual of this lane's row (see the residual path above)
+              const uint4* g = reinterpret_cast<const uint4*>(p.rb + static_cast<long long>(p.row0 + row0 + lane) * p.ld_rb + col0);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) rbv[k] = ldg_nc_v4(g + k);
+            }
             if (pending >= NSLAB) {  // the store that read this slab NSLAB units ago must have drained it
               if (lane == 0) bulk_wait_read<NSLAB - 1>();
               pending = NSLAB - 1;
@@ -460,9 +494,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             tmem_ld_wait();
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              sts128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4), __float_as_uint(__uint_as_float(r[4 * j]) + bv[j].x),
-                     __float_as_uint(__uint_as_float(r[4 * j + 1]) + bv[j].y), __float_as_uint(__uint_as_float(r[4 * j + 2]) + bv[j].z),
-                     __float_as_uint(__uint_as_float(r[4 * j + 3]) + bv[j].w));
+              const uint32_t m0 = (j & 1) ? rbv[j >> 1].z : rbv[j >> 1].x, m1 = (j & 1) ? rbv[j >> 1].w : rbv[j >> 1].y;
+              sts128(slab + row_off + ((static_cast<uint32_t>(j) ^ rsw) << 4),
+                     __float_as_uint(__uint_as_float(r[4 * j]) + bv[j].x + __uint_as_float(m0 << 16)),
+                     __float_as_uint(__uint_as_float(r[4 * j + 1]) + bv[j].y + __uint_as_float(m0 & 0xffff0000u)),
+                     __float_as_uint(__uint_as_float(r[4 * j + 2]) + bv[j].z + __uint_as_float(m1 << 16)),
+                     __float_as_uint(__uint_as_float(r[4 * j + 3]) + bv[j].w + __uint_as_float(m1 & 0xffff0000u)));
             }
           } else {
             uint32_t r0[32], r1[32];
@@ -597,6 +634,9 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   p.bias = epi.bias; p.res1 = epi.res1; p.res2 = epi.res2;
   p.c = c; p.ldc = ldc; p.relu = epi.relu; p.out_f32 = epi.out_f32; p.accumulate = epi.accumulate;
   p.ln_stats = epi.ln_stats; p.colsum = epi.colsum; p.xb = epi.xb; p.ld_xb = epi.ld_xb;
+  p.rb = epi.res_bf16; p.ld_rb = epi.ld_res_bf16;
+  FA_REQUIRE(!epi.res_bf16 || (epi.out_f32 && !epi.res2 && epi.ld_res_bf16 % 8 == 0 && (reinterpret_cast<uintptr_t>(epi.res_bf16) & 15) == 0),
+             "gemm: the bf16 residual needs the f32 output, at most one f32 residual, 16-byte aligned rows");
   p.ln_slots = epi.ln_mode == 2 ? N / 32 : epi.ln_slots;
   p.ln_inv_dim = epi.ln_dim > 0 ? 1.f / static_cast<float>(epi.ln_dim) : 0.f;
   FA_REQUIRE(epi.out_f32 || N * 4 * (epi.ln_mode == 1 ? 2 : 1) <= 16384, "gemm: N=%d too wide for the staged epilogue constants", N);
@@ -715,7 +755,8 @@ int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D&
 extern "C" int fa_op_gemm_ln(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev,
                              const float* res1_dev, void* c_dev, int64_t ldc, int32_t M, int32_t N, int32_t K, int32_t relu,
                              int32_t out_f32, int32_t ln_mode, void* ln_stats_dev, int32_t* n_slots, int32_t ln_dim,
-                             const float* colsum_dev, void* xb_dev, int64_t ld_xb, fa_stream_t stream) {
+                             const float* colsum_dev, void* xb_dev, int64_t ld_xb, const void* res_bf16_dev, int64_t ld_res_bf16,
+                             fa_stream_t stream) {
   using namespace fa;
   FA_REQUIRE(a_dev && w_dev && c_dev && n_slots && (ln_mode == 1 || ln_mode == 2), "gemm_ln: bad arguments");
   const int bn = gemm_block_n(M, N, res1_dev ? 1 : 0);
@@ -730,6 +771,7 @@ extern "C" int fa_op_gemm_ln(const void* a_dev, int64_t lda, const void* w_dev, 
   e.bias = bias_dev; e.res1 = res1_dev; e.relu = relu; e.out_f32 = out_f32;
   e.ln_mode = ln_mode; e.ln_stats = static_cast<float2*>(ln_stats_dev); e.ln_dim = ln_dim; e.colsum = colsum_dev;
   e.xb = static_cast<__nv_bfloat16*>(xb_dev); e.ld_xb = ld_xb;
+  e.res_bf16 = static_cast<const __nv_bfloat16*>(res_bf16_dev); e.ld_res_bf16 = ld_res_bf16;
   if (ln_mode == 2) *n_slots = N / 32;
   e.ln_slots = *n_slots;
   return launch_gemm(ta, tb, tc, res1_dev ? &tr1 : nullptr, nullptr, bn, M, N, K, e, c_dev, ldc, 0, pair,
@@ -737,8 +779,9 @@ extern "C" int fa_op_gemm_ln(const void* a_dev, int64_t lda, const void* w_dev, 
 }
 
 extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev,
-                          const float* res1_dev, const float* res2_dev, void* c_dev, int64_t ldc, int32_t M, int32_t N,
-                          int32_t K, int32_t relu, int32_t out_f32, fa_stream_t stream) {
+                          const float* res1_dev, const float* res2_dev, const void* res_bf16_dev, int64_t ld_res_bf16,
+                          void* c_dev, int64_t ldc, int32_t M, int32_t N, int32_t K, int32_t relu, int32_t out_f32,
+                          fa_stream_t stream) {
   using namespace fa;
   FA_REQUIRE(a_dev && w_dev && c_dev, "gemm: NULL pointer");
   // a residual that IS the output buffer is applied as an in-place accumulate (C += ...)
@@ -758,6 +801,7 @@ extern "C" int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int
   if (int r = make_tensor_map(&tc, c_dev, out_f32 ? 4 : 2, M, N, ldc, 32)) return r;
   GemmEpilogue e;
   e.bias = bias_dev; e.res1 = res1_dev; e.res2 = res2_dev; e.relu = relu; e.out_f32 = out_f32; e.accumulate = accumulate;
+  e.res_bf16 = static_cast<const __nv_bfloat16*>(res_bf16_dev); e.ld_res_bf16 = ld_res_bf16;
   return launch_gemm(ta, tb, tc, res1_dev ? &tr1 : nullptr, res2_dev ? &tr2 : nullptr, bn, M, N, K, e, c_dev, ldc, 0, pair,
                      static_cast<cudaStream_t>(stream));
 }

@@ -105,6 +105,13 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
   return v;
 }
 
+// 16-byte read-only global load (data no thread of this grid writes)
+__device__ __forceinline__ uint4 ldg_nc_v4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
 // ---------------------------------------------------------------- clusters
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;

@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfunasr_b200.so")
-ABI_VERSION = 6
+ABI_VERSION = 7
 FE_TILE_ROWS = 5  # FA_FE_TILE_ROWS
 
 i32, i64, f32, vp, sz = C.c_int32, C.c_int64, C.c_float, C.c_void_p, C.c_size_t
@@ -29,7 +29,7 @@ class ModelCfg(C.Structure):
 
 class SanmLayerW(C.Structure):
     _fields_ = [(n, vp) for n in ("ln1_g", "ln1_b", "qkv_w", "qkv_b", "fsmn_w", "out_w", "out_b", "ln2_g", "ln2_b",
-                                  "ffn1_w", "ffn1_b", "ffn2_w", "ffn2_b", "out_w_ext", "qkv_colsum", "ffn1_colsum")]
+                                  "ffn1_w", "ffn1_b", "ffn2_w", "ffn2_b", "qkv_colsum", "ffn1_colsum")]
 
 
 class AdaptorLayerW(C.Structure):
@@ -70,10 +70,10 @@ PROTOTYPES = {
     "fa_resample_sinc_pcm": (C.c_int, [vp, i32, i32, f32, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp]),
     "fa_profile_enable": (C.c_int, [i32]),
     "fa_profile_collect": (C.c_int, [vp, vp, i32]),
-    "fa_op_gemm": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, vp, i64, i32, i32, i32, i32, i32, vp]),
+    "fa_op_gemm": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, vp, i64, vp, i64, i32, i32, i32, i32, i32, vp]),
     "fa_op_layernorm": (C.c_int, [vp, vp, vp, vp, vp, i32, i32, vp]),
     "fa_op_embed_layernorm": (C.c_int, [vp, vp, vp, i32, f32, vp, vp, vp, i32, i32, vp]),
-    "fa_op_gemm_ln": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, i64, i32, i32, i32, i32, i32, i32, vp, C.POINTER(C.c_int32), i32, vp, vp, i64, vp]),
+    "fa_op_gemm_ln": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, i64, i32, i32, i32, i32, i32, i32, vp, C.POINTER(C.c_int32), i32, vp, vp, i64, vp, i64, vp]),
     "fa_op_fsmn": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, i32, i32, i32, i32, vp]),
     "fa_op_fsmn_bf16": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, i64, i32, i32, i32, i32, vp]),
     "fa_op_attention": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, vp, i64, vp]),

@@ -174,11 +174,7 @@ class Plan:
                     d, ln1_g=ar.vec(L.norm1.weight), ln1_b=ar.vec(L.norm1.bias),
                     qkv_w=ar.mat(qkv_w), qkv_b=ar.vec(qkv_b),
                     fsmn_w=ar.vec(a.fsmn_block.weight.squeeze(1).t().contiguous()),  # [D,1,K] -> tap-major [K,D] f32
-                    out_b=ar.vec(a.linear_out.bias),
-                    # [Wo | I]: the out-projection adds the bf16 FSMN memory on the tensor cores (fa_sanm_layer_w.out_w_ext);
-                    # the plain Wo (fa_sanm_layer_w.out_w) stays NULL
-                    out_w_ext=ar.mat(torch.cat([a.linear_out.weight.detach().float(),
-                                                torch.eye(a.linear_out.weight.shape[0], device=a.linear_out.weight.device)], dim=1)),
+                    out_w=ar.mat(a.linear_out.weight), out_b=ar.vec(a.linear_out.bias),
                     ln2_g=ar.vec(L.norm2.weight), ln2_b=ar.vec(L.norm2.bias),
                     ffn1_w=ar.mat(ffn1_w), ffn1_b=ar.vec(ffn1_b),
                     ffn2_w=ar.mat(f.w_2.weight), ffn2_b=ar.vec(f.w_2.bias)))

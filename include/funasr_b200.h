@@ -44,7 +44,7 @@ extern "C" {
 
 typedef void* fa_stream_t; /* cudaStream_t */
 
-#define FA_ABI_VERSION 6
+#define FA_ABI_VERSION 7
 
 int fa_abi_version(void);
 const char* fa_last_error(void);
@@ -128,7 +128,9 @@ typedef struct {
   const void* qkv_w;    /* bf16 [3*d_model, d_in|d_model]   self_attn.linear_q_k_v.weight */
   const float* qkv_b;   /* [3*d_model] */
   const float* fsmn_w;  /* f32 [fsmn_kernel, d_model] TAP-MAJOR = self_attn.fsmn_block.weight[d_model,1,K] transposed */
-  const void* out_w;    /* bf16 [d_model, d_model]           self_attn.linear_out.weight */
+  const void* out_w;    /* bf16 [d_model, d_model]           self_attn.linear_out.weight.  The FSMN memory is kept in bf16
+                           beside the attention context and added to the f32 result by this GEMM's epilogue
+                           (VLLM/model_executor/models/funasr.py:253 `att_outs + fsmn_memory`). */
   const float* out_b;
   const float* ln2_g;
   const float* ln2_b;
@@ -136,10 +138,6 @@ typedef struct {
   const float* ffn1_b;
   const void* ffn2_w;   /* bf16 [d_model, d_ff]              feed_forward.w_2.weight */
   const float* ffn2_b;
-  /* optional (ABI 4): bf16 [d_model, 2*d_model] = [out_w | I].  When non-NULL the plan keeps the FSMN memory in bf16 next
-     to the attention context ([ctx | mem], K = 2*d_model) and the out-projection's tensor-core pass adds it
-     (VLLM/model_executor/models/funasr.py:253 `att_outs + fsmn_memory`), instead of an f32 memory buffer read by the epilogue. */
-  const void* out_w_ext;
   /* optional (ABI 4): LayerNorm folded into the GEMMs (norm1 -> qkv, norm2 -> ffn1; VLLM/...:83-91,120,138).  When
      qkv_colsum is non-NULL, qkv_w holds bf16(W * gamma1) (column k scaled by gamma1[k]), qkv_b holds b + W beta1 and
      qkv_colsum[n] = sum_k float(qkv_w[n, k]); the plan then feeds the GEMM the raw bf16 residual stream and applies
@@ -276,18 +274,20 @@ int fa_profile_collect(float* ms_per_kind, int32_t* launches_per_kind, int32_t n
 
 /* ------------------------------------------------------------------ single ops (parity tests) */
 /* C[M,N] = A[M,K] (bf16) * W[N,K]^T (bf16) + bias; relu optional; then
- *   out_f32 == 0: bf16 C;   out_f32 == 1: f32 C = acc + bias (+ res1) (+ res2)   (res* f32 [M,N] or NULL) */
+ *   out_f32 == 0: bf16 C;   out_f32 == 1: f32 C = acc + bias (+ res1) (+ res2) (+ res_bf16)
+ *   (res1/res2 f32 [M,N] with row stride ldc, or NULL; res_bf16 bf16 [M,N] with row stride ld_res_bf16, or NULL, not
+ *   together with res2) */
 int fa_op_gemm(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev,
-               const float* res1_dev, const float* res2_dev, void* c_dev, int64_t ldc, int32_t M, int32_t N,
-               int32_t K, int32_t relu, int32_t out_f32, fa_stream_t stream);
+               const float* res1_dev, const float* res2_dev, const void* res_bf16_dev, int64_t ld_res_bf16, void* c_dev,
+               int64_t ldc, int32_t M, int32_t N, int32_t K, int32_t relu, int32_t out_f32, fa_stream_t stream);
 /* One GEMM with a folded-LayerNorm epilogue (how the plan runs norm1 -> qkv and norm2 -> ffn1 without an LN kernel).
-   ln_mode 2 (producer): c (f32, may alias res1) = a w^T + bias + res1; xb = bf16(c); ln_stats[M, *n_slots] (float2 = sum, sum
+   ln_mode 2 (producer): c (f32, may alias res1) = a w^T + bias + res1 (+ res_bf16, bf16 [M,N] or NULL); xb = bf16(c); ln_stats[M, *n_slots] (float2 = sum, sum
    of squares of the bf16 row pieces; *n_slots is written).  ln_mode 1 (consumer): a = raw bf16 rows, w = bf16(W * gamma),
    bias = b + W beta, colsum[n] = sum_k w[n, k]; c = rstd * (a w^T - mean * colsum) + bias over ln_dim columns, eps 1e-12. */
 int fa_op_gemm_ln(const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw, const float* bias_dev, const float* res1_dev,
                   void* c_dev, int64_t ldc, int32_t M, int32_t N, int32_t K, int32_t relu, int32_t out_f32, int32_t ln_mode,
                   void* ln_stats_dev, int32_t* n_slots, int32_t ln_dim, const float* colsum_dev, void* xb_dev, int64_t ld_xb,
-                  fa_stream_t stream);
+                  const void* res_bf16_dev, int64_t ld_res_bf16, fa_stream_t stream);
 /* y = LN(x) (eps 1e-12); y_bf16 and/or y_f32 may be NULL */
 int fa_op_layernorm(const float* x_dev, const float* g_dev, const float* b_dev, void* y_bf16_dev, float* y_f32_dev,
                     int32_t M, int32_t D, fa_stream_t stream);

@@ -28,19 +28,22 @@ def cu_of(lens):
     return cu
 
 
-def op_gemm(a_bf16, w_bf16, bias=None, res1=None, res2=None, relu=False, out_f32=False, out=None):
-    """``out`` given and passed again as ``res1`` / ``res2`` = in-place accumulate (C += ...)."""
+def op_gemm(a_bf16, w_bf16, bias=None, res1=None, res2=None, relu=False, out_f32=False, out=None, res_bf16=None):
+    """``out`` given and passed again as ``res1`` / ``res2`` = in-place accumulate (C += ...).  ``res_bf16``: one more
+    residual kept in bf16 (any row stride)."""
     M, K = a_bf16.shape
     N = w_bf16.shape[0]
     c = out if out is not None else torch.empty((M, N), dtype=torch.float32 if out_f32 else torch.bfloat16, device="cuda")
     _lib.check(lib().fa_op_gemm(a_bf16.data_ptr(), a_bf16.stride(0), w_bf16.data_ptr(), w_bf16.stride(0), _lib.ptr(bias),
-                                _lib.ptr(res1), _lib.ptr(res2), c.data_ptr(), N, M, N, K, int(relu), int(out_f32), stream()),
+                                _lib.ptr(res1), _lib.ptr(res2), _lib.ptr(res_bf16), res_bf16.stride(0) if res_bf16 is not None else 0,
+                                c.data_ptr(), N, M, N, K, int(relu), int(out_f32), stream()),
                "fa_op_gemm")
     return c
 
 
-def op_gemm_ln_producer(a_bf16, w_bf16, bias, x, inplace=True, xb=None, stats=None):
-    """x_new = a w^T + bias + x (f32, written over x when inplace), its bf16 copy and the row partials [M, n_slots, 2]."""
+def op_gemm_ln_producer(a_bf16, w_bf16, bias, x, inplace=True, xb=None, stats=None, res_bf16=None):
+    """x_new = a w^T + bias + x (+ res_bf16) (f32, written over x when inplace), its bf16 copy and the row partials
+    [M, n_slots, 2]."""
     import ctypes
     M, K = a_bf16.shape
     N = w_bf16.shape[0]
@@ -50,7 +53,8 @@ def op_gemm_ln_producer(a_bf16, w_bf16, bias, x, inplace=True, xb=None, stats=No
     ns = ctypes.c_int32(0)
     _lib.check(lib().fa_op_gemm_ln(a_bf16.data_ptr(), a_bf16.stride(0), w_bf16.data_ptr(), w_bf16.stride(0), bias.data_ptr(),
                                    x.data_ptr(), c.data_ptr(), N, M, N, K, 0, 1, 2, stats.data_ptr(), ctypes.byref(ns), N, None,
-                                   xb.data_ptr(), N, stream()), "fa_op_gemm_ln")
+                                   xb.data_ptr(), N, _lib.ptr(res_bf16), res_bf16.stride(0) if res_bf16 is not None else 0, stream()),
+               "fa_op_gemm_ln")
     n = ns.value
     return c, xb, stats.view(-1)[: M * n * 2].view(M, n, 2), n
 
@@ -63,7 +67,7 @@ def op_gemm_ln_consumer(xb, w_fold_bf16, bias_fold, colsum, stats, n_slots, relu
     ns = ctypes.c_int32(n_slots)
     _lib.check(lib().fa_op_gemm_ln(xb.data_ptr(), xb.stride(0), w_fold_bf16.data_ptr(), w_fold_bf16.stride(0), bias_fold.data_ptr(),
                                    None, c.data_ptr(), N, M, N, K, int(relu), 0, 1, stats.data_ptr(), ctypes.byref(ns), K,
-                                   colsum.data_ptr(), None, 0, stream()), "fa_op_gemm_ln")
+                                   colsum.data_ptr(), None, 0, None, 0, stream()), "fa_op_gemm_ln")
     return c
 
 

@@ -57,6 +57,33 @@ def test_gemm_residual_epilogues(U, M):
     assert (acc1 - (want - r2)).abs().max().item() < 2e-3 * want.abs().max().item()
 
 
+@pytest.mark.parametrize("M", [1, 167, 2672, 40001])
+def test_gemm_bf16_residual(U, M):
+    """The out-projection's form (VLLM/model_executor/models/funasr.py:238,253): x (+)= ctx Wo^T + b + mem with the FSMN
+    memory kept in bf16 in the right half of a [ctx | mem] row (row stride 2 D), through the epilogues the plan uses:
+    plain f32 store (layer 0), in-place accumulate, staged f32 residual, folded-LN producer.  The bf16 values are exact in
+    f32, so the result differs from the f32-residual epilogue by summation order only."""
+    g = torch.Generator().manual_seed(M + 11)
+    D = 512
+    cm = bf(torch.randn(M, 2 * D, generator=g)).cuda()  # [ctx | mem]
+    ctx, mem = cm[:, :D], cm[:, D:]
+    w = bf(torch.randn(D, D, generator=g) / math.sqrt(D)).cuda()
+    bias, x0 = torch.randn(D, generator=g).cuda(), (2 * torch.randn(M, D, generator=g)).cuda()
+    base = ctx.float() @ w.float().t() + bias + mem.float()
+    tol = 2e-3 * max(1.0, (base + x0).abs().max().item())
+    got = U.op_gemm(ctx, w, bias, out_f32=True, res_bf16=mem)
+    assert (got - base).abs().max().item() < tol
+    acc = x0.clone()
+    U.op_gemm(ctx, w, bias, acc, None, out_f32=True, out=acc, res_bf16=mem)
+    assert (acc - (base + x0)).abs().max().item() < tol
+    got1 = U.op_gemm(ctx, w, bias, x0, None, out_f32=True, res_bf16=mem)
+    assert (got1 - (base + x0)).abs().max().item() < tol
+    x, xb, stats, n = U.op_gemm_ln_producer(ctx, w, bias, x0.clone(), res_bf16=mem)
+    assert (x - (base + x0)).abs().max().item() < tol
+    assert torch.equal(xb, x.to(torch.bfloat16))
+    assert torch.allclose(stats.sum(dim=1)[:, 0], xb.float().sum(dim=1), rtol=1e-4, atol=1e-2)
+
+
 @pytest.mark.parametrize("M", [300, 2672, 40001])  # narrow, medium and 256-wide (CTA pair) tiles; always one partial per 32 columns
 def test_gemm_folded_layernorm(U, M):
     """x += a W2^T + b2 ; y = relu(LN(x) W1^T + b1) with the LayerNorm folded into the two GEMM epilogues
