@@ -42,7 +42,7 @@ if which in ("frontend", "all"):
     print(f"frontend 1h: best {best*1e3:.1f} us avg {avg*1e3:.1f} us -> {byt/best/1e6:.0f} GB/s algorithmic")
 
 if which in ("gemm", "all"):
-    for name, N, K, relu, f32, nres in [("qkv", 1536, 512, 0, 0, 0), ("out", 512, 1024, 0, 1, 1), ("ffn1", 2048, 512, 1, 0, 0),
+    for name, N, K, relu, f32, nres in [("qkv", 1536, 512, 0, 0, 0), ("out", 512, 512, 0, 1, 1), ("ffn1", 2048, 512, 1, 0, 0),
                                          ("ffn2", 512, 2048, 0, 1, 1), ("qkv0", 1536, 560, 0, 0, 0)]:
         a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
         w = (torch.randn(N, K, device="cuda") / math.sqrt(K)).to(torch.bfloat16)
@@ -57,13 +57,19 @@ if which in ("gemm", "all"):
 
 if which in ("gemmln", "all"):
     # folded-LayerNorm epilogues: producer (x += ..., bf16 copy, row partials) and consumer (normalise in the epilogue)
-    for name, K in [("out+ln", 1024), ("ffn2+ln", 2048)]:
-        a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+    for name, K in [("out+ln", 512), ("ffn2+ln", 2048)]:
+        # the out-projection reads [ctx | mem] rows: A = left half, bf16 residual = right half (row stride 2 K)
+        cm = torch.randn(M, 2 * K if K == 512 else K, device="cuda").to(torch.bfloat16)
+        a = cm[:, :K]
+        mem = cm[:, K:] if K == 512 else None
         w = (torch.randn(512, K, device="cuda") / math.sqrt(K)).to(torch.bfloat16)
         bias, x = torch.randn(512, device="cuda"), torch.randn(M, 512, device="cuda")
         xb_, st_ = torch.empty(M, 512, device="cuda", dtype=torch.bfloat16), torch.zeros(M, 16, 2, device="cuda")
-        best, avg = timeit(lambda: U.op_gemm_ln_producer(a, w, bias, x, xb=xb_, stats=st_))
-        print(f"gemm {name:8s} M={M} N=512 K={K}: best {best*1e3:.1f} us avg {avg*1e3:.1f} us (producer)")
+        best, avg = timeit(lambda: U.op_gemm_ln_producer(a, w, bias, x, xb=xb_, stats=st_, res_bf16=mem))
+        print(f"gemm {name:8s} M={M} N=512 K={K}: best {best*1e3:.1f} us avg {avg*1e3:.1f} us (producer{', bf16 residual' if mem is not None else ''})")
+        if mem is not None:
+            best, avg = timeit(lambda: U.op_gemm_ln_producer(a, w, bias, x, xb=xb_, stats=st_))
+            print(f"gemm {name:8s} M={M} N=512 K={K}: best {best*1e3:.1f} us avg {avg*1e3:.1f} us (producer, without the bf16 residual)")
         r1 = torch.randn(M, 512, device="cuda")
         best, avg = timeit(lambda: U.op_gemm(a, w, bias, r1, None, out_f32=True, out=x))
         print(f"gemm {name[:-3]:8s} M={M} N=512 K={K}: best {best*1e3:.1f} us (staged residual, no LN outputs)")
