@@ -39,7 +39,10 @@ constexpr int BQ = 128;   // query rows per tile = UMMA M
 constexpr int BKV = 64;   // keys per block
 constexpr int NST = 3;    // K/V stages
 constexpr int NQ = 2;     // query tiles per work item (at most)
-constexpr int FSMN_WARPS = 2;   // filler warps: each takes every other FSMN item of its CTA
+#ifndef FA_ATTN_FSMN_WARPS
+#define FA_ATTN_FSMN_WARPS 2
+#endif
+constexpr int FSMN_WARPS = FA_ATTN_FSMN_WARPS;   // filler warps (ids 0, 1 and 12 ..): each takes every FSMN_WARPS-th FSMN unit of its CTA
 constexpr int THREADS = (10 + FSMN_WARPS) * 32;
 // Warp ids by role.  The issue arbiter of a sub-partition favours its higher warp ids: the two latency-critical single-lane
 // roles sit on top, the FSMN filler warps at the bottom (they only take slots nobody else wants); the softmax warps keep
@@ -437,7 +440,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
     // arithmetic as the stand-alone kernel.  Rows outside the utterance enter as zeros (VLLM/...:181-201: mask,
     // ConstantPad1d, depthwise Conv1d, + inputs, mask).
     constexpr int K = FSMN_K;
-    const int f = warp - W_FSMN;
+    const int f = warp < 2 ? warp : warp - 10;
     const int left = p.fsmn_left;
     // FSMN work units are independent of the attention work items: (utterance, head, chunk of fsmn_rows output rows), dealt
     // round-robin to every FSMN warp of the grid, so that a small batch still spreads over all of them.
