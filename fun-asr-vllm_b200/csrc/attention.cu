@@ -78,6 +78,9 @@ struct Params {
   __nv_bfloat16* mem;   // bf16 [rows, ld_mem], column h * 128 + c
   long long ld_mem;
   int fsmn_rows, fsmn_chunks;  // FSMN work unit = fsmn_rows output rows of one (utterance, head); chunks = ceil(max_len / rows)
+  // housekeeping for the launch that follows: the dependency counters of the GEMM chain (gemm_chain.cu) must be zero on its entry
+  int* zero_ints;
+  int n_zero;
 };
 
 struct Item {  // decoded identically by every warp role
@@ -189,6 +192,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
   auto tS = [&](int q, int buf) { return tmem + (2 * q + buf) * BKV; };
   auto tO = [&](int q) { return tmem + 4 * BKV + q * HD; };
   pdl_wait();  // qkv comes from the previous kernel
+  for (int i = blockIdx.x * THREADS + threadIdx.x; i < p.n_zero; i += gridDim.x * THREADS) p.zero_ints[i] = 0;
 
   if (warp == W_PRODUCER) {
     // ===================== TMA producer =====================
@@ -534,7 +538,7 @@ bool attention_can_fuse_fsmn(int kernel, int64_t ld_mem, const void* mem) {
 
 int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base,
                      int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, const float* fsmn_w, int fsmn_left,
-                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream) {
+                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream, int* zero_ints, int n_zero) {
   FA_REQUIRE(ld % 8 == 0 && ld_ctx % 8 == 0, "attention: row strides must be multiples of 8 elements");
   FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0,
              "attention: qkv and ctx must be 16-byte aligned");
@@ -568,6 +572,7 @@ int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t
   p.scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(attn::HD));
   p.qkv = qkv; p.ld_qkv = ld;
   p.fsmn_w = fsmn_w; p.fsmn_left = fsmn_left; p.mem = mem; p.ld_mem = ld_mem;
+  p.zero_ints = zero_ints; p.n_zero = zero_ints ? n_zero : 0;
   const int n_items = n_utts * p.groups * n_heads;
   const int grid = n_items < sms ? n_items : sms;
   // FSMN units (each chunk re-reads K - 1 halo rows, so no smaller than 32 rows): whole utterances when every FSMN warp of

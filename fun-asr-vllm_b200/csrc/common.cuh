@@ -110,6 +110,34 @@ int launch_gemm(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMap2D&
                 const TensorMap2D* tr2, int block_n, int M, int N, int K, const GemmEpilogue& epi, void* c, int64_t ldc,
                 int row0, bool pair, cudaStream_t stream);
 
+// ---- the row-local GEMM chain of a SAN-M block in one launch (gemm_chain.cu) ----
+#define FA_CHAIN_MAX_PROBS 4
+#define FA_CHAIN_MAX_SLOTS 32
+struct ChainProb {
+  const TensorMap2D* ta;  // A [rows, K] bf16, box 128 rows x 64 columns
+  const TensorMap2D* tb;  // W [N, K] bf16, box 128 rows x 64 columns (each CTA of a pair stages half of a 256-wide tile)
+  const TensorMap2D* tc;  // C [rows, N]: f32 box 32 x 32 (kind 0, also the map the old C rows are read through) or bf16 box 32 x 64
+  int N = 0, K = 0;
+  int kind = 0;  // 0: f32 C = acc + bias + C (+ res_bf16), xb = bf16(C), row partials -> stats (folded-LN producer)
+                 // 1: bf16 C = rstd * (acc - mean * colsum) + bias (, relu) from the partials of the problem before it
+  int relu = 0;
+  const float* bias = nullptr;
+  const float* colsum = nullptr;
+  float2* stats = nullptr;
+  __nv_bfloat16* xb = nullptr;
+  int64_t ld_xb = 0;
+  const __nv_bfloat16* res_bf16 = nullptr;
+  int64_t ld_res_bf16 = 0;
+  void* c = nullptr;
+};
+struct ChainDesc {
+  int n_probs = 0;
+  ChainProb p[FA_CHAIN_MAX_PROBS];  // problem i + 1 reads what problem i writes for the same rows
+};
+// rows [row0, row0 + M) of every matrix; flags: n_probs * ceil(M / 256) ints, zero on entry (dirty afterwards)
+int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStream_t stream);
+int gemm_chain_flag_ints(int n_probs, int max_rows);
+
 int launch_layernorm(const float* x, const float* g, const float* b, const float* g2, const float* b2,
                      __nv_bfloat16* y_bf16, float* y_f32, int M, int D, cudaStream_t stream);
 // Row-range convention of the kernels below: every data pointer addresses LOCAL row 0 of a slab of M rows holding the
@@ -126,7 +154,7 @@ int attention_kv_box();
 bool attention_can_fuse_fsmn(int kernel, int64_t ld_mem, const void* mem);
 int launch_attention(const TensorMap2D* tm, const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base,
                      int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, const float* fsmn_w, int fsmn_left,
-                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream);
+                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream, int* zero_ints = nullptr, int n_zero = 0);
 // dst[i] = cu[min(i, n_utts)], i = 0..n_pad: cu_seqlens copied to a fixed address, padded with the total row count
 int launch_pad_cu(const int32_t* cu, int n_utts, int32_t* dst, int n_pad, cudaStream_t stream);
 int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, int dst_bf16, const int32_t* cu,
