@@ -141,6 +141,8 @@ struct Workspace {
   __nv_bfloat16* actx;   // [cap, ad_dim]
   __nv_bfloat16* ah;     // [cap, ad_ff]
   int32_t* cu;           // [cap + 8]        cu_seqlens at a FIXED address, padded to the utterance bucket (graph replay)
+  int32_t* chain_flags;  // [2][chain_ints]  dependency counters of the GEMM chain, one set per half-batch stream
+  int chain_ints;
   size_t bytes;
 };
 
@@ -170,6 +172,8 @@ Workspace carve(const fa_model_cfg& c, int cap, unsigned char* base) {
   w.actx = reinterpret_cast<__nv_bfloat16*>(take(n * c.ad_dim * 2));
   w.ah = reinterpret_cast<__nv_bfloat16*>(take(n * c.ad_ff * 2));
   w.cu = reinterpret_cast<int32_t*>(take((n + 8) * 4));
+  w.chain_ints = gemm_chain_flag_ints(FA_CHAIN_MAX_PROBS, cap);
+  w.chain_flags = reinterpret_cast<int32_t*>(take(static_cast<size_t>(2) * w.chain_ints * 4));
   w.bytes = off;
   return w;
 }
@@ -195,6 +199,7 @@ struct RunArgs {
   int M, n_utts, max_len, row0;
   const int32_t* cu;
   cudaStream_t s;
+  int lane = 0;  // which half-batch stream of the dual-stream schedule (own set of chain counters)
 };
 using Step = std::function<int(const RunArgs&)>;
 
@@ -262,6 +267,7 @@ struct fa_plan {
   int cap;
   int n_streams;        // 1: everything on the caller's stream; 2: two half-batches, the second on `aux` (fork/join by events)
   int graph_max_rows;   // batches of up to this many rows replay a captured CUDA graph of the program (0: never)
+  int chain = 1;        // 1: the row-local GEMMs between two attention kernels run as ONE launch (gemm_chain.cu)
   cudaStream_t aux = nullptr;
   cudaStream_t cap_stream = nullptr;  // only ever used in capture mode: nothing executes on it
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -297,6 +303,48 @@ struct Builder {
     if (ln_mode == 2) { op.epi.xb = p->ws.xn; op.epi.ld_xb = N; }
     if (!rc) prog.push_back([op](const RunArgs& r) { return run_gemm_op(op, r); });
   }
+  // Layer i's out-projection, ffn1, ffn2 and layer i+1's qkv as one step: the chain launch when the plan's switch is on,
+  // the four GEMMs one after the other otherwise (same arithmetic, bit-identical results).
+  void chain(std::vector<Step>& prog, const GemmOp (&ops)[4]) {
+    if (rc) return;
+    fa_plan* pl = p;
+    struct Pack { GemmOp op[4]; };
+    Pack pk;
+    for (int i = 0; i < 4; ++i) pk.op[i] = ops[i];
+    prog.push_back([pk, pl](const RunArgs& r) {
+      if (!pl->chain) {
+        for (int i = 0; i < 4; ++i)
+          if (int e = run_gemm_op(pk.op[i], r)) return e;
+        return 0;
+      }
+      ChainDesc d;
+      d.n_probs = 4;
+      for (int i = 0; i < 4; ++i) {
+        const GemmOp& o = pk.op[i];
+        ChainProb& c = d.p[i];
+        c.ta = &o.ta; c.tb = &o.tb[1]; c.tc = &o.tc;
+        c.N = o.N; c.K = o.K;
+        c.kind = o.epi.ln_mode == 2 ? 0 : 1;
+        c.relu = o.epi.relu;
+        c.bias = o.epi.bias; c.colsum = o.epi.colsum; c.stats = o.epi.ln_stats;
+        c.xb = o.epi.xb; c.ld_xb = o.epi.ld_xb;
+        c.res_bf16 = o.epi.res_bf16; c.ld_res_bf16 = o.epi.ld_res_bf16;
+        c.c = o.c;
+      }
+      return launch_gemm_chain(d, r.M, r.row0, pl->ws.chain_flags + r.lane * pl->ws.chain_ints, r.s);
+    });
+  }
+  int make(GemmOp* op, const void* a, int lda, const void* w, int N, int K, const float* bias, void* c, bool out_f32, bool relu,
+           const float* res1, int ln_mode, const float* colsum, int ln_dim, int prod_N, const __nv_bfloat16* res_bf16, int ld_res_bf16) {
+    if (int e = make_gemm_op(op, p->cap, a, lda, w, N, K, bias, c, out_f32, relu, res1, nullptr, false)) return e;
+    op->epi.res_bf16 = res_bf16;
+    op->epi.ld_res_bf16 = ld_res_bf16;
+    op->epi.ln_mode = ln_mode;
+    op->epi.ln_stats = p->ws.stats;
+    if (ln_mode == 1) { op->epi.colsum = colsum; op->epi.ln_dim = ln_dim; op->prod_N = prod_N; }
+    if (ln_mode == 2) { op->epi.xb = p->ws.xn; op->epi.ld_xb = N; }
+    return 0;
+  }
   void ln(std::vector<Step>& prog, const float* x, const float* g, const float* b, const float* g2, const float* b2,
           __nv_bfloat16* y_bf16, float* y_f32, int D) {
     prog.push_back([=](const RunArgs& r) {
@@ -306,7 +354,7 @@ struct Builder {
   }
   // fsmn_w != nullptr: the FSMN memory is produced by the attention kernel itself (bf16, beside the context: column D + c)
   void attention(std::vector<Step>& prog, const __nv_bfloat16* qkv, __nv_bfloat16* ctx, int H, int D, int ld_ctx,
-                 const float* fsmn_w = nullptr, int fsmn_left = 0) {
+                 const float* fsmn_w = nullptr, int fsmn_left = 0, bool zero_chain = false) {
     if (rc) return;
     // one tensor map over the whole qkv buffer, encoded once per plan: utterances are addressed by their ABSOLUTE packed rows
     // (base 0).  Key / value rows past the end of a batch are workspace rows, which hold finite values (the caller hands in a
@@ -315,9 +363,13 @@ struct Builder {
     const int cap = p->cap;
     rc = make_tensor_map_bf16(&tm, qkv, cap, 3 * D, 3 * D, attention_kv_box());
     if (rc) return;
-    prog.push_back([tm, qkv, ctx, H, D, ld_ctx, cap, fsmn_w, fsmn_left](const RunArgs& r) {
+    fa_plan* pl = p;
+    prog.push_back([tm, qkv, ctx, H, D, ld_ctx, cap, fsmn_w, fsmn_left, zero_chain, pl](const RunArgs& r) {
+      // the chain that follows this attention wants its dependency counters zero: this kernel clears them on its way
+      const bool z = zero_chain && pl->chain;
+      const int nz = gemm_chain_flag_ints(FA_CHAIN_MAX_PROBS, r.M);
       return launch_attention(&tm, qkv, 3 * D, r.cu, r.n_utts, 0, r.max_len, H, ctx, ld_ctx, cap, fsmn_w, fsmn_left,
-                              fsmn_w ? ctx + D : nullptr, ld_ctx, r.s);
+                              fsmn_w ? ctx + D : nullptr, ld_ctx, r.s, z ? pl->ws.chain_flags + r.lane * pl->ws.chain_ints : nullptr, z ? nz : 0);
     });
   }
 };
@@ -334,6 +386,7 @@ int build_programs(fa_plan* p) {
   float* x = ws.x;    // current residual stream
   float* xo = ws.x2;  // next
   std::vector<Step>& E = p->enc_prog;
+  bool qkv_in_chain = false;  // this layer's qkv GEMM is the last problem of the previous layer's chain step
   for (int i = 0; i < nl; ++i) {
     const fa_sanm_layer_w& L = w.layers[i];
     const int din = (i == 0) ? c.d_in : d;
@@ -344,9 +397,15 @@ int build_programs(fa_plan* p) {
     const bool fold_next = (i + 1 < nl) && w.layers[i + 1].qkv_colsum != nullptr;
     if (fold_qkv && (i == 0 || i == c.n_blocks)) { set_error("plan_create: layer %d takes its input from a LayerNorm kernel; its qkv weights must not be LN-folded", i); return 2; }
     if (fold_ffn1 && i == 0) { set_error("plan_create: layer 0 has no residual out-projection; its ffn1 weights must not be LN-folded"); return 2; }
+    // Chain step (gemm_chain.cu): out-projection, ffn1, ffn2 of this layer and the qkv GEMM of the next one are row-local and
+    // LN-folded into each other -> one launch.  Needs the folded forms and 256-wide tiles everywhere.
+    const bool chain_ok = fold_ffn1 && fold_next && d % 256 == 0 && d <= 512 && c.d_ff % 256 == 0 &&
+                          2 * (c.d_ff + 3 * d) * 4 <= 28 * 1024;
     // q|k|v = LN1(x) W^T + b                                              VM:206
-    if (fold_qkv) B.gemm(E, ws.xn, d, L.qkv_w, 3 * d, d, L.qkv_b, ws.qkv, false, false, nullptr, nullptr, false, 1, L.qkv_colsum, d, d);
+    if (qkv_in_chain) {}
+    else if (fold_qkv) B.gemm(E, ws.xn, d, L.qkv_w, 3 * d, d, L.qkv_b, ws.qkv, false, false, nullptr, nullptr, false, 1, L.qkv_colsum, d, d);
     else B.gemm(E, a_in, din, L.qkv_w, 3 * d, din, L.qkv_b, ws.qkv, false);
+    qkv_in_chain = false;
     // FSMN memory on v                                                     VM:249,181-201
     // The memory is kept in bf16 beside the attention context (row = [ctx | mem]); the out-projection's epilogue adds it to
     // the f32 result (GemmEpilogue::res_bf16).  With the model's 11-tap kernel the FSMN runs inside the attention kernel, on
@@ -364,7 +423,18 @@ int build_programs(fa_plan* p) {
       });
     }
     // masked MHA                                                           VM:250-252,222-236
-    B.attention(E, ws.qkv, ws.ctx, c.n_heads, d, 2 * d, fuse_fsmn ? L.fsmn_w : nullptr, left);
+    B.attention(E, ws.qkv, ws.ctx, c.n_heads, d, 2 * d, fuse_fsmn ? L.fsmn_w : nullptr, left, chain_ok);
+    if (chain_ok) {
+      const fa_sanm_layer_w& Ln = w.layers[i + 1];
+      GemmOp ops[4];
+      if (!B.rc) B.rc = B.make(&ops[0], ws.ctx, 2 * d, L.out_w, d, d, L.out_b, x, true, false, x, 2, nullptr, 0, 0, mem, 2 * d);
+      if (!B.rc) B.rc = B.make(&ops[1], ws.xn, d, L.ffn1_w, c.d_ff, d, L.ffn1_b, ws.h, false, true, nullptr, 1, L.ffn1_colsum, d, d, nullptr, 0);
+      if (!B.rc) B.rc = B.make(&ops[2], ws.h, c.d_ff, L.ffn2_w, d, c.d_ff, L.ffn2_b, x, true, false, x, 2, nullptr, 0, 0, nullptr, 0);
+      if (!B.rc) B.rc = B.make(&ops[3], ws.xn, d, Ln.qkv_w, 3 * d, d, Ln.qkv_b, ws.qkv, false, false, nullptr, 1, Ln.qkv_colsum, d, d, nullptr, 0);
+      B.chain(E, ops);
+      qkv_in_chain = true;
+      continue;  // (a chained layer is neither the last main block nor the last block: nothing else follows it)
+    }
     // x (+)= ctx Wo^T + b + mem   (no residual when in_size != size: layer 0 overwrites x)   VM:238,253,123-136
     // Folded-LN form: the epilogue reads the old x through its TMA ring and writes x_new, its bf16 copy and the row
     // statistics.  Otherwise the residual stream is updated IN PLACE by a TMA reduce-add of acc + bias + mem.
@@ -455,6 +525,7 @@ extern "C" int fa_plan_create(const fa_model_cfg* cfg, const fa_model_w* w, void
   p->cap = cap;
   p->n_streams = default_streams();
   p->graph_max_rows = FA_DEFAULT_GRAPH_ROWS;
+  if (const char* e = getenv("FA_CHAIN")) p->chain = atoi(e) != 0;  // A/B measurements
   p->ws = ws;
   if (int rc = build_programs(p)) {
     delete p;
@@ -469,6 +540,16 @@ extern "C" void fa_plan_destroy(fa_plan* plan) { delete plan; }
 extern "C" int fa_plan_set_streams(fa_plan* plan, int32_t n_streams) {
   FA_REQUIRE(plan != nullptr && (n_streams == 1 || n_streams == 2), "set_streams: 1 or 2 streams");
   plan->n_streams = n_streams;
+  return 0;
+}
+
+extern "C" int fa_plan_set_chain(fa_plan* plan, int32_t on) {
+  FA_REQUIRE(plan != nullptr, "set_chain: NULL plan");
+  if ((on != 0) != (plan->chain != 0)) {  // captured graphs hold the other schedule
+    for (GraphEntry& g : plan->graphs) cudaGraphExecDestroy(g.exec);
+    plan->graphs.clear();
+  }
+  plan->chain = on != 0;
   return 0;
 }
 
@@ -677,7 +758,8 @@ int run_dual(fa_plan* p, const Slab (&sl)[2], const int32_t* cu, cudaStream_t s,
   if (int rc = ensure_streams(p)) return rc;
   FA_CHECK_CUDA(cudaEventRecord(p->ev_fork, s));
   FA_CHECK_CUDA(cudaStreamWaitEvent(p->aux, p->ev_fork, 0));
-  const RunArgs a[2] = {args_of(sl[0], cu, s), args_of(sl[1], cu, p->aux)};
+  RunArgs a[2] = {args_of(sl[0], cu, s), args_of(sl[1], cu, p->aux)};
+  a[1].lane = 1;
   int rc = 0;
   auto both = [&](const std::function<int(int)>& f) {
     for (int k = 0; k < 2 && !rc; ++k) rc = f(k);

@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfunasr_b200.so")
-ABI_VERSION = 7
+ABI_VERSION = 8
 FE_TILE_ROWS = 5  # FA_FE_TILE_ROWS
 
 i32, i64, f32, vp, sz = C.c_int32, C.c_int64, C.c_float, C.c_void_p, C.c_size_t
@@ -59,6 +59,7 @@ PROTOTYPES = {
     "fa_plan_workspace_bytes": (sz, [C.POINTER(ModelCfg), i32]),
     "fa_plan_create": (C.c_int, [C.POINTER(ModelCfg), C.POINTER(ModelW), vp, sz, i32, C.POINTER(vp)]),
     "fa_plan_destroy": (None, [vp]),
+    "fa_plan_set_chain": (C.c_int, [vp, i32]),
     "fa_plan_set_graph_rows": (C.c_int, [vp, i32]),
     "fa_plan_set_streams": (C.c_int, [vp, i32]),
     "fa_encoder_forward": (C.c_int, [vp, vp, i32, vp, vp, i32, i32, i32, vp, i32, vp]),

@@ -137,7 +137,7 @@ class Plan:
         t.handle, t.cap = C.c_void_p(None), 0
         t.arena, t.cfg, t.w = self.arena, self.cfg, self.w
         t._layers, t._ad_layers = getattr(self, "_layers", None), getattr(self, "_ad_layers", None)
-        for k in ("graph_rows", "n_streams"):
+        for k in ("graph_rows", "n_streams", "chain"):
             if getattr(self, k, None) is not None:
                 setattr(t, k, getattr(self, k))
         t._create(self.cap if max_tokens is None else max_tokens)
@@ -244,12 +244,20 @@ class Plan:
             _lib.check(lib.fa_plan_set_graph_rows(self.handle, self.graph_rows), "fa_plan_set_graph_rows")
         if getattr(self, "n_streams", None) is not None:
             _lib.check(lib.fa_plan_set_streams(self.handle, self.n_streams), "fa_plan_set_streams")
+        if getattr(self, "chain", None) is not None:
+            _lib.check(lib.fa_plan_set_chain(self.handle, self.chain), "fa_plan_set_chain")
 
     def set_graph_rows(self, n: int):
         """Batches of up to ``n`` packed rows replay a captured CUDA graph of the launch program (``fa_plan_set_graph_rows``);
         0 turns replay off."""
         self.graph_rows = int(n)
         _lib.check(_lib.load().fa_plan_set_graph_rows(self.handle, int(n)), "fa_plan_set_graph_rows")
+
+    def set_chain(self, on: bool):
+        """True (default): the row-local GEMMs between two attention kernels run as one launch (``fa_plan_set_chain``);
+        False: one launch per GEMM.  Bit-identical results."""
+        self.chain = int(bool(on))
+        _lib.check(_lib.load().fa_plan_set_chain(self.handle, self.chain), "fa_plan_set_chain")
 
     def set_streams(self, n: int):
         """1 = everything on the caller's stream; 2 = two half-batches on two streams (``fa_plan_set_streams``)."""

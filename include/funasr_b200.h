@@ -44,7 +44,7 @@ extern "C" {
 
 typedef void* fa_stream_t; /* cudaStream_t */
 
-#define FA_ABI_VERSION 7
+#define FA_ABI_VERSION 8
 
 int fa_abi_version(void);
 const char* fa_last_error(void);
@@ -202,6 +202,12 @@ int fa_plan_set_streams(fa_plan* plan, int32_t n_streams);
  * up to 48 graphs are kept per plan, least recently used first out.  max_rows == 0 turns replay off; larger batches use the
  * dual-stream schedule above.  Needs a workspace that was zero-filled before fa_plan_create (rows past the end of a batch
  * are computed on whatever the workspace holds and must stay finite). */
+/* Chain schedule (new, on by default).  The GEMMs between two attention kernels of the encoder - out-projection, ffn1, ffn2
+ * of block i and the qkv projection of block i + 1 - touch every token row on its own, so they run as ONE cooperative launch
+ * whose tiles wait on per-row-block counters instead of on grid boundaries (csrc/gemm_chain.cu): three launch boundaries
+ * per block disappear and the FFN hidden rows are consumed out of L2.  Same tile arithmetic: results are bit-identical to
+ * on == 0 (one launch per GEMM).  Environment override at plan creation: FA_CHAIN=0. */
+int fa_plan_set_chain(fa_plan* plan, int32_t on);
 #define FA_DEFAULT_GRAPH_ROWS 8192
 int fa_plan_set_graph_rows(fa_plan* plan, int32_t max_rows);
 

@@ -168,6 +168,32 @@ def test_dual_stream_schedule_is_invisible():
     assert torch.equal(y, y0) and torch.equal(z, z0)
 
 
+def test_chain_schedule_is_invisible():
+    """fa_plan_set_chain: out-projection -> ffn1 -> ffn2 -> next qkv of a block as ONE launch with per-row-block dependency
+    counters (csrc/gemm_chain.cu) against one launch per GEMM: same tile arithmetic, so bit-identical - for one partial row
+    block, a ragged multi-row-block batch, the dual-stream schedule and graph replay; repeated calls re-use the counters.
+    (4 + 2 blocks: layers 1, 2 and 4 are chained; 2 + 1 has no chainable layer.)"""
+    import funasr_b200 as fb
+
+    _, _, enc, ad = _pair(4, 2)
+    tower = fb.AudioTower(enc, ad)
+    plan = tower.plan()
+    for lens, streams, graph_rows in [([50], 1, 0), ([167] * 9 + [40, 500, 98, 130, 5, 64, 129, 333, 255, 17, 80], 1, 0),
+                                      ([167] * 9 + [40, 500, 98, 130, 5, 64, 129, 333, 255, 17, 80], 2, 0),
+                                      ([167] * 16, 1, 8192), ([257, 1, 255], 1, 8192)]:
+        x, il = _batch(lens)
+        feats = torch.cat([x[b, :t] for b, t in enumerate(lens)]).cuda()
+        plan.set_graph_rows(graph_rows)
+        plan.set_streams(streams)
+        plan.set_chain(False)
+        want, _ = tower.forward_packed(feats, il.numpy(), out_dtype=torch.float32)
+        want = want.clone()
+        plan.set_chain(True)
+        for _ in range(3):
+            got, _ = tower.forward_packed(feats, il.numpy(), out_dtype=torch.float32)
+            assert torch.equal(got, want), (lens[:3], streams, graph_rows)
+
+
 def test_full_depth_50_20_one_utterance():
     """The Nano stack (50 + 20 blocks + adaptor) on one 3 s utterance: error growth through 70 layers stays in budget."""
     o_enc, o_ad, enc, ad = _pair(50, 20)
