@@ -115,6 +115,16 @@ __device__ __forceinline__ void wait_counter(const int* f, int need) {
   }
 }
 
+// mbarrier wait with the same watchdog (shadows ptx::mbar_wait inside this file): a tile-list bug must fail, not hang
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_test(bar, parity)) return;
+  const long long t0 = clock64();
+  int n = 0;
+  while (!mbar_test(bar, parity)) {
+    if ((++n & 1023) == 0 && clock64() - t0 > 6000000000ll) __trap();
+  }
+}
+
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p) {
   extern __shared__ unsigned char smem_raw[];
@@ -126,10 +136,13 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
-  auto dep_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 4 + a); };  // the tile's dependency has been observed by this CTA
-  const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 6);
-  auto res_bar = [&](int w, int slot) { return bar_base + 8u * (2 * STAGES + 7 + w * 2 + slot); };
-  static_assert(8 * (2 * STAGES + 7 + EPI_WARPS * 2) <= BAR_BYTES, "barrier region too small");
+  // "the dependency of this CTA's tile number i has been observed": a ring of four (index i & 3).  The producer is never more
+  // than two tiles ahead of the epilogue (operand ring + accumulator hand-over), so a barrier is not completed twice before
+  // the epilogue has waited on it - with a ring of two it could be (arrive for tile i + 2 while tile i - 1 still drains).
+  auto dep_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 4 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 8);
+  auto res_bar = [&](int w, int slot) { return bar_base + 8u * (2 * STAGES + 9 + w * 2 + slot); };
+  static_assert(8 * (2 * STAGES + 9 + EPI_WARPS * 2) <= BAR_BYTES, "barrier region too small");
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   pdl_launch_dependents();
@@ -160,8 +173,8 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
       mbar_init(tempty_bar(a), EPI_WARPS * 2);
-      mbar_init(dep_bar(a), 1);
     }
+    for (int a = 0; a < 4; ++a) mbar_init(dep_bar(a), 1);
     for (int w = 0; w < EPI_WARPS; ++w)
       for (int sl = 0; sl < 2; ++sl) mbar_init(res_bar(w, sl), 1);
     fence_mbar_init();
@@ -194,7 +207,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
           wait_counter(p.flags + P.dep * p.n_rb + rbk, P.dep_need);
           fence_proxy_async_all();  // the TMA reads below are ordered after the acquire
         }
-        mbar_arrive(dep_bar(it & 1));
+        mbar_arrive(dep_bar(it & 3));
         const int arow = p.row0 + (rbk * 2 + static_cast<int>(rank)) * BM;
         const int brow = tn * BN + static_cast<int>(rank) * (BN / 2);
         for (int kb = 0; kb < P.num_kb; ++kb) {
@@ -262,7 +275,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
       const bool my_row = row0 + lane < p.M;
       const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
       const CUtensorMap* mc = &maps.c[pi];
-      mbar_wait(dep_bar(acc), acc_phase);  // whatever this tile reads from earlier tiles is complete and visible
+      mbar_wait(dep_bar(it & 3), (it >> 2) & 1);  // whatever this tile reads from earlier tiles is complete and visible
       if (P.kind == 0) {
         // ---- f32 tile: C = acc + bias + C_old (+ bf16 residual); bf16 copy and row partials of the new rows.  Units of 32
         // columns; this warp takes units hf, hf + 2, ...; C_old arrives by TMA in the slab the result leaves from.
