@@ -19,6 +19,7 @@
 #include <cuda.h>
 #include <cooperative_groups.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -47,6 +48,9 @@ static_assert(SMEM_BYTES <= 227 * 1024, "chain: shared memory budget");
 constexpr int TMEM_COLS = 2 * BN;
 constexpr int MAX_PROBS = FA_CHAIN_MAX_PROBS;
 constexpr int MAX_SLOTS = FA_CHAIN_MAX_SLOTS;
+#ifndef FA_CHAIN_DIST
+#define FA_CHAIN_DIST 24
+#endif
 constexpr int WARPS_PER_TILE = 2 * EPI_WARPS;  // epilogue warps of both CTAs bump a tile's counter
 
 struct Maps {
@@ -517,9 +521,13 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
   int n_slots = 0, cvec = 0;
   for (int i = 0; i < d.n_probs; ++i) n_slots += d.p[i].N / BN;
   FA_REQUIRE(n_slots <= MAX_SLOTS, "chain: %d tiles per row block exceed %d", n_slots, MAX_SLOTS);
-  int dist = ceil_div(2 * pairs, n_slots);
-  if (dist > p.n_rb / 4) dist = p.n_rb / 4;
-  if (dist < 1) dist = 1;
+  // A tile is published ~15 us after it was picked up (32 k-blocks of ffn2, epilogue, store completion, counter) and a macro
+  // step is picked up every ~0.8 us by 74 pairs: its dependencies must lie ~20 steps back or the pairs wait in list order
+  // (measured with 2 steps at 11 row blocks: 118 us per chain against 45 us for four launches).  Few row blocks: problem-major
+  // order (dist = n_rb), i.e. four launches' worth of tiles without the three grid hand-overs.
+  int dist = FA_CHAIN_DIST;
+  if (const char* e = getenv("FA_CHAIN_DIST")) dist = atoi(e) > 0 ? atoi(e) : dist;  // measurement switch
+  if (dist > p.n_rb) dist = p.n_rb;
   for (int i = 0; i < d.n_probs; ++i) {
     const ChainProb& s = d.p[i];
     Prob& P = p.pr[i];
