@@ -48,6 +48,9 @@ static_assert(SMEM_BYTES <= 227 * 1024, "chain: shared memory budget");
 constexpr int TMEM_COLS = 2 * BN;
 constexpr int MAX_PROBS = FA_CHAIN_MAX_PROBS;
 constexpr int MAX_SLOTS = FA_CHAIN_MAX_SLOTS;
+#ifndef FA_CHAIN_PUB
+#define FA_CHAIN_PUB 2  // 2: deferred publication; 1: immediate; 0: immediate with an extra __threadfence (measurement builds)
+#endif
 #ifndef FA_CHAIN_DIST
 #define FA_CHAIN_DIST 24
 #endif
@@ -80,6 +83,7 @@ struct Prob {
 
 struct Params {
   int M, row0, n_rb, n_prob, n_slots, n_steps;
+  int defer;   // publications may wait for the pair's next tile (no tile within reach of a pair's next one depends on it)
   int* flags;  // [n_prob][n_rb], zero on entry
   unsigned char slot_prob[MAX_SLOTS], slot_tn[MAX_SLOTS];
   Prob pr[MAX_PROBS];
@@ -268,6 +272,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
     const uint32_t my_slabs = slab_base + ew * 2 * SLAB_BYTES;
     int it = 0;
     int nres = 0;  // residual slabs this warp has requested so far (ring slot = nres & 1)
+    int* pend = nullptr;  // counter of the previous tile when its publication was deferred
     for (int g = cl; g < total; g += ncl) {
       int pi, rbk, tn;
       if (!decode(g, pi, rbk, tn)) continue;
@@ -475,17 +480,47 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
           }
         }
       }
-      // ---- this warp's part of the tile is in global memory: publish it
-      if (lane == 0) {
-        bulk_wait<0>();            // the TMA stores have been performed (not only read their slabs)
-        fence_proxy_async_all();
+      // ---- publish this warp's part of the tile: its TMA stores must have been PERFORMED (not only have read their slabs),
+      // which takes microseconds.  When the list guarantees that nothing this pair does next can depend on the tile (p.defer,
+      // see the launcher) the wait is deferred: the counter is bumped after the NEXT tile's epilogue, by which time the stores
+      // are long complete (wait_group N with N = the groups committed since), so the epilogue never stalls on a store.
+      __syncwarp();  // the other lanes' plain stores (bf16 copy, partials, ragged rows) are ordered before lane 0's release
+      const int my_groups = rows_full ? (P.kind == 0 ? BN / 32 / 2 : BN / 64 / 2) : 0;
+      if (pend != nullptr) {
+        if (lane == 0) {
+          if (my_groups == 4) bulk_wait<4>();
+          else if (my_groups == 2) bulk_wait<2>();
+          else bulk_wait<0>();
+          fence_proxy_async_all();
+          red_release_add(pend, 1);
+        }
+        pend = nullptr;
       }
-      __syncwarp();                // the other lanes' plain stores (bf16 copy, partials, ragged rows) are ordered before lane 0's release
-      if (lane == 0) {
-        __threadfence();
-        red_release_add(p.flags + pi * p.n_rb + rbk, 1);
+      int* mine = p.flags + pi * p.n_rb + rbk;
+      bool defer = false;
+      if (FA_CHAIN_PUB == 2 && p.defer) {
+        for (int g2 = g + ncl; g2 < total; g2 += ncl) {  // this pair's next tile: deferring needs one, on another row block
+          int pi2, rb2, tn2;
+          if (decode(g2, pi2, rb2, tn2)) {
+            defer = rb2 != rbk;
+            break;
+          }
+        }
+      }
+      if (defer) {
+        pend = mine;
+      } else if (lane == 0) {
+        bulk_wait<0>();
+        fence_proxy_async_all();
+        if (FA_CHAIN_PUB == 0) __threadfence();
+        red_release_add(mine, 1);
       }
       ++it;
+    }
+    if (pend != nullptr && lane == 0) {
+      bulk_wait<0>();
+      fence_proxy_async_all();
+      red_release_add(pend, 1);
     }
   }
 
@@ -579,6 +614,11 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
   }
   p.n_slots = n_slots;
   p.n_steps = p.n_rb + p.pr[d.n_probs - 1].delay;
+  // Deferred publication makes "tile T is published" wait for the epilogue of the pair's next tile, up to `pairs` list
+  // positions later; that tile's dependencies lie at least (dist - 1) * n_slots positions before it.  When the second
+  // distance is the larger one, every such wait points to an earlier list position and the walk stays deadlock-free.
+  p.defer = (dist - 1) * n_slots > pairs + n_slots ? 1 : 0;
+  if (const char* e = getenv("FA_CHAIN_DEFER")) p.defer = p.defer && atoi(e) != 0;
   const long long tiles = static_cast<long long>(p.n_rb) * n_slots;
   int use_pairs = pairs;
   if (tiles < use_pairs) use_pairs = static_cast<int>(tiles);
@@ -589,7 +629,7 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
   cfg.blockDim = dim3(NUM_THREADS);
   cfg.dynamicSmemBytes = SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[3];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
@@ -615,6 +655,16 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
     cfg.gridDim = dim3(2 * use_pairs);
   }
   cfg.numAttrs = 2;
+  if (const char* e = getenv("FA_CHAIN_COOP")) {  // measurement switch: plain launch (only safe when nothing else runs on the device)
+    if (atoi(e) == 0) cfg.numAttrs = 1;
+  }
+  if (const char* e = getenv("FA_CHAIN_PDL")) {  // measurement switch: programmatic dependent launch on top
+    if (atoi(e) != 0) {
+      attr[cfg.numAttrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[cfg.numAttrs].val.programmaticStreamSerializationAllowed = 1;
+      ++cfg.numAttrs;
+    }
+  }
   ProfScope _ps(K_GEMM, stream);
   FA_CHECK_CUDA(cudaLaunchKernelEx(&cfg, chain_kernel, maps, p));
   return 0;
