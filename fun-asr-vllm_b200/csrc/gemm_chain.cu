@@ -51,6 +51,9 @@ constexpr int MAX_SLOTS = FA_CHAIN_MAX_SLOTS;
 #ifndef FA_CHAIN_PUB
 #define FA_CHAIN_PUB 2  // 2: deferred publication; 1: immediate; 0: immediate with an extra __threadfence (measurement builds)
 #endif
+#ifndef FA_CHAIN_L2PF
+#define FA_CHAIN_L2PF 1
+#endif
 #ifndef FA_CHAIN_DIST
 #define FA_CHAIN_DIST 24
 #endif
@@ -83,7 +86,7 @@ struct Prob {
 
 struct Params {
   int M, row0, n_rb, n_prob, n_slots, n_steps;
-  int defer;   // publications may wait for the pair's next tile (no tile within reach of a pair's next one depends on it)
+  int defer;   // > 0: a publication may wait for the pair's next tile when that tile lies at most this many list positions ahead
   int* flags;  // [n_prob][n_rb], zero on entry
   unsigned char slot_prob[MAX_SLOTS], slot_tn[MAX_SLOTS];
   Prob pr[MAX_PROBS];
@@ -217,6 +220,13 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         }
         mbar_arrive(dep_bar(it & 3));
         const int arow = p.row0 + (rbk * 2 + static_cast<int>(rank)) * BM;
+        if (FA_CHAIN_L2PF && P.kind == 0) {
+          // The f32 epilogue is a chain of dependent round trips (old C rows in, new rows out, per 32-column unit): ask L2
+          // for the tile's old rows now, a main loop ahead, so those round trips end in L2 instead of HBM.
+          for (int r4 = 0; r4 < BM / 32; ++r4)
+#pragma unroll
+            for (int c8 = 0; c8 < BN / 32; ++c8) tma_prefetch_l2_2d(&maps.c[pi], tn * BN + c8 * 32, arow + r4 * 32);
+        }
         const int brow = tn * BN + static_cast<int>(rank) * (BN / 2);
         for (int kb = 0; kb < P.num_kb; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
@@ -498,8 +508,9 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
       }
       int* mine = p.flags + pi * p.n_rb + rbk;
       bool defer = false;
-      if (FA_CHAIN_PUB == 2 && p.defer) {
-        for (int g2 = g + ncl; g2 < total; g2 += ncl) {  // this pair's next tile: deferring needs one, on another row block
+      if (FA_CHAIN_PUB == 2 && p.defer > 0) {
+        // this pair's next tile: deferring needs one within p.defer list positions (see the launcher), on another row block
+        for (int g2 = g + ncl; g2 < total && g2 - g <= p.defer; g2 += ncl) {
           int pi2, rb2, tn2;
           if (decode(g2, pi2, rb2, tn2)) {
             defer = rb2 != rbk;
@@ -614,11 +625,14 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
   }
   p.n_slots = n_slots;
   p.n_steps = p.n_rb + p.pr[d.n_probs - 1].delay;
-  // Deferred publication makes "tile T is published" wait for the epilogue of the pair's next tile, up to `pairs` list
-  // positions later; that tile's dependencies lie at least (dist - 1) * n_slots positions before it.  When the second
-  // distance is the larger one, every such wait points to an earlier list position and the walk stays deadlock-free.
-  p.defer = (dist - 1) * n_slots > pairs + n_slots ? 1 : 0;
-  if (const char* e = getenv("FA_CHAIN_DEFER")) p.defer = p.defer && atoi(e) != 0;
+  // Deferred publication makes "tile at list position g is published" wait for the epilogue of the pair's next tile at
+  // g2 <= g + R.  That tile's dependencies sit in macro step t2 - dist, i.e. at positions <= g2 - (dist - 1) n_slots - 1
+  // <= g - n_slots - 1 for R = (dist - 2) n_slots: every wait points to a strictly earlier list position than g, whatever
+  // is deferred there in turn, so the walk stays deadlock-free.  (Empty slots make "the next tile" arbitrarily far in the
+  // problem-major order of small launches: there the publication is immediate.)
+  p.defer = (dist - 2) * n_slots;
+  if (p.defer < pairs) p.defer = 0;
+  if (const char* e = getenv("FA_CHAIN_DEFER")) p.defer = atoi(e) != 0 ? p.defer : 0;
   const long long tiles = static_cast<long long>(p.n_rb) * n_slots;
   int use_pairs = pairs;
   if (tiles < use_pairs) use_pairs = static_cast<int>(tiles);

@@ -61,6 +61,10 @@ __device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const void* tmap,
       "l"(tmap), "r"(cluster_bar), "r"(x), "r"(y)
       : "memory");
 }
+// asks L2 for the box (no shared-memory destination, no completion to wait for)
+__device__ __forceinline__ void tma_prefetch_l2_2d(const void* tmap, int x, int y) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(tmap), "r"(x), "r"(y) : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int x, int y) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap), "r"(src), "r"(x),
                "r"(y)

@@ -1,16 +1,14 @@
 #!/bin/bash
-# r02-aa: where the chain loses its time: publication variants (immediate + fence, immediate, deferred), plain vs cooperative launch,
-# PDL on top, dependency distance.  chain_check.py prints per-call times of a 4+2-block tower (three chained layers).
+# r02-ab: chain with deferred publication (+ L2 prefetch of the old residual rows for the f32 tiles): check + timings.
 set -u
-O=gpurun_out/r2aa
+O=gpurun_out/r2ab
 mkdir -p $O
 run() { name=$1; shift; timeout 200 env "$@" python profiles/scripts/chain_check.py > $O/check_$name.log 2>&1; echo "$name exit $?"; grep -E "rows|OK|MISMATCH|rror" $O/check_$name.log | cut -c1-200 | tail -11; }
-run deferred FA_X=0
-run deferred_nocoop FA_CHAIN_COOP=0
-run deferred_pdl FA_CHAIN_PDL=1
-run deferred_nocoop_pdl FA_CHAIN_COOP=0 FA_CHAIN_PDL=1
-run deferred_dist48 FA_CHAIN_DIST=48
-run deferred_dist12 FA_CHAIN_DIST=12
-for v in pub0 pub1; do
-timeout 200 python profiles/scripts/with_lib.py $v profiles/scripts/chain_check.py > $O/check_$v.log 2>&1; echo "$v exit $?"; grep -E "rows|OK|MISMATCH|rror" $O/check_$v.log | cut -c1-200 | tail -11
-done
+run default FA_X=0
+run nodefer FA_CHAIN_DEFER=0
+run dist48 FA_CHAIN_DIST=48
+run dist16 FA_CHAIN_DIST=16
+timeout 200 python profiles/scripts/with_lib.py nopf profiles/scripts/chain_check.py > $O/check_nopf.log 2>&1; echo "nopf exit $?"; grep -E "rows|OK|MISMATCH|rror" $O/check_nopf.log | cut -c1-200 | tail -11
+timeout 200 python bench.py --no-cpu-baseline --no-extras > $O/bench_chain.json 2> $O/bench_chain.err; echo "bench exit $?"; tail -3 $O/bench_chain.err
+python -c "
+import json; d=json.load(open('$O/bench_chain.json')); print(d['ms_per_step'], d['e2e']['ms_per_step'], d['kernel_ms_per_step'], d['clocks'])"
