@@ -126,6 +126,19 @@ __device__ __forceinline__ void wait_counter(const int* f, int need) {
   }
 }
 
+// ---- per-tile timeline of one CTA (make variant NAME=ctrace DEFS=-DFA_CHAIN_TRACE: profiling builds only) ----
+#ifdef FA_CHAIN_TRACE
+constexpr int TR_TILES = 128, TR_EV = 8, TR_ROLES = 4;  // roles: 0 producer, 1 MMA, 2 epilogue warp 2, 3 epilogue warp 6
+__device__ long long g_ctrace[TR_ROLES * TR_TILES * TR_EV];
+__device__ int g_ctrace_block = 0;
+#define FA_CTRACE(role, it, ev, val)                                                                             \
+  do {                                                                                                           \
+    if (static_cast<int>(blockIdx.x) == g_ctrace_block && (it) < TR_TILES) g_ctrace[((role) * TR_TILES + (it)) * TR_EV + (ev)] = (val); \
+  } while (0)
+#else
+#define FA_CTRACE(role, it, ev, val)
+#endif
+
 // mbarrier wait with the same watchdog (shadows ptx::mbar_wait inside this file): a tile-list bug must fail, not hang
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_test(bar, parity)) return;
@@ -214,11 +227,14 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         int pi, rbk, tn;
         if (!decode(g, pi, rbk, tn)) continue;
         const Prob& P = p.pr[pi];
+        FA_CTRACE(0, it, 0, (static_cast<long long>(pi) << 40) | (static_cast<long long>(rbk) << 8) | tn);
+        FA_CTRACE(0, it, 1, clock64());
         if (P.dep >= 0) {
           wait_counter(p.flags + P.dep * p.n_rb + rbk, P.dep_need);
           fence_proxy_async_all();  // the TMA reads below are ordered after the acquire
         }
         mbar_arrive(dep_bar(it & 3));
+        FA_CTRACE(0, it, 2, clock64());
         const int arow = p.row0 + (rbk * 2 + static_cast<int>(rank)) * BM;
         if (FA_CHAIN_L2PF && P.kind == 0) {
           // The f32 epilogue is a chain of dependent round trips (old C rows in, new rows out, per 32-column unit): ask L2
@@ -237,6 +253,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
           tma_load_2d_pair(sa + A_BYTES, &maps.b[pi], lead_bar, kb * BK, brow);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        FA_CTRACE(0, it, 3, clock64());
         ++it;
       }
     }
@@ -251,11 +268,14 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         if (!decode(g, pi, rbk, tn)) continue;
         const int num_kb = p.pr[pi].num_kb;
         const int acc = it & 1;
+        if (lane == 0) FA_CTRACE(1, it, 1, clock64());
         mbar_wait(tempty_bar(acc), ((it >> 1) & 1) ^ 1);
+        if (lane == 0) FA_CTRACE(1, it, 2, clock64());
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(full_bar(stage), phase);
+          if (lane == 0 && kb == 0) FA_CTRACE(1, it, 3, clock64());
           tc_fence_after();
           if (elect_one()) {
             const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -269,6 +289,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
           __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        if (lane == 0) FA_CTRACE(1, it, 4, clock64());
         ++it;
       }
     }
@@ -294,6 +315,9 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
       const bool my_row = row0 + lane < p.M;
       const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
       const CUtensorMap* mc = &maps.c[pi];
+      [[maybe_unused]] const int trole = 2 + (ew >> 2);
+      [[maybe_unused]] const bool tr = lane == 0 && (ew & 3) == 0;
+      if (tr) FA_CTRACE(trole, it, 1, clock64());
       mbar_wait(dep_bar(it & 3), (it >> 2) & 1);  // whatever this tile reads from earlier tiles is complete and visible
       if (P.kind == 0) {
         // ---- f32 tile: C = acc + bias + C_old (+ bf16 residual); bf16 copy and row partials of the new rows.  Units of 32
@@ -329,7 +353,9 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         }
         uint4 rbv[4];
         ld_rb(0, rbv);
+        if (tr) FA_CTRACE(trole, it, 2, clock64());
         mbar_wait(tfull_bar(acc), acc_phase);
+        if (tr) FA_CTRACE(trole, it, 3, clock64());
         tc_fence_after();
         for (int i = 0; i < UH; ++i) {
           float ln_s = 0.f, ln_ss = 0.f;
@@ -430,7 +456,9 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
           ln_rs = rsqrtf(fmaxf(fmaf(-mu, mu, ss * P.inv_dim), 0.f) + 1e-12f);
           ln_nm = -ln_rs * mu;
         }
+        if (tr) FA_CTRACE(trole, it, 2, clock64());
         mbar_wait(tfull_bar(acc), acc_phase);
+        if (tr) FA_CTRACE(trole, it, 3, clock64());
         tc_fence_after();
         constexpr int UNITS = BN / 64;
 #pragma unroll 1
@@ -495,6 +523,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
       // see the launcher) the wait is deferred: the counter is bumped after the NEXT tile's epilogue, by which time the stores
       // are long complete (wait_group N with N = the groups committed since), so the epilogue never stalls on a store.
       __syncwarp();  // the other lanes' plain stores (bf16 copy, partials, ragged rows) are ordered before lane 0's release
+      if (tr) FA_CTRACE(trole, it, 4, clock64());
       const int my_groups = rows_full ? (P.kind == 0 ? BN / 32 / 2 : BN / 64 / 2) : 0;
       if (pend != nullptr) {
         if (lane == 0) {
@@ -526,6 +555,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         if (FA_CHAIN_PUB == 0) __threadfence();
         red_release_add(mine, 1);
       }
+      if (tr) FA_CTRACE(trole, it, 5, clock64());
       ++it;
     }
     if (pend != nullptr && lane == 0) {
@@ -544,6 +574,18 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
 }
 
 }  // namespace chain
+
+#ifdef FA_CHAIN_TRACE
+// profiling builds only: choose the traced CTA (block index) / copy the trace of the last launch to the host
+extern "C" __attribute__((visibility("default"))) int fa_debug_chain_trace(long long* dst_host, int n, int next_block) {
+  cudaDeviceSynchronize();
+  const int cap = chain::TR_ROLES * chain::TR_TILES * chain::TR_EV;
+  if (n > cap) n = cap;
+  cudaMemcpyFromSymbol(dst_host, chain::g_ctrace, sizeof(long long) * n);
+  cudaMemcpyToSymbol(chain::g_ctrace_block, &next_block, sizeof(int));
+  return n;
+}
+#endif
 
 int gemm_chain_flag_ints(int n_probs, int max_rows) { return n_probs * ceil_div(max_rows, 2 * chain::BM); }
 
