@@ -318,6 +318,9 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
       [[maybe_unused]] const int trole = 2 + (ew >> 2);
       [[maybe_unused]] const bool tr = lane == 0 && (ew & 3) == 0;
       if (tr) FA_CTRACE(trole, it, 1, clock64());
+#ifdef FA_CHAIN_TRACE
+      long long tr_res = 0, tr_rd = 0;
+#endif
       mbar_wait(dep_bar(it & 3), (it >> 2) & 1);  // whatever this tile reads from earlier tiles is complete and visible
       if (P.kind == 0) {
         // ---- f32 tile: C = acc + bias + C_old (+ bf16 residual); bf16 copy and row partials of the new rows.  Units of 32
@@ -365,7 +368,13 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
           const uint32_t slab = my_slabs + (rn & 1) * SLAB_BYTES;
           uint4 rbn[4];
           ld_rb(i + 1, rbn);
+#ifdef FA_CHAIN_TRACE
+          const long long tq0 = clock64();
+#endif
           mbar_wait(res_bar(ew, rn & 1), (rn >> 1) & 1);
+#ifdef FA_CHAIN_TRACE
+          tr_res += clock64() - tq0;
+#endif
           uint32_t r[32];
           tmem_ld32_nowait(tmem_row + u * 32, r);
           tmem_ld_wait();
@@ -406,11 +415,17 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
           if (rows_full) {
             fence_async_smem();
             __syncwarp();
+#ifdef FA_CHAIN_TRACE
+            const long long tq1 = clock64();
+#endif
             if (lane == 0) {
               tma_store_2d(mc, slab, col0, p.row0 + row0);
               bulk_commit();
               bulk_wait_read<0>();
             }
+#ifdef FA_CHAIN_TRACE
+            tr_rd += clock64() - tq1;
+#endif
           } else {
             __syncwarp();
             if (my_row) {
@@ -524,6 +539,9 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
       // are long complete (wait_group N with N = the groups committed since), so the epilogue never stalls on a store.
       __syncwarp();  // the other lanes' plain stores (bf16 copy, partials, ragged rows) are ordered before lane 0's release
       if (tr) FA_CTRACE(trole, it, 4, clock64());
+#ifdef FA_CHAIN_TRACE
+      if (tr) { FA_CTRACE(trole, it, 6, tr_res); FA_CTRACE(trole, it, 7, tr_rd); }
+#endif
       const int my_groups = rows_full ? (P.kind == 0 ? BN / 32 / 2 : BN / 64 / 2) : 0;
       if (pend != nullptr) {
         if (lane == 0) {

@@ -56,7 +56,7 @@ for blk in blocks:
         m = kind == k
         if m.any():
             print(f"  {names[k]:5s}: main loop {np.mean((mma[:n, 4] - mma[:n, 3])[m]):8.0f}  first operands {np.mean((mma[:n, 3] - mma[:n, 2])[m]):7.0f}  acc-free wait {np.mean((mma[:n, 2] - mma[:n, 1])[m]):7.0f}"
-                  f"  epilogue work {np.mean((e0[:n, 4] - e0[:n, 3])[m]):8.0f}  publish {np.mean((e0[:n, 5] - e0[:n, 4])[m]):7.0f}  producer dep wait {np.mean((prod[:n, 2] - prod[:n, 1])[m]):7.0f}")
+                  f"  epilogue work {np.mean((e0[:n, 4] - e0[:n, 3])[m]):8.0f}  (residual wait {np.mean(e0[:n, 6][m]):6.0f}, store-read wait {np.mean(e0[:n, 7][m]):6.0f})  publish {np.mean((e0[:n, 5] - e0[:n, 4])[m]):7.0f}  producer dep wait {np.mean((prod[:n, 2] - prod[:n, 1])[m]):7.0f}")
     print("first 12 tiles (cycles from start): kind  prod[dep0 dep1 loads]  mma[accwait go first end]  epi[top dep full done pub]")
     for i in range(min(n, 12)):
         print(f"  {names[kind[i]]:5s} rb{int((ids[i] >> 8) & 0xffffffff):4d}  {[int(x - t0) for x in prod[i, 1:4]]}  {[int(x - t0) for x in mma[i, 1:5]]}  {[int(x - t0) for x in e0[i, 1:6]]}")
