@@ -206,6 +206,7 @@ using Step = std::function<int(const RunArgs&)>;
 // One nn.Linear resolved against fixed workspace buffers: A map (activations), one B map per tile width, C map.
 struct GemmOp {
   TensorMap2D ta, tc, tr1, tr2;
+  TensorMap2D txb;  // folded-LN producer: the bf16 copy as 32 x 32 boxes (the chain kernel stores it by TMA)
   TensorMap2D tb[3];
   bool tb_ok[3] = {false, false, false};
   int N = 0, K = 0;
@@ -322,7 +323,7 @@ struct Builder {
       for (int i = 0; i < 4; ++i) {
         const GemmOp& o = pk.op[i];
         ChainProb& c = d.p[i];
-        c.ta = &o.ta; c.tb = &o.tb[1]; c.tc = &o.tc;
+        c.ta = &o.ta; c.tb = &o.tb[1]; c.tc = &o.tc; c.txb = &o.txb;
         c.N = o.N; c.K = o.K;
         c.kind = o.epi.ln_mode == 2 ? 0 : 1;
         c.relu = o.epi.relu;
@@ -342,7 +343,11 @@ struct Builder {
     op->epi.ln_mode = ln_mode;
     op->epi.ln_stats = p->ws.stats;
     if (ln_mode == 1) { op->epi.colsum = colsum; op->epi.ln_dim = ln_dim; op->prod_N = prod_N; }
-    if (ln_mode == 2) { op->epi.xb = p->ws.xn; op->epi.ld_xb = N; }
+    if (ln_mode == 2) {
+      op->epi.xb = p->ws.xn;
+      op->epi.ld_xb = N;
+      if (int e = make_tensor_map_w(&op->txb, p->ws.xn, 2, p->cap, N, N, 32, 64)) return e;
+    }
     return 0;
   }
   void ln(std::vector<Step>& prog, const float* x, const float* g, const float* b, const float* g2, const float* b2,

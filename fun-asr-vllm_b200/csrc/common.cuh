@@ -102,6 +102,10 @@ int make_tensor_map_bf16(TensorMap2D* out, const void* base, uint64_t rows, uint
 int make_tensor_map(TensorMap2D* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld,
                     uint32_t box_rows);
 
+// box = box_rows x (box_bytes / elem_bytes) columns; box_bytes 128 (128B swizzle) or 64 (64B swizzle)
+int make_tensor_map_w(TensorMap2D* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld,
+                      uint32_t box_rows, uint32_t box_bytes);
+
 int gemm_block_n(int M, int N, int n_res);  // tile-N heuristic (64 / 128 / 256); n_res = f32 residuals in the epilogue
 // Rows [row0, row0 + M) of the A / C / residual matrices the maps describe (tr1 / tr2: f32 maps like tc, NULL when
 // epi.res1 / epi.res2 are; the epi.res* pointers only select the epilogue variant).
@@ -117,6 +121,7 @@ struct ChainProb {
   const TensorMap2D* ta;  // A [rows, K] bf16, box 128 rows x 64 columns
   const TensorMap2D* tb;  // W [N, K] bf16, box 128 rows x 64 columns (each CTA of a pair stages half of a 256-wide tile)
   const TensorMap2D* tc;  // C [rows, N]: f32 box 32 x 32 (kind 0, also the map the old C rows are read through) or bf16 box 32 x 64
+  const TensorMap2D* txb = nullptr;  // kind 0: the bf16 copy xb [rows, N], box 32 rows x 32 columns (64 bytes, 64B swizzle)
   int N = 0, K = 0;
   int kind = 0;  // 0: f32 C = acc + bias + C (+ res_bf16), xb = bf16(C), row partials -> stats (folded-LN producer)
                  // 1: bf16 C = rstd * (acc - mean * colsum) + bias (, relu) from the partials of the problem before it

@@ -34,16 +34,19 @@ constexpr int BN = 256;
 constexpr int BK = 64;
 constexpr int UMMA_K = 16;
 constexpr int EPI_WARPS = 8;
-constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;
+constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS + 32;  // + the publisher warp
+constexpr int W_PUBLISH = 2 + EPI_WARPS;
 constexpr int SLAB_BYTES = 32 * 128;
 constexpr int A_BYTES = BM * BK * 2;
 constexpr int B_BYTES = BN / 2 * BK * 2;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int STAGES = 4;
 constexpr int SLABS_BYTES = EPI_WARPS * 2 * SLAB_BYTES;  // per warp: 2 ring slots (f32 tiles) or 2 output slabs (bf16 tiles)
-constexpr int CVEC_BYTES = 28 * 1024;                    // [bias | colsum] of the LN-consumer problems, staged once per CTA
+constexpr int XSLAB_BYTES = 32 * 64;                     // bf16 copy of a 32 x 32 unit: 64-byte rows, 64B swizzle
+constexpr int XSLABS_BYTES = EPI_WARPS * XSLAB_BYTES;
 constexpr int BAR_BYTES = 1024;
-constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + SLABS_BYTES + CVEC_BYTES + BAR_BYTES;
+constexpr int PUB_RING = 8;
+constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + SLABS_BYTES + XSLABS_BYTES + BAR_BYTES;
 static_assert(SMEM_BYTES <= 227 * 1024, "chain: shared memory budget");
 constexpr int TMEM_COLS = 2 * BN;
 constexpr int MAX_PROBS = FA_CHAIN_MAX_PROBS;
@@ -57,10 +60,10 @@ constexpr int MAX_SLOTS = FA_CHAIN_MAX_SLOTS;
 #ifndef FA_CHAIN_DIST
 #define FA_CHAIN_DIST 24
 #endif
-constexpr int WARPS_PER_TILE = 2 * EPI_WARPS;  // epilogue warps of both CTAs bump a tile's counter
+constexpr int PUBS_PER_TILE = 2;  // the publisher warp of each CTA of the pair bumps a tile's counter once
 
 struct Maps {
-  CUtensorMap a[MAX_PROBS], b[MAX_PROBS], c[MAX_PROBS];
+  CUtensorMap a[MAX_PROBS], b[MAX_PROBS], c[MAX_PROBS], xb[MAX_PROBS];
 };
 
 struct Prob {
@@ -68,9 +71,8 @@ struct Prob {
   int kind;      // 0: f32 C = acc + bias + C_old (+ rb), bf16 copy + row partials (LN producer); 1: bf16 C = LN-folded epilogue
   int relu;
   int dep;       // problem whose tiles of the same row block must be complete (-1: only the previous kernel)
-  int dep_need;  // WARPS_PER_TILE * tiles_n of that problem
+  int dep_need;  // PUBS_PER_TILE * tiles_n of that problem
   int delay;     // macro steps this problem runs behind problem 0
-  int cvec_off;  // consumer: float offset of [bias | colsum] in the staged constants
   int slots;     // row partials per row (producer: N / 32 written; consumer: read)
   float inv_dim;
   const float* bias;
@@ -154,8 +156,8 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
   extern __shared__ unsigned char smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t slab_base = smem_base + STAGES * STAGE_BYTES;
-  const uint32_t cvec_base = slab_base + SLABS_BYTES;
-  const uint32_t bar_base = cvec_base + CVEC_BYTES;
+  const uint32_t xslab_base = slab_base + SLABS_BYTES;
+  const uint32_t bar_base = xslab_base + XSLABS_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
@@ -166,7 +168,11 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
   auto dep_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 4 + a); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 8);
   auto res_bar = [&](int w, int slot) { return bar_base + 8u * (2 * STAGES + 9 + w * 2 + slot); };
-  static_assert(8 * (2 * STAGES + 9 + EPI_WARPS * 2) <= BAR_BYTES, "barrier region too small");
+  // "every epilogue warp of this CTA has its part of tile number i in global memory" (ring of PUB_RING, index i % PUB_RING):
+  // the publisher warp waits here and does the gpu-scope release + counter bump, so the ~4 k cycles of that fence (measured:
+  // a fifth of the epilogue warps' time when they published themselves) are spent by a warp that has nothing else to do
+  auto pub_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 9 + EPI_WARPS * 2 + a); };
+  static_assert(8 * (2 * STAGES + 9 + EPI_WARPS * 2 + PUB_RING) <= BAR_BYTES, "barrier region too small");
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   pdl_launch_dependents();
@@ -189,6 +195,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
       prefetch_tmap(&maps.a[i]);
       prefetch_tmap(&maps.b[i]);
       prefetch_tmap(&maps.c[i]);
+      if (p.pr[i].kind == 0) prefetch_tmap(&maps.xb[i]);
     }
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar(s), 1);
@@ -199,17 +206,10 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
       mbar_init(tempty_bar(a), EPI_WARPS * 2);
     }
     for (int a = 0; a < 4; ++a) mbar_init(dep_bar(a), 1);
+    for (int a = 0; a < PUB_RING; ++a) mbar_init(pub_bar(a), EPI_WARPS);
     for (int w = 0; w < EPI_WARPS; ++w)
       for (int sl = 0; sl < 2; ++sl) mbar_init(res_bar(w, sl), 1);
     fence_mbar_init();
-  }
-  for (int i = 0; i < p.n_prob; ++i) {  // weights-side constants: not produced by any kernel of the step
-    const Prob& P = p.pr[i];
-    if (P.kind != 1) continue;
-    for (int j = threadIdx.x; j < P.N; j += NUM_THREADS) {
-      asm volatile("st.shared.f32 [%0], %1;" ::"r"(cvec_base + 4u * (P.cvec_off + j)), "f"(__ldg(P.bias + j)) : "memory");
-      asm volatile("st.shared.f32 [%0], %1;" ::"r"(cvec_base + 4u * (P.cvec_off + P.N + j)), "f"(__ldg(P.colsum + j)) : "memory");
-    }
   }
   if (warp == 1) tmem_alloc_pair<TMEM_COLS>(tmem_slot);
   tc_fence_before();
@@ -293,6 +293,19 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         ++it;
       }
     }
+  } else if (warp == W_PUBLISH) {
+    // ===================== publisher: tile complete in this CTA -> release at gpu scope, bump the tile's counter =====================
+    if (lane == 0) {
+      int it = 0;
+      for (int g = cl; g < total; g += ncl) {
+        int pi, rbk, tn;
+        if (!decode(g, pi, rbk, tn)) continue;
+        mbar_wait(pub_bar(it % PUB_RING), (it / PUB_RING) & 1);  // all eight epilogue warps: stores performed / ordered before their arrive
+        fence_proxy_async_all();
+        red_release_add(p.flags + pi * p.n_rb + rbk, 1);   // release.gpu: cumulative over what the arrivals ordered before it
+        ++it;
+      }
+    }
   } else {
     // ===================== epilogue warps =====================
     const int q = warp & 3;
@@ -301,9 +314,12 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
     const uint32_t rsw = static_cast<uint32_t>(lane & 7);
     const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
     const uint32_t my_slabs = slab_base + ew * 2 * SLAB_BYTES;
+    const uint32_t my_xslab = xslab_base + ew * XSLAB_BYTES;
+    const uint32_t xrow_off = static_cast<uint32_t>(lane) * 64u;
+    const uint32_t xsw = static_cast<uint32_t>(lane >> 1) & 3u;  // 64B swizzle: 16-byte chunk index ^ bits [8:7] of the byte offset
     int it = 0;
     int nres = 0;  // residual slabs this warp has requested so far (ring slot = nres & 1)
-    int* pend = nullptr;  // counter of the previous tile when its publication was deferred
+    int pend = -1;  // number of the previous tile when its publication was deferred
     for (int g = cl; g < total; g += ncl) {
       int pi, rbk, tn;
       if (!decode(g, pi, rbk, tn)) continue;
@@ -402,9 +418,14 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
             const float b2 = __uint_as_float(hi << 16), b3 = __uint_as_float(hi & 0xffff0000u);
             ln_s += (b0 + b1) + (b2 + b3);
             ln_ss = fmaf(b0, b0, fmaf(b1, b1, fmaf(b2, b2, fmaf(b3, b3, ln_ss))));
-            if ((j & 1) && my_row)
-              *reinterpret_cast<uint4*>(P.xb + static_cast<long long>(p.row0 + row0 + lane) * P.ld_xb + col0 + 4 * (j - 1)) =
-                  make_uint4(xbp[0], xbp[1], xbp[2], xbp[3]);
+            if (j & 1) {
+              // bf16 copy: through its own swizzled slab and a TMA store (a 16-byte store per lane with a 1 KB row pitch is 32
+              // LSU wavefronts per instruction - the f32 epilogue was LSU-bound on these); ragged last rows: straight to global
+              if (rows_full) sts128(my_xslab + xrow_off + ((static_cast<uint32_t>(j >> 1) ^ xsw) << 4), xbp[0], xbp[1], xbp[2], xbp[3]);
+              else if (my_row)
+                *reinterpret_cast<uint4*>(P.xb + static_cast<long long>(p.row0 + row0 + lane) * P.ld_xb + col0 + 4 * (j - 1)) =
+                    make_uint4(xbp[0], xbp[1], xbp[2], xbp[3]);
+            }
           }
           if (my_row) P.stats[static_cast<long long>(p.row0 + row0 + lane) * P.slots + (col0 >> 5)] = make_float2(ln_s, ln_ss);
           if (i == UH - 1) {
@@ -420,6 +441,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
 #endif
             if (lane == 0) {
               tma_store_2d(mc, slab, col0, p.row0 + row0);
+              tma_store_2d(&maps.xb[pi], my_xslab, col0, p.row0 + row0);
               bulk_commit();
               bulk_wait_read<0>();
             }
@@ -487,12 +509,13 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             const uint32_t(&r)[32] = half ? r1 : r0;
-            const uint32_t bp = cvec_base + 4u * (P.cvec_off + col0 + half * 32);
-            const uint32_t cp = bp + 4u * P.N;
+            // per-column constants: warp-uniform 16-byte loads that live in L1 after the first tile of a problem
+            const float4* bp = reinterpret_cast<const float4*>(P.bias + col0 + half * 32);
+            const float4* cp = reinterpret_cast<const float4*>(P.colsum + col0 + half * 32);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const float4 b0 = lds128(bp + 32 * j), b1 = lds128(bp + 32 * j + 16);
-              const float4 c0 = lds128(cp + 32 * j), c1 = lds128(cp + 32 * j + 16);
+              const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
+              const float4 c0 = __ldg(cp + 2 * j), c1 = __ldg(cp + 2 * j + 1);
               const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
               const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
               float v[8];
@@ -543,17 +566,15 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
       if (tr) { FA_CTRACE(trole, it, 6, tr_res); FA_CTRACE(trole, it, 7, tr_rd); }
 #endif
       const int my_groups = rows_full ? (P.kind == 0 ? BN / 32 / 2 : BN / 64 / 2) : 0;
-      if (pend != nullptr) {
+      if (pend >= 0) {
         if (lane == 0) {
           if (my_groups == 4) bulk_wait<4>();
           else if (my_groups == 2) bulk_wait<2>();
           else bulk_wait<0>();
-          fence_proxy_async_all();
-          red_release_add(pend, 1);
+          mbar_arrive(pub_bar(pend % PUB_RING));
         }
-        pend = nullptr;
+        pend = -1;
       }
-      int* mine = p.flags + pi * p.n_rb + rbk;
       bool defer = false;
       if (FA_CHAIN_PUB == 2 && p.defer > 0) {
         // this pair's next tile: deferring needs one within p.defer list positions (see the launcher), on another row block
@@ -566,20 +587,17 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         }
       }
       if (defer) {
-        pend = mine;
+        pend = it;
       } else if (lane == 0) {
         bulk_wait<0>();
-        fence_proxy_async_all();
-        if (FA_CHAIN_PUB == 0) __threadfence();
-        red_release_add(mine, 1);
+        mbar_arrive(pub_bar(it % PUB_RING));
       }
       if (tr) FA_CTRACE(trole, it, 5, clock64());
       ++it;
     }
-    if (pend != nullptr && lane == 0) {
+    if (pend >= 0 && lane == 0) {
       bulk_wait<0>();
-      fence_proxy_async_all();
-      red_release_add(pend, 1);
+      mbar_arrive(pub_bar(pend % PUB_RING));
     }
   }
 
@@ -624,7 +642,7 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
   // earlier when there are many row blocks, 1 when the launch is a handful of row blocks and latency is everything.
   const int sms = sm_count();
   const int pairs = sms / 2;
-  int n_slots = 0, cvec = 0;
+  int n_slots = 0;
   for (int i = 0; i < d.n_probs; ++i) n_slots += d.p[i].N / BN;
   FA_REQUIRE(n_slots <= MAX_SLOTS, "chain: %d tiles per row block exceed %d", n_slots, MAX_SLOTS);
   // A tile is published ~15 us after it was picked up (32 k-blocks of ffn2, epilogue, store completion, counter) and a macro
@@ -642,7 +660,7 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
     P.N = s.N; P.K = s.K; P.tiles_n = s.N / BN; P.num_kb = s.K / BK;
     P.kind = s.kind; P.relu = s.relu;
     P.dep = i - 1;
-    P.dep_need = i > 0 ? WARPS_PER_TILE * (d.p[i - 1].N / BN) : 0;
+    P.dep_need = i > 0 ? PUBS_PER_TILE * (d.p[i - 1].N / BN) : 0;
     P.delay = i * dist;
     P.bias = s.bias; P.colsum = s.colsum; P.stats = s.stats;
     P.xb = s.xb; P.ld_xb = s.ld_xb; P.rb = s.res_bf16; P.ld_rb = s.ld_res_bf16;
@@ -655,32 +673,94 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
       FA_REQUIRE(i > 0 && d.p[i - 1].kind == 0 && s.colsum && s.stats && s.K == d.p[i - 1].N, "chain: consumer %d must follow its LN producer", i);
       P.slots = d.p[i - 1].N / 32;
       P.inv_dim = 1.f / static_cast<float>(s.K);
-      P.cvec_off = cvec;
-      cvec += 2 * s.N;
     }
     memcpy(&maps.a[i], s.ta->bytes, sizeof(CUtensorMap));
     memcpy(&maps.b[i], s.tb->bytes, sizeof(CUtensorMap));
     memcpy(&maps.c[i], s.tc->bytes, sizeof(CUtensorMap));
+    if (s.kind == 0) {
+      FA_REQUIRE(s.txb != nullptr, "chain: producer %d needs the tensor map of its bf16 copy", i);
+      memcpy(&maps.xb[i], s.txb->bytes, sizeof(CUtensorMap));
+    } else {
+      maps.xb[i] = maps.c[i];
+    }
   }
-  for (int i = d.n_probs; i < MAX_PROBS; ++i) { maps.a[i] = maps.a[0]; maps.b[i] = maps.b[0]; maps.c[i] = maps.c[0]; }
-  FA_REQUIRE(cvec * 4 <= CVEC_BYTES, "chain: %d bytes of epilogue constants exceed the staged %d", cvec * 4, CVEC_BYTES);
-  // Slots of a macro step, long tiles first and the problems interleaved, so that the static round-robin deals every pair a
-  // similar mix (consecutive list positions go to consecutive pairs).
+  for (int i = d.n_probs; i < MAX_PROBS; ++i) { maps.a[i] = maps.a[0]; maps.b[i] = maps.b[0]; maps.c[i] = maps.c[0]; maps.xb[i] = maps.c[0]; }
+  // CTA pairs the device can hold at once (GPCs with an odd SM count leave a few SMs without a partner): cached per device
+  static SmemOptIn opt;
+  if (int r = opt_in_smem(chain_kernel, SMEM_BYTES, opt)) return r;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[3];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const long long tiles = static_cast<long long>(p.n_rb) * n_slots;
+  int use_pairs = pairs;
   {
-    int left[MAX_PROBS], n = 0;
-    for (int i = 0; i < d.n_probs; ++i) left[i] = d.p[i].N / BN;
-    while (n < n_slots) {
-      int best = -1;
-      double best_w = -1.0;
-      for (int i = 0; i < d.n_probs; ++i) {
-        if (left[i] == 0) continue;
-        const double w = static_cast<double>(left[i]) / (d.p[i].N / BN) + 1e-3 * d.p[i].K;  // furthest behind its share; ties: longest k loop
-        if (w > best_w) { best_w = w; best = i; }
+    static std::atomic<int> max_pairs[64];
+    int dev = 0;
+    FA_CHECK_CUDA(cudaGetDevice(&dev));
+    int mp = dev < 64 ? max_pairs[dev].load(std::memory_order_relaxed) : 0;
+    if (mp <= 0) {
+      cfg.gridDim = dim3(2 * pairs);
+      FA_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&mp, chain_kernel, &cfg));
+      FA_REQUIRE(mp > 0, "chain: the device cannot hold a single CTA pair of the chain kernel");
+      if (dev < 64) max_pairs[dev].store(mp, std::memory_order_relaxed);
+    }
+    if (use_pairs > mp) use_pairs = mp;
+  }
+  if (tiles < use_pairs) use_pairs = static_cast<int>(tiles);
+  // Slots of a macro step.  List position g goes to pair g % use_pairs, so the k-th tile of a pair sits in slot
+  // (c + k * stride) % n_slots with stride = use_pairs % n_slots: a pair walks one of gcd(stride, n_slots) cycles through the
+  // slots.  Every cycle gets its share of each problem, in the order that keeps the tensor pipe busy while an f32 epilogue
+  // (HBM round trips, ~4x its main loop) drains: f32 tiles back to back by growing K - the long main loop of ffn2 covers
+  // the epilogue of the out-projection tile before it - then the bf16 problems interleaved.
+  {
+    auto gcd = [](int a, int b) { while (b) { const int t = a % b; a = b; b = t; } return a; };
+    while (use_pairs > 1 && gcd(use_pairs % n_slots, n_slots) > 2) --use_pairs;
+    const int stride = use_pairs % n_slots;
+    const int cycles = use_pairs > 1 ? gcd(stride, n_slots) : 1;
+    bool even = true;
+    for (int i = 0; i < d.n_probs; ++i) even = even && (d.p[i].N / BN) % cycles == 0;
+    int next_tn[MAX_PROBS] = {0, 0, 0, 0};
+    if (even && use_pairs > 1) {
+      const int len = n_slots / cycles;
+      for (int c0 = 0; c0 < cycles; ++c0) {
+        int left[MAX_PROBS], seq[MAX_SLOTS], n = 0;
+        for (int i = 0; i < d.n_probs; ++i) left[i] = d.p[i].N / BN / cycles;
+        for (;;) {  // f32 problems first, by growing K
+          int best = -1;
+          for (int i = 0; i < d.n_probs; ++i)
+            if (left[i] > 0 && d.p[i].kind == 0 && (best < 0 || d.p[i].K < d.p[best].K)) best = i;
+          if (best < 0) break;
+          while (left[best] > 0) { seq[n++] = best; --left[best]; }
+        }
+        while (n < len) {  // bf16 problems: the one furthest behind its share
+          int best = -1;
+          double best_w = -1.0;
+          for (int i = 0; i < d.n_probs; ++i) {
+            if (left[i] == 0) continue;
+            const double w = static_cast<double>(left[i]) / (d.p[i].N / BN / cycles) + 1e-6 * i;
+            if (w > best_w) { best_w = w; best = i; }
+          }
+          seq[n++] = best;
+          --left[best];
+        }
+        for (int j = 0; j < len; ++j) {
+          const int slot = (c0 + j * stride) % n_slots;
+          p.slot_prob[slot] = static_cast<unsigned char>(seq[j]);
+          p.slot_tn[slot] = static_cast<unsigned char>(next_tn[seq[j]]++);
+        }
       }
-      p.slot_prob[n] = static_cast<unsigned char>(best);
-      p.slot_tn[n] = static_cast<unsigned char>(d.p[best].N / BN - left[best]);
-      --left[best];
-      ++n;
+    } else {
+      int n = 0;
+      for (int i = 0; i < d.n_probs; ++i)
+        for (int t = 0; t < d.p[i].N / BN; ++t) { p.slot_prob[n] = static_cast<unsigned char>(i); p.slot_tn[n] = static_cast<unsigned char>(t); ++n; }
     }
   }
   p.n_slots = n_slots;
@@ -693,41 +773,11 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
   p.defer = (dist - 2) * n_slots;
   if (p.defer < pairs) p.defer = 0;
   if (const char* e = getenv("FA_CHAIN_DEFER")) p.defer = atoi(e) != 0 ? p.defer : 0;
-  const long long tiles = static_cast<long long>(p.n_rb) * n_slots;
-  int use_pairs = pairs;
-  if (tiles < use_pairs) use_pairs = static_cast<int>(tiles);
-  static SmemOptIn opt;
-  if (int r = opt_in_smem(chain_kernel, SMEM_BYTES, opt)) return r;
-  cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * use_pairs);
-  cfg.blockDim = dim3(NUM_THREADS);
-  cfg.dynamicSmemBytes = SMEM_BYTES;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[3];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
   // every CTA spins on counters other CTAs of the same grid bump: all of them must be resident, whatever else is running
   // on the device (another stream's chain, the other plan of the overlapped pipeline) -> cooperative launch
   attr[1].id = cudaLaunchAttributeCooperative;
   attr[1].val.cooperative = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  {  // CTA pairs the device can hold at once (GPCs with an odd SM count leave a few SMs without a partner): cached per device
-    static std::atomic<int> max_pairs[64];
-    int dev = 0;
-    FA_CHECK_CUDA(cudaGetDevice(&dev));
-    int mp = dev < 64 ? max_pairs[dev].load(std::memory_order_relaxed) : 0;
-    if (mp <= 0) {
-      cfg.gridDim = dim3(2 * pairs);
-      FA_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&mp, chain_kernel, &cfg));
-      FA_REQUIRE(mp > 0, "chain: the device cannot hold a single CTA pair of the chain kernel");
-      if (dev < 64) max_pairs[dev].store(mp, std::memory_order_relaxed);
-    }
-    if (use_pairs > mp) use_pairs = mp;
-    cfg.gridDim = dim3(2 * use_pairs);
-  }
   cfg.numAttrs = 2;
   if (const char* e = getenv("FA_CHAIN_COOP")) {  // measurement switch: plain launch (only safe when nothing else runs on the device)
     if (atoi(e) == 0) cfg.numAttrs = 1;

@@ -688,6 +688,11 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
 // box_cols * elem_bytes == 128 (one SWIZZLE_128B span).
 int make_tensor_map(TensorMap2D* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld,
                     uint32_t box_rows) {
+  return make_tensor_map_w(out, base, elem_bytes, rows, cols, ld, box_rows, 128);
+}
+
+int make_tensor_map_w(TensorMap2D* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld,
+                      uint32_t box_rows, uint32_t box_bytes) {
   gemm::EncodeTiledFn fn = gemm::get_encode_fn();
   FA_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
   FA_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "TMA element size must be 2 or 4");
@@ -697,10 +702,12 @@ int make_tensor_map(TensorMap2D* out, const void* base, int elem_bytes, uint64_t
   CUtensorMap m;
   cuuint64_t gdim[2] = {cols, rows};
   cuuint64_t gstride[1] = {ld * elem_bytes};
-  cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / elem_bytes), box_rows};
+  FA_REQUIRE(box_bytes == 128 || box_bytes == 64, "TMA box width must be 128 or 64 bytes");
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(box_bytes / elem_bytes), box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(&m, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
-                  const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  box_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   FA_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows %llu cols %llu ld %llu)", (int)r,
              (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld);
