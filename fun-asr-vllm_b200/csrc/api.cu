@@ -359,7 +359,7 @@ struct Builder {
   }
   // fsmn_w != nullptr: the FSMN memory is produced by the attention kernel itself (bf16, beside the context: column D + c)
   void attention(std::vector<Step>& prog, const __nv_bfloat16* qkv, __nv_bfloat16* ctx, int H, int D, int ld_ctx,
-                 const float* fsmn_w = nullptr, int fsmn_left = 0, bool zero_chain = false) {
+                 const float* fsmn_w = nullptr, int fsmn_left = 0, bool zero_chain = false, float* fsmn_acc = nullptr) {
     if (rc) return;
     // one tensor map over the whole qkv buffer, encoded once per plan: utterances are addressed by their ABSOLUTE packed rows
     // (base 0).  Key / value rows past the end of a batch are workspace rows, which hold finite values (the caller hands in a
@@ -369,12 +369,13 @@ struct Builder {
     rc = make_tensor_map_bf16(&tm, qkv, cap, 3 * D, 3 * D, attention_kv_box());
     if (rc) return;
     fa_plan* pl = p;
-    prog.push_back([tm, qkv, ctx, H, D, ld_ctx, cap, fsmn_w, fsmn_left, zero_chain, pl](const RunArgs& r) {
+    prog.push_back([tm, qkv, ctx, H, D, ld_ctx, cap, fsmn_w, fsmn_left, zero_chain, pl, fsmn_acc](const RunArgs& r) {
       // the chain that follows this attention wants its dependency counters zero: this kernel clears them on its way
       const bool z = zero_chain && pl->chain;
       const int nz = gemm_chain_flag_ints(FA_CHAIN_MAX_PROBS, r.M);
       return launch_attention(&tm, qkv, 3 * D, r.cu, r.n_utts, 0, r.max_len, H, ctx, ld_ctx, cap, fsmn_w, fsmn_left,
-                              fsmn_w ? ctx + D : nullptr, ld_ctx, r.s, z ? pl->ws.chain_flags + r.lane * pl->ws.chain_ints : nullptr, z ? nz : 0);
+                              fsmn_w ? ctx + D : nullptr, ld_ctx, r.s, z ? pl->ws.chain_flags + r.lane * pl->ws.chain_ints : nullptr, z ? nz : 0,
+                              fsmn_acc, D);
     });
   }
 };
@@ -428,7 +429,11 @@ int build_programs(fa_plan* p) {
       });
     }
     // masked MHA                                                           VM:250-252,222-236
-    B.attention(E, ws.qkv, ws.ctx, c.n_heads, d, 2 * d, fuse_fsmn ? L.fsmn_w : nullptr, left, chain_ok);
+    // Layers with a residual out-projection (all but layer 0): the fused FSMN adds its memory straight into the f32 residual
+    // stream (x += mem in L2; x then += ctx Wo^T + b), so the out-projection has no memory operand to read.
+    const bool mem_into_x = fuse_fsmn && i != 0;
+    if (mem_into_x) mem = nullptr;
+    B.attention(E, ws.qkv, ws.ctx, c.n_heads, d, 2 * d, fuse_fsmn ? L.fsmn_w : nullptr, left, chain_ok, mem_into_x ? x : nullptr);
     if (chain_ok) {
       const fa_sanm_layer_w& Ln = w.layers[i + 1];
       GemmOp ops[4];

@@ -77,6 +77,8 @@ struct Params {
   int fsmn_left;
   __nv_bfloat16* mem;   // bf16 [rows, ld_mem], column h * 128 + c
   long long ld_mem;
+  float* acc;           // alternative destination: the f32 residual stream, acc[row, h * 128 + c] += memory (one vector red per
+  long long ld_acc;     // lane and row, added in L2; the out-projection then needs no memory operand at all)
   int fsmn_rows, fsmn_chunks;  // FSMN work unit = fsmn_rows output rows of one (utterance, head); chunks = ceil(max_len / rows)
   // housekeeping for the launch that follows: the dependency counters of the GEMM chain (gemm_chain.cu) must be zero on its entry
   int* zero_ints;
@@ -469,8 +471,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
       // walk i = 0 .. total-1 reads input row t0 - left + i and completes output row t0 + i - (K - 1)
       const int r0 = t0 - left, total = (t1 - t0) + K - 1;
       const char* vnext = reinterpret_cast<const char*>(p.qkv + static_cast<long long>(start + r0) * p.ld_qkv + 2 * dm + h * HD + 4 * lane);
-      char* mrow = reinterpret_cast<char*>(p.mem + static_cast<long long>(start + t0 - (K - 1)) * p.ld_mem + h * HD + 4 * lane);
-      const long long vstep = p.ld_qkv * 2, mstep = p.ld_mem * 2;
+      const bool to_acc = p.acc != nullptr;
+      char* mrow = to_acc ? reinterpret_cast<char*>(p.acc + static_cast<long long>(start + t0 - (K - 1)) * p.ld_acc + h * HD + 4 * lane)
+                          : reinterpret_cast<char*>(p.mem + static_cast<long long>(start + t0 - (K - 1)) * p.ld_mem + h * HD + 4 * lane);
+      const long long vstep = p.ld_qkv * 2, mstep = to_acc ? p.ld_acc * 4 : p.ld_mem * 2;
       auto load_row = [&](int i) -> uint2 {  // next value row in walking order (zeros outside the utterance)
         uint2 v = make_uint2(0u, 0u);
         if (static_cast<unsigned>(r0 + i) < static_cast<unsigned>(len)) v = __ldg(reinterpret_cast<const uint2*>(vnext));
@@ -491,7 +495,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
           a23[sl] = __ffma2_rn(make_float2(w4[k].z, w4[k].w), v23, a23[sl]);
         }
         const int sd = (x + 1) % K;  // this output has now seen tap K - 1
-        if (store) *reinterpret_cast<uint2*>(mrow) = make_uint2(pack_bf16x2(a01[sd].x, a01[sd].y), pack_bf16x2(a23[sd].x, a23[sd].y));
+        if (store) {
+          if (to_acc) red_add_v4_f32(reinterpret_cast<float*>(mrow), a01[sd].x, a01[sd].y, a23[sd].x, a23[sd].y);
+          else *reinterpret_cast<uint2*>(mrow) = make_uint2(pack_bf16x2(a01[sd].x, a01[sd].y), pack_bf16x2(a23[sd].x, a23[sd].y));
+        }
         mrow += mstep;
       };
       // a ring of K rows in registers: row i + K is requested as soon as row i has been consumed, so K - 1 rows of
@@ -538,15 +545,17 @@ bool attention_can_fuse_fsmn(int kernel, int64_t ld_mem, const void* mem) {
 
 int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base,
                      int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, const float* fsmn_w, int fsmn_left,
-                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream, int* zero_ints, int n_zero) {
+                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream, int* zero_ints, int n_zero, float* acc, int64_t ld_acc) {
   FA_REQUIRE(ld % 8 == 0 && ld_ctx % 8 == 0, "attention: row strides must be multiples of 8 elements");
   FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0,
              "attention: qkv and ctx must be 16-byte aligned");
   FA_REQUIRE(max_len > 0 && n_utts > 0 && n_heads > 0 && n_rows > 0, "attention: empty problem");
   FA_REQUIRE(ld >= 3 * n_heads * attn::HD, "attention: qkv rows hold q|k|v of %d heads x 128", n_heads);
   if (fsmn_w != nullptr) {
-    FA_REQUIRE(mem != nullptr && attention_can_fuse_fsmn(attn::FSMN_K, ld_mem, mem) && (reinterpret_cast<uintptr_t>(fsmn_w) & 15) == 0,
-               "attention: fused FSMN needs an 8-byte aligned bf16 memory buffer and 16-byte aligned taps");
+    FA_REQUIRE((reinterpret_cast<uintptr_t>(fsmn_w) & 15) == 0 &&
+                   (acc != nullptr ? (ld_acc % 4 == 0 && (reinterpret_cast<uintptr_t>(acc) & 15) == 0)
+                                   : (mem != nullptr && attention_can_fuse_fsmn(attn::FSMN_K, ld_mem, mem))),
+               "attention: fused FSMN needs an 8-byte aligned bf16 memory buffer (or a 16-byte aligned f32 accumulator) and 16-byte aligned taps");
     FA_REQUIRE(fsmn_left >= 0 && fsmn_left < attn::FSMN_K, "attention: FSMN left pad %d outside the %d-tap window", fsmn_left, attn::FSMN_K);
   }
   static SmemOptIn opt;
@@ -573,6 +582,7 @@ int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t
   p.qkv = qkv; p.ld_qkv = ld;
   p.fsmn_w = fsmn_w; p.fsmn_left = fsmn_left; p.mem = mem; p.ld_mem = ld_mem;
   p.zero_ints = zero_ints; p.n_zero = zero_ints ? n_zero : 0;
+  p.acc = fsmn_w ? acc : nullptr; p.ld_acc = ld_acc;
   const int n_items = n_utts * p.groups * n_heads;
   const int grid = n_items < sms ? n_items : sms;
   // FSMN units (each chunk re-reads K - 1 halo rows, so no smaller than 32 rows): whole utterances when every FSMN warp of
@@ -603,14 +613,14 @@ extern "C" int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_
 extern "C" int fa_op_attention_fsmn(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqlens_dev, int32_t n_utts,
                                     int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx,
                                     const float* fsmn_w_dev, int32_t fsmn_kernel, int32_t fsmn_left, void* mem_bf16_dev, int64_t ld_mem,
-                                    fa_stream_t stream) {
+                                    float* acc_f32_dev, int64_t ld_acc, fa_stream_t stream) {
   using namespace fa;
-  FA_REQUIRE(qkv_dev && cu_seqlens_dev && ctx_dev && fsmn_w_dev && mem_bf16_dev, "attention_fsmn: NULL pointer");
-  FA_REQUIRE(attention_can_fuse_fsmn(fsmn_kernel, ld_mem, mem_bf16_dev), "attention_fsmn: only the %d-tap kernel with 8-byte aligned memory rows is fused",
-             attn::FSMN_K);
+  FA_REQUIRE(qkv_dev && cu_seqlens_dev && ctx_dev && fsmn_w_dev && (mem_bf16_dev || acc_f32_dev), "attention_fsmn: NULL pointer");
+  FA_REQUIRE(fsmn_kernel == attn::FSMN_K && (acc_f32_dev || attention_can_fuse_fsmn(fsmn_kernel, ld_mem, mem_bf16_dev)),
+             "attention_fsmn: only the %d-tap kernel with 8-byte aligned memory rows is fused", attn::FSMN_K);
   return launch_attention(nullptr, static_cast<const __nv_bfloat16*>(qkv_dev), ld_qkv, cu_seqlens_dev, n_utts, 0, max_len, n_heads,
                           static_cast<__nv_bfloat16*>(ctx_dev), ld_ctx, n_rows, fsmn_w_dev, fsmn_left, static_cast<__nv_bfloat16*>(mem_bf16_dev),
-                          ld_mem, static_cast<cudaStream_t>(stream));
+                          ld_mem, static_cast<cudaStream_t>(stream), nullptr, 0, acc_f32_dev, ld_acc);
 }
 
 #ifdef FA_ATTN_TRACE

@@ -44,9 +44,10 @@ constexpr int STAGES = 4;
 constexpr int SLABS_BYTES = EPI_WARPS * 2 * SLAB_BYTES;  // per warp: 2 ring slots (f32 tiles) or 2 output slabs (bf16 tiles)
 constexpr int XSLAB_BYTES = 32 * 64;                     // bf16 copy of a 32 x 32 unit: 64-byte rows, 64B swizzle
 constexpr int XSLABS_BYTES = EPI_WARPS * XSLAB_BYTES;
+constexpr int CVEC_BYTES = 2 * 2 * BN * 4;               // [bias | colsum] of a bf16 tile's 256 columns, two tiles deep
 constexpr int BAR_BYTES = 1024;
 constexpr int PUB_RING = 8;
-constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + SLABS_BYTES + XSLABS_BYTES + BAR_BYTES;
+constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + SLABS_BYTES + XSLABS_BYTES + CVEC_BYTES + BAR_BYTES;
 static_assert(SMEM_BYTES <= 227 * 1024, "chain: shared memory budget");
 constexpr int TMEM_COLS = 2 * BN;
 constexpr int MAX_PROBS = FA_CHAIN_MAX_PROBS;
@@ -157,7 +158,8 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t slab_base = smem_base + STAGES * STAGE_BYTES;
   const uint32_t xslab_base = slab_base + SLABS_BYTES;
-  const uint32_t bar_base = xslab_base + XSLABS_BYTES;
+  const uint32_t cvec_base = xslab_base + XSLABS_BYTES;
+  const uint32_t bar_base = cvec_base + CVEC_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
@@ -320,6 +322,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
     int it = 0;
     int nres = 0;  // residual slabs this warp has requested so far (ring slot = nres & 1)
     int pend = -1;  // number of the previous tile when its publication was deferred
+    int nbf = 0;    // bf16 tiles this warp has seen (parity = constants buffer)
     for (int g = cl; g < total; g += ncl) {
       int pi, rbk, tn;
       if (!decode(g, pi, rbk, tn)) continue;
@@ -467,6 +470,16 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         nres = nres0 + UH;
       } else {
         // ---- bf16 tile: rstd * (acc - mean * colsum) + bias (, relu) with the row's statistics from the producer's partials
+        // The tile's 256 bias / colsum values go to shared memory first (one of each per epilogue thread; buffer = parity of
+        // the warp's bf16-tile count, so a warp that runs ahead never overwrites what a slower one still reads): broadcast
+        // LDS in the inner loop instead of L1 round trips (4.7 k against 3.1 k cycles per tile measured).
+        const uint32_t cv = cvec_base + static_cast<uint32_t>(nbf & 1) * (2 * BN * 4);
+        {
+          const int c = (ew << 5) | lane;
+          asm volatile("st.shared.f32 [%0], %1;" ::"r"(cv + 4u * c), "f"(__ldg(P.bias + tn * BN + c)) : "memory");
+          asm volatile("st.shared.f32 [%0], %1;" ::"r"(cv + 4u * (BN + c)), "f"(__ldg(P.colsum + tn * BN + c)) : "memory");
+        }
+        ++nbf;
         float ln_rs, ln_nm;
         {
           float s = 0.f, ss = 0.f;
@@ -493,6 +506,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
           ln_rs = rsqrtf(fmaxf(fmaf(-mu, mu, ss * P.inv_dim), 0.f) + 1e-12f);
           ln_nm = -ln_rs * mu;
         }
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");  // the eight epilogue warps: constants of this tile staged
         if (tr) FA_CTRACE(trole, it, 2, clock64());
         mbar_wait(tfull_bar(acc), acc_phase);
         if (tr) FA_CTRACE(trole, it, 3, clock64());
@@ -509,13 +523,12 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             const uint32_t(&r)[32] = half ? r1 : r0;
-            // per-column constants: warp-uniform 16-byte loads that live in L1 after the first tile of a problem
-            const float4* bp = reinterpret_cast<const float4*>(P.bias + col0 + half * 32);
-            const float4* cp = reinterpret_cast<const float4*>(P.colsum + col0 + half * 32);
+            const uint32_t bp = cv + 4u * (u * 64 + half * 32);
+            const uint32_t cp = bp + 4u * BN;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
-              const float4 c0 = __ldg(cp + 2 * j), c1 = __ldg(cp + 2 * j + 1);
+              const float4 b0 = lds128(bp + 32 * j), b1 = lds128(bp + 32 * j + 16);
+              const float4 c0 = lds128(cp + 32 * j), c1 = lds128(cp + 32 * j + 16);
               const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
               const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
               float v[8];

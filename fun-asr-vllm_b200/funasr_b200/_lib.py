@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfunasr_b200.so")
-ABI_VERSION = 8
+ABI_VERSION = 9
 FE_TILE_ROWS = 5  # FA_FE_TILE_ROWS
 
 i32, i64, f32, vp, sz = C.c_int32, C.c_int64, C.c_float, C.c_void_p, C.c_size_t
@@ -78,7 +78,7 @@ PROTOTYPES = {
     "fa_op_fsmn": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, i32, i32, i32, i32, vp]),
     "fa_op_fsmn_bf16": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, i64, i32, i32, i32, i32, vp]),
     "fa_op_attention": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, vp, i64, vp]),
-    "fa_op_attention_fsmn": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, vp, i64, vp, i32, i32, vp, i64, vp]),
+    "fa_op_attention_fsmn": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, vp, i64, vp, i32, i32, vp, i64, vp, i64, vp]),
 }
 
 PROFILE_KINDS = ("frontend", "gemm", "attention", "layernorm", "fsmn", "repack", "splice")

@@ -44,7 +44,7 @@ extern "C" {
 
 typedef void* fa_stream_t; /* cudaStream_t */
 
-#define FA_ABI_VERSION 8
+#define FA_ABI_VERSION 9
 
 int fa_abi_version(void);
 const char* fa_last_error(void);
@@ -128,9 +128,10 @@ typedef struct {
   const void* qkv_w;    /* bf16 [3*d_model, d_in|d_model]   self_attn.linear_q_k_v.weight */
   const float* qkv_b;   /* [3*d_model] */
   const float* fsmn_w;  /* f32 [fsmn_kernel, d_model] TAP-MAJOR = self_attn.fsmn_block.weight[d_model,1,K] transposed */
-  const void* out_w;    /* bf16 [d_model, d_model]           self_attn.linear_out.weight.  The FSMN memory is kept in bf16
-                           beside the attention context and added to the f32 result by this GEMM's epilogue
-                           (VLLM/model_executor/models/funasr.py:253 `att_outs + fsmn_memory`). */
+  const void* out_w;    /* bf16 [d_model, d_model]           self_attn.linear_out.weight.  The FSMN memory
+                           (VLLM/model_executor/models/funasr.py:253 `att_outs + fsmn_memory`) is added by the attention kernel
+                           straight into the f32 residual stream; layer 0 (no residual) keeps it in bf16 beside the attention
+                           context and this GEMM's epilogue adds it. */
   const float* out_b;
   const float* ln2_g;
   const float* ln2_b;
@@ -315,11 +316,13 @@ int fa_op_attention(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqle
                     int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx, fa_stream_t stream);
 /* attention and the FSMN memory of the same value rows in ONE kernel (the plan's form): ctx as above, and
  * mem[r, h*128 + c] bf16 (row stride ld_mem) = v + depthwise_conv_time(v), w f32 [11, H*128] tap-major, `fsmn_left` rows of
- * left context.  Only the model's 11-tap kernel is fused (FA_ERR_INVALID otherwise).  VLLM/...:181-201,222-252 */
+ * left context.  Only the model's 11-tap kernel is fused (FA_ERR_INVALID otherwise).  VLLM/...:181-201,222-252
+ * acc_f32_dev != NULL (the plan's form for every block with a residual out-projection): the memory is not stored but ADDED,
+ * in f32, to acc[r, h*128 + c] (row stride ld_acc) - the residual stream - and mem_bf16_dev may be NULL. */
 int fa_op_attention_fsmn(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_seqlens_dev, int32_t n_utts,
                          int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx,
                          const float* fsmn_w_dev, int32_t fsmn_kernel, int32_t fsmn_left, void* mem_bf16_dev,
-                         int64_t ld_mem, fa_stream_t stream);
+                         int64_t ld_mem, float* acc_f32_dev, int64_t ld_acc, fa_stream_t stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

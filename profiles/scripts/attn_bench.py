@@ -60,7 +60,7 @@ def main():
 
         def fused():
             _lib.check(lib.fa_op_attention_fsmn(qkv.data_ptr(), 3 * dm, cu_d.data_ptr(), len(lens), mx, H, M, cm.data_ptr(), 2 * dm,
-                                                w.data_ptr(), 11, 5, cm.data_ptr() + 2 * dm, 2 * dm, st))
+                                                w.data_ptr(), 11, 5, cm.data_ptr() + 2 * dm, 2 * dm, None, 0, st))
 
         def fsmn():
             _lib.check(lib.fa_op_fsmn_bf16(qkv.data_ptr(), 3 * dm, 2 * dm, w.data_ptr(), cu_d.data_ptr(), len(lens),

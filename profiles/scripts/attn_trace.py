@@ -41,7 +41,7 @@ def main():
     def run():
         if mode == "fused":
             _lib.check(lib.fa_op_attention_fsmn(qkv.data_ptr(), 3 * dm, cu_d.data_ptr(), len(lens), max(lens), H, M, cm.data_ptr(),
-                                                2 * dm, w.data_ptr(), 11, 5, cm.data_ptr() + 2 * dm, 2 * dm, st))
+                                                2 * dm, w.data_ptr(), 11, 5, cm.data_ptr() + 2 * dm, 2 * dm, None, 0, st))
         else:
             _lib.check(lib.fa_op_attention(qkv.data_ptr(), 3 * dm, cu_d.data_ptr(), len(lens), max(lens), H, M, cm.data_ptr(), 2 * dm, st))
 

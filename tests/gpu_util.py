@@ -117,15 +117,17 @@ def op_attention(qkv_bf16, cu, n_heads):
     return ctx
 
 
-def op_attention_fsmn(qkv_bf16, w, cu, n_heads, left):
-    """ctx|mem [M, 2*dm] bf16 from the fused kernel (the plan's layout: memory beside the context)."""
+def op_attention_fsmn(qkv_bf16, w, cu, n_heads, left, acc=None):
+    """ctx|mem [M, 2*dm] bf16 from the fused kernel (the plan's layout: memory beside the context).  ``acc`` (f32 [M, dm]):
+    the memory is added to it instead (the plan's form for blocks with a residual out-projection) and mem stays zero."""
     M = qkv_bf16.shape[0]
     dm = n_heads * 128
     cm = torch.zeros((M, 2 * dm), dtype=torch.bfloat16, device="cuda")
     cu_d = dev(cu)
     _lib.check(lib().fa_op_attention_fsmn(qkv_bf16.data_ptr(), qkv_bf16.stride(0), cu_d.data_ptr(), len(cu) - 1,
                                           int(np.diff(cu).max()), n_heads, M, cm.data_ptr(), 2 * dm, w.data_ptr(), w.shape[0], left,
-                                          cm.data_ptr() + 2 * dm, 2 * dm, stream()))
+                                          cm.data_ptr() + 2 * dm, 2 * dm, _lib.ptr(acc), acc.stride(0) if acc is not None else 0,
+                                          stream()))
     return cm
 
 

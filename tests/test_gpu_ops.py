@@ -303,6 +303,12 @@ def test_attention_fsmn_fused(U, lens, H, left):
     alone = U.op_fsmn_bf16(qkv.cuda(), 2 * dm, wt, cu, dm, K, left).cpu()
     assert torch.equal(cm[:, dm:].cpu(), alone[:, dm:])
     assert torch.equal(cm[:, :dm].cpu(), U.op_attention(qkv.cuda(), cu, H).cpu())  # the FSMN warps do not perturb attention
+    # the plan's form for blocks with a residual: x += memory, in f32, straight from the FSMN warps (one add per element)
+    x0 = torch.randn(M, dm, generator=g)
+    x = x0.clone().cuda()
+    cm2 = U.op_attention_fsmn(qkv.cuda(), wt, cu, H, left, acc=x)
+    assert torch.equal(cm2[:, :dm], cm[:, :dm]) and not cm2[:, dm:].any()
+    assert (x.cpu() - (x0 + want_mem)).abs().max().item() < 1e-4 * max(1.0, want_mem.abs().max().item())
 
 
 def test_attention_fsmn_rejects_other_kernels(U):
