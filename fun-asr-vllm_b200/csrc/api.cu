@@ -268,7 +268,8 @@ struct fa_plan {
   int cap;
   int n_streams;        // 1: everything on the caller's stream; 2: two half-batches, the second on `aux` (fork/join by events)
   int graph_max_rows;   // batches of up to this many rows replay a captured CUDA graph of the program (0: never)
-  int chain = 1;        // 1: the row-local GEMMs between two attention kernels run as ONE launch (gemm_chain.cu)
+  int chain = 0;        // 1: the row-local GEMMs between two attention kernels run as ONE launch (gemm_chain.cu); measured slower
+                        // than one launch per GEMM so far (profiles/r02/chain_r2ae.md), so it is opt-in
   cudaStream_t aux = nullptr;
   cudaStream_t cap_stream = nullptr;  // only ever used in capture mode: nothing executes on it
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;

@@ -203,11 +203,13 @@ int fa_plan_set_streams(fa_plan* plan, int32_t n_streams);
  * up to 48 graphs are kept per plan, least recently used first out.  max_rows == 0 turns replay off; larger batches use the
  * dual-stream schedule above.  Needs a workspace that was zero-filled before fa_plan_create (rows past the end of a batch
  * are computed on whatever the workspace holds and must stay finite). */
-/* Chain schedule (new, on by default).  The GEMMs between two attention kernels of the encoder - out-projection, ffn1, ffn2
+/* Chain schedule (new, opt-in).  The GEMMs between two attention kernels of the encoder - out-projection, ffn1, ffn2
  * of block i and the qkv projection of block i + 1 - touch every token row on its own, so they run as ONE cooperative launch
  * whose tiles wait on per-row-block counters instead of on grid boundaries (csrc/gemm_chain.cu): three launch boundaries
  * per block disappear and the FFN hidden rows are consumed out of L2.  Same tile arithmetic: results are bit-identical to
- * on == 0 (one launch per GEMM).  Environment override at plan creation: FA_CHAIN=0. */
+ * on == 0 (one launch per GEMM, the default: on B200 the chain's pipeline fill and drain - three dependent stages of ~20 us
+ * each per launch - and its f32 epilogues still cost more than the launch boundaries they replace, profiles/r02/chain_r2ae.md).
+ * Environment override at plan creation: FA_CHAIN=1. */
 int fa_plan_set_chain(fa_plan* plan, int32_t on);
 #define FA_DEFAULT_GRAPH_ROWS 8192
 int fa_plan_set_graph_rows(fa_plan* plan, int32_t max_rows);

@@ -62,13 +62,19 @@ def main():
             _lib.check(lib.fa_op_attention_fsmn(qkv.data_ptr(), 3 * dm, cu_d.data_ptr(), len(lens), mx, H, M, cm.data_ptr(), 2 * dm,
                                                 w.data_ptr(), 11, 5, cm.data_ptr() + 2 * dm, 2 * dm, None, 0, st))
 
+        xacc = torch.zeros((M, dm), dtype=torch.float32, device="cuda")
+
+        def fused_acc():  # the memory added straight into an f32 residual stream (vector red) instead of the bf16 store
+            _lib.check(lib.fa_op_attention_fsmn(qkv.data_ptr(), 3 * dm, cu_d.data_ptr(), len(lens), mx, H, M, cm.data_ptr(), 2 * dm,
+                                                w.data_ptr(), 11, 5, None, 0, xacc.data_ptr(), dm, st))
+
         def fsmn():
             _lib.check(lib.fa_op_fsmn_bf16(qkv.data_ptr(), 3 * dm, 2 * dm, w.data_ptr(), cu_d.data_ptr(), len(lens),
                                            cm.data_ptr() + 2 * dm, 2 * dm, M, dm, 11, 5, st))
 
         bytes_attn = M * 3 * dm * 2 + M * dm * 2
         out[name] = {"rows": M, "utts": len(lens), "attention_us": round(time_it(attn, flush, iters), 1),
-                     "fused_us": round(time_it(fused, flush, iters), 1), "fsmn_us": round(time_it(fsmn, flush, iters), 1),
+                     "fused_us": round(time_it(fused, flush, iters), 1), "fused_acc_us": round(time_it(fused_acc, flush, iters), 1), "fsmn_us": round(time_it(fsmn, flush, iters), 1),
                      "hbm_floor_us": round((bytes_attn + M * dm * 2) / 6458.1e3, 1)}
         print(name, json.dumps(out[name]), flush=True)
 
