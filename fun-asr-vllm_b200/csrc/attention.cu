@@ -142,6 +142,10 @@ __device__ __forceinline__ void trace(int ev, int a, int b) {
 #endif
 
 // ---------------------------------------------------------------- kernel
+// ACC: the FSMN memory is added into the f32 residual stream (p.acc) instead of being stored as bf16 (p.mem).  Compile-time:
+// with both stores in one instruction stream the walk over the value rows lost its load pipelining (141 against 108 us per
+// layer at 1 h of 10 s utterances, profiles/r02/attn_r2af.txt).
+template <bool ACC>
 __global__ void __launch_bounds__(THREADS, 1)
 attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
   extern __shared__ unsigned char smem_raw[];
@@ -471,7 +475,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
       // walk i = 0 .. total-1 reads input row t0 - left + i and completes output row t0 + i - (K - 1)
       const int r0 = t0 - left, total = (t1 - t0) + K - 1;
       const char* vnext = reinterpret_cast<const char*>(p.qkv + static_cast<long long>(start + r0) * p.ld_qkv + 2 * dm + h * HD + 4 * lane);
-      const bool to_acc = p.acc != nullptr;
+      constexpr bool to_acc = ACC;
       char* mrow = to_acc ? reinterpret_cast<char*>(p.acc + static_cast<long long>(start + t0 - (K - 1)) * p.ld_acc + h * HD + 4 * lane)
                           : reinterpret_cast<char*>(p.mem + static_cast<long long>(start + t0 - (K - 1)) * p.ld_mem + h * HD + 4 * lane);
       const long long vstep = p.ld_qkv * 2, mstep = to_acc ? p.ld_acc * 4 : p.ld_mem * 2;
@@ -559,7 +563,11 @@ int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t
     FA_REQUIRE(fsmn_left >= 0 && fsmn_left < attn::FSMN_K, "attention: FSMN left pad %d outside the %d-tap window", fsmn_left, attn::FSMN_K);
   }
   static SmemOptIn opt;
-  if (int r = opt_in_smem(attn::attention_kernel, attn::SMEM_BYTES, opt)) return r;
+  static SmemOptIn opt_acc;
+  const bool use_acc = fsmn_w != nullptr && acc != nullptr;
+  if (int r = use_acc ? opt_in_smem(attn::attention_kernel<true>, attn::SMEM_BYTES, opt_acc)
+                      : opt_in_smem(attn::attention_kernel<false>, attn::SMEM_BYTES, opt))
+    return r;
   // Without a prebuilt map: rows = the valid packed rows only, so key/value rows past the end are zero-filled by TMA instead
   // of reading memory whose contents are undefined (NaN there would leak into O through 0 * NaN).
   TensorMap2D tm;
@@ -595,7 +603,8 @@ int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t
   p.fsmn_rows = ceil_div(max_len, fs_chunks) < 32 ? 32 : ceil_div(max_len, fs_chunks);
   p.fsmn_chunks = ceil_div(max_len, p.fsmn_rows);
   ProfScope _ps(K_ATTENTION, stream);
-  FA_CHECK_CUDA(launch_pdl(attn::attention_kernel, dim3(grid), dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, p));
+  if (use_acc) FA_CHECK_CUDA(launch_pdl(attn::attention_kernel<true>, dim3(grid), dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, p));
+  else FA_CHECK_CUDA(launch_pdl(attn::attention_kernel<false>, dim3(grid), dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, p));
   return 0;
 }
 

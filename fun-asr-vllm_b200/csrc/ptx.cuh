@@ -118,7 +118,8 @@ __device__ __forceinline__ uint4 ldg_nc_v4(const uint4* p) {
 
 // four adjacent f32 += (a, b, c, d), performed in L2, nothing returned (16-byte aligned)
 __device__ __forceinline__ void red_add_v4_f32(float* p, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+  // (no "memory" clobber: the compiler may keep unrelated loads in flight across it)
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d));
 }
 
 // ---------------------------------------------------------------- clusters
