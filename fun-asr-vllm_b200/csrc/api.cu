@@ -249,7 +249,6 @@ int run_gemm_op(const GemmOp& op, const RunArgs& a) {
   FA_REQUIRE(bn != 0 && op.tb_ok[idx], "gemm N=%d unsupported", op.N);
   const bool pair = gemm_use_pair(a.M, bn) && op.tb_ok[1];
   GemmEpilogue epi = op.epi;
-  if (epi.ln_mode == 2) epi.txb = &op.txb;
   if (epi.ln_mode == 1) epi.ln_slots = op.prod_N / 32;  // the producer leaves one partial per 32 columns of its output
   return launch_gemm(op.ta, op.tb[pair ? 1 : idx], op.tc, epi.res1 ? &op.tr1 : nullptr, epi.res2 ? &op.tr2 : nullptr, bn, a.M,
                      op.N, op.K, epi, op.c, op.ldc, a.row0, pair, a.s);
@@ -303,11 +302,7 @@ struct Builder {
     op.epi.ln_mode = ln_mode;
     if (ln_mode != 0) op.epi.ln_stats = p->ws.stats;
     if (ln_mode == 1) { op.epi.colsum = colsum; op.epi.ln_dim = ln_dim; op.prod_N = prod_N; }
-    if (ln_mode == 2) {
-      op.epi.xb = p->ws.xn;
-      op.epi.ld_xb = N;
-      if (!rc) rc = make_tensor_map_w(&op.txb, p->ws.xn, 2, p->cap, N, N, 32, 64);
-    }
+    if (ln_mode == 2) { op.epi.xb = p->ws.xn; op.epi.ld_xb = N; }
     if (!rc) prog.push_back([op](const RunArgs& r) { return run_gemm_op(op, r); });
   }
   // Layer i's out-projection, ffn1, ffn2 and layer i+1's qkv as one step: the chain launch when the plan's switch is on,
@@ -437,8 +432,7 @@ int build_programs(fa_plan* p) {
     // masked MHA                                                           VM:250-252,222-236
     // Layers with a residual out-projection (all but layer 0): the fused FSMN adds its memory straight into the f32 residual
     // stream (x += mem in L2; x then += ctx Wo^T + b), so the out-projection has no memory operand to read.
-    static const bool into_x_enabled = [] { const char* e = getenv("FA_MEM_INTO_X"); return e == nullptr || atoi(e) != 0; }();  // measurement switch
-    const bool mem_into_x = fuse_fsmn && i != 0 && into_x_enabled;
+    const bool mem_into_x = fuse_fsmn && i != 0;
     if (mem_into_x) mem = nullptr;
     B.attention(E, ws.qkv, ws.ctx, c.n_heads, d, 2 * d, fuse_fsmn ? L.fsmn_w : nullptr, left, chain_ok, mem_into_x ? x : nullptr);
     if (chain_ok) {

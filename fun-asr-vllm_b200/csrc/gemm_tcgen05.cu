@@ -44,7 +44,7 @@ constexpr int BAR_BYTES = 512;
 // CTA stages its own 128 rows of A and only HALF of the B tile, so the operand bytes an SM pulls through its 64 B/clk
 // L2 port drop from 48 KB to 32 KB per 128x256x64 of MMA work (ncu, profiles/r01_e_campaign.md: the 1-CTA kernel moves
 // 54 B/clk/SM into the SMs at 63 % tensor-pipe activity, i.e. it is L2->SM ingress bound).
-template <int BN, int NRES, int CTAS, bool OUT_F32, bool XB = false>
+template <int BN, int NRES, int CTAS, bool OUT_F32>
 struct Cfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN / CTAS * BK * 2;
@@ -58,11 +58,7 @@ struct Cfg {
 #define FA_BF16_SLABS 2
 #endif
   static constexpr int SLABS_PER_WARP = NRES == 0 ? (OUT_F32 ? 1 : FA_BF16_SLABS) : RING * NRES;
-  // XB (folded-LN producer): one more slab per warp, 32 rows x 64 B (64B swizzle), for the bf16 copy of a unit: it leaves by
-  // TMA with the f32 rows.  (As 16-byte stores per lane with a 1 KB row pitch it cost 32 LSU wavefronts per instruction and
-  // made the epilogue LSU-bound: 90 against 64 us for the out-projection with and without the LN outputs.)
-  static constexpr int XSLAB_BYTES = 32 * 64;
-  static constexpr int SLABS_BYTES = EPI_WARPS * (SLABS_PER_WARP * SLAB_BYTES + (XB ? XSLAB_BYTES : 0));
+  static constexpr int SLABS_BYTES = EPI_WARPS * SLABS_PER_WARP * SLAB_BYTES;
   // bf16 output: bias (and the folded-LN column sums) of all N columns are staged in smem once per CTA, so the epilogue's
   // per-column constants are short-latency broadcast LDS instead of L1 round trips (ncu: a fifth of its stall samples)
   static constexpr int CVEC_BYTES = OUT_F32 ? 0 : 16384;
@@ -106,8 +102,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_r1,
                  const __grid_constant__ CUtensorMap tmap_r2, const Params p) {
-  // (LN == 2: tmap_r2 is not a residual - NRES is 1 - but the 32 x 32 bf16 map of the bf16 copy xb)
-  using C = Cfg<BN, NRES, CTAS, OUT_F32, LN == 2>;
+  using C = Cfg<BN, NRES, CTAS, OUT_F32>;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024B alignment
   const uint32_t slab_base = smem_base + C::STAGES * C::STAGE_BYTES;  // 1024-aligned: STAGE_BYTES is a multiple of 1024
@@ -296,9 +291,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       constexpr int LAG = RES_RING >= 3 ? 1 : 0;  // stores allowed to be still reading their slab when the next load is issued
       constexpr uint32_t SLOT_BYTES = NRES * SLAB_BYTES;
       const uint32_t ring = slab_base + ew * RES_RING * SLOT_BYTES;
-      [[maybe_unused]] const uint32_t xslab = slab_base + EPI_WARPS * RES_RING * SLOT_BYTES + ew * C::XSLAB_BYTES;
-      [[maybe_unused]] const uint32_t xrow_off = static_cast<uint32_t>(lane) * 64u;
-      [[maybe_unused]] const uint32_t xsw = static_cast<uint32_t>(lane >> 1) & 3u;  // 64B swizzle: chunk ^ bits [8:7] of the offset
       const int my_tiles = (num_tiles - cl + ncl - 1) / ncl;
       const int total = my_tiles * UH;
       auto coords = [&](int n, int& row0, int& col0, int& u) {
@@ -386,12 +378,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const float b2 = __uint_as_float(hi << 16), b3 = __uint_as_float(hi & 0xffff0000u);
             ln_s += (b0 + b1) + (b2 + b3);
             ln_ss = fmaf(b0, b0, fmaf(b1, b1, fmaf(b2, b2, fmaf(b3, b3, ln_ss))));
-            if (j & 1) {
-              if (row0 + 32 <= p.M) sts128(xslab + xrow_off + ((static_cast<uint32_t>(j >> 1) ^ xsw) << 4), xbp[0], xbp[1], xbp[2], xbp[3]);
-              else if (row0 + lane < p.M)  // ragged last rows of the launch: straight to global
-                *reinterpret_cast<uint4*>(p.xb + static_cast<long long>(p.row0 + row0 + lane) * p.ld_xb + col0 + 4 * (j - 1)) =
-                    make_uint4(xbp[0], xbp[1], xbp[2], xbp[3]);
-            }
+            if ((j & 1) && row0 + lane < p.M)
+              *reinterpret_cast<uint4*>(p.xb + static_cast<long long>(p.row0 + row0 + lane) * p.ld_xb + col0 + 4 * (j - 1)) =
+                  make_uint4(xbp[0], xbp[1], xbp[2], xbp[3]);
           }
         }
         if constexpr (LN == 2) {
@@ -414,7 +403,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if (lane == 0) {
             if (p.accumulate) tma_reduce_add_2d(&tmap_c, slab, col0, p.row0 + row0);
             else tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
-            if constexpr (LN == 2) tma_store_2d(&tmap_r2, xslab, col0, p.row0 + row0);
             bulk_commit();
             bulk_wait_read<LAG>();  // the store that left slot (n + RES_RING - LAG) % RES_RING has read its slab
           }
@@ -617,7 +605,7 @@ static EncodeTiledFn get_encode_fn() {
 template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS, int LN>
 static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mr1,
                     const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
-  using C = Cfg<BN, NRES, CTAS, OUT_F32, LN == 2>;
+  using C = Cfg<BN, NRES, CTAS, OUT_F32>;
   auto kern = gemm_bf16_kernel<BN, OUT_F32, RELU, NRES, CTAS, LN>;
   static SmemOptIn opt;  // one per kernel instantiation
   if (int r = opt_in_smem(kern, C::SMEM_BYTES, opt)) return r;
@@ -671,15 +659,6 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   memcpy(&mc, tc.bytes, sizeof(mc));
   memcpy(&mr1, (tr1 ? tr1 : &tc)->bytes, sizeof(mr1));
   memcpy(&mr2, (tr2 ? tr2 : &tc)->bytes, sizeof(mr2));
-  if (epi.ln_mode == 2) {  // the bf16 copy leaves by TMA: its 32 x 32 map travels in the (unused) second-residual slot
-    TensorMap2D txb_local;
-    const TensorMap2D* txb = epi.txb;
-    if (txb == nullptr) {
-      if (int r = make_tensor_map_w(&txb_local, epi.xb, 2, static_cast<uint64_t>(row0) + M, N, epi.ld_xb, 32, 64)) return r;
-      txb = &txb_local;
-    }
-    memcpy(&mr2, txb->bytes, sizeof(mr2));
-  }
   FA_REQUIRE((epi.res1 == nullptr) == (tr1 == nullptr) && (epi.res2 == nullptr) == (tr2 == nullptr),
              "gemm: every residual needs its tensor map");
   ProfScope _ps(K_GEMM, stream);
