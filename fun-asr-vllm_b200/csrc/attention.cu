@@ -18,8 +18,8 @@
 // MMA results it waits for are S of its own block (issued two blocks ahead) and, on the rare block that raises the running
 // maximum by more than 2^8, the P V products so far (O is then rescaled once in TMEM).  All 512 TMEM columns are used:
 // S[2 tiles][2 buffers] x 64 + O[2 tiles] x 128.
-// Warp roles (12 warps): 0..1 FSMN, 2..5 softmax / epilogue of query tile 0, 6..9 of query tile 1, 10 TMA producer, 11 MMA
-// issuer (+ TMEM alloc).  The producer runs ahead across work items (next item's Q as soon as the last S of the current one
+// Warp roles (16 warps, four warpgroups): 0..3 FSMN, 4..7 softmax / epilogue of query tile 0, 8..11 of query tile 1, 12 TMA
+// producer, 13 MMA issuer (+ TMEM alloc), 14..15 idle.  The producer runs ahead across work items (next item's Q as soon as the last S of the current one
 // has been issued, K/V as stages free up), every role has the next item's cu_seqlens loads in flight while it works on the
 // current one, and the epilogue of one item (O -> ctx) overlaps the first S MMAs of the next: nothing is set up or torn
 // down per work item.
@@ -39,15 +39,23 @@ constexpr int BQ = 128;   // query rows per tile = UMMA M
 constexpr int BKV = 64;   // keys per block
 constexpr int NST = 3;    // K/V stages
 constexpr int NQ = 2;     // query tiles per work item (at most)
-#ifndef FA_ATTN_FSMN_WARPS
-#define FA_ATTN_FSMN_WARPS 2
+// Four warpgroups (setmaxnreg works on aligned groups of four warps): 0 = FSMN filler warps, 1 and 2 = softmax / epilogue of
+// query tiles 0 and 1 (TMEM lane quarter = warp id mod 4), 3 = TMA producer, MMA issuer and two idle warps.  The kernel is
+// compiled for 128 registers per thread (512 threads); the control group hands its registers back (40 each) and the softmax
+// groups take 168, which they need to hold a 64-key S row in registers.  The FSMN walk is bound by the bytes one warp can
+// keep in flight (11 rows x 256 B): two warps per CTA took as long as the whole attention pipeline (fused 113 us against 72 us
+// for attention alone at 1 h of 10 s utterances), hence four.
+constexpr int FSMN_WARPS = 4;   // each takes every FSMN_WARPS-th FSMN unit of its CTA
+constexpr int THREADS = 16 * 32;
+#ifndef FA_ATTN_REGS
+#define FA_ATTN_REGS 168, 40, 136
 #endif
-constexpr int FSMN_WARPS = FA_ATTN_FSMN_WARPS;   // filler warps (ids 0, 1 and 12 ..): each takes every FSMN_WARPS-th FSMN unit of its CTA
-constexpr int THREADS = (10 + FSMN_WARPS) * 32;
+constexpr int REGS_[3] = {FA_ATTN_REGS};
+constexpr int REGS_SOFTMAX = REGS_[0], REGS_CONTROL = REGS_[1], REGS_FSMN = REGS_[2];  // 128 x 136 + 256 x 168 + 128 x 40 = the whole register file
 // Warp ids by role.  The issue arbiter of a sub-partition favours its higher warp ids: the two latency-critical single-lane
 // roles sit on top, the FSMN filler warps at the bottom (they only take slots nobody else wants); the softmax warps keep
-// ids 2..9 (TMEM lane quarter = warp id mod 4).
-constexpr int W_FSMN = 0, W_PRODUCER = 10, W_MMA = 11;
+// ids 4..11 (TMEM lane quarter = warp id mod 4).
+constexpr int W_FSMN = 0, W_SOFTMAX = 4, W_PRODUCER = 12, W_MMA = 13;
 constexpr int FSMN_K = 11;                 // taps compiled into the fused path (the model's kernel_size)
 constexpr int QPANEL = BQ * 128;           // [128 rows x 64 bf16] 128B-swizzled panel = 16 KB
 constexpr int KPANEL = BKV * 128;          // [64 rows x 64 bf16] panel = 8 KB
@@ -200,6 +208,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
   pdl_wait();  // qkv comes from the previous kernel
   for (int i = blockIdx.x * THREADS + threadIdx.x; i < p.n_zero; i += gridDim.x * THREADS) p.zero_ints[i] = 0;
 
+  if (warp >= W_PRODUCER) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS_CONTROL));  // the whole control warpgroup, idle warps included
   if (warp == W_PRODUCER) {
     // ===================== TMA producer =====================
     // (producer and MMA warps run their loops with all 32 lanes - waits and counters are warp-uniform - and elect one lane
@@ -301,9 +311,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
       gk0 += it.nb;
       ++n_it;
     });
-  } else if (warp >= 2 && warp < 10) {
+  }
+  } else if (warp >= W_SOFTMAX) {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_SOFTMAX));
     // ===================== softmax / epilogue warpgroups: thread = query row of tile q =====================
-    const int q = (warp - 2) >> 2;
+    const int q = (warp - W_SOFTMAX) >> 2;
     const int quarter = warp & 3;                   // TMEM lane quarter this warp may access (hardware: warp id mod 4)
     const int row = quarter * 32 + lane;            // row within the tile == TMEM lane
     const uint32_t lane_sel = static_cast<uint32_t>(quarter * 32) << 16;
@@ -439,8 +451,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
       }
     });
   } else if (fsmn_on) {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_FSMN));
     // ===================== FSMN warps: mem[t, c] = v[t, c] + sum_k w[k, c] v[t + k - left, c] ==============================
-    // Two filler warps per CTA that share NOTHING with the attention pipeline (no barrier, no shared memory): they stream
+    // Four filler warps per CTA that share NOTHING with the attention pipeline (no barrier, no shared memory): they stream
     // value rows straight from global memory - the same rows the TMA producers pull for P V at about the same time, so one
     // of the two reads hits L2 and V still crosses HBM once per layer - using issue slots the softmax warps leave idle.
     // lane = 4 adjacent channels of the head's 128 (one 8-byte load per row); a unit's rows are walked ONCE, in order: an
@@ -450,7 +463,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
     // arithmetic as the stand-alone kernel.  Rows outside the utterance enter as zeros (VLLM/...:181-201: mask,
     // ConstantPad1d, depthwise Conv1d, + inputs, mask).
     constexpr int K = FSMN_K;
-    const int f = warp < 2 ? warp : warp - 10;
+    const int f = warp - W_FSMN;
     const int left = p.fsmn_left;
     // FSMN work units are independent of the attention work items: (utterance, head, chunk of fsmn_rows output rows), dealt
     // round-robin to every FSMN warp of the grid, so that a small batch still spreads over all of them.
