@@ -248,3 +248,33 @@ def test_overlapped_pipeline_is_invisible():
         torch.cuda.synchronize()
         assert np.array_equal(cu0, cu1)
         assert torch.equal(got, want)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_two_devices_in_one_process():
+    """kernel attributes (dynamic shared memory opt-in) and the SM count are per DEVICE; one process that drives two
+    GPUs must get the same results on the second one (the frontend, the plan and every kernel class run on cuda:1 after
+    cuda:0 has used them)."""
+    import funasr_b200 as fb
+    from oracle import encoder as oe
+
+    conf = dict(oe.NANO_ENCODER_CONF, num_blocks=2, tp_blocks=1)
+    o_enc = oe.seeded_init_(oe.SenseVoiceEncoderSmall(560, **conf), seed=4321)
+    o_ad = oe.seeded_init_(oe.Transformer(**oe.NANO_ADAPTOR_CONF), seed=4322)
+    g = torch.Generator().manual_seed(3)
+    wavs = [0.5 * (2 * torch.rand(n, generator=g) - 1) for n in (16000, 32000, 8000)]
+    outs = []
+    for dev in ("cuda:0", "cuda:1"):
+        enc, ad = fb.SenseVoiceEncoderSmall(560, **conf), fb.Transformer(**oe.NANO_ADAPTOR_CONF)
+        enc.load_state_dict(o_enc.state_dict())
+        ad.load_state_dict(o_ad.state_dict())
+        enc.to(dev), ad.to(dev)
+        fe = fb.WavFrontend(window="povey", lfr_m=7, lfr_n=6, dither=0.0, device=dev)
+        with torch.cuda.device(dev):
+            feats, lens = fb.extract_fbank(wavs, frontend=fe, is_final=True)
+            y, ol = enc(feats, lens)
+            z, _ = ad(y, ol)
+            torch.cuda.synchronize()
+        assert z.device == torch.device(dev)
+        outs.append(z.cpu())
+    assert torch.equal(outs[0], outs[1])
