@@ -1,8 +1,6 @@
 #!/bin/bash
 set -u
-O=gpurun_out/r2ai
+O=gpurun_out/r2al
 mkdir -p $O
-timeout 300 python -m pytest tests/test_gpu_ops.py -x -q -k "attention" 2>&1 | tail -2
-python profiles/scripts/attn_bench.py 20 cfg5 cfg2 cfg3 long > $O/attn.txt 2>&1; cat $O/attn.txt
-timeout 200 python bench.py --no-cpu-baseline --no-extras > $O/bench.json 2> $O/bench.err; python -c "
-import json; d=json.load(open('$O/bench.json')); print(d['ms_per_step'], d['e2e']['ms_per_step'], d['kernel_ms_per_step'])"
+python profiles/scripts/attn_bench.py 20 cfg5 long > $O/attn.txt 2>&1; cat $O/attn.txt
+python profiles/scripts/with_lib.py ftop profiles/scripts/attn_bench.py 20 cfg5 long > $O/attn_ftop.txt 2>&1; cat $O/attn_ftop.txt
