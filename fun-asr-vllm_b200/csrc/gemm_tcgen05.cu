@@ -54,10 +54,7 @@ struct Cfg {
   // no residual: bf16 output (K = d_model GEMMs, little main-loop time per tile) gets two slabs so a store drains while the
   // next unit is produced; the f32 accumulate output (K = d_ff) keeps one slab and one more operand stage
   static constexpr int RING = res_ring(NRES);
-#ifndef FA_BF16_SLABS
-#define FA_BF16_SLABS 2
-#endif
-  static constexpr int SLABS_PER_WARP = NRES == 0 ? (OUT_F32 ? 1 : FA_BF16_SLABS) : RING * NRES;
+  static constexpr int SLABS_PER_WARP = NRES == 0 ? (OUT_F32 ? 1 : 2) : RING * NRES;
   static constexpr int SLABS_BYTES = EPI_WARPS * SLABS_PER_WARP * SLAB_BYTES;
   // bf16 output: bias (and the folded-LN column sums) of all N columns are staged in smem once per CTA, so the epilogue's
   // per-column constants are short-latency broadcast LDS instead of L1 round trips (ncu: a fifth of its stall samples)

@@ -91,6 +91,16 @@ if which in ("attn", "all"):
         fl = 4 * H * 128 * float((np.array(lens, dtype=np.float64) ** 2).sum())
         print(f"attention H={H} T={lens[0]} x{len(lens)}: best {best*1e3:.1f} us -> {fl/best/1e9:.0f} TFLOP/s")
 
+if which in ("attnfsmn", "all"):
+    # the plan's form: attention + FSMN memory in one kernel, the memory added into the f32 residual stream
+    lens = [167] * 360
+    cu = U.cu_of(lens)
+    qkv = torch.randn(M, 1536, device="cuda").to(torch.bfloat16)
+    wt = (torch.randn(11, 512, device="cuda") / 3.3)
+    x = torch.zeros(M, 512, device="cuda")
+    best, avg = timeit(lambda: U.op_attention_fsmn(qkv, wt, cu, 4, 5, acc=x))
+    print(f"attention+fsmn (memory into x) H=4 T=167 x360: best {best*1e3:.1f} us avg {avg*1e3:.1f} us -> {(M*1536*2 + M*512*2 + M*512*8)/best/1e6:.0f} GB/s algorithmic")
+
 if which in ("fsmn", "all"):
     cu = U.cu_of([167] * 360)
     qkv = torch.randn(M, 1536, device="cuda").to(torch.bfloat16)
