@@ -52,12 +52,6 @@ static_assert(SMEM_BYTES <= 227 * 1024, "chain: shared memory budget");
 constexpr int TMEM_COLS = 2 * BN;
 constexpr int MAX_PROBS = FA_CHAIN_MAX_PROBS;
 constexpr int MAX_SLOTS = FA_CHAIN_MAX_SLOTS;
-#ifndef FA_CHAIN_PUB
-#define FA_CHAIN_PUB 2  // 2: deferred publication; 1: immediate; 0: immediate with an extra __threadfence (measurement builds)
-#endif
-#ifndef FA_CHAIN_L2PF
-#define FA_CHAIN_L2PF 1
-#endif
 #ifndef FA_CHAIN_DIST
 #define FA_CHAIN_DIST 24
 #endif
@@ -238,7 +232,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         mbar_arrive(dep_bar(it & 3));
         FA_CTRACE(0, it, 2, clock64());
         const int arow = p.row0 + (rbk * 2 + static_cast<int>(rank)) * BM;
-        if (FA_CHAIN_L2PF && P.kind == 0) {
+        if (P.kind == 0) {
           // The f32 epilogue is a chain of dependent round trips (old C rows in, new rows out, per 32-column unit): ask L2
           // for the tile's old rows now, a main loop ahead, so those round trips end in L2 instead of HBM.
           for (int r4 = 0; r4 < BM / 32; ++r4)
@@ -589,7 +583,7 @@ chain_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p
         pend = -1;
       }
       bool defer = false;
-      if (FA_CHAIN_PUB == 2 && p.defer > 0) {
+      if (p.defer > 0) {
         // this pair's next tile: deferring needs one within p.defer list positions (see the launcher), on another row block
         for (int g2 = g + ncl; g2 < total && g2 - g <= p.defer; g2 += ncl) {
           int pi2, rb2, tn2;
@@ -663,7 +657,6 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
   // (measured with 2 steps at 11 row blocks: 118 us per chain against 45 us for four launches).  Few row blocks: problem-major
   // order (dist = n_rb), i.e. four launches' worth of tiles without the three grid hand-overs.
   int dist = FA_CHAIN_DIST;
-  if (const char* e = getenv("FA_CHAIN_DIST")) dist = atoi(e) > 0 ? atoi(e) : dist;  // measurement switch
   if (dist > p.n_rb) dist = p.n_rb;
   for (int i = 0; i < d.n_probs; ++i) {
     const ChainProb& s = d.p[i];
@@ -705,7 +698,7 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
   cfg.blockDim = dim3(NUM_THREADS);
   cfg.dynamicSmemBytes = SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[3];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
@@ -785,23 +778,12 @@ int launch_gemm_chain(const ChainDesc& d, int M, int row0, int* flags, cudaStrea
   // problem-major order of small launches: there the publication is immediate.)
   p.defer = (dist - 2) * n_slots;
   if (p.defer < pairs) p.defer = 0;
-  if (const char* e = getenv("FA_CHAIN_DEFER")) p.defer = atoi(e) != 0 ? p.defer : 0;
   cfg.gridDim = dim3(2 * use_pairs);
   // every CTA spins on counters other CTAs of the same grid bump: all of them must be resident, whatever else is running
   // on the device (another stream's chain, the other plan of the overlapped pipeline) -> cooperative launch
   attr[1].id = cudaLaunchAttributeCooperative;
   attr[1].val.cooperative = 1;
   cfg.numAttrs = 2;
-  if (const char* e = getenv("FA_CHAIN_COOP")) {  // measurement switch: plain launch (only safe when nothing else runs on the device)
-    if (atoi(e) == 0) cfg.numAttrs = 1;
-  }
-  if (const char* e = getenv("FA_CHAIN_PDL")) {  // measurement switch: programmatic dependent launch on top
-    if (atoi(e) != 0) {
-      attr[cfg.numAttrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-      attr[cfg.numAttrs].val.programmaticStreamSerializationAllowed = 1;
-      ++cfg.numAttrs;
-    }
-  }
   ProfScope _ps(K_GEMM, stream);
   FA_CHECK_CUDA(cudaLaunchKernelEx(&cfg, chain_kernel, maps, p));
   return 0;
