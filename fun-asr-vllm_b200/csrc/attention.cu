@@ -41,15 +41,15 @@ constexpr int NST = 3;    // K/V stages
 constexpr int NQ = 2;     // query tiles per work item (at most)
 // Four warpgroups (setmaxnreg works on aligned groups of four warps): 0 = FSMN filler warps, 1 and 2 = softmax / epilogue of
 // query tiles 0 and 1 (TMEM lane quarter = warp id mod 4), 3 = TMA producer, MMA issuer and two idle warps.  The kernel is
-// compiled for 128 registers per thread (512 threads); the control group hands its registers back (40 each), the softmax
-// groups take 160 (a 64-key S row lives in registers) and the FSMN group 152 (taps, accumulators and an 11-row ring): no spills.  The FSMN walk is bound by the bytes one warp can
+// compiled for 128 registers per thread (512 threads); the control group hands most of its registers back (56 each), the softmax
+// groups take 152 (a 64-key S row lives in registers) and the FSMN group 152 (taps, accumulators and an 11-row ring): no spills.  The FSMN walk is bound by the bytes one warp can
 // keep in flight (11 rows x 256 B): two warps per CTA took as long as the whole attention pipeline (fused 113 us against 72 us
 // for attention alone at 1 h of 10 s utterances), hence four.
 constexpr int FSMN_WARPS = 4;   // each takes every FSMN_WARPS-th FSMN unit of its CTA
 constexpr int THREADS = 16 * 32;
 #ifndef FA_ATTN_RS
-#define FA_ATTN_RS 160
-#define FA_ATTN_RC 40
+#define FA_ATTN_RS 152
+#define FA_ATTN_RC 56
 #define FA_ATTN_RF 152
 #endif
 constexpr int REGS_SOFTMAX = FA_ATTN_RS, REGS_CONTROL = FA_ATTN_RC, REGS_FSMN = FA_ATTN_RF;
@@ -64,7 +64,10 @@ constexpr int KPANEL = BKV * 128;          // [64 rows x 64 bf16] panel = 8 KB
 constexpr int QT_BYTES = 2 * QPANEL;       // one query tile: d = 128 -> two panels
 constexpr int K_BYTES = 2 * KPANEL;
 constexpr int V_BYTES = 2 * KPANEL;
-constexpr int P_BYTES = QPANEL;            // P_qj: 128 rows x 64 keys bf16, one panel
+#ifndef FA_ATTN_P_TMEM
+#define FA_ATTN_P_TMEM 1  // P handed to the P V product through tensor memory (over the S columns it was computed from); 0: through smem
+#endif
+constexpr int P_BYTES = FA_ATTN_P_TMEM ? 0 : QPANEL;  // (smem form) P_qj: 128 rows x 64 keys bf16, one panel
 constexpr int BAR_BYTES = 512;
 constexpr int SMEM_BYTES = NQ * QT_BYTES + NST * (K_BYTES + V_BYTES) + NQ * 2 * P_BYTES + 1024 + BAR_BYTES;
 constexpr int TMEM_COLS = 512;             // S[q][buf] at (2q + buf) * 64, O[q] at 256 + 128 q
@@ -137,16 +140,18 @@ __device__ __forceinline__ void for_items(const Params& p, int n_items, Body&& b
 
 // ---------------------------------------------------------------- pipeline trace (make TRACE=1: profiling builds only)
 #ifdef FA_ATTN_TRACE
-__device__ unsigned long long g_trace[1 << 16];
-__device__ unsigned int g_trace_n;
-// event | item | block/tile | SM clock, CTA 0 only
-__device__ __forceinline__ void trace(int ev, int a, int b) {
-  if (blockIdx.x == 0 && ((threadIdx.x & 31) == 0 || threadIdx.x >= 64)) {
-    const unsigned int i = atomicAdd(&g_trace_n, 1u);
-    if (i < (1u << 16)) g_trace[i] = (static_cast<unsigned long long>(clock64()) << 24) | ((ev & 0xff) << 16) | ((a & 0xff) << 8) | (b & 0xff);
+// SM clock | event | item | block/tile, CTA 0 only, lane 0 of a warp.  One region per warp and a counter in a register: plain
+// stores, no atomics (an atomicAdd per event put a ~700-cycle L2 round trip into the role that was being timed).
+constexpr int TRACE_PER_WARP = 4096;
+__device__ unsigned long long g_trace[16 * TRACE_PER_WARP];
+__device__ __forceinline__ void trace(int& tn, int ev, int a, int b) {
+  if (blockIdx.x == 0 && (threadIdx.x & 31) == 0 && tn < TRACE_PER_WARP) {
+    g_trace[(threadIdx.x >> 5) * TRACE_PER_WARP + tn] =
+        (static_cast<unsigned long long>(clock64()) << 24) | ((ev & 0xff) << 16) | ((a & 0xff) << 8) | (b & 0xff);
+    ++tn;
   }
 }
-#define FA_TRACE(ev, a, b) trace(ev, a, b)
+#define FA_TRACE(ev, a, b) trace(tn, ev, a, b)
 #else
 #define FA_TRACE(ev, a, b)
 #endif
@@ -161,6 +166,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
   extern __shared__ unsigned char smem_raw[];
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef FA_ATTN_TRACE
+  int tn = 0;
+#endif
   const int dm = p.n_heads * HD;
   const int n_items = p.n_utts * p.groups * p.n_heads;
 
@@ -251,6 +259,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
   } else if (warp == W_MMA) {
     // ===================== MMA issuer =====================
     int n_it = 0, gk0 = 0;
+    // low words of the shared-memory descriptors of Q tile 0, K / V stage 0 and P buffer (0, 0); the high word is the same for
+    // all of them (SBO 1024 B, version 1, 128B swizzle)
+    const uint32_t q_lo = static_cast<uint32_t>(desc_kmajor(sQ(0))), k_lo = static_cast<uint32_t>(desc_kmajor(sK(0)));
+    const uint32_t p_lo = static_cast<uint32_t>(desc_kmajor(sP(0, 0))), v_lo = static_cast<uint32_t>(desc_mnmajor(sV(0), KPANEL, 1024));
+    constexpr uint32_t desc_hi = static_cast<uint32_t>((static_cast<uint64_t>(1024 >> 4) << 32 | (1ull << 46) | (2ull << 61)) >> 32);
+    auto mk_desc = [&](uint32_t lo) { return (static_cast<uint64_t>(desc_hi) << 32) | lo; };
     int cs0 = 0, cs1 = 0;  // S blocks issued per query tile
     int cp0 = 0, cp1 = 0;  // P V blocks issued per query tile
     for_items(p, n_items, [&](const Item& it) {
@@ -263,10 +277,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
           const int nkeys = min(BKV, it.len - j * BKV);
           const uint32_t idesc = make_idesc(BQ, (nkeys + 15) & ~15, 0);
           const uint32_t d = tS(q, cs & 1);
+          // descriptors: only the 14-bit address field (bytes >> 4) changes from one MMA to the next, so each one is a 32-bit
+          // add on a precomputed low word (the timeline showed the issuing thread, not the tensor pipe, bounding the kernel:
+          // ~85 cycles per S MMA and ~185 per P V MMA went into assembling 64-bit descriptors in a dependent chain)
+          const uint32_t aq = q_lo + static_cast<uint32_t>(q) * (QT_BYTES >> 4), bk = k_lo + static_cast<uint32_t>(st) * (K_BYTES >> 4);
 #pragma unroll
           for (int k = 0; k < HD / 16; ++k)
-            umma_f16(d, desc_kmajor(sQ(q) + (k >> 2) * QPANEL + (k & 3) * 32), desc_kmajor(sK(st) + (k >> 2) * KPANEL + (k & 3) * 32),
-                     idesc, k != 0);
+            umma_f16(d, mk_desc(aq + (k >> 2) * (QPANEL >> 4) + (k & 3) * 2), mk_desc(bk + (k >> 2) * (KPANEL >> 4) + (k & 3) * 2), idesc, k != 0);
           umma_commit(s_full(q, cs & 1));
           if (j == it.nb - 1 && q == it.nq - 1) umma_commit(q_empty);  // the producer may overwrite Q
         }
@@ -294,9 +311,16 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
           // the TMEM loads and only then produced the P this MMA waits for)
           tc_fence_after();
           if (elect_one()) {
-            const uint32_t idesc = make_idesc(BQ, HD, 1);
-            for (int k = 0; k < ksteps; ++k)  // O_q (+)= P_qj V_j
-              umma_f16(tO(q), desc_kmajor(sP(q, cp & 1) + k * 32), desc_mnmajor(sV(st) + k * 16 * 128, KPANEL, 1024), idesc, (j | k) != 0);
+            constexpr uint32_t idesc = make_idesc(BQ, HD, 1);
+            const uint32_t ap = p_lo + static_cast<uint32_t>(2 * q + (cp & 1)) * (P_BYTES >> 4), bv = v_lo + static_cast<uint32_t>(st) * (V_BYTES >> 4);
+            const uint32_t d = tO(q);
+#pragma unroll
+            for (int k = 0; k < BKV / 16; ++k)  // O_q (+)= P_qj V_j
+              if (k < ksteps) {
+                // A = P: 16 keys = 8 columns of packed bf16 pairs, over the first half of the S buffer the softmax read
+                if (FA_ATTN_P_TMEM) umma_f16_ts(d, tS(q, cp & 1) + k * 8, mk_desc(bv + k * (16 * 128 >> 4)), idesc, (j | k) != 0);
+                else umma_f16(d, mk_desc(ap + k * 2), mk_desc(bv + k * (16 * 128 >> 4)), idesc, (j | k) != 0);
+              }
             umma_commit(pv_done(q, cp & 1));
             if (q == it.nq - 1) umma_commit(kv_empty(st));  // K_j / V_j are free once everything issued so far has retired
           }
@@ -310,6 +334,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
           for (int q = 0; q < it.nq; ++q) issue_s(q, j + 2);
         }
       }
+      FA_TRACE(16, n_it, 0);
       gk0 += it.nb;
       ++n_it;
     });
@@ -387,8 +412,38 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
             tmem_st32(tO(q) + lane_sel + x * 32, o);
           }
         }
+#if FA_ATTN_P_TMEM
+        // ---- p = exp2(s c - m), row sum, bf16 pairs -> tensor memory, over the S columns this thread has just read: the A
+        // operand of the P V MMA (M = 128 lanes = query rows, 2 keys per 32-bit column).  The tensor pipe runs its MMAs in order,
+        // so the S MMA that next writes these columns (block c + 2) comes after the P V product that reads them.  No smem P
+        // buffer, no proxy fence; the P V MMA reads only V from shared memory (its operand traffic was what paced it).
+        {
+          uint32_t pk[32];
+          float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+          const int nch16 = (nkeys + 15) >> 4;  // 16-key MMA steps that will be issued
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2) {
+            if (row_ok && h2 * 2 < nch16) {
+#pragma unroll
+              for (int x = 0; x < 32; x += 2) {
+                const float p0 = ex2(fmaf(r[h2][x], p.scale_log2e, -m_used));      // masked keys: 2^-inf = 0
+                const float p1 = ex2(fmaf(r[h2][x + 1], p.scale_log2e, -m_used));
+                rs4[(x >> 1) & 3] += p0 + p1;
+                pk[h2 * 16 + (x >> 1)] = pack_bf16x2(p0, p1);
+              }
+            } else {
+#pragma unroll
+              for (int x = 0; x < 16; ++x) pk[h2 * 16 + x] = 0u;
+            }
+          }
+          l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
+          tmem_st32(tS(q, buf) + lane_sel, pk);  // (warp-wide: rows past the end of the utterance store zeros)
+        }
+#else
         // P_q[buf] was last read by the P V product of block c - 2
+        if ((threadIdx.x & 127) == 64) FA_TRACE(13, c, q);
         if (c >= 2) mbar_wait(pv_done(q, buf), par ^ 1u);
+        if ((threadIdx.x & 127) == 64) FA_TRACE(14, c, q);
         // ---- p = exp2(s c - m), row sum, bf16 -> swizzled smem (A operand of the P V MMA).
         // Rows past the end of the utterance skip the arithmetic: their P rows only feed O rows that are never stored.
         if (row_ok) {
@@ -413,7 +468,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
           }
           l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
         }
-        fence_async_smem();
+#endif
+        if (!FA_ATTN_P_TMEM) fence_async_smem();
         tc_fence_before();
         mbar_arrive(p_full(q, buf));
         if ((threadIdx.x & 127) == 64) FA_TRACE(7, c, q);
@@ -451,6 +507,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
           }
         }
       }
+      if ((threadIdx.x & 127) == 64) FA_TRACE(15, c, q);
     });
   } else if (fsmn_on) {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_FSMN));
@@ -650,14 +707,12 @@ extern "C" int fa_op_attention_fsmn(const void* qkv_dev, int64_t ld_qkv, const i
 #ifdef FA_ATTN_TRACE
 // profiling builds only: copies the trace of CTA 0 to the host and clears it; returns the number of events
 extern "C" __attribute__((visibility("default"))) int fa_debug_attention_trace(unsigned long long* dst_host, int cap) {
-  unsigned int n = 0;
+  int n = 16 * fa::attn::TRACE_PER_WARP;
+  if (n > cap) n = cap;
   cudaDeviceSynchronize();
-  cudaMemcpyFromSymbol(&n, fa::attn::g_trace_n, sizeof(n));
-  if (n > (1u << 16)) n = 1u << 16;
-  if (static_cast<int>(n) > cap) n = cap;
   cudaMemcpyFromSymbol(dst_host, fa::attn::g_trace, n * sizeof(unsigned long long));
-  const unsigned int zero = 0;
-  cudaMemcpyToSymbol(fa::attn::g_trace_n, &zero, sizeof(zero));
-  return static_cast<int>(n);
+  static unsigned long long zeros[16 * fa::attn::TRACE_PER_WARP];
+  cudaMemcpyToSymbol(fa::attn::g_trace, zeros, sizeof(zeros));
+  return n;
 }
 #endif

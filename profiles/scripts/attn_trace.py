@@ -17,7 +17,7 @@ import gpu_util as U  # noqa: E402
 from attn_bench import shapes  # noqa: E402
 
 EV = {1: "Q  issue", 2: "KV issue", 3: "S  issue", 4: "PV issue", 5: "sm wait", 6: "sm go", 7: "P  ready", 8: "epi go",
-      9: "fs vfull", 10: "fs rel", 11: "mma item", 12: "mma qfull"}
+      9: "fs vfull", 10: "fs rel", 11: "mma item", 12: "mma qfull", 13: "sm pbuf?", 14: "sm pbuf!", 15: "epi end", 16: "mma done"}
 
 
 def main():
@@ -33,6 +33,7 @@ def main():
     w = (torch.randn(11, dm, generator=g) / 3.3).cuda()
     cu_d = U.dev(cu)
     cm = torch.zeros((M, 2 * dm), dtype=torch.bfloat16, device="cuda")
+    xacc = torch.zeros((M, dm), dtype=torch.float32, device="cuda")
     lib, st = U.lib(), U.stream()
     lib.fa_debug_attention_trace.restype = C.c_int
     lib.fa_debug_attention_trace.argtypes = [C.c_void_p, C.c_int]
@@ -41,7 +42,7 @@ def main():
     def run():
         if mode == "fused":
             _lib.check(lib.fa_op_attention_fsmn(qkv.data_ptr(), 3 * dm, cu_d.data_ptr(), len(lens), max(lens), H, M, cm.data_ptr(),
-                                                2 * dm, w.data_ptr(), 11, 5, cm.data_ptr() + 2 * dm, 2 * dm, None, 0, st))
+                                                2 * dm, w.data_ptr(), 11, 5, None, 0, xacc.data_ptr(), dm, st))
         else:
             _lib.check(lib.fa_op_attention(qkv.data_ptr(), 3 * dm, cu_d.data_ptr(), len(lens), max(lens), H, M, cm.data_ptr(), 2 * dm, st))
 
@@ -50,7 +51,8 @@ def main():
     lib.fa_debug_attention_trace(buf.ctypes.data, len(buf))
     run()
     n = lib.fa_debug_attention_trace(buf.ctypes.data, len(buf))
-    ev = [(int(x) >> 24, (int(x) >> 16) & 0xff, (int(x) >> 8) & 0xff, int(x) & 0xff) for x in buf[:n]]
+    ev = [(int(x) >> 24, (int(x) >> 16) & 0xff, (int(x) >> 8) & 0xff, int(x) & 0xff) for x in buf[:n] if x != 0]
+    n = len(ev)
     ev.sort()
     t0 = ev[0][0]
     print(f"{mode} {name}: {n} events, CTA 0 span {ev[-1][0] - t0} cycles")
@@ -63,7 +65,7 @@ def main():
     lo, hi = first, first + count
     for t, e, a, b in ev:
         # a = item for producer/MMA events, block counter c for the softmax, global block for the FSMN
-        item = a if e in (1, 2, 3, 4, 11, 12) else a // nb
+        item = a if e in (1, 2, 3, 4, 11, 12, 16) else a // nb
         if lo <= item < hi:
             print(f"{t - t0:9d}  {EV.get(e, e):9s} a={a:3d} b={b:3d}")
 

@@ -1,10 +1,8 @@
 #!/bin/bash
 set -u
-O=gpurun_out/r2ap
+O=gpurun_out/r2av
 mkdir -p $O
-for wl in cfg2 cfg3; do
-for v in default fx96 fx160; do
-if [ $v = default ]; then cmd="python bench.py"; else cmd="python profiles/scripts/with_lib.py $v bench.py"; fi
-timeout 200 $cmd --no-cpu-baseline --no-extras --workload $wl > $O/bench_${v}_$wl.json 2> $O/err.txt; python -c "
-import json; d=json.load(open('$O/bench_${v}_$wl.json')); print('$wl $v', round(d['ms_per_step'],3), round(d['e2e']['ms_per_step'],3), d['kernel_ms_per_step']['gemm'])"
-done; done
+timeout 300 python -m pytest tests/test_gpu_ops.py -x -q -k "attention" 2>&1 | tail -3
+python profiles/scripts/attn_bench.py 20 cfg5 cfg2 cfg3 long > $O/attn.txt 2>&1; cat $O/attn.txt
+python profiles/scripts/with_lib.py psmem profiles/scripts/attn_bench.py 20 cfg5 cfg2 cfg3 long > $O/attn_psmem.txt 2>&1; cat $O/attn_psmem.txt
+timeout 600 python -m pytest tests -m gpu -x -q --deselect tests/test_gpu_zz_vllm_greedy.py 2>&1 | tail -2
