@@ -369,14 +369,17 @@ struct Builder {
     const int cap = p->cap;
     rc = make_tensor_map_bf16(&tm, qkv, cap, 3 * D, 3 * D, attention_kv_box());
     if (rc) return;
+    TensorMap2D tmc;  // the context rows as 32 x 64 boxes for the epilogue's TMA stores
+    rc = make_tensor_map(&tmc, ctx, 2, cap, D, ld_ctx, 32);
+    if (rc) return;
     fa_plan* pl = p;
-    prog.push_back([tm, qkv, ctx, H, D, ld_ctx, cap, fsmn_w, fsmn_left, zero_chain, pl, fsmn_acc](const RunArgs& r) {
+    prog.push_back([tm, tmc, qkv, ctx, H, D, ld_ctx, cap, fsmn_w, fsmn_left, zero_chain, pl, fsmn_acc](const RunArgs& r) {
       // the chain that follows this attention wants its dependency counters zero: this kernel clears them on its way
       const bool z = zero_chain && pl->chain;
       const int nz = gemm_chain_flag_ints(FA_CHAIN_MAX_PROBS, r.M);
       return launch_attention(&tm, qkv, 3 * D, r.cu, r.n_utts, 0, r.max_len, H, ctx, ld_ctx, cap, fsmn_w, fsmn_left,
                               fsmn_w ? ctx + D : nullptr, ld_ctx, r.s, z ? pl->ws.chain_flags + r.lane * pl->ws.chain_ints : nullptr, z ? nz : 0,
-                              fsmn_acc, D);
+                              fsmn_acc, D, &tmc);
     });
   }
 };

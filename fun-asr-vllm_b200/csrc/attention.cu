@@ -64,12 +64,9 @@ constexpr int KPANEL = BKV * 128;          // [64 rows x 64 bf16] panel = 8 KB
 constexpr int QT_BYTES = 2 * QPANEL;       // one query tile: d = 128 -> two panels
 constexpr int K_BYTES = 2 * KPANEL;
 constexpr int V_BYTES = 2 * KPANEL;
-#ifndef FA_ATTN_P_TMEM
-#define FA_ATTN_P_TMEM 1  // P handed to the P V product through tensor memory (over the S columns it was computed from); 0: through smem
-#endif
-constexpr int P_BYTES = FA_ATTN_P_TMEM ? 0 : QPANEL;  // (smem form) P_qj: 128 rows x 64 keys bf16, one panel
+constexpr int O_BYTES = 2 * QPANEL;        // epilogue staging of one query tile: 128 rows x 128 bf16 = two swizzled panels
 constexpr int BAR_BYTES = 512;
-constexpr int SMEM_BYTES = NQ * QT_BYTES + NST * (K_BYTES + V_BYTES) + NQ * 2 * P_BYTES + 1024 + BAR_BYTES;
+constexpr int SMEM_BYTES = NQ * QT_BYTES + NST * (K_BYTES + V_BYTES) + NQ * O_BYTES + 1024 + BAR_BYTES;
 constexpr int TMEM_COLS = 512;             // S[q][buf] at (2q + buf) * 64, O[q] at 256 + 128 q
 constexpr float RESCALE_THRESHOLD = 8.f;   // log2 units
 static_assert(SMEM_BYTES <= 227 * 1024, "attention: shared memory budget");
@@ -162,7 +159,7 @@ __device__ __forceinline__ void trace(int& tn, int ev, int a, int b) {
 // layer at 1 h of 10 s utterances, profiles/r02/attn_r2af.txt).
 template <bool ACC>
 __global__ void __launch_bounds__(THREADS, 1)
-attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
+attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_ctx, const Params p) {
   extern __shared__ unsigned char smem_raw[];
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -173,12 +170,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
   const int n_items = p.n_utts * p.groups * p.n_heads;
 
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sQ0 = sbase, sK0 = sQ0 + NQ * QT_BYTES, sV0 = sK0 + NST * K_BYTES, sP0 = sV0 + NST * V_BYTES;
-  const uint32_t bars = sP0 + NQ * 2 * P_BYTES;
+  const uint32_t sQ0 = sbase, sK0 = sQ0 + NQ * QT_BYTES, sV0 = sK0 + NST * K_BYTES, sO0 = sV0 + NST * V_BYTES;
+  const uint32_t bars = sO0 + NQ * O_BYTES;
   auto sQ = [&](int q) { return sQ0 + q * QT_BYTES; };
   auto sK = [&](int st) { return sK0 + st * K_BYTES; };
   auto sV = [&](int st) { return sV0 + st * V_BYTES; };
-  auto sP = [&](int q, int buf) { return sP0 + (2 * q + buf) * P_BYTES; };
+  auto sO = [&](int q) { return sO0 + q * O_BYTES; };
   const uint32_t q_full = bars, q_empty = bars + 8, tmem_slot = bars + 16;
   auto k_full = [&](int st) { return bars + 32 + 8 * st; };
   auto v_full = [&](int st) { return bars + 64 + 8 * st; };
@@ -192,6 +189,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
 
   if (warp == W_PRODUCER && lane == 0) {
     prefetch_tmap(&tmap_qkv);
+    prefetch_tmap(&tmap_ctx);
     mbar_init(q_full, 1);
     mbar_init(q_empty, 1);
     for (int st = 0; st < NST; ++st) {
@@ -262,7 +260,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
     // low words of the shared-memory descriptors of Q tile 0, K / V stage 0 and P buffer (0, 0); the high word is the same for
     // all of them (SBO 1024 B, version 1, 128B swizzle)
     const uint32_t q_lo = static_cast<uint32_t>(desc_kmajor(sQ(0))), k_lo = static_cast<uint32_t>(desc_kmajor(sK(0)));
-    const uint32_t p_lo = static_cast<uint32_t>(desc_kmajor(sP(0, 0))), v_lo = static_cast<uint32_t>(desc_mnmajor(sV(0), KPANEL, 1024));
+    const uint32_t v_lo = static_cast<uint32_t>(desc_mnmajor(sV(0), KPANEL, 1024));
     constexpr uint32_t desc_hi = static_cast<uint32_t>((static_cast<uint64_t>(1024 >> 4) << 32 | (1ull << 46) | (2ull << 61)) >> 32);
     auto mk_desc = [&](uint32_t lo) { return (static_cast<uint64_t>(desc_hi) << 32) | lo; };
     int cs0 = 0, cs1 = 0;  // S blocks issued per query tile
@@ -312,14 +310,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
           tc_fence_after();
           if (elect_one()) {
             constexpr uint32_t idesc = make_idesc(BQ, HD, 1);
-            const uint32_t ap = p_lo + static_cast<uint32_t>(2 * q + (cp & 1)) * (P_BYTES >> 4), bv = v_lo + static_cast<uint32_t>(st) * (V_BYTES >> 4);
+            const uint32_t bv = v_lo + static_cast<uint32_t>(st) * (V_BYTES >> 4);
             const uint32_t d = tO(q);
 #pragma unroll
             for (int k = 0; k < BKV / 16; ++k)  // O_q (+)= P_qj V_j
               if (k < ksteps) {
                 // A = P: 16 keys = 8 columns of packed bf16 pairs, over the first half of the S buffer the softmax read
-                if (FA_ATTN_P_TMEM) umma_f16_ts(d, tS(q, cp & 1) + k * 8, mk_desc(bv + k * (16 * 128 >> 4)), idesc, (j | k) != 0);
-                else umma_f16(d, mk_desc(ap + k * 2), mk_desc(bv + k * (16 * 128 >> 4)), idesc, (j | k) != 0);
+                umma_f16_ts(d, tS(q, cp & 1) + k * 8, mk_desc(bv + k * (16 * 128 >> 4)), idesc, (j | k) != 0);
               }
             umma_commit(pv_done(q, cp & 1));
             if (q == it.nq - 1) umma_commit(kv_empty(st));  // K_j / V_j are free once everything issued so far has retired
@@ -412,7 +409,6 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
             tmem_st32(tO(q) + lane_sel + x * 32, o);
           }
         }
-#if FA_ATTN_P_TMEM
         // ---- p = exp2(s c - m), row sum, bf16 pairs -> tensor memory, over the S columns this thread has just read: the A
         // operand of the P V MMA (M = 128 lanes = query rows, 2 keys per 32-bit column).  The tensor pipe runs its MMAs in order,
         // so the S MMA that next writes these columns (block c + 2) comes after the P V product that reads them.  No smem P
@@ -439,37 +435,6 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
           l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
           tmem_st32(tS(q, buf) + lane_sel, pk);  // (warp-wide: rows past the end of the utterance store zeros)
         }
-#else
-        // P_q[buf] was last read by the P V product of block c - 2
-        if ((threadIdx.x & 127) == 64) FA_TRACE(13, c, q);
-        if (c >= 2) mbar_wait(pv_done(q, buf), par ^ 1u);
-        if ((threadIdx.x & 127) == 64) FA_TRACE(14, c, q);
-        // ---- p = exp2(s c - m), row sum, bf16 -> swizzled smem (A operand of the P V MMA).
-        // Rows past the end of the utterance skip the arithmetic: their P rows only feed O rows that are never stored.
-        if (row_ok) {
-          float rs4[4] = {0.f, 0.f, 0.f, 0.f};
-          const int nch16 = (nkeys + 15) >> 4;  // 16-key MMA steps that will be issued
-          const uint32_t prow = sP(q, buf) + static_cast<uint32_t>(row) * 128u;
-#pragma unroll
-          for (int h2 = 0; h2 < 2; ++h2) {
-            if (h2 * 2 < nch16) {  // chunk read by at least one MMA step
-              uint32_t pk[16];
-#pragma unroll
-              for (int x = 0; x < 32; x += 2) {
-                const float p0 = ex2(fmaf(r[h2][x], p.scale_log2e, -m_used));      // masked keys: 2^-inf = 0
-                const float p1 = ex2(fmaf(r[h2][x + 1], p.scale_log2e, -m_used));
-                rs4[(x >> 1) & 3] += p0 + p1;
-                pk[x >> 1] = pack_bf16x2(p0, p1);
-              }
-#pragma unroll
-              for (int g = 0; g < 4; ++g)  // 32 keys = 64 B = four 16-byte chunks of this row
-                sts128(prow + ((static_cast<uint32_t>(h2 * 4 + g) ^ rsw) << 4), pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
-            }
-          }
-          l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
-        }
-#endif
-        if (!FA_ATTN_P_TMEM) fence_async_smem();
         tc_fence_before();
         mbar_arrive(p_full(q, buf));
         if ((threadIdx.x & 127) == 64) FA_TRACE(7, c, q);
@@ -479,36 +444,49 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Params p) {
       tc_fence_after();
       if ((threadIdx.x & 127) == 64) FA_TRACE(8, c, q);
       const float inv = 1.f / l_run;
+      // A warp whose 32 rows all belong to the utterance stages them in shared memory (its 32-row slice of the tile's two
+      // swizzled panels) and stores them with two TMA boxes; a 16-byte store per lane with a 2 KB row pitch is 32 LSU
+      // wavefronts per instruction, and the timeline showed this epilogue taking 3.3 k cycles per tile.  The ragged last
+      // rows of an utterance keep the per-lane stores (a box must not cover the next utterance's rows).
+      const bool box_rows = q0 + quarter * 32 + 32 <= it.len;  // warp-uniform
+      const uint32_t so = sO(q) + static_cast<uint32_t>(row) * 128u;
       __nv_bfloat16* dst = p.ctx + static_cast<long long>(it.start + q0 + row) * p.ld_ctx + it.h * HD;
+      if (lane == 0) bulk_wait_read<0>();  // the boxes of the previous item have left this warp's staging rows
+      __syncwarp();
 #pragma unroll 1
       for (int x = 0; x < 2; ++x) {
         uint32_t o0[32], o1[32];
         tmem_ld32_nowait(tO(q) + lane_sel + x * 64, o0);
         tmem_ld32_nowait(tO(q) + lane_sel + x * 64 + 32, o1);
         tmem_ld_wait();
-        if (row_ok) {
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const uint32_t(&o)[32] = hh ? o1 : o0;
 #pragma unroll
           for (int y = 0; y < 32; y += 8) {
             uint4 v;
-            v.x = pack_bf16x2(__uint_as_float(o0[y]) * inv, __uint_as_float(o0[y + 1]) * inv);
-            v.y = pack_bf16x2(__uint_as_float(o0[y + 2]) * inv, __uint_as_float(o0[y + 3]) * inv);
-            v.z = pack_bf16x2(__uint_as_float(o0[y + 4]) * inv, __uint_as_float(o0[y + 5]) * inv);
-            v.w = pack_bf16x2(__uint_as_float(o0[y + 6]) * inv, __uint_as_float(o0[y + 7]) * inv);
-            *reinterpret_cast<uint4*>(dst + x * 64 + y) = v;
+            v.x = pack_bf16x2(__uint_as_float(o[y]) * inv, __uint_as_float(o[y + 1]) * inv);
+            v.y = pack_bf16x2(__uint_as_float(o[y + 2]) * inv, __uint_as_float(o[y + 3]) * inv);
+            v.z = pack_bf16x2(__uint_as_float(o[y + 4]) * inv, __uint_as_float(o[y + 5]) * inv);
+            v.w = pack_bf16x2(__uint_as_float(o[y + 6]) * inv, __uint_as_float(o[y + 7]) * inv);
+            if (box_rows) sts128(so + x * QPANEL + ((static_cast<uint32_t>(hh * 4 + (y >> 3)) ^ rsw) << 4), v.x, v.y, v.z, v.w);
+            else if (row_ok) *reinterpret_cast<uint4*>(dst + x * 64 + hh * 32 + y) = v;
           }
-#pragma unroll
-          for (int y = 0; y < 32; y += 8) {
-            uint4 v;
-            v.x = pack_bf16x2(__uint_as_float(o1[y]) * inv, __uint_as_float(o1[y + 1]) * inv);
-            v.y = pack_bf16x2(__uint_as_float(o1[y + 2]) * inv, __uint_as_float(o1[y + 3]) * inv);
-            v.z = pack_bf16x2(__uint_as_float(o1[y + 4]) * inv, __uint_as_float(o1[y + 5]) * inv);
-            v.w = pack_bf16x2(__uint_as_float(o1[y + 6]) * inv, __uint_as_float(o1[y + 7]) * inv);
-            *reinterpret_cast<uint4*>(dst + x * 64 + 32 + y) = v;
-          }
+        }
+      }
+      if (box_rows) {
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          const uint32_t sw = sO(q) + static_cast<uint32_t>(quarter * 32) * 128u;
+          tma_store_2d(&tmap_ctx, sw, it.h * HD, it.start + q0 + quarter * 32);
+          tma_store_2d(&tmap_ctx, sw + QPANEL, it.h * HD + 64, it.start + q0 + quarter * 32);
+          bulk_commit();
         }
       }
       if ((threadIdx.x & 127) == 64) FA_TRACE(15, c, q);
     });
+    if (lane == 0) bulk_wait<0>();  // this warp's last context boxes are in global memory before the CTA retires
   } else if (fsmn_on) {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_FSMN));
     // ===================== FSMN warps: mem[t, c] = v[t, c] + sum_k w[k, c] v[t + k - left, c] ==============================
@@ -621,7 +599,8 @@ bool attention_can_fuse_fsmn(int kernel, int64_t ld_mem, const void* mem) {
 
 int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base,
                      int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, const float* fsmn_w, int fsmn_left,
-                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream, int* zero_ints, int n_zero, float* acc, int64_t ld_acc) {
+                     __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream, int* zero_ints, int n_zero, float* acc, int64_t ld_acc,
+                     const TensorMap2D* tm_ctx) {
   FA_REQUIRE(ld % 8 == 0 && ld_ctx % 8 == 0, "attention: row strides must be multiples of 8 elements");
   FA_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0,
              "attention: qkv and ctx must be 16-byte aligned");
@@ -647,8 +626,14 @@ int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t
     if (int r = make_tensor_map_bf16(&tm, qkv, n_rows, 3 * n_heads * attn::HD, ld, attn::BKV)) return r;
     tm_in = &tm;
   }
-  CUtensorMap m;
+  CUtensorMap m, mc;
   memcpy(&m, tm_in->bytes, sizeof(m));
+  TensorMap2D tmc;  // the context rows as 32 x 64 boxes (the epilogue's TMA stores)
+  if (tm_ctx == nullptr) {
+    if (int r = make_tensor_map(&tmc, ctx, 2, n_rows, static_cast<uint64_t>(n_heads) * attn::HD, ld_ctx, 32)) return r;
+    tm_ctx = &tmc;
+  }
+  memcpy(&mc, tm_ctx->bytes, sizeof(mc));
   const int sms = sm_count();
   // Query tiles per work item: two (K/V streamed once for both) unless that leaves SMs without an item.
   const int tiles = ceil_div(max_len, attn::BQ);
@@ -675,8 +660,8 @@ int launch_attention(const TensorMap2D* tm_in, const __nv_bfloat16* qkv, int64_t
   p.fsmn_rows = ceil_div(max_len, fs_chunks) < 32 ? 32 : ceil_div(max_len, fs_chunks);
   p.fsmn_chunks = ceil_div(max_len, p.fsmn_rows);
   ProfScope _ps(K_ATTENTION, stream);
-  if (use_acc) FA_CHECK_CUDA(launch_pdl(attn::attention_kernel<true>, dim3(grid), dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, p));
-  else FA_CHECK_CUDA(launch_pdl(attn::attention_kernel<false>, dim3(grid), dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, p));
+  if (use_acc) FA_CHECK_CUDA(launch_pdl(attn::attention_kernel<true>, dim3(grid), dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, mc, p));
+  else FA_CHECK_CUDA(launch_pdl(attn::attention_kernel<false>, dim3(grid), dim3(attn::THREADS), attn::SMEM_BYTES, stream, 1, m, mc, p));
   return 0;
 }
 

@@ -160,7 +160,8 @@ bool attention_can_fuse_fsmn(int kernel, int64_t ld_mem, const void* mem);
 int launch_attention(const TensorMap2D* tm, const __nv_bfloat16* qkv, int64_t ld, const int32_t* cu_seqlens, int n_utts, int base,
                      int max_len, int n_heads, __nv_bfloat16* ctx, int64_t ld_ctx, int n_rows, const float* fsmn_w, int fsmn_left,
                      __nv_bfloat16* mem, int64_t ld_mem, cudaStream_t stream, int* zero_ints = nullptr, int n_zero = 0,
-                     float* acc = nullptr, int64_t ld_acc = 0);  // acc != NULL: acc[row, h * 128 + c] += memory instead of the bf16 store
+                     float* acc = nullptr, int64_t ld_acc = 0,  // acc != NULL: acc[row, h * 128 + c] += memory instead of the bf16 store
+                     const TensorMap2D* tm_ctx = nullptr);      // prebuilt map of ctx (32 x 64 boxes), or NULL to encode one here
 // dst[i] = cu[min(i, n_utts)], i = 0..n_pad: cu_seqlens copied to a fixed address, padded with the total row count
 int launch_pad_cu(const int32_t* cu, int n_utts, int32_t* dst, int n_pad, cudaStream_t stream);
 int launch_repack_rows(const float* src, int src_tmax, void* dst, int dst_tmax, int dst_bf16, const int32_t* cu,
