@@ -1,9 +1,10 @@
 #!/bin/bash
 set -u
-O=gpurun_out/r2aw
+O=gpurun_out/r2ax
 mkdir -p $O
-timeout 300 python -m pytest tests/test_gpu_ops.py -x -q -k "attention" 2>&1 | tail -3
-python profiles/scripts/attn_bench.py 20 cfg5 cfg2 cfg3 long > $O/attn.txt 2>&1; cat $O/attn.txt
-timeout 600 python -m pytest tests -m gpu -x -q --deselect tests/test_gpu_zz_vllm_greedy.py 2>&1 | tail -2
-timeout 200 python bench.py --no-cpu-baseline > $O/bench.json 2> $O/bench.err; python -c "
-import json; d=json.load(open('$O/bench.json')); print(d['ms_per_step'], d['e2e']['ms_per_step'], d['kernel_ms_per_step']); print({k:(v.get('ms_per_step'), v.get('e2e_ms')) for k,v in d['workloads'].items()})"
+for rep in 1 2; do for v in 1 0; do
+FA_MEM_INTO_X=$v timeout 200 python bench.py --no-cpu-baseline --no-extras > $O/bench_intox${v}_$rep.json 2> $O/err.txt; python -c "
+import json; d=json.load(open('$O/bench_intox${v}_$rep.json')); print('into_x=$v', round(d['ms_per_step'],2), round(d['e2e']['ms_per_step'],2), d['kernel_ms_per_step']['gemm'], d['kernel_ms_per_step']['attention'])"
+done; done
+for v in 1 0; do FA_MEM_INTO_X=$v timeout 200 python bench.py --no-cpu-baseline --no-extras --workload cfg2 > $O/b2_$v.json 2>> $O/err.txt; FA_MEM_INTO_X=$v timeout 200 python bench.py --no-cpu-baseline --no-extras --workload cfg3 > $O/b3_$v.json 2>> $O/err.txt; python -c "
+import json; print('into_x=$v cfg2', round(json.load(open('$O/b2_$v.json'))['ms_per_step'],3), 'cfg3', round(json.load(open('$O/b3_$v.json'))['ms_per_step'],3))"; done
