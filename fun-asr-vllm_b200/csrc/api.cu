@@ -249,6 +249,7 @@ int run_gemm_op(const GemmOp& op, const RunArgs& a) {
   FA_REQUIRE(bn != 0 && op.tb_ok[idx], "gemm N=%d unsupported", op.N);
   const bool pair = gemm_use_pair(a.M, bn) && op.tb_ok[1];
   GemmEpilogue epi = op.epi;
+  if (epi.ln_mode == 2) epi.txb = &op.txb;
   if (epi.ln_mode == 1) epi.ln_slots = op.prod_N / 32;  // the producer leaves one partial per 32 columns of its output
   return launch_gemm(op.ta, op.tb[pair ? 1 : idx], op.tc, epi.res1 ? &op.tr1 : nullptr, epi.res2 ? &op.tr2 : nullptr, bn, a.M,
                      op.N, op.K, epi, op.c, op.ldc, a.row0, pair, a.s);
@@ -302,7 +303,11 @@ struct Builder {
     op.epi.ln_mode = ln_mode;
     if (ln_mode != 0) op.epi.ln_stats = p->ws.stats;
     if (ln_mode == 1) { op.epi.colsum = colsum; op.epi.ln_dim = ln_dim; op.prod_N = prod_N; }
-    if (ln_mode == 2) { op.epi.xb = p->ws.xn; op.epi.ld_xb = N; }
+    if (ln_mode == 2) {
+      op.epi.xb = p->ws.xn;
+      op.epi.ld_xb = N;
+      if (!rc) rc = make_tensor_map_w(&op.txb, p->ws.xn, 2, p->cap, N, N, 32, 64);
+    }
     if (!rc) prog.push_back([op](const RunArgs& r) { return run_gemm_op(op, r); });
   }
   // Layer i's out-projection, ffn1, ffn2 and layer i+1's qkv as one step: the chain launch when the plan's switch is on,

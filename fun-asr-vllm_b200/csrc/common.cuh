@@ -65,6 +65,10 @@ struct ProfScope {  // brackets the launches issued during its lifetime with two
 };
 
 // ---- internal launchers shared between api.cu and the op entry points -----------------------
+struct TensorMap2D {  // opaque 128-byte CUtensorMap
+  alignas(64) unsigned char bytes[128];
+};
+
 struct GemmEpilogue {
   const float* bias = nullptr;  // [N]
   const float* res1 = nullptr;  // f32 [M, N] (row stride ldc)
@@ -89,10 +93,7 @@ struct GemmEpilogue {
   const float* colsum = nullptr;  // consumer: [N] row sums of the bf16 weight
   __nv_bfloat16* xb = nullptr;  // producer: bf16 copy of C, row stride ld_xb
   int64_t ld_xb = 0;
-};
-
-struct TensorMap2D {  // opaque 128-byte CUtensorMap
-  alignas(64) unsigned char bytes[128];
+  const TensorMap2D* txb = nullptr;  // producer: prebuilt map of xb (32 x 32 boxes, 64B swizzle); NULL: encoded per launch
 };
 
 // rows x cols bf16 matrix, row stride ld (elements); box = box_rows x 64 cols, 128B swizzle.

@@ -44,7 +44,7 @@ constexpr int BAR_BYTES = 512;
 // CTA stages its own 128 rows of A and only HALF of the B tile, so the operand bytes an SM pulls through its 64 B/clk
 // L2 port drop from 48 KB to 32 KB per 128x256x64 of MMA work (ncu, profiles/r01_e_campaign.md: the 1-CTA kernel moves
 // 54 B/clk/SM into the SMs at 63 % tensor-pipe activity, i.e. it is L2->SM ingress bound).
-template <int BN, int NRES, int CTAS, bool OUT_F32>
+template <int BN, int NRES, int CTAS, bool OUT_F32, bool XBS = false>
 struct Cfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN / CTAS * BK * 2;
@@ -55,7 +55,12 @@ struct Cfg {
   // next unit is produced; the f32 accumulate output (K = d_ff) keeps one slab and one more operand stage
   static constexpr int RING = res_ring(NRES);
   static constexpr int SLABS_PER_WARP = NRES == 0 ? (OUT_F32 ? 1 : 2) : RING * NRES;
-  static constexpr int SLABS_BYTES = EPI_WARPS * SLABS_PER_WARP * SLAB_BYTES;
+  // XBS (folded-LN producer with a short k loop): one more slab per warp, 32 rows x 64 B (64B swizzle), for the bf16 copy of
+  // a unit, which then leaves by TMA with the f32 rows instead of as 16-byte stores per lane with a 1 KB row pitch (32 LSU
+  // wavefronts per instruction).  It costs the ring its fifth stage, which the K = 2048 producer (ffn2) needs more than the
+  // stores hurt it (127 -> 136 us with the slab); the K = 512 out-projection gains 90 -> 85 us.
+  static constexpr int XSLAB_BYTES = 32 * 64;
+  static constexpr int SLABS_BYTES = EPI_WARPS * (SLABS_PER_WARP * SLAB_BYTES + (XBS ? XSLAB_BYTES : 0));
   // bf16 output: bias (and the folded-LN column sums) of all N columns are staged in smem once per CTA, so the epilogue's
   // per-column constants are short-latency broadcast LDS instead of L1 round trips (ncu: a fifth of its stall samples)
   static constexpr int CVEC_BYTES = OUT_F32 ? 0 : 16384;
@@ -94,12 +99,13 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t a) { return desc_kma
 // ---------------------------------------------------------------- kernel
 // Epilogue variants are compile-time: OUT_F32 (f32 C, optional NRES f32 residuals) or bf16 C (optional RELU).
 // LN: 0 none, 1 consumer (bf16 output), 2 producer (f32 output, NRES == 1) of a folded LayerNorm.
-template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS, int LN>
+template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS, int LN, bool XBS = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_r1,
                  const __grid_constant__ CUtensorMap tmap_r2, const Params p) {
-  using C = Cfg<BN, NRES, CTAS, OUT_F32>;
+  // (XBS: tmap_r2 is not a residual - NRES is 1 - but the 32 x 32 map of the bf16 copy xb)
+  using C = Cfg<BN, NRES, CTAS, OUT_F32, XBS>;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024B alignment
   const uint32_t slab_base = smem_base + C::STAGES * C::STAGE_BYTES;  // 1024-aligned: STAGE_BYTES is a multiple of 1024
@@ -288,6 +294,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       constexpr int LAG = RES_RING >= 3 ? 1 : 0;  // stores allowed to be still reading their slab when the next load is issued
       constexpr uint32_t SLOT_BYTES = NRES * SLAB_BYTES;
       const uint32_t ring = slab_base + ew * RES_RING * SLOT_BYTES;
+      [[maybe_unused]] const uint32_t xslab = slab_base + EPI_WARPS * RES_RING * SLOT_BYTES + ew * C::XSLAB_BYTES;
+      [[maybe_unused]] const uint32_t xrow_off = static_cast<uint32_t>(lane) * 64u;
+      [[maybe_unused]] const uint32_t xsw = static_cast<uint32_t>(lane >> 1) & 3u;  // 64B swizzle: chunk ^ bits [8:7] of the offset
       const int my_tiles = (num_tiles - cl + ncl - 1) / ncl;
       const int total = my_tiles * UH;
       auto coords = [&](int n, int& row0, int& col0, int& u) {
@@ -375,9 +384,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const float b2 = __uint_as_float(hi << 16), b3 = __uint_as_float(hi & 0xffff0000u);
             ln_s += (b0 + b1) + (b2 + b3);
             ln_ss = fmaf(b0, b0, fmaf(b1, b1, fmaf(b2, b2, fmaf(b3, b3, ln_ss))));
-            if ((j & 1) && row0 + lane < p.M)
-              *reinterpret_cast<uint4*>(p.xb + static_cast<long long>(p.row0 + row0 + lane) * p.ld_xb + col0 + 4 * (j - 1)) =
-                  make_uint4(xbp[0], xbp[1], xbp[2], xbp[3]);
+            if (j & 1) {
+              if (XBS && row0 + 32 <= p.M) sts128(xslab + xrow_off + ((static_cast<uint32_t>(j >> 1) ^ xsw) << 4), xbp[0], xbp[1], xbp[2], xbp[3]);
+              else if (row0 + lane < p.M)  // (ragged last rows of the launch always go straight to global memory)
+                *reinterpret_cast<uint4*>(p.xb + static_cast<long long>(p.row0 + row0 + lane) * p.ld_xb + col0 + 4 * (j - 1)) =
+                    make_uint4(xbp[0], xbp[1], xbp[2], xbp[3]);
+            }
           }
         }
         if constexpr (LN == 2) {
@@ -400,6 +412,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if (lane == 0) {
             if (p.accumulate) tma_reduce_add_2d(&tmap_c, slab, col0, p.row0 + row0);
             else tma_store_2d(&tmap_c, slab, col0, p.row0 + row0);
+            if constexpr (XBS) tma_store_2d(&tmap_r2, xslab, col0, p.row0 + row0);
             bulk_commit();
             bulk_wait_read<LAG>();  // the store that left slot (n + RES_RING - LAG) % RES_RING has read its slab
           }
@@ -599,11 +612,11 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS, int LN>
+template <int BN, bool OUT_F32, bool RELU, int NRES, int CTAS, int LN, bool XBS = false>
 static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mr1,
                     const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
-  using C = Cfg<BN, NRES, CTAS, OUT_F32>;
-  auto kern = gemm_bf16_kernel<BN, OUT_F32, RELU, NRES, CTAS, LN>;
+  using C = Cfg<BN, NRES, CTAS, OUT_F32, XBS>;
+  auto kern = gemm_bf16_kernel<BN, OUT_F32, RELU, NRES, CTAS, LN, XBS>;
   static SmemOptIn opt;  // one per kernel instantiation
   if (int r = opt_in_smem(kern, C::SMEM_BYTES, opt)) return r;
   // the CTA pair of cta_group::2 is one cluster
@@ -612,13 +625,13 @@ static int launch_v(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensor
 }
 
 // pair == true: BN is 256 and `mb` boxes BN/2 rows (each CTA of a pair stages half of the B tile)
-template <int BN, bool OUT_F32, bool RELU, int NRES, int LN = 0>
+template <int BN, bool OUT_F32, bool RELU, int NRES, int LN = 0, bool XBS = false>
 static int launch_p(bool pair, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mr1,
                     const CUtensorMap& mr2, const Params& p, int grid, cudaStream_t stream) {
   if constexpr (BN == 256) {
-    if (pair) return launch_v<BN, OUT_F32, RELU, NRES, 2, LN>(ma, mb, mc, mr1, mr2, p, grid, stream);
+    if (pair) return launch_v<BN, OUT_F32, RELU, NRES, 2, LN, XBS>(ma, mb, mc, mr1, mr2, p, grid, stream);
   }
-  return launch_v<BN, OUT_F32, RELU, NRES, 1, LN>(ma, mb, mc, mr1, mr2, p, grid, stream);
+  return launch_v<BN, OUT_F32, RELU, NRES, 1, LN, XBS>(ma, mb, mc, mr1, mr2, p, grid, stream);
 }
 
 template <int BN>
@@ -656,6 +669,17 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   memcpy(&mc, tc.bytes, sizeof(mc));
   memcpy(&mr1, (tr1 ? tr1 : &tc)->bytes, sizeof(mr1));
   memcpy(&mr2, (tr2 ? tr2 : &tc)->bytes, sizeof(mr2));
+  static const bool xbs_on = [] { const char* e = getenv("FA_XBS"); return e == nullptr || atoi(e) != 0; }();  // measurement switch
+  const bool xbs = epi.ln_mode == 2 && K <= 1024 && xbs_on;  // short k loop: the bf16 copy leaves by TMA (see Cfg::XSLAB_BYTES)
+  if (xbs) {  // its 32 x 32 map travels in the (unused) second-residual slot
+    TensorMap2D txb_local;
+    const TensorMap2D* txb = epi.txb;
+    if (txb == nullptr) {
+      if (int r = make_tensor_map_w(&txb_local, epi.xb, 2, static_cast<uint64_t>(row0) + M, N, epi.ld_xb, 32, 64)) return r;
+      txb = &txb_local;
+    }
+    memcpy(&mr2, txb->bytes, sizeof(mr2));
+  }
   FA_REQUIRE((epi.res1 == nullptr) == (tr1 == nullptr) && (epi.res2 == nullptr) == (tr2 == nullptr),
              "gemm: every residual needs its tensor map");
   ProfScope _ps(K_GEMM, stream);
@@ -666,7 +690,9 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
       if constexpr (BN <= 128) return launch_p<BN, true, false, 2>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
       else FA_REQUIRE(false, "gemm: two residuals are compiled for tile N <= 128 only");
     }
-    if (epi.res1 && epi.ln_mode == 2) return launch_p<BN, true, false, 1, 2>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
+    if (epi.res1 && epi.ln_mode == 2)
+      return xbs ? launch_p<BN, true, false, 1, 2, true>(pair, ma, mb, mc, mr1, mr2, p, grid, stream)
+                 : launch_p<BN, true, false, 1, 2>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
     if (epi.res1) return launch_p<BN, true, false, 1>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
     return launch_p<BN, true, false, 0>(pair, ma, mb, mc, mr1, mr2, p, grid, stream);
   }
