@@ -669,8 +669,8 @@ static int launch_t(const TensorMap2D& ta, const TensorMap2D& tb, const TensorMa
   memcpy(&mc, tc.bytes, sizeof(mc));
   memcpy(&mr1, (tr1 ? tr1 : &tc)->bytes, sizeof(mr1));
   memcpy(&mr2, (tr2 ? tr2 : &tc)->bytes, sizeof(mr2));
-  static const bool xbs_on = [] { const char* e = getenv("FA_XBS"); return e == nullptr || atoi(e) != 0; }();  // measurement switch
-  const bool xbs = epi.ln_mode == 2 && K <= 1024 && xbs_on;  // short k loop: the bf16 copy leaves by TMA (see Cfg::XSLAB_BYTES)
+  // (inside the cfg5 step: 43.9 / 44.2 ms with it, 44.6 / 44.7 ms without)
+  const bool xbs = epi.ln_mode == 2 && K <= 1024;  // short k loop: the bf16 copy leaves by TMA (see Cfg::XSLAB_BYTES)
   if (xbs) {  // its 32 x 32 map travels in the (unused) second-residual slot
     TensorMap2D txb_local;
     const TensorMap2D* txb = epi.txb;
