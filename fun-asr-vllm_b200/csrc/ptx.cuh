@@ -25,11 +25,19 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n\t"
       ".reg .pred p;\n\t"
+#ifdef FA_MBAR_HINT
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"  // suspend-time hint: the hardware parks the thread
+#else
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+#endif
       "selp.u32 %0, 1, 0, p;\n\t"
       "}"
       : "=r"(ok)
+#ifdef FA_MBAR_HINT
+      : "r"(bar), "r"(parity), "r"(static_cast<uint32_t>(FA_MBAR_HINT))
+#else
       : "r"(bar), "r"(parity)
+#endif
       : "memory");
   return ok != 0;
 }
