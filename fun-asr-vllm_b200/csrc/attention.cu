@@ -505,20 +505,42 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
     // FSMN work units are independent of the attention work items: (utterance, head, chunk of fsmn_rows output rows), dealt
     // round-robin to every FSMN warp of the grid, so that a small batch still spreads over all of them.
     const int n_units = p.n_utts * p.n_heads * p.fsmn_chunks;
-    for (int u = blockIdx.x * FSMN_WARPS + f; u < n_units; u += gridDim.x * FSMN_WARPS) {
-      const int h = u % p.n_heads, c = (u / p.n_heads) % p.fsmn_chunks, b = u / (p.n_heads * p.fsmn_chunks);
-      const int c0 = __ldg(p.cu + b), c1 = __ldg(p.cu + b + 1);
+    // Per unit the timeline showed 4-7 k cycles before the first row (utterance bounds, then the taps, then the ring's first
+    // loads: three dependent round trips).  The bounds of the next unit are requested a unit ahead, and the taps are only
+    // reloaded when the head changes (with a unit stride that is a multiple of the head count it never does).
+    float4 w4[K];
+    int w_head = -1;
+    const int u_first = blockIdx.x * FSMN_WARPS + f, u_step = gridDim.x * FSMN_WARPS;
+    int c0n = 0, c1n = 0;
+    if (u_first < n_units) {
+      const int b = u_first / (p.n_heads * p.fsmn_chunks);
+      c0n = __ldg(p.cu + b);
+      c1n = __ldg(p.cu + b + 1);
+    }
+    for (int u = u_first; u < n_units; u += u_step) {
+      const int h = u % p.n_heads, c = (u / p.n_heads) % p.fsmn_chunks;
+      const int c0 = c0n, c1 = c1n;
+      if (u + u_step < n_units) {
+        const int b = (u + u_step) / (p.n_heads * p.fsmn_chunks);
+        c0n = __ldg(p.cu + b);
+        c1n = __ldg(p.cu + b + 1);
+      }
       const int start = c0 - p.base, len = c1 - c0;
       const int t0 = c * p.fsmn_rows;  // output rows [t0, t1) of the utterance
       if (t0 >= len) continue;
       const int t1 = min(len, t0 + p.fsmn_rows);
-      float4 w4[K];
       float2 a01[K], a23[K];
+      if (h != w_head) {
+        w_head = h;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          w4[k] = __ldg(reinterpret_cast<const float4*>(p.fsmn_w + static_cast<long long>(k) * dm + h * HD) + lane);
+          const float one = (k == left) ? 1.f : 0.f;  // "+ inputs" = tap `left` with weight + 1
+          w4[k].x += one; w4[k].y += one; w4[k].z += one; w4[k].w += one;
+        }
+      }
 #pragma unroll
       for (int k = 0; k < K; ++k) {
-        w4[k] = __ldg(reinterpret_cast<const float4*>(p.fsmn_w + static_cast<long long>(k) * dm + h * HD) + lane);
-        const float one = (k == left) ? 1.f : 0.f;  // "+ inputs" = tap `left` with weight + 1
-        w4[k].x += one; w4[k].y += one; w4[k].z += one; w4[k].w += one;
         a01[k] = make_float2(0.f, 0.f);
         a23[k] = make_float2(0.f, 0.f);
       }
