@@ -17,7 +17,8 @@ from .pipeline import AudioPipeline
 from .registry import install, patch, tables
 from .sharding import gather_results, shard_contiguous, shard_lpt
 from .splice import splice_embeds
+from .vllm_route import install_vllm_route, patch_vllm_model
 
 __all__ = ["AudioPipeline", "AudioTower", "audio_embeddings", "inference_batched", "FunASRB200Error", "LIB_PATH", "Resample", "pack_pcm", "pcm_to_mono", "SenseVoiceEncoderSmall", "Transformer",
            "WavFrontend", "extract_fbank", "fake_token_len", "gather_results", "install", "load_cmvn", "pack_waveforms",
-           "patch", "shard_contiguous", "shard_lpt", "splice_embeds", "tables"]
+           "install_vllm_route", "patch", "patch_vllm_model", "shard_contiguous", "shard_lpt", "splice_embeds", "tables"]
