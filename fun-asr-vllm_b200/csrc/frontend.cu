@@ -39,27 +39,27 @@ constexpr int RAW_TILE_FRAMES = 30;                                  // raw log-
 constexpr int MAX_SAMPLES = (MAX_FRAMES - 1) * SHIFT + FRAME_LEN;    // 5200
 constexpr int THREADS = 256;
 constexpr int SLOTS = THREADS / 16;  // frames in flight per CTA (one per half-warp)
-constexpr int MAX_TAPS = 1024;
+constexpr int MEL_GROUPS = NMEL / 16;  // a lane of a half-warp owns mel bins hl, hl + 16, ..., one per group
+constexpr int MEL_MAXJ = 5;             // four-tap steps per band (bands start on a multiple of four FFT bins): <= 20 taps
+constexpr int MEL_W = MEL_GROUPS * MEL_MAXJ * 16 * 4;  // weights as [group][step][lane] float4: conflict-free 16-byte loads
 
 struct __align__(16) Tables {
   float window[FRAME_LEN];
   double2 tw256[16][16];  // [q][t] = W256^(t q) = (cos, -sin)(2 pi t q / 256): pass-1 -> pass-2 twiddles, lane t reads [q][t]
   double2 tw512[130];     // W512^k, k = 0..128
-  int mel_start[NMEL];
-  int mel_count[NMEL];
-  int mel_woff[NMEL];
-  float mel_w[MAX_TAPS];
+  int mel_start[NMEL];       // first FFT bin of the band, rounded down to a multiple of four (16-byte power loads)
+  int mel_steps[8];          // per group: four-tap steps of its widest band (uniform over the lanes; shorter bands carry zeros)
+  float mel_w[MEL_W];
 };
 
 struct __align__(16) Smem {
   double2 tw256[16][16];
   double2 tw512[130];
-  double work[SLOTS][16 * 17];  // 16x17 padded transpose buffer (real parts, then imaginary parts)
+  double2 work[SLOTS][16 * 17];  // 16x17 padded complex transpose buffer; the slot's power spectrum (264 floats) reuses it
   float samples[MAX_SAMPLES + 8];
   float logmel[MAX_FRAMES + 1][NMEL];
-  float power[SLOTS][264];
   float window[FRAME_LEN];
-  float mel_w[MAX_TAPS];
+  float mel_w[MEL_W];
 };
 
 typedef double2 cplx;
@@ -97,12 +97,29 @@ __device__ __forceinline__ void fft16(cplx (&x)[16]) {
   for (int q0 = 0; q0 < 4; ++q0) dft4(x[4 * q0 + 0], x[4 * q0 + 1], x[4 * q0 + 2], x[4 * q0 + 3]);
 }
 
+// Utterance of tile `id`: the last b with tile_off[b] <= id.  A 32-way search (every lane probes one pivot, a ballot picks the
+// interval): two dependent load rounds for up to 1024 utterances instead of ten.  Called by whole, converged warps.
+__device__ __forceinline__ int utterance_of_tile(const int32_t* __restrict__ tile_off, int n_utts, int id, int lane) {
+  int lo = 0, hi = n_utts;
+  while (hi - lo > 1) {
+    const int step = (hi - lo + 31) >> 5;
+    const int pos = lo + step * lane;
+    const bool le = pos < hi && __ldg(tile_off + pos) <= id;
+    const unsigned m = __ballot_sync(0xffffffffu, le) | 1u;  // tile_off[lo] <= id holds by construction
+    const int k = 31 - __clz(m);
+    lo += step * k;
+    hi = min(lo + step, hi);
+  }
+  return lo;
+}
+
 template <int MODE>  // 0: LFR + CMVN rows, 1: raw log-mel rows
 __global__ void __launch_bounds__(THREADS, 2)
 fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, const int64_t* __restrict__ wav_start,
              const int32_t* __restrict__ wav_len, const int32_t* __restrict__ out_row, const int32_t* __restrict__ tile_off, int n_utts,
              int n_tiles, const float* __restrict__ cmvn, float* __restrict__ out, int64_t out_ld, float upscale, float preemph,
              float log_floor) {
+  const float log_of_floor = logf(log_floor);
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15;
@@ -112,16 +129,14 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
   for (int i = tid; i < FRAME_LEN; i += THREADS) s.window[i] = __ldg(&tab->window[i]);
   for (int i = tid; i < 130; i += THREADS) s.tw512[i] = tab->tw512[i];
   for (int i = tid; i < 256; i += THREADS) (&s.tw256[0][0])[i] = (&tab->tw256[0][0])[i];
-  for (int i = tid; i < MAX_TAPS / 4; i += THREADS)
+  for (int i = tid; i < MEL_W / 4; i += THREADS)
     reinterpret_cast<float4*>(s.mel_w)[i] = __ldg(reinterpret_cast<const float4*>(tab->mel_w) + i);
-  for (int i = tid; i < SLOTS * 8; i += THREADS) s.power[i >> 3][256 + (i & 7)] = 0.f;  // read (x 0) by the padded mel taps
   // this lane's five mel bins (hl, hl + 16, ..., hl + 64): first FFT bin, taps padded to a multiple of 4, weight offset
-  int mel_st[NMEL / 16], mel_n4[NMEL / 16], mel_wo[NMEL / 16];
+  int mel_st[MEL_GROUPS], mel_nj[MEL_GROUPS];
 #pragma unroll
-  for (int i = 0; i < NMEL / 16; ++i) {
+  for (int i = 0; i < MEL_GROUPS; ++i) {
     mel_st[i] = __ldg(&tab->mel_start[hl + 16 * i]);
-    mel_n4[i] = (__ldg(&tab->mel_count[hl + 16 * i]) + 3) >> 2;
-    mel_wo[i] = __ldg(&tab->mel_woff[hl + 16 * i]);
+    mel_nj[i] = __ldg(&tab->mel_steps[i]);
   }
 
   const int first_tile = MODE == 0 ? static_cast<int>(blockIdx.x) : 0;
@@ -130,13 +145,28 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
   for (int id = first_tile; id < tile_end; id += tile_step) {
   int b, ti;
   if (MODE == 0) {
-    int lo = 0, hi = n_utts;
-    while (hi - lo > 1) {
-      int mid = (lo + hi) >> 1;
-      if (tile_off[mid] <= id) lo = mid; else hi = mid;
+    b = utterance_of_tile(tile_off, n_utts, id, lane);
+    ti = id - __ldg(tile_off + b);
+    // the PCM of this CTA's next tile is requested into L2 now, a whole tile of arithmetic ahead of its staging loop
+    if (warp == 1 && id + tile_step < tile_end) {
+      const int nb = utterance_of_tile(tile_off, n_utts, id + tile_step, lane);
+      const int nti = id + tile_step - __ldg(tile_off + nb);
+      const int nn = wav_len[nb];
+      if (lane == 0 && nn >= FRAME_LEN) {
+        const int nm = 1 + (nn - FRAME_LEN) / SHIFT;
+        const int nT = (nm + LFR_N - 1) / LFR_N;
+        const int ni0 = nti * TILE_ROWS;
+        if (ni0 < nT) {
+          const int ni1 = min(ni0 + TILE_ROWS, nT);
+          const int nlo = max(LFR_N * ni0 - LFR_LEFT, 0);
+          const int nhi = min(LFR_N * (ni1 - 1) + LFR_M - 1 - LFR_LEFT, nm - 1);
+          const float* nsrc = wav + wav_start[nb] + static_cast<int64_t>(nlo) * SHIFT;
+          const uint32_t nbytes = static_cast<uint32_t>(((nhi - nlo) * SHIFT + FRAME_LEN) * 4);
+          if ((reinterpret_cast<uintptr_t>(nsrc) & 15) == 0)
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nsrc), "r"(nbytes) : "memory");
+        }
+      }
     }
-    b = lo;
-    ti = id - tile_off[b];
   } else {
     b = blockIdx.y;
     ti = blockIdx.x;
@@ -177,8 +207,8 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
   __syncthreads();
 
   const int slot = warp * 2 + (lane >> 4);
-  double* work = s.work[slot];
-  float* power = s.power[slot];
+  double2* work = s.work[slot];
+  float* power = reinterpret_cast<float*>(s.work[slot]);  // written after the transpose has been read back
   const int partner = (16 - hl) & 15;  // lane holding Z[256 - k] for this lane's k = hl + 16 p
 
   for (int fb = warp * 2; fb < nF; fb += SLOTS) {
@@ -189,18 +219,23 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
 
     // ---- load 13 sample pairs (complex point n = hl + 16 j  <->  samples 2n, 2n+1), frame mean
     float2 xf[13];
-    double part = 0.0;
+    float ps[13];
 #pragma unroll
     for (int j = 0; j < 13; ++j) {
       const int sidx = 2 * hl + 32 * j;
       float2 v = make_float2(0.f, 0.f);
       if (j < 12 || hl < 8) v = *reinterpret_cast<const float2*>(xs + sidx);
       xf[j] = v;
-      part += static_cast<double>(v.x) + static_cast<double>(v.y);
+      ps[j] = v.x + v.y;
     }
+    // frame mean (TA:183-186): the lane's 26 samples by an fp32 pairwise tree, the 16 lane sums in fp64 (the reference sums in
+    // fp32 as well; both are within a few 1e-8 relative of the exact mean, far inside the log-mel budget)
+    const float lane_sum = (((ps[0] + ps[1]) + (ps[2] + ps[3])) + ((ps[4] + ps[5]) + (ps[6] + ps[7]))) +
+                           (((ps[8] + ps[9]) + (ps[10] + ps[11])) + ps[12]);
+    double part = static_cast<double>(lane_sum);
 #pragma unroll
     for (int o = 8; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-    const float mean = static_cast<float>(part / static_cast<double>(FRAME_LEN));  // TA:183-186, correctly rounded
+    const float mean = static_cast<float>(part * (1.0 / static_cast<double>(FRAME_LEN)));
 
     // ---- DC removal, pre-emphasis (replicate-left, TA:193-198), window (TA:201-204): the reference's fp32 operation
     // sequence, one rounding per torch op (no FMA contraction), so the frames entering the FFT carry the same bits.
@@ -220,26 +255,16 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     }
     x[13] = x[14] = x[15] = mk(0.0, 0.0);  // zero padding 400 -> 512 (TA:207-211)
 
-    // ---- pass 1: DFT16 over j, twiddle W256^(t q), transpose through smem (real parts, then imaginary parts)
+    // ---- pass 1: DFT16 over j, twiddle W256^(t q), transpose through smem
     fft16(x);
 #pragma unroll
     for (int q = 1; q < 16; ++q) x[POS16(q)] = cmul(x[POS16(q)], s.tw256[q][hl]);
-    {
-      double im[16];
+    {  // 16-byte accesses: rows of 17 complex values keep both directions at the two-wavefront minimum
 #pragma unroll
-      for (int q = 0; q < 16; ++q) {
-        work[q * 17 + hl] = x[POS16(q)].x;
-        im[q] = x[POS16(q)].y;
-      }
+      for (int q = 0; q < 16; ++q) work[q * 17 + hl] = x[POS16(q)];
       __syncwarp();
 #pragma unroll
-      for (int t = 0; t < 16; ++t) x[t].x = work[hl * 17 + t];
-      __syncwarp();
-#pragma unroll
-      for (int q = 0; q < 16; ++q) work[q * 17 + hl] = im[q];
-      __syncwarp();
-#pragma unroll
-      for (int t = 0; t < 16; ++t) x[t].y = work[hl * 17 + t];
+      for (int t = 0; t < 16; ++t) x[t] = work[hl * 17 + t];
       __syncwarp();
     }
     // ---- pass 2: DFT16 over t -> Z[hl + 16 p] at x[POS16(p)]
@@ -265,24 +290,31 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
         power[256 - k] = static_cast<float>(br * br + bi * bi);
       }
     }
+    if (hl < 7) power[257 + hl] = 0.f;  // read (x 0) by the padded mel taps
     __syncwarp();
 
-    // ---- sparse mel projection + log (TA:621-633); bins hl, hl+16, ..., hl+64
-    // (each band is padded to a multiple of four taps with zero weights: one 16-byte weight load per four FMAs, same
-    // summation order)
+    // ---- sparse mel projection + log (TA:621-633); bins hl, hl+16, ..., hl+64.  Every band is a whole number of aligned
+    // four-tap steps (zero weights in the padding); the step count of a group is uniform over the lanes, so all loads of
+    // the frame are issued up front under uniform predicates and the four partial sums of a band are independent.
 #pragma unroll
-    for (int i = 0; i < NMEL / 16; ++i) {
-      const float4* wv = reinterpret_cast<const float4*>(s.mel_w + mel_wo[i]);
-      const float* pw = power + mel_st[i];
-      float acc = 0.f;
-      for (int j = 0; j < mel_n4[i]; ++j) {
-        const float4 w = wv[j];
-        acc = fmaf(w.x, pw[4 * j], acc);
-        acc = fmaf(w.y, pw[4 * j + 1], acc);
-        acc = fmaf(w.z, pw[4 * j + 2], acc);
-        acc = fmaf(w.w, pw[4 * j + 3], acc);
+    for (int i = 0; i < MEL_GROUPS; ++i) {
+      const float4* pw = reinterpret_cast<const float4*>(power + mel_st[i]);
+      const float4* wv = reinterpret_cast<const float4*>(s.mel_w) + i * MEL_MAXJ * 16 + hl;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+      for (int j = 0; j < MEL_MAXJ; ++j) {
+        if (j < mel_nj[i]) {
+          const float4 w = wv[j * 16];
+          const float4 pv = pw[j];
+          a0 = fmaf(w.x, pv.x, a0);
+          a1 = fmaf(w.y, pv.y, a1);
+          a2 = fmaf(w.z, pv.z, a2);
+          a3 = fmaf(w.w, pv.w, a3);
+        }
       }
-      if (active) s.logmel[f][hl + 16 * i] = logf(fmaxf(acc, log_floor));
+      const float acc = (a0 + a1) + (a2 + a3);
+      // fast log: |err| < 4e-6 at these magnitudes; the floor itself (silence) maps to the exactly rounded log(eps) of the reference
+      if (active) s.logmel[f][hl + 16 * i] = acc > log_floor ? __logf(acc) : log_of_floor;
     }
     __syncwarp();
   }
@@ -348,7 +380,6 @@ extern "C" int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float*
   for (int q = 0; q < 16; ++q)
     for (int l = 0; l < 16; ++l) t->tw256[q][l] = make_double2(cos(two_pi * (q * l) / 256.0), -sin(two_pi * (q * l) / 256.0));
   for (int k = 0; k <= 128; ++k) t->tw512[k] = make_double2(cos(two_pi * k / 512.0), -sin(two_pi * k / 512.0));
-  int off = 0;
   for (int b = 0; b < NMEL; ++b) {
     const float* row = mel_banks + static_cast<size_t>(b) * NBIN;
     int first = -1, last = -1;
@@ -357,15 +388,18 @@ extern "C" int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float*
         if (first < 0) first = k;
         last = k;
       }
-    const int cnt = first < 0 ? 0 : last - first + 1;
-    const int cnt4 = (cnt + 3) & ~3;  // the kernel reads each band four taps at a time; the padding weights are zero
-    FA_REQUIRE(off + cnt4 <= MAX_TAPS, "mel filterbank has more than %d taps", MAX_TAPS);
-    t->mel_start[b] = first < 0 ? 0 : first;
-    t->mel_count[b] = cnt;
-    t->mel_woff[b] = off;
-    for (int j = 0; j < cnt; ++j) t->mel_w[off + j] = row[first + j];
-    off += cnt4;
+    const int start = first < 0 ? 0 : (first & ~3);
+    const int steps = first < 0 ? 0 : (last - start) / 4 + 1;
+    FA_REQUIRE(steps <= MEL_MAXJ, "mel band %d spans %d FFT bins: more than the %d aligned taps the kernel is compiled for", b,
+               last - first + 1, 4 * MEL_MAXJ);
+    const int g = b / 16, l = b % 16;
+    t->mel_start[b] = start;
+    if (steps > t->mel_steps[g]) t->mel_steps[g] = steps;
+    for (int k = first; first >= 0 && k <= last; ++k)
+      t->mel_w[((g * MEL_MAXJ + (k - start) / 4) * 16 + l) * 4 + ((k - start) & 3)] = row[k];
   }
+  for (int b = 0; b < NMEL; ++b)  // the kernel reads whole steps: they must stay inside the zero-padded power row (264 floats)
+    FA_REQUIRE(t->mel_start[b] + 4 * t->mel_steps[b / 16] <= 264, "mel band %d: padded taps run past the spectrum", b);
   return 0;
 }
 
