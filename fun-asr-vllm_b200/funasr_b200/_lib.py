@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfunasr_b200.so")
-ABI_VERSION = 9
+ABI_VERSION = 10
 FE_TILE_ROWS = 5  # FA_FE_TILE_ROWS
 
 i32, i64, f32, vp, sz = C.c_int32, C.c_int64, C.c_float, C.c_void_p, C.c_size_t
@@ -73,6 +73,8 @@ PROTOTYPES = {
     "fa_profile_collect": (C.c_int, [vp, vp, i32]),
     "fa_op_gemm": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, vp, i64, vp, i64, i32, i32, i32, i32, i32, vp]),
     "fa_op_layernorm": (C.c_int, [vp, vp, vp, vp, vp, i32, i32, vp]),
+    "fa_static_ln_capacity": (C.c_size_t, []),
+    "fa_op_ln_linear_static": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, i64, i32, i32, i32, i32, i32, vp]),
     "fa_op_embed_layernorm": (C.c_int, [vp, vp, vp, i32, f32, vp, vp, vp, i32, i32, vp]),
     "fa_op_gemm_ln": (C.c_int, [vp, i64, vp, i64, vp, vp, vp, i64, i32, i32, i32, i32, i32, i32, vp, C.POINTER(C.c_int32), i32, vp, vp, i64, vp, i64, vp]),
     "fa_op_fsmn": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, i32, i32, i32, i32, vp]),

@@ -44,7 +44,7 @@ extern "C" {
 
 typedef void* fa_stream_t; /* cudaStream_t */
 
-#define FA_ABI_VERSION 9
+#define FA_ABI_VERSION 10
 
 int fa_abi_version(void);
 const char* fa_last_error(void);
@@ -325,6 +325,23 @@ int fa_op_attention_fsmn(const void* qkv_dev, int64_t ld_qkv, const int32_t* cu_
                          int32_t max_len, int32_t n_heads, int32_t n_rows, void* ctx_dev, int64_t ld_ctx,
                          const float* fsmn_w_dev, int32_t fsmn_kernel, int32_t fsmn_left, void* mem_bf16_dev,
                          int64_t ld_mem, float* acc_f32_dev, int64_t ld_acc, fa_stream_t stream);
+
+/* ------------------------------------------------------------------ allocation-free variant
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ *   C[M,N] = LayerNorm(x[M,D]; g, b, eps 1e-12) (rounded to bf16) * W[N,D]^T (bf16) + bias; bf16 C (relu optional), or f32
+ *   C with out_f32 == 1.  Same two kernels as fa_op_layernorm(y_bf16) followed by fa_op_gemm, bit for bit; the
+ *   normalized bf16 rows between them live in a file-scope `static __device__` array of FA_STATIC_LN_ELEMS elements
+ *   (4 MiB, held by every GPU that loads the library until exit) instead of a caller buffer, and the call makes no
+ *   cudaMalloc / cudaFree / allocating library call.
+ *   Limit: M * D <= FA_STATIC_LN_ELEMS (4096 rows at D = 512), D % 8 == 0; anything larger is refused with an error.
+ *   All calls on a device share the array (it keeps the last call's contents; nothing in it needs clearing, a call
+ *   writes every row it reads): calls that overlap on the GPU - two streams, two host threads - race. */
+#define FA_STATIC_LN_ELEMS (2 * 1024 * 1024)
+size_t fa_static_ln_capacity(void); /* = FA_STATIC_LN_ELEMS */
+int fa_op_ln_linear_static(const float* x_dev, const float* g_dev, const float* b_dev, const void* w_dev, int64_t ldw,
+                           const float* bias_dev, void* c_dev, int64_t ldc, int32_t M, int32_t N, int32_t D, int32_t relu,
+                           int32_t out_f32, fa_stream_t stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop
