@@ -52,6 +52,17 @@ struct __align__(16) Tables {
   float mel_w[MEL_W];
 };
 
+// Everything a tile needs, resolved once: by every warp for a CTA's first tile, by warp 1 one tile ahead afterwards.
+struct TileDesc {
+  int valid;  // 0: nothing to do (utterance shorter than one frame, or a tile past its end)
+  int m;      // frames of the utterance (TA:62-66 snip_edges)
+  int i0, i1; // LFR rows [i0, i1) (MODE 0)
+  int f_lo;   // first frame staged
+  int nF;     // frames staged
+  int orow;   // output row of the utterance
+  int src_lo, src_hi;  // element offset of the tile's first sample in `wav` (two 32-bit halves)
+};
+
 struct __align__(16) Smem {
   double2 tw256[16][16];
   double2 tw512[130];
@@ -60,6 +71,7 @@ struct __align__(16) Smem {
   float logmel[MAX_FRAMES + 1][NMEL];
   float window[FRAME_LEN];
   float mel_w[MEL_W];
+  TileDesc desc[2];  // this tile and the CTA's next one (resolved by warp 1 during the frame phase), by tile parity
 };
 
 typedef double2 cplx;
@@ -113,25 +125,70 @@ __device__ __forceinline__ int utterance_of_tile(const int32_t* __restrict__ til
   return lo;
 }
 
+template <int MODE>
+__device__ __forceinline__ TileDesc resolve_tile(int id, const int32_t* __restrict__ tile_off, int n_utts,
+                                                 const int64_t* __restrict__ wav_start, const int32_t* __restrict__ wav_len,
+                                                 const int32_t* __restrict__ out_row, int lane) {
+  TileDesc d;
+  d.valid = 0; d.m = d.i0 = d.i1 = d.f_lo = d.nF = d.orow = d.src_lo = d.src_hi = 0;
+  int b, ti;
+  if (MODE == 0) {
+    b = utterance_of_tile(tile_off, n_utts, id, lane);
+    ti = id - __ldg(tile_off + b);
+  } else {
+    b = blockIdx.y;
+    ti = blockIdx.x;
+  }
+  const int n = __ldg(wav_len + b);
+  if (n < FRAME_LEN) return d;
+  const int m = 1 + (n - FRAME_LEN) / SHIFT;
+  int f_hi;
+  if (MODE == 0) {
+    const int T = (m + LFR_N - 1) / LFR_N;  // VLLM:43
+    d.i0 = ti * TILE_ROWS;
+    if (d.i0 >= T) return d;
+    d.i1 = min(d.i0 + TILE_ROWS, T);
+    d.f_lo = max(LFR_N * d.i0 - LFR_LEFT, 0);
+    f_hi = min(LFR_N * (d.i1 - 1) + LFR_M - 1 - LFR_LEFT, m - 1);
+  } else {
+    d.f_lo = ti * RAW_TILE_FRAMES;
+    if (d.f_lo >= m) return d;
+    f_hi = min(d.f_lo + RAW_TILE_FRAMES - 1, m - 1);
+  }
+  d.m = m;
+  d.nF = f_hi - d.f_lo + 1;
+  d.orow = __ldg(out_row + b);
+  const int64_t src = __ldg(wav_start + b) + static_cast<int64_t>(d.f_lo) * SHIFT;
+  d.src_lo = static_cast<int>(static_cast<uint32_t>(src));
+  d.src_hi = static_cast<int>(src >> 32);
+  d.valid = 1;
+  return d;
+}
+__device__ __forceinline__ int64_t tile_src(const TileDesc& d) {
+  return (static_cast<int64_t>(d.src_hi) << 32) | static_cast<uint32_t>(d.src_lo);
+}
+
 template <int MODE>  // 0: LFR + CMVN rows, 1: raw log-mel rows
 __global__ void __launch_bounds__(THREADS, 2)
 fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, const int64_t* __restrict__ wav_start,
              const int32_t* __restrict__ wav_len, const int32_t* __restrict__ out_row, const int32_t* __restrict__ tile_off, int n_utts,
-             int n_tiles, const float* __restrict__ cmvn, float* __restrict__ out, int64_t out_ld, float upscale, float preemph,
-             float log_floor) {
+             int n_tiles, const float* __restrict__ cmvn, float* __restrict__ out, int64_t out_ld, float win_scale, float smp_scale,
+             float preemph, float log_floor) {
   const float log_of_floor = logf(log_floor);
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15;
   pdl_launch_dependents();  // the first kernel of the path: its successor's prologue may overlap it
 
-  // ---- tables into shared memory, once per CTA (MODE 0 CTAs are persistent over tiles)
-  for (int i = tid; i < FRAME_LEN; i += THREADS) s.window[i] = __ldg(&tab->window[i]);
+  // ---- tables into shared memory, once per CTA (MODE 0 CTAs are persistent over tiles).  The sample scale (x 32768,
+  // VLLM:140-141) is folded into the window when it is a power of two: scaling by 2^k commutes with every fp32 rounding of the
+  // DC removal, the pre-emphasis and the window product, so the frames entering the FFT carry the same bits either way.
+  for (int i = tid; i < FRAME_LEN; i += THREADS) s.window[i] = __ldg(&tab->window[i]) * win_scale;
   for (int i = tid; i < 130; i += THREADS) s.tw512[i] = tab->tw512[i];
   for (int i = tid; i < 256; i += THREADS) (&s.tw256[0][0])[i] = (&tab->tw256[0][0])[i];
   for (int i = tid; i < MEL_W / 4; i += THREADS)
     reinterpret_cast<float4*>(s.mel_w)[i] = __ldg(reinterpret_cast<const float4*>(tab->mel_w) + i);
-  // this lane's five mel bins (hl, hl + 16, ..., hl + 64): first FFT bin, taps padded to a multiple of 4, weight offset
+  // this lane's five mel bins (hl, hl + 16, ..., hl + 64): first FFT bin (a multiple of four), four-tap steps of the group
   int mel_st[MEL_GROUPS], mel_nj[MEL_GROUPS];
 #pragma unroll
   for (int i = 0; i < MEL_GROUPS; ++i) {
@@ -139,72 +196,48 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     mel_nj[i] = __ldg(&tab->mel_steps[i]);
   }
 
+  // PCM of a tile -> shared memory, asynchronously (16-byte cp.async; nS is a multiple of 8); the caller waits before use
+  auto stage = [&](const TileDesc& d) {
+    const float* src = wav + tile_src(d);
+    const int nS = (d.nF - 1) * SHIFT + FRAME_LEN;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+      const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(s.samples));
+      for (int i = tid; i < nS / 4; i += THREADS)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * i), "l"(src + 4 * i) : "memory");
+    } else {
+      for (int i = tid; i < nS; i += THREADS) s.samples[i] = __ldg(src + i);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
   const int first_tile = MODE == 0 ? static_cast<int>(blockIdx.x) : 0;
   const int tile_step = MODE == 0 ? static_cast<int>(gridDim.x) : 1;
   const int tile_end = MODE == 0 ? n_tiles : 1;
-  for (int id = first_tile; id < tile_end; id += tile_step) {
-  int b, ti;
-  if (MODE == 0) {
-    b = utterance_of_tile(tile_off, n_utts, id, lane);
-    ti = id - __ldg(tile_off + b);
-    // the PCM of this CTA's next tile is requested into L2 now, a whole tile of arithmetic ahead of its staging loop
-    if (warp == 1 && id + tile_step < tile_end) {
-      const int nb = utterance_of_tile(tile_off, n_utts, id + tile_step, lane);
-      const int nti = id + tile_step - __ldg(tile_off + nb);
-      const int nn = wav_len[nb];
-      if (lane == 0 && nn >= FRAME_LEN) {
-        const int nm = 1 + (nn - FRAME_LEN) / SHIFT;
-        const int nT = (nm + LFR_N - 1) / LFR_N;
-        const int ni0 = nti * TILE_ROWS;
-        if (ni0 < nT) {
-          const int ni1 = min(ni0 + TILE_ROWS, nT);
-          const int nlo = max(LFR_N * ni0 - LFR_LEFT, 0);
-          const int nhi = min(LFR_N * (ni1 - 1) + LFR_M - 1 - LFR_LEFT, nm - 1);
-          const float* nsrc = wav + wav_start[nb] + static_cast<int64_t>(nlo) * SHIFT;
-          const uint32_t nbytes = static_cast<uint32_t>(((nhi - nlo) * SHIFT + FRAME_LEN) * 4);
-          if ((reinterpret_cast<uintptr_t>(nsrc) & 15) == 0)
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nsrc), "r"(nbytes) : "memory");
-        }
-      }
-    }
-  } else {
-    b = blockIdx.y;
-    ti = blockIdx.x;
-  }
-  const int64_t w0 = wav_start[b];
-  const int n = wav_len[b];
-  if (n < FRAME_LEN) continue;
-  const int m = 1 + (n - FRAME_LEN) / SHIFT;  // TA:62-66 snip_edges
-  int i0 = 0, i1 = 0, f_lo, f_hi;
-  if (MODE == 0) {
-    const int T = (m + LFR_N - 1) / LFR_N;  // VLLM:43
-    i0 = ti * TILE_ROWS;
-    if (i0 >= T) continue;
-    i1 = min(i0 + TILE_ROWS, T);
-    f_lo = max(LFR_N * i0 - LFR_LEFT, 0);
-    f_hi = min(LFR_N * (i1 - 1) + LFR_M - 1 - LFR_LEFT, m - 1);
-  } else {
-    f_lo = ti * RAW_TILE_FRAMES;
-    if (f_lo >= m) continue;
-    f_hi = min(f_lo + RAW_TILE_FRAMES - 1, m - 1);
-  }
-  const int nF = f_hi - f_lo + 1;
-  const int nS = (nF - 1) * SHIFT + FRAME_LEN;
-
-  // ---- stage PCM (x upscale, VLLM:140-141) into shared memory; nS is a multiple of 8
   {
-    const float* src = wav + w0 + static_cast<int64_t>(f_lo) * SHIFT;
-    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
-      for (int i = tid; i < nS / 4; i += THREADS) {
-        float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
-        v.x *= upscale; v.y *= upscale; v.z *= upscale; v.w *= upscale;
-        reinterpret_cast<float4*>(s.samples)[i] = v;
-      }
-    } else {
-      for (int i = tid; i < nS; i += THREADS) s.samples[i] = __ldg(src + i) * upscale;
+    const TileDesc first = resolve_tile<MODE>(first_tile, tile_off, n_utts, wav_start, wav_len, out_row, lane);
+    if (tid == 0) s.desc[0] = first;
+    if (first_tile < tile_end && first.valid) stage(first);
+  }
+  int par = 0;  // descriptors live in shared memory (only the parity is carried in a register across the frame loop)
+  for (int id = first_tile; id < tile_end; id += tile_step, par ^= 1) {
+  asm volatile("cp.async.wait_all;" ::: "memory");
+  __syncthreads();  // this tile's samples have landed; the previous tile's rows have left the log-mel buffer
+  const TileDesc& cur = s.desc[par];
+  const bool has_next = MODE == 0 && id + tile_step < tile_end;
+  if (has_next && warp == 1) {
+    // one warp resolves the CTA's next tile while the others start on the frames; its PCM is requested into L2 now, a whole
+    // tile of arithmetic ahead of the cp.async that stages it
+    const TileDesc nx = resolve_tile<MODE>(id + tile_step, tile_off, n_utts, wav_start, wav_len, out_row, lane);
+    if (lane == 0) {
+      s.desc[par ^ 1] = nx;
+      const float* nsrc = wav + tile_src(nx);
+      if (nx.valid && (reinterpret_cast<uintptr_t>(nsrc) & 15) == 0)
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nsrc),
+                     "r"(static_cast<uint32_t>(((nx.nF - 1) * SHIFT + FRAME_LEN) * 4))
+                     : "memory");
     }
   }
-  __syncthreads();
+  const int nF = cur.valid ? cur.nF : 0;
 
   const int slot = warp * 2 + (lane >> 4);
   double2* work = s.work[slot];
@@ -225,6 +258,7 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
       const int sidx = 2 * hl + 32 * j;
       float2 v = make_float2(0.f, 0.f);
       if (j < 12 || hl < 8) v = *reinterpret_cast<const float2*>(xs + sidx);
+      if (smp_scale != 1.f) { v.x *= smp_scale; v.y *= smp_scale; }  // a scale that is not a power of two (uniform branch)
       xf[j] = v;
       ps[j] = v.x + v.y;
     }
@@ -244,7 +278,8 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     for (int j = 0; j < 13; ++j) {
       const int sidx = 2 * hl + 32 * j;
       if (j < 12 || hl < 8) {
-        const float rp = xs[sidx > 0 ? sidx - 1 : 0];
+        float rp = xs[sidx > 0 ? sidx - 1 : 0];
+        if (smp_scale != 1.f) rp *= smp_scale;
         const float a0 = __fsub_rn(xf[j].x, mean), a1 = __fsub_rn(xf[j].y, mean), ap = __fsub_rn(rp, mean);
         const float y0 = __fsub_rn(a0, __fmul_rn(preemph, ap));
         const float y1 = __fsub_rn(a1, __fmul_rn(preemph, a0));
@@ -318,38 +353,54 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     }
     __syncwarp();
   }
-  __syncthreads();
+  // this thread's CMVN column (MODE 0: threads 0..139 own one float4 column of the 560 for every row of the tile), requested
+  // before the barrier so that its latency overlaps the wait
+  constexpr int V = FEAT / 4;  // 140 float4 per row
+  float4 mu = make_float4(0.f, 0.f, 0.f, 0.f), sc = make_float4(1.f, 1.f, 1.f, 1.f);
+  if (MODE == 0 && cmvn != nullptr && tid < V) {
+    mu = __ldg(reinterpret_cast<const float4*>(cmvn) + tid);
+    sc = __ldg(reinterpret_cast<const float4*>(cmvn + FEAT) + tid);
+  }
+  __syncthreads();  // log-mel rows complete, samples free, s.next visible
+
+  if (has_next && s.desc[par ^ 1].valid) stage(s.desc[par ^ 1]);  // lands while this tile's rows are written out
+  const int m = cur.m, i0 = cur.i0, i1 = cur.i1, f_lo = cur.f_lo;
 
   if (MODE == 0) {
     // ---- LFR gather (VLLM:40-60 closed form) + CMVN (VLLM:23-37), coalesced float4 rows
-    const int rows = i1 - i0;
-    constexpr int V = FEAT / 4;  // 140 float4 per row
-    float* obase = out + static_cast<int64_t>(out_row[b] + i0) * out_ld;
-    for (int idx = tid; idx < rows * V; idx += THREADS) {
-      const int r = idx / V, c4 = idx - r * V;
-      const int col = c4 * 4, j = col / NMEL, c = col - j * NMEL;
-      int fr = LFR_N * (i0 + r) + j - LFR_LEFT;
-      fr = min(max(fr, 0), m - 1) - f_lo;
-      float4 v = *reinterpret_cast<const float4*>(&s.logmel[fr][c]);
-      if (cmvn != nullptr) {
-        const float4 mu = __ldg(reinterpret_cast<const float4*>(cmvn + col));
-        const float4 sc = __ldg(reinterpret_cast<const float4*>(cmvn + FEAT + col));
-        v.x = (v.x + mu.x) * sc.x; v.y = (v.y + mu.y) * sc.y;
-        v.z = (v.z + mu.z) * sc.z; v.w = (v.w + mu.w) * sc.w;
+    if (cur.valid && tid < V) {
+      const int col = tid * 4, j = col / NMEL, c = col - j * NMEL;
+      float* obase = out + static_cast<int64_t>(cur.orow + i0) * out_ld + col;
+      for (int r = 0; r < i1 - i0; ++r) {
+        int fr = LFR_N * (i0 + r) + j - LFR_LEFT;
+        fr = min(max(fr, 0), m - 1) - f_lo;
+        float4 v = *reinterpret_cast<const float4*>(&s.logmel[fr][c]);
+        if (cmvn != nullptr) {
+          v.x = (v.x + mu.x) * sc.x; v.y = (v.y + mu.y) * sc.y;
+          v.z = (v.z + mu.z) * sc.z; v.w = (v.w + mu.w) * sc.w;
+        }
+        *reinterpret_cast<float4*>(obase + static_cast<int64_t>(r) * out_ld) = v;
       }
-      *reinterpret_cast<float4*>(obase + static_cast<int64_t>(r) * out_ld + col) = v;
     }
-  } else {
-    constexpr int V = NMEL / 4;
-    float* obase = out + static_cast<int64_t>(out_row[b] + f_lo) * out_ld;
-    for (int idx = tid; idx < nF * V; idx += THREADS) {
-      const int r = idx / V, c4 = idx - r * V;
+  } else if (cur.valid) {
+    constexpr int VM = NMEL / 4;
+    float* obase = out + static_cast<int64_t>(cur.orow + f_lo) * out_ld;
+    for (int idx = tid; idx < nF * VM; idx += THREADS) {
+      const int r = idx / VM, c4 = idx - r * VM;
       *reinterpret_cast<float4*>(obase + static_cast<int64_t>(r) * out_ld + c4 * 4) =
           *reinterpret_cast<const float4*>(&s.logmel[r][c4 * 4]);
     }
   }
-  __syncthreads();  // samples / logmel are rewritten by the next tile
   }
+  asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
+// A power-of-two sample scale goes into the window (exact); anything else is applied to the samples as they are read.
+struct Scales { float win, smp; };
+static Scales split_scale(float upscale) {
+  int e = 0;
+  const bool pow2 = upscale > 0.f && frexpf(upscale, &e) == 0.5f;
+  return pow2 ? Scales{upscale, 1.f} : Scales{1.f, upscale};
 }
 
 static int check_cfg(const fa_frontend_cfg* c) {
@@ -417,13 +468,14 @@ extern "C" int fa_frontend_forward(const fa_frontend_cfg* cfg, const void* table
   if (n_tiles <= 0) return 0;
   static SmemOptIn opt0;
   if (int r = opt_in_smem(fbank_kernel<0>, (int)sizeof(Smem), opt0)) return r;
+  const Scales sc = split_scale(cfg->upscale);
   ProfScope _ps(K_FRONTEND, static_cast<cudaStream_t>(stream));
   // persistent CTAs (two per SM: registers and shared memory), tiles dealt round-robin: the tables are staged once per CTA
   const int grid = n_tiles < 2 * sm_count() ? n_tiles : 2 * sm_count();
   fbank_kernel<0><<<grid, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
       static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, tile_off_dev, n_utts, n_tiles,
       cmvn_dev,
-      out_dev, out_ld, cfg->upscale, cfg->preemph, cfg->log_floor);
+      out_dev, out_ld, sc.win, sc.smp, cfg->preemph, cfg->log_floor);
   FA_CHECK_LAUNCH();
   return 0;
 }
@@ -439,11 +491,12 @@ extern "C" int fa_frontend_logmel(const fa_frontend_cfg* cfg, const void* tables
   static SmemOptIn opt1;
   if (int r = opt_in_smem(fbank_kernel<1>, (int)sizeof(Smem), opt1)) return r;
   dim3 grid(ceil_div(max_frames, RAW_TILE_FRAMES), n_utts);
+  const Scales sc = split_scale(cfg->upscale);
   ProfScope _ps(K_FRONTEND, static_cast<cudaStream_t>(stream));
   fbank_kernel<1><<<grid, THREADS, sizeof(Smem), static_cast<cudaStream_t>(stream)>>>(
       static_cast<const Tables*>(tables_dev), wav_dev, wav_start_dev, wav_len_dev, out_row_dev, nullptr, n_utts, 1, nullptr,
       out_dev,
-      out_ld, cfg->upscale, cfg->preemph, cfg->log_floor);
+      out_ld, sc.win, sc.smp, cfg->preemph, cfg->log_floor);
   FA_CHECK_LAUNCH();
   return 0;
 }
