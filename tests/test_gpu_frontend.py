@@ -137,6 +137,29 @@ def test_translation_and_linearity_properties():
     np.testing.assert_allclose(c - a, math.log(4.0), atol=2e-5)
 
 
+def test_sample_scale_in_the_window_or_on_the_samples_gives_the_same_bits():
+    """The x32768 of ``upsacle_samples`` (VLLM/transformers_utils/processors/funasr.py:140-141) is a power of two: the kernel
+    folds it into the window, which must give the bits of scaling the samples first (what the reference does).  A scale that
+    is not a power of two takes the other branch (samples scaled as they are read): identical to pre-scaled input."""
+    from funasr_b200 import WavFrontend, pack_waveforms
+
+    g = torch.Generator().manual_seed(5)
+    w = 0.4 * (2 * torch.rand(48000, generator=g) - 1)
+    lens = np.array([48000])
+    mk = lambda up: WavFrontend(fs=16000, window="hamming", n_mels=80, frame_length=25, frame_shift=10, lfr_m=7, lfr_n=6,
+                                dither=0.0, upsacle_samples=up, device="cuda")
+    fe_up, fe_raw = mk(True), mk(False)
+    a, _ = fe_up.logmel(*pack_waveforms([w], "cuda"), lens)
+    b, _ = fe_raw.logmel(*pack_waveforms([w * 32768.0], "cuda"), lens)
+    assert torch.equal(a, b)
+    fe3 = mk(False)
+    fe3._cfg.upscale = 3.0  # not a power of two
+    c, _ = fe3.logmel(*pack_waveforms([w], "cuda"), lens)
+    d, _ = fe_raw.logmel(*pack_waveforms([w * 3.0], "cuda"), lens)
+    assert torch.equal(c, d)
+    assert not torch.equal(c, b)
+
+
 def test_short_or_empty_input_raises():
     from funasr_b200 import extract_fbank
 
