@@ -40,8 +40,12 @@ ENC_CONF = dict(output_size=512, attention_heads=4, linear_units=2048, num_block
 AD_CONF = dict(downsample_rate=1, encoder_dim=512, llm_dim=1024, ffn_dim=2048, n_layer=2, attention_heads=8)
 GEMM_FLOP_PER_TOKEN = 465_715_200  # SURVEY.md §8d / BASELINE.md §4
 ATTN_FLOP_PER_TOKEN_PER_T = 151_552
-DFMA_PEAK_TFLOPS = 37.0  # B200 fp64 FMA pipe (nominal; MEASURED_PEAKS.json has no fp64 figure)
-FE_FP64_FLOP_PER_FRAME = 19_500  # 256-pt complex FFT (two radix-16 passes) + twiddles + split + |X|^2, in fp64
+# Frontend, per warp and frame pair, counted on the executed path of the shipped SASS (cuobjdump -sass, the frame loop of
+# fbank_kernel<0>): 1200 warp instructions of which 466 are fp64 (258 DADD + 122 DFMA + 86 DMUL).  A sub-partition
+# issues one warp instruction per clock and its fp64 pipe takes one every two clocks.
+FE_INSTR_PER_FRAME_PAIR = 1200
+FE_FP64_INSTR_PER_FRAME_PAIR = 466
+SM_SUBPARTITIONS = 148 * 4
 
 
 def workload_lengths(name: str) -> np.ndarray:
@@ -475,12 +479,15 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
         if fe_ms > 0:
             fe_bytes = float(4 * main_in.lengths.sum() + 4 * 560 * main_in.T.sum())
             frames = float((1 + (main_in.lengths - 400) // 160).sum())
+            fe_clk = 1e6 * float((clocks or {}).get("sm_max_mhz") or 1965.0)
             line["roofline_frontend"] = {"bound": "hbm", "kernel": "fbank_kernel<0>", "achieved": fe_bytes / (fe_ms * 1e-3) / 1e9,
                                          "peak": hbm, "unit": "GB/s", "frac": fe_bytes / (fe_ms * 1e-3) / 1e9 / hbm, "traffic": traffic_fe,
                                          "ms": fe_ms,
-                                         # the FFT runs in fp64 (parity): fraction of the DFMA pipe's nominal peak
-                                         "frac_fp64": frames * FE_FP64_FLOP_PER_FRAME / (fe_ms * 1e-3) / 1e12 / DFMA_PEAK_TFLOPS,
-                                         "fp64_peak_tflops_nominal": DFMA_PEAK_TFLOPS}
+                                         # the FFT runs in fp64 (parity): share of the fp64 pipe's and of the
+                                         # issue slots' cycles the kernel's instruction counts account for, at the max SM clock
+                                         "frac_fp64": frames / 2 * FE_FP64_INSTR_PER_FRAME_PAIR * 2 / (SM_SUBPARTITIONS * fe_clk * fe_ms * 1e-3),
+                                         "frac_issue": frames / 2 * FE_INSTR_PER_FRAME_PAIR / (SM_SUBPARTITIONS * fe_clk * fe_ms * 1e-3),
+                                         "sm_clock_hz_assumed": fe_clk}
         if strong:
             line["strong"] = strong
         if world == 1 and not args.no_extras:

@@ -24,6 +24,9 @@
 namespace fa {
 namespace fe {
 
+#ifndef FA_FE_MEL_BATCH
+#define FA_FE_MEL_BATCH 1  // 0: one mel group at a time for every bank (measurement builds)
+#endif
 constexpr int FRAME_LEN = 400;
 constexpr int SHIFT = 160;
 constexpr int NFFT = 512;
@@ -45,10 +48,11 @@ constexpr int MEL_W = MEL_GROUPS * MEL_MAXJ * 16 * 4;  // weights as [group][ste
 
 struct __align__(16) Tables {
   float window[FRAME_LEN];
-  double2 tw256[16][16];  // [q][t] = W256^(t q) = (cos, -sin)(2 pi t q / 256): pass-1 -> pass-2 twiddles, lane t reads [q][t]
-  double2 tw512[130];     // W512^k, k = 0..128
+  double2 tw256[16];  // [t] = W256^t = (cos, -sin)(2 pi t / 256): lane t builds its pass-1 -> pass-2 twiddles W256^(t q) from it
+  double2 sc512[16];  // [t] = (sin, cos)(2 pi t / 512): lane t builds its split constants for k = t + 16 p from it
   int mel_start[NMEL];       // first FFT bin of the band, rounded down to a multiple of four (16-byte power loads)
-  int mel_steps[8];          // per group: four-tap steps of its widest band (uniform over the lanes; shorter bands carry zeros)
+  int mel_steps[8];          // per group: four-tap steps of its widest band (uniform over the lanes; shorter bands carry zeros);
+                             // [7]: 1 when every group has exactly mel_cap<true>() steps (the batched mel path), else 0
   float mel_w[MEL_W];
 };
 
@@ -64,9 +68,11 @@ struct TileDesc {
 };
 
 struct __align__(16) Smem {
-  double2 tw256[16][16];
-  double2 tw512[130];
-  double2 work[SLOTS][16 * 17];  // 16x17 padded complex transpose buffer; the slot's power spectrum (264 floats) reuses it
+  double2 tw256[16];
+  double2 sc512[16];
+  // 16x17 padded complex transpose buffer; the slot's power spectrum (264 floats) reuses it.  Slots are 64 bytes (16 banks) out of
+  // step with each other, so that the two half-warps of a warp (two slots) store their power values into different banks.
+  double2 work[SLOTS][16 * 17 + 4];
   float samples[MAX_SAMPLES + 8];
   float logmel[MAX_FRAMES + 1][NMEL];
   float window[FRAME_LEN];
@@ -78,6 +84,14 @@ typedef double2 cplx;
 __device__ __forceinline__ cplx mk(double re, double im) { return make_double2(re, im); }
 __device__ __forceinline__ cplx cmul(cplx a, cplx b) { return mk(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 
+// cos / sin (p pi / 16), p = 0..8
+__device__ __host__ constexpr double cos_p16(int p) {
+  constexpr double t[9] = {1.0, 0.98078528040323044913, 0.92387953251128675613, 0.83146961230254523708, 0.70710678118654752440,
+                           0.55557023301960222474, 0.38268343236508977173, 0.19509032201612826785, 0.0};
+  return t[p];
+}
+__device__ __host__ constexpr double sin_p16(int p) { return cos_p16(8 - p); }
+
 // 4-point DFT in place: (a,b,c,d) -> (X0,X1,X2,X3), W4 = -i.
 __device__ __forceinline__ void dft4(cplx& a, cplx& b, cplx& c, cplx& d) {
   const cplx s0 = mk(a.x + c.x, a.y + c.y), s1 = mk(a.x - c.x, a.y - c.y);
@@ -88,13 +102,27 @@ __device__ __forceinline__ void dft4(cplx& a, cplx& b, cplx& c, cplx& d) {
   d = mk(s1.x - s3.y, s1.y + s3.x);  // s1 + i*s3
 }
 
+// The same with d == 0 (the zero padding 400 -> 512 of the frame): four additions fewer.
+__device__ __forceinline__ void dft4_d0(cplx& a, cplx& b, cplx& c, cplx& d) {
+  const cplx s0 = mk(a.x + c.x, a.y + c.y), s1 = mk(a.x - c.x, a.y - c.y), s2 = b;
+  a = mk(s0.x + s2.x, s0.y + s2.y);
+  c = mk(s0.x - s2.x, s0.y - s2.y);
+  b = mk(s1.x + s2.y, s1.y - s2.x);
+  d = mk(s1.x - s2.y, s1.y + s2.x);
+}
+
 // 16-point DFT, 4x4 Cooley-Tukey in registers.  Input x[j] natural order; output X[q] is left at
-// position POS16(q) = 4*(q&3) + (q>>2).
+// position POS16(q) = 4*(q&3) + (q>>2).  ZPAD: x[13], x[14], x[15] are known to be zero.
 #define POS16(q) (4 * ((q)&3) + ((q) >> 2))
+template <bool ZPAD>
 __device__ __forceinline__ void fft16(cplx (&x)[16]) {
   constexpr double C1 = 0.92387953251128675613, S1 = 0.38268343236508977173, R = 0.70710678118654752440;
+  dft4(x[0], x[4], x[8], x[12]);
 #pragma unroll
-  for (int j0 = 0; j0 < 4; ++j0) dft4(x[j0], x[4 + j0], x[8 + j0], x[12 + j0]);
+  for (int j0 = 1; j0 < 4; ++j0) {
+    if (ZPAD) dft4_d0(x[j0], x[4 + j0], x[8 + j0], x[12 + j0]);
+    else dft4(x[j0], x[4 + j0], x[8 + j0], x[12 + j0]);
+  }
   // A[j0][q0] now sits at x[4*q0 + j0]; multiply by W16^(j0*q0)
   x[4 * 1 + 1] = cmul(x[4 * 1 + 1], mk(C1, -S1));  // W^1
   x[4 * 2 + 1] = mk(R * (x[4 * 2 + 1].x + x[4 * 2 + 1].y), R * (x[4 * 2 + 1].y - x[4 * 2 + 1].x));  // W^2 = R(1 - i)
@@ -168,6 +196,55 @@ __device__ __forceinline__ int64_t tile_src(const TileDesc& d) {
   return (static_cast<int64_t>(d.src_hi) << 32) | static_cast<uint32_t>(d.src_lo);
 }
 
+// Compile-time bound on the four-tap steps of a group: the Kaldi mel banks of the compiled geometry (80 bands, 20 Hz .. Nyquist
+// at 16 kHz) need exactly {2, 2, 3, 3, 5}; any other bank takes the generic bound, one group at a time (Tables::mel_steps[7]).
+template <bool STD>
+__device__ __host__ constexpr int mel_cap(int g) { return !STD ? MEL_MAXJ : g < 2 ? 2 : g < 4 ? 3 : 5; }
+
+// Mel bands hl + 16 i, i in [I0, I1): loads first, multiplies after.  Accumulation order as in a plain loop over the steps (four
+// independent partial sums per band), so the result does not depend on the batching.
+template <bool STD>
+__device__ __host__ constexpr int mel_off(int g0, int g) {  // steps of groups [g0, g)
+  int n = 0;
+  for (int i = g0; i < g; ++i) n += mel_cap<STD>(i);
+  return n;
+}
+template <int I0, int I1, bool STD>
+__device__ __forceinline__ void mel_groups(const float* power, const float* mel_w, const int (&mel_st)[MEL_GROUPS],
+                                           const int (&mel_nj)[MEL_GROUPS], int hl, bool active, float* logrow, float log_floor,
+                                           float log_of_floor) {
+  constexpr int NS = mel_off<STD>(I0, I1);
+  float4 w[NS], pv[NS];
+#pragma unroll
+  for (int i = I0; i < I1; ++i) {
+    const float4* pw = reinterpret_cast<const float4*>(power + mel_st[i]);
+    const float4* wv = reinterpret_cast<const float4*>(mel_w) + i * MEL_MAXJ * 16 + hl;
+#pragma unroll
+    for (int j = 0; j < mel_cap<STD>(i); ++j) {
+      // STD: the group has exactly mel_cap steps (Tables::mel_steps[7]); otherwise a uniform predicate, zeros beyond the last step
+      const bool on = STD || j < mel_nj[i];
+      w[mel_off<STD>(I0, i) + j] = on ? wv[j * 16] : make_float4(0.f, 0.f, 0.f, 0.f);
+      pv[mel_off<STD>(I0, i) + j] = on ? pw[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+#pragma unroll
+  for (int i = I0; i < I1; ++i) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+    for (int j = 0; j < mel_cap<STD>(i); ++j) {
+      if (STD || j < mel_nj[i]) {
+        a0 = fmaf(w[mel_off<STD>(I0, i) + j].x, pv[mel_off<STD>(I0, i) + j].x, a0);
+        a1 = fmaf(w[mel_off<STD>(I0, i) + j].y, pv[mel_off<STD>(I0, i) + j].y, a1);
+        a2 = fmaf(w[mel_off<STD>(I0, i) + j].z, pv[mel_off<STD>(I0, i) + j].z, a2);
+        a3 = fmaf(w[mel_off<STD>(I0, i) + j].w, pv[mel_off<STD>(I0, i) + j].w, a3);
+      }
+    }
+    const float acc = (a0 + a1) + (a2 + a3);
+    // fast log: |err| < 4e-6 at these magnitudes; the floor itself (silence) maps to the exactly rounded log(eps) of the reference
+    if (active) logrow[hl + 16 * i] = acc > log_floor ? __logf(acc) : log_of_floor;
+  }
+}
+
 template <int MODE>  // 0: LFR + CMVN rows, 1: raw log-mel rows
 __global__ void __launch_bounds__(THREADS, 2)
 fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, const int64_t* __restrict__ wav_start,
@@ -184,8 +261,10 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
   // VLLM:140-141) is folded into the window when it is a power of two: scaling by 2^k commutes with every fp32 rounding of the
   // DC removal, the pre-emphasis and the window product, so the frames entering the FFT carry the same bits either way.
   for (int i = tid; i < FRAME_LEN; i += THREADS) s.window[i] = __ldg(&tab->window[i]) * win_scale;
-  for (int i = tid; i < 130; i += THREADS) s.tw512[i] = tab->tw512[i];
-  for (int i = tid; i < 256; i += THREADS) (&s.tw256[0][0])[i] = (&tab->tw256[0][0])[i];
+  if (tid < 16) {
+    s.tw256[tid] = tab->tw256[tid];
+    s.sc512[tid] = tab->sc512[tid];
+  }
   for (int i = tid; i < MEL_W / 4; i += THREADS)
     reinterpret_cast<float4*>(s.mel_w)[i] = __ldg(reinterpret_cast<const float4*>(tab->mel_w) + i);
   // this lane's five mel bins (hl, hl + 16, ..., hl + 64): first FFT bin (a multiple of four), four-tap steps of the group
@@ -195,6 +274,7 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     mel_st[i] = __ldg(&tab->mel_start[hl + 16 * i]);
     mel_nj[i] = __ldg(&tab->mel_steps[i]);
   }
+  const bool mel_std = FA_FE_MEL_BATCH && __ldg(&tab->mel_steps[7]) != 0;
 
   // PCM of a tile -> shared memory, asynchronously (16-byte cp.async; nS is a multiple of 8); the caller waits before use
   auto stage = [&](const TileDesc& d) {
@@ -277,9 +357,12 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
 #pragma unroll
     for (int j = 0; j < 13; ++j) {
       const int sidx = 2 * hl + 32 * j;
+      // the sample before the pair (replicate-left at the frame start, TA:193-198) is the second sample of lane hl - 1's pair j;
+      // lane 0 takes lane 15's pair j - 1.  A shuffle instead of a second pass over the staged samples.
+      const float snd = hl == 15 ? xf[j > 0 ? j - 1 : 0].y : xf[j].y;
+      float rp = __shfl_sync(0xffffffffu, snd, (hl + 15) & 15, 16);
+      if (j == 0 && hl == 0) rp = xf[0].x;
       if (j < 12 || hl < 8) {
-        float rp = xs[sidx > 0 ? sidx - 1 : 0];
-        if (smp_scale != 1.f) rp *= smp_scale;
         const float a0 = __fsub_rn(xf[j].x, mean), a1 = __fsub_rn(xf[j].y, mean), ap = __fsub_rn(rp, mean);
         const float y0 = __fsub_rn(a0, __fmul_rn(preemph, ap));
         const float y1 = __fsub_rn(a1, __fmul_rn(preemph, a0));
@@ -291,9 +374,26 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
     x[13] = x[14] = x[15] = mk(0.0, 0.0);  // zero padding 400 -> 512 (TA:207-211)
 
     // ---- pass 1: DFT16 over j, twiddle W256^(t q), transpose through smem
-    fft16(x);
+    fft16<true>(x);
 #pragma unroll
-    for (int q = 1; q < 16; ++q) x[POS16(q)] = cmul(x[POS16(q)], s.tw256[q][hl]);
+    {  // twiddles W256^(hl q), q = 1..15, as two interleaved product chains (odd and even q) from the lane's W256^hl: fourteen
+       // complex products instead of fifteen 16-byte table reads per lane (shared-memory wavefronts are what bounds this kernel);
+       // the chains add a few 1e-16 of relative error
+      const cplx w1 = s.tw256[hl];
+      const cplx w2 = cmul(w1, w1);
+      cplx po = w1, pe = w2;
+      x[POS16(1)] = cmul(x[POS16(1)], po);
+      x[POS16(2)] = cmul(x[POS16(2)], pe);
+#pragma unroll
+      for (int q = 3; q < 16; q += 2) {
+        po = cmul(po, w2);
+        x[POS16(q)] = cmul(x[POS16(q)], po);
+        if (q + 1 < 16) {
+          pe = cmul(pe, w2);
+          x[POS16(q + 1)] = cmul(x[POS16(q + 1)], pe);
+        }
+      }
+    }
     {  // 16-byte accesses: rows of 17 complex values keep both directions at the two-wavefront minimum
 #pragma unroll
       for (int q = 0; q < 16; ++q) work[q * 17 + hl] = x[POS16(q)];
@@ -303,11 +403,17 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
       __syncwarp();
     }
     // ---- pass 2: DFT16 over t -> Z[hl + 16 p] at x[POS16(p)]
-    fft16(x);
+    fft16<false>(x);
 
-    // ---- split the packed real FFT:  X[k] = Xe + W512^k Xo,  X[256-k] = conj(Xe - W512^k Xo),  k = hl + 16 p.
-    // Z[256 - k] = Z[(16 - hl) + 16 (15 - p)] lives in lane (16 - hl) & 15 at p' = 15 - p; for hl == 0 it is this
-    // lane's own Z[16 ((16 - p) & 15)].
+    // ---- split the packed real FFT and take |.|^2 in one step.  With zk = Z[k], zm = Z[256 - k], A = zk + conj(zm),
+    // B = zk - conj(zm), w' = -i W512^k:  2 X[k] = A + w' B,  2 conj(X[256-k]) = A - w' B, hence (|w'| = 1)
+    //   |X[k]|^2, |X[256-k]|^2 = (|zk|^2 + |zm|^2) / 2  +-  (Re(w') / 2 * (|zk|^2 - |zm|^2) - Im(w') * Im(zk zm))
+    // (12 fp64 operations per bin pair instead of 20 through Xe and W512^k Xo).  The difference form loses
+    // eps64 * (|X[k]| / |X[256-k]|)^2 relative precision on the weaker bin of a pair: 1e-8 at 80 dB between the two, 1e-4 at 120 dB,
+    // still under the 1e-3 log-mel budget where the reference's own fp32 FFT is off by tens of per cent.
+    // k = hl + 16 p; Z[256 - k] = Z[(16 - hl) + 16 (15 - p)] lives in lane (16 - hl) & 15 at p' = 15 - p; for hl == 0 it is
+    // this lane's own Z[16 ((16 - p) & 15)].
+    const cplx sc = s.sc512[hl];  // (sin, cos)(2 pi hl / 512); the constants of bin k = hl + 16 p follow by a rotation by p pi / 16
 #pragma unroll
     for (int p = 0; p < 9; ++p) {
       const cplx own = x[POS16((16 - p) & 15)];
@@ -317,39 +423,35 @@ fbank_kernel(const Tables* __restrict__ tab, const float* __restrict__ wav, cons
       const int k = hl + 16 * p;
       if (k <= 128) {
         const cplx zk = x[POS16(p & 15)];
-        const cplx xe = mk(0.5 * (zk.x + zm.x), 0.5 * (zk.y - zm.y));
-        const cplx xo = mk(0.5 * (zk.y + zm.y), -0.5 * (zk.x - zm.x));
-        const cplx t = cmul(xo, s.tw512[k]);
-        const double ar = xe.x + t.x, ai = xe.y + t.y, br = xe.x - t.x, bi = xe.y - t.y;
-        power[k] = static_cast<float>(ar * ar + ai * ai);  // TA:616-618 |rfft|^2
-        power[256 - k] = static_cast<float>(br * br + bi * bi);
+        // u = (-sin(theta) / 2, cos(theta)), theta = 2 pi k / 512 = theta_hl + p pi / 16
+        cplx u;
+        if (p == 0) u = mk(-0.5 * sc.x, sc.y);
+        else if (p == 8) u = mk(-0.5 * sc.y, -sc.x);
+        else u = mk(fma(sc.x, -0.5 * cos_p16(p), sc.y * (-0.5 * sin_p16(p))), fma(sc.y, cos_p16(p), -(sc.x * sin_p16(p))));
+        const double nk = fma(zk.x, zk.x, zk.y * zk.y), nm = fma(zm.x, zm.x, zm.y * zm.y);
+        const double e = fma(zk.x, zm.y, zk.y * zm.x);
+        const double sum = nk + nm, c = fma(u.y, e, u.x * (nk - nm));
+        power[k] = static_cast<float>(fma(0.5, sum, c));  // TA:616-618 |rfft|^2
+        power[256 - k] = static_cast<float>(fma(0.5, sum, -c));
       }
     }
     if (hl < 7) power[257 + hl] = 0.f;  // read (x 0) by the padded mel taps
     __syncwarp();
 
     // ---- sparse mel projection + log (TA:621-633); bins hl, hl+16, ..., hl+64.  Every band is a whole number of aligned
-    // four-tap steps (zero weights in the padding); the step count of a group is uniform over the lanes, so all loads of
-    // the frame are issued up front under uniform predicates and the four partial sums of a band are independent.
-#pragma unroll
-    for (int i = 0; i < MEL_GROUPS; ++i) {
-      const float4* pw = reinterpret_cast<const float4*>(power + mel_st[i]);
-      const float4* wv = reinterpret_cast<const float4*>(s.mel_w) + i * MEL_MAXJ * 16 + hl;
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll
-      for (int j = 0; j < MEL_MAXJ; ++j) {
-        if (j < mel_nj[i]) {
-          const float4 w = wv[j * 16];
-          const float4 pv = pw[j];
-          a0 = fmaf(w.x, pv.x, a0);
-          a1 = fmaf(w.y, pv.y, a1);
-          a2 = fmaf(w.z, pv.z, a2);
-          a3 = fmaf(w.w, pv.w, a3);
-        }
-      }
-      const float acc = (a0 + a1) + (a2 + a3);
-      // fast log: |err| < 4e-6 at these magnitudes; the floor itself (silence) maps to the exactly rounded log(eps) of the reference
-      if (active) s.logmel[f][hl + 16 * i] = acc > log_floor ? __logf(acc) : log_of_floor;
+    // four-tap steps (zero weights in the padding); the step count of a group is uniform over the lanes.  The loads of groups
+    // 0-1, 2-3 and 4 are all issued before the first multiply of their batch (the FFT's registers are free by now), so a lane
+    // waits for shared memory three times per frame instead of once per group and step.
+    if (mel_std) {
+      mel_groups<0, 2, true>(power, s.mel_w, mel_st, mel_nj, hl, active, &s.logmel[f][0], log_floor, log_of_floor);
+      mel_groups<2, 4, true>(power, s.mel_w, mel_st, mel_nj, hl, active, &s.logmel[f][0], log_floor, log_of_floor);
+      mel_groups<4, MEL_GROUPS, true>(power, s.mel_w, mel_st, mel_nj, hl, active, &s.logmel[f][0], log_floor, log_of_floor);
+    } else {
+      mel_groups<0, 1, false>(power, s.mel_w, mel_st, mel_nj, hl, active, &s.logmel[f][0], log_floor, log_of_floor);
+      mel_groups<1, 2, false>(power, s.mel_w, mel_st, mel_nj, hl, active, &s.logmel[f][0], log_floor, log_of_floor);
+      mel_groups<2, 3, false>(power, s.mel_w, mel_st, mel_nj, hl, active, &s.logmel[f][0], log_floor, log_of_floor);
+      mel_groups<3, 4, false>(power, s.mel_w, mel_st, mel_nj, hl, active, &s.logmel[f][0], log_floor, log_of_floor);
+      mel_groups<4, 5, false>(power, s.mel_w, mel_st, mel_nj, hl, active, &s.logmel[f][0], log_floor, log_of_floor);
     }
     __syncwarp();
   }
@@ -428,9 +530,10 @@ extern "C" int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float*
   std::memset(t, 0, sizeof(Tables));
   for (int i = 0; i < FRAME_LEN; ++i) t->window[i] = window[i];
   const double two_pi = 6.283185307179586476925286766559;
-  for (int q = 0; q < 16; ++q)
-    for (int l = 0; l < 16; ++l) t->tw256[q][l] = make_double2(cos(two_pi * (q * l) / 256.0), -sin(two_pi * (q * l) / 256.0));
-  for (int k = 0; k <= 128; ++k) t->tw512[k] = make_double2(cos(two_pi * k / 512.0), -sin(two_pi * k / 512.0));
+  for (int l = 0; l < 16; ++l) {
+    t->tw256[l] = make_double2(cos(two_pi * l / 256.0), -sin(two_pi * l / 256.0));
+    t->sc512[l] = make_double2(sin(two_pi * l / 512.0), cos(two_pi * l / 512.0));
+  }
   for (int b = 0; b < NMEL; ++b) {
     const float* row = mel_banks + static_cast<size_t>(b) * NBIN;
     int first = -1, last = -1;
@@ -449,6 +552,9 @@ extern "C" int fa_frontend_tables_build(const fa_frontend_cfg* cfg, const float*
     for (int k = first; first >= 0 && k <= last; ++k)
       t->mel_w[((g * MEL_MAXJ + (k - start) / 4) * 16 + l) * 4 + ((k - start) & 3)] = row[k];
   }
+  t->mel_steps[7] = 1;
+  for (int g = 0; g < MEL_GROUPS; ++g)
+    if (t->mel_steps[g] != mel_cap<true>(g)) t->mel_steps[7] = 0;
   for (int b = 0; b < NMEL; ++b)  // the kernel reads whole steps: they must stay inside the zero-padded power row (264 floats)
     FA_REQUIRE(t->mel_start[b] + 4 * t->mel_steps[b / 16] <= 264, "mel band %d: padded taps run past the spectrum", b);
   return 0;
