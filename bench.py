@@ -40,11 +40,12 @@ ENC_CONF = dict(output_size=512, attention_heads=4, linear_units=2048, num_block
 AD_CONF = dict(downsample_rate=1, encoder_dim=512, llm_dim=1024, ffn_dim=2048, n_layer=2, attention_heads=8)
 GEMM_FLOP_PER_TOKEN = 465_715_200  # SURVEY.md §8d / BASELINE.md §4
 ATTN_FLOP_PER_TOKEN_PER_T = 151_552
-# Frontend, per warp and frame pair, counted on the executed path of the shipped SASS (cuobjdump -sass, the frame loop of
-# fbank_kernel<0>): 1200 warp instructions of which 466 are fp64 (258 DADD + 122 DFMA + 86 DMUL).  A sub-partition
-# issues one warp instruction per clock and its fp64 pipe takes one every two clocks.
-FE_INSTR_PER_FRAME_PAIR = 1200
-FE_FP64_INSTR_PER_FRAME_PAIR = 466
+# Frontend: warp instructions the kernel executes per frame pair of the utterances (ncu "Instructions Executed" of a cfg5 launch,
+# profiles/r02/ncu_source_frontend_r2bi.csv.gz: 255.6 M in all, 105.7 M of them fp64 (DADD / DFMA / DMUL), for 179 640 frame pairs;
+# the tile overlap of one frame in 31 and the per-tile code are included).  A sub-partition issues one warp instruction per clock
+# and its fp64 pipe takes one every two clocks.
+FE_INSTR_PER_FRAME_PAIR = 1423
+FE_FP64_INSTR_PER_FRAME_PAIR = 588
 SM_SUBPARTITIONS = 148 * 4
 
 
