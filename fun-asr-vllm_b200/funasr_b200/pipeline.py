@@ -8,8 +8,10 @@ from __future__ import annotations
 import numpy as np
 import torch
 
+from . import _lib
 from .encoder import AudioTower
 from .frontend import WavFrontend
+from .ingest import PCM_S16
 
 
 class AudioPipeline:
@@ -51,6 +53,31 @@ class AudioPipeline:
             self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
         return self._twin_plans
 
+    def _pcm16_meta(self, starts: np.ndarray, n: np.ndarray) -> int:
+        """Utterance starts (int64) and lengths (int32) of an int16 batch on the device, for ``fa_pcm_to_mono_f32``: one small
+        copy from a pinned buffer kept across calls (an event guards its re-use).  Returns the device address."""
+        B = len(n)
+        if getattr(self, "_meta_pin", None) is None or self._meta_pin.numel() < 3 * B:
+            self._meta_pin = torch.empty(3 * max(B, 64), dtype=torch.int32).pin_memory()
+            self._meta_dev = torch.empty(self._meta_pin.numel(), dtype=torch.int32, device=self.device)
+            self._meta_ev = torch.cuda.Event()
+        else:
+            self._meta_ev.synchronize()  # the previous call's copy has read the buffer
+        h = self._meta_pin.numpy()
+        h[: 2 * B] = np.ascontiguousarray(starts, np.int64).view(np.int32)
+        h[2 * B: 3 * B] = n.astype(np.int32)
+        self._meta_dev[: 3 * B].copy_(self._meta_pin[: 3 * B], non_blocking=True)
+        self._meta_ev.record(torch.cuda.current_stream(self.device))
+        return self._meta_dev.data_ptr()
+
+    def _pcm16_to_f32(self, raw: torch.Tensor, dev: torch.Tensor, meta: int, B: int, b0: int, b1: int, max_len: int):
+        """int16 samples of utterances [b0, b1) in ``raw`` -> f32 / 32768 at the same offsets of ``dev`` (what
+        ``torchaudio.load`` / ``.float()`` hand the reference, /root/reference/infer.py:320-325), on the current stream."""
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.load().fa_pcm_to_mono_f32(raw.data_ptr(), PCM_S16, 1, 1.0 / 32768.0, meta + 8 * b0, meta + 8 * B + 4 * b0,
+                                                      dev.data_ptr(), meta + 8 * b0, b1 - b0, int(max_len),
+                                                      _lib.stream_ptr(self.device)), "fa_pcm_to_mono_f32")
+
     @staticmethod
     def _cut(T: np.ndarray) -> int:
         """Utterance index that halves the cost 0.4657 T + 1.5155e-4 T^2, 0 < cut < B."""
@@ -66,8 +93,16 @@ class AudioPipeline:
         ``overlap`` (default: on for batches of >= 8 utterances and >= 8192 rows): the batch is cut on an utterance boundary
         into two halves of equal cost, each with its own stream and workspace.  The copy engine then moves the second half's
         PCM while the first half computes, and the first half's embeddings go back to the host while the second half
-        finishes; utterances are independent, so the rows are bit-identical to the single-pass schedule."""
+        finishes; utterances are independent, so the rows are bit-identical to the single-pass schedule.
+
+        ``host_pcm`` may be int16 (mono, what a 16 kHz wav file holds; same ``starts``): half the bytes cross PCIe and the
+        conversion to the f32 samples ``torchaudio.load`` would have produced (x / 32768, exact) runs on the GPU."""
         total = host_pcm.numel()
+        pcm16 = host_pcm.dtype == torch.int16
+        if not pcm16 and host_pcm.dtype != torch.float32:
+            raise TypeError(f"host PCM must be float32 or int16, not {host_pcm.dtype}")
+        if pcm16 and (getattr(self, "_dev_raw", None) is None or self._dev_raw.numel() < total):
+            self._dev_raw = torch.empty(total, dtype=torch.int16, device=self.device)
         if self._dev_in is None or self._dev_in.numel() < total:
             self._dev_in = torch.empty(total, dtype=torch.float32, device=self.device)
         dev = self._dev_in[:total]
@@ -76,8 +111,14 @@ class AudioPipeline:
         rows = int(T.sum())
         if overlap is None:
             overlap = len(T) >= 8 and rows >= 8192
+        B = len(T)
+        meta = self._pcm16_meta(starts, n_samples) if pcm16 else 0
         if not overlap or len(T) < 2:
-            dev.copy_(host_pcm, non_blocking=True)
+            if pcm16:
+                self._dev_raw[:total].copy_(host_pcm, non_blocking=True)
+                self._pcm16_to_f32(self._dev_raw, dev, meta, B, 0, B, n_samples.max())
+            else:
+                dev.copy_(host_pcm, non_blocking=True)
             out, cu = self.embed_device(dev, starts, n_samples)
             out_host[: out.shape[0]].copy_(out, non_blocking=True)
             return cu
@@ -94,9 +135,11 @@ class AudioPipeline:
         halves = ((main, slice(0, cut), 0, s_cut, 0, r_cut), (self._aux, slice(cut, len(T)), s_cut, total, r_cut, rows))
         for st, _, s0, s1, _, _ in halves:  # both copies queued first: the DMA engine runs them back to back
             with torch.cuda.stream(st):
-                dev[s0:s1].copy_(host_pcm[s0:s1], non_blocking=True)
+                (self._dev_raw if pcm16 else dev)[s0:s1].copy_(host_pcm[s0:s1], non_blocking=True)
         for k, (st, sl, s0, s1, r0, r1) in enumerate(halves):
             with torch.cuda.stream(st):
+                if pcm16:
+                    self._pcm16_to_f32(self._dev_raw, dev, meta, B, sl.start, sl.stop, n_samples[sl].max())
                 feats, cu_h = self.frontend.forward_packed(dev[s0:s1], starts[sl] - s0, n_samples[sl])
                 plans[k].encode_adapt(feats, 0, np.diff(cu_h), out[r0:r1], 0)
                 out_host[r0:r1].copy_(out[r0:r1], non_blocking=True)

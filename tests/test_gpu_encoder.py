@@ -250,6 +250,42 @@ def test_overlapped_pipeline_is_invisible():
         assert torch.equal(got, want)
 
 
+def test_pipeline_int16_host_pcm_matches_float_host_pcm():
+    """AudioPipeline.run_pinned on int16 host PCM (what a 16 kHz wav file holds): the GPU-side x / 32768 gives the very f32 samples
+    ``torchaudio.load`` hands the reference, so the embeddings are bit-identical to the run on the f32 host buffer, in the
+    single-pass and in the overlapped schedule, call after call (the starts / lengths buffer is re-used)."""
+    import funasr_b200 as fb
+
+    _, _, enc, ad = _pair(2, 1)
+    fe = fb.WavFrontend(fs=16000, window="povey", n_mels=80, frame_length=25, frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0,
+                        cmvn=None, device="cuda")
+    g = torch.Generator().manual_seed(11)
+    n = np.array([16000, 48000, 8000, 24007, 33333, 400, 64000, 16001], np.int64)
+    starts = np.zeros(len(n), np.int64)
+    starts[1:] = np.cumsum((n[:-1] + 7) // 8 * 8)  # 16-byte aligned for both sample types
+    total = int(starts[-1] + (n[-1] + 7) // 8 * 8)
+    raw = torch.zeros(total, dtype=torch.int16).pin_memory()
+    for s0, k in zip(starts, n):
+        raw[s0:s0 + k] = torch.randint(-32768, 32768, (int(k),), generator=g).to(torch.int16)
+    raw[int(starts[1])] = -32768
+    raw[int(starts[1]) + 1] = 32767
+    host = (raw.float() / 32768.0).pin_memory()  # the reference's conversion (torchaudio.load normalisation), exact in f32
+    pipe = fb.AudioPipeline(fe, fb.AudioTower(enc, ad), "cuda")
+    _, T = fe.lengths(n)
+    rows = int(T.sum())
+    want = torch.empty((rows, 1024), dtype=torch.bfloat16).pin_memory()
+    cu0 = pipe.run_pinned(host, starts, n, want, overlap=False)
+    torch.cuda.synchronize()
+    for overlap in (False, True, True, False):
+        got = torch.zeros((rows, 1024), dtype=torch.bfloat16).pin_memory()
+        cu1 = pipe.run_pinned(raw, starts, n, got, overlap=overlap)
+        torch.cuda.synchronize()
+        assert np.array_equal(cu0, cu1)
+        assert torch.equal(got, want), f"overlap={overlap}"
+    with pytest.raises(TypeError):
+        pipe.run_pinned(host.double(), starts, n, want)
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
 def test_two_devices_in_one_process():
     """kernel attributes (dynamic shared memory opt-in) and the SM count are per DEVICE; one process that drives two
