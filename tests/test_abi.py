@@ -74,15 +74,26 @@ def test_tables_blob_is_sparse_mel(frontend_golden):
     _lib.check(lib.fa_frontend_tables_build(C.byref(cfg), win.ctypes.data, mel.ctypes.data, blob.ctypes.data))
     f = blob.view(np.float32)
     np.testing.assert_array_equal(f[:400], win)
-    # fp64 twiddles: tw256[q][t] = W256^(t q) (16 x 16 double2), then W512^k for k = 0..128
-    d = blob[1600:1600 + 16 * 16 * 16 + 129 * 16].view(np.float64)
-    tw256 = d[:512].reshape(16, 16, 2)
-    ang = 2 * np.pi * np.outer(np.arange(16), np.arange(16)) / 256
-    np.testing.assert_allclose(tw256[..., 0], np.cos(ang), atol=1e-15)
-    np.testing.assert_allclose(tw256[..., 1], -np.sin(ang), atol=1e-15)
-    tw512 = d[512:].reshape(129, 2)
-    np.testing.assert_allclose(tw512[:, 0], np.cos(2 * np.pi * np.arange(129) / 512), atol=1e-15)
-    np.testing.assert_allclose(tw512[:, 1], -np.sin(2 * np.pi * np.arange(129) / 512), atol=1e-15)
+    # fp64 constants the lanes build their twiddles from: tw256[t] = W256^t = (cos, -sin)(2 pi t / 256), then
+    # sc512[t] = (sin, cos)(2 pi t / 512), t = 0..15
+    d = blob[1600:1600 + 2 * 16 * 16].view(np.float64).reshape(2, 16, 2)
+    t = np.arange(16)
+    np.testing.assert_allclose(d[0, :, 0], np.cos(2 * np.pi * t / 256), atol=1e-15)
+    np.testing.assert_allclose(d[0, :, 1], -np.sin(2 * np.pi * t / 256), atol=1e-15)
+    np.testing.assert_allclose(d[1, :, 0], np.sin(2 * np.pi * t / 512), atol=1e-15)
+    np.testing.assert_allclose(d[1, :, 1], np.cos(2 * np.pi * t / 512), atol=1e-15)
+    # sparse mel: first bin of each band (a multiple of four), four-tap steps per group of 16 bands, weights [group][step][lane][4]
+    i32 = blob[2112:2112 + 88 * 4].view(np.int32)
+    start, steps = i32[:80], i32[80:88]
+    assert steps[:5].tolist() == [2, 2, 3, 3, 5] and steps[7] == 1  # the standard bank: exactly the batched path's step counts
+    w = blob[2464:2464 + 5 * 5 * 16 * 4 * 4].view(np.float32).reshape(5, 5, 16, 4)
+    dense = np.zeros((80, 257 + 24), np.float32)
+    for b_ in range(80):
+        assert start[b_] % 4 == 0
+        for j in range(5):
+            dense[b_, start[b_] + 4 * j:start[b_] + 4 * j + 4] += w[b_ // 16, j, b_ % 16]
+    np.testing.assert_array_equal(dense[:, :257], mel)
+    assert not dense[:, 257:].any()
     bad = _lib.FrontendCfg(16000, 320, 160, 512, 80, 7, 6, 0.97, 32768.0, FLT_EPS)
     assert lib.fa_frontend_tables_build(C.byref(bad), win.ctypes.data, mel.ctypes.data, blob.ctypes.data) != 0
     assert b"not the compiled one" in lib.fa_last_error()
