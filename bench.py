@@ -344,7 +344,8 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
             pipe.embed_device(inp.dev_pcm, inp.starts, inp.lengths, out=inp.out_dev)
 
         def step_e2e():
-            pipe.run_pinned(inp.host_pcm, inp.starts, inp.lengths, inp.out_host, overlap=False if args.no_overlap else None)
+            pipe.run_pinned(inp.host_pcm, inp.starts, inp.lengths, inp.out_host, overlap=False if args.no_overlap else None,
+                            pieces=args.e2e_pieces)
 
         return step_device, step_e2e
 
@@ -415,7 +416,8 @@ def run_b200(args, rank: int, local_rank: int, world: int) -> None:
     host_pcm16 = (main_in.host_pcm * 32767.0).round().to(torch.int16).pin_memory()
 
     def step_e2e16():
-        pipe.run_pinned(host_pcm16, main_in.starts, main_in.lengths, main_in.out_host, overlap=False if args.no_overlap else None)
+        pipe.run_pinned(host_pcm16, main_in.starts, main_in.lengths, main_in.out_host, overlap=False if args.no_overlap else None,
+                        pieces=args.e2e_pieces)
 
     for _ in range(2):
         step_e2e16()
@@ -664,6 +666,7 @@ def main():
     ap.add_argument("--workload", default="cfg5", choices=["cfg5", "cfg2", "cfg3"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the workloads / e2e_dropin / gpu_eager / strong sections")
+    ap.add_argument("--e2e-pieces", type=int, default=2, help="e2e leg: pieces of the overlapped schedule (two streams)")
     ap.add_argument("--no-overlap", action="store_true", help="e2e leg: one pass instead of the two-half overlapped schedule")
     ap.add_argument("--graph-rows", type=int, default=None, help="batches up to this many rows replay a CUDA graph (0 = off)")
     ap.add_argument("--streams", type=int, default=None, help="1 = single stream, 2 = dual-stream half-batch schedule")

@@ -39,18 +39,20 @@ class AudioPipeline:
         out, _ = self.tower.forward_packed(feats, np.diff(cu), out=out)
         return out, cu
 
-    def _twins(self, n0: int, n1: int):
-        """Two plans (own workspaces, the tower's weights) + auxiliary stream for the overlapped schedule.  Each runs its half
-        on ONE stream: the two halves already are the two streams (measured: letting each half split again doubles the
+    def _twins(self, sizes):
+        """One plan per piece (own workspaces, the tower's weights) + auxiliary streams for the overlapped schedule.  Each piece
+        runs on ONE stream: the pieces already are the streams (measured: letting each half split again doubles the
         launches and loses 5 ms at cfg5, 5 ms at cfg3)."""
         plan = self.tower.plan()
-        if getattr(self, "_twin_of", None) is not plan:
-            self._twin_plans = (plan.twin(max(n0, 128)), plan.twin(max(n1, 128)))
+        if getattr(self, "_twin_of", None) is not plan or len(self._twin_plans) != len(sizes):
+            self._twin_plans = tuple(plan.twin(max(int(n), 128)) for n in sizes)
             for t in self._twin_plans:
                 t.set_streams(1)
             self._twin_of = plan
             self._aux = torch.cuda.Stream(self.device)
+            self._d2h = torch.cuda.Stream(self.device)
             self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
+            self._ev_done = [torch.cuda.Event() for _ in sizes]
         return self._twin_plans
 
     def _pcm16_meta(self, starts: np.ndarray, n: np.ndarray) -> int:
@@ -84,9 +86,24 @@ class AudioPipeline:
         c = np.cumsum(0.4657152 * T + 1.51552e-4 * T.astype(np.float64) ** 2)
         return int(min(max(np.searchsorted(c, 0.5 * c[-1]) + 1, 1), len(T) - 1))
 
+    @staticmethod
+    def _cuts(T: np.ndarray, pieces: int) -> list[int]:
+        """Utterance boundaries 0 = c_0 < c_1 < ... < c_k = B of k <= pieces contiguous pieces of equal cost."""
+        if pieces == 2:
+            return [0, AudioPipeline._cut(T), len(T)]
+        c = np.cumsum(0.4657152 * T + 1.51552e-4 * T.astype(np.float64) ** 2)
+        cuts = [0]
+        for i in range(1, pieces):
+            b = int(min(max(np.searchsorted(c, i * c[-1] / pieces) + 1, cuts[-1] + 1), len(T) - 1))
+            if b > cuts[-1]:
+                cuts.append(b)
+        if cuts[-1] != len(T):
+            cuts.append(len(T))
+        return cuts
+
     @torch.no_grad()
     def run_pinned(self, host_pcm: torch.Tensor, starts: np.ndarray, n_samples: np.ndarray, out_host: torch.Tensor,
-                   overlap: bool | None = None):
+                   overlap: bool | None = None, pieces: int = 2):
         """Pinned packed PCM on the host -> pinned bf16 ``[sum T, llm_dim]`` on the host: H2D, the whole path, D2H, all
         enqueued on (or joined back into) the current stream (no sync here; the caller synchronises once).
 
@@ -94,6 +111,10 @@ class AudioPipeline:
         into two halves of equal cost, each with its own stream and workspace.  The copy engine then moves the second half's
         PCM while the first half computes, and the first half's embeddings go back to the host while the second half
         finishes; utterances are independent, so the rows are bit-identical to the single-pass schedule.
+
+        ``pieces`` > 2 cuts the batch further (alternating between the two streams, copies back on a third): measured slower
+        at cfg5 (45.7-46.5 ms with 2, 50.1 / 48.6 / 51.6 ms with 3 / 4 / 6: profiles/r02/e2e_pieces_r2bm.md), the smaller GEMMs
+        cost more than the shorter first copy in and last copy out save; kept for batches far above an hour.
 
         ``host_pcm`` may be int16 (mono, what a 16 kHz wav file holds; same ``starts``): half the bytes cross PCIe and the
         conversion to the f32 samples ``torchaudio.load`` would have produced (x / 32768, exact) runs on the GPU."""
@@ -122,9 +143,10 @@ class AudioPipeline:
             out, cu = self.embed_device(dev, starts, n_samples)
             out_host[: out.shape[0]].copy_(out, non_blocking=True)
             return cu
-        cut = self._cut(T)
-        r_cut, s_cut = int(T[:cut].sum()), int(starts[cut])
-        plans = self._twins(r_cut, rows - r_cut)
+        cuts = self._cuts(T, max(2, int(pieces)))
+        rcum = np.concatenate([[0], np.cumsum(T)]).astype(np.int64)
+        scut = [int(starts[c]) if c < len(T) else total for c in cuts]
+        plans = self._twins([rcum[c1] - rcum[c0] for c0, c1 in zip(cuts[:-1], cuts[1:])])
         main = torch.cuda.current_stream(self.device)
         dim = self.tower.adaptor.llm_dim
         if getattr(self, "_dev_out", None) is None or self._dev_out.shape[0] < rows or self._dev_out.shape[1] != dim:
@@ -132,19 +154,33 @@ class AudioPipeline:
         out = self._dev_out[:rows]
         self._ev_fork.record(main)
         self._aux.wait_event(self._ev_fork)
-        halves = ((main, slice(0, cut), 0, s_cut, 0, r_cut), (self._aux, slice(cut, len(T)), s_cut, total, r_cut, rows))
-        for st, _, s0, s1, _, _ in halves:  # both copies queued first: the DMA engine runs them back to back
+        self._d2h.wait_event(self._ev_fork)
+        # piece k on stream k % 2; (stream, utterances, first sample, end sample, first row, end row)
+        parts = [((main, self._aux)[k % 2], slice(c0, c1), scut[k], scut[k + 1], int(rcum[c0]), int(rcum[c1]))
+                 for k, (c0, c1) in enumerate(zip(cuts[:-1], cuts[1:]))]
+        for st, _, s0, s1, _, _ in parts:  # all copies queued first: the DMA engine runs them back to back
             with torch.cuda.stream(st):
                 (self._dev_raw if pcm16 else dev)[s0:s1].copy_(host_pcm[s0:s1], non_blocking=True)
-        for k, (st, sl, s0, s1, r0, r1) in enumerate(halves):
+        two = len(parts) == 2
+        for k, (st, sl, s0, s1, r0, r1) in enumerate(parts):
             with torch.cuda.stream(st):
                 if pcm16:
                     self._pcm16_to_f32(self._dev_raw, dev, meta, B, sl.start, sl.stop, n_samples[sl].max())
                 feats, cu_h = self.frontend.forward_packed(dev[s0:s1], starts[sl] - s0, n_samples[sl])
                 plans[k].encode_adapt(feats, 0, np.diff(cu_h), out[r0:r1], 0)
-                out_host[r0:r1].copy_(out[r0:r1], non_blocking=True)
+                if two:  # each stream's only piece: its copy back follows it on the same stream
+                    out_host[r0:r1].copy_(out[r0:r1], non_blocking=True)
+                else:  # a later piece follows on this stream: the copy back goes to a stream of its own
+                    self._ev_done[k].record(st)
+            if not two:
+                self._d2h.wait_event(self._ev_done[k])
+                with torch.cuda.stream(self._d2h):
+                    out_host[r0:r1].copy_(out[r0:r1], non_blocking=True)
         self._ev_join.record(self._aux)
         main.wait_event(self._ev_join)
+        if not two:
+            self._ev_join.record(self._d2h)
+            main.wait_event(self._ev_join)
         cu = np.zeros(len(T) + 1, np.int32)
         cu[1:] = np.cumsum(T)
         return cu

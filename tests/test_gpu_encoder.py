@@ -248,6 +248,12 @@ def test_overlapped_pipeline_is_invisible():
         torch.cuda.synchronize()
         assert np.array_equal(cu0, cu1)
         assert torch.equal(got, want)
+    for pieces in (3, 4, 64):  # more pieces than two: alternating streams, copies back on a stream of their own
+        got = torch.zeros((rows, 1024), dtype=torch.bfloat16).pin_memory()
+        cu1 = pipe.run_pinned(host, starts, n, got, overlap=True, pieces=pieces)
+        torch.cuda.synchronize()
+        assert np.array_equal(cu0, cu1)
+        assert torch.equal(got, want), f"pieces={pieces}"
 
 
 def test_pipeline_int16_host_pcm_matches_float_host_pcm():
