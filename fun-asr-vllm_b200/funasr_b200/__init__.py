@@ -13,12 +13,12 @@ from .encoder import AudioTower, SenseVoiceEncoderSmall, Transformer
 from .batched import audio_embeddings, inference_batched
 from .ingest import Resample, pack_pcm, pcm_to_mono
 from .frontend import WavFrontend, extract_fbank, fake_token_len, load_cmvn, pack_waveforms
-from .pipeline import AudioPipeline
+from .pipeline import AudioPipeline, StreamingPipeline
 from .registry import install, patch, tables
 from .sharding import gather_results, shard_contiguous, shard_lpt
 from .splice import splice_embeds
 from .vllm_route import install_vllm_route, patch_vllm_model
 
-__all__ = ["AudioPipeline", "AudioTower", "audio_embeddings", "inference_batched", "FunASRB200Error", "LIB_PATH", "Resample", "pack_pcm", "pcm_to_mono", "SenseVoiceEncoderSmall", "Transformer",
+__all__ = ["AudioPipeline", "StreamingPipeline", "AudioTower", "audio_embeddings", "inference_batched", "FunASRB200Error", "LIB_PATH", "Resample", "pack_pcm", "pcm_to_mono", "SenseVoiceEncoderSmall", "Transformer",
            "WavFrontend", "extract_fbank", "fake_token_len", "gather_results", "install", "load_cmvn", "pack_waveforms",
            "install_vllm_route", "patch", "patch_vllm_model", "shard_contiguous", "shard_lpt", "splice_embeds", "tables"]

@@ -207,3 +207,39 @@ class AudioPipeline:
         res.copy_(out, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return [res[cu[b]:cu[b + 1]] for b in range(len(wavs))], np.diff(cu)
+
+
+class StreamingPipeline:
+    """A serving loop over ``AudioPipeline.run_pinned``: ``lanes`` pipelines (own streams, workspaces and device buffers, the
+    tower's weights shared) take the submitted batches in turn, so that the copy in of batch n + 1 and the copy back of batch
+    n - 1 run under the compute of batch n; every batch still makes its own H2D and D2H.  Results are bit-identical to
+    ``run_pinned`` (utterances and batches are independent).
+
+        sp = StreamingPipeline(frontend, tower, "cuda:0")
+        for host_pcm, starts, n, out_host in batches:      # pinned buffers; a buffer pair may be re-used after its ticket is done
+            ticket = sp.submit(host_pcm, starts, n, out_host)
+        sp.drain()                                          # or ticket.synchronize() per batch
+    """
+
+    def __init__(self, frontend: WavFrontend, tower: AudioTower, device=None, lanes: int = 2):
+        self.pipes = [AudioPipeline(frontend, tower, device) for _ in range(max(1, int(lanes)))]
+        self.device = self.pipes[0].device
+        self.streams = [torch.cuda.Stream(self.device) for _ in self.pipes]
+        self._n = 0
+
+    @torch.no_grad()
+    def submit(self, host_pcm: torch.Tensor, starts, n_samples, out_host: torch.Tensor, **kw) -> torch.cuda.Event:
+        """Enqueue one batch (arguments of ``AudioPipeline.run_pinned``); returns the event that marks ``out_host`` complete."""
+        k = self._n % len(self.pipes)
+        self._n += 1
+        st = self.streams[k]
+        st.wait_stream(torch.cuda.current_stream(self.device))  # whatever produced the inputs on the caller's stream
+        with torch.cuda.stream(st):
+            self.pipes[k].run_pinned(host_pcm, starts, n_samples, out_host, **kw)
+            ev = torch.cuda.Event()
+            ev.record(st)
+        return ev
+
+    def drain(self) -> None:
+        for st in self.streams:
+            st.synchronize()

@@ -292,6 +292,48 @@ def test_pipeline_int16_host_pcm_matches_float_host_pcm():
         pipe.run_pinned(host.double(), starts, n, want)
 
 
+def test_streaming_pipeline_matches_single_batches():
+    """StreamingPipeline: batches submitted back to back on two lanes (copies of one batch under the compute of another) give the
+    rows of AudioPipeline.run_pinned on each batch alone, f32 and int16 host PCM, whatever the lane."""
+    import funasr_b200 as fb
+
+    _, _, enc, ad = _pair(2, 1)
+    fe = fb.WavFrontend(fs=16000, window="povey", n_mels=80, frame_length=25, frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0,
+                        cmvn=None, device="cuda")
+    tower = fb.AudioTower(enc, ad)
+    g = torch.Generator().manual_seed(21)
+    batches = []
+    for n in ([16000, 48000, 8000, 24007, 33333, 400, 64000, 16001], [160000, 9000, 31999], [4000] * 9):
+        n = np.array(n, np.int64)
+        starts = np.zeros(len(n), np.int64)
+        starts[1:] = np.cumsum((n[:-1] + 7) // 8 * 8)
+        total = int(starts[-1] + (n[-1] + 7) // 8 * 8)
+        raw = torch.zeros(total, dtype=torch.int16).pin_memory()
+        for s0, k in zip(starts, n):
+            raw[s0:s0 + k] = torch.randint(-20000, 20000, (int(k),), generator=g).to(torch.int16)
+        batches.append((raw, (raw.float() / 32768.0).pin_memory(), starts, n))
+    single = fb.AudioPipeline(fe, tower, "cuda")
+    want = []
+    for raw, host, starts, n in batches:
+        rows = int(fe.lengths(n)[1].sum())
+        w = torch.empty((rows, 1024), dtype=torch.bfloat16).pin_memory()
+        single.run_pinned(host, starts, n, w, overlap=False)
+        torch.cuda.synchronize()
+        want.append(w.clone())
+    sp = fb.StreamingPipeline(fe, tower, "cuda")
+    jobs = []
+    for rep in range(3):
+        for b, (raw, host, starts, n) in enumerate(batches):
+            got = torch.zeros_like(want[b]).pin_memory()
+            src = raw if (rep + b) % 2 else host
+            ev = sp.submit(src, starts, n, got, overlap=bool(rep % 2) if len(n) >= 2 else False)
+            jobs.append((b, got, ev))
+    for b, got, ev in jobs:
+        ev.synchronize()
+        assert torch.equal(got, want[b]), f"batch {b}"
+    sp.drain()
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
 def test_two_devices_in_one_process():
     """kernel attributes (dynamic shared memory opt-in) and the SM count are per DEVICE; one process that drives two
