@@ -573,6 +573,29 @@ def extra_workloads(args, fb, pipe, fe, dev, measure, profile, gemm_roofline, ti
                      "gemm_tflops_share_of_timed_step": share, "gemm_frac_share_of_timed_step": share / peak_tf,
                      "whole_step_tflops": (gemm_flop + attn_flop) / (d * 1e-3) / 1e12,
                      "kernel_ms_launch_by_launch": {k: round(ms, 4) for k, (ms, n) in prof.items()}}
+        # a serving loop over batches of this size (StreamingPipeline: batches back to back on 2 / 4 lanes, every batch with its own
+        # H2D and D2H, no L2 flush between them): what concurrency gives back where one batch alone cannot fill the GPU
+        for lanes in (2, 4):
+            sp = fb.StreamingPipeline(fe, pipe.tower, dev, lanes=lanes)
+            outs = [torch.empty_like(inp.out_host).pin_memory() for _ in range(lanes)]
+
+            def run(k):
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for i in range(k):
+                    sp.submit(inp.host_pcm, inp.starts, inp.lengths, outs[i % lanes])
+                for st in sp.streams:
+                    torch.cuda.current_stream().wait_stream(st)
+                b.record()
+                torch.cuda.synchronize()
+                return a.elapsed_time(b) / k
+
+            run(2 * lanes)
+            ms = run(40)
+            out[name][f"e2e_streaming_{lanes}_lanes_ms"] = ms
+            out[name][f"e2e_streaming_{lanes}_lanes_audio_s_per_s"] = inp.audio_s / (ms * 1e-3)
+            del sp, outs
     # cfg1: fbank + LFR + CMVN on one 10 s waveform, batch 1 (launch/latency bound: 1 MB of traffic)
     inp = Inputs(workload_lengths("cfg1"), 3000, dev, AD_CONF["llm_dim"])
     for _ in range(5):

@@ -15,10 +15,19 @@ from .ingest import PCM_S16
 
 
 class AudioPipeline:
-    def __init__(self, frontend: WavFrontend, tower: AudioTower, device=None):
+    def __init__(self, frontend: WavFrontend, tower: AudioTower, device=None, private_plan: bool = False):
+        """``private_plan``: run the single-pass schedule on a plan of this pipeline's own (own workspace, the tower's weights)
+        instead of the tower's: needed when several pipelines over one tower have work in flight at once (StreamingPipeline)."""
         self.frontend, self.tower = frontend, tower
         self.device = torch.device(device) if device is not None else tower.encoder._device()
         self._pin_in = self._pin_out = self._dev_in = None
+        self._private, self._own, self._own_of = bool(private_plan), None, None
+
+    def _own_plan(self):
+        plan = self.tower.plan()
+        if self._own_of is not plan:
+            self._own, self._own_of = plan.twin(), plan
+        return self._own
 
     def _staging(self, n_in: int, n_out_rows: int, dim: int):
         if self._pin_in is None or self._pin_in.numel() < n_in:
@@ -36,7 +45,12 @@ class AudioPipeline:
     def embed_device(self, wav_dev: torch.Tensor, starts: np.ndarray, n_samples: np.ndarray, out: torch.Tensor | None = None):
         """Device-resident whole path: packed PCM on the GPU -> packed bf16 ``[sum T, llm_dim]`` on the GPU."""
         feats, cu = self.frontend.forward_packed(wav_dev, starts, n_samples)
-        out, _ = self.tower.forward_packed(feats, np.diff(cu), out=out)
+        if self._private:
+            if out is None:
+                out = torch.empty((int(cu[-1]), self.tower.adaptor.llm_dim), dtype=torch.bfloat16, device=feats.device)
+            self._own_plan().encode_adapt(feats, 0, np.diff(cu), out, 0)
+        else:
+            out, _ = self.tower.forward_packed(feats, np.diff(cu), out=out)
         return out, cu
 
     def _twins(self, sizes):
@@ -222,7 +236,7 @@ class StreamingPipeline:
     """
 
     def __init__(self, frontend: WavFrontend, tower: AudioTower, device=None, lanes: int = 2):
-        self.pipes = [AudioPipeline(frontend, tower, device) for _ in range(max(1, int(lanes)))]
+        self.pipes = [AudioPipeline(frontend, tower, device, private_plan=True) for _ in range(max(1, int(lanes)))]
         self.device = self.pipes[0].device
         self.streams = [torch.cuda.Stream(self.device) for _ in self.pipes]
         self._n = 0

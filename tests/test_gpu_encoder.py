@@ -321,6 +321,8 @@ def test_streaming_pipeline_matches_single_batches():
         torch.cuda.synchronize()
         want.append(w.clone())
     sp = fb.StreamingPipeline(fe, tower, "cuda")
+    own = [p._own_plan() for p in sp.pipes]  # no workspace is shared between lanes, nor with the tower's own plan
+    assert own[0] is not own[1] and tower.plan() not in own
     jobs = []
     for rep in range(3):
         for b, (raw, host, starts, n) in enumerate(batches):
