@@ -1,8 +1,8 @@
 #!/bin/bash
-# r02-bo: final state of round 2: full GPU suite, smoke, default bench, reference arm, ncu launch list of one cfg5 step.
+# r02-bo / bs: final state of round 2: full GPU suite, smoke, default bench, reference arm, ncu launch list of one cfg5 step.
 # Usage: gpurun --timeout 1000 -- 'bash profiles/scripts/campaign_r2bo.sh'
 set -u
-O=gpurun_out/r2bo
+O=gpurun_out/${RUN:-r2bo}
 mkdir -p $O
 timeout 600 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest exit $?"; tail -3 $O/pytest_gpu.log
 timeout 240 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > $O/smoke.log 2>&1; echo "smoke exit $?"; tail -2 $O/smoke.log
