@@ -95,3 +95,26 @@ def test_bind_to_gpu_numa_is_best_effort():
     got = bind_to_gpu_numa(0)
     after = os.sched_getaffinity(0)
     assert got is None and after == before or set(got) == after and after <= before
+
+
+def test_pipeline_piece_boundaries():
+    """Host logic of AudioPipeline.run_pinned's overlapped schedule: contiguous pieces of near-equal cost, every piece non-empty,
+    boundaries strictly increasing from 0 to B, never more pieces than asked for (or than utterances)."""
+    import numpy as np
+
+    from funasr_b200.pipeline import AudioPipeline as P
+
+    cost = lambda T: 0.4657152 * T + 1.51552e-4 * T.astype(np.float64) ** 2
+    rng = np.random.default_rng(5)
+    for B in (2, 3, 10, 64, 360):
+        for T in (np.full(B, 167), rng.integers(1, 500, B)):
+            for pieces in (2, 3, 4, 8, 1000):
+                cuts = P._cuts(T, pieces)
+                assert cuts[0] == 0 and cuts[-1] == B and all(a < b for a, b in zip(cuts[:-1], cuts[1:]))
+                assert len(cuts) - 1 <= min(pieces, B)
+                if B >= 8 * pieces:  # enough utterances: every piece within one utterance's cost (each side) of the equal share
+                    c = cost(T)
+                    share, worst = c.sum() / pieces, c.max()
+                    for a, b in zip(cuts[:-1], cuts[1:]):
+                        assert abs(c[a:b].sum() - share) <= 2 * worst + 1e-9
+    assert P._cuts(np.full(360, 167), 2) == [0, P._cut(np.full(360, 167)), 360]
