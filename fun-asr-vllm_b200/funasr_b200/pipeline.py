@@ -235,7 +235,8 @@ class StreamingPipeline:
         sp.drain()                                          # or ticket.synchronize() per batch
     """
 
-    def __init__(self, frontend: WavFrontend, tower: AudioTower, device=None, lanes: int = 2):
+    def __init__(self, frontend: WavFrontend, tower: AudioTower, device=None, lanes: int = 2, overlap: bool | None = None):
+        self.overlap = overlap  # run_pinned's schedule inside a lane (None: its default, two halves from 8192 rows on)
         self.pipes = [AudioPipeline(frontend, tower, device, private_plan=True) for _ in range(max(1, int(lanes)))]
         self.device = self.pipes[0].device
         self.streams = [torch.cuda.Stream(self.device) for _ in self.pipes]
@@ -244,6 +245,7 @@ class StreamingPipeline:
     @torch.no_grad()
     def submit(self, host_pcm: torch.Tensor, starts, n_samples, out_host: torch.Tensor, **kw) -> torch.cuda.Event:
         """Enqueue one batch (arguments of ``AudioPipeline.run_pinned``); returns the event that marks ``out_host`` complete."""
+        kw.setdefault("overlap", self.overlap)
         k = self._n % len(self.pipes)
         self._n += 1
         st = self.streams[k]
