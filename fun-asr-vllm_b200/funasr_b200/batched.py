@@ -16,7 +16,6 @@ import torch
 
 from .encoder import AudioTower
 from .frontend import WavFrontend, fake_token_len, pack_waveforms
-from .pipeline import AudioPipeline
 
 
 def _as_waveform(x, loader: Callable | None):
@@ -37,21 +36,53 @@ def _as_waveform(x, loader: Callable | None):
     return x
 
 
+class KnownFeatures:
+    """Frontend stand-in for ONE utterance whose features the batched pass has already computed.  ``model.inference`` still
+    calls ``extract_fbank(data_src, frontend=frontend)`` for every utterance (``/root/reference/model.py:372``: it needs the
+    length for ``fake_token_len``); handed this object instead of the real frontend, that call gets the known ``[1, T, 560]``
+    features back (funasr's ``extract_fbank`` calls ``frontend(data, data_len)``; this package's looks ``known`` up first)
+    instead of running the fbank kernel a second time.  Anything else (another waveform, attribute reads such as ``fs``,
+    ``frame_shift``, ``lfr_n``: ``model.py:379-384``) goes to the real frontend."""
+
+    def __init__(self, real: WavFrontend, n_samples: int, feats: torch.Tensor, lens: torch.Tensor):
+        self._real, self._n, self._feats, self._lens = real, int(n_samples), feats, lens
+
+    def __getattr__(self, name):
+        return getattr(self._real, name)
+
+    def known(self, n_samples: int):
+        return (self._feats, self._lens) if int(n_samples) == self._n else None
+
+    def forward(self, input, input_lengths=None, **kwargs):
+        x = input if torch.is_tensor(input) else torch.as_tensor(input)
+        if input_lengths is None:
+            lens = [int(x.shape[-1])]
+        else:
+            lens = [int(v) for v in (input_lengths.tolist() if torch.is_tensor(input_lengths) else input_lengths)]
+        if (x.dim() == 1 or x.shape[0] == 1) and len(lens) == 1 and lens[0] == self._n:
+            return self._feats, self._lens
+        return self._real(input, input_lengths, **kwargs)
+
+    __call__ = forward
+
+
 @torch.no_grad()
-def audio_embeddings(wavs: Sequence[torch.Tensor], frontend: WavFrontend, tower: AudioTower, out_dtype=torch.bfloat16):
+def audio_embeddings(wavs: Sequence[torch.Tensor], frontend: WavFrontend, tower: AudioTower, out_dtype=torch.bfloat16,
+                     return_features: bool = False):
     """One packed pass over a list of 1-D waveforms.  Returns (list of ``[T_b, llm_dim]`` GPU tensors - views of one packed
     buffer -, ``T`` int64 array of rows per utterance, ``fake`` int64 array: the rows ``model.py:391-396`` will take when
-    ``use_low_frame_rate`` is set)."""
+    ``use_low_frame_rate`` is set) and, with ``return_features``, the list of ``[T_b, 560]`` f32 feature views as a fourth item."""
     dev = tower.encoder._device()
     pcm, starts = pack_waveforms(list(wavs), dev)
     n = np.asarray([int(w.numel()) for w in wavs], np.int64)
-    pipe = AudioPipeline(frontend, tower, dev)
-    out, cu = pipe.embed_device(pcm, starts, n)
+    feats, cu = frontend.forward_packed(pcm, starts, n)
+    out, _ = tower.forward_packed(feats, np.diff(cu))
     if out.dtype != out_dtype:
         out = out.to(out_dtype)
     T = np.diff(cu).astype(np.int64)
     fake = np.asarray([fake_token_len(int(t), True) for t in T], np.int64)
-    return [out[cu[b]:cu[b + 1]] for b in range(len(T))], T, fake
+    res = ([out[cu[b]:cu[b + 1]] for b in range(len(T))], T, fake)
+    return res + ([feats[cu[b]:cu[b + 1]] for b in range(len(T))],) if return_features else res
 
 
 @torch.no_grad()
@@ -70,14 +101,16 @@ def inference_batched(model, data_in: Sequence, *, frontend: WavFrontend, tower:
         raise ValueError("model has no CUDA audio tower: call funasr_b200.patch(model, kwargs) first or pass tower=")
     kwargs.pop("batch_size", None)
     wavs = [_as_waveform(x, loader) for x in data_in]
-    embeds, T, _ = audio_embeddings(wavs, frontend, tower)
+    embeds, T, _, feats = audio_embeddings(wavs, frontend, tower, return_features=True)
     results = []
     for b, (w, e) in enumerate(zip(wavs, embeds)):
+        # the model's own extract_fbank call (model.py:372) gets this utterance's features back instead of recomputing them
+        fe_b = KnownFeatures(frontend, int(w.numel()), feats[b].unsqueeze(0), torch.tensor([int(T[b])], dtype=torch.int64))
         emb = e.unsqueeze(0)  # [1, T_b, llm_dim], what model.audio_adaptor would have returned for this utterance
         if embed_dtype is not None:
             emb = emb.to(embed_dtype)
         lens = torch.tensor([int(T[b])], dtype=torch.int32, device=emb.device)
         k = {"key": [key[b]]} if key is not None else {}
-        results.append(model.inference(data_in=[w], frontend=frontend, audio_embedding=emb, audio_embedding_lens=lens,
+        results.append(model.inference(data_in=[w], frontend=fe_b, audio_embedding=emb, audio_embedding_lens=lens,
                                        **k, **kwargs))
     return results

@@ -45,6 +45,32 @@ def test_argument_errors():
     assert batched._as_waveform("x", lambda p: torch.ones(7)).shape == (7,)
 
 
+def test_known_features_stand_in():
+    """batched.KnownFeatures: the utterance it was built for gets its features back from funasr's call form
+    (`frontend(data, data_len)`) and from this package's extract_fbank; anything else reaches the real frontend."""
+    import funasr_b200 as fb
+    from funasr_b200.batched import KnownFeatures
+
+    class Real:
+        fs, frame_shift, lfr_n = 16000, 10, 6
+        calls = 0
+
+        def __call__(self, x, lens=None, **kw):
+            Real.calls += 1
+            return "real", lens
+
+    feats, lens = torch.arange(2 * 560, dtype=torch.float32).reshape(1, 2, 560), torch.tensor([2])
+    kf = KnownFeatures(Real(), 1000, feats, lens)
+    assert kf.fs == 16000 and kf.lfr_n == 6
+    for x, l in ((torch.zeros(1, 1000), torch.tensor([1000])), (torch.zeros(1000), None), (np.zeros((1, 1000), np.float32), [1000])):
+        f, n = kf(x, l)
+        assert f is feats and n is lens
+    assert kf(torch.zeros(1, 999), [999])[0] == "real" and kf(torch.zeros(2, 1000), [1000, 1000])[0] == "real" and Real.calls == 2
+    f, n = fb.extract_fbank([torch.zeros(1000)], frontend=kf, is_final=True)
+    assert torch.equal(f, feats) and n.dtype == torch.int32 and n.tolist() == [2]
+    assert kf.known(1001) is None
+
+
 @pytest.mark.gpu
 def test_batched_inference_equals_per_utterance_reference_path():
     import funasr_b200 as fb
@@ -65,7 +91,18 @@ def test_batched_inference_equals_per_utterance_reference_path():
     wavs = [0.5 * (2 * torch.rand(n, generator=g) - 1) for n in (16000, 52000, 8123, 160000)]
     with pytest.raises(NotImplementedError):
         model.inference(data_in=wavs, frontend=fe, batch_size=4)  # the reference's behaviour
+    n_fbank = [0]
+    real_forward_packed = fe.forward_packed
+
+    def counting(*a, **k):
+        n_fbank[0] += 1
+        return real_forward_packed(*a, **k)
+
+    fe.forward_packed = counting
     got = inference_batched(model, wavs, frontend=fe, batch_size=4, key=["a", "b", "c", "d"], embed_dtype=torch.float32)
+    fe.forward_packed = real_forward_packed
+    # one fbank launch for the whole batch: the model's own extract_fbank call per utterance (model.py:372) got the known features
+    assert n_fbank[0] == 1, n_fbank
     assert all(c["bypass"] for c in model.calls) and [c["key"] for c in model.calls] == [["a"], ["b"], ["c"], ["d"]]
     for w, (rows, olen) in zip(wavs, got):
         want_rows, want_len = model.inference(data_in=[w], frontend=fe)  # per-utterance path: encoder + adaptor inside
